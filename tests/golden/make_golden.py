@@ -1,0 +1,170 @@
+#!/usr/bin/env python
+"""Generate tests/golden/*.npz by running the REFERENCE's own code in the build container.
+
+Needs /root/reference (read-only mount) and the image's transformers; it therefore runs
+only here, never on the GPU box -- the .npz files it writes are committed.
+
+  python tests/golden/make_golden.py
+
+What is executed:
+  * HF `Data2VecAudioForCTC` (what centralized/finetune_ASRs.py:164 instantiates), eager attention
+  * /root/reference/federated/src/models.py::Data2VecAudioForCTC for STAGE 0/1/2 (imported as is);
+    its Gumbel noise comes from `Tensor.exponential_`, which is patched to replay a seeded
+    sample queue so that the oracle/kernels can be fed the very same noise
+  * /root/reference/federated/src/utils.py:240-249 `average_weights`, exec'd from the sliced source
+    (the module itself cannot be imported: librosa + env-dependent np.load at import)
+Weights come from oracle.data2vec_ref.init_state_dict (seeded, own RNG stream) and are loaded
+into the reference modules with load_state_dict(strict) -- so fixtures only hold outputs.
+"""
+import copy
+import os
+import sys
+from types import SimpleNamespace
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+REF = "/root/reference"
+sys.path.insert(0, os.path.join(REF, "federated", "src"))
+
+from oracle import data2vec_ref as R  # noqa: E402
+from oracle import dacs_ref as D  # noqa: E402
+
+OUT = os.path.dirname(os.path.abspath(__file__))
+torch.set_num_threads(8)
+
+
+def hf_config(cfg):
+    from transformers import Data2VecAudioConfig
+    return Data2VecAudioConfig(**cfg.to_hf_kwargs())
+
+
+def grads_of(model, names):
+    return {n: p.grad.detach().clone() for n, p in model.named_parameters() if n in names and p.grad is not None}
+
+
+def case_plain_ctc(tag, cfg, batch, samples, seed, use_mask):
+    from transformers import Data2VecAudioForCTC
+    sd = R.init_state_dict(cfg, seed=seed, dacs=False)
+    m = Data2VecAudioForCTC(hf_config(cfg))
+    m.load_state_dict(sd, strict=True)
+    m.freeze_feature_encoder()
+    m.train()
+    b = R.synth_batch(cfg, batch, samples, seed=1234 + seed, ragged=use_mask, max_label=12)
+    out = m(input_values=b["input_values"], attention_mask=b["attention_mask"] if use_mask else None,
+            labels=b["labels"], output_hidden_states=True)
+    out.loss.backward()
+    keep = ["lm_head.weight", "lm_head.bias",
+            "data2vec_audio.encoder.layers.0.attention.q_proj.weight",
+            "data2vec_audio.encoder.layers.0.attention.v_proj.bias",
+            "data2vec_audio.encoder.layers.1.feed_forward.intermediate_dense.weight",
+            "data2vec_audio.encoder.layers.1.final_layer_norm.weight",
+            "data2vec_audio.encoder.layer_norm.bias",
+            "data2vec_audio.encoder.pos_conv_embed.layers.0.conv.weight",
+            "data2vec_audio.encoder.pos_conv_embed.layers.1.conv.bias",
+            "data2vec_audio.feature_projection.projection.weight",
+            "data2vec_audio.feature_projection.layer_norm.weight"]
+    g = grads_of(m, keep)
+    gnorm = {n: float(p.grad.norm()) for n, p in m.named_parameters() if p.grad is not None}
+    ids = out.logits.argmax(-1)
+    np.savez_compressed(
+        os.path.join(OUT, f"{tag}.npz"),
+        seed=seed, batch=batch, samples=samples, use_mask=int(use_mask),
+        loss=out.loss.detach().numpy(), logits=out.logits.detach().numpy(), argmax=ids.numpy(),
+        hidden_last=out.hidden_states[-1].detach().numpy(), hidden_first=out.hidden_states[0].detach().numpy(),
+        grad_names=np.array(list(g.keys())), **{"grad:" + k: v.numpy() for k, v in g.items()},
+        gnorm_names=np.array(list(gnorm.keys())), gnorm_values=np.array(list(gnorm.values())),
+    )
+    print(tag, "loss", float(out.loss), "logits", tuple(out.logits.shape))
+
+
+class _ReplayExponential:
+    """Patch Tensor.exponential_ to replay queued Exp(1) samples (models.py:112)."""
+
+    def __init__(self, queue):
+        self.queue = list(queue)
+
+    def __enter__(self):
+        self.orig = torch.Tensor.exponential_
+        q = self.queue
+
+        def fake(t, *a, **k):
+            src = q.pop(0)
+            assert src.shape == t.shape, (src.shape, t.shape)
+            return t.copy_(src)
+
+        torch.Tensor.exponential_ = fake
+        return self
+
+    def __exit__(self, *a):
+        torch.Tensor.exponential_ = self.orig
+
+
+def case_dacs(tag, cfg, batch, samples, seed, stage, toggle_ratio=0, ad_loss="recall"):
+    import models as refmodels  # /root/reference/federated/src/models.py
+    sd = R.init_state_dict(cfg, seed=seed, dacs=True)
+    args = SimpleNamespace(LAMBDA=0.5, TOGGLE_RATIO=toggle_ratio, GS_TAU=1, AD_loss=ad_loss, W_LOSS=None, STAGE=stage)
+    hc = hf_config(cfg)
+    m = refmodels.Data2VecAudioForCTC(hc, args)
+    m.load_state_dict(sd, strict=True)
+    m.config.ctc_zero_infinity = True
+    m.train()
+    b = R.synth_batch(cfg, batch, samples, seed=4321 + seed, ragged=True, max_label=12)
+    T = int(R.conv_out_lengths(cfg, torch.tensor([samples]))[0])
+    shape = (batch, T, cfg.hidden_size, 2)
+    e_lm = torch.empty(shape).exponential_(generator=torch.Generator().manual_seed(1238 + seed))
+    e_ad = torch.empty(shape).exponential_(generator=torch.Generator().manual_seed(2238 + seed))
+    with _ReplayExponential([e_lm, e_ad]):
+        out = m(input_values=b["input_values"], attention_mask=b["attention_mask"], labels=b["labels"],
+                dementia_labels=b["dementia_labels"])
+    out.loss.backward()
+    g = {n: p.grad.detach().clone() for n, p in m.named_parameters()
+         if p.grad is not None and (n.startswith(("arbitrator", "dementia_head", "lm_head")) or
+                                    n.endswith("layers.1.final_layer_norm.weight"))}
+    gnorm = {n: float(p.grad.norm()) for n, p in m.named_parameters() if p.grad is not None}
+    np.savez_compressed(
+        os.path.join(OUT, f"{tag}.npz"),
+        seed=seed, batch=batch, samples=samples, stage=stage, toggle_ratio=toggle_ratio, ad_loss=ad_loss,
+        exp_lm=e_lm.numpy(), exp_ad=e_ad.numpy(),
+        loss=out.loss.detach().numpy(), logits=out.logits.detach().numpy(),
+        grad_names=np.array(list(g.keys())), **{"grad:" + k: v.numpy() for k, v in g.items()},
+        gnorm_names=np.array(list(gnorm.keys())), gnorm_values=np.array(list(gnorm.values())),
+    )
+    print(tag, "stage", stage, "loss", float(out.loss), "trainable-with-grad", len(gnorm))
+
+
+def case_fedavg(tag):
+    src = open(os.path.join(REF, "federated", "src", "utils.py"), encoding="utf-8").read().splitlines()
+    body = "\n".join(src[239:249])  # lines 240-249
+    ns = {"copy": copy, "torch": torch}
+    exec(body, ns)
+    average_weights = ns["average_weights"]
+    out = {}
+    for n_clients in (2, 3, 8):
+        g = torch.Generator().manual_seed(77 + n_clients)
+        ws = [{"a.weight": torch.randn(37, 19, generator=g) * (1 + i), "a.bias": torch.randn(19, generator=g),
+               "b.weight": torch.randn(5, 3, 7, generator=g) * 1e-3} for i in range(n_clients)]
+        avg = average_weights(copy.deepcopy(ws))
+        for k, v in avg.items():
+            out[f"n{n_clients}:{k}"] = v.numpy()
+    np.savez_compressed(os.path.join(OUT, f"{tag}.npz"), **out)
+    print(tag, "ok")
+
+
+def main():
+    cfg = R.ArchConfig.tiny()
+    case_plain_ctc("plain_ctc_masked", cfg, batch=3, samples=8000, seed=0, use_mask=True)
+    case_plain_ctc("plain_ctc_nomask", cfg, batch=2, samples=6000, seed=1, use_mask=False)
+    cfgb = R.ArchConfig.tiny(conv_bias=True)
+    case_plain_ctc("plain_ctc_convbias", cfgb, batch=2, samples=6000, seed=2, use_mask=True)
+    for stage in (0, 1, 2):
+        case_dacs(f"dacs_stage{stage}", cfg, batch=3, samples=8000, seed=10 + stage, stage=stage)
+    case_dacs("dacs_stage2_toggle", cfg, batch=2, samples=6000, seed=20, stage=2, toggle_ratio=0.3)
+    case_dacs("dacs_stage2_f1", cfg, batch=2, samples=6000, seed=21, stage=2, ad_loss="f1")
+    case_fedavg("fedavg")
+
+
+if __name__ == "__main__":
+    main()
