@@ -1,0 +1,270 @@
+/* b200asr -- C ABI of the B200-native client-local ASR update + FedAvg hot path.
+ *
+ * Drop-in boundary.  The reference (JackingChen/Privacy-preserve-Federated-ASR)
+ * is pure Python over torch/ATen + HF transformers; the interface each entry point replaces is the ATen /
+ * transformers call the reference makes on the hot path, cited as <file>:<line> into /root/reference or
+ * `HF:` = transformers/models/data2vec/modeling_data2vec_audio.py.
+ *
+ * Conventions
+ *   - every function returns 0 (B200ASR_OK) or a negative B200ASR_ERR_*; b200asr_last_error() gives the text.
+ *   - plain device pointers + sizes only; the library never allocates or frees user-visible memory.
+ *     Scratch is a caller-provided `workspace` (+ a *_workspace_bytes query where its size is not obvious).
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*); no host synchronisation.
+ *   - `dtype` selects the storage type of activations/weights: B200ASR_F32 or B200ASR_BF16.  Statistics,
+ *     accumulators, losses, CTC state and FedAvg are always fp32.
+ *   - matrices are row-major; `ld*` are element strides.
+ */
+#ifndef B200ASR_H_
+#define B200ASR_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200ASR_OK 0
+#define B200ASR_ERR_BAD_ARG (-1)
+#define B200ASR_ERR_UNSUPPORTED (-2)
+#define B200ASR_ERR_CUDA (-3)
+
+#define B200ASR_F32 0
+#define B200ASR_BF16 1
+
+#define B200ASR_ABI_VERSION 1
+
+/* activation codes */
+#define B200ASR_ACT_NONE 0
+#define B200ASR_ACT_GELU 1
+
+const char* b200asr_last_error(void);
+int b200asr_abi_version(void);
+/* number of kernel launches issued through this library since load (bench.py's gpu_launches) */
+long long b200asr_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * LayerNorm over the last dim (+ optional residual add before, + optional GELU after).
+ * Replaces torch.nn.functional.layer_norm / nn.LayerNorm at HF:70-74 (conv layers: LN(512)+GELU),
+ * HF:160-172 (feature projection), HF:119-126 (pos-conv LN without affine + GELU), HF:381-383,
+ * HF:313-346 (post-LN encoder block).
+ *   s = x (+ res);  y = act(LN(s) * w + b)
+ *   w, b   : fp32 [cols] or NULL (no affine)
+ *   sum_out: NULL or [rows, cols] (dtype) receives s (saved for backward when res != NULL)
+ *   mean, rstd: NULL or fp32 [rows]
+ */
+int b200asr_layernorm_fwd(const void* x, const void* res, const float* w, const float* b, void* y, void* sum_out,
+                          float* mean, float* rstd, int rows, int cols, float eps, int act, int dtype, void* stream);
+/* Backward of the above w.r.t. s (dx) and w, b.  `s` is the pre-norm input.  dw/db: fp32 [cols] or NULL.
+ * workspace: fp32, >= b200asr_layernorm_bwd_workspace_bytes(cols) bytes (only used when dw/db != NULL).
+ * dres_add: NULL or [rows, cols] (dtype) added to dx (fuses the residual-branch gradient sum). */
+size_t b200asr_layernorm_bwd_workspace_bytes(int cols);
+int b200asr_layernorm_bwd(const void* dy, const void* s, const float* w, const float* b, const float* mean,
+                          const float* rstd, const void* dres_add, void* dx, float* dw, float* db, void* workspace,
+                          size_t workspace_bytes, int rows, int cols, int act, int dtype, void* stream);
+
+/* Column sums of a [rows, cols] matrix (bias gradients: what autograd does for nn.Linear.bias).
+ * out fp32 [cols]; workspace >= b200asr_colsum_workspace_bytes(cols). */
+size_t b200asr_colsum_workspace_bytes(int cols);
+int b200asr_colsum(const void* x, float* out, void* workspace, size_t workspace_bytes, int rows, int cols, int ld,
+                   int dtype, void* stream);
+
+/* Zero the frames t >= lengths[b] of x [B, T, cols] in place (HF:369-371 `hidden_states[~mask] = 0`). */
+int b200asr_mask_frames(void* x, const int* lengths, int B, int T, int cols, int dtype, void* stream);
+
+/* dtype conversion / copy helpers used by the host shim for weight shadows: dst[i] = (dtype) src_f32[i]. */
+int b200asr_cast_f32(const float* src, void* dst, long long n, int dst_dtype, void* stream);
+/* dst_f32[i] = (float) src[i] */
+int b200asr_cast_to_f32(const void* src, float* dst, long long n, int src_dtype, void* stream);
+/* x[i] *= host_scale * (*dev_scale)   (dev_scale may be NULL)  -- upstream-gradient scaling, GRL -lambda. */
+int b200asr_scale(void* x, long long n, float host_scale, const float* dev_scale, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Waveform feature extractor layer 0: Conv1d(1 -> C, k, stride) + LayerNorm(C, affine) + GELU, fused.
+ * Replaces HF:51-75 for layer_id 0 (reached from federated/src/models.py:395, finetune_ASRs.py:231).
+ *   x [B, L] fp32 waveform; w fp32 [C, k]; bias fp32 [C] or NULL; ln_w, ln_b fp32 [C]
+ *   y [B, Tout, C] (dtype), channels-last, Tout = (L - k) / stride + 1
+ */
+int b200asr_conv0_ln_gelu_fwd(const float* x, const float* w, const float* bias, const float* ln_w,
+                              const float* ln_b, void* y, int B, int L, int C, int k, int stride, float eps,
+                              int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * General (batched) matrix product with fused epilogue -- every dense contraction of the path:
+ * nn.Linear forward/backward (HF:160-172, 203-346; federated/src/models.py:292-296), conv layers 1-6 as
+ * implicit GEMM over overlapping channels-last windows (HF:57-63), attention products in fp32 mode.
+ *
+ *   C[m, n] = epi( sum_k A(m, k) * B(n, k) )           m < M, n < N, k < K
+ *   A(m, k) = a_kmajor ? A[m*lda + k] : A[k*lda + m]
+ *   B(n, k) = b_kmajor ? B[n*ldb + k] : B[k*ldb + n]
+ *   epi(v)  = v*alpha (+ bias[n]) -> (aux_out = that, if given) -> (GELU if act) (* gelu'(aux_in[m,n]) if
+ *             mul_gelu_grad) (+ residual[m, n])
+ * Two batch dims (batch0 fastest) with element strides per operand; batch counts of 1 for a plain GEMM.
+ * dtype = storage of A and B (both the same).  BF16 runs on tcgen05 tensor cores (TMA -> smem -> UMMA ->
+ * TMEM), F32 runs on FP32 FMA pipes (parity mode; no TF32).  c_dtype = storage of C, residual, aux.
+ * bias is fp32 [N].
+ */
+typedef struct b200asr_gemm_args {
+    const void* A;
+    const void* B;
+    void* C;
+    const float* bias;     /* NULL or [N] */
+    const void* residual;  /* NULL or [M, N] with ldc / batch strides of C */
+    void* aux_out;         /* NULL or [M, N]: pre-activation copy (ldc, C strides) */
+    const void* aux_in;    /* NULL or [M, N]: pre-activation for mul_gelu_grad (ldc, C strides) */
+    int M, N, K;
+    int lda, ldb, ldc;
+    int a_kmajor, b_kmajor;
+    int act;            /* B200ASR_ACT_* */
+    int mul_gelu_grad;  /* 0/1 */
+    float alpha;
+    int batch0, batch1;
+    long long sa0, sa1, sb0, sb1, sc0, sc1; /* element strides of the batch dims */
+    int dtype, c_dtype;
+} b200asr_gemm_args;
+int b200asr_gemm(const b200asr_gemm_args* args, void* stream);
+
+/* test hook: run b200asr_gemm on a forced back end (0 = fp32 FMA pipes, 1 = tcgen05 tensor cores). */
+int b200asr_gemm_backend(const b200asr_gemm_args* args, int backend, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Row softmax with key-length masking, in place on scores [B, H, Tq, ldk] (HF:189-197 eager attention).
+ * Keys k >= klen[b] get probability 0 (klen NULL = all valid).  Columns in [Tk, ldk) are zero-filled.
+ * lse: NULL or fp32 [B, H, Tq] = log-sum-exp of each row. */
+int b200asr_softmax_rows(void* s, const int* klen, float* lse, int B, int H, int Tq, int Tk, int ldk, int dtype,
+                         void* stream);
+/* Softmax backward in place: dp <- P * (dP - rowsum(dP * P)).  If lse != NULL, `p` holds the scaled logits S on
+ * entry and is first overwritten with P = exp(S - lse) (keys >= klen[b] -> 0). */
+int b200asr_softmax_rows_bwd(void* p, void* dp, const float* lse, const int* klen, int B, int H, int Tq, int Tk,
+                             int ldk, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Multi-head self-attention, replaces Data2VecAudioAttention.forward's bmm -> softmax -> bmm
+ * (HF:189-197 eager path == transformers 4.17).
+ *   qkv [B, T, 3, H, dh] packed projections (q NOT pre-scaled; `scale` is applied to the logits)
+ *   out [B, T, H*dh]; lse fp32 [B, H, T] (log-sum-exp of the scaled logits, saved for backward)
+ *   klen int32 [B] or NULL: number of valid key frames per utterance.
+ *   workspace >= b200asr_mha_fwd_workspace_bytes(...)
+ */
+size_t b200asr_mha_fwd_workspace_bytes(int B, int T, int H, int dh, int dtype);
+int b200asr_mha_fwd(const void* qkv, void* out, float* lse, const int* klen, void* workspace, size_t workspace_bytes,
+                    int B, int T, int H, int dh, float scale, int dtype, void* stream);
+/* dqkv [B, T, 3, H, dh] (fully written).  workspace >= b200asr_mha_bwd_workspace_bytes(...). */
+size_t b200asr_mha_bwd_workspace_bytes(int B, int T, int H, int dh, int dtype);
+int b200asr_mha_bwd(const void* qkv, const void* out, const void* dout, const float* lse, const int* klen,
+                    void* dqkv, void* workspace, size_t workspace_bytes, int B, int T, int H, int dh, float scale,
+                    int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Grouped positional convolution (HF:89-128): y[b,t,g*Cg+o] = bias + sum_{j,i} W[g*Cg+o, i, j] *
+ * x[b, t+j-k/2, g*Cg+i]  (zero padding; for even k the reference drops the last frame, which equals
+ * computing only t < T).  Channels-last x, y [B, T, C] (dtype).
+ * Weights are consumed in a packed layout produced once per weight update by b200asr_posconv_pack_weight
+ * from the HF layout w [C, Cg, k] (dtype): w_fwd [groups][k][Cg in][Cg out], w_bwd [groups][k][Cg out][Cg in].
+ */
+int b200asr_posconv_pack_weight(const void* w, void* w_fwd, void* w_bwd, int C, int groups, int k, int dtype,
+                                void* stream);
+int b200asr_posconv_fwd(const void* x, const void* w_fwd, const float* bias, void* y, int B, int T, int C, int groups,
+                        int k, int dtype, void* stream);
+/* dx [B,T,C] (dtype) and dw fp32 [C, Cg, k] (HF layout; overwritten); dbias via b200asr_colsum.  Either output
+ * may be NULL. */
+int b200asr_posconv_bwd(const void* x, const void* w_bwd, const void* dy, void* dx, float* dw, int B, int T, int C,
+                        int groups, int k, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * CTC: log_softmax(fp32) + alpha/beta recursions + gradient w.r.t. the logits, one launch for `n_heads`
+ * logit tensors sharing targets.  Replaces nn.functional.log_softmax + nn.functional.ctc_loss at
+ * federated/src/models.py:498-533, centralized/trainer_data2vec_2st.py:384-408, HF:897-908.
+ *   logits [n_heads, B, T, V] (dtype); targets int32 flat (concatenated, as `labels.masked_select`);
+ *   tgt_off/tgt_len/in_len int32 [B]; loss fp32 [n_heads, B] = -log p(target) per utterance (inf -> 0
+ *   when zero_infinity); grad (dtype) [n_heads, B, T, V] = grad_scale[h, b] * d loss[h, b] / d logits, or NULL
+ *   (forward only); grad_scale fp32 [n_heads, B] or NULL (= 1: reduction "sum").
+ *   workspace >= b200asr_ctc_workspace_bytes(...).
+ */
+size_t b200asr_ctc_workspace_bytes(int n_heads, int B, int T, int max_tgt_len);
+int b200asr_ctc_fwd_bwd(const void* logits, const int* targets, const int* tgt_off, const int* tgt_len,
+                        const int* in_len, const float* grad_scale, float* loss, void* grad, void* workspace,
+                        size_t workspace_bytes,
+                        int n_heads, int B, int T, int V, int max_tgt_len, int blank, int zero_infinity, int dtype,
+                        void* stream);
+
+/* Greedy decode (finetune_ASRs.py:113-122 `map_to_result`, update.py:162-178): ids = argmax(logits, -1);
+ * out_ids int32 [B, T] raw argmax; collapsed int32 [B, T] (repeat-collapsed, blank dropped, padded with -1);
+ * collapsed_len int32 [B].  in_len NULL = all T frames. */
+int b200asr_greedy_decode(const void* logits, const int* in_len, int* out_ids, int* collapsed, int* collapsed_len,
+                          int B, int T, int V, int blank, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * DACS toggling network, fused: score split + TOGGLE_RATIO lerp + Gumbel noise + softmax(2)/tau + hard
+ * straight-through mask + mask*hidden for both branches.  Replaces federated/src/models.py:428-455 +
+ * gumbel_softmax :75-129 (centralized/trainer_data2vec_2st.py:314-341, Models.py:76-130).
+ *   scores [M, 4d] = arbitrator(h); h [M, d]
+ *   noise_lm / noise_ad: fp32 [M, d, 2] Gumbel samples g = -log(Exp(1)) or NULL -> drawn in-kernel (Philox,
+ *   seed/offset).  Outputs (dtype): lm_masked, ad_masked [M, d]; soft_lm, soft_ad [M, d] = y_soft[...,0]
+ *   (saved for backward); lm_mask, ad_mask [M, d] in {0,1} (optional, may be NULL).
+ */
+int b200asr_dacs_mask_fwd(const void* scores, const void* h, const float* noise_lm, const float* noise_ad,
+                          void* lm_masked, void* ad_masked, void* soft_lm, void* soft_ad, void* lm_mask,
+                          void* ad_mask, long long M, int d, float tau, float toggle_ratio,
+                          unsigned long long seed, unsigned long long offset, int dtype, void* stream);
+/* Straight-through backward: d_scores [M, 4d] from d_lm_masked, d_ad_masked; dh [M, d] or NULL. */
+int b200asr_dacs_mask_bwd(const void* d_lm_masked, const void* d_ad_masked, const void* h, const void* soft_lm,
+                          const void* soft_ad, const void* lm_mask, const void* ad_mask, void* d_scores, void* dh,
+                          long long M, int d, float tau, float toggle_ratio, int dtype, void* stream);
+
+/* Mean over the time axis of per-frame AD logits (models.py:468-476): x [B, T, C] -> out fp32 [B, C]
+ * (mean over all T frames, as the reference does -- padded frames included). */
+int b200asr_mean_time_fwd(const void* x, float* out, int B, int T, int C, int dtype, void* stream);
+/* dx[b,t,c] = dout[b,c] * scale / T */
+int b200asr_mean_time_bwd(const float* dout, void* dx, int B, int T, int C, float scale, int dtype, void* stream);
+
+/* RecallLoss / CrossEntropy on [B, 2] mean AD logits (models.py:187-260, :535-541).
+ * kind: 0 recall, 1 prec, 2 f1, 3 recall_ori, 4 prec_ori, 5 cel.  w fp32 host [C] (normalised inside).
+ * loss fp32 [1]; dlogits fp32 [B, C] = d loss / d logits (NULL = forward only). */
+int b200asr_ad_loss(const float* logits, const long long* target, float* loss, float* dlogits, int B, int C,
+                    int kind, const float* w_host, void* stream);
+
+/* CosFace / AM-softmax diversity term without the N x N gather (models.py:131-185, call :592-607):
+ * rows of x1 [n, d] carry label 0, rows of x2 [n, d] label 1, fc_w fp32 [2, d] (not normalised, as the
+ * reference's no-op loop leaves it).  loss fp32 [1] (mean over 2n rows).  dx1/dx2 (dtype) = d loss / dx * gscale
+ * or NULL.  workspace: fp32 >= 2n floats. */
+int b200asr_cosface_fwd_bwd(const void* x1, const void* x2, const float* fc_w, float* loss, void* dx1, void* dx2,
+                            void* workspace, size_t workspace_bytes, long long n, int d, float s, float m,
+                            int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * FedAvg (federated/src/utils.py:240-249 `average_weights`), flat fp32 parameter buffers.
+ *   out[i] = (((in0[i] + in1[i]) + in2[i]) + ...) / K      when weights == NULL  (bit-exact with the
+ *            reference's left-to-right sum then torch.div)
+ *   out[i] = sum_j weights[j] * in_j[i]                     otherwise
+ * inputs: HOST array of K device pointers (K <= 16); weights: HOST array or NULL.  out may alias inputs[0].
+ */
+int b200asr_fedavg_scale_accum(const float* const* inputs, const float* weights, float* out, int K, long long n,
+                               void* stream);
+/* One rank's share of an N-rank FedAvg before the sum all-reduce: buf[i] *= w  (in place). */
+int b200asr_fedavg_prescale(float* buf, float w, long long n, void* stream);
+/* Fused multi-GPU FedAvg over NVLink peer memory: every rank passes the HOST array of the `world` ranks'
+ * device pointers to the same-sized flat buffer (peer-mapped, e.g. CUDA IPC), its own rank, and per-rank
+ * weights (NULL = uniform 1/world).  Rank r reduces slice r of every peer (scale-accumulate straight from
+ * peer memory) and writes the result back into every peer's slice.  Caller brackets with cross-rank barriers. */
+int b200asr_fedavg_peer_reduce(float* const* peer_bufs, const float* weights, int world, int rank, long long n,
+                               void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Fused AdamW on flat fp32 buffers (HF Trainer "adamw_hf" semantics = transformers.AdamW with
+ * correct_bias=True, configured at centralized/finetune_ASRs.py:202-220, federated/src/update.py:657-678):
+ *   g = grad * clip_coef,  clip_coef = min(1, max_norm / (sqrt(*gnorm_sq) + 1e-6)) (gnorm_sq NULL -> 1)
+ *   m = b1 m + (1-b1) g ; v = b2 v + (1-b2) g^2 ; p -= lr * sqrt(1-b2^t)/(1-b1^t) * m / (sqrt(v) + eps)
+ *   p -= lr * wd * p       (decoupled, applied after the Adam update as transformers.AdamW does)
+ * shadow: NULL or bf16 [n] refreshed with the new p (weight shadow for the tensor-core GEMMs).
+ */
+int b200asr_adamw_step(float* p, const float* grad, float* m, float* v, void* shadow_bf16, long long n, float lr,
+                       float beta1, float beta2, float eps, float weight_decay, int step, const float* gnorm_sq,
+                       float max_norm, void* stream);
+/* out[0] += sum(x^2)  (out must be zeroed by the caller for a fresh norm) */
+int b200asr_sumsq(const float* x, long long n, float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ASR_H_ */

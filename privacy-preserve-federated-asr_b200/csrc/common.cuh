@@ -1,0 +1,121 @@
+// Shared device/host helpers for the b200asr sm_100a kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <math.h>
+
+#include "../../include/b200asr.h"
+
+namespace b200asr {
+
+// ---- error plumbing (no exceptions cross the C boundary) -------------------
+void set_error(const char* fmt, ...);
+int check_launch(const char* what);  // cudaGetLastError -> status
+
+#define B200_REQUIRE(cond, ...)                       \
+    do {                                              \
+        if (!(cond)) {                                \
+            ::b200asr::set_error(__VA_ARGS__);        \
+            return B200ASR_ERR_BAD_ARG;               \
+        }                                             \
+    } while (0)
+
+static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+static inline long long ceil_div_ll(long long a, long long b) { return (a + b - 1) / b; }
+
+int num_sms();
+
+// ---- dtype helpers -----------------------------------------------------------
+template <typename T> __device__ __forceinline__ float to_f(T v);
+template <> __device__ __forceinline__ float to_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+// 16-byte vector of T (4 floats or 8 bf16) loaded/stored as one transaction
+template <typename T> struct Vec16 {
+    static constexpr int N = 16 / sizeof(T);
+    uint4 raw;
+    __device__ __forceinline__ void load(const T* p) { raw = *reinterpret_cast<const uint4*>(p); }
+    __device__ __forceinline__ void store(T* p) const { *reinterpret_cast<uint4*>(p) = raw; }
+    __device__ __forceinline__ void unpack(float* f) const;
+    __device__ __forceinline__ void pack(const float* f);
+};
+template <> __device__ __forceinline__ void Vec16<float>::unpack(float* f) const {
+    f[0] = __uint_as_float(raw.x); f[1] = __uint_as_float(raw.y);
+    f[2] = __uint_as_float(raw.z); f[3] = __uint_as_float(raw.w);
+}
+template <> __device__ __forceinline__ void Vec16<float>::pack(const float* f) {
+    raw.x = __float_as_uint(f[0]); raw.y = __float_as_uint(f[1]);
+    raw.z = __float_as_uint(f[2]); raw.w = __float_as_uint(f[3]);
+}
+__device__ __forceinline__ void bf2_unpack(uint32_t u, float& a, float& b) {
+    a = __uint_as_float(u << 16);
+    b = __uint_as_float(u & 0xffff0000u);
+}
+__device__ __forceinline__ uint32_t bf2_pack(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+template <> __device__ __forceinline__ void Vec16<__nv_bfloat16>::unpack(float* f) const {
+    bf2_unpack(raw.x, f[0], f[1]); bf2_unpack(raw.y, f[2], f[3]);
+    bf2_unpack(raw.z, f[4], f[5]); bf2_unpack(raw.w, f[6], f[7]);
+}
+template <> __device__ __forceinline__ void Vec16<__nv_bfloat16>::pack(const float* f) {
+    raw.x = bf2_pack(f[0], f[1]); raw.y = bf2_pack(f[2], f[3]);
+    raw.z = bf2_pack(f[4], f[5]); raw.w = bf2_pack(f[6], f[7]);
+}
+
+// ---- math --------------------------------------------------------------------
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+    const float pdf = 0.39894228040143267794f * __expf(-0.5f * x * x);
+    return cdf + x * pdf;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// block-wide sum for blockDim.x <= 1024; `red` is >= 32 floats of shared memory
+__device__ __forceinline__ float block_sum(float v, float* red) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) red[wid] = v;
+    __syncthreads();
+    float r = (lane < nw) ? red[lane] : 0.f;
+    r = warp_sum(r);
+    return r;
+}
+__device__ __forceinline__ float block_max(float v, float* red) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = warp_max(v);
+    __syncthreads();
+    if (lane == 0) red[wid] = v;
+    __syncthreads();
+    float r = (lane < nw) ? red[lane] : -INFINITY;
+    r = warp_max(r);
+    return r;
+}
+
+#define B200_DISPATCH_DTYPE(dtype, ...)                                        \
+    do {                                                                       \
+        if ((dtype) == B200ASR_F32) { using T = float; __VA_ARGS__ }           \
+        else if ((dtype) == B200ASR_BF16) { using T = __nv_bfloat16; __VA_ARGS__ } \
+        else { ::b200asr::set_error("unsupported dtype %d", (int)(dtype)); return B200ASR_ERR_BAD_ARG; } \
+    } while (0)
+
+}  // namespace b200asr

@@ -1,0 +1,242 @@
+// FedAvg on flat fp32 parameter buffers (federated/src/utils.py:240-249) and the fused AdamW step that shares
+// the flat layout.  HBM-bound streaming kernels: 128-bit loads, grid = multiple of the SM count, one pass.
+#include "common.cuh"
+
+namespace b200asr {
+
+constexpr int FEDAVG_MAX_K = 16;
+struct FedPtrs {
+    const float* in[FEDAVG_MAX_K];
+    float w[FEDAVG_MAX_K];
+};
+struct PeerPtrs {
+    float* buf[FEDAVG_MAX_K];
+    float w[FEDAVG_MAX_K];
+};
+
+__device__ __forceinline__ float4 ld_stream(const float* p) {
+    float4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+
+// uniform = 1: ((in0 + in1) + in2 ...) / K  (bit-exact with the reference's sequential sum then true division)
+template <int UNIFORM>
+__global__ void __launch_bounds__(256) fedavg_kernel(const FedPtrs p, float* __restrict__ out, int K, long long n) {
+    const long long nvec = n / 4;
+    const float kf = (float)K;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+        float4 acc = ld_stream(p.in[0] + 4 * i);
+        if (!UNIFORM) { acc.x *= p.w[0]; acc.y *= p.w[0]; acc.z *= p.w[0]; acc.w *= p.w[0]; }
+        for (int j = 1; j < K; ++j) {
+            const float4 v = ld_stream(p.in[j] + 4 * i);
+            if (UNIFORM) { acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w; }
+            else {
+                acc.x = fmaf(p.w[j], v.x, acc.x); acc.y = fmaf(p.w[j], v.y, acc.y);
+                acc.z = fmaf(p.w[j], v.z, acc.z); acc.w = fmaf(p.w[j], v.w, acc.w);
+            }
+        }
+        if (UNIFORM) { acc.x = __fdiv_rn(acc.x, kf); acc.y = __fdiv_rn(acc.y, kf); acc.z = __fdiv_rn(acc.z, kf); acc.w = __fdiv_rn(acc.w, kf); }
+        *reinterpret_cast<float4*>(out + 4 * i) = acc;
+    }
+    // tail (n % 4 elements)
+    const long long t0 = nvec * 4;
+    for (long long i = t0 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        float acc = UNIFORM ? p.in[0][i] : p.w[0] * p.in[0][i];
+        for (int j = 1; j < K; ++j) acc = UNIFORM ? acc + p.in[j][i] : fmaf(p.w[j], p.in[j][i], acc);
+        out[i] = UNIFORM ? __fdiv_rn(acc, kf) : acc;
+    }
+}
+
+__global__ void __launch_bounds__(256) prescale_kernel(float* __restrict__ x, float w, long long n) {
+    const long long nvec = n / 4;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+        float4 v = *reinterpret_cast<float4*>(x + 4 * i);
+        v.x *= w; v.y *= w; v.z *= w; v.w *= w;
+        *reinterpret_cast<float4*>(x + 4 * i) = v;
+    }
+    for (long long i = nvec * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        x[i] *= w;
+}
+
+// Rank `rank` owns slice [lo, hi): reads that slice from every peer (NVLink loads), reduces, writes the result
+// into every peer's slice (NVLink stores).  One kernel = reduce-scatter + all-gather with the scaling fused in.
+template <int UNIFORM>
+__global__ void __launch_bounds__(256) fedavg_peer_kernel(const PeerPtrs p, int world, long long lo, long long hi) {
+    const float kf = (float)world;
+    const long long nvec = (hi - lo) / 4;  // lo, hi are multiples of 4 except the global tail handled by the last rank
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+        const long long e = lo + 4 * i;
+        float4 acc = *reinterpret_cast<const float4*>(p.buf[0] + e);
+        if (!UNIFORM) { acc.x *= p.w[0]; acc.y *= p.w[0]; acc.z *= p.w[0]; acc.w *= p.w[0]; }
+        for (int j = 1; j < world; ++j) {
+            const float4 v = *reinterpret_cast<const float4*>(p.buf[j] + e);
+            if (UNIFORM) { acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w; }
+            else {
+                acc.x = fmaf(p.w[j], v.x, acc.x); acc.y = fmaf(p.w[j], v.y, acc.y);
+                acc.z = fmaf(p.w[j], v.z, acc.z); acc.w = fmaf(p.w[j], v.w, acc.w);
+            }
+        }
+        if (UNIFORM) { acc.x = __fdiv_rn(acc.x, kf); acc.y = __fdiv_rn(acc.y, kf); acc.z = __fdiv_rn(acc.z, kf); acc.w = __fdiv_rn(acc.w, kf); }
+        for (int j = 0; j < world; ++j) *reinterpret_cast<float4*>(p.buf[j] + e) = acc;
+    }
+    for (long long e = lo + nvec * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; e < hi; e += (long long)gridDim.x * blockDim.x) {
+        float acc = UNIFORM ? p.buf[0][e] : p.w[0] * p.buf[0][e];
+        for (int j = 1; j < world; ++j) acc = UNIFORM ? acc + p.buf[j][e] : fmaf(p.w[j], p.buf[j][e], acc);
+        if (UNIFORM) acc = __fdiv_rn(acc, kf);
+        for (int j = 0; j < world; ++j) p.buf[j][e] = acc;
+    }
+}
+
+// ---------------------------------------------------------------- AdamW (transformers.AdamW, correct_bias=True)
+__global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                                    float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, long long n,
+                                                    float lr, float b1, float b2, float eps, float wd, float step_size,
+                                                    const float* __restrict__ gnorm_sq, float max_norm) {
+    float clip = 1.f;
+    if (gnorm_sq) {
+        const float nrm = sqrtf(*gnorm_sq);
+        clip = fminf(1.f, max_norm / (nrm + 1e-6f));  // torch.nn.utils.clip_grad_norm_
+    }
+    const long long nvec = n / 4;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+        float4 pv = *reinterpret_cast<float4*>(p + 4 * i);
+        const float4 gv = *reinterpret_cast<const float4*>(g + 4 * i);
+        float4 mv = *reinterpret_cast<float4*>(m + 4 * i);
+        float4 vv = *reinterpret_cast<float4*>(v + 4 * i);
+        float pa[4] = {pv.x, pv.y, pv.z, pv.w};
+        const float ga[4] = {gv.x, gv.y, gv.z, gv.w};
+        float ma[4] = {mv.x, mv.y, mv.z, mv.w};
+        float va[4] = {vv.x, vv.y, vv.z, vv.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float gg = ga[j] * clip;
+            ma[j] = b1 * ma[j] + (1.f - b1) * gg;
+            va[j] = b2 * va[j] + (1.f - b2) * gg * gg;
+            pa[j] -= step_size * ma[j] / (sqrtf(va[j]) + eps);
+            pa[j] -= lr * wd * pa[j];
+        }
+        *reinterpret_cast<float4*>(p + 4 * i) = make_float4(pa[0], pa[1], pa[2], pa[3]);
+        *reinterpret_cast<float4*>(m + 4 * i) = make_float4(ma[0], ma[1], ma[2], ma[3]);
+        *reinterpret_cast<float4*>(v + 4 * i) = make_float4(va[0], va[1], va[2], va[3]);
+        if (shadow) {
+            uint2 o;
+            o.x = bf2_pack(pa[0], pa[1]);
+            o.y = bf2_pack(pa[2], pa[3]);
+            *reinterpret_cast<uint2*>(shadow + 4 * i) = o;
+        }
+    }
+    for (long long i = nvec * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float gg = g[i] * clip;
+        const float mm = b1 * m[i] + (1.f - b1) * gg;
+        const float vv = b2 * v[i] + (1.f - b2) * gg * gg;
+        float pp = p[i] - step_size * mm / (sqrtf(vv) + eps);
+        pp -= lr * wd * pp;
+        p[i] = pp; m[i] = mm; v[i] = vv;
+        if (shadow) shadow[i] = __float2bfloat16_rn(pp);
+    }
+}
+
+__global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ x, long long n, float* __restrict__ out) {
+    __shared__ float red[32];
+    float s = 0.f;
+    const long long nvec = n / 4;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+        const float4 v = *reinterpret_cast<const float4*>(x + 4 * i);
+        s += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+    for (long long i = nvec * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        s += x[i] * x[i];
+    s = block_sum(s, red);
+    if (threadIdx.x == 0) atomicAdd(out, s);
+}
+
+static int stream_grid(long long n) {
+    long long g = (n / 4 + 255) / 256;
+    const long long cap = (long long)num_sms() * 8;
+    return (int)(g < cap ? (g < 1 ? 1 : g) : cap);
+}
+
+}  // namespace b200asr
+
+using namespace b200asr;
+
+extern "C" {
+
+int b200asr_fedavg_scale_accum(const float* const* inputs, const float* weights, float* out, int K, long long n,
+                               void* stream) {
+    B200_REQUIRE(inputs && out, "fedavg: null pointer");
+    B200_REQUIRE(K >= 1 && K <= FEDAVG_MAX_K, "fedavg: K=%d out of range [1,%d]", K, FEDAVG_MAX_K);
+    if (n <= 0) return B200ASR_OK;
+    FedPtrs p;
+    for (int j = 0; j < FEDAVG_MAX_K; ++j) {
+        p.in[j] = j < K ? inputs[j] : nullptr;
+        p.w[j] = (j < K && weights) ? weights[j] : 0.f;
+        if (j < K) {
+            B200_REQUIRE(inputs[j], "fedavg: null client buffer %d", j);
+            B200_REQUIRE(((uintptr_t)inputs[j] & 15) == 0, "fedavg: client buffer %d not 16-byte aligned", j);
+        }
+    }
+    B200_REQUIRE(((uintptr_t)out & 15) == 0, "fedavg: out not 16-byte aligned");
+    if (weights) fedavg_kernel<0><<<stream_grid(n), 256, 0, as_stream(stream)>>>(p, out, K, n);
+    else fedavg_kernel<1><<<stream_grid(n), 256, 0, as_stream(stream)>>>(p, out, K, n);
+    return check_launch("fedavg_scale_accum");
+}
+
+int b200asr_fedavg_prescale(float* buf, float w, long long n, void* stream) {
+    B200_REQUIRE(buf && ((uintptr_t)buf & 15) == 0, "fedavg_prescale: bad pointer");
+    if (n <= 0) return B200ASR_OK;
+    prescale_kernel<<<stream_grid(n), 256, 0, as_stream(stream)>>>(buf, w, n);
+    return check_launch("fedavg_prescale");
+}
+
+int b200asr_fedavg_peer_reduce(float* const* peer_bufs, const float* weights, int world, int rank, long long n,
+                               void* stream) {
+    B200_REQUIRE(peer_bufs, "fedavg_peer_reduce: null pointer");
+    B200_REQUIRE(world >= 1 && world <= FEDAVG_MAX_K && rank >= 0 && rank < world, "fedavg_peer_reduce: bad world/rank");
+    if (n <= 0) return B200ASR_OK;
+    PeerPtrs p;
+    for (int j = 0; j < FEDAVG_MAX_K; ++j) {
+        p.buf[j] = j < world ? peer_bufs[j] : nullptr;
+        p.w[j] = (j < world && weights) ? weights[j] : 0.f;
+        if (j < world) B200_REQUIRE(peer_bufs[j] && ((uintptr_t)peer_bufs[j] & 15) == 0, "fedavg_peer_reduce: bad peer %d", j);
+    }
+    // slice boundaries on multiples of 4 elements (16 B); the last rank takes the remainder
+    const long long per = ((n / world) / 4) * 4;
+    const long long lo = per * rank;
+    const long long hi = (rank == world - 1) ? n : per * (rank + 1);
+    if (hi <= lo) return B200ASR_OK;
+    if (weights) fedavg_peer_kernel<0><<<stream_grid(hi - lo), 256, 0, as_stream(stream)>>>(p, world, lo, hi);
+    else fedavg_peer_kernel<1><<<stream_grid(hi - lo), 256, 0, as_stream(stream)>>>(p, world, lo, hi);
+    return check_launch("fedavg_peer_reduce");
+}
+
+int b200asr_adamw_step(float* p, const float* grad, float* m, float* v, void* shadow_bf16, long long n, float lr, float beta1,
+                       float beta2, float eps, float weight_decay, int step, const float* gnorm_sq, float max_norm,
+                       void* stream) {
+    B200_REQUIRE(p && grad && m && v, "adamw: null pointer");
+    B200_REQUIRE(step >= 1, "adamw: step must be >= 1");
+    B200_REQUIRE((((uintptr_t)p | (uintptr_t)grad | (uintptr_t)m | (uintptr_t)v) & 15) == 0, "adamw: buffers must be 16-byte aligned");
+    B200_REQUIRE(!shadow_bf16 || ((uintptr_t)shadow_bf16 & 7) == 0, "adamw: shadow must be 8-byte aligned");
+    if (n <= 0) return B200ASR_OK;
+    const double bc1 = 1.0 - pow((double)beta1, (double)step);
+    const double bc2 = 1.0 - pow((double)beta2, (double)step);
+    const float step_size = (float)((double)lr * sqrt(bc2) / bc1);
+    adamw_kernel<<<stream_grid(n), 256, 0, as_stream(stream)>>>(p, grad, m, v, (__nv_bfloat16*)shadow_bf16, n, lr, beta1, beta2,
+                                                                eps, weight_decay, step_size, gnorm_sq, max_norm);
+    return check_launch("adamw_step");
+}
+
+int b200asr_sumsq(const float* x, long long n, float* out, void* stream) {
+    B200_REQUIRE(x && out && ((uintptr_t)x & 15) == 0, "sumsq: bad pointer");
+    if (n <= 0) return B200ASR_OK;
+    long long g = (n / 4 + 255) / 256;
+    const long long cap = (long long)num_sms() * 4;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    sumsq_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(x, n, out);
+    return check_launch("sumsq");
+}
+
+}  // extern "C"

@@ -1,0 +1,17 @@
+// Internal: the two GEMM back ends behind b200asr_gemm.
+#pragma once
+#include <cuda_runtime.h>
+#include "../../include/b200asr.h"
+
+namespace b200asr {
+
+// fp32 FMA pipes (parity mode; HBM-bound skinny / unaligned products)
+int gemm_simt_launch(const b200asr_gemm_args& a, cudaStream_t st);
+// tcgen05 tensor cores (bf16 operands, fp32 accumulate in TMEM)
+bool gemm_tc_eligible(const b200asr_gemm_args& a, const char** why);
+int gemm_tc_launch(const b200asr_gemm_args& a, cudaStream_t st);
+
+// internal convenience used by the composed attention path
+int gemm_dispatch(const b200asr_gemm_args& a, cudaStream_t st);
+
+}  // namespace b200asr

@@ -1,0 +1,496 @@
+// bf16 GEMM on the 5th-generation tensor cores: TMA (128B-swizzled tiles) -> shared memory ring ->
+// tcgen05.mma (single issuing thread, fp32 accumulators in TMEM, double buffered) -> tcgen05.ld epilogue.
+// Persistent, warp specialised: warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2..5 =
+// epilogue (one TMEM lane quarter each).  Either operand may be K-major or MN-major in memory, so that
+// nn.Linear forward (NT), dgrad (NN) and wgrad (TN) all run without materialised transposes.
+#include <cuda.h>
+
+#include <mutex>
+
+#include "common.cuh"
+#include "gemm.h"
+
+namespace b200asr {
+
+namespace tc {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;   // 64 bf16 = 128 bytes = one swizzle-128B row
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 192;
+constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
+
+template <int BN> struct Cfg {
+    static constexpr int B_STAGE_BYTES = BN * BLOCK_K * 2;
+    static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+    static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+    static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;  // two accumulator buffers
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+struct Params {
+    void* C;
+    const float* bias;
+    const void* residual;
+    void* aux_out;
+    const void* aux_in;
+    int M, N, K;
+    int ldc;
+    int a_mn, b_mn;  // 1 = MN-major operand
+    int act, mul_gelu_grad;
+    float alpha;
+    int batch0, batch1;
+    long long sc0, sc1;
+    int tiles_m, tiles_n;
+    long long num_tiles;
+};
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra WAIT_DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "WAIT_DONE:\n\t"
+        "}" ::"r"(bar), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2,
+                                            int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_dst, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// 32 lanes x 32 consecutive fp32 columns: thread i of the warp gets TMEM lane (base_lane + i)
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// UMMA shared-memory descriptor, 128B swizzle (cute::UMMA::SmemDescriptor layout):
+//   [0,14) start>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 | [61,64) layout (2 = SWIZZLE_128B)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3fff);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+template <typename TC> __device__ __forceinline__ void store_row_chunk(TC* dst, const float* v, int ncols_valid, bool vec_ok);
+template <> __device__ __forceinline__ void store_row_chunk<float>(float* dst, const float* v, int n, bool vec_ok) {
+    if (n >= 32 && vec_ok) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (j < n) dst[j] = v[j];
+    }
+}
+template <> __device__ __forceinline__ void store_row_chunk<__nv_bfloat16>(__nv_bfloat16* dst, const float* v, int n, bool vec_ok) {
+    if (n >= 32 && vec_ok) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+            uint4 o;
+            o.x = bf2_pack(v[j], v[j + 1]);
+            o.y = bf2_pack(v[j + 2], v[j + 3]);
+            o.z = bf2_pack(v[j + 4], v[j + 5]);
+            o.w = bf2_pack(v[j + 6], v[j + 7]);
+            *reinterpret_cast<uint4*>(dst + j) = o;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (j < n) dst[j] = __float2bfloat16_rn(v[j]);
+    }
+}
+template <typename TC> __device__ __forceinline__ void load_row_chunk(const TC* src, float* v, int n, bool vec_ok);
+template <> __device__ __forceinline__ void load_row_chunk<float>(const float* src, float* v, int n, bool vec_ok) {
+    if (n >= 32 && vec_ok) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+            const float4 t = *reinterpret_cast<const float4*>(src + j);
+            v[j] = t.x; v[j + 1] = t.y; v[j + 2] = t.z; v[j + 3] = t.w;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = (j < n) ? src[j] : 0.f;
+    }
+}
+template <> __device__ __forceinline__ void load_row_chunk<__nv_bfloat16>(const __nv_bfloat16* src, float* v, int n, bool vec_ok) {
+    if (n >= 32 && vec_ok) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+            const uint4 t = *reinterpret_cast<const uint4*>(src + j);
+            bf2_unpack(t.x, v[j], v[j + 1]);
+            bf2_unpack(t.y, v[j + 2], v[j + 3]);
+            bf2_unpack(t.z, v[j + 4], v[j + 5]);
+            bf2_unpack(t.w, v[j + 6], v[j + 7]);
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = (j < n) ? __bfloat162float(src[j]) : 0.f;
+    }
+}
+
+template <int BN, typename TC>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const Params p) {
+    using C_ = Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    // 1024-byte alignment: the 128B swizzle pattern is a function of the absolute shared address
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars = smem_base + C_::STAGES * C_::STAGE_BYTES;
+    // barrier layout (8 bytes each): full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2], then tmem ptr
+    auto full_bar = [&](int s) { return bars + 8u * s; };
+    auto empty_bar = [&](int s) { return bars + 8u * (C_::STAGES + s); };
+    auto tfull_bar = [&](int s) { return bars + 8u * (2 * C_::STAGES + s); };
+    auto tempty_bar = [&](int s) { return bars + 8u * (2 * C_::STAGES + 2 + s); };
+    const uint32_t tmem_slot = bars + 8u * (2 * C_::STAGES + 4);
+    uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+    volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(smem_gen + C_::STAGES * C_::STAGE_BYTES + 8 * (2 * C_::STAGES + 4));
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < C_::STAGES; ++s) {
+            mbar_init(full_bar(s), 1);
+            mbar_init(empty_bar(s), 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(tfull_bar(s), 1);
+            mbar_init(tempty_bar(s), 4);  // one arrival per epilogue warp
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, C_::TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_gen;
+
+    const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+    const long long tiles_per_batch = (long long)p.tiles_m * p.tiles_n;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (long long tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+                const int z = (int)(tile / tiles_per_batch);
+                const int rem = (int)(tile % tiles_per_batch);
+                const int mb = rem / p.tiles_n, nb = rem % p.tiles_n;  // n fastest: neighbours share the A tile in L2
+                const int b0 = z % p.batch0, b1 = z / p.batch0;
+                const int m0 = mb * BLOCK_M, n0 = nb * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(empty_bar(stage), phase ^ 1u);
+                    mbar_expect_tx(full_bar(stage), C_::STAGE_BYTES);
+                    const uint32_t sa = smem_base + stage * C_::STAGE_BYTES;
+                    const uint32_t sb = sa + A_STAGE_BYTES;
+                    const int k0 = kb * BLOCK_K;
+                    if (!p.a_mn) {
+                        tma_load_4d(sa, &tma_a, full_bar(stage), k0, m0, b0, b1);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < BLOCK_M / 64; ++c)
+                            tma_load_4d(sa + c * (64 * BLOCK_K * 2), &tma_a, full_bar(stage), m0 + 64 * c, k0, b0, b1);
+                    }
+                    if (!p.b_mn) {
+                        tma_load_4d(sb, &tma_b, full_bar(stage), k0, n0, b0, b1);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < BN / 64; ++c)
+                            tma_load_4d(sb + c * (64 * BLOCK_K * 2), &tma_b, full_bar(stage), n0 + 64 * c, k0, b0, b1);
+                    }
+                    if (++stage == C_::STAGES) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            // instruction descriptor: D fp32, A/B bf16, majors, N>>3, M>>4 (cute::UMMA::InstrDescriptor)
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
+                                   ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
+            // K-major SW128: 8-row groups 1024 B apart (SBO); LBO unused (1).  +32 B per UMMA_K inside the atom.
+            // MN-major SW128: 64-element chunks along M/N are one TMA box (64 k-rows x 128 B = 8 KB) apart (LBO),
+            //                 8-k-row groups 1024 B apart (SBO).  +2048 B per UMMA_K.
+            const uint32_t a_lbo = p.a_mn ? 64 * BLOCK_K * 2 : 16, a_sbo = 1024;
+            const uint32_t b_lbo = p.b_mn ? 64 * BLOCK_K * 2 : 16, b_sbo = 1024;
+            const uint32_t a_kstep = p.a_mn ? (UMMA_K * 128) : (UMMA_K * 2);
+            const uint32_t b_kstep = p.b_mn ? (UMMA_K * 128) : (UMMA_K * 2);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (long long tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+                mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(full_bar(stage), phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_base + stage * C_::STAGE_BYTES;
+                    const uint32_t sb = sa + A_STAGE_BYTES;
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                        const uint64_t adesc = make_smem_desc(sa + k * a_kstep, a_lbo, a_sbo);
+                        const uint64_t bdesc = make_smem_desc(sb + k * b_kstep, b_lbo, b_sbo);
+                        umma_bf16(tmem_d, adesc, bdesc, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(empty_bar(stage));  // frees the smem slot once these MMAs have read it
+                    if (++stage == C_::STAGES) { stage = 0; phase ^= 1u; }
+                }
+                umma_commit(tfull_bar(acc));  // accumulator complete -> epilogue
+                if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+            }
+        }
+    } else {
+        // ===================== epilogue warps =====================
+        const int quarter = warp & 3;  // TMEM lanes [32*quarter, 32*quarter+32) are accessible to this warp
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        TC* Cb = (TC*)p.C;
+        const TC* Rb = (const TC*)p.residual;
+        TC* AOb = (TC*)p.aux_out;
+        const TC* AIb = (const TC*)p.aux_in;
+        const bool vec_ok = (p.ldc % (16 / (int)sizeof(TC)) == 0) && ((p.sc0 | p.sc1) % (16 / (int)sizeof(TC)) == 0) &&
+                            ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0) &&
+                            (!p.residual || (reinterpret_cast<uintptr_t>(p.residual) & 15) == 0) &&
+                            (!p.aux_out || (reinterpret_cast<uintptr_t>(p.aux_out) & 15) == 0) &&
+                            (!p.aux_in || (reinterpret_cast<uintptr_t>(p.aux_in) & 15) == 0);
+        for (long long tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            const int z = (int)(tile / tiles_per_batch);
+            const int rem = (int)(tile % tiles_per_batch);
+            const int mb = rem / p.tiles_n, nb = rem % p.tiles_n;
+            const int b0 = z % p.batch0, b1 = z / p.batch0;
+            const int m = mb * BLOCK_M + quarter * 32 + lane;
+            const int n0 = nb * BN;
+            const long long row_off = (long long)b0 * p.sc0 + (long long)b1 * p.sc1 + (long long)m * p.ldc;
+            mbar_wait(tfull_bar(acc), acc_phase);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32(taddr + c * 32, r);
+                tmem_ld_wait();
+                const int n = n0 + c * 32;
+                const int nvalid = p.N - n;  // may be <= 0 or > 32
+                if (m < p.M && nvalid > 0) {
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+                    if (p.bias) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (j < nvalid) v[j] += __ldg(p.bias + n + j);
+                    }
+                    if (AOb) store_row_chunk<TC>(AOb + row_off + n, v, nvalid, vec_ok);
+                    if (p.act == B200ASR_ACT_GELU) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+                    }
+                    if (p.mul_gelu_grad) {
+                        float u[32];
+                        load_row_chunk<TC>(AIb + row_off + n, u, nvalid, vec_ok);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] *= gelu_erf_grad(u[j]);
+                    }
+                    if (Rb) {
+                        float u[32];
+                        load_row_chunk<TC>(Rb + row_off + n, u, nvalid, vec_ok);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] += u[j];
+                    }
+                    store_row_chunk<TC>(Cb + row_off + n, v, nvalid, vec_ok);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar(acc));
+            if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, C_::TMEM_COLS);
+    }
+}
+
+// ---------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(f);
+    });
+    return fn;
+}
+
+// operand matrix X(r, k): kmajor -> X[r*ld + k], else X[k*ld + r];  r < R, k < K; batched with strides s0, s1.
+static int make_operand_map(CUtensorMap* map, const void* base, int R, int K, int ld, int kmajor, int box_r, int batch0,
+                            int batch1, long long s0, long long s1) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) {
+        set_error("gemm(tcgen05): cuTensorMapEncodeTiled entry point unavailable");
+        return B200ASR_ERR_CUDA;
+    }
+    cuuint64_t dims[4];
+    cuuint64_t strides[3];
+    cuuint32_t box[4];
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    const long long row_bytes = (long long)ld * 2;
+    if (kmajor) {
+        dims[0] = (cuuint64_t)K; dims[1] = (cuuint64_t)R;
+        box[0] = BLOCK_K; box[1] = (cuuint32_t)box_r;
+    } else {
+        dims[0] = (cuuint64_t)R; dims[1] = (cuuint64_t)K;
+        box[0] = 64; box[1] = BLOCK_K;
+    }
+    dims[2] = (cuuint64_t)batch0; dims[3] = (cuuint64_t)batch1;
+    box[2] = 1; box[3] = 1;
+    strides[0] = (cuuint64_t)row_bytes;
+    // unit batch dims still need a legal (multiple-of-16) stride
+    strides[1] = (cuuint64_t)((batch0 > 1 ? s0 : 8) * 2);
+    strides[2] = (cuuint64_t)((batch1 > 1 ? s1 : 8) * 2);
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("gemm(tcgen05): cuTensorMapEncodeTiled failed (%d) R=%d K=%d ld=%d kmajor=%d b=(%d,%d) s=(%lld,%lld)", (int)r,
+                  R, K, ld, kmajor, batch0, batch1, s0, s1);
+        return B200ASR_ERR_CUDA;
+    }
+    return B200ASR_OK;
+}
+
+template <int BN, typename TC>
+static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
+    using C_ = Cfg<BN>;
+    CUtensorMap ma, mb;
+    int rc = make_operand_map(&ma, a.A, a.M, a.K, a.lda, a.a_kmajor, BLOCK_M, a.batch0, a.batch1, a.sa0, a.sa1);
+    if (rc) return rc;
+    rc = make_operand_map(&mb, a.B, a.N, a.K, a.ldb, a.b_kmajor, BN, a.batch0, a.batch1, a.sb0, a.sb1);
+    if (rc) return rc;
+    Params p;
+    p.C = a.C; p.bias = a.bias; p.residual = a.residual; p.aux_out = a.aux_out; p.aux_in = a.aux_in;
+    p.M = a.M; p.N = a.N; p.K = a.K; p.ldc = a.ldc;
+    p.a_mn = a.a_kmajor ? 0 : 1; p.b_mn = a.b_kmajor ? 0 : 1;
+    p.act = a.act; p.mul_gelu_grad = a.mul_gelu_grad; p.alpha = a.alpha;
+    p.batch0 = a.batch0; p.batch1 = a.batch1; p.sc0 = a.sc0; p.sc1 = a.sc1;
+    p.tiles_m = ceil_div(a.M, BLOCK_M);
+    p.tiles_n = ceil_div(a.N, BN);
+    p.num_tiles = (long long)p.tiles_m * p.tiles_n * a.batch0 * a.batch1;
+    static bool attr_set = false;  // per instantiation
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C_::SMEM_BYTES);
+        if (e != cudaSuccess) {
+            set_error("gemm(tcgen05): cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+            return B200ASR_ERR_CUDA;
+        }
+        attr_set = true;
+    }
+    long long grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+    gemm_tc_kernel<BN, TC><<<(int)grid, NUM_THREADS, C_::SMEM_BYTES, st>>>(ma, mb, p);
+    return check_launch("gemm_tcgen05");
+}
+
+}  // namespace tc
+
+bool gemm_tc_eligible(const b200asr_gemm_args& a, const char** why) {
+    auto fail = [&](const char* w) { if (why) *why = w; return false; };
+    if (a.dtype != B200ASR_BF16) return fail("operands are not bf16");
+    if (a.M < 1 || a.N < 8 || a.K < 8) return fail("N or K below 8");
+    if (((uintptr_t)a.A & 15) || ((uintptr_t)a.B & 15)) return fail("operand base not 16-byte aligned");
+    if (a.lda % 8 || a.ldb % 8) return fail("leading dimension not a multiple of 8 elements");
+    if ((a.batch0 > 1 && (a.sa0 % 8 || a.sb0 % 8)) || (a.batch1 > 1 && (a.sa1 % 8 || a.sb1 % 8)))
+        return fail("batch stride not a multiple of 8 elements");
+    return true;
+}
+
+int gemm_tc_launch(const b200asr_gemm_args& a, cudaStream_t st) {
+    // 128x256 tiles halve the shared-memory read traffic per FLOP; use them when N is wide enough to
+    // still give every SM a tile, 128x64 for narrow outputs (attention context, head_dim 64).
+    const long long batches = (long long)a.batch0 * a.batch1;
+    int bn = 128;
+    if (a.N <= 64) bn = 64;
+    else if (a.N >= 1024 && (long long)ceil_div(a.M, 128) * ceil_div(a.N, 256) * batches >= num_sms()) bn = 256;
+    const bool f32c = a.c_dtype == B200ASR_F32;
+    switch (bn) {
+        case 64: return f32c ? tc::launch<64, float>(a, st) : tc::launch<64, __nv_bfloat16>(a, st);
+        case 256: return f32c ? tc::launch<256, float>(a, st) : tc::launch<256, __nv_bfloat16>(a, st);
+        default: return f32c ? tc::launch<128, float>(a, st) : tc::launch<128, __nv_bfloat16>(a, st);
+    }
+}
+
+}  // namespace b200asr

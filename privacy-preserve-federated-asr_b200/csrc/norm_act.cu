@@ -1,0 +1,340 @@
+// LayerNorm (+residual, +GELU) forward/backward, column sums.  HBM-bound: one warp per row, 128-bit
+// loads, values held in registers between the statistics pass and the normalise pass (one read, one write).
+#include "common.cuh"
+
+namespace b200asr {
+
+constexpr int LN_BWD_BLOCKS = 296;   // 2 x 148 SMs; fixed so that the workspace size is device independent
+constexpr int COLSUM_CHUNKS = 64;
+
+template <typename T, int NV>
+__global__ void __launch_bounds__(128) ln_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res,
+                                                     const float* __restrict__ w, const float* __restrict__ b,
+                                                     T* __restrict__ y, T* __restrict__ sum_out,
+                                                     float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                                                     int rows, int cols, float eps, int act) {
+    constexpr int N = Vec16<T>::N;
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    const int nvec = cols / N;
+    const float inv_cols = 1.0f / (float)cols;
+    for (int row = warp; row < rows; row += nwarps) {
+        const long long base = (long long)row * cols;
+        float v[NV][N];
+        float sum = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int vi = lane + 32 * i;
+            if (vi < nvec) {
+                Vec16<T> a;
+                a.load(x + base + (long long)vi * N);
+                a.unpack(v[i]);
+                if (res) {
+                    Vec16<T> r;
+                    float rf[N];
+                    r.load(res + base + (long long)vi * N);
+                    r.unpack(rf);
+#pragma unroll
+                    for (int j = 0; j < N; ++j) v[i][j] += rf[j];
+                }
+                if (sum_out) {
+                    Vec16<T> s;
+                    s.pack(v[i]);
+                    s.store(sum_out + base + (long long)vi * N);
+                    s.unpack(v[i]);  // statistics from the stored (rounded) value: backward sees the same numbers
+                }
+#pragma unroll
+                for (int j = 0; j < N; ++j) sum += v[i][j];
+            } else {
+#pragma unroll
+                for (int j = 0; j < N; ++j) v[i][j] = 0.f;
+            }
+        }
+        const float mean = warp_sum(sum) * inv_cols;
+        float sq = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int vi = lane + 32 * i;
+            if (vi < nvec) {
+#pragma unroll
+                for (int j = 0; j < N; ++j) {
+                    const float d = v[i][j] - mean;
+                    sq += d * d;
+                }
+            }
+        }
+        const float rstd = rsqrtf(warp_sum(sq) * inv_cols + eps);
+        if (lane == 0) {
+            if (mean_out) mean_out[row] = mean;
+            if (rstd_out) rstd_out[row] = rstd;
+        }
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int vi = lane + 32 * i;
+            if (vi < nvec) {
+                float o[N];
+#pragma unroll
+                for (int j = 0; j < N; ++j) {
+                    float t = (v[i][j] - mean) * rstd;
+                    if (w) t = t * __ldg(w + vi * N + j) + __ldg(b + vi * N + j);
+                    if (act == B200ASR_ACT_GELU) t = gelu_erf(t);
+                    o[j] = t;
+                }
+                Vec16<T> ov;
+                ov.pack(o);
+                ov.store(y + base + (long long)vi * N);
+            }
+        }
+    }
+}
+
+template <typename T, int NV>
+__global__ void __launch_bounds__(128) ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ s,
+                                                     const float* __restrict__ w, const float* __restrict__ b,
+                                                     const float* __restrict__ mean_in,
+                                                     const float* __restrict__ rstd_in,
+                                                     const T* __restrict__ dres_add, T* __restrict__ dx,
+                                                     float* __restrict__ partial, int rows, int cols, int act) {
+    constexpr int N = Vec16<T>::N;
+    extern __shared__ float sacc[];  // [2][cols] when partial != nullptr
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    const int nvec = cols / N;
+    const float inv_cols = 1.0f / (float)cols;
+    if (partial) {
+        for (int i = threadIdx.x; i < 2 * cols; i += blockDim.x) sacc[i] = 0.f;
+        __syncthreads();
+    }
+    float aw[NV][N], ab[NV][N];
+#pragma unroll
+    for (int i = 0; i < NV; ++i)
+#pragma unroll
+        for (int j = 0; j < N; ++j) aw[i][j] = ab[i][j] = 0.f;
+
+    for (int row = warp; row < rows; row += nwarps) {
+        const long long base = (long long)row * cols;
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        float xh[NV][N], dz[NV][N];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int vi = lane + 32 * i;
+            if (vi < nvec) {
+                Vec16<T> a, g;
+                a.load(s + base + (long long)vi * N);
+                g.load(dy + base + (long long)vi * N);
+                a.unpack(xh[i]);
+                g.unpack(dz[i]);
+#pragma unroll
+                for (int j = 0; j < N; ++j) {
+                    const float h = (xh[i][j] - mean) * rstd;
+                    xh[i][j] = h;
+                    const float wj = w ? __ldg(w + vi * N + j) : 1.f;
+                    float d = dz[i][j];
+                    if (act == B200ASR_ACT_GELU) {
+                        const float z = w ? h * wj + __ldg(b + vi * N + j) : h;
+                        d *= gelu_erf_grad(z);
+                    }
+                    aw[i][j] += d * h;
+                    ab[i][j] += d;
+                    d *= wj;
+                    dz[i][j] = d;
+                    s1 += d;
+                    s2 += d * h;
+                }
+            }
+        }
+        s1 = warp_sum(s1) * inv_cols;
+        s2 = warp_sum(s2) * inv_cols;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int vi = lane + 32 * i;
+            if (vi < nvec) {
+                float o[N];
+#pragma unroll
+                for (int j = 0; j < N; ++j) o[j] = rstd * (dz[i][j] - s1 - xh[i][j] * s2);
+                if (dres_add) {
+                    Vec16<T> r;
+                    float rf[N];
+                    r.load(dres_add + base + (long long)vi * N);
+                    r.unpack(rf);
+#pragma unroll
+                    for (int j = 0; j < N; ++j) o[j] += rf[j];
+                }
+                Vec16<T> ov;
+                ov.pack(o);
+                ov.store(dx + base + (long long)vi * N);
+            }
+        }
+    }
+    if (partial) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            const int vi = lane + 32 * i;
+            if (vi < nvec) {
+#pragma unroll
+                for (int j = 0; j < N; ++j) {
+                    atomicAdd(&sacc[vi * N + j], aw[i][j]);
+                    atomicAdd(&sacc[cols + vi * N + j], ab[i][j]);
+                }
+            }
+        }
+        __syncthreads();
+        float* out = partial + (long long)blockIdx.x * 2 * cols;
+        for (int i = threadIdx.x; i < 2 * cols; i += blockDim.x) out[i] = sacc[i];
+    }
+}
+
+// out[c] = sum_{p < nparts} partial[p * stride + c]
+__global__ void reduce_partials_kernel(const float* __restrict__ partial, float* __restrict__ out0,
+                                       float* __restrict__ out1, int nparts, int cols, int stride) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cols) return;
+    float a0 = 0.f, a1 = 0.f;
+    for (int p = 0; p < nparts; ++p) {
+        a0 += partial[(long long)p * stride + c];
+        if (out1) a1 += partial[(long long)p * stride + cols + c];
+    }
+    if (out0) out0[c] = a0;
+    if (out1) out1[c] = a1;
+}
+
+template <typename T>
+__global__ void colsum_partial_kernel(const T* __restrict__ x, float* __restrict__ partial, int rows, int cols,
+                                      int ld, int rows_per_chunk) {
+    // thread = one column; blockIdx.y = row chunk.  Warps read 32 consecutive columns: coalesced.
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cols) return;
+    const int r0 = blockIdx.y * rows_per_chunk;
+    const int r1 = min(rows, r0 + rows_per_chunk);
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    int r = r0;
+    for (; r + 3 < r1; r += 4) {
+        a0 += to_f<T>(x[(long long)r * ld + c]);
+        a1 += to_f<T>(x[(long long)(r + 1) * ld + c]);
+        a2 += to_f<T>(x[(long long)(r + 2) * ld + c]);
+        a3 += to_f<T>(x[(long long)(r + 3) * ld + c]);
+    }
+    for (; r < r1; ++r) a0 += to_f<T>(x[(long long)r * ld + c]);
+    partial[(long long)blockIdx.y * cols + c] = (a0 + a1) + (a2 + a3);
+}
+
+template <typename T>
+static int launch_ln_fwd(const void* x, const void* res, const float* w, const float* b, void* y, void* sum_out,
+                         float* mean, float* rstd, int rows, int cols, float eps, int act, cudaStream_t st) {
+    constexpr int N = Vec16<T>::N;
+    const int nvec = cols / N;
+    const int nv = ceil_div(nvec, 32);
+    const int warps_per_block = 4;
+    int grid = ceil_div(rows, warps_per_block);
+    const int cap = num_sms() * 16;
+    if (grid > cap) grid = cap;
+#define LN_FWD_CASE(NVV)                                                                                      \
+    ln_fwd_kernel<T, NVV><<<grid, 128, 0, st>>>((const T*)x, (const T*)res, w, b, (T*)y, (T*)sum_out, mean,   \
+                                                 rstd, rows, cols, eps, act)
+    if (nv <= 1) LN_FWD_CASE(1);
+    else if (nv <= 2) LN_FWD_CASE(2);
+    else if (nv <= 4) LN_FWD_CASE(4);
+    else if (nv <= 8) LN_FWD_CASE(8);
+    else if (nv <= 16) LN_FWD_CASE(16);
+    else { set_error("layernorm: cols=%d too large", cols); return B200ASR_ERR_UNSUPPORTED; }
+#undef LN_FWD_CASE
+    return check_launch("layernorm_fwd");
+}
+
+template <typename T>
+static int launch_ln_bwd(const void* dy, const void* s, const float* w, const float* b, const float* mean,
+                         const float* rstd, const void* dres, void* dx, float* partial, int rows, int cols, int act,
+                         cudaStream_t st) {
+    constexpr int N = Vec16<T>::N;
+    const int nvec = cols / N;
+    const int nv = ceil_div(nvec, 32);
+    int grid = ceil_div(rows, 4);
+    if (grid > LN_BWD_BLOCKS) grid = LN_BWD_BLOCKS;
+    if (partial) grid = LN_BWD_BLOCKS;  // finalize sums exactly LN_BWD_BLOCKS partials
+    const size_t smem = partial ? (size_t)2 * cols * sizeof(float) : 0;
+#define LN_BWD_CASE(NVV)                                                                                     \
+    ln_bwd_kernel<T, NVV><<<grid, 128, smem, st>>>((const T*)dy, (const T*)s, w, b, mean, rstd, (const T*)dres, \
+                                                    (T*)dx, partial, rows, cols, act)
+    if (nv <= 1) LN_BWD_CASE(1);
+    else if (nv <= 2) LN_BWD_CASE(2);
+    else if (nv <= 4) LN_BWD_CASE(4);
+    else if (nv <= 8) LN_BWD_CASE(8);
+    else { set_error("layernorm_bwd: cols=%d too large", cols); return B200ASR_ERR_UNSUPPORTED; }
+#undef LN_BWD_CASE
+    return check_launch("layernorm_bwd");
+}
+
+}  // namespace b200asr
+
+using namespace b200asr;
+
+extern "C" {
+
+int b200asr_layernorm_fwd(const void* x, const void* res, const float* w, const float* b, void* y, void* sum_out,
+                          float* mean, float* rstd, int rows, int cols, float eps, int act, int dtype,
+                          void* stream) {
+    if (rows <= 0) return B200ASR_OK;
+    B200_REQUIRE(x && y, "layernorm_fwd: null pointer");
+    B200_REQUIRE((w == nullptr) == (b == nullptr), "layernorm_fwd: w and b must both be given or both NULL");
+    B200_REQUIRE(cols > 0 && cols % (dtype == B200ASR_BF16 ? 8 : 4) == 0,
+                 "layernorm_fwd: cols=%d must be a multiple of the 16-byte vector width", cols);
+    B200_DISPATCH_DTYPE(dtype, {
+        return launch_ln_fwd<T>(x, res, w, b, y, sum_out, mean, rstd, rows, cols, eps, act, as_stream(stream));
+    });
+    return B200ASR_OK;
+}
+
+size_t b200asr_layernorm_bwd_workspace_bytes(int cols) { return (size_t)LN_BWD_BLOCKS * 2 * cols * sizeof(float); }
+
+int b200asr_layernorm_bwd(const void* dy, const void* s, const float* w, const float* b, const float* mean,
+                          const float* rstd, const void* dres_add, void* dx, float* dw, float* db, void* workspace,
+                          size_t workspace_bytes, int rows, int cols, int act, int dtype, void* stream) {
+    if (rows <= 0) return B200ASR_OK;
+    B200_REQUIRE(dy && s && mean && rstd && dx, "layernorm_bwd: null pointer");
+    B200_REQUIRE(cols > 0 && cols % (dtype == B200ASR_BF16 ? 8 : 4) == 0, "layernorm_bwd: bad cols=%d", cols);
+    float* partial = nullptr;
+    if (dw || db) {
+        B200_REQUIRE(workspace && workspace_bytes >= b200asr_layernorm_bwd_workspace_bytes(cols),
+                     "layernorm_bwd: workspace too small");
+        B200_REQUIRE((size_t)2 * cols * sizeof(float) <= 48 * 1024, "layernorm_bwd: cols=%d too large", cols);
+        partial = (float*)workspace;
+    }
+    int rc;
+    B200_DISPATCH_DTYPE(dtype, {
+        rc = launch_ln_bwd<T>(dy, s, w, b, mean, rstd, dres_add, dx, partial, rows, cols, act, as_stream(stream));
+    });
+    if (rc != B200ASR_OK) return rc;
+    if (partial) {
+        reduce_partials_kernel<<<ceil_div(cols, 128), 128, 0, as_stream(stream)>>>(partial, dw, db, LN_BWD_BLOCKS,
+                                                                                   cols, 2 * cols);
+        return check_launch("layernorm_bwd_reduce");
+    }
+    return B200ASR_OK;
+}
+
+size_t b200asr_colsum_workspace_bytes(int cols) { return (size_t)COLSUM_CHUNKS * cols * sizeof(float); }
+
+int b200asr_colsum(const void* x, float* out, void* workspace, size_t workspace_bytes, int rows, int cols, int ld,
+                   int dtype, void* stream) {
+    B200_REQUIRE(x && out && workspace, "colsum: null pointer");
+    B200_REQUIRE(rows > 0 && cols > 0 && ld >= cols, "colsum: bad shape");
+    B200_REQUIRE(workspace_bytes >= b200asr_colsum_workspace_bytes(cols), "colsum: workspace too small");
+    const int chunks = rows < COLSUM_CHUNKS ? rows : COLSUM_CHUNKS;
+    const int rpc = ceil_div(rows, chunks);
+    const int nchunks = ceil_div(rows, rpc);
+    dim3 grid(ceil_div(cols, 128), nchunks);
+    B200_DISPATCH_DTYPE(dtype, {
+        colsum_partial_kernel<T><<<grid, 128, 0, as_stream(stream)>>>((const T*)x, (float*)workspace, rows, cols, ld,
+                                                                        rpc);
+    });
+    int rc = check_launch("colsum_partial");
+    if (rc != B200ASR_OK) return rc;
+    reduce_partials_kernel<<<ceil_div(cols, 128), 128, 0, as_stream(stream)>>>((const float*)workspace, out, nullptr,
+                                                                               nchunks, cols, cols);
+    return check_launch("colsum_reduce");
+}
+
+}  // extern "C"
