@@ -79,6 +79,9 @@ int b200asr_cast_to_f32(const void* src, float* dst, long long n, int src_dtype,
 /* x[i] *= host_scale * (*dev_scale)   (dev_scale may be NULL)  -- upstream-gradient scaling, GRL -lambda. */
 int b200asr_scale(void* x, long long n, float host_scale, const float* dev_scale, int dtype, void* stream);
 
+/* y[i] += alpha * x[i]  (gradient accumulation where two branches meet: h + pos_conv(h), HF:381). */
+int b200asr_axpy(void* y, const void* x, float alpha, long long n, int dtype, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Waveform feature extractor layer 0: Conv1d(1 -> C, k, stride) + LayerNorm(C, affine) + GELU, fused.
  * Replaces HF:51-75 for layer_id 0 (reached from federated/src/models.py:395, finetune_ASRs.py:231).

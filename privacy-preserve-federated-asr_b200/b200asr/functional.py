@@ -1,0 +1,389 @@
+"""Autograd wiring of the hot path at block granularity (one autograd node per encoder layer, not per op).
+
+Each Function's forward/backward is a hand-scheduled sequence of C-ABI kernels (ops.py); torch only owns the
+tensors and the autograd graph.  Saved-for-backward tensors are chosen so that no activation is recomputed
+except the attention probabilities (rebuilt from the saved log-sum-exp).
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+
+from . import ops
+from ._lib import ACT_GELU, ACT_NONE
+
+
+# ----------------------------------------------------------------------------- weight shadows
+class ShadowCache:
+    """Compute-dtype copies of fp32 master parameters, refreshed when the parameter changes.
+
+    fp32 mode returns the parameter storage itself.  bf16 mode keeps a bf16 shadow (what the tcgen05 GEMM
+    reads); derived layouts (fused QKV, conv filters flattened for the implicit GEMM, packed pos-conv filters)
+    are cached under the same versioning.
+    """
+
+    epoch = 0  # bumped by invalidate_all(): kernels (fused AdamW, FedAvg) wrote parameters behind autograd's back
+
+    def __init__(self, dtype: torch.dtype):
+        self.dtype = dtype
+        self._cache = {}
+
+    @classmethod
+    def invalidate_all(cls):
+        cls.epoch += 1
+
+    @staticmethod
+    def _ver(ps):
+        return (ShadowCache.epoch,) + tuple((p.data_ptr(), p._version) for p in ps)
+
+    def _get(self, key, ps, make):
+        ver = self._ver(ps)
+        hit = self._cache.get(key)
+        if hit is not None and hit[0] == ver:
+            return hit[1]
+        with torch.no_grad():
+            val = make()
+        self._cache[key] = (ver, val)
+        return val
+
+    def _cast(self, t: torch.Tensor) -> torch.Tensor:
+        t = t.detach()
+        if not t.is_contiguous():
+            t = t.contiguous()
+        return t if self.dtype == torch.float32 else ops.cast_from_f32(t, self.dtype)
+
+    def weight(self, p: torch.Tensor) -> torch.Tensor:
+        return self._get(("w", id(p)), (p,), lambda: self._cast(p))
+
+    def qkv(self, q, k, v) -> torch.Tensor:
+        """[3d, d] = rows of q_proj, k_proj, v_proj (the packed projection the attention kernel consumes)."""
+        return self._get(("qkv", id(q)), (q, k, v), lambda: self._cast(torch.cat([q.detach(), k.detach(), v.detach()], 0)))
+
+    def qkv_bias(self, q, k, v) -> torch.Tensor:
+        return self._get(("qkvb", id(q)), (q, k, v), lambda: torch.cat([q.detach(), k.detach(), v.detach()], 0).contiguous())
+
+    def conv_flat(self, w) -> torch.Tensor:
+        """Conv1d filter [Cout, Cin, k] -> [Cout, k*Cin] matching channels-last windows (row = [tap][channel])."""
+        return self._get(("convflat", id(w)), (w,),
+                         lambda: self._cast(w.detach().permute(0, 2, 1).reshape(w.shape[0], -1)))
+
+    def posconv(self, w, groups):
+        return self._get(("posconv", id(w)), (w,), lambda: ops.posconv_pack(self._cast(w), groups))
+
+
+# ----------------------------------------------------------------------------- frozen feature extractor
+def feature_extractor_fwd(x: torch.Tensor, conv_w: List[torch.Tensor], conv_b: List[Optional[torch.Tensor]],
+                          ln_w: List[torch.Tensor], ln_b: List[torch.Tensor], kernels, strides, eps: float,
+                          cache: ShadowCache) -> torch.Tensor:
+    """HF:51-75,131-157 with the stack frozen (finetune_ASRs.py:200, models.py:302): forward only.
+    x [B, L] fp32 -> [B, T, C] channels-last.  Layer 0 is the fused direct kernel, layers 1.. are GEMMs whose
+    A operand is the overlapping-window view of the channels-last activations (row pitch = stride*C, row length
+    k*C), followed by the fused LayerNorm+GELU pass."""
+    cd = cache.dtype
+    with torch.no_grad():
+        h = ops.conv0_ln_gelu(x.float(), conv_w[0].detach(), None if conv_b[0] is None else conv_b[0].detach(),
+                              ln_w[0].detach(), ln_b[0].detach(), strides[0], eps, cd)
+        for i in range(1, len(conv_w)):
+            B, Tin, Cin = h.shape
+            k, s = kernels[i], strides[i]
+            Tout = (Tin - k) // s + 1
+            Cout = conv_w[i].shape[0]
+            wf = cache.conv_flat(conv_w[i])
+            y = torch.empty(B, Tout, Cout, dtype=cd, device=h.device)
+            ops.gemm_raw(h, wf, y, Tout, Cout, k * Cin, s * Cin, k * Cin, Cout, True, True,
+                         bias=None if conv_b[i] is None else conv_b[i].detach(),
+                         batch0=1, batch1=B, sa=(0, Tin * Cin), sb=(0, 0), sc=(0, Tout * Cout))
+            h, _, _, _ = ops.layernorm_fwd(y, ln_w[i].detach(), ln_b[i].detach(), eps, act=ACT_GELU, want_stats=False)
+    return h
+
+
+# ----------------------------------------------------------------------------- feature projection
+class FeatureProjectionFn(torch.autograd.Function):
+    """HF:160-172: LayerNorm(C) -> Linear(C -> d).  The input comes from the frozen extractor (no dx)."""
+
+    @staticmethod
+    def forward(ctx, feats, ln_w, ln_b, w, b, eps, cache: ShadowCache, klen=None):
+        M = feats.numel() // feats.shape[-1]
+        x2 = feats.reshape(M, feats.shape[-1])
+        n, _, mean, rstd = ops.layernorm_fwd(x2, ln_w, ln_b, eps)
+        wsh = cache.weight(w)
+        y, _ = ops.linear_fwd(n, wsh, b)
+        ctx.save_for_backward(x2, n, mean, rstd, ln_w, ln_b, wsh, klen)
+        ctx.out_shape = feats.shape[:-1] + (w.shape[0],)
+        y = y.view(ctx.out_shape)
+        if klen is not None:  # hidden_states[~attention_mask] = 0 (HF:369-371), fused here: y is our own buffer
+            ops.mask_frames_(y, klen)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, n, mean, rstd, ln_w, ln_b, wsh, klen = ctx.saved_tensors
+        if klen is not None:
+            dy = ops.mask_frames_(dy.clone(memory_format=torch.contiguous_format), klen)
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        db = ops.colsum(dy2)
+        dw = ops.linear_wgrad(dy2, n)
+        dn = ops.linear_dgrad(dy2, wsh)
+        _, dlw, dlb = ops.layernorm_bwd(dn, x2, ln_w, ln_b, mean, rstd)
+        return None, dlw, dlb, dw, db, None, None, None
+
+
+# ----------------------------------------------------------------------------- positional conv embedding + LN
+class PosConvEmbedFn(torch.autograd.Function):
+    """HF:89-128 + HF:381-383: y = LN(h + posconv(h)); posconv = n x {grouped conv -> LN(no affine) -> GELU}.
+    args: h [B,T,d], enc_ln_w, enc_ln_b, then conv weights (n), then conv biases (n)."""
+
+    @staticmethod
+    def forward(ctx, h, ln_w, ln_b, eps, groups, ksize, cache: ShadowCache, *wb):
+        n = len(wb) // 2
+        ws, bs = wb[:n], wb[n:]
+        B, T, d = h.shape
+        saved = []
+        y = h
+        packs = []
+        for j in range(n):
+            wf, wbk = cache.posconv(ws[j], groups)
+            packs.append(wbk)
+            c = ops.posconv_fwd(y, wf, bs[j], groups, ksize)
+            y_next, _, mean, rstd = ops.layernorm_fwd(c.view(B * T, d), None, None, 1e-5, act=ACT_GELU)
+            saved += [y, c, mean, rstd]
+            y = y_next.view(B, T, d)
+        out, s, mean, rstd = ops.layernorm_fwd(h.reshape(B * T, d), ln_w, ln_b, eps, res=y.reshape(B * T, d), want_sum=True)
+        ctx.save_for_backward(s, mean, rstd, ln_w, ln_b, *saved, *packs)
+        ctx.n, ctx.groups, ctx.ksize, ctx.shape = n, groups, ksize, (B, T, d)
+        return out.view(B, T, d)
+
+    @staticmethod
+    def backward(ctx, dout):
+        n, groups, k = ctx.n, ctx.groups, ctx.ksize
+        B, T, d = ctx.shape
+        t = ctx.saved_tensors
+        s, mean, rstd, ln_w, ln_b = t[:5]
+        saved = t[5:5 + 4 * n]
+        packs = t[5 + 4 * n:]
+        dout2 = dout.reshape(B * T, d)
+        ds, dlw, dlb = ops.layernorm_bwd(dout2, s, ln_w, ln_b, mean, rstd)
+        dy = ds  # gradient into posconv output; ds is also the residual-path gradient
+        dws, dbs = [None] * n, [None] * n
+        for j in range(n - 1, -1, -1):
+            y_in, c, cm, cr = saved[4 * j:4 * j + 4]
+            dc, _, _ = ops.layernorm_bwd(dy, c.view(B * T, d), None, None, cm, cr, act=ACT_GELU)
+            dbs[j] = ops.colsum(dc)
+            need_dx = j > 0 or ctx.needs_input_grad[0]
+            dx, dws[j] = ops.posconv_bwd(y_in, packs[j], dc.view(B, T, d), groups, k, want_dx=need_dx)
+            dy = dx.view(B * T, d) if dx is not None else None
+        dh = None
+        if ctx.needs_input_grad[0]:
+            dh = ops.axpy_(dy, ds).view(B, T, d)
+        return (dh, dlw, dlb, None, None, None, None, *dws, *dbs)
+
+
+# ----------------------------------------------------------------------------- transformer encoder layer
+class EncoderLayerFn(torch.autograd.Function):
+    """HF:203-346, post-LN block (data2vec / wav2vec2-base ordering), dropout = 0:
+         a = O(softmax(scale * Q K^T + keymask) V);  x1 = LN1(x + a);  y = LN2(x1 + W2 gelu(W1 x1)).
+    Residual adds, biases, GELU and gelu' ride in GEMM epilogues; the QKV projection is one N = 3d GEMM.
+    params order: q_w,q_b,k_w,k_b,v_w,v_b,o_w,o_b,ln1_w,ln1_b,w1,b1,w2,b2,ln2_w,ln2_b"""
+
+    @staticmethod
+    def forward(ctx, x, klen, meta, cache: ShadowCache, *P):
+        (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = P
+        B, T, H, eps = meta
+        M, d = x.shape
+        dh = d // H
+        scale = dh ** -0.5
+        wqkv = cache.qkv(q_w, k_w, v_w)
+        bqkv = cache.qkv_bias(q_b, k_b, v_b)
+        wo, w1s, w2s = cache.weight(o_w), cache.weight(w1), cache.weight(w2)
+        qkv, _ = ops.linear_fwd(x, wqkv, bqkv)
+        attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale)
+        s1, _ = ops.linear_fwd(attn, wo, o_b, residual=x)
+        x1, _, m1, r1 = ops.layernorm_fwd(s1, ln1_w, ln1_b, eps)
+        g, u = ops.linear_fwd(x1, w1s, b1, act=ACT_GELU, want_preact=True)
+        s2, _ = ops.linear_fwd(g, w2s, b2, residual=x1)
+        y, _, m2, r2 = ops.layernorm_fwd(s2, ln2_w, ln2_b, eps)
+        ctx.save_for_backward(x, qkv, attn, lse, s1, m1, r1, x1, u, g, s2, m2, r2, wqkv, wo, w1s, w2s, ln1_w, ln1_b,
+                              ln2_w, ln2_b)
+        ctx.klen = klen
+        ctx.meta = (B, T, H, dh, scale)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x, qkv, attn, lse, s1, m1, r1, x1, u, g, s2, m2, r2, wqkv, wo, w1s, w2s, ln1_w, ln1_b, ln2_w,
+         ln2_b) = ctx.saved_tensors
+        B, T, H, dh, scale = ctx.meta
+        d = x.shape[1]
+        wg = any(ctx.needs_input_grad[4:])  # parameter gradients wanted?
+        ds2, dln2w, dln2b = ops.layernorm_bwd(dy, s2, ln2_w, ln2_b, m2, r2, want_wgrad=wg)
+        db2 = ops.colsum(ds2) if wg else None
+        dw2 = ops.linear_wgrad(ds2, g) if wg else None
+        du = ops.linear_dgrad(ds2, w2s, gelu_preact=u)            # (ds2 W2) * gelu'(u)
+        db1 = ops.colsum(du) if wg else None
+        dw1 = ops.linear_wgrad(du, x1) if wg else None
+        dx1 = ops.linear_dgrad(du, w1s, residual=ds2)            # + residual path of s2 = x1 + ...
+        ds1, dln1w, dln1b = ops.layernorm_bwd(dx1, s1, ln1_w, ln1_b, m1, r1, want_wgrad=wg)
+        dbo = ops.colsum(ds1) if wg else None
+        dwo = ops.linear_wgrad(ds1, attn) if wg else None
+        dattn = ops.linear_dgrad(ds1, wo)
+        dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale)
+        dx = ops.linear_dgrad(dqkv, wqkv, residual=ds1) if ctx.needs_input_grad[0] else None
+        if wg:
+            dbqkv = ops.colsum(dqkv)
+            dwqkv = ops.linear_wgrad(dqkv, x)
+            dqw, dkw, dvw = dwqkv[:d], dwqkv[d:2 * d], dwqkv[2 * d:]
+            dqb, dkb, dvb = dbqkv[:d], dbqkv[d:2 * d], dbqkv[2 * d:]
+        else:
+            dqw = dkw = dvw = dqb = dkb = dvb = None
+        return (dx, None, None, None, dqw, dqb, dkw, dkb, dvw, dvb, dwo, dbo, dln1w, dln1b, dw1, db1, dw2, db2,
+                dln2w, dln2b)
+
+
+# ----------------------------------------------------------------------------- heads
+class LinearFn(torch.autograd.Function):
+    """nn.Linear on [.., K] activations (lm_head, dementia_head, arbitrator: models.py:292-296)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, cache: ShadowCache):
+        K = x.shape[-1]
+        x2 = x.reshape(-1, K)
+        wsh = cache.weight(w)
+        y, _ = ops.linear_fwd(x2, wsh, b)
+        ctx.save_for_backward(x2, wsh)
+        return y.view(x.shape[:-1] + (w.shape[0],))
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, wsh = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = ops.linear_dgrad(dy2, wsh).view(dy.shape[:-1] + (wsh.shape[1],))
+        if ctx.needs_input_grad[1]:
+            dw = ops.linear_wgrad(dy2, x2)
+        if ctx.needs_input_grad[2]:
+            db = ops.colsum(dy2)
+        return dx, dw, db, None
+
+
+class GradReverseFn(torch.autograd.Function):
+    """ReverseLayerF (models.py:61-73): identity forward, grad * (-lambda) backward."""
+
+    @staticmethod
+    def forward(ctx, x, lam):
+        ctx.lam = float(lam)
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return ops.scale_(g.clone(memory_format=torch.contiguous_format), -ctx.lam), None
+
+
+class CTCLossFn(torch.autograd.Function):
+    """log_softmax(fp32) + F.ctc_loss (models.py:498-533; HF:897-908), loss and d loss / d logits in one launch.
+    Returns the reduced loss (0-dim fp32): reduction 'sum' or 'mean' (per-utterance / target length, batch mean)."""
+
+    @staticmethod
+    def forward(ctx, logits, targets, tgt_off, tgt_len, in_len, max_tgt, blank, zero_infinity, reduction):
+        B = logits.shape[0]
+        gs = None
+        if reduction == "mean":
+            gs = (1.0 / (tgt_len.clamp(min=1).float() * B)).view(1, B).contiguous()
+        loss, grad = ops.ctc_fwd_bwd(logits.unsqueeze(0), targets, tgt_off, tgt_len, in_len, max_tgt, blank,
+                                     zero_infinity, grad_scale=gs, want_grad=ctx.needs_input_grad[0])
+        ctx.save_for_backward(grad)
+        ctx.shape = logits.shape
+        per = loss[0]
+        if reduction == "mean":
+            return (per * gs[0]).sum()
+        return per.sum()
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        if grad is None:
+            return (None,) * 9
+        out = ops.scale_(grad.clone(), 1.0, g.reshape(1).float().contiguous())
+        return (out.view(ctx.shape),) + (None,) * 8
+
+
+class DacsMaskFn(torch.autograd.Function):
+    """Fused gumbel_softmax(hard) masks + masked hidden states (models.py:428-455, :75-129)."""
+
+    @staticmethod
+    def forward(ctx, scores, h, tau, ratio, noise_lm, noise_ad, seed, offset):
+        d = h.shape[-1]
+        s2, h2 = scores.reshape(-1, 4 * d), h.reshape(-1, d)
+        lm, ad, sl, sa, ml, ma = ops.dacs_mask_fwd(s2, h2, tau, ratio, noise_lm, noise_ad, seed, offset)
+        ctx.save_for_backward(h2, sl, sa, ml, ma)
+        ctx.cfg = (tau, ratio, scores.shape, h.shape)
+        ctx.mark_non_differentiable(ml, ma)
+        return lm.view(h.shape), ad.view(h.shape), ml.view(h.shape), ma.view(h.shape)
+
+    @staticmethod
+    def backward(ctx, d_lm, d_ad, _dml, _dma):
+        h2, sl, sa, ml, ma = ctx.saved_tensors
+        tau, ratio, sshape, hshape = ctx.cfg
+        d = h2.shape[1]
+        if d_lm is None:
+            d_lm = torch.zeros_like(h2)
+        if d_ad is None:
+            d_ad = torch.zeros_like(h2)
+        ds, dh = ops.dacs_mask_bwd(d_lm.reshape(-1, d), d_ad.reshape(-1, d), h2, sl, sa, ml, ma, tau, ratio,
+                                   want_dh=ctx.needs_input_grad[1])
+        return ds.view(sshape), (dh.view(hshape) if dh is not None else None), None, None, None, None, None, None
+
+
+class MeanTimeFn(torch.autograd.Function):
+    """torch.mean(x, dim=1) of per-frame AD logits (models.py:468-476) -> fp32 [B, C]."""
+
+    @staticmethod
+    def forward(ctx, x):
+        ctx.T, ctx.dtype = x.shape[1], x.dtype
+        return ops.mean_time_fwd(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return ops.mean_time_bwd(g.float(), ctx.T, ctx.dtype)
+
+
+class AdLossFn(torch.autograd.Function):
+    """RecallLoss / CrossEntropy on [B, C] mean AD logits (models.py:187-260, :535-541)."""
+
+    @staticmethod
+    def forward(ctx, logits, target, kind, weights):
+        loss, dl = ops.ad_loss(logits.float(), target, kind, weights, want_grad=ctx.needs_input_grad[0])
+        ctx.save_for_backward(dl)
+        return loss[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        return ops.scale_(dl.clone(), 1.0, g.reshape(1).float().contiguous()), None, None, None
+
+
+class CosFaceFn(torch.autograd.Function):
+    """AngularPenaltySMLoss('cosface') on cat(lm_masked, AD_masked) with labels 0/1 (models.py:131-185, :592-607)."""
+
+    @staticmethod
+    def forward(ctx, x1, x2, fc_w, s, m):
+        d = x1.shape[-1]
+        need = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
+        loss, dx1, dx2 = ops.cosface_fwd_bwd(x1.reshape(-1, d), x2.reshape(-1, d), fc_w.detach().float().contiguous(), s, m,
+                                             want_grad=need)
+        ctx.save_for_backward(dx1, dx2)
+        ctx.shape = x1.shape
+        return loss[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        dx1, dx2 = ctx.saved_tensors
+        if dx1 is None:
+            return None, None, None, None, None
+        gs = g.reshape(1).float().contiguous()
+        return (ops.scale_(dx1, 1.0, gs).view(ctx.shape), ops.scale_(dx2, 1.0, gs).view(ctx.shape), None, None, None)

@@ -1,0 +1,385 @@
+"""Drop-in nn.Modules for the reference's model classes (same sub-module names, state_dict keys, forward
+signature and return type), computing through the b200asr C-ABI kernels.
+
+  Data2VecAudioForCTC       <-> HF transformers Data2VecAudioForCTC as built at centralized/finetune_ASRs.py:164
+  DacsData2VecAudioForCTC   <-> federated/src/models.py:262-631 (and centralized/trainer_data2vec_2st.py:159-505)
+
+`load_state_dict(reference_model.state_dict())` works key for key.  Parameters stay fp32 (master weights);
+`compute_dtype` selects the activation / GEMM operand type (bf16 = tcgen05 path, fp32 = parity mode).
+"""
+from __future__ import annotations
+
+import contextlib
+import math
+import warnings
+from dataclasses import dataclass
+from typing import List, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from . import functional as Fn
+from . import ops
+
+try:  # the reference returns transformers' CausalLMOutput; use it when available so isinstance checks hold
+    from transformers.modeling_outputs import CausalLMOutput
+except Exception:  # pragma: no cover
+    @dataclass
+    class CausalLMOutput:  # type: ignore[no-redef]
+        loss: Optional[torch.Tensor] = None
+        logits: Optional[torch.Tensor] = None
+        hidden_states: Optional[Tuple[torch.Tensor, ...]] = None
+        attentions: Optional[Tuple[torch.Tensor, ...]] = None
+
+        def __getitem__(self, i):
+            return tuple(v for v in (self.loss, self.logits, self.hidden_states, self.attentions) if v is not None)[i]
+
+
+def _cfg(config, name, default):
+    return getattr(config, name, default)
+
+
+class _Affine(nn.Module):
+    """Parameter holder with the names nn.Linear / nn.Conv1d / nn.LayerNorm use (`weight`, `bias`)."""
+
+    def __init__(self, wshape, bias=True, kind="linear", std=0.02):
+        super().__init__()
+        w = torch.empty(*wshape)
+        if kind == "ln":
+            w.fill_(1.0)
+        elif kind == "conv":
+            nn.init.kaiming_normal_(w)
+        else:
+            w.normal_(0.0, std)
+        self.weight = nn.Parameter(w)
+        if bias:
+            self.bias = nn.Parameter(torch.zeros(wshape[0]))
+        else:
+            self.register_parameter("bias", None)
+
+
+class _ConvLayer(nn.Module):
+    def __init__(self, cin, cout, k, bias):
+        super().__init__()
+        self.conv = _Affine((cout, cin, k), bias=bias, kind="conv")
+        self.layer_norm = _Affine((cout,), kind="ln")
+
+
+class _FeatureExtractor(nn.Module):
+    def __init__(self, config):
+        super().__init__()
+        dims, ks = list(config.conv_dim), list(config.conv_kernel)
+        self.conv_layers = nn.ModuleList(
+            [_ConvLayer(1 if i == 0 else dims[i - 1], dims[i], ks[i], bool(_cfg(config, "conv_bias", False)))
+             for i in range(len(dims))])
+
+    def _freeze_parameters(self):
+        for p in self.parameters():
+            p.requires_grad = False
+
+
+class _FeatureProjection(nn.Module):
+    def __init__(self, config):
+        super().__init__()
+        self.layer_norm = _Affine((config.conv_dim[-1],), kind="ln")
+        self.projection = _Affine((config.hidden_size, config.conv_dim[-1]))
+
+
+class _PosConvLayer(nn.Module):
+    def __init__(self, config):
+        super().__init__()
+        d, g, k = config.hidden_size, config.num_conv_pos_embedding_groups, config.conv_pos_kernel_size
+        self.conv = _Affine((d, d // g, k), kind="conv")
+
+
+class _PosConvEmbed(nn.Module):
+    def __init__(self, config):
+        super().__init__()
+        self.layers = nn.ModuleList([_PosConvLayer(config) for _ in range(config.num_conv_pos_embeddings)])
+
+
+class _Attention(nn.Module):
+    def __init__(self, d):
+        super().__init__()
+        self.k_proj, self.v_proj, self.q_proj, self.out_proj = (_Affine((d, d)) for _ in range(4))
+
+
+class _FeedForward(nn.Module):
+    def __init__(self, d, f):
+        super().__init__()
+        self.intermediate_dense = _Affine((f, d))
+        self.output_dense = _Affine((d, f))
+
+
+class _EncoderLayer(nn.Module):
+    def __init__(self, config):
+        super().__init__()
+        d = config.hidden_size
+        self.attention = _Attention(d)
+        self.layer_norm = _Affine((d,), kind="ln")
+        self.feed_forward = _FeedForward(d, config.intermediate_size)
+        self.final_layer_norm = _Affine((d,), kind="ln")
+
+    def params(self):
+        a, f = self.attention, self.feed_forward
+        return (a.q_proj.weight, a.q_proj.bias, a.k_proj.weight, a.k_proj.bias, a.v_proj.weight, a.v_proj.bias,
+                a.out_proj.weight, a.out_proj.bias, self.layer_norm.weight, self.layer_norm.bias,
+                f.intermediate_dense.weight, f.intermediate_dense.bias, f.output_dense.weight, f.output_dense.bias,
+                self.final_layer_norm.weight, self.final_layer_norm.bias)
+
+
+class _Encoder(nn.Module):
+    def __init__(self, config):
+        super().__init__()
+        self.pos_conv_embed = _PosConvEmbed(config)
+        self.layer_norm = _Affine((config.hidden_size,), kind="ln")
+        self.layers = nn.ModuleList([_EncoderLayer(config) for _ in range(config.num_hidden_layers)])
+
+
+def conv_out_lengths(config, lengths: torch.Tensor) -> torch.Tensor:
+    """_get_feat_extract_output_lengths (HF:507-526; centralized/Models.py:249-271 with the integer-floor
+    semantics of the pinned torch 1.7.1): floor((len - k) / s) + 1 per conv layer."""
+    for k, s in zip(config.conv_kernel, config.conv_stride):
+        lengths = torch.div(lengths - k, s, rounding_mode="floor") + 1
+    return lengths
+
+
+class Data2VecAudioModel(nn.Module):
+    """`data2vec_audio` sub-module: feature extractor -> projection -> encoder (HF:744-800)."""
+
+    def __init__(self, config, compute_dtype=torch.bfloat16):
+        super().__init__()
+        self.config = config
+        self.feature_extractor = _FeatureExtractor(config)
+        self.feature_projection = _FeatureProjection(config)
+        self.encoder = _Encoder(config)
+        if _cfg(config, "mask_time_prob", 0.0) > 0.0 or _cfg(config, "mask_feature_prob", 0.0) > 0.0:
+            self.masked_spec_embed = nn.Parameter(torch.empty(config.hidden_size).uniform_())
+        self.cache = Fn.ShadowCache(compute_dtype)
+        self._warned = False
+
+    @property
+    def compute_dtype(self):
+        return self.cache.dtype
+
+    def set_compute_dtype(self, dtype):
+        self.cache = Fn.ShadowCache(dtype)
+
+    def _check_unsupported(self):
+        c = self.config
+        if self.training and not self._warned:
+            drops = [_cfg(c, n, 0.0) for n in ("hidden_dropout", "attention_dropout", "activation_dropout",
+                                               "feat_proj_dropout", "layerdrop")]
+            if any(d > 0 for d in drops):
+                warnings.warn("b200asr: dropout / LayerDrop are not applied by this build (treated as 0)")
+            self._warned = True
+        if self.training and _cfg(c, "mask_time_prob", 0.0) > 0.0 and _cfg(c, "apply_spec_augment", True):
+            raise NotImplementedError("SpecAugment (mask_time_prob > 0) is not supported; every reference entry "
+                                      "point sets mask_time_prob=0 (finetune_ASRs.py:162-163)")
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.feature_extractor.parameters()):
+            raise NotImplementedError("the conv feature extractor is forward-only: call freeze_feature_encoder() "
+                                      "as every reference entry point does (finetune_ASRs.py:200, models.py:302)")
+        if _cfg(c, "feat_extract_norm", "layer") != "layer":
+            raise NotImplementedError("feat_extract_norm='group' (wav2vec2-base GroupNorm stack) is not built yet")
+        if _cfg(c, "do_stable_layer_norm", False):
+            raise NotImplementedError("pre-LN (do_stable_layer_norm) encoder ordering is not built yet")
+
+    def forward(self, input_values, attention_mask=None, output_hidden_states=False):
+        """Returns (hidden [B,T,d] in compute dtype, frame_lengths int32 [B] or None, hidden_states tuple|None)."""
+        c = self.config
+        self._check_unsupported()
+        cache = self.cache
+        fe = self.feature_extractor.conv_layers
+        feats = Fn.feature_extractor_fwd(
+            input_values, [l.conv.weight for l in fe], [l.conv.bias for l in fe], [l.layer_norm.weight for l in fe],
+            [l.layer_norm.bias for l in fe], list(c.conv_kernel), list(c.conv_stride), 1e-5, cache)
+        B, T, _ = feats.shape
+        klen = None
+        if attention_mask is not None:
+            klen = conv_out_lengths(c, attention_mask.sum(-1)).to(torch.int32).contiguous()
+        fp = self.feature_projection
+        eps = float(_cfg(c, "layer_norm_eps", 1e-5))
+        h = Fn.FeatureProjectionFn.apply(feats, fp.layer_norm.weight, fp.layer_norm.bias, fp.projection.weight,
+                                         fp.projection.bias, eps, cache, klen)
+        enc = self.encoder
+        pcs = enc.pos_conv_embed.layers
+        h = Fn.PosConvEmbedFn.apply(h, enc.layer_norm.weight, enc.layer_norm.bias, eps,
+                                    int(c.num_conv_pos_embedding_groups), int(c.conv_pos_kernel_size), cache,
+                                    *[l.conv.weight for l in pcs], *[l.conv.bias for l in pcs])
+        d = h.shape[-1]
+        x = h.view(B * T, d)
+        collected = [h] if output_hidden_states else None
+        meta = (B, T, int(c.num_attention_heads), eps)
+        for layer in enc.layers:
+            x = Fn.EncoderLayerFn.apply(x, klen, meta, cache, *layer.params())
+            if collected is not None:
+                collected.append(x.view(B, T, d))
+        return x.view(B, T, d), klen, (tuple(collected) if collected is not None else None)
+
+
+def _ctc_index_tensors(config, input_values, attention_mask, labels, klen):
+    """models.py:486-496 / HF:884-895 without the host sync of `masked_select`: the padded label matrix is
+    consumed in place (row b starts at b*Lmax; valid labels are the row prefix, as the collators build them)."""
+    B, Lmax = labels.shape
+    if klen is None:
+        T = int(conv_out_lengths(config, torch.tensor(input_values.shape[-1])))
+        in_len = torch.full((B,), T, dtype=torch.int32, device=labels.device)
+    else:
+        in_len = klen
+    tgt_len = (labels >= 0).sum(-1).to(torch.int32)
+    tgt_off = torch.arange(B, dtype=torch.int32, device=labels.device) * Lmax
+    targets = labels.clamp(min=0).to(torch.int32).contiguous().view(-1)
+    return targets, tgt_off, tgt_len, in_len, Lmax
+
+
+class _CTCBase(nn.Module):
+    validate_labels = True  # reference raises ValueError on labels >= vocab_size (costs one host sync)
+
+    def freeze_feature_encoder(self):
+        self.data2vec_audio.feature_extractor._freeze_parameters()
+
+    freeze_feature_extractor = freeze_feature_encoder
+
+    def _ctc(self, logits, idx):
+        c = self.config
+        targets, tgt_off, tgt_len, in_len, lmax = idx
+        return Fn.CTCLossFn.apply(logits, targets, tgt_off, tgt_len, in_len, lmax, int(c.pad_token_id),
+                                  bool(_cfg(c, "ctc_zero_infinity", False)), _cfg(c, "ctc_loss_reduction", "sum"))
+
+    def _check_labels(self, labels):
+        if self.validate_labels and not torch.cuda.is_current_stream_capturing():
+            if int(labels.max()) >= self.config.vocab_size:
+                raise ValueError(f"Label values must be <= vocab_size: {self.config.vocab_size}")
+
+    @torch.no_grad()
+    def greedy_decode(self, logits, klen=None):
+        """argmax + repeat/blank collapse on device (finetune_ASRs.py:113-122); returns (ids, list of id lists)."""
+        ids, col, clen = ops.greedy_decode(logits, klen, int(self.config.pad_token_id))
+        col, clen = col.cpu(), clen.cpu()
+        return ids.long(), [col[b, : int(clen[b])].tolist() for b in range(col.shape[0])]
+
+
+class Data2VecAudioForCTC(_CTCBase):
+    """HF Data2VecAudioForCTC (HF:803-916) as instantiated by centralized/finetune_ASRs.py:164."""
+
+    def __init__(self, config, compute_dtype=torch.bfloat16):
+        super().__init__()
+        if config.vocab_size is None:
+            raise ValueError("config.vocab_size must be defined for the CTC head")
+        self.config = config
+        self.data2vec_audio = Data2VecAudioModel(config, compute_dtype)
+        self.lm_head = _Affine((config.vocab_size, config.hidden_size))
+
+    def forward(self, input_values, attention_mask=None, output_attentions=None, output_hidden_states=None,
+                return_dict=None, labels=None):
+        if output_attentions:
+            raise NotImplementedError("output_attentions is not available from the fused attention path")
+        if labels is not None:
+            self._check_labels(labels)
+        h, klen, hs = self.data2vec_audio(input_values, attention_mask, bool(output_hidden_states))
+        logits = Fn.LinearFn.apply(h, self.lm_head.weight, self.lm_head.bias, self.data2vec_audio.cache)
+        loss = None
+        if labels is not None:
+            loss = self._ctc(logits, _ctc_index_tensors(self.config, input_values, attention_mask, labels, klen))
+        if return_dict is False:
+            out = (logits,) + ((hs,) if hs is not None else ())
+            return ((loss,) + out) if loss is not None else out
+        return CausalLMOutput(loss=loss, logits=logits, hidden_states=hs, attentions=None)
+
+
+class _CosFaceHolder(nn.Module):
+    """`criterion_similar` (AngularPenaltySMLoss, models.py:131-185): holds fc.weight [2, d] (no bias)."""
+
+    def __init__(self, d):
+        super().__init__()
+        self.fc = _Affine((2, d), bias=False)
+        self.s, self.m = 30.0, 0.4
+
+
+class DacsData2VecAudioForCTC(_CTCBase):
+    """federated/src/models.py:262-631 `Data2VecAudioForCTC(config, args)`: encoder + arbitrator (toggling
+    network) + lm_head + dementia_head + CosFace; STAGE 0/1/2 freezing and loss selection (:304-323, :612-620).
+    `args` carries LAMBDA, TOGGLE_RATIO, GS_TAU, AD_loss, W_LOSS, STAGE (federated/src/options.py)."""
+
+    def __init__(self, config, args, compute_dtype=torch.bfloat16):
+        super().__init__()
+        if config.vocab_size is None:
+            raise ValueError("config.vocab_size must be defined for the CTC head")
+        self.config = config
+        d = config.hidden_size
+        self.data2vec_audio = Data2VecAudioModel(config, compute_dtype)
+        self.alpha = float(args.LAMBDA)
+        self.TOGGLE_RATIO = float(args.TOGGLE_RATIO)
+        self.GS_TAU = float(args.GS_TAU)
+        self.AD_loss = args.AD_loss
+        self.W_LOSS = [0.1, 0.9] if args.W_LOSS is None else list(args.W_LOSS)
+        self.STAGE = int(args.STAGE)
+        self.arbitrator = _Affine((4 * d, d))
+        self.lm_head = _Affine((config.vocab_size, d))
+        self.dementia_head = _Affine((2, d))
+        self.criterion_similar = _CosFaceHolder(d)
+        self.freeze_feature_encoder()
+        frozen = {0: ("dementia_head", "arbitrator", "criterion_similar"),
+                  1: ("data2vec_audio", "lm_head", "arbitrator", "criterion_similar"),
+                  2: ("data2vec_audio", "lm_head", "dementia_head", "criterion_similar")}[self.STAGE]
+        for name in frozen:
+            for p in getattr(self, name).parameters():
+                p.requires_grad = False
+        self.gumbel_seed = 0
+        self._gumbel_calls = 0
+
+    def _ad_weights(self):
+        if self.AD_loss == "recall":
+            return self.W_LOSS
+        if self.AD_loss == "prec":
+            return [0.1, 0.9]
+        return [0.5, 0.5]
+
+    def _ad(self, mean_logits, dementia_labels):
+        w = None if self.AD_loss == "cel" else self._ad_weights()
+        return Fn.AdLossFn.apply(mean_logits, dementia_labels, self.AD_loss, w)
+
+    def forward(self, input_values, attention_mask=None, output_attentions=None, output_hidden_states=None,
+                return_dict=None, labels=None, dementia_labels=None, gumbel_noise=None, return_masks=False):
+        """Same signature as models.py:375-384 plus two optional extras: `gumbel_noise=(g_lm, g_ad)` fp32
+        [B,T,d,2] externally drawn Gumbel samples (parity runs), `return_masks` for the `_eval` twin's dict."""
+        if output_attentions:
+            raise NotImplementedError("output_attentions is not available from the fused attention path")
+        c = self.config
+        cache = self.data2vec_audio.cache
+        if labels is not None:
+            self._check_labels(labels)
+        h, klen, hs = self.data2vec_audio(input_values, attention_mask, bool(output_hidden_states))
+        lin = lambda x, m: Fn.LinearFn.apply(x, m.weight, m.bias, cache)
+        stage = self.STAGE
+        g_lm, g_ad = gumbel_noise if gumbel_noise is not None else (None, None)
+        self._gumbel_calls += 1
+        # stages 0/1 only report the masked logits (their loss never touches the toggling branch): no graph needed
+        with (contextlib.nullcontext() if stage == 2 else torch.no_grad()):
+            score = lin(h, self.arbitrator)
+            lm_masked, ad_masked, lm_mask, ad_mask = Fn.DacsMaskFn.apply(
+                score, h, self.GS_TAU, self.TOGGLE_RATIO, g_lm, g_ad, self.gumbel_seed, self._gumbel_calls)
+            logits = lin(lm_masked, self.lm_head)  # the returned logits are always the lm-masked ones (:629-631)
+        final_loss = None
+        if labels is not None:
+            idx = _ctc_index_tensors(c, input_values, attention_mask, labels, klen)
+            if stage == 0:
+                final_loss = self._ctc(lin(h, self.lm_head), idx)
+            elif stage == 1:
+                final_loss = self._ad(Fn.MeanTimeFn.apply(lin(h, self.dementia_head)), dementia_labels)
+            else:
+                loss = self._ctc(logits, idx)
+                ad_rev = self._ad(Fn.GradReverseFn.apply(Fn.MeanTimeFn.apply(lin(lm_masked, self.dementia_head)), self.alpha),
+                                  dementia_labels)
+                loss_r = self._ctc(Fn.GradReverseFn.apply(lin(ad_masked, self.lm_head), self.alpha), idx)
+                ad = self._ad(Fn.MeanTimeFn.apply(lin(ad_masked, self.dementia_head)), dementia_labels)
+                cf = self.criterion_similar
+                score_loss = Fn.CosFaceFn.apply(lm_masked, ad_masked, cf.fc.weight, cf.s, cf.m)
+                final_loss = loss + ad_rev + loss_r + ad + score_loss
+        if return_masks:  # Data2VecAudioForCTC_eval (models.py:999-1004)
+            logits = {"ASR logits": logits, "dementia logits": lin(lm_masked, self.dementia_head), "hidden_states": h,
+                      "lm_mask": lm_mask, "dementia_mask": ad_mask}
+        if return_dict is False:
+            out = (logits,) + ((hs,) if hs is not None else ())
+            return ((final_loss,) + out) if final_loss is not None else out
+        return CausalLMOutput(loss=final_loss, logits=logits, hidden_states=hs, attentions=None)

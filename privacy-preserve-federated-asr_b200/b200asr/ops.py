@@ -1,0 +1,408 @@
+"""Raw (non-autograd) operators: torch tensors in, C-ABI calls on the current CUDA stream, torch tensors out.
+
+torch is used for device memory and streams only.  Every function requires CUDA tensors and raises if the
+library reports an error -- there is no eager fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import torch
+
+from . import _lib
+from ._lib import ACT_GELU, ACT_NONE, BF16, F32, GemmArgs, check, lib
+
+_DT = {torch.float32: F32, torch.bfloat16: BF16}
+
+
+def dt(t: torch.Tensor) -> int:
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise TypeError(f"b200asr supports float32 and bfloat16 tensors, got {t.dtype}") from None
+
+
+def _p(t: Optional[torch.Tensor]):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("b200asr operators need CUDA tensors (no CPU fallback)")
+    return t.data_ptr()
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _c(t: torch.Tensor) -> torch.Tensor:
+    return t if t.is_contiguous() else t.contiguous()
+
+
+_WS = {}
+
+
+def workspace(nbytes: int, device) -> torch.Tensor:
+    """Shared scratch buffer (all library calls are serialised on the current stream)."""
+    key = (torch.device(device).index, torch.cuda.is_current_stream_capturing())
+    buf = _WS.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
+        _WS[key] = buf
+    return buf
+
+
+# ----------------------------------------------------------------------------- norm / elementwise
+def layernorm_fwd(x, w, b, eps, res=None, act=ACT_NONE, want_sum=False, want_stats=True):
+    """y = act(LN(x (+res)) * w + b) over the last dim.  Returns (y, s_or_None, mean, rstd)."""
+    x = _c(x)
+    cols = x.shape[-1]
+    rows = x.numel() // cols
+    y = torch.empty_like(x)
+    s = torch.empty_like(x) if (want_sum and res is not None) else None
+    mean = torch.empty(rows, dtype=torch.float32, device=x.device) if want_stats else None
+    rstd = torch.empty(rows, dtype=torch.float32, device=x.device) if want_stats else None
+    if res is not None:
+        res = _c(res)
+    check(lib.b200asr_layernorm_fwd(_p(x), _p(res), _p(w), _p(b), _p(y), _p(s), _p(mean), _p(rstd), rows, cols,
+                                    float(eps), act, dt(x), _st()), "layernorm_fwd")
+    return y, s, mean, rstd
+
+
+def layernorm_bwd(dy, s, w, b, mean, rstd, act=ACT_NONE, dres_add=None, want_wgrad=True):
+    """Returns (dx, dw, db); dw/db are None when the LN has no affine or want_wgrad is False."""
+    dy = _c(dy)
+    s = _c(s)
+    cols = s.shape[-1]
+    rows = s.numel() // cols
+    dx = torch.empty_like(s)
+    dw = db = ws = None
+    nws = 0
+    if w is not None and want_wgrad:
+        dw = torch.empty(cols, dtype=torch.float32, device=s.device)
+        db = torch.empty(cols, dtype=torch.float32, device=s.device)
+        nws = lib.b200asr_layernorm_bwd_workspace_bytes(cols)
+        ws = workspace(nws, s.device)
+    check(lib.b200asr_layernorm_bwd(_p(dy), _p(s), _p(w), _p(b), _p(mean), _p(rstd), _p(dres_add), _p(dx), _p(dw),
+                                    _p(db), _p(ws), nws, rows, cols, act, dt(s), _st()), "layernorm_bwd")
+    return dx, dw, db
+
+
+def colsum(x: torch.Tensor) -> torch.Tensor:
+    """fp32 column sums of x viewed as [rows, cols] (bias gradient)."""
+    x = _c(x)
+    cols = x.shape[-1]
+    rows = x.numel() // cols
+    out = torch.empty(cols, dtype=torch.float32, device=x.device)
+    nws = lib.b200asr_colsum_workspace_bytes(cols)
+    ws = workspace(nws, x.device)
+    check(lib.b200asr_colsum(_p(x), _p(out), _p(ws), nws, rows, cols, cols, dt(x), _st()), "colsum")
+    return out
+
+
+def mask_frames_(x: torch.Tensor, lengths: torch.Tensor) -> torch.Tensor:
+    """x [B, T, C]: zero frames t >= lengths[b] in place."""
+    B, T, Cc = x.shape
+    assert x.is_contiguous() and lengths.dtype == torch.int32
+    check(lib.b200asr_mask_frames(_p(x), _p(lengths), B, T, Cc, dt(x), _st()), "mask_frames")
+    return x
+
+
+def cast_from_f32(src: torch.Tensor, dtype: torch.dtype, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    assert src.dtype == torch.float32
+    src = _c(src)
+    if out is None:
+        out = torch.empty(src.shape, dtype=dtype, device=src.device)
+    check(lib.b200asr_cast_f32(_p(src), _p(out), src.numel(), _DT[dtype], _st()), "cast_f32")
+    return out
+
+
+def cast_to_f32(src: torch.Tensor) -> torch.Tensor:
+    src = _c(src)
+    out = torch.empty(src.shape, dtype=torch.float32, device=src.device)
+    check(lib.b200asr_cast_to_f32(_p(src), _p(out), src.numel(), dt(src), _st()), "cast_to_f32")
+    return out
+
+
+def scale_(x: torch.Tensor, host_scale: float = 1.0, dev_scale: Optional[torch.Tensor] = None) -> torch.Tensor:
+    assert x.is_contiguous()
+    if dev_scale is not None:
+        assert dev_scale.dtype == torch.float32 and dev_scale.numel() == 1
+    check(lib.b200asr_scale(_p(x), x.numel(), float(host_scale), _p(dev_scale), dt(x), _st()), "scale")
+    return x
+
+
+def axpy_(y: torch.Tensor, x: torch.Tensor, alpha: float = 1.0) -> torch.Tensor:
+    assert y.is_contiguous() and x.is_contiguous() and y.dtype == x.dtype and y.numel() == x.numel()
+    check(lib.b200asr_axpy(_p(y), _p(x), float(alpha), y.numel(), dt(y), _st()), "axpy")
+    return y
+
+
+# ----------------------------------------------------------------------------- feature extractor layer 0
+def conv0_ln_gelu(x, w, bias, ln_w, ln_b, stride: int, eps: float, out_dtype: torch.dtype) -> torch.Tensor:
+    """x [B, L] fp32 -> [B, Tout, C] channels-last (HF:51-75, layer 0)."""
+    x = _c(x)
+    B, L = x.shape
+    Cc, cin, k = w.shape
+    assert cin == 1 and x.dtype == torch.float32
+    Tout = (L - k) // stride + 1
+    y = torch.empty(B, Tout, Cc, dtype=out_dtype, device=x.device)
+    check(lib.b200asr_conv0_ln_gelu_fwd(_p(x), _p(_c(w)), _p(bias), _p(ln_w), _p(ln_b), _p(y), B, L, Cc, k, stride,
+                                        float(eps), _DT[out_dtype], _st()), "conv0_ln_gelu_fwd")
+    return y
+
+
+# ----------------------------------------------------------------------------- GEMM
+def gemm_raw(A, B, Cout, M, N, K, lda, ldb, ldc, a_kmajor=True, b_kmajor=True, bias=None, residual=None,
+             aux_out=None, aux_in=None, act=ACT_NONE, mul_gelu_grad=False, alpha=1.0, batch0=1, batch1=1,
+             sa=(0, 0), sb=(0, 0), sc=(0, 0), a_off=0, b_off=0, c_off=0, backend: Optional[int] = None):
+    """C[m,n] = epi(sum_k A(m,k) B(n,k)); offsets in elements.  See include/b200asr.h b200asr_gemm."""
+    g = GemmArgs()
+    esa, esc = A.element_size(), Cout.element_size()
+    g.A = A.data_ptr() + a_off * esa
+    g.B = B.data_ptr() + b_off * esa
+    g.C = Cout.data_ptr() + c_off * esc
+    g.bias = _p(bias)
+    g.residual = (residual.data_ptr() + c_off * esc) if residual is not None else None
+    g.aux_out = (aux_out.data_ptr() + c_off * esc) if aux_out is not None else None
+    g.aux_in = (aux_in.data_ptr() + c_off * esc) if aux_in is not None else None
+    g.M, g.N, g.K = M, N, K
+    g.lda, g.ldb, g.ldc = lda, ldb, ldc
+    g.a_kmajor, g.b_kmajor = int(a_kmajor), int(b_kmajor)
+    g.act, g.mul_gelu_grad, g.alpha = act, int(mul_gelu_grad), float(alpha)
+    g.batch0, g.batch1 = batch0, batch1
+    g.sa0, g.sa1 = sa
+    g.sb0, g.sb1 = sb
+    g.sc0, g.sc1 = sc
+    assert A.dtype == B.dtype
+    g.dtype, g.c_dtype = dt(A), dt(Cout)
+    if bias is not None:
+        assert bias.dtype == torch.float32
+    if backend is None:
+        check(lib.b200asr_gemm(C.byref(g), _st()), "gemm")
+    else:
+        check(lib.b200asr_gemm_backend(C.byref(g), backend, _st()), "gemm_backend")
+    return Cout
+
+
+def linear_fwd(x, w, bias=None, act=ACT_NONE, residual=None, want_preact=False, out_dtype=None):
+    """y = act(x @ w.T + bias) (+ residual).  x [M, K], w [N, K] (same dtype).  Returns (y, preact_or_None)."""
+    x = _c(x)
+    M, K = x.shape
+    N = w.shape[0]
+    y = torch.empty(M, N, dtype=out_dtype or x.dtype, device=x.device)
+    pre = torch.empty_like(y) if want_preact else None
+    gemm_raw(x, w, y, M, N, K, K, K, N, True, True, bias=bias, residual=residual, aux_out=pre, act=act)
+    return y, pre
+
+
+def linear_dgrad(dy, w, residual=None, gelu_preact=None):
+    """dx = dy @ w  (* gelu'(preact)) (+ residual).  dy [M, N], w [N, K] -> [M, K]."""
+    dy = _c(dy)
+    M, N = dy.shape
+    K = w.shape[1]
+    dx = torch.empty(M, K, dtype=dy.dtype, device=dy.device)
+    gemm_raw(dy, w, dx, M, K, N, N, K, K, True, False, residual=residual, aux_in=gelu_preact,
+             mul_gelu_grad=gelu_preact is not None)
+    return dx
+
+
+def linear_wgrad(dy, x):
+    """dw = dy.T @ x in fp32.  dy [M, N], x [M, K] -> [N, K]."""
+    dy = _c(dy)
+    x = _c(x)
+    M, N = dy.shape
+    K = x.shape[1]
+    dw = torch.empty(N, K, dtype=torch.float32, device=dy.device)
+    gemm_raw(dy, x, dw, N, K, M, N, K, K, False, False)
+    return dw
+
+
+# ----------------------------------------------------------------------------- attention
+def mha_fwd(qkv, klen, B, T, H, dh, scale):
+    """qkv [B*T, 3*H*dh] packed; returns (ctx [B*T, H*dh], lse [B, H, T])."""
+    assert qkv.is_contiguous()
+    out = torch.empty(B * T, H * dh, dtype=qkv.dtype, device=qkv.device)
+    lse = torch.empty(B, H, T, dtype=torch.float32, device=qkv.device)
+    nws = lib.b200asr_mha_fwd_workspace_bytes(B, T, H, dh, dt(qkv))
+    ws = workspace(nws, qkv.device)
+    check(lib.b200asr_mha_fwd(_p(qkv), _p(out), _p(lse), _p(klen), _p(ws), nws, B, T, H, dh, float(scale), dt(qkv),
+                              _st()), "mha_fwd")
+    return out, lse
+
+
+def mha_bwd(qkv, out, dout, lse, klen, B, T, H, dh, scale):
+    dout = _c(dout)
+    dqkv = torch.empty_like(qkv)
+    nws = lib.b200asr_mha_bwd_workspace_bytes(B, T, H, dh, dt(qkv))
+    ws = workspace(nws, qkv.device)
+    check(lib.b200asr_mha_bwd(_p(qkv), _p(out), _p(dout), _p(lse), _p(klen), _p(dqkv), _p(ws), nws, B, T, H, dh,
+                              float(scale), dt(qkv), _st()), "mha_bwd")
+    return dqkv
+
+
+# ----------------------------------------------------------------------------- positional conv
+def posconv_pack(w: torch.Tensor, groups: int):
+    """HF weight [C, Cg, k] (compute dtype) -> (w_fwd, w_bwd) packed [groups, k, Cg, Cg]."""
+    w = _c(w)
+    Cc, Cg, k = w.shape
+    wf = torch.empty(groups, k, Cg, Cg, dtype=w.dtype, device=w.device)
+    wb = torch.empty_like(wf)
+    check(lib.b200asr_posconv_pack_weight(_p(w), _p(wf), _p(wb), Cc, groups, k, dt(w), _st()), "posconv_pack_weight")
+    return wf, wb
+
+
+def posconv_fwd(x, w_fwd, bias, groups, k):
+    x = _c(x)
+    B, T, Cc = x.shape
+    y = torch.empty_like(x)
+    check(lib.b200asr_posconv_fwd(_p(x), _p(w_fwd), _p(bias), _p(y), B, T, Cc, groups, k, dt(x), _st()), "posconv_fwd")
+    return y
+
+
+def posconv_bwd(x, w_bwd, dy, groups, k, want_dx=True, want_dw=True):
+    x, dy = _c(x), _c(dy)
+    B, T, Cc = x.shape
+    dx = torch.empty_like(x) if want_dx else None
+    dw = torch.empty(Cc, Cc // groups, k, dtype=torch.float32, device=x.device) if want_dw else None
+    check(lib.b200asr_posconv_bwd(_p(x), _p(w_bwd), _p(dy), _p(dx), _p(dw), B, T, Cc, groups, k, dt(x), _st()),
+          "posconv_bwd")
+    return dx, dw
+
+
+# ----------------------------------------------------------------------------- CTC / greedy decode
+def ctc_fwd_bwd(logits, targets, tgt_off, tgt_len, in_len, max_tgt_len, blank, zero_infinity, grad_scale=None,
+                want_grad=True):
+    """logits [n_heads, B, T, V]; int32 index tensors.  Returns (loss [n_heads, B] fp32, grad or None)."""
+    logits = _c(logits)
+    nh, B, T, V = logits.shape
+    loss = torch.empty(nh, B, dtype=torch.float32, device=logits.device)
+    grad = torch.empty_like(logits) if want_grad else None
+    nws = lib.b200asr_ctc_workspace_bytes(nh, B, T, max(1, max_tgt_len))
+    ws = workspace(nws, logits.device)
+    check(lib.b200asr_ctc_fwd_bwd(_p(logits), _p(targets), _p(tgt_off), _p(tgt_len), _p(in_len), _p(grad_scale),
+                                  _p(loss), _p(grad), _p(ws), nws, nh, B, T, V, max_tgt_len, blank,
+                                  int(bool(zero_infinity)), dt(logits), _st()), "ctc_fwd_bwd")
+    return loss, grad
+
+
+def greedy_decode(logits, in_len=None, blank=0):
+    """logits [B, T, V] -> (ids [B,T] int32, collapsed [B,T] int32 padded -1, collapsed_len [B] int32)."""
+    logits = _c(logits)
+    B, T, V = logits.shape
+    ids = torch.empty(B, T, dtype=torch.int32, device=logits.device)
+    col = torch.empty(B, T, dtype=torch.int32, device=logits.device)
+    clen = torch.empty(B, dtype=torch.int32, device=logits.device)
+    check(lib.b200asr_greedy_decode(_p(logits), _p(in_len), _p(ids), _p(col), _p(clen), B, T, V, blank, dt(logits),
+                                    _st()), "greedy_decode")
+    return ids, col, clen
+
+
+# ----------------------------------------------------------------------------- DACS
+def dacs_mask_fwd(scores, h, tau, toggle_ratio, noise_lm=None, noise_ad=None, seed=0, offset=0, want_masks=True):
+    """scores [M, 4d], h [M, d] -> (lm_masked, ad_masked, soft_lm, soft_ad, lm_mask, ad_mask)."""
+    scores, h = _c(scores), _c(h)
+    M, d = h.shape
+    outs = [torch.empty_like(h) for _ in range(6 if want_masks else 4)]
+    lm_mask, ad_mask = (outs[4], outs[5]) if want_masks else (None, None)
+    if noise_lm is not None:
+        assert noise_lm.dtype == torch.float32 and noise_ad.dtype == torch.float32
+        noise_lm, noise_ad = _c(noise_lm), _c(noise_ad)
+    check(lib.b200asr_dacs_mask_fwd(_p(scores), _p(h), _p(noise_lm), _p(noise_ad), _p(outs[0]), _p(outs[1]), _p(outs[2]),
+                                    _p(outs[3]), _p(lm_mask), _p(ad_mask), M, d, float(tau), float(toggle_ratio),
+                                    int(seed), int(offset), dt(h), _st()), "dacs_mask_fwd")
+    return outs[0], outs[1], outs[2], outs[3], lm_mask, ad_mask
+
+
+def dacs_mask_bwd(d_lm, d_ad, h, soft_lm, soft_ad, lm_mask, ad_mask, tau, toggle_ratio, want_dh=False):
+    d_lm, d_ad = _c(d_lm), _c(d_ad)
+    M, d = h.shape
+    d_scores = torch.empty(M, 4 * d, dtype=h.dtype, device=h.device)
+    dh = torch.empty_like(h) if want_dh else None
+    check(lib.b200asr_dacs_mask_bwd(_p(d_lm), _p(d_ad), _p(h), _p(soft_lm), _p(soft_ad), _p(lm_mask), _p(ad_mask),
+                                    _p(d_scores), _p(dh), M, d, float(tau), float(toggle_ratio), dt(h), _st()),
+          "dacs_mask_bwd")
+    return d_scores, dh
+
+
+def mean_time_fwd(x):
+    x = _c(x)
+    B, T, Cc = x.shape
+    out = torch.empty(B, Cc, dtype=torch.float32, device=x.device)
+    check(lib.b200asr_mean_time_fwd(_p(x), _p(out), B, T, Cc, dt(x), _st()), "mean_time_fwd")
+    return out
+
+
+def mean_time_bwd(dout, T, dtype, scale=1.0):
+    dout = _c(dout)
+    B, Cc = dout.shape
+    dx = torch.empty(B, T, Cc, dtype=dtype, device=dout.device)
+    check(lib.b200asr_mean_time_bwd(_p(dout), _p(dx), B, T, Cc, float(scale), _DT[dtype], _st()), "mean_time_bwd")
+    return dx
+
+
+AD_LOSS_KINDS = {"recall": 0, "prec": 1, "f1": 2, "recall_ori": 3, "prec_ori": 4, "cel": 5}
+
+
+def ad_loss(logits, target, kind: str, weights: Optional[Sequence[float]], want_grad=True):
+    """logits fp32 [B, C], target int64 [B] -> (loss [1] fp32, dlogits [B, C] or None)."""
+    logits = _c(logits)
+    B, Cc = logits.shape
+    assert logits.dtype == torch.float32 and target.dtype == torch.int64
+    loss = torch.empty(1, dtype=torch.float32, device=logits.device)
+    dl = torch.empty_like(logits) if want_grad else None
+    w = (C.c_float * Cc)(*[float(v) for v in weights]) if weights is not None else None
+    check(lib.b200asr_ad_loss(_p(logits), _p(target), _p(loss), _p(dl), B, Cc, AD_LOSS_KINDS[kind], w, _st()), "ad_loss")
+    return loss, dl
+
+
+def cosface_fwd_bwd(x1, x2, fc_w, s=30.0, m=0.4, want_grad=True):
+    x1, x2 = _c(x1), _c(x2)
+    n, d = x1.shape
+    loss = torch.empty(1, dtype=torch.float32, device=x1.device)
+    dx1 = torch.empty_like(x1) if want_grad else None
+    dx2 = torch.empty_like(x2) if want_grad else None
+    nws = 2 * n * 4
+    ws = workspace(nws, x1.device)
+    check(lib.b200asr_cosface_fwd_bwd(_p(x1), _p(x2), _p(fc_w), _p(loss), _p(dx1), _p(dx2), _p(ws), nws, n, d, float(s),
+                                      float(m), dt(x1), _st()), "cosface_fwd_bwd")
+    return loss, dx1, dx2
+
+
+# ----------------------------------------------------------------------------- FedAvg / optimizer
+def fedavg_scale_accum(inputs: Sequence[torch.Tensor], weights: Optional[Sequence[float]], out: torch.Tensor):
+    K = len(inputs)
+    n = out.numel()
+    for t in inputs:
+        assert t.dtype == torch.float32 and t.is_contiguous() and t.numel() == n and t.is_cuda
+    ptrs = (C.c_void_p * K)(*[t.data_ptr() for t in inputs])
+    w = (C.c_float * K)(*[float(v) for v in weights]) if weights is not None else None
+    check(lib.b200asr_fedavg_scale_accum(ptrs, w, _p(out), K, n, _st()), "fedavg_scale_accum")
+    return out
+
+
+def fedavg_prescale_(buf: torch.Tensor, w: float):
+    assert buf.dtype == torch.float32 and buf.is_contiguous()
+    check(lib.b200asr_fedavg_prescale(_p(buf), float(w), buf.numel(), _st()), "fedavg_prescale")
+    return buf
+
+
+def fedavg_peer_reduce(peer_ptrs: Sequence[int], weights: Optional[Sequence[float]], rank: int, n: int):
+    world = len(peer_ptrs)
+    ptrs = (C.c_void_p * world)(*[int(p) for p in peer_ptrs])
+    w = (C.c_float * world)(*[float(v) for v in weights]) if weights is not None else None
+    check(lib.b200asr_fedavg_peer_reduce(ptrs, w, world, rank, n, _st()), "fedavg_peer_reduce")
+
+
+def adamw_step_(p, grad, m, v, shadow, lr, beta1, beta2, eps, weight_decay, step, gnorm_sq=None, max_norm=1.0):
+    for t in (p, grad, m, v):
+        assert t.dtype == torch.float32 and t.is_contiguous()
+    check(lib.b200asr_adamw_step(_p(p), _p(grad), _p(m), _p(v), _p(shadow), p.numel(), float(lr), float(beta1),
+                                 float(beta2), float(eps), float(weight_decay), int(step), _p(gnorm_sq),
+                                 float(max_norm), _st()), "adamw_step")
+
+
+def sumsq_(x: torch.Tensor, out: torch.Tensor):
+    assert x.dtype == torch.float32 and x.is_contiguous() and out.dtype == torch.float32
+    check(lib.b200asr_sumsq(_p(x), x.numel(), _p(out), _st()), "sumsq")
+    return out

@@ -74,6 +74,13 @@ __global__ void scale_kernel(T* __restrict__ x, long long n, float hs, const flo
 }
 
 template <typename T>
+__global__ void axpy_kernel(T* __restrict__ y, const T* __restrict__ x, float alpha, long long n) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) y[i] = from_f<T>(to_f<T>(y[i]) + alpha * to_f<T>(x[i]));
+}
+
+template <typename T>
 __global__ void mask_frames_kernel(T* __restrict__ x, const int* __restrict__ lengths, int T_, int cols) {
     // grid: (frames, B); zero rows t >= lengths[b]
     const int b = blockIdx.y;
@@ -128,6 +135,15 @@ int b200asr_scale(void* x, long long n, float host_scale, const float* dev_scale
         scale_kernel<T><<<grid_for(n, 256), 256, 0, as_stream(stream)>>>((T*)x, n, host_scale, dev_scale);
     });
     return check_launch("scale");
+}
+
+int b200asr_axpy(void* y, const void* x, float alpha, long long n, int dtype, void* stream) {
+    if (n <= 0) return B200ASR_OK;
+    B200_REQUIRE(x && y, "axpy: null pointer");
+    B200_DISPATCH_DTYPE(dtype, {
+        axpy_kernel<T><<<grid_for(n, 256), 256, 0, as_stream(stream)>>>((T*)y, (const T*)x, alpha, n);
+    });
+    return check_launch("axpy");
 }
 
 int b200asr_mask_frames(void* x, const int* lengths, int B, int T_, int cols, int dtype, void* stream) {

@@ -1,0 +1,288 @@
+"""GPU parity, part 2: attention, positional conv, CTC, greedy decode, DACS kernels, FedAvg, AdamW."""
+import copy
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+if not torch.cuda.is_available():
+    pytest.skip("needs a CUDA device", allow_module_level=True)
+
+from b200asr import fedavg as FA  # noqa: E402
+from b200asr import ops  # noqa: E402
+from oracle import dacs_ref as D  # noqa: E402
+from oracle import data2vec_ref as R  # noqa: E402
+
+DEV = "cuda"
+
+
+def rel(a, b):
+    a, b = a.float().cpu(), b.float().cpu()
+    return float((a - b).abs().max() / max(float(b.abs().max()), 1e-6))
+
+
+# ----------------------------------------------------------------------------- attention
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,T,H,dh,masked", [(2, 37, 2, 64, True), (3, 130, 4, 64, True), (1, 249, 16, 64, False)])
+def test_mha_fwd_bwd(dtype, B, T, H, dh, masked):
+    g = torch.Generator().manual_seed(4)
+    D_ = H * dh
+    qkv = (torch.randn(B, T, 3, H, dh, generator=g)).to(dtype)
+    dout = torch.randn(B, T, D_, generator=g).to(dtype)
+    klen = torch.tensor([T] + [max(1, T - 7 * (i + 1)) for i in range(B - 1)], dtype=torch.int32) if masked else None
+    scale = dh ** -0.5
+    x = qkv.float().requires_grad_(True)
+    q, k, v = (x[:, :, i].transpose(1, 2) for i in range(3))  # [B,H,T,dh]
+    s = (q * scale) @ k.transpose(-1, -2)
+    if masked:
+        km = torch.arange(T)[None, :] < klen[:, None]
+        s = s.masked_fill(~km[:, None, None, :], torch.finfo(torch.float32).min)
+    ref = (torch.softmax(s, -1) @ v).transpose(1, 2).reshape(B, T, D_)
+    ref.backward(dout.float())
+    qd = qkv.reshape(B * T, 3 * D_).to(DEV)
+    kl = klen.to(DEV) if masked else None
+    out, lse = ops.mha_fwd(qd, kl, B, T, H, dh, scale)
+    t = 3e-5 if dtype == torch.float32 else 2e-2
+    assert rel(out.view(B, T, D_), ref.detach()) < t
+    dqkv = ops.mha_bwd(qd, out, dout.reshape(B * T, D_).to(DEV), lse, kl, B, T, H, dh, scale)
+    assert rel(dqkv.view(B, T, 3, H, dh), x.grad) < (1e-4 if dtype == torch.float32 else 3e-2)
+
+
+# ----------------------------------------------------------------------------- positional conv
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("C,groups,k,T", [(128, 2, 19, 50), (1024, 16, 19, 77), (128, 2, 128, 150)])
+def test_posconv_fwd_bwd(dtype, C, groups, k, T):
+    g = torch.Generator().manual_seed(5)
+    B = 2
+    Cg = C // groups
+    x = torch.randn(B, T, C, generator=g).to(dtype)
+    w = (torch.randn(C, Cg, k, generator=g) * (1.0 / math.sqrt(Cg * k))).to(dtype)
+    bias = torch.randn(C, generator=g) * 0.1
+    dy = torch.randn(B, T, C, generator=g).to(dtype)
+    xr, wr = x.float().requires_grad_(True), w.float().requires_grad_(True)
+    ref = F.conv1d(xr.transpose(1, 2), wr, bias, padding=k // 2, groups=groups)
+    if k % 2 == 0:
+        ref = ref[:, :, :-1]
+    ref = ref.transpose(1, 2)
+    ref.backward(dy.float())
+    wf, wb = ops.posconv_pack(w.to(DEV), groups)
+    y = ops.posconv_fwd(x.to(DEV), wf, bias.to(DEV), groups, k)
+    t = 3e-5 if dtype == torch.float32 else 2e-2
+    assert rel(y, ref.detach()) < t
+    dx, dw = ops.posconv_bwd(x.to(DEV), wb, dy.to(DEV), groups, k)
+    assert rel(dx, xr.grad) < t
+    assert rel(dw, wr.grad) < (1e-4 if dtype == torch.float32 else 2e-2)
+
+
+# ----------------------------------------------------------------------------- CTC
+def _ctc_case(dtype, B, T, V, lens, tlens, seed, zero_inf=True, repeat=False):
+    g = torch.Generator().manual_seed(seed)
+    logits = (torch.randn(B, T, V, generator=g) * 2).to(dtype)
+    Lmax = max(max(tlens), 1)
+    labels = torch.full((B, Lmax), -100, dtype=torch.long)
+    for b, n in enumerate(tlens):
+        lab = torch.randint(1, V, (n,), generator=g)
+        if repeat and n > 3:
+            lab[1] = lab[0]
+            lab[3] = lab[2]
+        labels[b, :n] = lab
+    il = torch.tensor(lens, dtype=torch.long)
+    tl = torch.tensor(tlens, dtype=torch.long)
+    lr = logits.float().requires_grad_(True)
+    lp = F.log_softmax(lr, -1).transpose(0, 1)
+    ref = F.ctc_loss(lp, labels.masked_select(labels >= 0), il, tl, blank=0, reduction="none", zero_infinity=zero_inf)
+    ref.sum().backward()
+    targets = labels.clamp(min=0).to(torch.int32).view(-1).to(DEV)
+    off = (torch.arange(B, dtype=torch.int32) * Lmax).to(DEV)
+    loss, grad = ops.ctc_fwd_bwd(logits.to(DEV).unsqueeze(0), targets, off, tl.to(torch.int32).to(DEV),
+                                 il.to(torch.int32).to(DEV), Lmax, 0, zero_inf)
+    t = 2e-5 if dtype == torch.float32 else 1e-3
+    np.testing.assert_allclose(loss[0].cpu().numpy(), ref.detach().numpy(), rtol=t, atol=1e-4)
+    assert rel(grad[0], lr.grad) < (1e-4 if dtype == torch.float32 else 1e-2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_ctc_matches_torch(dtype):
+    _ctc_case(dtype, 3, 50, 32, [50, 41, 30], [12, 7, 1], 0)
+    _ctc_case(dtype, 2, 60, 32, [60, 33], [20, 15], 1, repeat=True)
+    _ctc_case(dtype, 4, 499, 32, [499, 450, 300, 499], [120, 60, 20, 100], 2)  # config-2 shape: S up to 241
+    _ctc_case(dtype, 2, 40, 8, [40, 10], [5, 9], 3)                          # utterance 1 infeasible -> zero_infinity
+    _ctc_case(dtype, 2, 30, 40, [30, 30], [3, 0], 4)                         # empty target, V > 32
+
+
+def test_ctc_third_opinion_fp64():
+    g = torch.Generator().manual_seed(11)
+    T, V = 40, 12
+    logits = torch.randn(1, T, V, generator=g)
+    tgt = [3, 3, 5, 1, 1, 7]
+    nll, grad_lp = R.ctc_alpha_beta_numpy(F.log_softmax(logits[0], -1).numpy(), tgt)
+    loss, grad = ops.ctc_fwd_bwd(logits.to(DEV).unsqueeze(0), torch.tensor(tgt, dtype=torch.int32, device=DEV),
+                                 torch.zeros(1, dtype=torch.int32, device=DEV),
+                                 torch.tensor([len(tgt)], dtype=torch.int32, device=DEV),
+                                 torch.tensor([T], dtype=torch.int32, device=DEV), len(tgt), 0, True)
+    assert abs(float(loss[0, 0]) - nll) < 1e-4
+    p = torch.softmax(logits[0], -1).numpy()
+    g_logits = grad_lp - p * grad_lp.sum(-1, keepdims=True)
+    np.testing.assert_allclose(grad[0, 0].cpu().numpy(), g_logits, atol=3e-5)
+
+
+def test_greedy_decode():
+    g = torch.Generator().manual_seed(6)
+    logits = torch.randn(3, 64, 32, generator=g)
+    logits[0, 5] = logits[0, 4]  # force a repeat
+    ids_ref, seqs_ref = R.greedy_ids(logits)
+    ids, col, clen = ops.greedy_decode(logits.to(DEV))
+    assert torch.equal(ids.cpu().long(), ids_ref)
+    for b in range(3):
+        assert col[b, : int(clen[b])].cpu().tolist() == seqs_ref[b]
+    lens = torch.tensor([64, 10, 0], dtype=torch.int32, device=DEV)
+    _, col, clen = ops.greedy_decode(logits.to(DEV), lens)
+    _, s10 = R.greedy_ids(logits[1:2, :10])
+    assert col[1, : int(clen[1])].cpu().tolist() == s10[0] and int(clen[2]) == 0
+
+
+# ----------------------------------------------------------------------------- DACS
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("tau,ratio", [(1.0, 0.0), (0.5, 0.3)])
+def test_dacs_mask_fwd_bwd(dtype, tau, ratio):
+    g = torch.Generator().manual_seed(7)
+    M, d = 77, 128
+    scores = torch.randn(M, 4 * d, generator=g).to(dtype)
+    h = torch.randn(M, d, generator=g).to(dtype)
+    g_lm, g_ad = D.gen_gumbels((M, d, 2), 1), D.gen_gumbels((M, d, 2), 2)
+    dl, da = torch.randn(M, d, generator=g).to(dtype), torch.randn(M, d, generator=g).to(dtype)
+    sr, hr = scores.float().requires_grad_(True), h.float().requires_grad_(True)
+    lm_s = torch.stack((sr[:, :d], sr[:, d:2 * d]), -1)
+    ad_s = torch.stack((sr[:, 2 * d:3 * d], sr[:, 3 * d:]), -1)
+    if ratio:
+        lm_s = torch.stack(((lm_s[..., 1] - lm_s[..., 0]) * ratio + lm_s[..., 0], lm_s[..., 1]), -1)
+        ad_s = torch.stack(((ad_s[..., 1] - ad_s[..., 0]) * ratio + ad_s[..., 0], ad_s[..., 1]), -1)
+    lm_mask = D.gumbel_hard_mask(lm_s, g_lm, tau)
+    ad_mask = D.gumbel_hard_mask(ad_s, g_ad, tau)
+    ((lm_mask * hr) * dl.float()).sum().add(((ad_mask * hr) * da.float()).sum()).backward()
+    cu = lambda t: t.to(DEV)
+    lm, ad, sl, sa, ml, ma = ops.dacs_mask_fwd(cu(scores), cu(h), tau, ratio, cu(g_lm), cu(g_ad))
+    assert torch.equal(ml.float().cpu().round(), lm_mask.detach().round())
+    assert torch.equal(ma.float().cpu().round(), ad_mask.detach().round())
+    assert rel(lm, (lm_mask * hr).detach()) < (1e-6 if dtype == torch.float32 else 1e-2)
+    ds, dh = ops.dacs_mask_bwd(cu(dl), cu(da), cu(h), sl, sa, ml, ma, tau, ratio, want_dh=True)
+    t = 2e-5 if dtype == torch.float32 else 2e-2
+    assert rel(ds, sr.grad) < t
+    assert rel(dh, hr.grad) < t
+
+
+def test_dacs_mask_internal_rng_statistics():
+    M, d = 512, 256
+    scores = torch.zeros(M, 4 * d, device=DEV)
+    h = torch.ones(M, d, device=DEV)
+    lm, ad, sl, sa, ml, ma = ops.dacs_mask_fwd(scores, h, 1.0, 0.0, seed=123, offset=1)
+    assert abs(float(ml.mean()) - 0.5) < 0.01 and abs(float(ma.mean()) - 0.5) < 0.01
+    lm2 = ops.dacs_mask_fwd(scores, h, 1.0, 0.0, seed=123, offset=1)[0]
+    assert torch.equal(lm, lm2)
+    lm3 = ops.dacs_mask_fwd(scores, h, 1.0, 0.0, seed=123, offset=2)[0]
+    assert not torch.equal(lm, lm3)
+    assert abs(float((ml * ma).mean()) - 0.25) < 0.01  # lm / AD masks independent
+
+
+@pytest.mark.parametrize("kind", ["recall", "prec", "f1", "recall_ori", "prec_ori", "cel"])
+def test_ad_loss(kind):
+    g = torch.Generator().manual_seed(8)
+    x = torch.randn(6, 2, generator=g)
+    y = torch.tensor([0, 1, 1, 0, 1, 0])
+    xr = x.clone().requires_grad_(True)
+    w = [0.1, 0.9] if kind in ("recall", "prec") else [0.5, 0.5]
+    ref = F.cross_entropy(xr, y) if kind == "cel" else D.recall_loss(xr, y, w, kind)
+    ref.backward()
+    loss, dl = ops.ad_loss(x.to(DEV), y.to(DEV), kind, None if kind == "cel" else w)
+    assert abs(float(loss) - float(ref)) < 1e-5 * max(1, abs(float(ref)))
+    assert rel(dl, xr.grad) < 1e-4
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_mean_time_and_cosface(dtype):
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(3, 41, 2, generator=g).to(dtype)
+    assert rel(ops.mean_time_fwd(x.to(DEV)), x.float().mean(1)) < 1e-5
+    dout = torch.randn(3, 2, generator=g)
+    assert rel(ops.mean_time_bwd(dout.to(DEV), 41, dtype), (dout / 41)[:, None, :].expand(3, 41, 2)) < 1e-2
+    n, d = 50, 128
+    x1, x2 = torch.randn(n, d, generator=g).to(dtype), torch.randn(n, d, generator=g).to(dtype)
+    x1[3] = 0  # an all-zero row (a frame whose mask is all off) must stay finite
+    fc = torch.randn(2, d, generator=g) * 0.2
+    a, b = x1.float().requires_grad_(True), x2.float().requires_grad_(True)
+    labels = torch.cat((torch.zeros(n, dtype=torch.long), torch.ones(n, dtype=torch.long)))
+    ref = D.cosface_loss(torch.cat((a, b), 0), labels, fc)
+    ref.backward()
+    loss, d1, d2 = ops.cosface_fwd_bwd(x1.to(DEV), x2.to(DEV), fc.to(DEV))
+    t = 1e-5 if dtype == torch.float32 else 1e-3
+    assert abs(float(loss) - float(ref)) < t * max(1.0, abs(float(ref)))
+    assert rel(d1, a.grad) < (1e-4 if dtype == torch.float32 else 2e-2)
+    assert rel(d2, b.grad) < (1e-4 if dtype == torch.float32 else 2e-2)
+
+
+# ----------------------------------------------------------------------------- FedAvg / AdamW
+def test_fedavg_bit_exact_vs_reference_golden(golden_dir):
+    gold = np.load(os.path.join(golden_dir, "fedavg.npz"))
+    for n_clients in (2, 3, 8):
+        gen = torch.Generator().manual_seed(77 + n_clients)
+        ws = [{"a.weight": torch.randn(37, 19, generator=gen) * (1 + i), "a.bias": torch.randn(19, generator=gen),
+               "b.weight": torch.randn(5, 3, 7, generator=gen) * 1e-3} for i in range(n_clients)]
+        avg = FA.average_weights([{k: v.to(DEV) for k, v in w.items()} for w in ws])
+        for k, v in avg.items():
+            assert np.array_equal(v.cpu().numpy(), gold[f"n{n_clients}:{k}"]), (n_clients, k)
+        avg_cpu = FA.average_weights(ws)  # CPU state_dicts in, CPU out (the reference's calling convention)
+        for k, v in avg_cpu.items():
+            assert v.device.type == "cpu" and np.array_equal(v.numpy(), gold[f"n{n_clients}:{k}"])
+
+
+def test_fedavg_flat_weighted_and_large():
+    g = torch.Generator().manual_seed(10)
+    n = (1 << 22) + 3
+    xs = [torch.randn(n, generator=g) for _ in range(4)]
+    ref = D.average_weights([{"w": x} for x in xs])["w"]
+    out = FA.fedavg_local([x.to(DEV) for x in xs])
+    assert torch.equal(out.cpu(), ref)
+    w = [0.1, 0.2, 0.3, 0.4]
+    outw = FA.fedavg_local([x.to(DEV) for x in xs], w)
+    refw = sum(wi * x for wi, x in zip(w, xs))
+    assert rel(outw, refw) < 1e-6
+    # the fused peer kernel, emulated on one GPU: every "rank" reduces its slice of all buffers in place
+    bufs = [x.to(DEV).clone() for x in xs]
+    for r in range(4):
+        ops.fedavg_peer_reduce([b.data_ptr() for b in bufs], None, r, n)
+    torch.cuda.synchronize()
+    for b in bufs:
+        assert torch.equal(b.cpu(), ref)
+
+
+def test_adamw_matches_transformers_formula():
+    g = torch.Generator().manual_seed(12)
+    n = 10007
+    p = torch.randn(n, generator=g)
+    m, v = torch.zeros(n), torch.zeros(n)
+    pd, md, vd = p.to(DEV).clone(), m.to(DEV), v.to(DEV)
+    pad = lambda t: t  # noqa
+    lr, b1, b2, eps, wd = 1e-3, 0.9, 0.999, 1e-8, 0.005
+    for step in range(1, 4):
+        grad = torch.randn(n, generator=g) * 3
+        gn = grad.norm()
+        clip = min(1.0, 1.0 / (float(gn) + 1e-6))
+        gg = grad * clip
+        m = b1 * m + (1 - b1) * gg
+        v = b2 * v + (1 - b2) * gg * gg
+        step_size = lr * math.sqrt(1 - b2 ** step) / (1 - b1 ** step)
+        p = p - step_size * m / (v.sqrt() + eps)
+        p = p - lr * wd * p
+        gd = grad.to(DEV)
+        gsq = torch.zeros(1, device=DEV)
+        ops.sumsq_(gd, gsq)
+        assert abs(float(gsq.sqrt()) - float(gn)) < 1e-3 * float(gn)
+        shadow = torch.empty(n, dtype=torch.bfloat16, device=DEV)
+        ops.adamw_step_(pd, gd, md, vd, shadow, lr, b1, b2, eps, wd, step, gsq, 1.0)
+        assert rel(pd, p) < 1e-5
+        assert torch.equal(shadow.cpu(), pd.cpu().to(torch.bfloat16))
