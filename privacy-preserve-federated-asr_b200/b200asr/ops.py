@@ -41,6 +41,25 @@ def _c(t: torch.Tensor) -> torch.Tensor:
 
 _WS = {}
 
+# bench.py's roofline leg: when set to a list, every GEMM / attention call is bracketed by CUDA events on the
+# launching stream and (kind, start, end, flops) is appended.  None (the default) adds no work.
+PROFILE = None
+
+
+def _prof_begin():
+    if PROFILE is None:
+        return None
+    e = torch.cuda.Event(enable_timing=True)
+    e.record()
+    return e
+
+
+def _prof_end(kind, e0, flops):
+    if e0 is not None:
+        e1 = torch.cuda.Event(enable_timing=True)
+        e1.record()
+        PROFILE.append((kind, e0, e1, flops))
+
 
 def workspace(nbytes: int, device) -> torch.Tensor:
     """Shared scratch buffer (all library calls are serialised on the current stream)."""
@@ -178,10 +197,12 @@ def gemm_raw(A, B, Cout, M, N, K, lda, ldb, ldc, a_kmajor=True, b_kmajor=True, b
     g.dtype, g.c_dtype = dt(A), dt(Cout)
     if bias is not None:
         assert bias.dtype == torch.float32
+    e0 = _prof_begin()
     if backend is None:
         check(lib.b200asr_gemm(C.byref(g), _st()), "gemm")
     else:
         check(lib.b200asr_gemm_backend(C.byref(g), backend, _st()), "gemm_backend")
+    _prof_end("gemm", e0, 2.0 * M * N * K * batch0 * batch1)
     return Cout
 
 
@@ -226,8 +247,10 @@ def mha_fwd(qkv, klen, B, T, H, dh, scale):
     lse = torch.empty(B, H, T, dtype=torch.float32, device=qkv.device)
     nws = lib.b200asr_mha_fwd_workspace_bytes(B, T, H, dh, dt(qkv))
     ws = workspace(nws, qkv.device)
+    e0 = _prof_begin()
     check(lib.b200asr_mha_fwd(_p(qkv), _p(out), _p(lse), _p(klen), _p(ws), nws, B, T, H, dh, float(scale), dt(qkv),
                               _st()), "mha_fwd")
+    _prof_end("mha_fwd", e0, 4.0 * B * H * T * T * dh)
     return out, lse
 
 
@@ -236,8 +259,10 @@ def mha_bwd(qkv, out, dout, lse, klen, B, T, H, dh, scale):
     dqkv = torch.empty_like(qkv)
     nws = lib.b200asr_mha_bwd_workspace_bytes(B, T, H, dh, dt(qkv))
     ws = workspace(nws, qkv.device)
+    e0 = _prof_begin()
     check(lib.b200asr_mha_bwd(_p(qkv), _p(out), _p(dout), _p(lse), _p(klen), _p(dqkv), _p(ws), nws, B, T, H, dh,
                               float(scale), dt(qkv), _st()), "mha_bwd")
+    _prof_end("mha_bwd", e0, 10.0 * B * H * T * T * dh)
     return dqkv
 
 

@@ -261,10 +261,14 @@ __global__ void __launch_bounds__(256) cosface_kernel(const T* __restrict__ x1, 
             const float* Wy = fcw + (y ? d : 0);
             const float* Wo = fcw + (y ? 0 : d);
             const float inv = 1.0f / norm;
+            // F.normalize: x / max(||x||, eps).  Below eps the denominator is a constant, so the reference's
+            // autograd has no projection term there (d xn / dx = 1 / eps).
+            const bool clamped = sqrtf(nn) < 1e-12f;
             for (int c = lane; c < d; c += 32) {
                 const float xn = to_f<T>(x[c]) * inv;
-                const float g = (gy * (Wy[c] - xn * wy) + go * (Wo[c] - xn * wo)) * inv;
-                dx[c] = from_f<T>(sqrtf(nn) > 1e-12f ? g : 0.f);
+                const float g = clamped ? (gy * Wy[c] + go * Wo[c]) * inv
+                                        : (gy * (Wy[c] - xn * wy) + go * (Wo[c] - xn * wo)) * inv;
+                dx[c] = from_f<T>(g);
             }
         }
     }

@@ -67,6 +67,8 @@ def test_plain_ctc_vs_reference_golden(golden_dir, name, conv_bias, dtype):
         ref = g["grad:" + str(n)]
         assert relinf(params[str(n)].grad, ref) < gt, n
     for n, v in zip(g["gnorm_names"], g["gnorm_values"]):
+        if str(n).endswith("k_proj.bias"):
+            continue  # exactly zero in exact arithmetic (softmax shift invariance): both sides hold rounding noise only
         got = float(params[str(n)].grad.float().norm())
         assert abs(got - v) <= gt * max(v, 1e-3), (n, got, v)
 
