@@ -152,6 +152,9 @@ int b200asr_softmax_rows_bwd(void* p, void* dp, const float* lse, const int* kle
 size_t b200asr_mha_fwd_workspace_bytes(int B, int T, int H, int dh, int dtype);
 int b200asr_mha_fwd(const void* qkv, void* out, float* lse, const int* klen, void* workspace, size_t workspace_bytes,
                     int B, int T, int H, int dh, float scale, int dtype, void* stream);
+/* test hook: bf16 + head_dim 64 runs the fused tcgen05 flash-attention kernels; 0 forces the composed
+ * (batched GEMM + row softmax) path that fp32 parity mode and other head sizes use.  Returns the old setting. */
+int b200asr_mha_set_fused(int on);
 /* dqkv [B, T, 3, H, dh] (fully written).  workspace >= b200asr_mha_bwd_workspace_bytes(...). */
 size_t b200asr_mha_bwd_workspace_bytes(int B, int T, int H, int dh, int dtype);
 int b200asr_mha_bwd(const void* qkv, const void* out, const void* dout, const float* lse, const int* klen,

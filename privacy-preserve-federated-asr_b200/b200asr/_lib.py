@@ -57,6 +57,7 @@ SIGNATURES = {
     "b200asr_softmax_rows_bwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]),
     "b200asr_mha_fwd_workspace_bytes": (sz, [i32, i32, i32, i32, i32]),
     "b200asr_mha_fwd": (i32, [vp, vp, vp, vp, vp, sz, i32, i32, i32, i32, f32, i32, vp]),
+    "b200asr_mha_set_fused": (i32, [i32]),
     "b200asr_mha_bwd_workspace_bytes": (sz, [i32, i32, i32, i32, i32]),
     "b200asr_mha_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, sz, i32, i32, i32, i32, f32, i32, vp]),
     "b200asr_posconv_pack_weight": (i32, [vp, vp, vp, i32, i32, i32, i32, vp]),

@@ -2,6 +2,7 @@
 // (tcgen05 for bf16, fp32 FMA for parity mode) + row-softmax kernels, the scores living in a caller-provided
 // workspace; backward recomputes the probabilities from the saved log-sum-exp (no [B,H,T,T] tensor is kept
 // between forward and backward).
+#include "attn.h"
 #include "common.cuh"
 #include "gemm.h"
 
@@ -76,6 +77,8 @@ static int softmax_grid(long long rows) {
     return (int)(g < cap ? (g < 1 ? 1 : g) : cap);
 }
 
+static int g_mha_fused = 1;  // test hook (b200asr_mha_set_fused): 0 = composed GEMM + softmax path
+
 static int round_up8(int x) { return (x + 7) & ~7; }
 
 static size_t elem_size(int dtype) { return dtype == B200ASR_BF16 ? 2 : 4; }
@@ -130,6 +133,12 @@ int b200asr_softmax_rows_bwd(void* p, void* dp, const float* lse, const int* kle
     return check_launch("softmax_rows_bwd");
 }
 
+int b200asr_mha_set_fused(int on) {
+    const int old = g_mha_fused;
+    g_mha_fused = on ? 1 : 0;
+    return old;
+}
+
 size_t b200asr_mha_fwd_workspace_bytes(int B, int T, int H, int dh, int dtype) {
     (void)dh;
     return (size_t)B * H * T * round_up8(T) * elem_size(dtype);
@@ -141,6 +150,7 @@ int b200asr_mha_fwd(const void* qkv, void* out, float* lse, const int* klen, voi
     B200_REQUIRE(B > 0 && T > 0 && H > 0 && dh > 0 && dh % 8 == 0, "mha_fwd: bad shape");
     B200_REQUIRE(workspace_bytes >= b200asr_mha_fwd_workspace_bytes(B, T, H, dh, dtype), "mha_fwd: workspace too small");
     cudaStream_t st = as_stream(stream);
+    if (g_mha_fused && mha_tc_eligible(dtype, dh, qkv)) return mha_fwd_tc_launch(qkv, out, lse, klen, B, T, H, scale, st);
     const int D = H * dh, ldk = round_up8(T);
     const size_t es = elem_size(dtype);
     int rc = gemm_qk(qkv, workspace, B, T, H, dh, ldk, scale, dtype, st);
@@ -165,7 +175,7 @@ int b200asr_mha_fwd(const void* qkv, void* out, float* lse, const int* klen, voi
 
 size_t b200asr_mha_bwd_workspace_bytes(int B, int T, int H, int dh, int dtype) {
     (void)dh;
-    return 2 * (size_t)B * H * T * round_up8(T) * elem_size(dtype);
+    return 2 * (size_t)B * H * T * round_up8(T) * elem_size(dtype) + 512;
 }
 
 int b200asr_mha_bwd(const void* qkv, const void* out, const void* dout, const float* lse, const int* klen, void* dqkv,
@@ -176,6 +186,10 @@ int b200asr_mha_bwd(const void* qkv, const void* out, const void* dout, const fl
     B200_REQUIRE(B > 0 && T > 0 && H > 0 && dh > 0 && dh % 8 == 0, "mha_bwd: bad shape");
     B200_REQUIRE(workspace_bytes >= b200asr_mha_bwd_workspace_bytes(B, T, H, dh, dtype), "mha_bwd: workspace too small");
     cudaStream_t st = as_stream(stream);
+    if (g_mha_fused && mha_tc_eligible(dtype, dh, qkv) && ((reinterpret_cast<uintptr_t>(dout) | reinterpret_cast<uintptr_t>(dqkv)) & 15) == 0) {
+        B200_REQUIRE(out, "mha_bwd: the fused path needs the forward output");
+        return mha_bwd_tc_launch(qkv, out, dout, lse, klen, dqkv, workspace, B, T, H, scale, st);
+    }
     const int D = H * dh, ldk = round_up8(T);
     const size_t es = elem_size(dtype);
     const size_t plane = (size_t)B * H * T * ldk * es;

@@ -1,0 +1,647 @@
+// Fused multi-head self-attention on the 5th-generation tensor cores (bf16, head_dim 64), replacing the
+// bmm -> softmax -> bmm of Data2VecAudioAttention (HF:189-197) without ever materialising the [B,H,T,T]
+// probabilities in HBM on the forward pass.
+//
+// Forward  (one CTA = 128 queries of one (utterance, head); keys stream through in blocks of 64):
+//   warp 0      TMA producer: Q tile once, then a ring of {K_j, V_j} tiles (128B-swizzled boxes of the packed
+//               [B,T,3,H,dh] projection buffer, out-of-range frames zero-filled by TMA)
+//   warp 1      TMEM owner + single-thread tcgen05.mma issuer:  S_j = Q K_j^T  (double buffered in TMEM),
+//               O += P_j V_j
+//   warps 2..5  online softmax, one query row per thread (TMEM lane): tcgen05.ld S_j, running max / sum in the
+//               log2 domain, P_j -> bf16 -> swizzled shared memory (the A operand of the P V product),
+//               O rescale in TMEM only when a row maximum moved, final O / l -> bf16 -> HBM, log-sum-exp saved.
+// Backward (one CTA = 128 keys of one (utterance, head); queries stream through in blocks of 64):
+//   S^T = K_j Q_i^T and dP^T = V_j dO_i^T land in TMEM (double buffered); 8 element-wise warps rebuild
+//   P^T = exp2(S^T c - lse) and dS^T = P^T (dP^T - D) scale, one key row per thread (no cross-thread reduction
+//   is needed in this orientation), write both as bf16 A operands into swizzled shared memory and dS^T to HBM;
+//   dV += P^T dO_i and dK += dS^T Q_i accumulate in TMEM over the whole query loop.  dQ = dS K is one batched
+//   tcgen05 GEMM over the stored dS^T (it stays L2-resident between the two kernels at the sizes of this path).
+#include <cuda.h>
+
+#include "attn.h"
+#include "common.cuh"
+#include "gemm.h"
+#include "tc_ptx.cuh"
+
+namespace b200asr {
+namespace attn {
+
+using namespace tc;
+
+constexpr int DH = 64;
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float LN2 = 0.6931471805599453f;
+
+// ------------------------------------------------------------------------------------------ forward
+constexpr int FQ = 128;       // queries per CTA (= TMEM lanes)
+constexpr int FK = 64;        // keys per block
+constexpr int F_STAGES = 3;
+constexpr int F_THREADS = 192;
+constexpr int F_Q_BYTES = FQ * DH * 2;        // 16 KB
+constexpr int F_KV_BYTES = 2 * FK * DH * 2;   // K + V: 16 KB
+constexpr int F_P_BYTES = FQ * FK * 2;        // 16 KB
+constexpr int F_SMEM = F_Q_BYTES + F_STAGES * F_KV_BYTES + F_P_BYTES + 1024 + 256;
+constexpr int F_TMEM_COLS = 256;              // S[2] (2 x 64) + O (64) -> next power of two
+
+struct FwdParams {
+    __nv_bfloat16* out;
+    float* lse;
+    const int* klen;
+    int B, T, H;
+    float scale_log2;  // softmax scale * log2(e)
+};
+
+__global__ void __launch_bounds__(F_THREADS, 2)
+mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
+                  const __grid_constant__ CUtensorMap map_v, const FwdParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
+    const uint32_t sQ = base;
+    const uint32_t sKV = sQ + F_Q_BYTES;
+    const uint32_t sP = sKV + F_STAGES * F_KV_BYTES;
+    const uint32_t bars = sP + F_P_BYTES;
+    uint8_t* genP = gen + F_Q_BYTES + F_STAGES * F_KV_BYTES;
+    const uint32_t q_full = bars;
+    auto kv_full = [&](int s) { return bars + 8u * (1 + s); };
+    auto kv_empty = [&](int s) { return bars + 8u * (1 + F_STAGES + s); };
+    auto s_full = [&](int s) { return bars + 8u * (1 + 2 * F_STAGES + s); };
+    auto s_free = [&](int s) { return bars + 8u * (3 + 2 * F_STAGES + s); };
+    const uint32_t p_ready = bars + 8u * (5 + 2 * F_STAGES);
+    const uint32_t pv_done = bars + 8u * (6 + 2 * F_STAGES);
+    const uint32_t tmem_slot = bars + 8u * (7 + 2 * F_STAGES);
+    volatile uint32_t* tmem_slot_gen =
+        reinterpret_cast<volatile uint32_t*>(genP + F_P_BYTES + 8 * (7 + 2 * F_STAGES));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q0 = blockIdx.x * FQ, h = blockIdx.y, b = blockIdx.z;
+    const int T = p.T, H = p.H;
+    const int kl = p.klen ? min(max(p.klen[b], 0), T) : T;
+    const int nkb = (kl + FK - 1) / FK;
+    const int D = H * DH;
+
+    if (nkb == 0) {  // no valid key: probabilities are all zero (softmax_rows_kernel convention), lse = -inf
+        if (warp >= 2) {
+            const int row = (warp & 3) * 32 + lane, t = q0 + row;
+            if (t < T) {
+                uint4* o = reinterpret_cast<uint4*>(p.out + ((long long)b * T + t) * D + h * DH);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) o[c] = make_uint4(0, 0, 0, 0);
+                p.lse[((long long)b * H + h) * T + t] = -INFINITY;
+            }
+        }
+        return;
+    }
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_q);
+        tma_prefetch_desc(&map_k);
+        tma_prefetch_desc(&map_v);
+        mbar_init(q_full, 1);
+        for (int s = 0; s < F_STAGES; ++s) {
+            mbar_init(kv_full(s), 1);
+            mbar_init(kv_empty(s), 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(s_full(s), 1);
+            mbar_init(s_free(s), 4);
+        }
+        mbar_init(p_ready, 4);
+        mbar_init(pv_done, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, F_TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_gen;
+    const uint32_t tmem_o = tmem_base + 128;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(q_full, F_Q_BYTES);
+            tma_load_4d(sQ, &map_q, q_full, 0, q0, h, b);
+            for (int j = 0; j < nkb; ++j) {
+                const int s = j % F_STAGES;
+                mbar_wait(kv_empty(s), ((j / F_STAGES) & 1) ^ 1u);
+                mbar_expect_tx(kv_full(s), F_KV_BYTES);
+                tma_load_4d(sKV + s * F_KV_BYTES, &map_k, kv_full(s), 0, j * FK, h, b);
+                tma_load_4d(sKV + s * F_KV_BYTES + FK * DH * 2, &map_v, kv_full(s), 0, j * FK, h, b);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc_s = make_idesc_bf16(FQ, FK, 0, 0);
+            const uint32_t idesc_pv = make_idesc_bf16(FQ, DH, 0, 1);
+            auto issue_s = [&](int j) {
+                const int s = j % F_STAGES;
+                mbar_wait(kv_full(s), (j / F_STAGES) & 1);
+                if (j >= 2) mbar_wait(s_free(j & 1), ((j >> 1) - 1) & 1);
+                tc_fence_after();
+                const uint32_t sk = sKV + s * F_KV_BYTES;
+#pragma unroll
+                for (int k = 0; k < DH / 16; ++k)
+                    umma_bf16(tmem_base + (uint32_t)((j & 1) * FK), make_smem_desc(sQ + k * 32, 16, 1024),
+                              make_smem_desc(sk + k * 32, 16, 1024), idesc_s, k > 0 ? 1u : 0u);
+                umma_commit(s_full(j & 1));
+            };
+            mbar_wait(q_full, 0);
+            issue_s(0);
+            for (int j = 0; j < nkb; ++j) {
+                if (j + 1 < nkb) issue_s(j + 1);
+                mbar_wait(p_ready, j & 1);
+                tc_fence_after();
+                const int s = j % F_STAGES;
+                const uint32_t sv = sKV + s * F_KV_BYTES + FK * DH * 2;
+#pragma unroll
+                for (int k = 0; k < FK / 16; ++k)
+                    umma_bf16(tmem_o, make_smem_desc(sP + k * 32, 16, 1024), make_smem_desc(sv + k * 2048, 8192, 1024),
+                              idesc_pv, (j > 0 || k > 0) ? 1u : 0u);
+                umma_commit(kv_empty(s));
+                umma_commit(pv_done);
+            }
+        }
+    } else {
+        const int quarter = warp & 3;
+        const int row = quarter * 32 + lane;
+        const uint32_t tlane = tmem_base + ((uint32_t)(quarter * 32) << 16);
+        const uint32_t tlane_o = tlane + 128;
+        float m = -INFINITY, l = 0.f;
+        const float c2 = p.scale_log2;
+        for (int j = 0; j < nkb; ++j) {
+            mbar_wait(s_full(j & 1), (j >> 1) & 1);
+            tc_fence_after();
+            uint32_t r[64];
+            tmem_ld_32x32(tlane + (uint32_t)((j & 1) * FK), r);
+            tmem_ld_32x32(tlane + (uint32_t)((j & 1) * FK + 32), r + 32);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(s_free(j & 1));
+            const int nvalid = kl - j * FK;  // >= 1
+            float mx = -INFINITY;
+            if (nvalid >= FK) {
+#pragma unroll
+                for (int c = 0; c < FK; ++c) mx = fmaxf(mx, __uint_as_float(r[c]));
+            } else {
+#pragma unroll
+                for (int c = 0; c < FK; ++c) {
+                    if (c >= nvalid) r[c] = __float_as_uint(-INFINITY);
+                    mx = fmaxf(mx, __uint_as_float(r[c]));
+                }
+            }
+            const float m_new = fmaxf(m, mx * c2);
+            const float alpha = fast_exp2(m - m_new);
+            float sum = 0.f;
+            uint32_t pk[32];
+#pragma unroll
+            for (int c = 0; c < FK; c += 2) {
+                const float p0 = fast_exp2(fmaf(__uint_as_float(r[c]), c2, -m_new));
+                const float p1 = fast_exp2(fmaf(__uint_as_float(r[c + 1]), c2, -m_new));
+                sum += p0 + p1;
+                pk[c >> 1] = bf2_pack(p0, p1);
+            }
+            l = fmaf(l, alpha, sum);
+            m = m_new;
+            if (j > 0) {
+                mbar_wait(pv_done, (j - 1) & 1);
+                tc_fence_after();
+            }
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                *reinterpret_cast<uint4*>(genP + sw128_offset(row, c)) =
+                    make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+            if (j > 0 && __any_sync(0xffffffffu, alpha != 1.0f)) {
+#pragma unroll
+                for (int hh = 0; hh < 2; ++hh) {
+                    uint32_t o[32];
+                    tmem_ld_32x32(tlane_o + hh * 32, o);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * alpha);
+                    tmem_st_32x32(tlane_o + hh * 32, o);
+                }
+                tmem_st_wait();
+            }
+            fence_proxy_async();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(p_ready);
+        }
+        mbar_wait(pv_done, (nkb - 1) & 1);
+        tc_fence_after();
+        const int t = q0 + row;
+        const float inv = 1.0f / l;
+        __nv_bfloat16* orow = p.out + ((long long)b * T + t) * D + h * DH;
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            uint32_t o[32];
+            tmem_ld_32x32(tlane_o + hh * 32, o);
+            tmem_ld_wait();
+            if (t < T) {
+#pragma unroll
+                for (int c = 0; c < 32; c += 8) {
+                    uint4 v;
+                    v.x = bf2_pack(__uint_as_float(o[c]) * inv, __uint_as_float(o[c + 1]) * inv);
+                    v.y = bf2_pack(__uint_as_float(o[c + 2]) * inv, __uint_as_float(o[c + 3]) * inv);
+                    v.z = bf2_pack(__uint_as_float(o[c + 4]) * inv, __uint_as_float(o[c + 5]) * inv);
+                    v.w = bf2_pack(__uint_as_float(o[c + 6]) * inv, __uint_as_float(o[c + 7]) * inv);
+                    *reinterpret_cast<uint4*>(orow + hh * 32 + c) = v;
+                }
+            }
+        }
+        if (t < T) p.lse[((long long)b * H + h) * T + t] = (m + log2f(l)) * LN2;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, F_TMEM_COLS);
+    }
+}
+
+// ------------------------------------------------------------------------------------------ backward
+constexpr int BK = 128;       // keys per CTA (= TMEM lanes)
+constexpr int BQ = 64;        // queries per block
+constexpr int B_STAGES = 3;
+constexpr int B_THREADS = 320;  // TMA warp, MMA warp, 8 element-wise warps
+constexpr int B_KV_BYTES = 2 * BK * DH * 2;   // K_j + V_j: 32 KB
+constexpr int B_QD_BYTES = 2 * BQ * DH * 2;   // Q_i + dO_i: 16 KB
+constexpr int B_PT_BYTES = BK * BQ * 2;       // one P^T (or dS^T) operand tile: 16 KB
+constexpr int B_SMEM = B_KV_BYTES + B_STAGES * B_QD_BYTES + 4 * B_PT_BYTES + 1024 /*lse, D*/ + 1024 + 256;
+constexpr int B_TMEM_COLS = 512;  // S^T[2], dP^T[2] (4 x 64) + dV (64) + dK (64)
+
+struct BwdParams {
+    const float* lse;   // [B,H,T] natural-log sum-exp of the scaled logits
+    const float* dsum;  // [B,H,T] D = rowsum(dO * O)
+    const int* klen;
+    __nv_bfloat16* dqkv;  // [B,T,3,H,dh]: this kernel writes the K and V thirds
+    __nv_bfloat16* dst;   // dS^T [B,H,T(key),ldq] (scaled by `scale`)
+    int B, T, H, ldq;
+    float scale, scale_log2;
+};
+
+__global__ void __launch_bounds__(B_THREADS, 1)
+mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
+                  const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_do,
+                  const BwdParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
+    const uint32_t sK = base, sV = base + BK * DH * 2;
+    const uint32_t sQD = base + B_KV_BYTES;
+    const uint32_t sPT = sQD + B_STAGES * B_QD_BYTES;   // PT[0], PT[1], DST[0], DST[1]
+    uint8_t* genPT = gen + B_KV_BYTES + B_STAGES * B_QD_BYTES;
+    float* lseD = reinterpret_cast<float*>(genPT + 4 * B_PT_BYTES);  // [2][128]: lse*log2e (64) then D (64)
+    const uint32_t bars = sPT + 4 * B_PT_BYTES + 1024;
+    const uint32_t kv_full = bars;
+    auto qd_full = [&](int s) { return bars + 8u * (1 + s); };
+    auto qd_empty = [&](int s) { return bars + 8u * (1 + B_STAGES + s); };
+    auto sdp_full = [&](int s) { return bars + 8u * (1 + 2 * B_STAGES + s); };
+    auto sdp_free = [&](int s) { return bars + 8u * (3 + 2 * B_STAGES + s); };
+    auto pds_ready = [&](int s) { return bars + 8u * (5 + 2 * B_STAGES + s); };
+    auto pds_free = [&](int s) { return bars + 8u * (7 + 2 * B_STAGES + s); };
+    const uint32_t dkv_done = bars + 8u * (9 + 2 * B_STAGES);
+    const uint32_t tmem_slot = bars + 8u * (10 + 2 * B_STAGES);
+    volatile uint32_t* tmem_slot_gen =
+        reinterpret_cast<volatile uint32_t*>(genPT + 4 * B_PT_BYTES + 1024 + 8 * (10 + 2 * B_STAGES));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int k0 = blockIdx.x * BK, h = blockIdx.y, b = blockIdx.z;
+    const int T = p.T, H = p.H, ldq = p.ldq;
+    const int kl = p.klen ? min(max(p.klen[b], 0), T) : T;
+    const int nqb = (T + BQ - 1) / BQ;
+    const int D = H * DH;
+    const long long bh = (long long)b * H + h;
+
+    if (k0 >= kl) {  // fully masked key block: dK = dV = 0, dS^T rows = 0
+        if (warp >= 2) {
+            const int et = threadIdx.x - 64;  // 0..255: two threads per key row
+            const int row = et >> 1, half = et & 1, key = k0 + row;
+            if (key < T) {
+                __nv_bfloat16* dk = p.dqkv + (((long long)b * T + key) * 3 + 1) * D + h * DH + half * 32;
+                __nv_bfloat16* dv = dk + D;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    reinterpret_cast<uint4*>(dk)[c] = make_uint4(0, 0, 0, 0);
+                    reinterpret_cast<uint4*>(dv)[c] = make_uint4(0, 0, 0, 0);
+                }
+                uint4* drow = reinterpret_cast<uint4*>(p.dst + (bh * T + key) * ldq);
+                for (int c = half; c < ldq / 8; c += 2) drow[c] = make_uint4(0, 0, 0, 0);
+            }
+        }
+        return;
+    }
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_k);
+        tma_prefetch_desc(&map_v);
+        tma_prefetch_desc(&map_q);
+        tma_prefetch_desc(&map_do);
+        mbar_init(kv_full, 1);
+        for (int s = 0; s < B_STAGES; ++s) {
+            mbar_init(qd_full(s), 1);
+            mbar_init(qd_empty(s), 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(sdp_full(s), 1);
+            mbar_init(sdp_free(s), 8);
+            mbar_init(pds_ready(s), 8);
+            mbar_init(pds_free(s), 1);
+        }
+        mbar_init(dkv_done, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, B_TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_gen;
+    // TMEM columns: S^T[s] at 64 s, dP^T[s] at 128 + 64 s, dV at 256, dK at 320
+    const uint32_t tm_dv = tmem_base + 256, tm_dk = tmem_base + 320;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(kv_full, B_KV_BYTES);
+            tma_load_4d(sK, &map_k, kv_full, 0, k0, h, b);
+            tma_load_4d(sV, &map_v, kv_full, 0, k0, h, b);
+            for (int i = 0; i < nqb; ++i) {
+                const int s = i % B_STAGES;
+                mbar_wait(qd_empty(s), ((i / B_STAGES) & 1) ^ 1u);
+                mbar_expect_tx(qd_full(s), B_QD_BYTES);
+                tma_load_4d(sQD + s * B_QD_BYTES, &map_q, qd_full(s), 0, i * BQ, h, b);
+                tma_load_4d(sQD + s * B_QD_BYTES + BQ * DH * 2, &map_do, qd_full(s), 0, i * BQ, h, b);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc_kk = make_idesc_bf16(BK, BQ, 0, 0);  // S^T, dP^T: both operands K-major
+            const uint32_t idesc_km = make_idesc_bf16(BK, DH, 0, 1);  // dV, dK: B operand MN-major
+            auto issue_sdp = [&](int i) {
+                const int s = i % B_STAGES;
+                mbar_wait(qd_full(s), (i / B_STAGES) & 1);
+                if (i >= 2) mbar_wait(sdp_free(i & 1), ((i >> 1) - 1) & 1);
+                tc_fence_after();
+                const uint32_t sq = sQD + s * B_QD_BYTES, sdo = sq + BQ * DH * 2;
+                const uint32_t t_st = tmem_base + (uint32_t)((i & 1) * BQ), t_dp = tmem_base + 128 + (uint32_t)((i & 1) * BQ);
+#pragma unroll
+                for (int k = 0; k < DH / 16; ++k)
+                    umma_bf16(t_st, make_smem_desc(sK + k * 32, 16, 1024), make_smem_desc(sq + k * 32, 16, 1024), idesc_kk,
+                              k > 0 ? 1u : 0u);
+#pragma unroll
+                for (int k = 0; k < DH / 16; ++k)
+                    umma_bf16(t_dp, make_smem_desc(sV + k * 32, 16, 1024), make_smem_desc(sdo + k * 32, 16, 1024), idesc_kk,
+                              k > 0 ? 1u : 0u);
+                umma_commit(sdp_full(i & 1));
+            };
+            mbar_wait(kv_full, 0);
+            issue_sdp(0);
+            for (int i = 0; i < nqb; ++i) {
+                if (i + 1 < nqb) issue_sdp(i + 1);
+                mbar_wait(pds_ready(i & 1), (i >> 1) & 1);
+                tc_fence_after();
+                const int s = i % B_STAGES;
+                const uint32_t sq = sQD + s * B_QD_BYTES, sdo = sq + BQ * DH * 2;
+                const uint32_t spt = sPT + (i & 1) * B_PT_BYTES, sdst = sPT + (2 + (i & 1)) * B_PT_BYTES;
+#pragma unroll
+                for (int k = 0; k < BQ / 16; ++k)
+                    umma_bf16(tm_dv, make_smem_desc(spt + k * 32, 16, 1024), make_smem_desc(sdo + k * 2048, 8192, 1024),
+                              idesc_km, (i > 0 || k > 0) ? 1u : 0u);
+#pragma unroll
+                for (int k = 0; k < BQ / 16; ++k)
+                    umma_bf16(tm_dk, make_smem_desc(sdst + k * 32, 16, 1024), make_smem_desc(sq + k * 2048, 8192, 1024),
+                              idesc_km, (i > 0 || k > 0) ? 1u : 0u);
+                umma_commit(qd_empty(s));
+                umma_commit(pds_free(i & 1));
+            }
+            umma_commit(dkv_done);
+        }
+    } else {
+        const int quarter = warp & 3, half = (warp - 2) >> 2;
+        const int row = quarter * 32 + lane;
+        const int key = k0 + row;
+        const bool key_valid = key < kl;
+        const int et = threadIdx.x - 64;  // 0..255
+        const uint32_t tlane = tmem_base + ((uint32_t)(quarter * 32) << 16);
+        const float c2 = p.scale_log2, sc = p.scale;
+        __nv_bfloat16* dst_row = p.dst + (bh * T + key) * ldq;
+        for (int i = 0; i < nqb; ++i) {
+            const int slot = i & 1;
+            if (et < 128) {
+                const int q = i * BQ + (et & 63);
+                float v;
+                if (et < 64) v = (q < T) ? p.lse[bh * T + q] * LOG2E : INFINITY;
+                else v = (q < T) ? p.dsum[bh * T + q] : 0.f;
+                lseD[slot * 128 + et] = v;
+            }
+            named_bar_sync(1, 256);
+            mbar_wait(sdp_full(slot), (i >> 1) & 1);
+            tc_fence_after();
+            uint32_t s[32], dp[32];
+            tmem_ld_32x32(tlane + (uint32_t)(slot * BQ + half * 32), s);
+            tmem_ld_32x32(tlane + 128 + (uint32_t)(slot * BQ + half * 32), dp);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sdp_free(slot));
+            uint32_t pp[16], dd[16];
+            const float* l2 = lseD + slot * 128 + half * 32;
+            const float* dq = l2 + 64;
+#pragma unroll
+            for (int c = 0; c < 32; c += 2) {
+                float p0 = fast_exp2(fmaf(__uint_as_float(s[c]), c2, -l2[c]));
+                float p1 = fast_exp2(fmaf(__uint_as_float(s[c + 1]), c2, -l2[c + 1]));
+                if (!key_valid) p0 = p1 = 0.f;
+                const float d0 = p0 * (__uint_as_float(dp[c]) - dq[c]) * sc;
+                const float d1 = p1 * (__uint_as_float(dp[c + 1]) - dq[c + 1]) * sc;
+                pp[c >> 1] = bf2_pack(p0, p1);
+                dd[c >> 1] = bf2_pack(d0, d1);
+            }
+            if (i >= 2) mbar_wait(pds_free(slot), ((i >> 1) - 1) & 1);
+            uint8_t* gpt = genPT + slot * B_PT_BYTES;
+            uint8_t* gds = genPT + (2 + slot) * B_PT_BYTES;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const uint32_t off = sw128_offset(row, half * 4 + c);
+                *reinterpret_cast<uint4*>(gpt + off) = make_uint4(pp[4 * c], pp[4 * c + 1], pp[4 * c + 2], pp[4 * c + 3]);
+                *reinterpret_cast<uint4*>(gds + off) = make_uint4(dd[4 * c], dd[4 * c + 1], dd[4 * c + 2], dd[4 * c + 3]);
+            }
+            if (key < T) {
+                const int qb = i * BQ + half * 32;
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    if (qb + 8 * c + 8 <= ldq)
+                        *reinterpret_cast<uint4*>(dst_row + qb + 8 * c) =
+                            make_uint4(dd[4 * c], dd[4 * c + 1], dd[4 * c + 2], dd[4 * c + 3]);
+            }
+            fence_proxy_async();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(pds_ready(slot));
+        }
+        mbar_wait(dkv_done, 0);
+        tc_fence_after();
+        uint32_t a[32], c_[32];
+        tmem_ld_32x32(tlane + 256 + (uint32_t)(half * 32), a);   // dV
+        tmem_ld_32x32(tlane + 320 + (uint32_t)(half * 32), c_);  // dK
+        tmem_ld_wait();
+        if (key < T) {
+            __nv_bfloat16* dk = p.dqkv + (((long long)b * T + key) * 3 + 1) * D + h * DH + half * 32;
+            __nv_bfloat16* dv = dk + D;
+#pragma unroll
+            for (int c = 0; c < 32; c += 8) {
+                uint4 v;
+                v.x = bf2_pack(__uint_as_float(a[c]), __uint_as_float(a[c + 1]));
+                v.y = bf2_pack(__uint_as_float(a[c + 2]), __uint_as_float(a[c + 3]));
+                v.z = bf2_pack(__uint_as_float(a[c + 4]), __uint_as_float(a[c + 5]));
+                v.w = bf2_pack(__uint_as_float(a[c + 6]), __uint_as_float(a[c + 7]));
+                *reinterpret_cast<uint4*>(dv + c) = v;
+                v.x = bf2_pack(__uint_as_float(c_[c]), __uint_as_float(c_[c + 1]));
+                v.y = bf2_pack(__uint_as_float(c_[c + 2]), __uint_as_float(c_[c + 3]));
+                v.z = bf2_pack(__uint_as_float(c_[c + 4]), __uint_as_float(c_[c + 5]));
+                v.w = bf2_pack(__uint_as_float(c_[c + 6]), __uint_as_float(c_[c + 7]));
+                *reinterpret_cast<uint4*>(dk + c) = v;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, B_TMEM_COLS);
+    }
+}
+
+// D[b,h,t] = sum_c dO[b,t,h,c] * O[b,t,h,c]   (one warp per frame, 8 lanes per head per 256-column sweep)
+__global__ void __launch_bounds__(256) mha_bwd_dsum_kernel(const __nv_bfloat16* __restrict__ o,
+                                                           const __nv_bfloat16* __restrict__ dout,
+                                                           float* __restrict__ dsum, int B, int T, int H) {
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    const int D = H * DH;
+    for (long long f = warp; f < (long long)B * T; f += nwarps) {
+        const int b = (int)(f / T), t = (int)(f % T);
+        const __nv_bfloat16* op = o + f * D;
+        const __nv_bfloat16* dp = dout + f * D;
+        for (int c0 = 0; c0 < D; c0 += 256) {
+            const int c = c0 + lane * 8;
+            float acc = 0.f;
+            if (c < D) {
+                Vec16<__nv_bfloat16> a, g;
+                float af[8], gf[8];
+                a.load(op + c);
+                g.load(dp + c);
+                a.unpack(af);
+                g.unpack(gf);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc = fmaf(af[j], gf[j], acc);
+            }
+            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+            if ((lane & 7) == 0 && c < D) dsum[((long long)b * H + c / DH) * T + t] = acc;
+        }
+    }
+}
+
+static int make_head_map(CUtensorMap* map, const void* base, int T, int H, int B, long long row_stride_elems,
+                         long long batch_stride_elems, int box_rows, const char* what) {
+    const cuuint64_t dims[4] = {(cuuint64_t)DH, (cuuint64_t)T, (cuuint64_t)H, (cuuint64_t)B};
+    const cuuint64_t strides[3] = {(cuuint64_t)row_stride_elems * 2, (cuuint64_t)DH * 2, (cuuint64_t)batch_stride_elems * 2};
+    const cuuint32_t box[4] = {(cuuint32_t)DH, (cuuint32_t)box_rows, 1, 1};
+    return encode_map_bf16_4d(map, base, dims, strides, box, what);
+}
+
+}  // namespace attn
+
+bool mha_tc_eligible(int dtype, int dh, const void* qkv) {
+    return dtype == B200ASR_BF16 && dh == attn::DH && (reinterpret_cast<uintptr_t>(qkv) & 15) == 0;
+}
+
+int mha_fwd_tc_launch(const void* qkv, void* out, float* lse, const int* klen, int B, int T, int H, float scale,
+                      cudaStream_t st) {
+    using namespace attn;
+    const int D = H * DH;
+    const __nv_bfloat16* q = (const __nv_bfloat16*)qkv;
+    CUtensorMap mq, mk, mv;
+    int rc = make_head_map(&mq, q, T, H, B, 3LL * D, (long long)T * 3 * D, FQ, "mha_fwd(tcgen05)");
+    if (rc) return rc;
+    rc = make_head_map(&mk, q + D, T, H, B, 3LL * D, (long long)T * 3 * D, FK, "mha_fwd(tcgen05)");
+    if (rc) return rc;
+    rc = make_head_map(&mv, q + 2 * D, T, H, B, 3LL * D, (long long)T * 3 * D, FK, "mha_fwd(tcgen05)");
+    if (rc) return rc;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(mha_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM);
+        if (e != cudaSuccess) {
+            set_error("mha_fwd(tcgen05): cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+            return B200ASR_ERR_CUDA;
+        }
+        attr_set = true;
+    }
+    FwdParams p;
+    p.out = (__nv_bfloat16*)out; p.lse = lse; p.klen = klen; p.B = B; p.T = T; p.H = H;
+    p.scale_log2 = scale * LOG2E;
+    dim3 grid(ceil_div(T, FQ), H, B);
+    mha_fwd_tc_kernel<<<grid, F_THREADS, F_SMEM, st>>>(mq, mk, mv, p);
+    return check_launch("mha_fwd_tcgen05");
+}
+
+size_t mha_bwd_tc_workspace_bytes(int B, int T, int H) {
+    const size_t ldq = (size_t)((T + 7) & ~7);
+    return (size_t)B * H * T * ldq * 2 + (((size_t)B * H * T * 4 + 255) & ~(size_t)255);
+}
+
+int mha_bwd_tc_launch(const void* qkv, const void* out, const void* dout, const float* lse, const int* klen, void* dqkv,
+                      void* workspace, int B, int T, int H, float scale, cudaStream_t st) {
+    using namespace attn;
+    const int D = H * DH;
+    const int ldq = (T + 7) & ~7;
+    const __nv_bfloat16* q = (const __nv_bfloat16*)qkv;
+    float* dsum = (float*)workspace;
+    __nv_bfloat16* dst = (__nv_bfloat16*)((char*)workspace + (((size_t)B * H * T * 4 + 255) & ~(size_t)255));
+    {
+        long long frames = (long long)B * T;
+        long long g = (frames + 7) / 8;
+        if (g > (long long)num_sms() * 8) g = (long long)num_sms() * 8;
+        mha_bwd_dsum_kernel<<<(int)g, 256, 0, st>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, dsum, B, T, H);
+        int rc = check_launch("mha_bwd_dsum");
+        if (rc) return rc;
+    }
+    CUtensorMap mk, mv, mq, mdo;
+    int rc = make_head_map(&mk, q + D, T, H, B, 3LL * D, (long long)T * 3 * D, BK, "mha_bwd(tcgen05)");
+    if (rc) return rc;
+    rc = make_head_map(&mv, q + 2 * D, T, H, B, 3LL * D, (long long)T * 3 * D, BK, "mha_bwd(tcgen05)");
+    if (rc) return rc;
+    rc = make_head_map(&mq, q, T, H, B, 3LL * D, (long long)T * 3 * D, BQ, "mha_bwd(tcgen05)");
+    if (rc) return rc;
+    rc = make_head_map(&mdo, dout, T, H, B, (long long)D, (long long)T * D, BQ, "mha_bwd(tcgen05)");
+    if (rc) return rc;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(mha_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
+        if (e != cudaSuccess) {
+            set_error("mha_bwd(tcgen05): cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+            return B200ASR_ERR_CUDA;
+        }
+        attr_set = true;
+    }
+    BwdParams p;
+    p.lse = lse; p.dsum = dsum; p.klen = klen; p.dqkv = (__nv_bfloat16*)dqkv; p.dst = dst;
+    p.B = B; p.T = T; p.H = H; p.ldq = ldq; p.scale = scale; p.scale_log2 = scale * LOG2E;
+    dim3 grid(ceil_div(T, BK), H, B);
+    mha_bwd_tc_kernel<<<grid, B_THREADS, B_SMEM, st>>>(mk, mv, mq, mdo, p);
+    rc = check_launch("mha_bwd_tcgen05");
+    if (rc) return rc;
+    // dQ[q, n] = sum_key dS^T[key, q] K[key, n]   (dS already carries the softmax scale)
+    b200asr_gemm_args g = {};
+    g.dtype = B200ASR_BF16; g.c_dtype = B200ASR_BF16; g.batch0 = H; g.batch1 = B; g.alpha = 1.f;
+    g.A = dst; g.B = q + D; g.C = dqkv;
+    g.M = T; g.N = DH; g.K = T; g.lda = ldq; g.ldb = 3 * D; g.ldc = 3 * D; g.a_kmajor = 0; g.b_kmajor = 0;
+    g.sa0 = (long long)T * ldq; g.sa1 = (long long)H * T * ldq; g.sb0 = DH; g.sb1 = (long long)T * 3 * D;
+    g.sc0 = DH; g.sc1 = (long long)T * 3 * D;
+    return gemm_dispatch(g, st);
+}
+
+}  // namespace b200asr

@@ -187,18 +187,35 @@ __global__ void __launch_bounds__(128) ln_bwd_kernel(const T* __restrict__ dy, c
     }
 }
 
-// out[c] = sum_{p < nparts} partial[p * stride + c]
-__global__ void reduce_partials_kernel(const float* __restrict__ partial, float* __restrict__ out0,
-                                       float* __restrict__ out1, int nparts, int cols, int stride) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= cols) return;
-    float a0 = 0.f, a1 = 0.f;
-    for (int p = 0; p < nparts; ++p) {
-        a0 += partial[(long long)p * stride + c];
-        if (out1) a1 += partial[(long long)p * stride + cols + c];
+// out[c] = sum_{p < nparts} partial[p * stride + c] for c < ncols_total; columns [0, cols) go to out0, [cols, 2 cols)
+// to out1.  One block = 32 columns x 8 warps; warp w sums partials w, w+8, ... (coalesced 128-byte rows, 4 loads
+// in flight per thread), then a fixed-order shared-memory combine: deterministic.
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ partial, float* __restrict__ out0,
+                                                              float* __restrict__ out1, int nparts, int cols,
+                                                              int ncols_total, int stride) {
+    __shared__ float red[8][33];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + lane;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    if (c < ncols_total) {
+        int p = w;
+        for (; p + 24 < nparts; p += 32) {
+            a0 += partial[(long long)p * stride + c];
+            a1 += partial[(long long)(p + 8) * stride + c];
+            a2 += partial[(long long)(p + 16) * stride + c];
+            a3 += partial[(long long)(p + 24) * stride + c];
+        }
+        for (; p < nparts; p += 8) a0 += partial[(long long)p * stride + c];
     }
-    if (out0) out0[c] = a0;
-    if (out1) out1[c] = a1;
+    red[w][lane] = (a0 + a1) + (a2 + a3);
+    __syncthreads();
+    if (w == 0 && c < ncols_total) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += red[i][lane];
+        if (c < cols) { if (out0) out0[c] = t; }
+        else if (out1) out1[c - cols] = t;
+    }
 }
 
 template <typename T>
@@ -308,8 +325,8 @@ int b200asr_layernorm_bwd(const void* dy, const void* s, const float* w, const f
     });
     if (rc != B200ASR_OK) return rc;
     if (partial) {
-        reduce_partials_kernel<<<ceil_div(cols, 128), 128, 0, as_stream(stream)>>>(partial, dw, db, LN_BWD_BLOCKS,
-                                                                                   cols, 2 * cols);
+        reduce_partials_kernel<<<ceil_div(2 * cols, 32), 256, 0, as_stream(stream)>>>(partial, dw, db, LN_BWD_BLOCKS, cols,
+                                                                                      2 * cols, 2 * cols);
         return check_launch("layernorm_bwd_reduce");
     }
     return B200ASR_OK;
@@ -332,8 +349,8 @@ int b200asr_colsum(const void* x, float* out, void* workspace, size_t workspace_
     });
     int rc = check_launch("colsum_partial");
     if (rc != B200ASR_OK) return rc;
-    reduce_partials_kernel<<<ceil_div(cols, 128), 128, 0, as_stream(stream)>>>((const float*)workspace, out, nullptr,
-                                                                               nchunks, cols, cols);
+    reduce_partials_kernel<<<ceil_div(cols, 32), 256, 0, as_stream(stream)>>>((const float*)workspace, out, nullptr,
+                                                                              nchunks, cols, cols, cols);
     return check_launch("colsum_reduce");
 }
 

@@ -53,6 +53,64 @@ def test_mha_fwd_bwd(dtype, B, T, H, dh, masked):
     assert rel(dqkv.view(B, T, 3, H, dh), x.grad) < (1e-4 if dtype == torch.float32 else 3e-2)
 
 
+def _mha_ref(qkv, dout, klen, scale):
+    B, T, _, H, dh = qkv.shape
+    x = qkv.float().requires_grad_(True)
+    q, k, v = (x[:, :, i].transpose(1, 2) for i in range(3))
+    s = (q * scale) @ k.transpose(-1, -2)
+    if klen is not None:
+        km = torch.arange(T)[None, :] < klen[:, None]
+        s = s.masked_fill(~km[:, None, None, :], torch.finfo(torch.float32).min)
+    ref = (torch.softmax(s, -1) @ v).transpose(1, 2).reshape(B, T, H * dh)
+    ref.backward(dout.float())
+    return ref.detach(), x.grad
+
+
+@pytest.mark.parametrize("fused", [1, 0])
+@pytest.mark.parametrize("B,T,H,klens", [
+    (2, 499, 3, None),                 # BASELINE configs[1] frame count, all keys valid
+    (3, 499, 2, [499, 300, 64]),       # ragged: key blocks partly / fully masked
+    (2, 128, 2, [128, 1]),             # exact tile, single valid key
+    (1, 1499, 2, [1311]),              # 30 s utterances (configs[4]): 12 query tiles x 21 key blocks
+    (2, 65, 1, [65, 64]),              # one frame past a block boundary
+    (2, 8, 16, None),                  # tiny T
+])
+def test_mha_bf16_fused_vs_composed(fused, B, T, H, klens):
+    """bf16, head_dim 64: the fused tcgen05 flash kernels (fused=1) and the composed GEMM+softmax path (fused=0)
+    against the fp32 eager reference of HF:189-197."""
+    from b200asr._lib import lib
+    g = torch.Generator().manual_seed(40 + T)
+    dh, D_ = 64, H * 64
+    qkv = torch.randn(B, T, 3, H, dh, generator=g).to(torch.bfloat16)
+    dout = torch.randn(B, T, D_, generator=g).to(torch.bfloat16)
+    klen = torch.tensor(klens, dtype=torch.int32) if klens is not None else None
+    scale = dh ** -0.5
+    ref, gref = _mha_ref(qkv, dout, klen, scale)
+    old = lib.b200asr_mha_set_fused(fused)
+    try:
+        qd = qkv.reshape(B * T, 3 * D_).to(DEV)
+        kl = klen.to(DEV) if klen is not None else None
+        out, lse = ops.mha_fwd(qd, kl, B, T, H, dh, scale)
+        dqkv = ops.mha_bwd(qd, out, dout.reshape(B * T, D_).to(DEV), lse, kl, B, T, H, dh, scale)
+        torch.cuda.synchronize()
+    finally:
+        lib.b200asr_mha_set_fused(old)
+    assert rel(out.view(B, T, D_), ref) < 2e-2
+    # log-sum-exp of the scaled logits (saved for backward) against fp32
+    x = qkv.float()
+    s = (x[:, :, 0].transpose(1, 2) * scale) @ x[:, :, 1].transpose(1, 2).transpose(-1, -2)
+    if klen is not None:
+        km = torch.arange(T)[None, :] < klen[:, None]
+        s = s.masked_fill(~km[:, None, None, :], float("-inf"))
+    assert float((lse.cpu() - torch.logsumexp(s, -1)).abs().max()) < 2e-2
+    got = dqkv.view(B, T, 3, H, dh).float().cpu()
+    for i, name in enumerate("qkv"):
+        assert rel(got[:, :, i], gref[:, :, i]) < 3e-2, name
+    if klen is not None:  # masked keys receive exactly zero gradient
+        for b in range(B):
+            assert float(got[b, int(klen[b]):, 1:].abs().max() if int(klen[b]) < T else 0.0) == 0.0
+
+
 # ----------------------------------------------------------------------------- positional conv
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("C,groups,k,T", [(128, 2, 19, 50), (1024, 16, 19, 77), (128, 2, 128, 150)])
