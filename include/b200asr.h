@@ -32,7 +32,7 @@ extern "C" {
 #define B200ASR_F32 0
 #define B200ASR_BF16 1
 
-#define B200ASR_ABI_VERSION 1
+#define B200ASR_ABI_VERSION 2
 
 /* activation codes */
 #define B200ASR_ACT_NONE 0
@@ -166,16 +166,19 @@ int b200asr_mha_bwd(const void* qkv, const void* out, const void* dout, const fl
  * x[b, t+j-k/2, g*Cg+i]  (zero padding; for even k the reference drops the last frame, which equals
  * computing only t < T).  Channels-last x, y [B, T, C] (dtype).
  * Weights are consumed in a packed layout produced once per weight update by b200asr_posconv_pack_weight
- * from the HF layout w [C, Cg, k] (dtype): w_fwd [groups][k][Cg in][Cg out], w_bwd [groups][k][Cg out][Cg in].
+ * from the HF layout w [C, Cg, k] (dtype) into two buffers of C*Cg*k elements each (an internal layout: tap-major
+ * K-major rows for the tcgen05 implicit GEMM when Cg == 64 and dtype is bf16, [groups][k][Cg][Cg] otherwise).
  */
 int b200asr_posconv_pack_weight(const void* w, void* w_fwd, void* w_bwd, int C, int groups, int k, int dtype,
                                 void* stream);
 int b200asr_posconv_fwd(const void* x, const void* w_fwd, const float* bias, void* y, int B, int T, int C, int groups,
                         int k, int dtype, void* stream);
 /* dx [B,T,C] (dtype) and dw fp32 [C, Cg, k] (HF layout; overwritten); dbias via b200asr_colsum.  Either output
- * may be NULL. */
-int b200asr_posconv_bwd(const void* x, const void* w_bwd, const void* dy, void* dx, float* dw, int B, int T, int C,
-                        int groups, int k, int dtype, void* stream);
+ * may be NULL.  workspace >= b200asr_posconv_bwd_workspace_bytes(...) (tap-major staging of the tensor-core weight
+ * gradient; only needed when dw != NULL). */
+size_t b200asr_posconv_bwd_workspace_bytes(int C, int groups, int k);
+int b200asr_posconv_bwd(const void* x, const void* w_bwd, const void* dy, void* dx, float* dw, void* workspace,
+                        size_t workspace_bytes, int B, int T, int C, int groups, int k, int dtype, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * CTC: log_softmax(fp32) + alpha/beta recursions + gradient w.r.t. the logits, one launch for `n_heads`

@@ -62,7 +62,8 @@ SIGNATURES = {
     "b200asr_mha_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, sz, i32, i32, i32, i32, f32, i32, vp]),
     "b200asr_posconv_pack_weight": (i32, [vp, vp, vp, i32, i32, i32, i32, vp]),
     "b200asr_posconv_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]),
-    "b200asr_posconv_bwd": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]),
+    "b200asr_posconv_bwd_workspace_bytes": (sz, [i32, i32, i32]),
+    "b200asr_posconv_bwd": (i32, [vp, vp, vp, vp, vp, vp, sz, i32, i32, i32, i32, i32, i32, vp]),
     "b200asr_ctc_workspace_bytes": (sz, [i32, i32, i32, i32]),
     "b200asr_ctc_fwd_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, sz, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "b200asr_greedy_decode": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]),

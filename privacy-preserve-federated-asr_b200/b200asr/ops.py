@@ -88,8 +88,9 @@ def layernorm_fwd(x, w, b, eps, res=None, act=ACT_NONE, want_sum=False, want_sta
     return y, s, mean, rstd
 
 
-def layernorm_bwd(dy, s, w, b, mean, rstd, act=ACT_NONE, dres_add=None, want_wgrad=True):
-    """Returns (dx, dw, db); dw/db are None when the LN has no affine or want_wgrad is False."""
+def layernorm_bwd(dy, s, w, b, mean, rstd, act=ACT_NONE, dres_add=None, want_wgrad=True, dw_out=None, db_out=None):
+    """Returns (dx, dw, db); dw/db are None when the LN has no affine or want_wgrad is False.
+    dw_out/db_out: optional preallocated fp32 [cols] destinations (overwritten)."""
     dy = _c(dy)
     s = _c(s)
     cols = s.shape[-1]
@@ -98,8 +99,8 @@ def layernorm_bwd(dy, s, w, b, mean, rstd, act=ACT_NONE, dres_add=None, want_wgr
     dw = db = ws = None
     nws = 0
     if w is not None and want_wgrad:
-        dw = torch.empty(cols, dtype=torch.float32, device=s.device)
-        db = torch.empty(cols, dtype=torch.float32, device=s.device)
+        dw = dw_out if dw_out is not None else torch.empty(cols, dtype=torch.float32, device=s.device)
+        db = db_out if db_out is not None else torch.empty(cols, dtype=torch.float32, device=s.device)
         nws = lib.b200asr_layernorm_bwd_workspace_bytes(cols)
         ws = workspace(nws, s.device)
     check(lib.b200asr_layernorm_bwd(_p(dy), _p(s), _p(w), _p(b), _p(mean), _p(rstd), _p(dres_add), _p(dx), _p(dw),
@@ -107,12 +108,13 @@ def layernorm_bwd(dy, s, w, b, mean, rstd, act=ACT_NONE, dres_add=None, want_wgr
     return dx, dw, db
 
 
-def colsum(x: torch.Tensor) -> torch.Tensor:
-    """fp32 column sums of x viewed as [rows, cols] (bias gradient)."""
+def colsum(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """fp32 column sums of x viewed as [rows, cols] (bias gradient); `out` fp32 [cols] is overwritten if given."""
     x = _c(x)
     cols = x.shape[-1]
     rows = x.numel() // cols
-    out = torch.empty(cols, dtype=torch.float32, device=x.device)
+    if out is None:
+        out = torch.empty(cols, dtype=torch.float32, device=x.device)
     nws = lib.b200asr_colsum_workspace_bytes(cols)
     ws = workspace(nws, x.device)
     check(lib.b200asr_colsum(_p(x), _p(out), _p(ws), nws, rows, cols, cols, dt(x), _st()), "colsum")
@@ -228,14 +230,15 @@ def linear_dgrad(dy, w, residual=None, gelu_preact=None):
     return dx
 
 
-def linear_wgrad(dy, x):
-    """dw = dy.T @ x in fp32.  dy [M, N], x [M, K] -> [N, K]."""
+def linear_wgrad(dy, x, out=None, accumulate=False):
+    """dw = dy.T @ x in fp32.  dy [M, N], x [M, K] -> [N, K].  `out` (fp32, contiguous [N, K]) receives the result
+    (added to its contents when `accumulate`: the epilogue's residual operand aliases the output)."""
     dy = _c(dy)
     x = _c(x)
     M, N = dy.shape
     K = x.shape[1]
-    dw = torch.empty(N, K, dtype=torch.float32, device=dy.device)
-    gemm_raw(dy, x, dw, N, K, M, N, K, K, False, False)
+    dw = out if out is not None else torch.empty(N, K, dtype=torch.float32, device=dy.device)
+    gemm_raw(dy, x, dw, N, K, M, N, K, K, False, False, residual=dw if (accumulate and out is not None) else None)
     return dw
 
 
@@ -285,13 +288,17 @@ def posconv_fwd(x, w_fwd, bias, groups, k):
     return y
 
 
-def posconv_bwd(x, w_bwd, dy, groups, k, want_dx=True, want_dw=True):
+def posconv_bwd(x, w_bwd, dy, groups, k, want_dx=True, want_dw=True, dw_out=None):
     x, dy = _c(x), _c(dy)
     B, T, Cc = x.shape
     dx = torch.empty_like(x) if want_dx else None
-    dw = torch.empty(Cc, Cc // groups, k, dtype=torch.float32, device=x.device) if want_dw else None
-    check(lib.b200asr_posconv_bwd(_p(x), _p(w_bwd), _p(dy), _p(dx), _p(dw), B, T, Cc, groups, k, dt(x), _st()),
-          "posconv_bwd")
+    dw = None
+    if want_dw:
+        dw = dw_out if dw_out is not None else torch.empty(Cc, Cc // groups, k, dtype=torch.float32, device=x.device)
+    nws = lib.b200asr_posconv_bwd_workspace_bytes(Cc, groups, k) if want_dw else 0
+    ws = workspace(nws, x.device) if want_dw else None
+    check(lib.b200asr_posconv_bwd(_p(x), _p(w_bwd), _p(dy), _p(dx), _p(dw), _p(ws), nws, B, T, Cc, groups, k, dt(x),
+                                  _st()), "posconv_bwd")
     return dx, dw
 
 

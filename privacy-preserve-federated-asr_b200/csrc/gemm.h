@@ -11,6 +11,12 @@ int gemm_simt_launch(const b200asr_gemm_args& a, cudaStream_t st);
 bool gemm_tc_eligible(const b200asr_gemm_args& a, const char** why);
 int gemm_tc_launch(const b200asr_gemm_args& a, cudaStream_t st);
 
+// grouped positional conv (64 channels per group, bf16) on the tcgen05 GEMM kernel's conv addressing modes
+int posconv_tc_taps(const void* x, const void* w_pack, const float* bias, void* y, int B, int T, int C, int groups, int k,
+                    int tap_pad, cudaStream_t st);
+int posconv_tc_wgrad(const void* x, const void* dy, float* dwt, int B, int T, int C, int groups, int k, int pad,
+                     cudaStream_t st);
+
 // internal convenience used by the composed attention path
 int gemm_dispatch(const b200asr_gemm_args& a, cudaStream_t st);
 

@@ -44,6 +44,14 @@ struct Params {
     long long sc0, sc1;
     int tiles_m, tiles_n;
     long long num_tiles;
+    // operand addressing mode of the TMA producer
+    //   0  plain GEMM
+    //   1  convolution taps (grouped positional conv forward / data gradient): K-block kb is filter tap kb; the A rows
+    //      of that block are the activation frames m0 + kb - tap_pad (out-of-range frames zero-filled by TMA)
+    //   2  convolution weight gradient: both operands MN-major, K runs over (utterance, 64-frame block); N-block nb is
+    //      filter tap nb, whose B rows are the activation frames t0 + nb - tap_pad
+    int mode, tap_pad, tblocks, num_kb;
+    long long bias_sb0;  // bias element stride per batch0 index (grouped conv: channels per group)
 };
 
 template <typename TC> __device__ __forceinline__ void store_row_chunk(TC* dst, const float* v, int ncols_valid, bool vec_ok);
@@ -142,7 +150,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_gen;
 
-    const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+    const int num_kb = p.num_kb;
     const long long tiles_per_batch = (long long)p.tiles_m * p.tiles_n;
 
     if (warp == 0) {
@@ -162,6 +170,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                     const uint32_t sa = smem_base + stage * C_::STAGE_BYTES;
                     const uint32_t sb = sa + A_STAGE_BYTES;
                     const int k0 = kb * BLOCK_K;
+                    if (p.mode != 0) {
+                        if (p.mode == 1) {
+                            tma_load_4d(sa, &tma_a, full_bar(stage), 0, m0 + kb - p.tap_pad, b0, b1);
+                            tma_load_4d(sb, &tma_b, full_bar(stage), k0, n0, b0, 0);
+                        } else {
+                            const int bb = kb / p.tblocks, t0 = (kb % p.tblocks) * BLOCK_K;
+#pragma unroll
+                            for (int c = 0; c < BLOCK_M / 64; ++c)
+                                tma_load_4d(sa + c * (64 * BLOCK_K * 2), &tma_a, full_bar(stage), m0 + 64 * c, t0, b0, bb);
+                            tma_load_4d(sb, &tma_b, full_bar(stage), 0, t0 + nb - p.tap_pad, b0, bb);
+                        }
+                        if (++stage == C_::STAGES) { stage = 0; phase ^= 1u; }
+                        continue;
+                    }
                     if (!p.a_mn) {
                         tma_load_4d(sa, &tma_a, full_bar(stage), k0, m0, b0, b1);
                     } else {
@@ -256,9 +278,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
                     if (p.bias) {
+                        const float* bp = p.bias + (long long)b0 * p.bias_sb0 + n;
 #pragma unroll
                         for (int j = 0; j < 32; ++j)
-                            if (j < nvalid) v[j] += __ldg(p.bias + n + j);
+                            if (j < nvalid) v[j] += __ldg(bp + j);
                     }
                     if (AOb) store_row_chunk<TC>(AOb + row_off + n, v, nvalid, vec_ok);
                     if (p.act == B200ASR_ACT_GELU) {
@@ -367,6 +390,23 @@ static int make_operand_map(CUtensorMap* map, const void* base, int R, int K, in
 }
 
 template <int BN, typename TC>
+static int launch_kernel(const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, cudaStream_t st) {
+    using C_ = Cfg<BN>;
+    static bool attr_set = false;  // per instantiation
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C_::SMEM_BYTES);
+        if (e != cudaSuccess) {
+            set_error("gemm(tcgen05): cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+            return B200ASR_ERR_CUDA;
+        }
+        attr_set = true;
+    }
+    long long grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+    gemm_tc_kernel<BN, TC><<<(int)grid, NUM_THREADS, C_::SMEM_BYTES, st>>>(ma, mb, p);
+    return check_launch("gemm_tcgen05");
+}
+
+template <int BN, typename TC>
 static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
     using C_ = Cfg<BN>;
     CUtensorMap ma, mb;
@@ -383,18 +423,59 @@ static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
     p.tiles_m = ceil_div(a.M, BLOCK_M);
     p.tiles_n = ceil_div(a.N, BN);
     p.num_tiles = (long long)p.tiles_m * p.tiles_n * a.batch0 * a.batch1;
-    static bool attr_set = false;  // per instantiation
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C_::SMEM_BYTES);
-        if (e != cudaSuccess) {
-            set_error("gemm(tcgen05): cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
-            return B200ASR_ERR_CUDA;
-        }
-        attr_set = true;
+    p.mode = 0; p.tap_pad = 0; p.tblocks = 1; p.num_kb = ceil_div(a.K, BLOCK_K); p.bias_sb0 = 0;
+    return launch_kernel<BN, TC>(ma, mb, p, st);
+}
+
+// ---------------------------------------------------------------- grouped positional conv on the same kernel
+// x, y channels-last [B, T, C] bf16, 64 channels per group.  w_pack [groups][64 n][k][64 c] (K-major rows of k*64).
+//   forward:       n = out channel o, c = in channel i,  tap_pad = k/2,         w_pack[g][o][j][i] = W[g*64+o][i][j]
+//   data gradient: n = in channel i,  c = out channel o, tap_pad = k-1-k/2,     w_pack[g][i][j][o] = W[g*64+o][i][k-1-j]
+static int posconv_taps_launch(const void* x, const void* w_pack, const float* bias, void* y, int B, int T, int C,
+                               int groups, int k, int tap_pad, cudaStream_t st) {
+    CUtensorMap ma, mb;
+    {
+        const cuuint64_t dims[4] = {64, (cuuint64_t)T, (cuuint64_t)groups, (cuuint64_t)B};
+        const cuuint64_t strides[3] = {(cuuint64_t)C * 2, 128, (cuuint64_t)T * C * 2};
+        const cuuint32_t box[4] = {64, BLOCK_M, 1, 1};
+        int rc = encode_map_bf16_4d(&ma, x, dims, strides, box, "posconv(tcgen05) A");
+        if (rc) return rc;
     }
-    long long grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
-    gemm_tc_kernel<BN, TC><<<(int)grid, NUM_THREADS, C_::SMEM_BYTES, st>>>(ma, mb, p);
-    return check_launch("gemm_tcgen05");
+    {
+        const cuuint64_t dims[4] = {(cuuint64_t)k * 64, 64, (cuuint64_t)groups, 1};
+        const cuuint64_t strides[3] = {(cuuint64_t)k * 64 * 2, (cuuint64_t)64 * k * 64 * 2, 16};
+        const cuuint32_t box[4] = {64, 64, 1, 1};
+        int rc = encode_map_bf16_4d(&mb, w_pack, dims, strides, box, "posconv(tcgen05) B");
+        if (rc) return rc;
+    }
+    Params p = {};
+    p.C = y; p.bias = bias; p.M = T; p.N = 64; p.K = k * 64; p.ldc = C; p.alpha = 1.f;
+    p.batch0 = groups; p.batch1 = B; p.sc0 = 64; p.sc1 = (long long)T * C;
+    p.tiles_m = ceil_div(T, BLOCK_M); p.tiles_n = 1;
+    p.num_tiles = (long long)p.tiles_m * groups * B;
+    p.mode = 1; p.tap_pad = tap_pad; p.tblocks = 1; p.num_kb = k; p.bias_sb0 = 64;
+    return launch_kernel<64, __nv_bfloat16>(ma, mb, p, st);
+}
+
+// dwt[g*64+o][j][i] = sum_{b,t} dy[b,t,g*64+o] * x[b, t+j-pad, g*64+i]   (fp32, tap-major; permuted by the caller)
+static int posconv_wgrad_launch(const void* x, const void* dy, float* dwt, int B, int T, int C, int groups, int k, int pad,
+                                cudaStream_t st) {
+    CUtensorMap ma, mb;
+    const cuuint64_t dims[4] = {64, (cuuint64_t)T, (cuuint64_t)groups, (cuuint64_t)B};
+    const cuuint64_t strides[3] = {(cuuint64_t)C * 2, 128, (cuuint64_t)T * C * 2};
+    const cuuint32_t box[4] = {64, BLOCK_K, 1, 1};
+    int rc = encode_map_bf16_4d(&ma, dy, dims, strides, box, "posconv_wgrad(tcgen05) A");
+    if (rc) return rc;
+    rc = encode_map_bf16_4d(&mb, x, dims, strides, box, "posconv_wgrad(tcgen05) B");
+    if (rc) return rc;
+    Params p = {};
+    p.C = dwt; p.M = 64; p.N = k * 64; p.K = B * T; p.ldc = k * 64; p.alpha = 1.f;
+    p.a_mn = 1; p.b_mn = 1;
+    p.batch0 = groups; p.batch1 = 1; p.sc0 = (long long)64 * k * 64; p.sc1 = 0;
+    p.tiles_m = 1; p.tiles_n = k;
+    p.num_tiles = (long long)k * groups;
+    p.mode = 2; p.tap_pad = pad; p.tblocks = ceil_div(T, BLOCK_K); p.num_kb = B * p.tblocks; p.bias_sb0 = 0;
+    return launch_kernel<64, float>(ma, mb, p, st);
 }
 
 }  // namespace tc
@@ -425,4 +506,15 @@ int gemm_tc_launch(const b200asr_gemm_args& a, cudaStream_t st) {
     }
 }
 
+}  // namespace b200asr
+
+namespace b200asr {
+int posconv_tc_taps(const void* x, const void* w_pack, const float* bias, void* y, int B, int T, int C, int groups, int k,
+                    int tap_pad, cudaStream_t st) {
+    return tc::posconv_taps_launch(x, w_pack, bias, y, B, T, C, groups, k, tap_pad, st);
+}
+int posconv_tc_wgrad(const void* x, const void* dy, float* dwt, int B, int T, int C, int groups, int k, int pad,
+                     cudaStream_t st) {
+    return tc::posconv_wgrad_launch(x, dy, dwt, B, T, C, groups, k, pad, st);
+}
 }  // namespace b200asr

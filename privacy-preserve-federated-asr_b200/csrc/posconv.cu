@@ -3,6 +3,7 @@
 // and every tap's [Cg x Cg] filter slice streams through a second buffer.  The same kernel computes the data
 // gradient (taps reversed, filter slice transposed); the weight gradient reduces over time per (group, tap).
 #include "common.cuh"
+#include "gemm.h"
 
 namespace b200asr {
 
@@ -25,6 +26,37 @@ __global__ void posconv_pack_kernel(const T* __restrict__ w, T* __restrict__ wf,
         wf[(((long long)g * k + j) * Cg + i) * Cg + o] = v;
         wb[(((long long)g * k + j) * Cg + o) * Cg + i] = v;
     }
+}
+
+// tensor-core layouts (64 channels per group, bf16): K-major rows of k*64 per output column of the implicit GEMM
+//   wf[g][o][j][i] = W[g*64+o][i][j]          (forward:  n = o, taps ascending)
+//   wb[g][i][j][o] = W[g*64+o][i][k-1-j]      (data gradient: n = i, taps reversed)
+__global__ void posconv_pack_tc_kernel(const __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ wf,
+                                       __nv_bfloat16* __restrict__ wb, int C, int k) {
+    const long long total = (long long)C * 64 * k;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+        const int j = (int)(idx % k);
+        const int i = (int)((idx / k) % 64);
+        const int co = (int)(idx / ((long long)k * 64));
+        const int g = co / 64, o = co % 64;
+        const __nv_bfloat16 v = w[idx];
+        wf[(((long long)g * 64 + o) * k + j) * 64 + i] = v;
+        wb[(((long long)g * 64 + i) * k + (k - 1 - j)) * 64 + o] = v;
+    }
+}
+
+// dw[c][i][j] = dwt[c][j][i]   (tap-major fp32 result of the tensor-core weight gradient -> HF layout [C, Cg, k])
+__global__ void posconv_dw_permute_kernel(const float* __restrict__ dwt, float* __restrict__ dw, long long total, int Cg, int k) {
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+        const int j = (int)(idx % k);
+        const int i = (int)((idx / k) % Cg);
+        const long long c = idx / ((long long)k * Cg);
+        dw[idx] = dwt[(c * k + j) * Cg + i];
+    }
+}
+
+static bool posconv_tc_ok(int dtype, int C, int groups, const void* a, const void* b) {
+    return dtype == B200ASR_BF16 && C == groups * 64 && ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 15) == 0;
 }
 
 // y[b, t, g*Cg + c] = bias[c] + sum_j sum_r W[g][jj][r][c] * x[b, t + j - pad, g*Cg + r],  jj = flip ? k-1-j : j
@@ -162,6 +194,11 @@ int b200asr_posconv_pack_weight(const void* w, void* w_fwd, void* w_bwd, int C, 
     const long long total = (long long)C * Cg * k;
     long long g = (total + 255) / 256;
     if (g > num_sms() * 8) g = num_sms() * 8;
+    if (posconv_tc_ok(dtype, C, groups, w_fwd, w_bwd)) {
+        posconv_pack_tc_kernel<<<(int)g, 256, 0, as_stream(stream)>>>((const __nv_bfloat16*)w, (__nv_bfloat16*)w_fwd,
+                                                                       (__nv_bfloat16*)w_bwd, C, k);
+        return check_launch("posconv_pack_weight");
+    }
     B200_DISPATCH_DTYPE(dtype, {
         posconv_pack_kernel<T><<<(int)g, 256, 0, as_stream(stream)>>>((const T*)w, (T*)w_fwd, (T*)w_bwd, C, Cg, k);
     });
@@ -172,17 +209,42 @@ int b200asr_posconv_fwd(const void* x, const void* w_fwd, const float* bias, voi
                         int dtype, void* stream) {
     B200_REQUIRE(x && w_fwd && y, "posconv_fwd: null pointer");
     B200_REQUIRE(B > 0 && T_ > 0 && C > 0 && groups > 0 && C % groups == 0 && k > 0, "posconv_fwd: bad shape");
+    if (posconv_tc_ok(dtype, C, groups, x, w_fwd) && (reinterpret_cast<uintptr_t>(y) & 15) == 0)
+        return posconv_tc_taps(x, w_fwd, bias, y, B, T_, C, groups, k, k / 2, as_stream(stream));
     B200_DISPATCH_DTYPE(dtype, { return launch_posconv<T>(x, w_fwd, bias, y, B, T_, C, groups, k, k / 2, 0, as_stream(stream)); });
     return B200ASR_OK;
 }
 
-int b200asr_posconv_bwd(const void* x, const void* w_bwd, const void* dy, void* dx, float* dw, int B, int T_, int C, int groups,
-                        int k, int dtype, void* stream) {
+size_t b200asr_posconv_bwd_workspace_bytes(int C, int groups, int k) {
+    return (size_t)C * (C / (groups > 0 ? groups : 1)) * k * sizeof(float);
+}
+
+int b200asr_posconv_bwd(const void* x, const void* w_bwd, const void* dy, void* dx, float* dw, void* workspace,
+                        size_t workspace_bytes, int B, int T_, int C, int groups, int k, int dtype, void* stream) {
     B200_REQUIRE(x && w_bwd && dy, "posconv_bwd: null pointer");
     B200_REQUIRE(B > 0 && T_ > 0 && C > 0 && groups > 0 && C % groups == 0 && k > 0, "posconv_bwd: bad shape");
     cudaStream_t st = as_stream(stream);
     const int pad = k / 2;
     const int Cg = C / groups;
+    if (posconv_tc_ok(dtype, C, groups, x, dy) && (!dx || (reinterpret_cast<uintptr_t>(dx) & 15) == 0) &&
+        (reinterpret_cast<uintptr_t>(w_bwd) & 15) == 0) {
+        if (dx) {
+            int rc = posconv_tc_taps(dy, w_bwd, nullptr, dx, B, T_, C, groups, k, k - 1 - pad, st);
+            if (rc) return rc;
+        }
+        if (dw) {
+            B200_REQUIRE(workspace && workspace_bytes >= b200asr_posconv_bwd_workspace_bytes(C, groups, k),
+                         "posconv_bwd: workspace too small");
+            int rc = posconv_tc_wgrad(x, dy, (float*)workspace, B, T_, C, groups, k, pad, st);
+            if (rc) return rc;
+            const long long total = (long long)C * Cg * k;
+            long long g = (total + 255) / 256;
+            if (g > num_sms() * 8) g = num_sms() * 8;
+            posconv_dw_permute_kernel<<<(int)g, 256, 0, st>>>((const float*)workspace, dw, total, Cg, k);
+            return check_launch("posconv_dw_permute");
+        }
+        return B200ASR_OK;
+    }
     if (dx) {
         // dx[t] = sum_j dy[t - j + pad] W_j^T = sum_j' dy[t + j' - (k-1-pad)] W_{k-1-j'}^T
         int rc;
