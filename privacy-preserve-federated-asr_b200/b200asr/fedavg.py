@@ -45,9 +45,17 @@ def _aligned(t: torch.Tensor) -> torch.Tensor:
 
 class FlatParams:
     """Re-homes the given parameters as views into ONE flat fp32 buffer (16-byte aligned segments), so FedAvg,
-    the optimizer and the gradient norm each touch the sub-network with a single streaming kernel."""
+    the optimizer and the gradient norm each touch the sub-network with a single streaming kernel.
 
-    def __init__(self, named_params: Iterable, device=None):
+    Also the hub of two per-step shortcuts of the host layer (functional.py):
+      * `grad` is the flat fp32 gradient; with `direct_grads` the backward kernels write each parameter's slice in
+        place (functional.grad_sink) instead of handing tensors to autograd's per-parameter accumulation;
+      * `shadow` (optional) is a flat bf16 copy of `flat` that whoever updates `flat` keeps current (the fused AdamW
+        kernel writes it in the same pass): the tensor-core GEMMs read weight views of it, so there is no per-step
+        cast or QKV concat.  `epoch` counts raw-pointer updates of `flat`; the shadow is valid iff it was refreshed
+        at the current epoch."""
+
+    def __init__(self, named_params: Iterable, device=None, with_shadow: bool = False, direct_grads: bool = True):
         named = [(n, p) for n, p in named_params]
         if not named:
             raise ValueError("FlatParams: no parameters")
@@ -61,20 +69,44 @@ class FlatParams:
         self.numel = off
         self.flat = torch.zeros(off, dtype=torch.float32, device=device)
         self.grad = torch.zeros(off, dtype=torch.float32, device=device)
+        self.shadow = torch.zeros(off, dtype=torch.bfloat16, device=device) if with_shadow else None
+        self.epoch = 0
+        self.shadow_epoch = -1
+        self.direct_grads = direct_grads
         with torch.no_grad():
             for p, o in zip(self.params, self.offsets):
                 v = self.flat[o:o + p.numel()].view(p.shape)
                 v.copy_(p.data)
                 p.data = v
                 p.grad = self.grad[o:o + p.numel()].view(p.shape)
+                p._b200_flat, p._b200_off, p._b200_grad, p._b200_fresh = self, o, p.grad, False
+                p._b200_pver = p._version
+        if with_shadow:
+            self.refresh_shadow()
 
     def manifest(self):
         return [(n, o, tuple(p.shape)) for n, o, p in zip(self.names, self.offsets, self.params)]
 
-    def mark_updated(self):
-        """A kernel wrote the flat buffer behind autograd's back: invalidate cached weight shadows."""
-        from .functional import ShadowCache
-        ShadowCache.invalidate_all()
+    def shadow_valid(self) -> bool:
+        return self.shadow is not None and self.shadow_epoch == self.epoch
+
+    def refresh_shadow(self):
+        """One streaming cast of the whole flat buffer (after FedAvg, load_state_dict, ...)."""
+        if self.shadow is not None:
+            ops.cast_from_f32(self.flat, torch.bfloat16, out=self.shadow)
+            self.shadow_epoch = self.epoch
+            for p in self.params:
+                p._b200_pver = p._version
+
+    def mark_updated(self, shadow_written: bool = False):
+        """A kernel wrote the flat buffer behind autograd's back: bump the epoch so cached weight shadows and derived
+        layouts of THESE parameters are rebuilt (frozen parameters elsewhere keep theirs)."""
+        self.epoch += 1
+        if self.shadow is not None:
+            if shadow_written:
+                self.shadow_epoch = self.epoch
+            else:
+                self.refresh_shadow()
 
 
 def fedavg_local(flats: Sequence[torch.Tensor], weights: Optional[Sequence[float]] = None,

@@ -20,22 +20,26 @@ class ShadowCache:
 
     fp32 mode returns the parameter storage itself.  bf16 mode keeps a bf16 shadow (what the tcgen05 GEMM
     reads); derived layouts (fused QKV, conv filters flattened for the implicit GEMM, packed pos-conv filters)
-    are cached under the same versioning.
+    are cached under the same versioning.  Parameters re-homed into a FlatParams buffer whose owner keeps a flat
+    bf16 shadow current (the fused AdamW writes it in the same pass as the fp32 update) are served as views of that
+    shadow: no per-step cast or concat kernels.
     """
-
-    epoch = 0  # bumped by invalidate_all(): kernels (fused AdamW, FedAvg) wrote parameters behind autograd's back
 
     def __init__(self, dtype: torch.dtype):
         self.dtype = dtype
         self._cache = {}
 
-    @classmethod
-    def invalidate_all(cls):
-        cls.epoch += 1
+    @staticmethod
+    def invalidate_all():
+        """Kept for callers that wrote parameters through raw pointers without a FlatParams owner."""
+        ShadowCache._global_epoch += 1
+
+    _global_epoch = 0
 
     @staticmethod
     def _ver(ps):
-        return (ShadowCache.epoch,) + tuple((p.data_ptr(), p._version) for p in ps)
+        return (ShadowCache._global_epoch,) + tuple(
+            (p.data_ptr(), p._version, getattr(p, "_b200_flat").epoch if hasattr(p, "_b200_flat") else 0) for p in ps)
 
     def _get(self, key, ps, make):
         ver = self._ver(ps)
@@ -53,14 +57,39 @@ class ShadowCache:
             t = t.contiguous()
         return t if self.dtype == torch.float32 else ops.cast_from_f32(t, self.dtype)
 
+    def _flat_shadow(self, ps):
+        """View of the owner's flat bf16 shadow covering the adjacent parameters ps, or None."""
+        if self.dtype != torch.bfloat16:
+            return None
+        fp = getattr(ps[0], "_b200_flat", None)
+        if fp is None or not fp.shadow_valid():
+            return None
+        off = ps[0]._b200_off
+        nxt = off
+        for p in ps:
+            if getattr(p, "_b200_flat", None) is not fp or p._b200_off != nxt or p._version != p._b200_pver:
+                return None
+            nxt += p.numel()
+        return fp.shadow[off:nxt]
+
     def weight(self, p: torch.Tensor) -> torch.Tensor:
+        v = self._flat_shadow((p,))
+        if v is not None:
+            return v.view(p.shape)
         return self._get(("w", id(p)), (p,), lambda: self._cast(p))
 
     def qkv(self, q, k, v) -> torch.Tensor:
         """[3d, d] = rows of q_proj, k_proj, v_proj (the packed projection the attention kernel consumes)."""
+        f = self._flat_shadow((q, k, v))
+        if f is not None:
+            return f.view(3 * q.shape[0], q.shape[1])
         return self._get(("qkv", id(q)), (q, k, v), lambda: self._cast(torch.cat([q.detach(), k.detach(), v.detach()], 0)))
 
     def qkv_bias(self, q, k, v) -> torch.Tensor:
+        fp = getattr(q, "_b200_flat", None)
+        if (fp is not None and getattr(k, "_b200_flat", None) is fp and getattr(v, "_b200_flat", None) is fp
+                and k._b200_off == q._b200_off + q.numel() and v._b200_off == k._b200_off + k.numel()):
+            return fp.flat[q._b200_off:q._b200_off + 3 * q.numel()]  # adjacent fp32 biases: a view, always current
         return self._get(("qkvb", id(q)), (q, k, v), lambda: torch.cat([q.detach(), k.detach(), v.detach()], 0).contiguous())
 
     def conv_flat(self, w) -> torch.Tensor:
@@ -69,7 +98,76 @@ class ShadowCache:
                          lambda: self._cast(w.detach().permute(0, 2, 1).reshape(w.shape[0], -1)))
 
     def posconv(self, w, groups):
-        return self._get(("posconv", id(w)), (w,), lambda: ops.posconv_pack(self._cast(w), groups))
+        return self._get(("posconv", id(w)), (w,), lambda: ops.posconv_pack(self.weight(w), groups))
+
+
+# ----------------------------------------------------------------------------- gradient sinks
+def grad_sink(ps):
+    """Direct-write destination for the gradient of the adjacent parameters `ps` (a tuple): parameters owned by a
+    FlatParams buffer expose their slice of the flat fp32 gradient; backward kernels write there and autograd
+    receives None for them (no per-parameter accumulate / copy launches).  Returns (flat view, overwrite) or
+    (None, True) when the parameters are not flat-owned, not adjacent, or disagree about being fresh."""
+    fp = getattr(ps[0], "_b200_flat", None)
+    if fp is None or not fp.direct_grads:
+        return None, True
+    off = ps[0]._b200_off
+    nxt = off
+    fresh = ps[0]._b200_fresh
+    for p in ps:
+        if getattr(p, "_b200_flat", None) is not fp or p._b200_off != nxt or p._b200_fresh != fresh:
+            return None, True
+        nxt += p.numel()
+    for p in ps:
+        p._b200_fresh = False
+        p.grad = p._b200_grad
+    return fp.grad[off:nxt], fresh
+
+
+def _wgrad(ps, need, dy, x):
+    """dW = dy^T x for one parameter or several adjacent ones stacked along the output dim."""
+    if not need:
+        return None
+    ps = ps if isinstance(ps, tuple) else (ps,)
+    sink, fresh = grad_sink(ps)
+    if sink is None:
+        return ops.linear_wgrad(dy, x)
+    ops.linear_wgrad(dy, x, out=sink.view(dy.shape[1], x.shape[1]), accumulate=not fresh)
+    return None
+
+
+def _bgrad(ps, need, dy):
+    if not need:
+        return None
+    ps = ps if isinstance(ps, tuple) else (ps,)
+    sink, fresh = grad_sink(ps)
+    if sink is None:
+        return ops.colsum(dy)
+    if fresh:
+        ops.colsum(dy, out=sink)
+    else:
+        ops.axpy_(sink, ops.colsum(dy))
+    return None
+
+
+def _ln_bwd(dy, s, w, b, mean, rstd, need, **kw):
+    """LayerNorm backward whose affine gradients go straight to the sinks when both are fresh."""
+    if need and w is not None:
+        sw, fw = grad_sink((w,))
+        sb, fb = grad_sink((b,))
+        if sw is not None and sb is not None and fw and fb:
+            dx, _, _ = ops.layernorm_bwd(dy, s, w, b, mean, rstd, dw_out=sw, db_out=sb, **kw)
+            return dx, None, None
+        dx, dw, db = ops.layernorm_bwd(dy, s, w, b, mean, rstd, **kw)
+        if sw is not None:
+            if fw: sw.copy_(dw)
+            else: ops.axpy_(sw, dw)
+            dw = None
+        if sb is not None:
+            if fb: sb.copy_(db)
+            else: ops.axpy_(sb, db)
+            db = None
+        return dx, dw, db
+    return ops.layernorm_bwd(dy, s, w, b, mean, rstd, want_wgrad=False, **kw)
 
 
 # ----------------------------------------------------------------------------- frozen feature extractor
@@ -109,7 +207,8 @@ class FeatureProjectionFn(torch.autograd.Function):
         n, _, mean, rstd = ops.layernorm_fwd(x2, ln_w, ln_b, eps)
         wsh = cache.weight(w)
         y, _ = ops.linear_fwd(n, wsh, b)
-        ctx.save_for_backward(x2, n, mean, rstd, ln_w, ln_b, wsh, klen)
+        ctx.save_for_backward(x2, n, mean, rstd, wsh, klen)
+        ctx.params = (ln_w, ln_b, w, b)
         ctx.out_shape = feats.shape[:-1] + (w.shape[0],)
         y = y.view(ctx.out_shape)
         if klen is not None:  # hidden_states[~attention_mask] = 0 (HF:369-371), fused here: y is our own buffer
@@ -118,16 +217,20 @@ class FeatureProjectionFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
-        x2, n, mean, rstd, ln_w, ln_b, wsh, klen = ctx.saved_tensors
+        x2, n, mean, rstd, wsh, klen = ctx.saved_tensors
+        ln_w, ln_b, w, b = ctx.params
+        need = ctx.needs_input_grad
         if klen is not None:
             dy = ops.mask_frames_(dy.clone(memory_format=torch.contiguous_format), klen)
         dy2 = dy.reshape(-1, dy.shape[-1])
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        db = ops.colsum(dy2)
-        dw = ops.linear_wgrad(dy2, n)
-        dn = ops.linear_dgrad(dy2, wsh)
-        _, dlw, dlb = ops.layernorm_bwd(dn, x2, ln_w, ln_b, mean, rstd)
+        db = _bgrad(b, need[4], dy2)
+        dw = _wgrad(w, need[3], dy2, n)
+        dlw = dlb = None
+        if need[1] or need[2]:
+            dn = ops.linear_dgrad(dy2, wsh)
+            _, dlw, dlb = _ln_bwd(dn, x2, ln_w, ln_b, mean, rstd, True)
         return None, dlw, dlb, dw, db, None, None, None
 
 
@@ -152,7 +255,8 @@ class PosConvEmbedFn(torch.autograd.Function):
             saved += [y, c, mean, rstd]
             y = y_next.view(B, T, d)
         out, s, mean, rstd = ops.layernorm_fwd(h.reshape(B * T, d), ln_w, ln_b, eps, res=y.reshape(B * T, d), want_sum=True)
-        ctx.save_for_backward(s, mean, rstd, ln_w, ln_b, *saved, *packs)
+        ctx.save_for_backward(s, mean, rstd, *saved, *packs)
+        ctx.params = (ln_w, ln_b, ws, bs)
         ctx.n, ctx.groups, ctx.ksize, ctx.shape = n, groups, ksize, (B, T, d)
         return out.view(B, T, d)
 
@@ -161,19 +265,30 @@ class PosConvEmbedFn(torch.autograd.Function):
         n, groups, k = ctx.n, ctx.groups, ctx.ksize
         B, T, d = ctx.shape
         t = ctx.saved_tensors
-        s, mean, rstd, ln_w, ln_b = t[:5]
-        saved = t[5:5 + 4 * n]
-        packs = t[5 + 4 * n:]
+        s, mean, rstd = t[:3]
+        saved = t[3:3 + 4 * n]
+        packs = t[3 + 4 * n:]
+        ln_w, ln_b, ws, bs = ctx.params
+        need = ctx.needs_input_grad
         dout2 = dout.reshape(B * T, d)
-        ds, dlw, dlb = ops.layernorm_bwd(dout2, s, ln_w, ln_b, mean, rstd)
+        ds, dlw, dlb = _ln_bwd(dout2, s, ln_w, ln_b, mean, rstd, need[1] or need[2])
         dy = ds  # gradient into posconv output; ds is also the residual-path gradient
         dws, dbs = [None] * n, [None] * n
         for j in range(n - 1, -1, -1):
             y_in, c, cm, cr = saved[4 * j:4 * j + 4]
             dc, _, _ = ops.layernorm_bwd(dy, c.view(B * T, d), None, None, cm, cr, act=ACT_GELU)
-            dbs[j] = ops.colsum(dc)
-            need_dx = j > 0 or ctx.needs_input_grad[0]
-            dx, dws[j] = ops.posconv_bwd(y_in, packs[j], dc.view(B, T, d), groups, k, want_dx=need_dx)
+            dbs[j] = _bgrad(bs[j], need[7 + n + j], dc)
+            need_dx = j > 0 or need[0]
+            want_dw = need[7 + j]
+            sink, fresh = grad_sink((ws[j],)) if want_dw else (None, True)
+            if sink is not None and fresh:
+                dx, _ = ops.posconv_bwd(y_in, packs[j], dc.view(B, T, d), groups, k, want_dx=need_dx,
+                                        dw_out=sink.view(ws[j].shape))
+            else:
+                dx, dws[j] = ops.posconv_bwd(y_in, packs[j], dc.view(B, T, d), groups, k, want_dx=need_dx, want_dw=want_dw)
+                if sink is not None:
+                    ops.axpy_(sink, dws[j].view(-1))
+                    dws[j] = None
             dy = dx.view(B * T, d) if dx is not None else None
         dh = None
         if ctx.needs_input_grad[0]:
@@ -205,39 +320,40 @@ class EncoderLayerFn(torch.autograd.Function):
         g, u = ops.linear_fwd(x1, w1s, b1, act=ACT_GELU, want_preact=True)
         s2, _ = ops.linear_fwd(g, w2s, b2, residual=x1)
         y, _, m2, r2 = ops.layernorm_fwd(s2, ln2_w, ln2_b, eps)
-        ctx.save_for_backward(x, qkv, attn, lse, s1, m1, r1, x1, u, g, s2, m2, r2, wqkv, wo, w1s, w2s, ln1_w, ln1_b,
-                              ln2_w, ln2_b)
+        ctx.save_for_backward(x, qkv, attn, lse, s1, m1, r1, x1, u, g, s2, m2, r2, wqkv, wo, w1s, w2s)
+        ctx.params = P
         ctx.klen = klen
         ctx.meta = (B, T, H, dh, scale)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        (x, qkv, attn, lse, s1, m1, r1, x1, u, g, s2, m2, r2, wqkv, wo, w1s, w2s, ln1_w, ln1_b, ln2_w,
-         ln2_b) = ctx.saved_tensors
+        (x, qkv, attn, lse, s1, m1, r1, x1, u, g, s2, m2, r2, wqkv, wo, w1s, w2s) = ctx.saved_tensors
+        (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = ctx.params
         B, T, H, dh, scale = ctx.meta
         d = x.shape[1]
         wg = any(ctx.needs_input_grad[4:])  # parameter gradients wanted?
-        ds2, dln2w, dln2b = ops.layernorm_bwd(dy, s2, ln2_w, ln2_b, m2, r2, want_wgrad=wg)
-        db2 = ops.colsum(ds2) if wg else None
-        dw2 = ops.linear_wgrad(ds2, g) if wg else None
+        ds2, dln2w, dln2b = _ln_bwd(dy, s2, ln2_w, ln2_b, m2, r2, wg)
+        db2 = _bgrad(b2, wg, ds2)
+        dw2 = _wgrad(w2, wg, ds2, g)
         du = ops.linear_dgrad(ds2, w2s, gelu_preact=u)            # (ds2 W2) * gelu'(u)
-        db1 = ops.colsum(du) if wg else None
-        dw1 = ops.linear_wgrad(du, x1) if wg else None
+        db1 = _bgrad(b1, wg, du)
+        dw1 = _wgrad(w1, wg, du, x1)
         dx1 = ops.linear_dgrad(du, w1s, residual=ds2)            # + residual path of s2 = x1 + ...
-        ds1, dln1w, dln1b = ops.layernorm_bwd(dx1, s1, ln1_w, ln1_b, m1, r1, want_wgrad=wg)
-        dbo = ops.colsum(ds1) if wg else None
-        dwo = ops.linear_wgrad(ds1, attn) if wg else None
+        ds1, dln1w, dln1b = _ln_bwd(dx1, s1, ln1_w, ln1_b, m1, r1, wg)
+        dbo = _bgrad(o_b, wg, ds1)
+        dwo = _wgrad(o_w, wg, ds1, attn)
         dattn = ops.linear_dgrad(ds1, wo)
         dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale)
         dx = ops.linear_dgrad(dqkv, wqkv, residual=ds1) if ctx.needs_input_grad[0] else None
+        dqw = dkw = dvw = dqb = dkb = dvb = None
         if wg:
-            dbqkv = ops.colsum(dqkv)
-            dwqkv = ops.linear_wgrad(dqkv, x)
-            dqw, dkw, dvw = dwqkv[:d], dwqkv[d:2 * d], dwqkv[2 * d:]
-            dqb, dkb, dvb = dbqkv[:d], dbqkv[d:2 * d], dbqkv[2 * d:]
-        else:
-            dqw = dkw = dvw = dqb = dkb = dvb = None
+            dbqkv = _bgrad((q_b, k_b, v_b), True, dqkv)
+            dwqkv = _wgrad((q_w, k_w, v_w), True, dqkv, x)
+            if dwqkv is not None:
+                dqw, dkw, dvw = dwqkv[:d], dwqkv[d:2 * d], dwqkv[2 * d:]
+            if dbqkv is not None:
+                dqb, dkb, dvb = dbqkv[:d], dbqkv[d:2 * d], dbqkv[2 * d:]
         return (dx, None, None, None, dqw, dqb, dkw, dkb, dvw, dvb, dwo, dbo, dln1w, dln1b, dw1, db1, dw2, db2,
                 dln2w, dln2b)
 
@@ -253,6 +369,7 @@ class LinearFn(torch.autograd.Function):
         wsh = cache.weight(w)
         y, _ = ops.linear_fwd(x2, wsh, b)
         ctx.save_for_backward(x2, wsh)
+        ctx.params = (w, b)
         return y.view(x.shape[:-1] + (w.shape[0],))
 
     @staticmethod
@@ -264,10 +381,9 @@ class LinearFn(torch.autograd.Function):
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             dx = ops.linear_dgrad(dy2, wsh).view(dy.shape[:-1] + (wsh.shape[1],))
-        if ctx.needs_input_grad[1]:
-            dw = ops.linear_wgrad(dy2, x2)
-        if ctx.needs_input_grad[2]:
-            db = ops.colsum(dy2)
+        w, b = ctx.params
+        dw = _wgrad(w, ctx.needs_input_grad[1], dy2, x2)
+        db = _bgrad(b, ctx.needs_input_grad[2], dy2) if b is not None else None
         return dx, dw, db, None
 
 

@@ -101,7 +101,9 @@ class _PosConvEmbed(nn.Module):
 class _Attention(nn.Module):
     def __init__(self, d):
         super().__init__()
-        self.k_proj, self.v_proj, self.q_proj, self.out_proj = (_Affine((d, d)) for _ in range(4))
+        # q, k, v registered back to back: in a FlatParams buffer the three weights (and the three biases) are adjacent,
+        # so the fused [3d, d] projection, its bf16 shadow and its gradient are plain views (no concat / split kernels)
+        self.q_proj, self.k_proj, self.v_proj, self.out_proj = (_Affine((d, d)) for _ in range(4))
 
 
 class _FeedForward(nn.Module):

@@ -20,14 +20,18 @@ def _no_decay(name: str) -> bool:
 
 class FusedAdamW:
     def __init__(self, named_params: Iterable, lr=1e-5, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.005,
-                 max_grad_norm: Optional[float] = 1.0, warmup_steps: int = 0, total_steps: Optional[int] = None):
+                 max_grad_norm: Optional[float] = 1.0, warmup_steps: int = 0, total_steps: Optional[int] = None,
+                 bf16_shadow: bool = True):
+        """bf16_shadow: keep a flat bf16 copy of the decayed group (the GEMM weights) current inside the update
+        kernel, which the bf16 compute path then reads directly (functional.ShadowCache)."""
+        wd_shadow = bf16_shadow
         named = [(n, p) for n, p in named_params if p.requires_grad]
         dec = [(n, p) for n, p in named if not _no_decay(n)]
         nod = [(n, p) for n, p in named if _no_decay(n)]
         self.groups = []
         for items, wd in ((dec, weight_decay), (nod, 0.0)):
             if items:
-                fp = FlatParams(items)
+                fp = FlatParams(items, with_shadow=(wd_shadow and items is dec))
                 self.groups.append(dict(fp=fp, wd=wd, m=torch.zeros_like(fp.flat), v=torch.zeros_like(fp.flat)))
         self.lr, self.betas, self.eps = lr, betas, eps
         self.max_grad_norm = max_grad_norm
@@ -45,20 +49,29 @@ class FusedAdamW:
         return self.lr
 
     def zero_grad(self):
+        """No memset: every parameter is marked fresh, the backward kernels overwrite their slice of the flat
+        gradient (functional.grad_sink); parameters that end up with no gradient are zeroed in step()."""
         for g in self.groups:
-            fp = g["fp"]
-            fp.grad.zero_()
-            for p, o in zip(fp.params, fp.offsets):  # autograd may have replaced .grad; re-home it into the flat buffer
-                if p.grad is None or p.grad.data_ptr() != fp.grad.data_ptr() + 4 * o:
-                    p.grad = fp.grad[o:o + p.numel()].view(p.shape)
+            for p in g["fp"].params:
+                p.grad = None
+                p._b200_fresh = True
 
     def _gather_stray_grads(self):
         for g in self.groups:
             fp = g["fp"]
-            for p, o in zip(fp.params, fp.offsets):
-                if p.grad is not None and p.grad.data_ptr() != fp.grad.data_ptr() + 4 * o:
-                    fp.grad[o:o + p.numel()].view(p.shape).copy_(p.grad)
-                    p.grad = fp.grad[o:o + p.numel()].view(p.shape)
+            for p in fp.params:
+                if p.grad is None:
+                    if p._b200_fresh:  # untouched this step
+                        p._b200_grad.zero_()
+                        p._b200_fresh = False
+                    p.grad = p._b200_grad
+                elif p.grad.data_ptr() != p._b200_grad.data_ptr():  # autograd delivered its own tensor
+                    if p._b200_fresh:
+                        p._b200_grad.copy_(p.grad)
+                        p._b200_fresh = False
+                    else:
+                        p._b200_grad.add_(p.grad)
+                    p.grad = p._b200_grad
 
     def step(self):
         self._gather_stray_grads()
@@ -72,6 +85,6 @@ class FusedAdamW:
             gn = self.gnorm_sq
         for g in self.groups:
             fp = g["fp"]
-            ops.adamw_step_(fp.flat, fp.grad, g["m"], g["v"], None, lr, self.betas[0], self.betas[1], self.eps, g["wd"],
+            ops.adamw_step_(fp.flat, fp.grad, g["m"], g["v"], fp.shadow, lr, self.betas[0], self.betas[1], self.eps, g["wd"],
                             self.step_count, gn, self.max_grad_norm or 0.0)
-            fp.mark_updated()
+            fp.mark_updated(shadow_written=fp.shadow is not None)

@@ -132,3 +132,65 @@ def test_label_validation_and_unsupported_paths():
         model(x, labels=torch.tensor([[1, 99]], device=DEV))
     with pytest.raises(NotImplementedError):
         model(x, output_attentions=True)
+
+
+def _hf_adamw_reference(params, grads, state, lr, step, wd_of, betas=(0.9, 0.999), eps=1e-8, max_norm=1.0):
+    """transformers.AdamW (correct_bias=True) + clip_grad_norm_, as HF Trainer 4.17 runs it (finetune_ASRs.py:202-220)."""
+    total = torch.sqrt(sum((g.double() ** 2).sum() for g in grads.values())).float()
+    clip = min(1.0, float(max_norm / (total + 1e-6)))
+    for n, p in params.items():
+        g = grads[n] * clip
+        m, v = state.setdefault(n, (torch.zeros_like(p), torch.zeros_like(p)))
+        m.mul_(betas[0]).add_(g, alpha=1 - betas[0])
+        v.mul_(betas[1]).addcmul_(g, g, value=1 - betas[1])
+        step_size = lr * (1 - betas[1] ** step) ** 0.5 / (1 - betas[0] ** step)
+        p.addcdiv_(m, v.sqrt().add_(eps), value=-step_size)
+        p.add_(p, alpha=-lr * wd_of(n))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_training_loop_flat_grads_shadows_vs_oracle(dtype):
+    """Three client-local updates through the product path (FlatParams-owned parameters: backward kernels write the
+    flat gradient in place, the fused AdamW refreshes the bf16 weight shadow) against the CPU oracle stepping with
+    the reference's optimizer semantics."""
+    from b200asr.optim import FusedAdamW, _no_decay
+    cfg = R.ArchConfig.tiny()
+    sd = R.init_state_dict(cfg, seed=3, dacs=False)
+    model = M.Data2VecAudioForCTC(ns(cfg), compute_dtype=dtype)
+    model.load_state_dict(sd)
+    model.freeze_feature_encoder()
+    model.to(DEV).train()
+    lr, wd = 1e-3, 0.01
+    opt = FusedAdamW(model.named_parameters(), lr=lr, weight_decay=wd, max_grad_norm=1.0)
+    ref = {k: v.clone() for k, v in sd.items()}
+    trainable = [n for n, p in model.named_parameters() if p.requires_grad]
+    state = {}
+    batches = [R.synth_batch(cfg, 2, 6000, seed=50 + i, ragged=True, max_label=12) for i in range(3)]
+    tol = TOL[dtype]
+    for step, b in enumerate(batches, 1):
+        opt.zero_grad()
+        out = model(b["input_values"].to(DEV), b["attention_mask"].to(DEV), labels=b["labels"].to(DEV))
+        out.loss.backward()
+        # oracle step
+        leaf = {k: v.clone().requires_grad_(k in trainable) for k, v in ref.items()}
+        loss_ref, _ = R.ctc_forward(leaf, cfg, b["input_values"], b["attention_mask"], b["labels"])
+        loss_ref.backward()
+        assert abs(float(out.loss) - float(loss_ref)) / abs(float(loss_ref)) < (tol if step == 1 else 3 * tol), step
+        params = dict(model.named_parameters())
+        for n in trainable:  # every trainable parameter's gradient landed in its slice of the flat buffer
+            p = params[n]
+            assert p.grad is not None and p.grad.data_ptr() == p._b200_grad.data_ptr(), n
+            if not n.endswith("k_proj.bias"):
+                assert relinf(p.grad, leaf[n].grad) < (2e-3 if dtype == torch.float32 else 8e-2), (step, n)
+        opt.step()
+        with torch.no_grad():
+            _hf_adamw_reference({n: ref[n] for n in trainable}, {n: leaf[n].grad for n in trainable}, state, lr, step,
+                                lambda n: 0.0 if _no_decay(n) else wd)
+        for g in opt.groups:
+            fp = g["fp"]
+            if fp.shadow is not None:  # bf16 shadow == round(flat) after every update
+                assert torch.equal(fp.shadow, fp.flat.to(torch.bfloat16))
+    if dtype == torch.float32:
+        params = dict(model.named_parameters())
+        for n in trainable:
+            assert relinf(params[n].detach(), ref[n]) < 2e-3, n
