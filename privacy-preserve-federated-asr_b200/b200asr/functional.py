@@ -131,7 +131,8 @@ def _wgrad(ps, need, dy, x):
     sink, fresh = grad_sink(ps)
     if sink is None:
         return ops.linear_wgrad(dy, x)
-    ops.linear_wgrad(dy, x, out=sink.view(dy.shape[1], x.shape[1]), accumulate=not fresh)
+    with ops.on_side_stream(dy, x):
+        ops.linear_wgrad(dy, x, out=sink.view(dy.shape[1], x.shape[1]), accumulate=not fresh)
     return None
 
 
@@ -143,7 +144,8 @@ def _bgrad(ps, need, dy):
     if sink is None:
         return ops.colsum(dy)
     if fresh:
-        ops.colsum(dy, out=sink)
+        with ops.on_side_stream(dy):
+            ops.colsum(dy, out=sink)
     else:
         ops.axpy_(sink, ops.colsum(dy))
     return None

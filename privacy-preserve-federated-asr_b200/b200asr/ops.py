@@ -62,13 +62,76 @@ def _prof_end(kind, e0, flops):
 
 
 def workspace(nbytes: int, device) -> torch.Tensor:
-    """Shared scratch buffer (all library calls are serialised on the current stream)."""
-    key = (torch.device(device).index, torch.cuda.is_current_stream_capturing())
+    """Scratch buffer shared by the library calls of one stream (they are serialised on it)."""
+    key = (torch.device(device).index, torch.cuda.current_stream().cuda_stream, torch.cuda.is_current_stream_capturing())
     buf = _WS.get(key)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
         _WS[key] = buf
     return buf
+
+
+# ----------------------------------------------------------------------------- side stream (weight gradients)
+# The weight / bias gradient kernels of a layer depend only on tensors that already exist when the data-gradient
+# chain moves on, so they run on a second stream: their CTAs fill the SMs the persistent GEMM's last wave leaves idle.
+import os as _os
+
+SIDE_STREAM_ENABLED = _os.environ.get("B200ASR_SIDE_STREAM", "1") != "0"
+_SIDE = {}
+_SIDE_DIRTY = set()
+_SIDE_CB_QUEUED = [False]
+
+
+def _side_stream():
+    dev = torch.cuda.current_device()
+    st = _SIDE.get(dev)
+    if st is None:
+        st = _SIDE[dev] = torch.cuda.Stream(device=dev)
+    return st
+
+
+def join_side_stream():
+    """Make the current stream wait for everything queued on the side stream (end of backward, optimizer step)."""
+    _SIDE_CB_QUEUED[0] = False
+    dev = torch.cuda.current_device()
+    if dev in _SIDE_DIRTY:
+        torch.cuda.current_stream().wait_stream(_SIDE[dev])
+        _SIDE_DIRTY.discard(dev)
+
+
+class on_side_stream:
+    """Context manager: fork the side stream from the current one and run the enclosed launches there.  `tensors` are
+    the operands read inside (their memory must not be recycled by the caching allocator until the side stream is
+    done with them).  Outputs must be long-lived buffers (the flat gradient)."""
+
+    def __init__(self, *tensors):
+        self.tensors = tensors
+        self.ctx = None
+
+    def __enter__(self):
+        if not SIDE_STREAM_ENABLED:
+            return self
+        side = _side_stream()
+        side.wait_stream(torch.cuda.current_stream())
+        for t in self.tensors:
+            if t is not None:
+                t.record_stream(side)
+        self.ctx = torch.cuda.stream(side)
+        self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if self.ctx is None:
+            return False
+        self.ctx.__exit__(*exc)
+        _SIDE_DIRTY.add(torch.cuda.current_device())
+        if not _SIDE_CB_QUEUED[0]:
+            try:  # joined automatically when the running backward pass ends
+                torch.autograd.Variable._execution_engine.queue_callback(join_side_stream)
+                _SIDE_CB_QUEUED[0] = True
+            except RuntimeError:  # not inside a backward pass: join right away
+                join_side_stream()
+        return False
 
 
 # ----------------------------------------------------------------------------- norm / elementwise

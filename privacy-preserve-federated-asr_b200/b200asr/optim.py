@@ -74,6 +74,7 @@ class FusedAdamW:
                     p.grad = p._b200_grad
 
     def step(self):
+        ops.join_side_stream()
         self._gather_stray_grads()
         lr = self.current_lr()
         self.step_count += 1

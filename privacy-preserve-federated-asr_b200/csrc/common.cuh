@@ -78,6 +78,26 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
     return cdf + x * pdf;
 }
 
+// erf-GELU for the bf16 tensor-core epilogues: Abramowitz-Stegun 7.1.26 (|erf error| <= 1.5e-7, far below bf16
+// rounding) with one MUFU exp and one MUFU rcp shared between the value and the derivative.
+__device__ __forceinline__ void erf_fast_parts(float x, float& erfv, float& e) {
+    const float z = fabsf(x) * 0.70710678118654752440f;
+    const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+    e = __expf(-z * z);  // = exp(-x^2 / 2)
+    const float poly = fmaf(fmaf(fmaf(fmaf(1.061405429f, t, -1.453152027f), t, 1.421413741f), t, -0.284496736f), t, 0.254829592f) * t;
+    erfv = copysignf(fmaf(-poly, e, 1.0f), x);
+}
+__device__ __forceinline__ float gelu_fast(float x) {
+    float er, e;
+    erf_fast_parts(x, er, e);
+    return 0.5f * x * (1.0f + er);
+}
+__device__ __forceinline__ float gelu_grad_fast(float x) {
+    float er, e;
+    erf_fast_parts(x, er, e);
+    return fmaf(x * 0.39894228040143267794f, e, 0.5f * (1.0f + er));
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

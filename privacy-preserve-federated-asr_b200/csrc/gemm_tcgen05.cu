@@ -18,7 +18,7 @@ namespace tc {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;   // 64 bf16 = 128 bytes = one swizzle-128B row
 constexpr int UMMA_K = 16;
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 320;  // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quarter: column halves)
 constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
 
 template <int BN> struct Cfg {
@@ -140,7 +140,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(tfull_bar(s), 1);
-            mbar_init(tempty_bar(s), 4);  // one arrival per epilogue warp
+            mbar_init(tempty_bar(s), 8);  // one arrival per epilogue warp
         }
         fence_barrier_init();
     }
@@ -244,6 +244,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     } else {
         // ===================== epilogue warps =====================
         const int quarter = warp & 3;  // TMEM lanes [32*quarter, 32*quarter+32) are accessible to this warp
+        const int chalf = (warp - 2) >> 2;  // which half of the tile's columns this warp drains
+        constexpr int CHUNKS = BN / 64;     // 32-column chunks per warp
         int acc = 0;
         uint32_t acc_phase = 0;
         TC* Cb = (TC*)p.C;
@@ -267,7 +269,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
+            for (int c = chalf * CHUNKS; c < (chalf + 1) * CHUNKS; ++c) {
                 uint32_t r[32];
                 tmem_ld_32x32(taddr + c * 32, r);
                 tmem_ld_wait();
@@ -279,20 +281,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
                     if (p.bias) {
                         const float* bp = p.bias + (long long)b0 * p.bias_sb0 + n;
+                        if (nvalid >= 32 && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (j < nvalid) v[j] += __ldg(bp + j);
+                            for (int j = 0; j < 32; j += 4) {
+                                const float4 bv = __ldg(reinterpret_cast<const float4*>(bp + j));
+                                v[j] += bv.x; v[j + 1] += bv.y; v[j + 2] += bv.z; v[j + 3] += bv.w;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (j < nvalid) v[j] += __ldg(bp + j);
+                        }
                     }
                     if (AOb) store_row_chunk<TC>(AOb + row_off + n, v, nvalid, vec_ok);
                     if (p.act == B200ASR_ACT_GELU) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+                        for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);
                     }
                     if (p.mul_gelu_grad) {
                         float u[32];
                         load_row_chunk<TC>(AIb + row_off + n, u, nvalid, vec_ok);
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] *= gelu_erf_grad(u[j]);
+                        for (int j = 0; j < 32; ++j) v[j] *= gelu_grad_fast(u[j]);
                     }
                     if (Rb) {
                         float u[32];
