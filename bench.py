@@ -243,6 +243,13 @@ def run_b200(args):
     clk = clocks.stop() if clocks else None
     ms_e2e, _, last_loss = timed(args.steps, e2e=True)
 
+    # ---- host enqueue time of one step (no synchronisation inside: pure Python + launch cost; the GPU queue holds a step)
+    torch.cuda.synchronize()
+    h0 = time.perf_counter()
+    local_step(resident[0])
+    host_ms = (time.perf_counter() - h0) * 1e3
+    torch.cuda.synchronize()
+
     # ---- roofline leg: one extra instrumented step, every GEMM / attention call bracketed by CUDA events
     ops.PROFILE = []
     local_step(resident[0])
@@ -280,6 +287,7 @@ def run_b200(args):
                     "d2h_bytes_per_step": 4, "last_loss": last_loss},
             "gpu_launches": int(launches) * args.steps,
             "gpu_launches_per_step": int(launches),
+            "host_enqueue_ms_per_step": host_ms,
             "step_tflops": algo_tflop * world / (ms_step * 1e-3),
             "step_frac_of_tensor_peak": algo_tflop / (ms_step * 1e-3) / peak,
             "fedavg_round_s": ms_step * 1e-3, "fedavg_agg_ms": agg_ms if world > 1 else None,

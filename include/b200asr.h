@@ -56,12 +56,14 @@ long long b200asr_launch_count(void);
 int b200asr_layernorm_fwd(const void* x, const void* res, const float* w, const float* b, void* y, void* sum_out,
                           float* mean, float* rstd, int rows, int cols, float eps, int act, int dtype, void* stream);
 /* Backward of the above w.r.t. s (dx) and w, b.  `s` is the pre-norm input.  dw/db: fp32 [cols] or NULL.
- * workspace: fp32, >= b200asr_layernorm_bwd_workspace_bytes(cols) bytes (only used when dw/db != NULL).
+ * dx_colsum: NULL or fp32 [cols] = column sums of dx (the bias gradient of the nn.Linear whose output + residual
+ * fed this LayerNorm: HF:330-343 -- saves a separate reduction pass over dx).
+ * workspace: fp32, >= b200asr_layernorm_bwd_workspace_bytes(cols) bytes (only used when dw/db/dx_colsum != NULL).
  * dres_add: NULL or [rows, cols] (dtype) added to dx (fuses the residual-branch gradient sum). */
 size_t b200asr_layernorm_bwd_workspace_bytes(int cols);
 int b200asr_layernorm_bwd(const void* dy, const void* s, const float* w, const float* b, const float* mean,
-                          const float* rstd, const void* dres_add, void* dx, float* dw, float* db, void* workspace,
-                          size_t workspace_bytes, int rows, int cols, int act, int dtype, void* stream);
+                          const float* rstd, const void* dres_add, void* dx, float* dw, float* db, float* dx_colsum,
+                          void* workspace, size_t workspace_bytes, int rows, int cols, int act, int dtype, void* stream);
 
 /* Column sums of a [rows, cols] matrix (bias gradients: what autograd does for nn.Linear.bias).
  * out fp32 [cols]; workspace >= b200asr_colsum_workspace_bytes(cols). */

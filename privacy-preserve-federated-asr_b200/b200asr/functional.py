@@ -151,25 +151,41 @@ def _bgrad(ps, need, dy):
     return None
 
 
-def _ln_bwd(dy, s, w, b, mean, rstd, need, **kw):
-    """LayerNorm backward whose affine gradients go straight to the sinks when both are fresh."""
+def _ln_bwd(dy, s, w, b, mean, rstd, need, in_bias=None, **kw):
+    """LayerNorm backward.  Affine gradients go straight to their sinks when fresh.  `in_bias` = the bias parameter
+    of the Linear / conv whose output fed this LayerNorm: its gradient is the column sum of dx, which the kernel
+    emits in the same pass.  Returns (dx, dw, db, d_in_bias) with None for everything already delivered to a sink."""
+    cols = s.shape[-1]
+    dxsum = bias_sink = None
+    bias_fresh = True
+    if in_bias is not None and need:
+        bias_sink, bias_fresh = grad_sink((in_bias,))
+        dxsum = bias_sink if (bias_sink is not None and bias_fresh) else torch.empty(cols, dtype=torch.float32, device=s.device)
+    dw = db = None
     if need and w is not None:
         sw, fw = grad_sink((w,))
         sb, fb = grad_sink((b,))
         if sw is not None and sb is not None and fw and fb:
-            dx, _, _ = ops.layernorm_bwd(dy, s, w, b, mean, rstd, dw_out=sw, db_out=sb, **kw)
-            return dx, None, None
-        dx, dw, db = ops.layernorm_bwd(dy, s, w, b, mean, rstd, **kw)
-        if sw is not None:
-            if fw: sw.copy_(dw)
-            else: ops.axpy_(sw, dw)
-            dw = None
-        if sb is not None:
-            if fb: sb.copy_(db)
-            else: ops.axpy_(sb, db)
-            db = None
-        return dx, dw, db
-    return ops.layernorm_bwd(dy, s, w, b, mean, rstd, want_wgrad=False, **kw)
+            dx, _, _ = ops.layernorm_bwd(dy, s, w, b, mean, rstd, dw_out=sw, db_out=sb, dxsum_out=dxsum, **kw)
+        else:
+            dx, dw, db = ops.layernorm_bwd(dy, s, w, b, mean, rstd, dxsum_out=dxsum, **kw)
+            if sw is not None:
+                if fw: sw.copy_(dw)
+                else: ops.axpy_(sw, dw)
+                dw = None
+            if sb is not None:
+                if fb: sb.copy_(db)
+                else: ops.axpy_(sb, db)
+                db = None
+    else:
+        dx, _, _ = ops.layernorm_bwd(dy, s, w, b, mean, rstd, want_wgrad=False, dxsum_out=dxsum, **kw)
+    d_in_bias = None
+    if dxsum is not None and dxsum is not bias_sink:
+        if bias_sink is not None:
+            ops.axpy_(bias_sink, dxsum)
+        else:
+            d_in_bias = dxsum
+    return dx, dw, db, d_in_bias
 
 
 # ----------------------------------------------------------------------------- frozen feature extractor
@@ -232,7 +248,7 @@ class FeatureProjectionFn(torch.autograd.Function):
         dlw = dlb = None
         if need[1] or need[2]:
             dn = ops.linear_dgrad(dy2, wsh)
-            _, dlw, dlb = _ln_bwd(dn, x2, ln_w, ln_b, mean, rstd, True)
+            _, dlw, dlb, _ = _ln_bwd(dn, x2, ln_w, ln_b, mean, rstd, True)
         return None, dlw, dlb, dw, db, None, None, None
 
 
@@ -273,13 +289,12 @@ class PosConvEmbedFn(torch.autograd.Function):
         ln_w, ln_b, ws, bs = ctx.params
         need = ctx.needs_input_grad
         dout2 = dout.reshape(B * T, d)
-        ds, dlw, dlb = _ln_bwd(dout2, s, ln_w, ln_b, mean, rstd, need[1] or need[2])
+        ds, dlw, dlb, _ = _ln_bwd(dout2, s, ln_w, ln_b, mean, rstd, need[1] or need[2])
         dy = ds  # gradient into posconv output; ds is also the residual-path gradient
         dws, dbs = [None] * n, [None] * n
         for j in range(n - 1, -1, -1):
             y_in, c, cm, cr = saved[4 * j:4 * j + 4]
-            dc, _, _ = ops.layernorm_bwd(dy, c.view(B * T, d), None, None, cm, cr, act=ACT_GELU)
-            dbs[j] = _bgrad(bs[j], need[7 + n + j], dc)
+            dc, _, _, dbs[j] = _ln_bwd(dy, c.view(B * T, d), None, None, cm, cr, need[7 + n + j], in_bias=bs[j], act=ACT_GELU)
             need_dx = j > 0 or need[0]
             want_dw = need[7 + j]
             sink, fresh = grad_sink((ws[j],)) if want_dw else (None, True)
@@ -335,15 +350,13 @@ class EncoderLayerFn(torch.autograd.Function):
         B, T, H, dh, scale = ctx.meta
         d = x.shape[1]
         wg = any(ctx.needs_input_grad[4:])  # parameter gradients wanted?
-        ds2, dln2w, dln2b = _ln_bwd(dy, s2, ln2_w, ln2_b, m2, r2, wg)
-        db2 = _bgrad(b2, wg, ds2)
+        ds2, dln2w, dln2b, db2 = _ln_bwd(dy, s2, ln2_w, ln2_b, m2, r2, wg, in_bias=b2)
         dw2 = _wgrad(w2, wg, ds2, g)
         du = ops.linear_dgrad(ds2, w2s, gelu_preact=u)            # (ds2 W2) * gelu'(u)
         db1 = _bgrad(b1, wg, du)
         dw1 = _wgrad(w1, wg, du, x1)
         dx1 = ops.linear_dgrad(du, w1s, residual=ds2)            # + residual path of s2 = x1 + ...
-        ds1, dln1w, dln1b = _ln_bwd(dx1, s1, ln1_w, ln1_b, m1, r1, wg)
-        dbo = _bgrad(o_b, wg, ds1)
+        ds1, dln1w, dln1b, dbo = _ln_bwd(dx1, s1, ln1_w, ln1_b, m1, r1, wg, in_bias=o_b)
         dwo = _wgrad(o_w, wg, ds1, attn)
         dattn = ops.linear_dgrad(ds1, wo)
         dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale)

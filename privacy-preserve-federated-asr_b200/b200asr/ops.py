@@ -151,9 +151,11 @@ def layernorm_fwd(x, w, b, eps, res=None, act=ACT_NONE, want_sum=False, want_sta
     return y, s, mean, rstd
 
 
-def layernorm_bwd(dy, s, w, b, mean, rstd, act=ACT_NONE, dres_add=None, want_wgrad=True, dw_out=None, db_out=None):
+def layernorm_bwd(dy, s, w, b, mean, rstd, act=ACT_NONE, dres_add=None, want_wgrad=True, dw_out=None, db_out=None,
+                  dxsum_out=None):
     """Returns (dx, dw, db); dw/db are None when the LN has no affine or want_wgrad is False.
-    dw_out/db_out: optional preallocated fp32 [cols] destinations (overwritten)."""
+    dw_out/db_out: optional preallocated fp32 [cols] destinations (overwritten).
+    dxsum_out: optional fp32 [cols] receiving the column sums of dx (bias gradient of the producing Linear)."""
     dy = _c(dy)
     s = _c(s)
     cols = s.shape[-1]
@@ -164,10 +166,11 @@ def layernorm_bwd(dy, s, w, b, mean, rstd, act=ACT_NONE, dres_add=None, want_wgr
     if w is not None and want_wgrad:
         dw = dw_out if dw_out is not None else torch.empty(cols, dtype=torch.float32, device=s.device)
         db = db_out if db_out is not None else torch.empty(cols, dtype=torch.float32, device=s.device)
+    if dw is not None or dxsum_out is not None:
         nws = lib.b200asr_layernorm_bwd_workspace_bytes(cols)
         ws = workspace(nws, s.device)
     check(lib.b200asr_layernorm_bwd(_p(dy), _p(s), _p(w), _p(b), _p(mean), _p(rstd), _p(dres_add), _p(dx), _p(dw),
-                                    _p(db), _p(ws), nws, rows, cols, act, dt(s), _st()), "layernorm_bwd")
+                                    _p(db), _p(dxsum_out), _p(ws), nws, rows, cols, act, dt(s), _st()), "layernorm_bwd")
     return dx, dw, db
 
 

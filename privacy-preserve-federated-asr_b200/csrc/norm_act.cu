@@ -7,6 +7,15 @@ namespace b200asr {
 constexpr int LN_BWD_BLOCKS = 296;   // 2 x 148 SMs; fixed so that the workspace size is device independent
 constexpr int COLSUM_CHUNKS = 64;
 
+// per-lane helpers: N consecutive fp32 affine parameters starting at column c (c is a multiple of N >= 4)
+template <int N> __device__ __forceinline__ void load_params(const float* __restrict__ p, int c, float* out) {
+#pragma unroll
+    for (int j = 0; j < N; j += 4) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(p + c + j));
+        out[j] = v.x; out[j + 1] = v.y; out[j + 2] = v.z; out[j + 3] = v.w;
+    }
+}
+
 template <typename T, int NV>
 __global__ void __launch_bounds__(128) ln_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res,
                                                      const float* __restrict__ w, const float* __restrict__ b,
@@ -73,11 +82,15 @@ __global__ void __launch_bounds__(128) ln_fwd_kernel(const T* __restrict__ x, co
         for (int i = 0; i < NV; ++i) {
             const int vi = lane + 32 * i;
             if (vi < nvec) {
-                float o[N];
+                float o[N], wv[N], bv[N];
+                if (w) {
+                    load_params<N>(w, vi * N, wv);
+                    load_params<N>(b, vi * N, bv);
+                }
 #pragma unroll
                 for (int j = 0; j < N; ++j) {
                     float t = (v[i][j] - mean) * rstd;
-                    if (w) t = t * __ldg(w + vi * N + j) + __ldg(b + vi * N + j);
+                    if (w) t = fmaf(t, wv[j], bv[j]);
                     if (act == B200ASR_ACT_GELU) t = gelu_erf(t);
                     o[j] = t;
                 }
@@ -89,60 +102,63 @@ __global__ void __launch_bounds__(128) ln_fwd_kernel(const T* __restrict__ x, co
     }
 }
 
-template <typename T, int NV>
-__global__ void __launch_bounds__(128) ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ s,
-                                                     const float* __restrict__ w, const float* __restrict__ b,
-                                                     const float* __restrict__ mean_in,
-                                                     const float* __restrict__ rstd_in,
-                                                     const T* __restrict__ dres_add, T* __restrict__ dx,
-                                                     float* __restrict__ partial, int rows, int cols, int act) {
+// LayerNorm backward.  One warp per row; the row is read twice (HBM, then L1) so that only the three column
+// accumulators stay in registers: dw += dz*xhat, db += dz, and (CS) the column sums of dx (= the bias gradient of
+// the nn.Linear that produced the LayerNorm input).  Per-block partials -> reduce_partials_kernel (deterministic).
+template <typename T, int NV, bool CS>
+__global__ void __launch_bounds__(256, 2) ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ s,
+                                                        const float* __restrict__ w, const float* __restrict__ b,
+                                                        const float* __restrict__ mean_in,
+                                                        const float* __restrict__ rstd_in,
+                                                        const T* __restrict__ dres_add, T* __restrict__ dx,
+                                                        float* __restrict__ partial, int rows, int cols, int act) {
     constexpr int N = Vec16<T>::N;
-    extern __shared__ float sacc[];  // [2][cols] when partial != nullptr
+    extern __shared__ float sacc[];  // [3][cols] when partial != nullptr
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int nwarps = (gridDim.x * blockDim.x) >> 5;
     const int nvec = cols / N;
     const float inv_cols = 1.0f / (float)cols;
     if (partial) {
-        for (int i = threadIdx.x; i < 2 * cols; i += blockDim.x) sacc[i] = 0.f;
+        for (int i = threadIdx.x; i < 3 * cols; i += blockDim.x) sacc[i] = 0.f;
         __syncthreads();
     }
-    float aw[NV][N], ab[NV][N];
+    float aw[NV][N], ab[NV][N], ac[CS ? NV : 1][N];
 #pragma unroll
     for (int i = 0; i < NV; ++i)
 #pragma unroll
-        for (int j = 0; j < N; ++j) aw[i][j] = ab[i][j] = 0.f;
+        for (int j = 0; j < N; ++j) {
+            aw[i][j] = ab[i][j] = 0.f;
+            if (CS) ac[i][j] = 0.f;
+        }
 
     for (int row = warp; row < rows; row += nwarps) {
         const long long base = (long long)row * cols;
         const float mean = mean_in[row], rstd = rstd_in[row];
-        float xh[NV][N], dz[NV][N];
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
             const int vi = lane + 32 * i;
             if (vi < nvec) {
                 Vec16<T> a, g;
+                float xh[N], dz[N], wv[N], bv[N];
                 a.load(s + base + (long long)vi * N);
                 g.load(dy + base + (long long)vi * N);
-                a.unpack(xh[i]);
-                g.unpack(dz[i]);
+                a.unpack(xh);
+                g.unpack(dz);
+                if (w) load_params<N>(w, vi * N, wv);
+                if (w && act == B200ASR_ACT_GELU) load_params<N>(b, vi * N, bv);
 #pragma unroll
                 for (int j = 0; j < N; ++j) {
-                    const float h = (xh[i][j] - mean) * rstd;
-                    xh[i][j] = h;
-                    const float wj = w ? __ldg(w + vi * N + j) : 1.f;
-                    float d = dz[i][j];
-                    if (act == B200ASR_ACT_GELU) {
-                        const float z = w ? h * wj + __ldg(b + vi * N + j) : h;
-                        d *= gelu_erf_grad(z);
-                    }
-                    aw[i][j] += d * h;
+                    const float h = (xh[j] - mean) * rstd;
+                    const float wj = w ? wv[j] : 1.f;
+                    float d = dz[j];
+                    if (act == B200ASR_ACT_GELU) d *= gelu_erf_grad(w ? fmaf(h, wj, bv[j]) : h);
+                    aw[i][j] = fmaf(d, h, aw[i][j]);
                     ab[i][j] += d;
                     d *= wj;
-                    dz[i][j] = d;
                     s1 += d;
-                    s2 += d * h;
+                    s2 = fmaf(d, h, s2);
                 }
             }
         }
@@ -152,9 +168,23 @@ __global__ void __launch_bounds__(128) ln_bwd_kernel(const T* __restrict__ dy, c
         for (int i = 0; i < NV; ++i) {
             const int vi = lane + 32 * i;
             if (vi < nvec) {
-                float o[N];
+                Vec16<T> a, g;
+                float xh[N], dz[N], wv[N], bv[N], o[N];
+                a.load(s + base + (long long)vi * N);   // L1 hit: this warp read the row a moment ago
+                g.load(dy + base + (long long)vi * N);
+                a.unpack(xh);
+                g.unpack(dz);
+                if (w) load_params<N>(w, vi * N, wv);
+                if (w && act == B200ASR_ACT_GELU) load_params<N>(b, vi * N, bv);
 #pragma unroll
-                for (int j = 0; j < N; ++j) o[j] = rstd * (dz[i][j] - s1 - xh[i][j] * s2);
+                for (int j = 0; j < N; ++j) {
+                    const float h = (xh[j] - mean) * rstd;
+                    const float wj = w ? wv[j] : 1.f;
+                    float d = dz[j];
+                    if (act == B200ASR_ACT_GELU) d *= gelu_erf_grad(w ? fmaf(h, wj, bv[j]) : h);
+                    d *= wj;
+                    o[j] = rstd * (d - s1 - h * s2);
+                }
                 if (dres_add) {
                     Vec16<T> r;
                     float rf[N];
@@ -166,6 +196,11 @@ __global__ void __launch_bounds__(128) ln_bwd_kernel(const T* __restrict__ dy, c
                 Vec16<T> ov;
                 ov.pack(o);
                 ov.store(dx + base + (long long)vi * N);
+                if (CS) {
+                    ov.unpack(o);  // sum what was stored (the rounded values the consumer GEMMs read)
+#pragma unroll
+                    for (int j = 0; j < N; ++j) ac[i][j] += o[j];
+                }
             }
         }
     }
@@ -178,21 +213,22 @@ __global__ void __launch_bounds__(128) ln_bwd_kernel(const T* __restrict__ dy, c
                 for (int j = 0; j < N; ++j) {
                     atomicAdd(&sacc[vi * N + j], aw[i][j]);
                     atomicAdd(&sacc[cols + vi * N + j], ab[i][j]);
+                    if (CS) atomicAdd(&sacc[2 * cols + vi * N + j], ac[i][j]);
                 }
             }
         }
         __syncthreads();
-        float* out = partial + (long long)blockIdx.x * 2 * cols;
-        for (int i = threadIdx.x; i < 2 * cols; i += blockDim.x) out[i] = sacc[i];
+        float* out = partial + (long long)blockIdx.x * 3 * cols;
+        for (int i = threadIdx.x; i < 3 * cols; i += blockDim.x) out[i] = sacc[i];
     }
 }
 
 // out[c] = sum_{p < nparts} partial[p * stride + c] for c < ncols_total; columns [0, cols) go to out0, [cols, 2 cols)
-// to out1.  One block = 32 columns x 8 warps; warp w sums partials w, w+8, ... (coalesced 128-byte rows, 4 loads
+// to out1, [2 cols, 3 cols) to out2.  One block = 32 columns x 8 warps; warp w sums partials w, w+8, ... (coalesced 128-byte rows, 4 loads
 // in flight per thread), then a fixed-order shared-memory combine: deterministic.
 __global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ partial, float* __restrict__ out0,
-                                                              float* __restrict__ out1, int nparts, int cols,
-                                                              int ncols_total, int stride) {
+                                                              float* __restrict__ out1, float* __restrict__ out2,
+                                                              int nparts, int cols, int ncols_total, int stride) {
     __shared__ float red[8][33];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + lane;
@@ -214,7 +250,8 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __res
 #pragma unroll
         for (int i = 0; i < 8; ++i) t += red[i][lane];
         if (c < cols) { if (out0) out0[c] = t; }
-        else if (out1) out1[c - cols] = t;
+        else if (c < 2 * cols) { if (out1) out1[c - cols] = t; }
+        else if (out2) out2[c - 2 * cols] = t;
     }
 }
 
@@ -236,6 +273,55 @@ __global__ void colsum_partial_kernel(const T* __restrict__ x, float* __restrict
     }
     for (; r < r1; ++r) a0 += to_f<T>(x[(long long)r * ld + c]);
     partial[(long long)blockIdx.y * cols + c] = (a0 + a1) + (a2 + a3);
+}
+
+// vectorised variant: a block = 32 column vectors (16 B each) x 8 row lanes; needs cols % N == 0, ld % N == 0 and a
+// 16-byte aligned base.  partial[chunk][cols].
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_partial_vec_kernel(const T* __restrict__ x, float* __restrict__ partial,
+                                                                 int rows, int cols, int ld, int rows_per_chunk) {
+    constexpr int N = Vec16<T>::N;
+    __shared__ float red[8][32][N + 1];
+    const int cv = threadIdx.x & 31, rl = threadIdx.x >> 5;
+    const int c = (blockIdx.x * 32 + cv) * N;
+    const int r0 = blockIdx.y * rows_per_chunk;
+    const int r1 = min(rows, r0 + rows_per_chunk);
+    float acc[N], acc2[N];
+#pragma unroll
+    for (int j = 0; j < N; ++j) acc[j] = acc2[j] = 0.f;
+    if (c < cols) {
+        int r = r0 + rl;
+        for (; r + 8 < r1; r += 16) {
+            Vec16<T> a, b;
+            float af[N], bf[N];
+            a.load(x + (long long)r * ld + c);
+            b.load(x + (long long)(r + 8) * ld + c);
+            a.unpack(af);
+            b.unpack(bf);
+#pragma unroll
+            for (int j = 0; j < N; ++j) { acc[j] += af[j]; acc2[j] += bf[j]; }
+        }
+        for (; r < r1; r += 8) {
+            Vec16<T> a;
+            float af[N];
+            a.load(x + (long long)r * ld + c);
+            a.unpack(af);
+#pragma unroll
+            for (int j = 0; j < N; ++j) acc[j] += af[j];
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < N; ++j) red[rl][cv][j] = acc[j] + acc2[j];
+    __syncthreads();
+    if (rl == 0 && c < cols) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+            float t = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) t += red[i][cv][j];
+            partial[(long long)blockIdx.y * cols + c + j] = t;
+        }
+    }
 }
 
 template <typename T>
@@ -263,18 +349,24 @@ static int launch_ln_fwd(const void* x, const void* res, const float* w, const f
 
 template <typename T>
 static int launch_ln_bwd(const void* dy, const void* s, const float* w, const float* b, const float* mean,
-                         const float* rstd, const void* dres, void* dx, float* partial, int rows, int cols, int act,
-                         cudaStream_t st) {
+                         const float* rstd, const void* dres, void* dx, float* partial, bool colsum, int rows, int cols,
+                         int act, cudaStream_t st) {
     constexpr int N = Vec16<T>::N;
     const int nvec = cols / N;
     const int nv = ceil_div(nvec, 32);
-    int grid = ceil_div(rows, 4);
+    int grid = ceil_div(rows, 8);
     if (grid > LN_BWD_BLOCKS) grid = LN_BWD_BLOCKS;
     if (partial) grid = LN_BWD_BLOCKS;  // finalize sums exactly LN_BWD_BLOCKS partials
-    const size_t smem = partial ? (size_t)2 * cols * sizeof(float) : 0;
-#define LN_BWD_CASE(NVV)                                                                                     \
-    ln_bwd_kernel<T, NVV><<<grid, 128, smem, st>>>((const T*)dy, (const T*)s, w, b, mean, rstd, (const T*)dres, \
-                                                    (T*)dx, partial, rows, cols, act)
+    const size_t smem = partial ? (size_t)3 * cols * sizeof(float) : 0;
+#define LN_BWD_CASE(NVV)                                                                                          \
+    do {                                                                                                          \
+        if (colsum)                                                                                               \
+            ln_bwd_kernel<T, NVV, true><<<grid, 256, smem, st>>>((const T*)dy, (const T*)s, w, b, mean, rstd,      \
+                                                                 (const T*)dres, (T*)dx, partial, rows, cols, act); \
+        else                                                                                                      \
+            ln_bwd_kernel<T, NVV, false><<<grid, 256, smem, st>>>((const T*)dy, (const T*)s, w, b, mean, rstd,     \
+                                                                  (const T*)dres, (T*)dx, partial, rows, cols, act); \
+    } while (0)
     if (nv <= 1) LN_BWD_CASE(1);
     else if (nv <= 2) LN_BWD_CASE(2);
     else if (nv <= 4) LN_BWD_CASE(4);
@@ -298,35 +390,40 @@ int b200asr_layernorm_fwd(const void* x, const void* res, const float* w, const 
     B200_REQUIRE((w == nullptr) == (b == nullptr), "layernorm_fwd: w and b must both be given or both NULL");
     B200_REQUIRE(cols > 0 && cols % (dtype == B200ASR_BF16 ? 8 : 4) == 0,
                  "layernorm_fwd: cols=%d must be a multiple of the 16-byte vector width", cols);
+    B200_REQUIRE(!w || (((uintptr_t)w | (uintptr_t)b) & 15) == 0, "layernorm_fwd: w/b must be 16-byte aligned");
     B200_DISPATCH_DTYPE(dtype, {
         return launch_ln_fwd<T>(x, res, w, b, y, sum_out, mean, rstd, rows, cols, eps, act, as_stream(stream));
     });
     return B200ASR_OK;
 }
 
-size_t b200asr_layernorm_bwd_workspace_bytes(int cols) { return (size_t)LN_BWD_BLOCKS * 2 * cols * sizeof(float); }
+size_t b200asr_layernorm_bwd_workspace_bytes(int cols) { return (size_t)LN_BWD_BLOCKS * 3 * cols * sizeof(float); }
 
 int b200asr_layernorm_bwd(const void* dy, const void* s, const float* w, const float* b, const float* mean,
-                          const float* rstd, const void* dres_add, void* dx, float* dw, float* db, void* workspace,
-                          size_t workspace_bytes, int rows, int cols, int act, int dtype, void* stream) {
+                          const float* rstd, const void* dres_add, void* dx, float* dw, float* db, float* dx_colsum,
+                          void* workspace, size_t workspace_bytes, int rows, int cols, int act, int dtype,
+                          void* stream) {
     if (rows <= 0) return B200ASR_OK;
     B200_REQUIRE(dy && s && mean && rstd && dx, "layernorm_bwd: null pointer");
     B200_REQUIRE(cols > 0 && cols % (dtype == B200ASR_BF16 ? 8 : 4) == 0, "layernorm_bwd: bad cols=%d", cols);
+    B200_REQUIRE(!w || (((uintptr_t)w | (uintptr_t)b) & 15) == 0, "layernorm_bwd: w/b must be 16-byte aligned");
     float* partial = nullptr;
-    if (dw || db) {
+    if (dw || db || dx_colsum) {
         B200_REQUIRE(workspace && workspace_bytes >= b200asr_layernorm_bwd_workspace_bytes(cols),
                      "layernorm_bwd: workspace too small");
-        B200_REQUIRE((size_t)2 * cols * sizeof(float) <= 48 * 1024, "layernorm_bwd: cols=%d too large", cols);
+        B200_REQUIRE((size_t)3 * cols * sizeof(float) <= 48 * 1024, "layernorm_bwd: cols=%d too large", cols);
         partial = (float*)workspace;
     }
     int rc;
     B200_DISPATCH_DTYPE(dtype, {
-        rc = launch_ln_bwd<T>(dy, s, w, b, mean, rstd, dres_add, dx, partial, rows, cols, act, as_stream(stream));
+        rc = launch_ln_bwd<T>(dy, s, w, b, mean, rstd, dres_add, dx, partial, dx_colsum != nullptr, rows, cols, act,
+                              as_stream(stream));
     });
     if (rc != B200ASR_OK) return rc;
     if (partial) {
-        reduce_partials_kernel<<<ceil_div(2 * cols, 32), 256, 0, as_stream(stream)>>>(partial, dw, db, LN_BWD_BLOCKS, cols,
-                                                                                      2 * cols, 2 * cols);
+        const int total = dx_colsum ? 3 * cols : 2 * cols;
+        reduce_partials_kernel<<<ceil_div(total, 32), 256, 0, as_stream(stream)>>>(partial, dw, db, dx_colsum, LN_BWD_BLOCKS,
+                                                                                   cols, total, 3 * cols);
         return check_launch("layernorm_bwd_reduce");
     }
     return B200ASR_OK;
@@ -339,17 +436,32 @@ int b200asr_colsum(const void* x, float* out, void* workspace, size_t workspace_
     B200_REQUIRE(x && out && workspace, "colsum: null pointer");
     B200_REQUIRE(rows > 0 && cols > 0 && ld >= cols, "colsum: bad shape");
     B200_REQUIRE(workspace_bytes >= b200asr_colsum_workspace_bytes(cols), "colsum: workspace too small");
-    const int chunks = rows < COLSUM_CHUNKS ? rows : COLSUM_CHUNKS;
-    const int rpc = ceil_div(rows, chunks);
-    const int nchunks = ceil_div(rows, rpc);
-    dim3 grid(ceil_div(cols, 128), nchunks);
-    B200_DISPATCH_DTYPE(dtype, {
-        colsum_partial_kernel<T><<<grid, 128, 0, as_stream(stream)>>>((const T*)x, (float*)workspace, rows, cols, ld,
-                                                                        rpc);
-    });
+    const int nvec = dtype == B200ASR_BF16 ? 8 : 4;
+    int nchunks;
+    if (cols % nvec == 0 && ld % nvec == 0 && ((uintptr_t)x & 15) == 0) {
+        const int gx = ceil_div(cols, 32 * nvec);
+        int chunks = (4 * num_sms()) / gx;
+        if (chunks > COLSUM_CHUNKS) chunks = COLSUM_CHUNKS;
+        if (chunks > ceil_div(rows, 8)) chunks = ceil_div(rows, 8);
+        if (chunks < 1) chunks = 1;
+        const int rpc = ceil_div(rows, chunks);
+        nchunks = ceil_div(rows, rpc);
+        dim3 grid(gx, nchunks);
+        B200_DISPATCH_DTYPE(dtype, {
+            colsum_partial_vec_kernel<T><<<grid, 256, 0, as_stream(stream)>>>((const T*)x, (float*)workspace, rows, cols, ld, rpc);
+        });
+    } else {
+        const int chunks = rows < COLSUM_CHUNKS ? rows : COLSUM_CHUNKS;
+        const int rpc = ceil_div(rows, chunks);
+        nchunks = ceil_div(rows, rpc);
+        dim3 grid(ceil_div(cols, 128), nchunks);
+        B200_DISPATCH_DTYPE(dtype, {
+            colsum_partial_kernel<T><<<grid, 128, 0, as_stream(stream)>>>((const T*)x, (float*)workspace, rows, cols, ld, rpc);
+        });
+    }
     int rc = check_launch("colsum_partial");
     if (rc != B200ASR_OK) return rc;
-    reduce_partials_kernel<<<ceil_div(cols, 32), 256, 0, as_stream(stream)>>>((const float*)workspace, out, nullptr,
+    reduce_partials_kernel<<<ceil_div(cols, 32), 256, 0, as_stream(stream)>>>((const float*)workspace, out, nullptr, nullptr,
                                                                               nchunks, cols, cols, cols);
     return check_launch("colsum_reduce");
 }

@@ -54,8 +54,10 @@ def test_layernorm_fwd_bwd(dtype, cols, affine, act, res):
     y, s, mean, rstd = ops.layernorm_fwd(cu(x), cu(w), cu(b), 1e-5, res=cu(r), act=act, want_sum=True)
     assert rel(y, y_ref.detach()) < tol(dtype)
     s_in = s if res else cu(x)
-    dx, dw, db = ops.layernorm_bwd(cu(dy), s_in, cu(w), cu(b), mean, rstd, act=act, dres_add=cu(dres))
+    dxsum = torch.empty(cols, dtype=torch.float32, device=DEV)
+    dx, dw, db = ops.layernorm_bwd(cu(dy), s_in, cu(w), cu(b), mean, rstd, act=act, dres_add=cu(dres), dxsum_out=dxsum)
     assert rel(dx, s_ref.grad + dres.float()) < tol(dtype)
+    assert rel(dxsum, dx.float().sum(0)) < 1e-5  # column sums of the stored dx (bias gradient of the producing Linear)
     if affine:
         assert rel(dw, wr.grad) < tol(dtype, 1e-4, 3e-2)
         assert rel(db, br.grad) < tol(dtype, 1e-4, 3e-2)
