@@ -129,6 +129,9 @@ typedef struct b200asr_gemm_args {
 } b200asr_gemm_args;
 int b200asr_gemm(const b200asr_gemm_args* args, void* stream);
 
+/* test / tuning hook: force the tcgen05 tile configuration: 0 = built-in cost model, else ncta * 1000 + bn
+ * (1064, 1128, 1256 single CTA; 2128, 2256 CTA pair = cluster of 2 with cta_group::2 MMA).  Returns the old value. */
+int b200asr_gemm_force_config(int cfg);
 /* test hook: run b200asr_gemm on a forced back end (0 = fp32 FMA pipes, 1 = tcgen05 tensor cores). */
 int b200asr_gemm_backend(const b200asr_gemm_args* args, int backend, void* stream);
 
@@ -272,6 +275,11 @@ int b200asr_fedavg_peer_reduce(float* const* peer_bufs, const float* weights, in
 int b200asr_adamw_step(float* p, const float* grad, float* m, float* v, void* shadow_bf16, long long n, float lr,
                        float beta1, float beta2, float eps, float weight_decay, int step, const float* gnorm_sq,
                        float max_norm, void* stream);
+/* Same update with the per-step scalars read from device memory: hyper fp32 [2] = {lr, lr * sqrt(1-b2^t) / (1-b1^t)}.
+ * No host value changes between steps, so the launch can be captured in a CUDA graph and replayed. */
+int b200asr_adamw_step_dev(float* p, const float* grad, float* m, float* v, void* shadow_bf16, long long n,
+                           const float* hyper, float beta1, float beta2, float eps, float weight_decay,
+                           const float* gnorm_sq, float max_norm, void* stream);
 /* out[0] += sum(x^2)  (out must be zeroed by the caller for a fresh norm) */
 int b200asr_sumsq(const float* x, long long n, float* out, void* stream);
 

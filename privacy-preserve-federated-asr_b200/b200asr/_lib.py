@@ -52,6 +52,7 @@ SIGNATURES = {
     "b200asr_axpy": (i32, [vp, vp, f32, i64, i32, vp]),
     "b200asr_conv0_ln_gelu_fwd": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, vp]),
     "b200asr_gemm": (i32, [C.POINTER(GemmArgs), vp]),
+    "b200asr_gemm_force_config": (i32, [i32]),
     "b200asr_gemm_backend": (i32, [C.POINTER(GemmArgs), i32, vp]),
     "b200asr_softmax_rows": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]),
     "b200asr_softmax_rows_bwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]),
@@ -77,6 +78,7 @@ SIGNATURES = {
     "b200asr_fedavg_prescale": (i32, [vp, f32, i64, vp]),
     "b200asr_fedavg_peer_reduce": (i32, [C.POINTER(vp), C.POINTER(f32), i32, i32, i64, vp]),
     "b200asr_adamw_step": (i32, [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i32, vp, f32, vp]),
+    "b200asr_adamw_step_dev": (i32, [vp, vp, vp, vp, vp, i64, vp, f32, f32, f32, f32, vp, f32, vp]),
     "b200asr_sumsq": (i32, [vp, i64, vp, vp]),
 }
 

@@ -500,6 +500,15 @@ def adamw_step_(p, grad, m, v, shadow, lr, beta1, beta2, eps, weight_decay, step
                                  float(max_norm), _st()), "adamw_step")
 
 
+def adamw_step_dev_(p, grad, m, v, shadow, hyper, beta1, beta2, eps, weight_decay, gnorm_sq=None, max_norm=1.0):
+    """AdamW with {lr, bias-corrected step size} read from the device tensor `hyper` (graph-replayable launch)."""
+    for t in (p, grad, m, v, hyper):
+        assert t.dtype == torch.float32 and t.is_contiguous()
+    check(lib.b200asr_adamw_step_dev(_p(p), _p(grad), _p(m), _p(v), _p(shadow), p.numel(), _p(hyper), float(beta1),
+                                     float(beta2), float(eps), float(weight_decay), _p(gnorm_sq), float(max_norm), _st()),
+          "adamw_step_dev")
+
+
 def sumsq_(x: torch.Tensor, out: torch.Tensor):
     assert x.dtype == torch.float32 and x.is_contiguous() and out.dtype == torch.float32
     check(lib.b200asr_sumsq(_p(x), x.numel(), _p(out), _st()), "sumsq")

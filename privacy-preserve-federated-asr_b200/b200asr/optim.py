@@ -73,19 +73,54 @@ class FusedAdamW:
                         p._b200_grad.add_(p.grad)
                     p.grad = p._b200_grad
 
+    def _clip_norm(self):
+        if self.max_grad_norm is None:
+            return None
+        self.gnorm_sq.zero_()
+        for g in self.groups:
+            ops.sumsq_(g["fp"].grad, self.gnorm_sq)
+        return self.gnorm_sq
+
     def step(self):
         ops.join_side_stream()
         self._gather_stray_grads()
         lr = self.current_lr()
         self.step_count += 1
-        gn = None
-        if self.max_grad_norm is not None:
-            self.gnorm_sq.zero_()
-            for g in self.groups:
-                ops.sumsq_(g["fp"].grad, self.gnorm_sq)
-            gn = self.gnorm_sq
+        gn = self._clip_norm()
         for g in self.groups:
             fp = g["fp"]
             ops.adamw_step_(fp.flat, fp.grad, g["m"], g["v"], fp.shadow, lr, self.betas[0], self.betas[1], self.eps, g["wd"],
                             self.step_count, gn, self.max_grad_norm or 0.0)
             fp.mark_updated(shadow_written=fp.shadow is not None)
+
+    # ---- CUDA-graph friendly split: per-step scalars live in device memory (graph.GraphedTrainStep)
+    def prepare_hyper(self):
+        """Host side of the next update: advances the step counter and uploads {lr, lr*sqrt(1-b2^t)/(1-b1^t)} to the
+        device tensor the captured AdamW launch reads.  Call once before every replay (outside the graph)."""
+        if not hasattr(self, "hyper_dev"):
+            dev = self.groups[0]["fp"].flat.device
+            self.hyper_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+            self.hyper_dev = torch.zeros(2, dtype=torch.float32, device=dev)
+        lr = self.current_lr()
+        self.step_count += 1
+        t = self.step_count
+        self.hyper_host[0] = lr
+        self.hyper_host[1] = lr * (1.0 - self.betas[1] ** t) ** 0.5 / (1.0 - self.betas[0] ** t)
+        self.hyper_dev.copy_(self.hyper_host, non_blocking=True)
+
+    def step_captured(self):
+        """Device side of the update, with no host-dependent scalar: what a CUDA graph captures."""
+        ops.join_side_stream()
+        self._gather_stray_grads()
+        gn = self._clip_norm()
+        for g in self.groups:
+            fp = g["fp"]
+            ops.adamw_step_dev_(fp.flat, fp.grad, g["m"], g["v"], fp.shadow, self.hyper_dev, self.betas[0], self.betas[1],
+                                self.eps, g["wd"], gn, self.max_grad_norm or 0.0)
+            fp.mark_updated(shadow_written=fp.shadow is not None)
+
+    def state_tensors(self):
+        out = []
+        for g in self.groups:
+            out += [g["fp"].flat, g["m"], g["v"]] + ([g["fp"].shadow] if g["fp"].shadow is not None else [])
+        return out

@@ -93,7 +93,12 @@ __global__ void __launch_bounds__(256) fedavg_peer_kernel(const PeerPtrs p, int 
 __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                     float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, long long n,
                                                     float lr, float b1, float b2, float eps, float wd, float step_size,
-                                                    const float* __restrict__ gnorm_sq, float max_norm) {
+                                                    const float* __restrict__ gnorm_sq, float max_norm,
+                                                    const float* __restrict__ hyper) {
+    if (hyper) {  // per-step scalars from device memory: the launch can be replayed from a CUDA graph
+        lr = hyper[0];
+        step_size = hyper[1];
+    }
     float clip = 1.f;
     if (gnorm_sq) {
         const float nrm = sqrtf(*gnorm_sq);
@@ -224,8 +229,20 @@ int b200asr_adamw_step(float* p, const float* grad, float* m, float* v, void* sh
     const double bc2 = 1.0 - pow((double)beta2, (double)step);
     const float step_size = (float)((double)lr * sqrt(bc2) / bc1);
     adamw_kernel<<<stream_grid(n), 256, 0, as_stream(stream)>>>(p, grad, m, v, (__nv_bfloat16*)shadow_bf16, n, lr, beta1, beta2,
-                                                                eps, weight_decay, step_size, gnorm_sq, max_norm);
+                                                                eps, weight_decay, step_size, gnorm_sq, max_norm, nullptr);
     return check_launch("adamw_step");
+}
+
+int b200asr_adamw_step_dev(float* p, const float* grad, float* m, float* v, void* shadow_bf16, long long n, const float* hyper,
+                           float beta1, float beta2, float eps, float weight_decay, const float* gnorm_sq, float max_norm,
+                           void* stream) {
+    B200_REQUIRE(p && grad && m && v && hyper, "adamw_dev: null pointer");
+    B200_REQUIRE((((uintptr_t)p | (uintptr_t)grad | (uintptr_t)m | (uintptr_t)v) & 15) == 0, "adamw_dev: buffers must be 16-byte aligned");
+    B200_REQUIRE(!shadow_bf16 || ((uintptr_t)shadow_bf16 & 7) == 0, "adamw_dev: shadow must be 8-byte aligned");
+    if (n <= 0) return B200ASR_OK;
+    adamw_kernel<<<stream_grid(n), 256, 0, as_stream(stream)>>>(p, grad, m, v, (__nv_bfloat16*)shadow_bf16, n, 0.f, beta1, beta2,
+                                                                eps, weight_decay, 0.f, gnorm_sq, max_norm, hyper);
+    return check_launch("adamw_step_dev");
 }
 
 int b200asr_sumsq(const float* x, long long n, float* out, void* stream) {

@@ -43,3 +43,7 @@ extern "C" int b200asr_gemm_backend(const b200asr_gemm_args* args, int backend, 
     }
     return gemm_tc_launch(*args, as_stream(stream));
 }
+
+// test / tuning hook: force the tcgen05 tile configuration (0 = cost model; else ncta * 1000 + bn, e.g. 2256 = CTA
+// pair with 256 x 256 tiles, 1128 = single CTA 128 x 128).  Returns the previous setting.
+extern "C" int b200asr_gemm_force_config(int cfg) { return gemm_tc_force_config(cfg); }

@@ -10,6 +10,7 @@ int gemm_simt_launch(const b200asr_gemm_args& a, cudaStream_t st);
 // tcgen05 tensor cores (bf16 operands, fp32 accumulate in TMEM)
 bool gemm_tc_eligible(const b200asr_gemm_args& a, const char** why);
 int gemm_tc_launch(const b200asr_gemm_args& a, cudaStream_t st);
+int gemm_tc_force_config(int cfg);  // test hook: 0 = cost model, else ncta * 1000 + bn
 
 // grouped positional conv (64 channels per group, bf16) on the tcgen05 GEMM kernel's conv addressing modes
 int posconv_tc_taps(const void* x, const void* w_pack, const float* bias, void* y, int B, int T, int C, int groups, int k,

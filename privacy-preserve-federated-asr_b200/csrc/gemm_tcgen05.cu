@@ -21,11 +21,15 @@ constexpr int UMMA_K = 16;
 constexpr int NUM_THREADS = 320;  // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quarter: column halves)
 constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
 
-template <int BN> struct Cfg {
-    static constexpr int B_STAGE_BYTES = BN * BLOCK_K * 2;
+// NCTA = 1: one CTA per 128 x BN tile.  NCTA = 2: a CTA pair (cluster of 2, tcgen05 cta_group::2) per 256 x BN tile; each
+// CTA stages its own 128 rows of A and HALF of the B tile, so the L2 -> shared-memory traffic per FLOP drops by 1.5x
+// (BN = 256) against the single-CTA 128 x 256 tile -- the measured limiter of this kernel (profiles/: ~6.3 KB/clk chip
+// wide L2 read cap reached at ~950 TFLOP/s).
+template <int BN, int NCTA = 1> struct Cfg {
+    static constexpr int B_STAGE_BYTES = (BN / NCTA) * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-    static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
-    static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;  // two accumulator buffers
+    static constexpr int STAGES = (NCTA == 2) ? (BN == 256 ? 6 : 8) : ((BN == 256) ? 4 : (BN == 128 ? 6 : 8));
+    static constexpr int TMEM_COLS = (NCTA == 2) ? 512 : ((2 * BN < 32) ? 32 : 2 * BN);  // two accumulator buffers
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
@@ -111,10 +115,15 @@ template <> __device__ __forceinline__ void load_row_chunk<__nv_bfloat16>(const 
     }
 }
 
-template <int BN, typename TC>
+template <int BN, typename TC, int NCTA>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const Params p) {
-    using C_ = Cfg<BN>;
+    using C_ = Cfg<BN, NCTA>;
+    constexpr int TILE_M = BLOCK_M * NCTA;  // rows of one (pair) tile
+    constexpr int BNH = BN / NCTA;          // B rows staged by this CTA
+    const uint32_t rank = (NCTA == 2) ? cluster_ctarank() : 0u;   // 0 = pair leader (issues the MMAs)
+    const int worker = (NCTA == 2) ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int nworkers = (NCTA == 2) ? (int)(gridDim.x >> 1) : (int)gridDim.x;
     extern __shared__ uint8_t smem_raw[];
     // 1024-byte alignment: the 128B swizzle pattern is a function of the absolute shared address
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -140,13 +149,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(tfull_bar(s), 1);
-            mbar_init(tempty_bar(s), 8);  // one arrival per epilogue warp
+            mbar_init(tempty_bar(s), 8 * NCTA);  // one arrival per epilogue warp (of both CTAs of a pair)
         }
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc(tmem_slot, C_::TMEM_COLS);
+    if (warp == 1) {
+        if constexpr (NCTA == 2) tmem_alloc_2sm(tmem_slot, C_::TMEM_COLS);
+        else tmem_alloc(tmem_slot, C_::TMEM_COLS);
+    }
     tc_fence_before();
     __syncthreads();
+    if constexpr (NCTA == 2) cluster_sync_all();  // the peer's barriers are initialised before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_gen;
 
@@ -158,18 +171,39 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (long long tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            for (long long tile = worker; tile < p.num_tiles; tile += nworkers) {
                 const int z = (int)(tile / tiles_per_batch);
                 const int rem = (int)(tile % tiles_per_batch);
                 const int mb = rem / p.tiles_n, nb = rem % p.tiles_n;  // n fastest: neighbours share the A tile in L2
                 const int b0 = z % p.batch0, b1 = z / p.batch0;
-                const int m0 = mb * BLOCK_M, n0 = nb * BN;
+                const int m0 = mb * TILE_M + (int)rank * BLOCK_M, n0 = nb * BN + (int)rank * BNH;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(empty_bar(stage), phase ^ 1u);
-                    mbar_expect_tx(full_bar(stage), C_::STAGE_BYTES);
                     const uint32_t sa = smem_base + stage * C_::STAGE_BYTES;
                     const uint32_t sb = sa + A_STAGE_BYTES;
                     const int k0 = kb * BLOCK_K;
+                    if constexpr (NCTA == 2) {
+                        // both CTAs' loads complete on the LEADER's full barrier, which expects the bytes of the pair
+                        const uint32_t fb = mapa_shared(full_bar(stage), 0);
+                        if (rank == 0) mbar_expect_tx(full_bar(stage), 2 * C_::STAGE_BYTES);
+                        if (!p.a_mn) {
+                            tma_load_4d_2sm(sa, &tma_a, fb, k0, m0, b0, b1);
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < BLOCK_M / 64; ++c)
+                                tma_load_4d_2sm(sa + c * (64 * BLOCK_K * 2), &tma_a, fb, m0 + 64 * c, k0, b0, b1);
+                        }
+                        if (!p.b_mn) {
+                            tma_load_4d_2sm(sb, &tma_b, fb, k0, n0, b0, b1);
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < BNH / 64; ++c)
+                                tma_load_4d_2sm(sb + c * (64 * BLOCK_K * 2), &tma_b, fb, n0 + 64 * c, k0, b0, b1);
+                        }
+                        if (++stage == C_::STAGES) { stage = 0; phase ^= 1u; }
+                        continue;
+                    }
+                    mbar_expect_tx(full_bar(stage), C_::STAGE_BYTES);
                     if (p.mode != 0) {
                         if (p.mode == 1) {
                             tma_load_4d(sa, &tma_a, full_bar(stage), 0, m0 + kb - p.tap_pad, b0, b1);
@@ -204,10 +238,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        if (lane == 0 && rank == 0) {
             // instruction descriptor: D fp32, A/B bf16, majors, N>>3, M>>4 (cute::UMMA::InstrDescriptor)
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
-                                   ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
+                                   ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
             // K-major SW128: 8-row groups 1024 B apart (SBO); LBO unused (1).  +32 B per UMMA_K inside the atom.
             // MN-major SW128: 64-element chunks along M/N are one TMA box (64 k-rows x 128 B = 8 KB) apart (LBO),
             //                 8-k-row groups 1024 B apart (SBO).  +2048 B per UMMA_K.
@@ -219,7 +253,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (long long tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            for (long long tile = worker; tile < p.num_tiles; tile += nworkers) {
                 mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
@@ -232,12 +266,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                     for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
                         const uint64_t adesc = make_smem_desc(sa + k * a_kstep, a_lbo, a_sbo);
                         const uint64_t bdesc = make_smem_desc(sb + k * b_kstep, b_lbo, b_sbo);
-                        umma_bf16(tmem_d, adesc, bdesc, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                        if constexpr (NCTA == 2) umma_bf16_2sm(tmem_d, adesc, bdesc, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                        else umma_bf16(tmem_d, adesc, bdesc, idesc, (kb > 0 || k > 0) ? 1u : 0u);
                     }
-                    umma_commit(empty_bar(stage));  // frees the smem slot once these MMAs have read it
+                    // frees the smem slot (in both CTAs of a pair) once these MMAs have read it
+                    if constexpr (NCTA == 2) umma_commit_2sm(empty_bar(stage), 3);
+                    else umma_commit(empty_bar(stage));
                     if (++stage == C_::STAGES) { stage = 0; phase ^= 1u; }
                 }
-                umma_commit(tfull_bar(acc));  // accumulator complete -> epilogue
+                // accumulator complete -> epilogue warps (of both CTAs)
+                if constexpr (NCTA == 2) umma_commit_2sm(tfull_bar(acc), 3);
+                else umma_commit(tfull_bar(acc));
                 if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
             }
         }
@@ -257,12 +296,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                             (!p.residual || (reinterpret_cast<uintptr_t>(p.residual) & 15) == 0) &&
                             (!p.aux_out || (reinterpret_cast<uintptr_t>(p.aux_out) & 15) == 0) &&
                             (!p.aux_in || (reinterpret_cast<uintptr_t>(p.aux_in) & 15) == 0);
-        for (long long tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        for (long long tile = worker; tile < p.num_tiles; tile += nworkers) {
             const int z = (int)(tile / tiles_per_batch);
             const int rem = (int)(tile % tiles_per_batch);
             const int mb = rem / p.tiles_n, nb = rem % p.tiles_n;
             const int b0 = z % p.batch0, b1 = z / p.batch0;
-            const int m = mb * BLOCK_M + quarter * 32 + lane;
+            const int m = mb * TILE_M + (int)rank * BLOCK_M + quarter * 32 + lane;
             const int n0 = nb * BN;
             const long long row_off = (long long)b0 * p.sc0 + (long long)b1 * p.sc1 + (long long)m * p.ldc;
             mbar_wait(tfull_bar(acc), acc_phase);
@@ -315,15 +354,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(tempty_bar(acc));
+            if (lane == 0) {
+                if constexpr (NCTA == 2) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0));
+                else mbar_arrive(tempty_bar(acc));
+            }
             if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
         }
     }
     tc_fence_before();
     __syncthreads();
+    if constexpr (NCTA == 2) cluster_sync_all();  // no CTA of the pair exits while its peer may still signal / read it
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, C_::TMEM_COLS);
+        if constexpr (NCTA == 2) tmem_dealloc_2sm(tmem_base, C_::TMEM_COLS);
+        else tmem_dealloc(tmem_base, C_::TMEM_COLS);
     }
 }
 
@@ -399,30 +443,52 @@ static int make_operand_map(CUtensorMap* map, const void* base, int R, int K, in
     return B200ASR_OK;
 }
 
-template <int BN, typename TC>
+template <int BN, typename TC, int NCTA = 1>
 static int launch_kernel(const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, cudaStream_t st) {
-    using C_ = Cfg<BN>;
+    using C_ = Cfg<BN, NCTA>;
     static bool attr_set = false;  // per instantiation
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C_::SMEM_BYTES);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, TC, NCTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             C_::SMEM_BYTES);
         if (e != cudaSuccess) {
             set_error("gemm(tcgen05): cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
             return B200ASR_ERR_CUDA;
         }
         attr_set = true;
     }
-    long long grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
-    gemm_tc_kernel<BN, TC><<<(int)grid, NUM_THREADS, C_::SMEM_BYTES, st>>>(ma, mb, p);
+    const long long workers = num_sms() / NCTA;
+    const long long grid = (p.num_tiles < workers ? p.num_tiles : workers) * NCTA;
+    if constexpr (NCTA == 1) {
+        gemm_tc_kernel<BN, TC, 1><<<(int)grid, NUM_THREADS, C_::SMEM_BYTES, st>>>(ma, mb, p);
+    } else {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)grid);
+        cfg.blockDim = dim3(NUM_THREADS);
+        cfg.dynamicSmemBytes = C_::SMEM_BYTES;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = NCTA;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, TC, NCTA>, ma, mb, p);
+        if (e != cudaSuccess) {
+            set_error("gemm(tcgen05, cta pair): launch failed: %s", cudaGetErrorString(e));
+            (void)cudaGetLastError();
+            return B200ASR_ERR_CUDA;
+        }
+    }
     return check_launch("gemm_tcgen05");
 }
 
-template <int BN, typename TC>
+template <int BN, typename TC, int NCTA = 1>
 static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
-    using C_ = Cfg<BN>;
     CUtensorMap ma, mb;
     int rc = make_operand_map(&ma, a.A, a.M, a.K, a.lda, a.a_kmajor, BLOCK_M, a.batch0, a.batch1, a.sa0, a.sa1);
     if (rc) return rc;
-    rc = make_operand_map(&mb, a.B, a.N, a.K, a.ldb, a.b_kmajor, BN, a.batch0, a.batch1, a.sb0, a.sb1);
+    rc = make_operand_map(&mb, a.B, a.N, a.K, a.ldb, a.b_kmajor, BN / NCTA, a.batch0, a.batch1, a.sb0, a.sb1);
     if (rc) return rc;
     Params p;
     p.C = a.C; p.bias = a.bias; p.residual = a.residual; p.aux_out = a.aux_out; p.aux_in = a.aux_in;
@@ -430,11 +496,11 @@ static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
     p.a_mn = a.a_kmajor ? 0 : 1; p.b_mn = a.b_kmajor ? 0 : 1;
     p.act = a.act; p.mul_gelu_grad = a.mul_gelu_grad; p.alpha = a.alpha;
     p.batch0 = a.batch0; p.batch1 = a.batch1; p.sc0 = a.sc0; p.sc1 = a.sc1;
-    p.tiles_m = ceil_div(a.M, BLOCK_M);
+    p.tiles_m = ceil_div(a.M, BLOCK_M * NCTA);
     p.tiles_n = ceil_div(a.N, BN);
     p.num_tiles = (long long)p.tiles_m * p.tiles_n * a.batch0 * a.batch1;
     p.mode = 0; p.tap_pad = 0; p.tblocks = 1; p.num_kb = ceil_div(a.K, BLOCK_K); p.bias_sb0 = 0;
-    return launch_kernel<BN, TC>(ma, mb, p, st);
+    return launch_kernel<BN, TC, NCTA>(ma, mb, p, st);
 }
 
 // ---------------------------------------------------------------- grouped positional conv on the same kernel
@@ -501,14 +567,52 @@ bool gemm_tc_eligible(const b200asr_gemm_args& a, const char** why) {
     return true;
 }
 
-int gemm_tc_launch(const b200asr_gemm_args& a, cudaStream_t st) {
-    // 128x256 tiles halve the shared-memory read traffic per FLOP; use them when N is wide enough to
-    // still give every SM a tile, 128x64 for narrow outputs (attention context, head_dim 64).
+static int g_force_cfg = 0;  // test hook: 0 = cost model, else (ncta * 1000 + bn)
+
+int gemm_tc_force_config(int cfg) {
+    const int old = g_force_cfg;
+    g_force_cfg = cfg;
+    return old;
+}
+
+// Tile shape / CTA-pair selection by a two-term cost model (cycles): tensor-pipe time of the busiest worker
+// (waves x 2*BN cycles per 64-deep K block) against the chip-wide L2 -> shared-memory fill time (bytes of every
+// staged operand tile / ~6.3 KB per clock, measured: profiles/r01_gemm_ncu_*.txt), plus a per-tile epilogue term.
+static void choose_config(const b200asr_gemm_args& a, int* ncta_out, int* bn_out) {
     const long long batches = (long long)a.batch0 * a.batch1;
-    int bn = 128;
-    if (a.N <= 64) bn = 64;
-    else if (a.N >= 1024 && (long long)ceil_div(a.M, 128) * ceil_div(a.N, 256) * batches >= num_sms()) bn = 256;
+    const int num_kb = ceil_div(a.K, tc::BLOCK_K);
+    const int sms = num_sms();
+    double best = 1e30;
+    int best_ncta = 1, best_bn = 128;
+    for (int ncta = 1; ncta <= 2; ++ncta) {
+        if (ncta == 2 && a.M <= 128) continue;
+        for (int bn = 64; bn <= 256; bn *= 2) {
+            if (ncta == 2 && bn == 64) continue;
+            if (bn > 64 && a.N <= bn / 2) continue;  // more than half of the tile would be padding
+            const long long tiles = (long long)ceil_div(a.M, 128 * ncta) * ceil_div(a.N, bn) * batches;
+            const long long workers = sms / ncta;
+            const long long waves = (tiles + workers - 1) / workers;
+            const double mma = (double)waves * 2.0 * bn * num_kb;
+            const double bytes = (double)tiles * ncta * (128.0 + (double)bn / ncta) * 128.0 * num_kb;
+            const double l2 = bytes / 6300.0;
+            const double epi = (double)waves * (600.0 + 8.0 * bn);
+            const double cost = (mma > l2 ? mma : l2) + epi;
+            if (cost < best) { best = cost; best_ncta = ncta; best_bn = bn; }
+        }
+    }
+    *ncta_out = best_ncta;
+    *bn_out = best_bn;
+}
+
+int gemm_tc_launch(const b200asr_gemm_args& a, cudaStream_t st) {
+    int ncta, bn;
+    choose_config(a, &ncta, &bn);
+    if (g_force_cfg) { ncta = g_force_cfg / 1000; bn = g_force_cfg % 1000; }
     const bool f32c = a.c_dtype == B200ASR_F32;
+    if (ncta == 2) {
+        if (bn == 256) return f32c ? tc::launch<256, float, 2>(a, st) : tc::launch<256, __nv_bfloat16, 2>(a, st);
+        return f32c ? tc::launch<128, float, 2>(a, st) : tc::launch<128, __nv_bfloat16, 2>(a, st);
+    }
     switch (bn) {
         case 64: return f32c ? tc::launch<64, float>(a, st) : tc::launch<64, __nv_bfloat16>(a, st);
         case 256: return f32c ? tc::launch<256, float>(a, st) : tc::launch<256, __nv_bfloat16>(a, st);

@@ -181,6 +181,24 @@ def test_gemm_tcgen05_batched_and_persistent():
     _gemm_case(1, torch.bfloat16, 128 * 40, 256 * 5, 128, True, True, "bias", seed=7)  # > 148 tiles: several per CTA
 
 
+@pytest.mark.parametrize("cfg", [2256, 2128, 1256, 1128, 1064])
+@pytest.mark.parametrize("a_k,b_k", [(True, True), (True, False), (False, False), (False, True)])
+def test_gemm_tcgen05_forced_tile_configs(cfg, a_k, b_k):
+    """Every tile configuration of the tcgen05 kernel (ncta*1000 + bn: single CTA 128 x {64,128,256}, CTA pair =
+    cluster of 2 with cta_group::2 MMA 256 x {128,256}) on every operand-major combination, ragged edges, several
+    tiles per worker, batches, and the full epilogue."""
+    from b200asr._lib import lib
+    old = lib.b200asr_gemm_force_config(cfg)
+    try:
+        _gemm_case(1, torch.bfloat16, 300, 264, 192, a_k, b_k, "all")
+        _gemm_case(1, torch.bfloat16, 3992, 1024, 320, a_k, b_k, "bias", seed=3)   # model shape: 16 pair rows, tail rows
+        _gemm_case(1, torch.bfloat16, 700, 520, 136, a_k, b_k, "gelugrad", batch=(3, 2), seed=4)
+        _gemm_case(1, torch.bfloat16, 1024, 1024, 1000, a_k, b_k, "res", c_dtype=torch.float32, seed=5)
+        _gemm_case(1, torch.bfloat16, 128 * 45, 256 * 4, 128, a_k, b_k, "none", seed=6)  # > 74 pair tiles
+    finally:
+        lib.b200asr_gemm_force_config(old)
+
+
 def test_gemm_tcgen05_overlapping_rows_conv_view():
     """Conv layers 1-6: A rows are overlapping windows of a channels-last tensor (row pitch = stride*C)."""
     g = torch.Generator().manual_seed(9)
