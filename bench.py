@@ -186,12 +186,21 @@ def run_b200(args):
     host = [synth_batch(BATCH, samples, 1234 + 100 * rank + i, frames) for i in range(4)]
     resident = [{k: v.to(dev) for k, v in hb.items()} for hb in host]
 
-    def local_step(batch):
+    def eager_step(batch):
         opt.zero_grad()
         out = model(batch["input_values"], batch["attention_mask"], labels=batch["labels"])
         out.loss.backward()
         opt.step()
         return out.loss
+
+    # the call a user makes: the whole update captured once as a CUDA graph, replayed per batch (b200asr/graph.py)
+    graphed = None
+    if not args.eager:
+        from b200asr.graph import GraphedTrainStep
+        graphed = GraphedTrainStep(model, opt, resident[0], max_label_len=120)
+
+    def local_step(batch):
+        return graphed(batch) if graphed is not None else eager_step(batch)
 
     def fedavg():
         if world > 1:
@@ -240,6 +249,8 @@ def run_b200(args):
     n0 = _lib.launch_count()
     ms_step, agg_ms, _ = timed(args.steps, e2e=False)
     launches = (_lib.launch_count() - n0) // args.steps
+    if graphed is not None:  # replays launch the captured kernels without passing through the host wrappers
+        launches = graphed.launches_per_replay
     clk = clocks.stop() if clocks else None
     ms_e2e, _, last_loss = timed(args.steps, e2e=True)
 
@@ -249,10 +260,14 @@ def run_b200(args):
     local_step(resident[0])
     host_ms = (time.perf_counter() - h0) * 1e3
     torch.cuda.synchronize()
+    h0 = time.perf_counter()
+    eager_step(resident[0])
+    host_eager_ms = (time.perf_counter() - h0) * 1e3
+    torch.cuda.synchronize()
 
     # ---- roofline leg: one extra instrumented step, every GEMM / attention call bracketed by CUDA events
     ops.PROFILE = []
-    local_step(resident[0])
+    eager_step(resident[0])
     torch.cuda.synchronize()
     prof, ops.PROFILE = ops.PROFILE, None
     kinds = {}
@@ -287,7 +302,8 @@ def run_b200(args):
                     "d2h_bytes_per_step": 4, "last_loss": last_loss},
             "gpu_launches": int(launches) * args.steps,
             "gpu_launches_per_step": int(launches),
-            "host_enqueue_ms_per_step": host_ms,
+            "host_enqueue_ms_per_step": host_ms, "host_enqueue_ms_per_step_eager": host_eager_ms,
+            "step_mode": "cuda_graph" if graphed is not None else "eager",
             "step_tflops": algo_tflop * world / (ms_step * 1e-3),
             "step_frac_of_tensor_peak": algo_tflop / (ms_step * 1e-3) / peak,
             "fedavg_round_s": ms_step * 1e-3, "fedavg_agg_ms": agg_ms if world > 1 else None,
@@ -308,6 +324,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--eager", action="store_true", help="issue every launch from Python instead of replaying the CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

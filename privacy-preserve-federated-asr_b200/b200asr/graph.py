@@ -39,9 +39,12 @@ class GraphedTrainStep:
                 self._body()
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
+        from . import _lib
         self.graph = torch.cuda.CUDAGraph()
+        n0 = _lib.launch_count()
         with torch.cuda.graph(self.graph):
             self.loss = self._body()
+        self.launches_per_replay = _lib.launch_count() - n0  # library kernels captured = launched by every replay
         for t, s in zip(opt.state_tensors(), saved):
             t.copy_(s)
         opt.step_count = step_count

@@ -99,14 +99,17 @@ class FusedAdamW:
         device tensor the captured AdamW launch reads.  Call once before every replay (outside the graph)."""
         if not hasattr(self, "hyper_dev"):
             dev = self.groups[0]["fp"].flat.device
-            self.hyper_host = torch.zeros(2, dtype=torch.float32).pin_memory()
             self.hyper_dev = torch.zeros(2, dtype=torch.float32, device=dev)
         lr = self.current_lr()
         self.step_count += 1
         t = self.step_count
-        self.hyper_host[0] = lr
-        self.hyper_host[1] = lr * (1.0 - self.betas[1] ** t) ** 0.5 / (1.0 - self.betas[0] ** t)
-        self.hyper_dev.copy_(self.hyper_host, non_blocking=True)
+        # a fresh pageable tensor per step: the copy is staged before the call returns, so the next step's values
+        # can never overtake this one in the stream
+        # (same arithmetic as b200asr_adamw_step: lr rounded to fp32 first, bias correction in double -> bit-identical
+        # to the eager path)
+        lr32 = float(torch.tensor(lr, dtype=torch.float32))
+        b1, b2 = float(torch.tensor(self.betas[0], dtype=torch.float32)), float(torch.tensor(self.betas[1], dtype=torch.float32))
+        self.hyper_dev.copy_(torch.tensor([lr32, lr32 * (1.0 - b2 ** t) ** 0.5 / (1.0 - b1 ** t)], dtype=torch.float32))
 
     def step_captured(self):
         """Device side of the update, with no host-dependent scalar: what a CUDA graph captures."""

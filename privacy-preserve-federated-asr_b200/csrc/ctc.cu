@@ -1,8 +1,13 @@
-// CTC loss: fp32 log-softmax + log-space alpha/beta recursions + gradient w.r.t. the logits, and greedy decode.
-// One CTA per (head, utterance).  The log-probabilities of the utterance live in shared memory (T*V*4 bytes);
+// CTC loss: fp32 softmax + alpha/beta recursions + gradient w.r.t. the logits, and greedy decode.
+// One CTA per (head, utterance).  The frame posteriors of the utterance live in shared memory (T*V*4 bytes);
 // warp 0 runs the alpha recursion while warp 1 runs beta concurrently (one warp per recursion: each lane owns
-// SPL consecutive lattice states, the two neighbour states come from the previous lane by shuffle); then all
-// warps combine alpha+beta into the gradient.  Latency-bound (T sequential steps), not bandwidth-bound.
+// SPL consecutive lattice states, the two neighbour states come from the previous lane by shuffle).
+// The recursions run in the linear domain in BLOCK FLOATING POINT: every lane keeps fp32 mantissas for its states
+// plus one integer exponent (true value = mantissa * 2^E), renormalised every frame by exact power-of-two
+// scalings -- a step is a handful of FADD/FMUL and integer ops, no exp/log on the T-step critical path and no
+// warp-wide reduction, yet the dynamic range is unbounded (a single per-frame scale underflows fp32 on wide lattices:
+// the frontier states of a 241-state lattice sit hundreds of binades below the bulk).  Logs are taken once, in
+// parallel, when all warps combine alpha*beta into the gradient.  Latency-bound (T sequential steps).
 #include "common.cuh"
 
 namespace b200asr {
@@ -10,23 +15,17 @@ namespace b200asr {
 namespace {
 constexpr int CTC_THREADS = 256;
 constexpr float NEG_INF = -INFINITY;
+constexpr int E_EMPTY = -(1 << 28);  // exponent of a lane whose states are all zero
 
-__device__ __forceinline__ float lse2(float a, float b) {
-    const float m = fmaxf(a, b);
-    if (m == NEG_INF) return NEG_INF;
-    return m + logf(expf(a - m) + expf(b - m));
-}
-__device__ __forceinline__ float lse3(float a, float b, float c) {
-    const float m = fmaxf(fmaxf(a, b), c);
-    if (m == NEG_INF) return NEG_INF;
-    return m + logf(expf(a - m) + expf(b - m) + expf(c - m));
-}
+// 2^d for d <= 127 (0 below the normal range)
+__device__ __forceinline__ float pow2i(int d) { return d < -126 ? 0.f : __int_as_float((d + 127) << 23); }
 
 // forward (DIR=+1) or backward (DIR=-1) lattice recursion by one warp.
 // state s of lane: s = lane*SPL + i.  ext[s] = blank (s even) or target[(s-1)/2] (s odd).
+// out[t][s] = mantissa, eout[t][lane] = exponent of that lane at frame t.
 template <int SPL, int DIR>
-__device__ void lattice_pass(const float* __restrict__ lp, int V, const int* __restrict__ tgt, int L, int Tb, int blank,
-                             float* __restrict__ out /* [T][Sld] */, int Sld) {
+__device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __restrict__ tgt, int L, int Tb, int blank,
+                             float* __restrict__ out /* [T][Sld] */, int Sld, int* __restrict__ eout /* [T][32] */) {
     const int lane = threadIdx.x & 31;
     const int S = 2 * L + 1;
     int lab[SPL];
@@ -44,60 +43,101 @@ __device__ void lattice_pass(const float* __restrict__ lp, int V, const int* __r
         }
     }
     float a[SPL];
+    int E = E_EMPTY;
     const int t0 = DIR > 0 ? 0 : Tb - 1;
-#pragma unroll
-    for (int i = 0; i < SPL; ++i) {
-        const int s = lane * SPL + i;
-        bool init;
-        if (DIR > 0) init = (s == 0) || (s == 1 && S > 1);
-        else init = (s == S - 1) || (s == S - 2 && S > 1);
-        a[i] = (init && s < S) ? lp[t0 * V + lab[i]] : NEG_INF;
-        if (s < S) out[(long long)t0 * Sld + s] = a[i];
-    }
-    for (int step = 1; step < Tb; ++step) {
-        const int t = DIR > 0 ? step : Tb - 1 - step;
-        float n1, n2;  // neighbour lane's two boundary states
-        if (DIR > 0) {
-            n1 = __shfl_up_sync(0xffffffffu, a[SPL - 1], 1);
-            n2 = __shfl_up_sync(0xffffffffu, a[SPL - 2], 1);
-            if (lane == 0) n1 = n2 = NEG_INF;
-        } else {
-            n1 = __shfl_down_sync(0xffffffffu, a[0], 1);
-            n2 = __shfl_down_sync(0xffffffffu, a[1], 1);
-            if (lane == 31) n1 = n2 = NEG_INF;
-        }
-        float nxt[SPL];
+    {
+        float m = 0.f;
 #pragma unroll
         for (int i = 0; i < SPL; ++i) {
-            float p1, p2;
-            if (DIR > 0) {
-                p1 = (i >= 1) ? a[i - 1] : n1;
-                p2 = (i >= 2) ? a[i - 2] : (i == 1 ? n1 : n2);
-                if (i == 0) { p1 = n1; p2 = n2; }
-            } else {
-                p1 = (i + 1 < SPL) ? a[i + 1] : n1;
-                p2 = (i + 2 < SPL) ? a[i + 2] : (i + 2 == SPL ? n1 : n2);
-            }
-            const float v = skip[i] ? lse3(a[i], p1, p2) : lse2(a[i], p1);
-            nxt[i] = v + lp[t * V + lab[i]];
+            const int s = lane * SPL + i;
+            bool init;
+            if (DIR > 0) init = (s == 0) || (s == 1 && S > 1);
+            else init = (s == S - 1) || (s == S - 2 && S > 1);
+            a[i] = (init && s < S) ? pr[t0 * V + lab[i]] : 0.f;
+            m = fmaxf(m, a[i]);
+        }
+        if (m > 0.f) {
+            const int k = ((__float_as_int(m) >> 23) & 0xff) - 127;
+            const float sc = pow2i(-k);
+#pragma unroll
+            for (int i = 0; i < SPL; ++i) a[i] *= sc;
+            E = k;
         }
 #pragma unroll
         for (int i = 0; i < SPL; ++i) {
             const int s = lane * SPL + i;
-            a[i] = (s < S) ? nxt[i] : NEG_INF;
+            if (s < S) out[(long long)t0 * Sld + s] = a[i];
+        }
+        eout[t0 * 32 + lane] = E;
+    }
+    for (int step = 1; step < Tb; ++step) {
+        const int t = DIR > 0 ? step : Tb - 1 - step;
+        float e[SPL];  // emission probabilities of this frame: independent of the recursion, issued first
+#pragma unroll
+        for (int i = 0; i < SPL; ++i) e[i] = pr[t * V + lab[i]];
+        float n1, n2;  // neighbour lane's two boundary states and its exponent
+        int En;
+        if (DIR > 0) {
+            n1 = __shfl_up_sync(0xffffffffu, a[SPL - 1], 1);
+            n2 = __shfl_up_sync(0xffffffffu, a[SPL - 2], 1);
+            En = __shfl_up_sync(0xffffffffu, E, 1);
+            if (lane == 0) { n1 = n2 = 0.f; En = E_EMPTY; }
+        } else {
+            n1 = __shfl_down_sync(0xffffffffu, a[0], 1);
+            n2 = __shfl_down_sync(0xffffffffu, a[1], 1);
+            En = __shfl_down_sync(0xffffffffu, E, 1);
+            if (lane == 31) { n1 = n2 = 0.f; En = E_EMPTY; }
+        }
+        const int Ec = max(E, En);  // common exponent of this step's operands
+        const float fo = pow2i(E - Ec), fn = pow2i(En - Ec);  // E_EMPTY - Ec underflows to 0 (the values are 0 anyway)
+        n1 *= fn;
+        n2 *= fn;
+        float as[SPL];
+#pragma unroll
+        for (int i = 0; i < SPL; ++i) as[i] = a[i] * fo;
+        float m = 0.f;
+#pragma unroll
+        for (int i = 0; i < SPL; ++i) {
+            float p1, p2;
+            if (DIR > 0) {
+                p1 = (i >= 1) ? as[i - 1] : n1;
+                p2 = (i >= 2) ? as[i - 2] : (i == 1 ? n1 : n2);
+                if (i == 0) { p1 = n1; p2 = n2; }
+            } else {
+                p1 = (i + 1 < SPL) ? as[i + 1] : n1;
+                p2 = (i + 2 < SPL) ? as[i + 2] : (i + 2 == SPL ? n1 : n2);
+            }
+            const int s = lane * SPL + i;
+            const float v = (as[i] + p1 + (skip[i] ? p2 : 0.f)) * e[i];
+            a[i] = (s < S) ? v : 0.f;
+            m = fmaxf(m, a[i]);
+        }
+        if (m > 0.f) {
+            const int k = ((__float_as_int(m) >> 23) & 0xff) - 127;
+            const float sc = pow2i(-k);
+#pragma unroll
+            for (int i = 0; i < SPL; ++i) a[i] *= sc;
+            E = Ec + k;
+        } else {
+            E = E_EMPTY;
+        }
+#pragma unroll
+        for (int i = 0; i < SPL; ++i) {
+            const int s = lane * SPL + i;
             if (s < S) out[(long long)t * Sld + s] = a[i];
         }
+        eout[t * 32 + lane] = E;
     }
 }
 
 template <int DIR>
-__device__ void lattice_dispatch(int spl, const float* lp, int V, const int* tgt, int L, int Tb, int blank, float* out,
-                                 int Sld) {
+__device__ void lattice_dispatch(int spl, const float* pr, int V, const int* tgt, int L, int Tb, int blank, float* out,
+                                 int Sld, int* eout) {
     switch (spl) {
-        case 2: lattice_pass<2, DIR>(lp, V, tgt, L, Tb, blank, out, Sld); break;
-        case 4: lattice_pass<4, DIR>(lp, V, tgt, L, Tb, blank, out, Sld); break;
-        case 8: lattice_pass<8, DIR>(lp, V, tgt, L, Tb, blank, out, Sld); break;
-        default: lattice_pass<16, DIR>(lp, V, tgt, L, Tb, blank, out, Sld); break;
+        case 2: lattice_pass<2, DIR>(pr, V, tgt, L, Tb, blank, out, Sld, eout); break;
+        case 4: lattice_pass<4, DIR>(pr, V, tgt, L, Tb, blank, out, Sld, eout); break;
+        case 8: lattice_pass<8, DIR>(pr, V, tgt, L, Tb, blank, out, Sld, eout); break;
+        default: lattice_pass<16, DIR>(pr, V, tgt, L, Tb, blank, out, Sld, eout); break;
     }
 }
 }  // namespace
@@ -116,16 +156,20 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     const int L = min(tgt_len[b], max_tgt);
     const int S = 2 * L + 1;
     const int Tb = max(0, min(in_len[b], T_));
-    float* lp = sm;                          // [T][V]
-    int* tgt_s = (int*)(lp + (size_t)T_ * V);  // [max_tgt]
-    float* acc_s = (float*)(tgt_s + max_tgt + 1);  // [nwarps][V]
+    float* pr = sm;                                  // [T][V] softmax probabilities
+    int* tgt_s = (int*)(pr + (size_t)T_ * V);        // [max_tgt + 1]
+    // [nwarps][V] occupancy sums in 2^-40 fixed point: integer atomics commute, so the gradient is reproducible
+    unsigned long long* acc_s = (unsigned long long*)(((uintptr_t)(tgt_s + max_tgt + 1) + 7) & ~(uintptr_t)7);
     const long long hb = (long long)head * B + b;
     const T* x = logits + hb * T_ * V;
-    float* alpha = ws + hb * 2 * T_ * Sld;
+    // workspace per (head, utterance): alpha, beta mantissas [T][Sld] fp32, then their lane exponents [T][32] int32
+    float* alpha = ws + hb * (2LL * T_ * Sld + 2LL * T_ * 32);
     float* beta = alpha + (long long)T_ * Sld;
+    int* ea = reinterpret_cast<int*>(beta + (long long)T_ * Sld);
+    int* eb = ea + (long long)T_ * 32;
 
     for (int i = threadIdx.x; i < L; i += blockDim.x) tgt_s[i] = targets[tgt_off[b] + i];
-    // ---- phase 1: fp32 log-softmax of the valid frames
+    // ---- phase 1: fp32 softmax of the valid frames
     for (int t = warp; t < Tb; t += nwarps) {
         float mx = NEG_INF;
         for (int v = lane; v < V; v += 32) mx = fmaxf(mx, to_f<T>(x[(long long)t * V + v]));
@@ -134,22 +178,28 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
         for (int v = lane; v < V; v += 32) sum += expf(to_f<T>(x[(long long)t * V + v]) - mx);
         sum = warp_sum(sum);
         const float lz = mx + logf(sum);
-        for (int v = lane; v < V; v += 32) lp[t * V + v] = to_f<T>(x[(long long)t * V + v]) - lz;
+        for (int v = lane; v < V; v += 32) pr[t * V + v] = expf(to_f<T>(x[(long long)t * V + v]) - lz);
     }
     __syncthreads();
     // ---- phase 2: alpha (warp 0) and beta (warp 1) concurrently
     if (Tb > 0) {
-        if (warp == 0) lattice_dispatch<+1>(spl, lp, V, tgt_s, L, Tb, blank, alpha, Sld);
-        else if (warp == 1) lattice_dispatch<-1>(spl, lp, V, tgt_s, L, Tb, blank, beta, Sld);
+        if (warp == 0) lattice_dispatch<+1>(spl, pr, V, tgt_s, L, Tb, blank, alpha, Sld, ea);
+        else if (warp == 1) lattice_dispatch<-1>(spl, pr, V, tgt_s, L, Tb, blank, beta, Sld, eb);
     }
     __threadfence_block();
     __syncthreads();
     // ---- phase 3: loss and gradient
+    constexpr float LN2 = 0.6931471805599453f, LOG2E = 1.4426950408889634f;
     float nll = INFINITY;
     if (Tb > 0) {
-        const float aT = alpha[(long long)(Tb - 1) * Sld + S - 1];
-        const float aT2 = S > 1 ? alpha[(long long)(Tb - 1) * Sld + S - 2] : NEG_INF;
-        nll = -lse2(aT, aT2);
+        const long long r = (long long)(Tb - 1);
+        const float a1 = alpha[r * Sld + S - 1];
+        const int e1 = ea[r * 32 + (S - 1) / spl];
+        const float a2 = S > 1 ? alpha[r * Sld + S - 2] : 0.f;
+        const int e2 = S > 1 ? ea[r * 32 + (S - 2) / spl] : E_EMPTY;
+        const int em = max(e1, e2);
+        const float tot = a1 * pow2i(e1 - em) + a2 * pow2i(e2 - em);
+        if (tot > 0.f) nll = -(logf(tot) + (float)em * LN2);
     }
     if (Tb == 0 && L == 0) nll = 0.f;  // empty input, empty target (torch convention)
     const bool infeasible = !(nll < INFINITY);
@@ -157,7 +207,7 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     if (!grad) return;
     const float gs = grad_scale ? grad_scale[hb] : 1.f;
     T* g = grad + hb * T_ * V;
-    float* acc = acc_s + warp * V;
+    unsigned long long* acc = acc_s + warp * V;
     for (int t = warp; t < T_; t += nwarps) {
         if (t >= Tb || infeasible) {
             // torch: gradient of padded frames is 0; zero_infinity zeroes infeasible utterances (NaN otherwise)
@@ -167,25 +217,34 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
         }
         const float* ar = alpha + (long long)t * Sld;
         const float* br = beta + (long long)t * Sld;
+        const int* ear = ea + (long long)t * 32;
+        const int* ebr = eb + (long long)t * 32;
+        // log2 of alpha_t(s) * beta_t(s): mantissa product + the two lane exponents (the only logs of the kernel)
         float mx = NEG_INF;
-        for (int s = lane; s < S; s += 32) mx = fmaxf(mx, ar[s] + br[s]);
+        for (int s = lane; s < S; s += 32) {
+            const float ab = ar[s] * br[s];
+            if (ab > 0.f) mx = fmaxf(mx, log2f(ab) + (float)(ear[s / spl] + ebr[s / spl]));
+        }
         mx = warp_max(mx);
-        for (int v = lane; v < V; v += 32) acc[v] = 0.f;
+        for (int v = lane; v < V; v += 32) acc[v] = 0ull;
         __syncwarp();
         for (int s = lane; s < S; s += 32) {
-            const float ab = ar[s] + br[s];
-            if (ab > NEG_INF) {
+            const float ab = ar[s] * br[s];
+            if (ab > 0.f) {
                 const int l = (s & 1) ? tgt_s[(s - 1) >> 1] : blank;
-                atomicAdd(&acc[l], expf(ab - mx));
+                const float rel2 = log2f(ab) + (float)(ear[s / spl] + ebr[s / spl]) - mx;  // <= 0
+                atomicAdd(&acc[l], (unsigned long long)(exp2f(rel2) * 1099511627776.0f));  // in [0, 2^40]
             }
         }
         __syncwarp();
+        // d nll / d logit = softmax - sum_{s: lab = v} alpha_t(s) beta_t(s) / (P p_t(v)),  P = exp(-nll)
+        // (ATen ctc_loss backward form)
+        const float fac = exp2f(mx + nll * LOG2E) * (1.0f / 1099511627776.0f);
         for (int v = lane; v < V; v += 32) {
-            const float l = lp[t * V + v];
-            const float a = acc[v];
-            // d nll / d logit = softmax - exp(log(sum alpha*beta) + nll - lp)      (ATen ctc_loss backward form)
-            const float occ = a > 0.f ? expf(mx + logf(a) + nll - l) : 0.f;
-            g[(long long)t * V + v] = from_f<T>((expf(l) - occ) * gs);
+            const float pv = pr[t * V + v];
+            const float a = (float)acc[v];
+            const float occ = a > 0.f ? a * fac / fmaxf(pv, 1e-37f) : 0.f;
+            g[(long long)t * V + v] = from_f<T>((pv - occ) * gs);
         }
         __syncwarp();
     }
@@ -235,7 +294,7 @@ using namespace b200asr;
 extern "C" {
 
 size_t b200asr_ctc_workspace_bytes(int n_heads, int B, int T, int max_tgt_len) {
-    return (size_t)n_heads * B * 2 * T * (2 * max_tgt_len + 1) * sizeof(float);
+    return (size_t)n_heads * B * (2 * (size_t)T * (2 * max_tgt_len + 1) + 2 * (size_t)T * 32) * sizeof(float);
 }
 
 int b200asr_ctc_fwd_bwd(const void* logits, const int* targets, const int* tgt_off, const int* tgt_len,
@@ -254,7 +313,8 @@ int b200asr_ctc_fwd_bwd(const void* logits, const int* targets, const int* tgt_o
         set_error("ctc: target length %d exceeds the supported 255", max_tgt_len);
         return B200ASR_ERR_UNSUPPORTED;
     }
-    const size_t smem = ((size_t)T_ * V + (max_tgt_len + 1) + (CTC_THREADS / 32) * V) * sizeof(float);
+    const size_t smem = ((size_t)T_ * V + (max_tgt_len + 1)) * sizeof(float) + 8 +
+                        (size_t)(CTC_THREADS / 32) * V * sizeof(unsigned long long);
     if (smem > 227 * 1024) {
         set_error("ctc: T*V=%d*%d log-probabilities do not fit in shared memory", T_, V);
         return B200ASR_ERR_UNSUPPORTED;

@@ -143,8 +143,15 @@ __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, const
     }
 }
 
+// Deterministic: every block parks its partial sum, the last block to finish adds them in block order (no
+// floating-point atomics, so the clipping coefficient -- and with it the whole update -- is reproducible bit for bit).
+constexpr int SUMSQ_MAX_BLOCKS = 1024;
+__device__ float g_sumsq_partial[SUMSQ_MAX_BLOCKS];
+__device__ unsigned int g_sumsq_arrived = 0;
+
 __global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ x, long long n, float* __restrict__ out) {
     __shared__ float red[32];
+    __shared__ bool is_last;
     float s = 0.f;
     const long long nvec = n / 4;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
@@ -154,7 +161,22 @@ __global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ x,
     for (long long i = nvec * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
         s += x[i] * x[i];
     s = block_sum(s, red);
-    if (threadIdx.x == 0) atomicAdd(out, s);
+    if (threadIdx.x == 0) {
+        g_sumsq_partial[blockIdx.x] = s;
+        __threadfence();
+        is_last = (atomicAdd(&g_sumsq_arrived, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        float t = 0.f;
+        for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) t += __ldcg(&g_sumsq_partial[i]);
+        t = block_sum(t, red);
+        if (threadIdx.x == 0) {
+            out[0] += t;
+            g_sumsq_arrived = 0;
+        }
+    }
 }
 
 static int stream_grid(long long n) {

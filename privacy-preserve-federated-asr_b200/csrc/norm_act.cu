@@ -205,19 +205,26 @@ __global__ void __launch_bounds__(256, 2) ln_bwd_kernel(const T* __restrict__ dy
         }
     }
     if (partial) {
+        // warps add their register accumulators into the block's shared sums one warp at a time: a fixed order, so
+        // the affine / bias gradients are bit-reproducible run to run (no floating-point atomics)
+        const int wib = threadIdx.x >> 5, nwb = blockDim.x >> 5;
+        for (int turn = 0; turn < nwb; ++turn) {
+            if (wib == turn) {
 #pragma unroll
-        for (int i = 0; i < NV; ++i) {
-            const int vi = lane + 32 * i;
-            if (vi < nvec) {
+                for (int i = 0; i < NV; ++i) {
+                    const int vi = lane + 32 * i;
+                    if (vi < nvec) {
 #pragma unroll
-                for (int j = 0; j < N; ++j) {
-                    atomicAdd(&sacc[vi * N + j], aw[i][j]);
-                    atomicAdd(&sacc[cols + vi * N + j], ab[i][j]);
-                    if (CS) atomicAdd(&sacc[2 * cols + vi * N + j], ac[i][j]);
+                        for (int j = 0; j < N; ++j) {
+                            sacc[vi * N + j] += aw[i][j];
+                            sacc[cols + vi * N + j] += ab[i][j];
+                            if (CS) sacc[2 * cols + vi * N + j] += ac[i][j];
+                        }
+                    }
                 }
             }
+            __syncthreads();
         }
-        __syncthreads();
         float* out = partial + (long long)blockIdx.x * 3 * cols;
         for (int i = threadIdx.x; i < 3 * cols; i += blockDim.x) out[i] = sacc[i];
     }

@@ -194,3 +194,50 @@ def test_training_loop_flat_grads_shadows_vs_oracle(dtype):
         params = dict(model.named_parameters())
         for n in trainable:
             assert relinf(params[n].detach(), ref[n]) < 2e-3, n
+
+
+def test_graphed_train_step_matches_eager():
+    """The CUDA-graph replay of the whole update (graph.GraphedTrainStep) follows the eager path step for step,
+    and building the graph leaves model / optimizer state untouched."""
+    from b200asr.graph import GraphedTrainStep
+    from b200asr.optim import FusedAdamW
+    cfg = R.ArchConfig.tiny()
+    sd = R.init_state_dict(cfg, seed=11, dacs=False)
+    batches = [R.synth_batch(cfg, 2, 6000, seed=70 + i, ragged=True, max_label=12) for i in range(4)]
+    dev = lambda b: {k: v.to(DEV) for k, v in b.items() if k in ("input_values", "attention_mask", "labels")}
+
+    def make():
+        m = M.Data2VecAudioForCTC(ns(cfg), compute_dtype=torch.bfloat16)
+        m.load_state_dict(sd)
+        m.freeze_feature_encoder()
+        m.to(DEV).train()
+        m.validate_labels = False
+        return m, FusedAdamW(m.named_parameters(), lr=1e-3, weight_decay=0.01, warmup_steps=2)
+
+    def run_eager():
+        m, o = make()
+        losses = []
+        for b in batches:
+            o.zero_grad()
+            out = m(**dev(b))
+            out.loss.backward()
+            o.step()
+            losses.append(float(out.loss))
+        return m, losses
+
+    m1, eager = run_eager()
+    m1b, eager2 = run_eager()
+    assert eager == eager2  # no floating-point atomics anywhere on the path: the update is reproducible bit for bit
+    for (n, p1), (_, p2) in zip(m1.named_parameters(), m1b.named_parameters()):
+        assert torch.equal(p1, p2), n
+    m2, o2 = make()
+    before = [t.clone() for t in o2.state_tensors()]
+    step = GraphedTrainStep(m2, o2, dev(batches[0]), max_label_len=16)
+    for t, b in zip(o2.state_tensors(), before):
+        assert torch.equal(t, b)
+    assert o2.step_count == 0
+    graphed = [float(step(dev(b))) for b in batches]
+    for a, b in zip(eager, graphed):
+        assert abs(a - b) <= 1e-4 * abs(a), (eager, graphed)
+    for (n, p1), (_, p2) in zip(m1.named_parameters(), m2.named_parameters()):
+        assert relinf(p2.detach(), p1.detach()) < 1e-4, n

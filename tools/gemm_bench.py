@@ -75,6 +75,9 @@ def conv(Tin, k, B=8, C=512):
     return mk, 2.0 * B * Tout * C * k * C
 
 
+SWEEP = "--sweep" in sys.argv
+from b200asr._lib import lib  # noqa: E402
+
 tot = 0.0
 for name, mk, fl, mult in [
     ("fwd  QKV   N=3072 K=1024 +bias", fwd(3072, 1024), 2.0 * M * 3072 * 1024, 24),
@@ -92,6 +95,11 @@ for name, mk, fl, mult in [
 ]:
     us = bench(name, mk, fl)
     tot += us * mult
+    if SWEEP:
+        for cfg in (1128, 1256, 2128, 2256):
+            lib.b200asr_gemm_force_config(cfg)
+            bench(f"    forced {cfg}", mk, fl)
+        lib.b200asr_gemm_force_config(0)
 print(f"encoder linears per step (24 layers): {tot / 1e3:.2f} ms; at measured sustained peak: "
       f"{24 * 12 * 2.0 * M * 1024 * 1024 * 1.0 / 1e12:.2f}.. see DESIGN")
 ctot = 0.0
