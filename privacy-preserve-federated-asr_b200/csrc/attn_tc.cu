@@ -268,7 +268,7 @@ constexpr int B_THREADS = 320;  // TMA warp, MMA warp, 8 element-wise warps
 constexpr int B_KV_BYTES = 2 * BK * DH * 2;   // K_j + V_j: 32 KB
 constexpr int B_QD_BYTES = 2 * BQ * DH * 2;   // Q_i + dO_i: 16 KB
 constexpr int B_PT_BYTES = BK * BQ * 2;       // one P^T (or dS^T) operand tile: 16 KB
-constexpr int B_SMEM = B_KV_BYTES + B_STAGES * B_QD_BYTES + 4 * B_PT_BYTES + 1024 /*lse, D*/ + 1024 + 256;
+constexpr int B_SMEM_FIXED = B_KV_BYTES + B_STAGES * B_QD_BYTES + 4 * B_PT_BYTES + 1024 + 256;  // + 2 * Tpad floats (lse, D)
 constexpr int B_TMEM_COLS = 512;  // S^T[2], dP^T[2] (4 x 64) + dV (64) + dK (64)
 
 struct BwdParams {
@@ -292,8 +292,7 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
     const uint32_t sQD = base + B_KV_BYTES;
     const uint32_t sPT = sQD + B_STAGES * B_QD_BYTES;   // PT[0], PT[1], DST[0], DST[1]
     uint8_t* genPT = gen + B_KV_BYTES + B_STAGES * B_QD_BYTES;
-    float* lseD = reinterpret_cast<float*>(genPT + 4 * B_PT_BYTES);  // [2][128]: lse*log2e (64) then D (64)
-    const uint32_t bars = sPT + 4 * B_PT_BYTES + 1024;
+    const uint32_t bars = sPT + 4 * B_PT_BYTES;
     const uint32_t kv_full = bars;
     auto qd_full = [&](int s) { return bars + 8u * (1 + s); };
     auto qd_empty = [&](int s) { return bars + 8u * (1 + B_STAGES + s); };
@@ -304,7 +303,12 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
     const uint32_t dkv_done = bars + 8u * (9 + 2 * B_STAGES);
     const uint32_t tmem_slot = bars + 8u * (10 + 2 * B_STAGES);
     volatile uint32_t* tmem_slot_gen =
-        reinterpret_cast<volatile uint32_t*>(genPT + 4 * B_PT_BYTES + 1024 + 8 * (10 + 2 * B_STAGES));
+        reinterpret_cast<volatile uint32_t*>(genPT + 4 * B_PT_BYTES + 8 * (10 + 2 * B_STAGES));
+    // whole-row softmax statistics of this (utterance, head), staged once: lse * log2(e) then D, Tpad floats each
+    // (Tpad = T rounded up to the 64-query block; the padding holds +inf / 0 so that out-of-range queries give P = 0)
+    const int Tpad = ((p.T + BQ - 1) / BQ) * BQ;
+    float* lse2_s = reinterpret_cast<float*>(genPT + 4 * B_PT_BYTES + 256);
+    float* dsum_s = lse2_s + Tpad;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int k0 = blockIdx.x * BK, h = blockIdx.y, b = blockIdx.z;
@@ -357,6 +361,11 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_gen;
+    for (int q = threadIdx.x; q < Tpad; q += blockDim.x) {
+        lse2_s[q] = (q < T) ? p.lse[bh * T + q] * LOG2E : INFINITY;
+        dsum_s[q] = (q < T) ? p.dsum[bh * T + q] : 0.f;
+    }
+    __syncthreads();
     // TMEM columns: S^T[s] at 64 s, dP^T[s] at 128 + 64 s, dV at 256, dK at 320
     const uint32_t tm_dv = tmem_base + 256, tm_dk = tmem_base + 320;
 
@@ -427,14 +436,6 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
         __nv_bfloat16* dst_row = p.dst + (bh * T + key) * ldq;
         for (int i = 0; i < nqb; ++i) {
             const int slot = i & 1;
-            if (et < 128) {
-                const int q = i * BQ + (et & 63);
-                float v;
-                if (et < 64) v = (q < T) ? p.lse[bh * T + q] * LOG2E : INFINITY;
-                else v = (q < T) ? p.dsum[bh * T + q] : 0.f;
-                lseD[slot * 128 + et] = v;
-            }
-            named_bar_sync(1, 256);
             mbar_wait(sdp_full(slot), (i >> 1) & 1);
             tc_fence_after();
             uint32_t s[32], dp[32];
@@ -445,17 +446,24 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
             __syncwarp();
             if (lane == 0) mbar_arrive(sdp_free(slot));
             uint32_t pp[16], dd[16];
-            const float* l2 = lseD + slot * 128 + half * 32;
-            const float* dq = l2 + 64;
+            const float4* l2v = reinterpret_cast<const float4*>(lse2_s + i * BQ + half * 32);  // broadcast 16-byte reads
+            const float4* dqv = reinterpret_cast<const float4*>(dsum_s + i * BQ + half * 32);
 #pragma unroll
-            for (int c = 0; c < 32; c += 2) {
-                float p0 = fast_exp2(fmaf(__uint_as_float(s[c]), c2, -l2[c]));
-                float p1 = fast_exp2(fmaf(__uint_as_float(s[c + 1]), c2, -l2[c + 1]));
-                if (!key_valid) p0 = p1 = 0.f;
-                const float d0 = p0 * (__uint_as_float(dp[c]) - dq[c]) * sc;
-                const float d1 = p1 * (__uint_as_float(dp[c + 1]) - dq[c + 1]) * sc;
+            for (int c = 0; c < 32; c += 4) {
+                const float4 l4 = l2v[c >> 2], d4 = dqv[c >> 2];
+                float p0 = fast_exp2(fmaf(__uint_as_float(s[c]), c2, -l4.x));
+                float p1 = fast_exp2(fmaf(__uint_as_float(s[c + 1]), c2, -l4.y));
+                float p2 = fast_exp2(fmaf(__uint_as_float(s[c + 2]), c2, -l4.z));
+                float p3 = fast_exp2(fmaf(__uint_as_float(s[c + 3]), c2, -l4.w));
+                if (!key_valid) p0 = p1 = p2 = p3 = 0.f;
+                const float d0 = p0 * (__uint_as_float(dp[c]) - d4.x) * sc;
+                const float d1 = p1 * (__uint_as_float(dp[c + 1]) - d4.y) * sc;
+                const float d2 = p2 * (__uint_as_float(dp[c + 2]) - d4.z) * sc;
+                const float d3 = p3 * (__uint_as_float(dp[c + 3]) - d4.w) * sc;
                 pp[c >> 1] = bf2_pack(p0, p1);
+                pp[(c >> 1) + 1] = bf2_pack(p2, p3);
                 dd[c >> 1] = bf2_pack(d0, d1);
+                dd[(c >> 1) + 1] = bf2_pack(d2, d3);
             }
             if (i >= 2) mbar_wait(pds_free(slot), ((i >> 1) - 1) & 1);
             uint8_t* gpt = genPT + slot * B_PT_BYTES;
@@ -620,7 +628,7 @@ int mha_bwd_tc_launch(const void* qkv, const void* out, const void* dout, const 
     if (rc) return rc;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(mha_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
+        cudaError_t e = cudaFuncSetAttribute(mha_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) {
             set_error("mha_bwd(tcgen05): cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
             return B200ASR_ERR_CUDA;
@@ -631,7 +639,13 @@ int mha_bwd_tc_launch(const void* qkv, const void* out, const void* dout, const 
     p.lse = lse; p.dsum = dsum; p.klen = klen; p.dqkv = (__nv_bfloat16*)dqkv; p.dst = dst;
     p.B = B; p.T = T; p.H = H; p.ldq = ldq; p.scale = scale; p.scale_log2 = scale * LOG2E;
     dim3 grid(ceil_div(T, BK), H, B);
-    mha_bwd_tc_kernel<<<grid, B_THREADS, B_SMEM, st>>>(mk, mv, mq, mdo, p);
+    const int Tpad = ceil_div(T, BQ) * BQ;
+    const size_t smem = (size_t)B_SMEM_FIXED + 2 * (size_t)Tpad * sizeof(float);
+    if (smem > 227 * 1024) {
+        set_error("mha_bwd(tcgen05): T=%d too long for the staged softmax statistics", T);
+        return B200ASR_ERR_UNSUPPORTED;
+    }
+    mha_bwd_tc_kernel<<<grid, B_THREADS, smem, st>>>(mk, mv, mq, mdo, p);
     rc = check_launch("mha_bwd_tcgen05");
     if (rc) return rc;
     // dQ[q, n] = sum_key dS^T[key, q] K[key, n]   (dS already carries the softmax scale)

@@ -98,6 +98,17 @@ __device__ __forceinline__ float gelu_grad_fast(float x) {
     return fmaf(x * 0.39894228040143267794f, e, 0.5f * (1.0f + er));
 }
 
+// storage-type dispatch: bf16 outputs take the MUFU-based approximation (error far below bf16 rounding), fp32
+// (parity mode) keeps the libm erff / expf forms
+template <typename T> __device__ __forceinline__ float gelu_for(float x) {
+    if constexpr (sizeof(T) == 2) return gelu_fast(x);
+    else return gelu_erf(x);
+}
+template <typename T> __device__ __forceinline__ float gelu_grad_for(float x) {
+    if constexpr (sizeof(T) == 2) return gelu_grad_fast(x);
+    else return gelu_erf_grad(x);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

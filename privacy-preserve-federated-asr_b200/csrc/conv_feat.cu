@@ -66,8 +66,8 @@ __global__ void __launch_bounds__(256) conv0_ln_gelu_kernel(const float* __restr
 #pragma unroll
         for (int i = 0; i < NP; ++i) {
             const int c = 2 * lane + 64 * i;
-            const float o0 = gelu_erf((acc[i][0] - mean) * rstd * lnw_s[c] + lnb_s[c]);
-            const float o1 = gelu_erf((acc[i][1] - mean) * rstd * lnw_s[c + 1] + lnb_s[c + 1]);
+            const float o0 = gelu_for<T>((acc[i][0] - mean) * rstd * lnw_s[c] + lnb_s[c]);
+            const float o1 = gelu_for<T>((acc[i][1] - mean) * rstd * lnw_s[c + 1] + lnb_s[c + 1]);
             if constexpr (sizeof(T) == 2) {
                 *reinterpret_cast<uint32_t*>(yp + c) = bf2_pack(o0, o1);
             } else {

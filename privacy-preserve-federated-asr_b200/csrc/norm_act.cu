@@ -4,7 +4,13 @@
 
 namespace b200asr {
 
-constexpr int LN_BWD_BLOCKS = 296;   // 2 x 148 SMs; fixed so that the workspace size is device independent
+constexpr int LN_BWD_BLOCKS = 148;  // one 512-thread block per SM; fixed so that the workspace size is device independent
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// (was 296)   // 2 x 148 SMs; fixed so that the workspace size is device independent
 constexpr int COLSUM_CHUNKS = 64;
 
 // per-lane helpers: N consecutive fp32 affine parameters starting at column c (c is a multiple of N >= 4)
@@ -91,7 +97,7 @@ __global__ void __launch_bounds__(128) ln_fwd_kernel(const T* __restrict__ x, co
                 for (int j = 0; j < N; ++j) {
                     float t = (v[i][j] - mean) * rstd;
                     if (w) t = fmaf(t, wv[j], bv[j]);
-                    if (act == B200ASR_ACT_GELU) t = gelu_erf(t);
+                    if (act == B200ASR_ACT_GELU) t = gelu_for<T>(t);
                     o[j] = t;
                 }
                 Vec16<T> ov;
@@ -102,125 +108,119 @@ __global__ void __launch_bounds__(128) ln_fwd_kernel(const T* __restrict__ x, co
     }
 }
 
-// LayerNorm backward.  One warp per row; the row is read twice (HBM, then L1) so that only the three column
-// accumulators stay in registers: dw += dz*xhat, db += dz, and (CS) the column sums of dx (= the bias gradient of
-// the nn.Linear that produced the LayerNorm input).  Per-block partials -> reduce_partials_kernel (deterministic).
-template <typename T, int NV, bool CS>
-__global__ void __launch_bounds__(256, 2) ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ s,
+// LayerNorm backward.  A GROUP of GS threads owns one row at a time (one 16-byte vector per thread, so the three
+// column accumulators -- dw += dz*xhat, db += dz and (CS) the column sums of dx, i.e. the bias gradient of the
+// nn.Linear that produced the LayerNorm input -- cost 3 x N registers); a block runs G groups on different rows and the
+// next row of a group is prefetched while the current one is reduced.  The row statistics cross the warps of a group
+// through shared memory + a named barrier.  Groups add their accumulators into the block's shared sums in a fixed
+// order, blocks write partials, reduce_partials_kernel finishes: deterministic, no floating-point atomics.
+template <typename T, bool CS>
+__global__ void __launch_bounds__(512, 1) ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ s,
                                                         const float* __restrict__ w, const float* __restrict__ b,
                                                         const float* __restrict__ mean_in,
                                                         const float* __restrict__ rstd_in,
                                                         const T* __restrict__ dres_add, T* __restrict__ dx,
-                                                        float* __restrict__ partial, int rows, int cols, int act) {
+                                                        float* __restrict__ partial, int rows, int cols, int act, int GS,
+                                                        int G) {
     constexpr int N = Vec16<T>::N;
-    extern __shared__ float sacc[];  // [3][cols] when partial != nullptr
-    const int lane = threadIdx.x & 31;
-    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int nwarps = (gridDim.x * blockDim.x) >> 5;
-    const int nvec = cols / N;
+    extern __shared__ float sm[];
+    float* sacc = sm;                 // [3][cols] block sums (when partial != nullptr)
+    float* xch = sm + 3 * cols;       // [2][G][16][2] per-warp row statistics, double buffered by row parity
+    const int g = threadIdx.x / GS, tg = threadIdx.x - g * GS;
+    const int lane = threadIdx.x & 31, wg = tg >> 5, nwg = GS >> 5;
+    const int c0 = tg * N;
+    const bool active = c0 < cols;
     const float inv_cols = 1.0f / (float)cols;
     if (partial) {
         for (int i = threadIdx.x; i < 3 * cols; i += blockDim.x) sacc[i] = 0.f;
-        __syncthreads();
     }
-    float aw[NV][N], ab[NV][N], ac[CS ? NV : 1][N];
+    float aw[N], ab[N], ac[N], wv[N], bv[N];
 #pragma unroll
-    for (int i = 0; i < NV; ++i)
-#pragma unroll
-        for (int j = 0; j < N; ++j) {
-            aw[i][j] = ab[i][j] = 0.f;
-            if (CS) ac[i][j] = 0.f;
+    for (int j = 0; j < N; ++j) { aw[j] = ab[j] = ac[j] = 0.f; wv[j] = 1.f; bv[j] = 0.f; }
+    if (w && active) {
+        load_params<N>(w, c0, wv);
+        load_params<N>(b, c0, bv);
+    }
+    const int ngroups = gridDim.x * G;
+    int row = blockIdx.x * G + g;
+    Vec16<T> a_nxt, g_nxt;
+    a_nxt.raw = make_uint4(0, 0, 0, 0);
+    g_nxt.raw = make_uint4(0, 0, 0, 0);
+    if (row < rows && active) {
+        a_nxt.load(s + (long long)row * cols + c0);
+        g_nxt.load(dy + (long long)row * cols + c0);
+    }
+    int parity = 0;
+    for (; row < rows; row += ngroups, parity ^= 1) {
+        const long long base = (long long)row * cols + c0;
+        Vec16<T> a = a_nxt, gg = g_nxt;
+        const int nrow = row + ngroups;
+        if (nrow < rows && active) {
+            a_nxt.load(s + (long long)nrow * cols + c0);
+            g_nxt.load(dy + (long long)nrow * cols + c0);
         }
-
-    for (int row = warp; row < rows; row += nwarps) {
-        const long long base = (long long)row * cols;
         const float mean = mean_in[row], rstd = rstd_in[row];
+        float xh[N], dz[N];
+        a.unpack(xh);
+        gg.unpack(dz);
         float s1 = 0.f, s2 = 0.f;
+        if (active) {
 #pragma unroll
-        for (int i = 0; i < NV; ++i) {
-            const int vi = lane + 32 * i;
-            if (vi < nvec) {
-                Vec16<T> a, g;
-                float xh[N], dz[N], wv[N], bv[N];
-                a.load(s + base + (long long)vi * N);
-                g.load(dy + base + (long long)vi * N);
-                a.unpack(xh);
-                g.unpack(dz);
-                if (w) load_params<N>(w, vi * N, wv);
-                if (w && act == B200ASR_ACT_GELU) load_params<N>(b, vi * N, bv);
-#pragma unroll
-                for (int j = 0; j < N; ++j) {
-                    const float h = (xh[j] - mean) * rstd;
-                    const float wj = w ? wv[j] : 1.f;
-                    float d = dz[j];
-                    if (act == B200ASR_ACT_GELU) d *= gelu_erf_grad(w ? fmaf(h, wj, bv[j]) : h);
-                    aw[i][j] = fmaf(d, h, aw[i][j]);
-                    ab[i][j] += d;
-                    d *= wj;
-                    s1 += d;
-                    s2 = fmaf(d, h, s2);
-                }
+            for (int j = 0; j < N; ++j) {
+                const float h = (xh[j] - mean) * rstd;
+                float d = dz[j];
+                if (act == B200ASR_ACT_GELU) d *= gelu_grad_for<T>(w ? fmaf(h, wv[j], bv[j]) : h);
+                aw[j] = fmaf(d, h, aw[j]);
+                ab[j] += d;
+                d *= wv[j];
+                xh[j] = h;
+                dz[j] = d;
+                s1 += d;
+                s2 = fmaf(d, h, s2);
             }
         }
-        s1 = warp_sum(s1) * inv_cols;
-        s2 = warp_sum(s2) * inv_cols;
+        s1 = warp_sum(s1);
+        s2 = warp_sum(s2);
+        if (nwg > 1) {
+            float* x2 = xch + ((parity * G + g) * 16) * 2;
+            if (lane == 0) { x2[2 * wg] = s1; x2[2 * wg + 1] = s2; }
+            named_bar_sync(1 + g, GS);
+            s1 = 0.f; s2 = 0.f;
+            for (int i = 0; i < nwg; ++i) { s1 += x2[2 * i]; s2 += x2[2 * i + 1]; }
+        }
+        s1 *= inv_cols;
+        s2 *= inv_cols;
+        if (active) {
+            float o[N];
 #pragma unroll
-        for (int i = 0; i < NV; ++i) {
-            const int vi = lane + 32 * i;
-            if (vi < nvec) {
-                Vec16<T> a, g;
-                float xh[N], dz[N], wv[N], bv[N], o[N];
-                a.load(s + base + (long long)vi * N);   // L1 hit: this warp read the row a moment ago
-                g.load(dy + base + (long long)vi * N);
-                a.unpack(xh);
-                g.unpack(dz);
-                if (w) load_params<N>(w, vi * N, wv);
-                if (w && act == B200ASR_ACT_GELU) load_params<N>(b, vi * N, bv);
+            for (int j = 0; j < N; ++j) o[j] = rstd * (dz[j] - s1 - xh[j] * s2);
+            if (dres_add) {
+                Vec16<T> r;
+                float rf[N];
+                r.load(dres_add + base);
+                r.unpack(rf);
 #pragma unroll
-                for (int j = 0; j < N; ++j) {
-                    const float h = (xh[j] - mean) * rstd;
-                    const float wj = w ? wv[j] : 1.f;
-                    float d = dz[j];
-                    if (act == B200ASR_ACT_GELU) d *= gelu_erf_grad(w ? fmaf(h, wj, bv[j]) : h);
-                    d *= wj;
-                    o[j] = rstd * (d - s1 - h * s2);
-                }
-                if (dres_add) {
-                    Vec16<T> r;
-                    float rf[N];
-                    r.load(dres_add + base + (long long)vi * N);
-                    r.unpack(rf);
+                for (int j = 0; j < N; ++j) o[j] += rf[j];
+            }
+            Vec16<T> ov;
+            ov.pack(o);
+            ov.store(dx + base);
+            if (CS) {
+                ov.unpack(o);  // sum what was stored (the rounded values the consumer GEMMs read)
 #pragma unroll
-                    for (int j = 0; j < N; ++j) o[j] += rf[j];
-                }
-                Vec16<T> ov;
-                ov.pack(o);
-                ov.store(dx + base + (long long)vi * N);
-                if (CS) {
-                    ov.unpack(o);  // sum what was stored (the rounded values the consumer GEMMs read)
-#pragma unroll
-                    for (int j = 0; j < N; ++j) ac[i][j] += o[j];
-                }
+                for (int j = 0; j < N; ++j) ac[j] += o[j];
             }
         }
     }
     if (partial) {
-        // warps add their register accumulators into the block's shared sums one warp at a time: a fixed order, so
-        // the affine / bias gradients are bit-reproducible run to run (no floating-point atomics)
-        const int wib = threadIdx.x >> 5, nwb = blockDim.x >> 5;
-        for (int turn = 0; turn < nwb; ++turn) {
-            if (wib == turn) {
+        __syncthreads();
+        for (int turn = 0; turn < G; ++turn) {
+            if (g == turn && active) {
 #pragma unroll
-                for (int i = 0; i < NV; ++i) {
-                    const int vi = lane + 32 * i;
-                    if (vi < nvec) {
-#pragma unroll
-                        for (int j = 0; j < N; ++j) {
-                            sacc[vi * N + j] += aw[i][j];
-                            sacc[cols + vi * N + j] += ab[i][j];
-                            if (CS) sacc[2 * cols + vi * N + j] += ac[i][j];
-                        }
-                    }
+                for (int j = 0; j < N; ++j) {
+                    sacc[c0 + j] += aw[j];
+                    sacc[cols + c0 + j] += ab[j];
+                    if (CS) sacc[2 * cols + c0 + j] += ac[j];
                 }
             }
             __syncthreads();
@@ -359,27 +359,20 @@ static int launch_ln_bwd(const void* dy, const void* s, const float* w, const fl
                          const float* rstd, const void* dres, void* dx, float* partial, bool colsum, int rows, int cols,
                          int act, cudaStream_t st) {
     constexpr int N = Vec16<T>::N;
-    const int nvec = cols / N;
-    const int nv = ceil_div(nvec, 32);
-    int grid = ceil_div(rows, 8);
+    const int GS = ceil_div(ceil_div(cols, N), 32) * 32;  // threads per row
+    if (GS > 512) { set_error("layernorm_bwd: cols=%d too large", cols); return B200ASR_ERR_UNSUPPORTED; }
+    int G = 512 / GS;
+    if (G > 8) G = 8;
+    int grid = ceil_div(rows, G);
     if (grid > LN_BWD_BLOCKS) grid = LN_BWD_BLOCKS;
     if (partial) grid = LN_BWD_BLOCKS;  // finalize sums exactly LN_BWD_BLOCKS partials
-    const size_t smem = partial ? (size_t)3 * cols * sizeof(float) : 0;
-#define LN_BWD_CASE(NVV)                                                                                          \
-    do {                                                                                                          \
-        if (colsum)                                                                                               \
-            ln_bwd_kernel<T, NVV, true><<<grid, 256, smem, st>>>((const T*)dy, (const T*)s, w, b, mean, rstd,      \
-                                                                 (const T*)dres, (T*)dx, partial, rows, cols, act); \
-        else                                                                                                      \
-            ln_bwd_kernel<T, NVV, false><<<grid, 256, smem, st>>>((const T*)dy, (const T*)s, w, b, mean, rstd,     \
-                                                                  (const T*)dres, (T*)dx, partial, rows, cols, act); \
-    } while (0)
-    if (nv <= 1) LN_BWD_CASE(1);
-    else if (nv <= 2) LN_BWD_CASE(2);
-    else if (nv <= 4) LN_BWD_CASE(4);
-    else if (nv <= 8) LN_BWD_CASE(8);
-    else { set_error("layernorm_bwd: cols=%d too large", cols); return B200ASR_ERR_UNSUPPORTED; }
-#undef LN_BWD_CASE
+    const size_t smem = ((size_t)3 * cols + 2 * 8 * 16 * 2) * sizeof(float);
+    if (colsum)
+        ln_bwd_kernel<T, true><<<grid, G * GS, smem, st>>>((const T*)dy, (const T*)s, w, b, mean, rstd, (const T*)dres, (T*)dx,
+                                                           partial, rows, cols, act, GS, G);
+    else
+        ln_bwd_kernel<T, false><<<grid, G * GS, smem, st>>>((const T*)dy, (const T*)s, w, b, mean, rstd, (const T*)dres, (T*)dx,
+                                                            partial, rows, cols, act, GS, G);
     return check_launch("layernorm_bwd");
 }
 
@@ -418,7 +411,7 @@ int b200asr_layernorm_bwd(const void* dy, const void* s, const float* w, const f
     if (dw || db || dx_colsum) {
         B200_REQUIRE(workspace && workspace_bytes >= b200asr_layernorm_bwd_workspace_bytes(cols),
                      "layernorm_bwd: workspace too small");
-        B200_REQUIRE((size_t)3 * cols * sizeof(float) <= 48 * 1024, "layernorm_bwd: cols=%d too large", cols);
+        B200_REQUIRE((size_t)3 * cols * sizeof(float) <= 40 * 1024, "layernorm_bwd: cols=%d too large", cols);
         partial = (float*)workspace;
     }
     int rc;

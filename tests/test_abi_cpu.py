@@ -29,7 +29,7 @@ def test_library_exports_every_declared_symbol():
     assert not missing, missing
     assert sorted(_lib.SIGNATURES) == syms  # the ctypes table binds exactly the header's API
     assert _lib.lib.b200asr_abi_version() == 2
-    assert _lib.lib.b200asr_layernorm_bwd_workspace_bytes(1024) == 296 * 3 * 1024 * 4
+    assert _lib.lib.b200asr_layernorm_bwd_workspace_bytes(1024) == 148 * 3 * 1024 * 4
 
 
 def test_library_is_sm100a_tcgen05_tma():

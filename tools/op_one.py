@@ -1,0 +1,21 @@
+#!/usr/bin/env python
+"""A few launches of the non-GEMM kernels at configs[1] sizes, for `ncu --set full -k regex:...` captures."""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "privacy-preserve-federated-asr_b200"))
+import torch
+from b200asr import ops
+M, D, B, T, H = 3992, 1024, 8, 499, 16
+bf = torch.bfloat16
+r = lambda *s, sc=1.0: (torch.randn(*s, device="cuda") * sc).to(bf)
+qkv, do = r(M, 3 * D), r(M, D, sc=0.1)
+x, dy = r(M, D), r(M, D)
+w, b = torch.ones(D, device="cuda"), torch.zeros(D, device="cuda")
+dw, db, dxs = (torch.empty(D, device="cuda") for _ in range(3))
+for _ in range(4):
+    out, lse = ops.mha_fwd(qkv, None, B, T, H, 64, 0.125)
+    ops.mha_bwd(qkv, out, do, lse, None, B, T, H, 64, 0.125)
+    y, _, mean, rstd = ops.layernorm_fwd(x, w, b, 1e-5)
+    ops.layernorm_bwd(dy, x, w, b, mean, rstd, dw_out=dw, db_out=db, dxsum_out=dxs)
+torch.cuda.synchronize()
+print("ok")
