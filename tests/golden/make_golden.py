@@ -80,6 +80,65 @@ def case_plain_ctc(tag, cfg, batch, samples, seed, use_mask):
     print(tag, "loss", float(out.loss), "logits", tuple(out.logits.shape))
 
 
+def case_variant_ctc(tag, cfg, batch, samples, seed, use_mask):
+    """Config-5 variants (centralized/finetune_ASRs.py:154-172): HF Wav2Vec2ForCTC / HubertForCTC, eager attention.
+    The oracle state_dict uses the transformers-4.17 weight_norm key names (weight_g / weight_v, the reference's
+    pinned version); the installed transformers registers them as parametrizations.weight.original0/1."""
+    import transformers as tf
+    Config, Model = {"wav2vec2": (tf.Wav2Vec2Config, tf.Wav2Vec2ForCTC), "hubert": (tf.HubertConfig, tf.HubertForCTC)}[cfg.model_type]
+    sd = R.init_state_dict(cfg, seed=seed, dacs=False)
+    m = Model(Config(**cfg.to_hf_kwargs()))
+    hf_sd = {}
+    for k, v in sd.items():
+        k = k.replace("conv.weight_g", "conv.parametrizations.weight.original0")
+        k = k.replace("conv.weight_v", "conv.parametrizations.weight.original1")
+        hf_sd[k] = v
+    missing, unexpected = m.load_state_dict(hf_sd, strict=False)
+    assert not unexpected, unexpected
+    assert all("masked_spec_embed" in k for k in missing), missing
+    m.freeze_feature_encoder()
+    m.train()
+    b = R.synth_batch(cfg, batch, samples, seed=1234 + seed, ragged=use_mask, max_label=12)
+    out = m(input_values=b["input_values"], attention_mask=b["attention_mask"] if use_mask else None,
+            labels=b["labels"], output_hidden_states=True)
+    out.loss.backward()
+    px = cfg.prefix
+    back = lambda n: n.replace("conv.parametrizations.weight.original0", "conv.weight_g").replace(
+        "conv.parametrizations.weight.original1", "conv.weight_v")
+    keep = ["lm_head.weight", "lm_head.bias",
+            px + "encoder.layers.0.attention.q_proj.weight", px + "encoder.layers.0.attention.out_proj.bias",
+            px + "encoder.layers.0.layer_norm.weight", px + "encoder.layers.1.feed_forward.output_dense.bias",
+            px + "encoder.layers.1.final_layer_norm.bias", px + "encoder.layer_norm.weight",
+            px + "encoder.pos_conv_embed.conv.weight_g", px + "encoder.pos_conv_embed.conv.weight_v",
+            px + "encoder.pos_conv_embed.conv.bias", px + "feature_projection.projection.weight"]
+    g = {back(n): p.grad.detach().clone() for n, p in m.named_parameters() if p.grad is not None and back(n) in keep}
+    gnorm = {back(n): float(p.grad.norm()) for n, p in m.named_parameters() if p.grad is not None}
+    np.savez_compressed(
+        os.path.join(OUT, f"{tag}.npz"),
+        seed=seed, batch=batch, samples=samples, use_mask=int(use_mask),
+        loss=out.loss.detach().numpy(), logits=out.logits.detach().numpy(), argmax=out.logits.argmax(-1).numpy(),
+        hidden_last=out.hidden_states[-1].detach().numpy(), hidden_first=out.hidden_states[0].detach().numpy(),
+        grad_names=np.array(list(g.keys())), **{"grad:" + k: v.numpy() for k, v in g.items()},
+        gnorm_names=np.array(list(gnorm.keys())), gnorm_values=np.array(list(gnorm.values())),
+    )
+    print(tag, "loss", float(out.loss), "logits", tuple(out.logits.shape), "grads", len(gnorm))
+
+
+VARIANTS = {
+    # tag: (config factory kwargs, batch, samples, seed, use_mask)
+    "w2v2_group_postln": ("tiny_wav2vec2", {}, 3, 8000, 30, True),           # wav2vec2-base-960h family
+    "w2v2_layer_stable": ("tiny_wav2vec2", dict(feat_extract_norm="layer", conv_bias=True, do_stable_layer_norm=True), 2, 6000, 31, True),  # wav2vec2-large-960h-lv60
+    "hubert_stable": ("tiny_hubert", {}, 3, 8000, 32, True),                # hubert-large / xlarge-ls960-ft family
+    "hubert_base_nomask": ("tiny_hubert", dict(feat_extract_norm="group", conv_bias=False, do_stable_layer_norm=False,
+                                               feat_proj_layer_norm=False), 2, 6000, 33, False),  # hubert-base-ls960
+}
+
+
+def variant_cfg(tag):
+    fac, kw, *_ = VARIANTS[tag]
+    return getattr(R.ArchConfig, fac)(**kw)
+
+
 class _ReplayExponential:
     """Patch Tensor.exponential_ to replay queued Exp(1) samples (models.py:112)."""
 
@@ -164,7 +223,13 @@ def main():
     case_dacs("dacs_stage2_toggle", cfg, batch=2, samples=6000, seed=20, stage=2, toggle_ratio=0.3)
     case_dacs("dacs_stage2_f1", cfg, batch=2, samples=6000, seed=21, stage=2, ad_loss="f1")
     case_fedavg("fedavg")
+    for tag, (_, _, batch, samples, seed, use_mask) in VARIANTS.items():
+        case_variant_ctc(tag, variant_cfg(tag), batch, samples, seed, use_mask)
 
 
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "variants":  # only (re)generate the config-5 variant fixtures
+        for tag, (_, _, batch, samples, seed, use_mask) in VARIANTS.items():
+            case_variant_ctc(tag, variant_cfg(tag), batch, samples, seed, use_mask)
+    else:
+        main()
