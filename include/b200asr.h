@@ -186,6 +186,33 @@ int b200asr_posconv_bwd(const void* x, const void* w_bwd, const void* dy, void* 
                         size_t workspace_bytes, int B, int T, int C, int groups, int k, int dtype, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Wav2Vec2 / Hubert members of the family (centralized/finetune_ASRs.py:154-172, BASELINE configs[4]).
+ *
+ * conv layer 0 with GroupNorm(num_groups = C, affine) + GELU: replaces nn.Conv1d + nn.GroupNorm + gelu of
+ * transformers wav2vec2/modeling_wav2vec2.py Wav2Vec2GroupNormConvLayer (feat_extract_norm = "group").  The
+ * statistics are per (utterance, channel) over ALL Tout frames (padded frames included, as torch does).
+ *   x [B, L] fp32; w fp32 [C, k]; bias fp32 [C] or NULL; gn_w, gn_b fp32 [C]; y [B, Tout, C] (dtype) channels-last
+ *   workspace >= b200asr_conv0_gn_gelu_workspace_bytes(...)
+ */
+size_t b200asr_conv0_gn_gelu_workspace_bytes(int B, int L, int C, int k, int stride);
+int b200asr_conv0_gn_gelu_fwd(const float* x, const float* w, const float* bias, const float* gn_w, const float* gn_b,
+                              void* y, void* workspace, size_t workspace_bytes, int B, int L, int C, int k, int stride,
+                              float eps, int dtype, void* stream);
+/* torch.nn.utils.weight_norm(conv, name="weight", dim=2) of the positional conv filter
+ * (wav2vec2/modeling_wav2vec2.py Wav2Vec2PositionalConvEmbedding.__init__): v fp32 [rows, k] (rows = C * C/groups,
+ * tap fastest), g fp32 [k];  w[r][j] = g[j] * v[r][j] / norm[j],  norm[j] = ||v[:, j]||_2  (written to `norm`, fp32 [k]).
+ * Backward: dv fp32 [rows, k], dg fp32 [k] from dw fp32 [rows, k].  workspace >= b200asr_weight_norm_workspace_bytes(k). */
+size_t b200asr_weight_norm_workspace_bytes(int k);
+int b200asr_weight_norm_fwd(const float* v, const float* g, float* w, float* norm, void* workspace, size_t workspace_bytes,
+                            int rows, int k, void* stream);
+int b200asr_weight_norm_bwd(const float* dw, const float* v, const float* g, const float* norm, float* dv, float* dg,
+                            void* workspace, size_t workspace_bytes, int rows, int k, void* stream);
+/* y = res + gelu(c) (res may be NULL) -- the activation after the weight-normed positional conv fused with
+ * `hidden_states + position_embeddings` (Wav2Vec2Encoder.forward); backward dc = dy * gelu'(c).  n % (16/sizeof) == 0. */
+int b200asr_gelu_add_fwd(const void* c, const void* res, void* y, long long n, int dtype, void* stream);
+int b200asr_gelu_bwd(const void* dy, const void* c, void* dc, long long n, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * CTC: log_softmax(fp32) + alpha/beta recursions + gradient w.r.t. the logits, one launch for `n_heads`
  * logit tensors sharing targets.  Replaces nn.functional.log_softmax + nn.functional.ctc_loss at
  * federated/src/models.py:498-533, centralized/trainer_data2vec_2st.py:384-408, HF:897-908.

@@ -100,6 +100,15 @@ class ShadowCache:
     def posconv(self, w, groups):
         return self._get(("posconv", id(w)), (w,), lambda: ops.posconv_pack(self.weight(w), groups))
 
+    def posconv_wn(self, g, v, groups):
+        """weight_norm(dim=2) filter of the wav2vec2 / hubert positional conv: (w_fwd, w_bwd, norm[k]) rebuilt when
+        weight_g / weight_v change (once per optimizer step)."""
+        def make():
+            w, norm = ops.weight_norm_fwd(v.detach(), g.detach())
+            wf, wb = ops.posconv_pack(self._cast(w), groups)
+            return wf, wb, norm
+        return self._get(("posconv_wn", id(v)), (g, v), make)
+
 
 # ----------------------------------------------------------------------------- gradient sinks
 def grad_sink(ps):
@@ -191,15 +200,17 @@ def _ln_bwd(dy, s, w, b, mean, rstd, need, in_bias=None, **kw):
 # ----------------------------------------------------------------------------- frozen feature extractor
 def feature_extractor_fwd(x: torch.Tensor, conv_w: List[torch.Tensor], conv_b: List[Optional[torch.Tensor]],
                           ln_w: List[torch.Tensor], ln_b: List[torch.Tensor], kernels, strides, eps: float,
-                          cache: ShadowCache) -> torch.Tensor:
+                          cache: ShadowCache, norm: str = "layer") -> torch.Tensor:
     """HF:51-75,131-157 with the stack frozen (finetune_ASRs.py:200, models.py:302): forward only.
     x [B, L] fp32 -> [B, T, C] channels-last.  Layer 0 is the fused direct kernel, layers 1.. are GEMMs whose
     A operand is the overlapping-window view of the channels-last activations (row pitch = stride*C, row length
     k*C), followed by the fused LayerNorm+GELU pass."""
     cd = cache.dtype
+    group = norm == "group"  # wav2vec2-base / hubert-base: GroupNorm after conv 0, plain conv + GELU afterwards
     with torch.no_grad():
-        h = ops.conv0_ln_gelu(x.float(), conv_w[0].detach(), None if conv_b[0] is None else conv_b[0].detach(),
-                              ln_w[0].detach(), ln_b[0].detach(), strides[0], eps, cd)
+        conv0 = ops.conv0_gn_gelu if group else ops.conv0_ln_gelu
+        h = conv0(x.float(), conv_w[0].detach(), None if conv_b[0] is None else conv_b[0].detach(),
+                  ln_w[0].detach(), ln_b[0].detach(), strides[0], eps, cd)
         for i in range(1, len(conv_w)):
             B, Tin, Cin = h.shape
             k, s = kernels[i], strides[i]
@@ -208,9 +219,12 @@ def feature_extractor_fwd(x: torch.Tensor, conv_w: List[torch.Tensor], conv_b: L
             wf = cache.conv_flat(conv_w[i])
             y = torch.empty(B, Tout, Cout, dtype=cd, device=h.device)
             ops.gemm_raw(h, wf, y, Tout, Cout, k * Cin, s * Cin, k * Cin, Cout, True, True,
-                         bias=None if conv_b[i] is None else conv_b[i].detach(),
+                         bias=None if conv_b[i] is None else conv_b[i].detach(), act=ACT_GELU if group else ACT_NONE,
                          batch0=1, batch1=B, sa=(0, Tin * Cin), sb=(0, 0), sc=(0, Tout * Cout))
-            h, _, _, _ = ops.layernorm_fwd(y, ln_w[i].detach(), ln_b[i].detach(), eps, act=ACT_GELU, want_stats=False)
+            if group:
+                h = y  # GELU rode in the GEMM epilogue; no norm on layers 1..6
+            else:
+                h, _, _, _ = ops.layernorm_fwd(y, ln_w[i].detach(), ln_b[i].detach(), eps, act=ACT_GELU, want_stats=False)
     return h
 
 
@@ -222,7 +236,10 @@ class FeatureProjectionFn(torch.autograd.Function):
     def forward(ctx, feats, ln_w, ln_b, w, b, eps, cache: ShadowCache, klen=None):
         M = feats.numel() // feats.shape[-1]
         x2 = feats.reshape(M, feats.shape[-1])
-        n, _, mean, rstd = ops.layernorm_fwd(x2, ln_w, ln_b, eps)
+        if ln_w is None:  # HubertFeatureProjection with feat_proj_layer_norm=False
+            n, mean, rstd = x2, None, None
+        else:
+            n, _, mean, rstd = ops.layernorm_fwd(x2, ln_w, ln_b, eps)
         wsh = cache.weight(w)
         y, _ = ops.linear_fwd(n, wsh, b)
         ctx.save_for_backward(x2, n, mean, rstd, wsh, klen)
@@ -246,7 +263,7 @@ class FeatureProjectionFn(torch.autograd.Function):
         db = _bgrad(b, need[4], dy2)
         dw = _wgrad(w, need[3], dy2, n)
         dlw = dlb = None
-        if need[1] or need[2]:
+        if ln_w is not None and (need[1] or need[2]):
             dn = ops.linear_dgrad(dy2, wsh)
             _, dlw, dlb, _ = _ln_bwd(dn, x2, ln_w, ln_b, mean, rstd, True)
         return None, dlw, dlb, dw, db, None, None, None
@@ -369,6 +386,156 @@ class EncoderLayerFn(torch.autograd.Function):
                 dqw, dkw, dvw = dwqkv[:d], dwqkv[d:2 * d], dwqkv[2 * d:]
             if dbqkv is not None:
                 dqb, dkb, dvb = dbqkv[:d], dbqkv[d:2 * d], dbqkv[2 * d:]
+        return (dx, None, None, None, dqw, dqb, dkw, dkb, dvw, dvb, dwo, dbo, dln1w, dln1b, dw1, db1, dw2, db2,
+                dln2w, dln2b)
+
+
+def _deliver(p, grad):
+    """Hand a finished fp32 gradient to p's flat-gradient sink (copy when fresh, add otherwise); returns what autograd
+    should receive (None when delivered)."""
+    sink, fresh = grad_sink((p,))
+    if sink is None:
+        return grad
+    if fresh:
+        sink.copy_(grad.reshape(-1))
+    else:
+        ops.axpy_(sink, grad.reshape(-1).contiguous())
+    return None
+
+
+class PosConvWeightNormFn(torch.autograd.Function):
+    """Wav2Vec2PositionalConvEmbedding / HubertPositionalConvEmbedding + the encoder's residual add (and LayerNorm for
+    the post-LN encoder): s = h + gelu(conv_{g * v / ||v||}(h)),  out = LN(s) or s (do_stable_layer_norm).
+    transformers wav2vec2/modeling_wav2vec2.py: PositionalConvEmbedding, Wav2Vec2Encoder.forward,
+    Wav2Vec2EncoderStableLayerNorm.forward."""
+
+    @staticmethod
+    def forward(ctx, h, ln_w, ln_b, eps, groups, ksize, cache: ShadowCache, g, v, bias):
+        B, T, d = h.shape
+        wf, wb, norm = cache.posconv_wn(g, v, groups)
+        c = ops.posconv_fwd(h, wf, bias, groups, ksize)
+        s = ops.gelu_add(c, h)
+        mean = rstd = None
+        out = s
+        if ln_w is not None:
+            out, _, mean, rstd = ops.layernorm_fwd(s.view(B * T, d), ln_w, ln_b, eps)
+        ctx.save_for_backward(h, c, s if ln_w is not None else None, mean, rstd, wb, norm)
+        ctx.params = (ln_w, ln_b, g, v, bias)
+        ctx.cfg = (groups, ksize, (B, T, d))
+        return out.view(B, T, d)
+
+    @staticmethod
+    def backward(ctx, dout):
+        h, c, s, mean, rstd, wb, norm = ctx.saved_tensors
+        ln_w, ln_b, g, v, bias = ctx.params
+        groups, k, (B, T, d) = ctx.cfg
+        need = ctx.needs_input_grad
+        dout2 = dout.reshape(B * T, d)
+        if not dout2.is_contiguous():
+            dout2 = dout2.contiguous()
+        dlw = dlb = None
+        ds = dout2
+        if ln_w is not None:
+            ds, dlw, dlb, _ = _ln_bwd(dout2, s.view(B * T, d), ln_w, ln_b, mean, rstd, need[1] or need[2])
+        dc = ops.gelu_bwd(ds, c.view(B * T, d))
+        dbias = _bgrad(bias, need[9], dc)
+        want_dw = need[7] or need[8]
+        dx, dW = ops.posconv_bwd(h, wb, dc.view(B, T, d), groups, k, want_dx=need[0], want_dw=want_dw)
+        dg = dv = None
+        if want_dw:
+            dv, dg = ops.weight_norm_bwd(dW, v.detach(), g.detach(), norm)
+            dv, dg = _deliver(v, dv), _deliver(g, dg)
+        dh = None
+        if need[0]:
+            dh = ops.axpy_(dx.view(B * T, d), ds).view(B, T, d)
+        return (dh, dlw, dlb, None, None, None, None, dg, dv, dbias)
+
+
+class LayerNormFn(torch.autograd.Function):
+    """A stand-alone affine LayerNorm over the last dim (the final encoder.layer_norm of the pre-LN encoder)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, eps):
+        x2 = x.reshape(-1, x.shape[-1])
+        y, _, mean, rstd = ops.layernorm_fwd(x2, w, b, eps)
+        ctx.save_for_backward(x2, mean, rstd)
+        ctx.params = (w, b)
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, mean, rstd = ctx.saved_tensors
+        w, b = ctx.params
+        need = ctx.needs_input_grad
+        dy2 = dy.reshape(x2.shape)
+        dx, dw, db, _ = _ln_bwd(dy2, x2, w, b, mean, rstd, need[1] or need[2])
+        return dx.view(dy.shape), dw, db, None
+
+
+class EncoderLayerStableFn(torch.autograd.Function):
+    """Pre-LN block (wav2vec2/modeling_wav2vec2.py Wav2Vec2EncoderLayerStableLayerNorm; wav2vec2-large-lv60,
+    hubert-large/xlarge), dropout = 0:
+         s1 = x + O(attn(LN1(x)));   y = s1 + W2 gelu(W1 LN2(s1)).
+    Same kernels as the post-LN block; the residual adds ride in the O / W2 GEMM epilogues and in the LayerNorm
+    backward (`dres_add`).  params order as EncoderLayerFn (ln1 = layer_norm, ln2 = final_layer_norm)."""
+
+    @staticmethod
+    def forward(ctx, x, klen, meta, cache: ShadowCache, *P):
+        (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = P
+        B, T, H, eps = meta
+        M, d = x.shape
+        dh = d // H
+        scale = dh ** -0.5
+        wqkv = cache.qkv(q_w, k_w, v_w)
+        bqkv = cache.qkv_bias(q_b, k_b, v_b)
+        wo, w1s, w2s = cache.weight(o_w), cache.weight(w1), cache.weight(w2)
+        n1, _, m1, r1 = ops.layernorm_fwd(x, ln1_w, ln1_b, eps)
+        qkv, _ = ops.linear_fwd(n1, wqkv, bqkv)
+        attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale)
+        s1, _ = ops.linear_fwd(attn, wo, o_b, residual=x)
+        n2, _, m2, r2 = ops.layernorm_fwd(s1, ln2_w, ln2_b, eps)
+        g, u = ops.linear_fwd(n2, w1s, b1, act=ACT_GELU, want_preact=True)
+        y, _ = ops.linear_fwd(g, w2s, b2, residual=s1)
+        ctx.save_for_backward(x, m1, r1, n1, qkv, attn, lse, s1, m2, r2, n2, u, g, wqkv, wo, w1s, w2s)
+        ctx.params = P
+        ctx.klen = klen
+        ctx.meta = (B, T, H, dh, scale)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x, m1, r1, n1, qkv, attn, lse, s1, m2, r2, n2, u, g, wqkv, wo, w1s, w2s) = ctx.saved_tensors
+        (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = ctx.params
+        B, T, H, dh, scale = ctx.meta
+        d = x.shape[1]
+        wg = any(ctx.needs_input_grad[4:])
+        if not dy.is_contiguous():
+            dy = dy.contiguous()
+        db2 = _bgrad(b2, wg, dy)
+        dw2 = _wgrad(w2, wg, dy, g)
+        du = ops.linear_dgrad(dy, w2s, gelu_preact=u)
+        db1 = _bgrad(b1, wg, du)
+        dw1 = _wgrad(w1, wg, du, n2)
+        dn2 = ops.linear_dgrad(du, w1s)
+        ds1, dln2w, dln2b, _ = _ln_bwd(dn2, s1, ln2_w, ln2_b, m2, r2, wg, dres_add=dy)   # + residual path of y
+        dbo = _bgrad(o_b, wg, ds1)
+        dwo = _wgrad(o_w, wg, ds1, attn)
+        dattn = ops.linear_dgrad(ds1, wo)
+        dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale)
+        dqw = dkw = dvw = dqb = dkb = dvb = None
+        if wg:
+            dbqkv = _bgrad((q_b, k_b, v_b), True, dqkv)
+            dwqkv = _wgrad((q_w, k_w, v_w), True, dqkv, n1)
+            if dwqkv is not None:
+                dqw, dkw, dvw = dwqkv[:d], dwqkv[d:2 * d], dwqkv[2 * d:]
+            if dbqkv is not None:
+                dqb, dkb, dvb = dbqkv[:d], dbqkv[d:2 * d], dbqkv[2 * d:]
+        dx = dln1w = dln1b = None
+        if ctx.needs_input_grad[0] or wg:
+            dn1 = ops.linear_dgrad(dqkv, wqkv)
+            dx, dln1w, dln1b, _ = _ln_bwd(dn1, x, ln1_w, ln1_b, m1, r1, wg, dres_add=ds1)  # + residual path of s1
+            if not ctx.needs_input_grad[0]:
+                dx = None
         return (dx, None, None, None, dqw, dqb, dkw, dkb, dvw, dvb, dwo, dbo, dln1w, dln1b, dw1, db1, dw2, db2,
                 dln2w, dln2b)
 

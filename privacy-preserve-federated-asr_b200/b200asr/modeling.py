@@ -59,18 +59,21 @@ class _Affine(nn.Module):
 
 
 class _ConvLayer(nn.Module):
-    def __init__(self, cin, cout, k, bias):
+    def __init__(self, cin, cout, k, bias, norm=True):
         super().__init__()
         self.conv = _Affine((cout, cin, k), bias=bias, kind="conv")
-        self.layer_norm = _Affine((cout,), kind="ln")
+        if norm:  # LayerNorm(C) ("layer") or GroupNorm(C groups, C) on layer 0 ("group"): both hold weight/bias [C]
+            self.layer_norm = _Affine((cout,), kind="ln")
 
 
 class _FeatureExtractor(nn.Module):
     def __init__(self, config):
         super().__init__()
         dims, ks = list(config.conv_dim), list(config.conv_kernel)
+        group = _cfg(config, "feat_extract_norm", "layer") == "group"
         self.conv_layers = nn.ModuleList(
-            [_ConvLayer(1 if i == 0 else dims[i - 1], dims[i], ks[i], bool(_cfg(config, "conv_bias", False)))
+            [_ConvLayer(1 if i == 0 else dims[i - 1], dims[i], ks[i], bool(_cfg(config, "conv_bias", False)),
+                        norm=(not group) or i == 0)
              for i in range(len(dims))])
 
     def _freeze_parameters(self):
@@ -79,9 +82,10 @@ class _FeatureExtractor(nn.Module):
 
 
 class _FeatureProjection(nn.Module):
-    def __init__(self, config):
+    def __init__(self, config, layer_norm=True):
         super().__init__()
-        self.layer_norm = _Affine((config.conv_dim[-1],), kind="ln")
+        if layer_norm:
+            self.layer_norm = _Affine((config.conv_dim[-1],), kind="ln")
         self.projection = _Affine((config.hidden_size, config.conv_dim[-1]))
 
 
@@ -96,6 +100,33 @@ class _PosConvEmbed(nn.Module):
     def __init__(self, config):
         super().__init__()
         self.layers = nn.ModuleList([_PosConvLayer(config) for _ in range(config.num_conv_pos_embeddings)])
+
+
+class _WeightNormConv(nn.Module):
+    """nn.utils.weight_norm(nn.Conv1d(d, d, k, groups), dim=2): parameters `weight_g` [1,1,k], `weight_v` [d, d/g, k],
+    `bias` [d] -- the transformers==4.17 (reference pin) key names; `parametrizations.weight.original0/1` keys of
+    newer checkpoints are renamed on load."""
+
+    def __init__(self, d, groups, k):
+        super().__init__()
+        v = torch.empty(d, d // groups, k).normal_(0.0, 2.0 * math.sqrt(1.0 / (k * d)))
+        self.weight_g = nn.Parameter(v.norm(dim=(0, 1), keepdim=True))
+        self.weight_v = nn.Parameter(v)
+        self.bias = nn.Parameter(torch.zeros(d))
+        self._register_load_state_dict_pre_hook(self._rename_parametrizations)
+
+    @staticmethod
+    def _rename_parametrizations(state_dict, prefix, *args):
+        for new, old in (("parametrizations.weight.original0", "weight_g"), ("parametrizations.weight.original1", "weight_v")):
+            if prefix + new in state_dict:
+                state_dict[prefix + old] = state_dict.pop(prefix + new)
+
+
+class _PosConvEmbedWeightNorm(nn.Module):
+    def __init__(self, config):
+        super().__init__()
+        self.conv = _WeightNormConv(config.hidden_size, config.num_conv_pos_embedding_groups,
+                                    config.num_conv_pos_embeddings)
 
 
 class _Attention(nn.Module):
@@ -131,9 +162,9 @@ class _EncoderLayer(nn.Module):
 
 
 class _Encoder(nn.Module):
-    def __init__(self, config):
+    def __init__(self, config, weight_norm_posconv=False):
         super().__init__()
-        self.pos_conv_embed = _PosConvEmbed(config)
+        self.pos_conv_embed = _PosConvEmbedWeightNorm(config) if weight_norm_posconv else _PosConvEmbed(config)
         self.layer_norm = _Affine((config.hidden_size,), kind="ln")
         self.layers = nn.ModuleList([_EncoderLayer(config) for _ in range(config.num_hidden_layers)])
 
@@ -147,14 +178,19 @@ def conv_out_lengths(config, lengths: torch.Tensor) -> torch.Tensor:
 
 
 class Data2VecAudioModel(nn.Module):
-    """`data2vec_audio` sub-module: feature extractor -> projection -> encoder (HF:744-800)."""
+    """`data2vec_audio` sub-module: feature extractor -> projection -> encoder (HF:744-800).  The wav2vec2 / hubert
+    sub-classes below switch the positional conv (one weight-normed conv), the conv-stack norm ("group") and the
+    LayerNorm ordering (do_stable_layer_norm) -- transformers wav2vec2/modeling_wav2vec2.py Wav2Vec2Model."""
+
+    family = "data2vec"
 
     def __init__(self, config, compute_dtype=torch.bfloat16):
         super().__init__()
         self.config = config
         self.feature_extractor = _FeatureExtractor(config)
-        self.feature_projection = _FeatureProjection(config)
-        self.encoder = _Encoder(config)
+        self.feature_projection = _FeatureProjection(
+            config, layer_norm=self.family != "hubert" or bool(_cfg(config, "feat_proj_layer_norm", True)))
+        self.encoder = _Encoder(config, weight_norm_posconv=self.family != "data2vec")
         if _cfg(config, "mask_time_prob", 0.0) > 0.0 or _cfg(config, "mask_feature_prob", 0.0) > 0.0:
             self.masked_spec_embed = nn.Parameter(torch.empty(config.hidden_size).uniform_())
         self.cache = Fn.ShadowCache(compute_dtype)
@@ -181,10 +217,13 @@ class Data2VecAudioModel(nn.Module):
         if torch.is_grad_enabled() and any(p.requires_grad for p in self.feature_extractor.parameters()):
             raise NotImplementedError("the conv feature extractor is forward-only: call freeze_feature_encoder() "
                                       "as every reference entry point does (finetune_ASRs.py:200, models.py:302)")
-        if _cfg(c, "feat_extract_norm", "layer") != "layer":
-            raise NotImplementedError("feat_extract_norm='group' (wav2vec2-base GroupNorm stack) is not built yet")
-        if _cfg(c, "do_stable_layer_norm", False):
-            raise NotImplementedError("pre-LN (do_stable_layer_norm) encoder ordering is not built yet")
+        if _cfg(c, "feat_extract_norm", "layer") not in ("layer", "group"):
+            raise ValueError(f"feat_extract_norm must be 'layer' or 'group', got {c.feat_extract_norm!r}")
+        if self.family == "data2vec" and (_cfg(c, "feat_extract_norm", "layer") != "layer"
+                                          or _cfg(c, "do_stable_layer_norm", False)):
+            raise NotImplementedError("Data2VecAudio has no GroupNorm / stable-LayerNorm variant (HF:51-157, 359-418)")
+        if _cfg(c, "conv_pos_batch_norm", False):
+            raise NotImplementedError("hubert conv_pos_batch_norm is not supported")
 
     def forward(self, input_values, attention_mask=None, output_hidden_states=False):
         """Returns (hidden [B,T,d] in compute dtype, frame_lengths int32 [B] or None, hidden_states tuple|None)."""
@@ -192,31 +231,57 @@ class Data2VecAudioModel(nn.Module):
         self._check_unsupported()
         cache = self.cache
         fe = self.feature_extractor.conv_layers
+        lns = [getattr(l, "layer_norm", None) for l in fe]
         feats = Fn.feature_extractor_fwd(
-            input_values, [l.conv.weight for l in fe], [l.conv.bias for l in fe], [l.layer_norm.weight for l in fe],
-            [l.layer_norm.bias for l in fe], list(c.conv_kernel), list(c.conv_stride), 1e-5, cache)
+            input_values, [l.conv.weight for l in fe], [l.conv.bias for l in fe],
+            [None if n is None else n.weight for n in lns], [None if n is None else n.bias for n in lns],
+            list(c.conv_kernel), list(c.conv_stride), 1e-5, cache, norm=_cfg(c, "feat_extract_norm", "layer"))
         B, T, _ = feats.shape
         klen = None
         if attention_mask is not None:
             klen = conv_out_lengths(c, attention_mask.sum(-1)).to(torch.int32).contiguous()
         fp = self.feature_projection
         eps = float(_cfg(c, "layer_norm_eps", 1e-5))
-        h = Fn.FeatureProjectionFn.apply(feats, fp.layer_norm.weight, fp.layer_norm.bias, fp.projection.weight,
-                                         fp.projection.bias, eps, cache, klen)
+        fln = getattr(fp, "layer_norm", None)
+        h = Fn.FeatureProjectionFn.apply(feats, None if fln is None else fln.weight, None if fln is None else fln.bias,
+                                         fp.projection.weight, fp.projection.bias, eps, cache, klen)
         enc = self.encoder
-        pcs = enc.pos_conv_embed.layers
-        h = Fn.PosConvEmbedFn.apply(h, enc.layer_norm.weight, enc.layer_norm.bias, eps,
-                                    int(c.num_conv_pos_embedding_groups), int(c.conv_pos_kernel_size), cache,
-                                    *[l.conv.weight for l in pcs], *[l.conv.bias for l in pcs])
+        stable = bool(_cfg(c, "do_stable_layer_norm", False))
+        if self.family == "data2vec":
+            pcs = enc.pos_conv_embed.layers
+            h = Fn.PosConvEmbedFn.apply(h, enc.layer_norm.weight, enc.layer_norm.bias, eps,
+                                        int(c.num_conv_pos_embedding_groups), int(c.conv_pos_kernel_size), cache,
+                                        *[l.conv.weight for l in pcs], *[l.conv.bias for l in pcs])
+        else:
+            pc = enc.pos_conv_embed.conv
+            h = Fn.PosConvWeightNormFn.apply(h, None if stable else enc.layer_norm.weight,
+                                             None if stable else enc.layer_norm.bias, eps,
+                                             int(c.num_conv_pos_embedding_groups), int(c.num_conv_pos_embeddings), cache,
+                                             pc.weight_g, pc.weight_v, pc.bias)
         d = h.shape[-1]
         x = h.view(B * T, d)
         collected = [h] if output_hidden_states else None
         meta = (B, T, int(c.num_attention_heads), eps)
-        for layer in enc.layers:
-            x = Fn.EncoderLayerFn.apply(x, klen, meta, cache, *layer.params())
+        block = Fn.EncoderLayerStableFn if stable else Fn.EncoderLayerFn
+        for li, layer in enumerate(enc.layers):
+            x = block.apply(x, klen, meta, cache, *layer.params())
+            if collected is not None and not (stable and li + 1 == len(enc.layers)):
+                collected.append(x.view(B, T, d))
+        if stable:  # Wav2Vec2EncoderStableLayerNorm: one LayerNorm after the last block
+            x = Fn.LayerNormFn.apply(x, enc.layer_norm.weight, enc.layer_norm.bias, eps)
             if collected is not None:
                 collected.append(x.view(B, T, d))
         return x.view(B, T, d), klen, (tuple(collected) if collected is not None else None)
+
+
+class Wav2Vec2Model(Data2VecAudioModel):
+    """`wav2vec2` sub-module of Wav2Vec2ForCTC (finetune_ASRs.py:154-158)."""
+    family = "wav2vec2"
+
+
+class HubertModel(Data2VecAudioModel):
+    """`hubert` sub-module of HubertForCTC (finetune_ASRs.py:166-172)."""
+    family = "hubert"
 
 
 def _ctc_index_tensors(config, input_values, attention_mask, labels, klen):
@@ -237,8 +302,14 @@ def _ctc_index_tensors(config, input_values, attention_mask, labels, klen):
 class _CTCBase(nn.Module):
     validate_labels = True  # reference raises ValueError on labels >= vocab_size (costs one host sync)
 
+    base_model_prefix = "data2vec_audio"
+
+    @property
+    def backbone(self):
+        return getattr(self, self.base_model_prefix)
+
     def freeze_feature_encoder(self):
-        self.data2vec_audio.feature_extractor._freeze_parameters()
+        self.backbone.feature_extractor._freeze_parameters()
 
     freeze_feature_extractor = freeze_feature_encoder
 
@@ -264,12 +335,14 @@ class _CTCBase(nn.Module):
 class Data2VecAudioForCTC(_CTCBase):
     """HF Data2VecAudioForCTC (HF:803-916) as instantiated by centralized/finetune_ASRs.py:164."""
 
+    backbone_cls = Data2VecAudioModel
+
     def __init__(self, config, compute_dtype=torch.bfloat16):
         super().__init__()
         if config.vocab_size is None:
             raise ValueError("config.vocab_size must be defined for the CTC head")
         self.config = config
-        self.data2vec_audio = Data2VecAudioModel(config, compute_dtype)
+        setattr(self, self.base_model_prefix, self.backbone_cls(config, compute_dtype))
         self.lm_head = _Affine((config.vocab_size, config.hidden_size))
 
     def forward(self, input_values, attention_mask=None, output_attentions=None, output_hidden_states=None,
@@ -278,8 +351,8 @@ class Data2VecAudioForCTC(_CTCBase):
             raise NotImplementedError("output_attentions is not available from the fused attention path")
         if labels is not None:
             self._check_labels(labels)
-        h, klen, hs = self.data2vec_audio(input_values, attention_mask, bool(output_hidden_states))
-        logits = Fn.LinearFn.apply(h, self.lm_head.weight, self.lm_head.bias, self.data2vec_audio.cache)
+        h, klen, hs = self.backbone(input_values, attention_mask, bool(output_hidden_states))
+        logits = Fn.LinearFn.apply(h, self.lm_head.weight, self.lm_head.bias, self.backbone.cache)
         loss = None
         if labels is not None:
             loss = self._ctc(logits, _ctc_index_tensors(self.config, input_values, attention_mask, labels, klen))
@@ -287,6 +360,21 @@ class Data2VecAudioForCTC(_CTCBase):
             out = (logits,) + ((hs,) if hs is not None else ())
             return ((loss,) + out) if loss is not None else out
         return CausalLMOutput(loss=loss, logits=logits, hidden_states=hs, attentions=None)
+
+
+class Wav2Vec2ForCTC(Data2VecAudioForCTC):
+    """HF Wav2Vec2ForCTC as instantiated by centralized/finetune_ASRs.py:154-158 (facebook/wav2vec2-base-960h:
+    feat_extract_norm='group', post-LN) and its large / lv60 configurations (layer norm stack, do_stable_layer_norm).
+    state_dict keys: `wav2vec2.*`, `lm_head.*`."""
+    base_model_prefix = "wav2vec2"
+    backbone_cls = Wav2Vec2Model
+
+
+class HubertForCTC(Data2VecAudioForCTC):
+    """HF HubertForCTC as instantiated by centralized/finetune_ASRs.py:166-172 (facebook/hubert-xlarge-ls960-ft:
+    layer-norm conv stack with bias, do_stable_layer_norm).  state_dict keys: `hubert.*`, `lm_head.*`."""
+    base_model_prefix = "hubert"
+    backbone_cls = HubertModel
 
 
 class _CosFaceHolder(nn.Module):

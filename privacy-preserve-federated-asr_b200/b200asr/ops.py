@@ -239,6 +239,69 @@ def conv0_ln_gelu(x, w, bias, ln_w, ln_b, stride: int, eps: float, out_dtype: to
     return y
 
 
+def conv0_gn_gelu(x, w, bias, gn_w, gn_b, stride: int, eps: float, out_dtype: torch.dtype) -> torch.Tensor:
+    """x [B, L] fp32 -> [B, Tout, C] channels-last: Conv1d(1->C) + GroupNorm(C groups) + GELU (wav2vec2
+    GroupNormConvLayer, feat_extract_norm='group')."""
+    x = _c(x)
+    B, L = x.shape
+    Cc, cin, k = w.shape
+    assert cin == 1 and x.dtype == torch.float32
+    Tout = (L - k) // stride + 1
+    y = torch.empty(B, Tout, Cc, dtype=out_dtype, device=x.device)
+    nws = lib.b200asr_conv0_gn_gelu_workspace_bytes(B, L, Cc, k, stride)
+    ws = workspace(nws, x.device)
+    check(lib.b200asr_conv0_gn_gelu_fwd(_p(x), _p(_c(w)), _p(bias), _p(gn_w), _p(gn_b), _p(y), _p(ws), nws, B, L, Cc, k,
+                                        stride, float(eps), _DT[out_dtype], _st()), "conv0_gn_gelu_fwd")
+    return y
+
+
+def weight_norm_fwd(v: torch.Tensor, g: torch.Tensor):
+    """weight_norm(dim=2): v fp32 [C, Cg, k], g fp32 [1, 1, k] -> (w fp32 [C, Cg, k], norm fp32 [k])."""
+    v, g = _c(v), _c(g)
+    assert v.dtype == torch.float32 and g.dtype == torch.float32
+    k = v.shape[-1]
+    rows = v.numel() // k
+    w = torch.empty_like(v)
+    norm = torch.empty(k, dtype=torch.float32, device=v.device)
+    nws = lib.b200asr_weight_norm_workspace_bytes(k)
+    ws = workspace(nws, v.device)
+    check(lib.b200asr_weight_norm_fwd(_p(v), _p(g), _p(w), _p(norm), _p(ws), nws, rows, k, _st()), "weight_norm_fwd")
+    return w, norm
+
+
+def weight_norm_bwd(dw, v, g, norm, dv_out=None, dg_out=None):
+    """(dv [C, Cg, k], dg [1, 1, k]) from dw fp32 [C, Cg, k]; optional preallocated fp32 destinations."""
+    dw, v, g = _c(dw), _c(v), _c(g)
+    k = v.shape[-1]
+    rows = v.numel() // k
+    dv = dv_out if dv_out is not None else torch.empty_like(v)
+    dg = dg_out if dg_out is not None else torch.empty(g.shape, dtype=torch.float32, device=v.device)
+    nws = lib.b200asr_weight_norm_workspace_bytes(k)
+    ws = workspace(nws, v.device)
+    check(lib.b200asr_weight_norm_bwd(_p(dw), _p(v), _p(g), _p(norm), _p(dv), _p(dg), _p(ws), nws, rows, k, _st()),
+          "weight_norm_bwd")
+    return dv, dg
+
+
+def gelu_add(c: torch.Tensor, res: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """y = res + gelu(c)."""
+    c = _c(c)
+    if res is not None:
+        res = _c(res)
+        assert res.dtype == c.dtype and res.numel() == c.numel()
+    y = torch.empty_like(c)
+    check(lib.b200asr_gelu_add_fwd(_p(c), _p(res), _p(y), c.numel(), dt(c), _st()), "gelu_add_fwd")
+    return y
+
+
+def gelu_bwd(dy: torch.Tensor, c: torch.Tensor) -> torch.Tensor:
+    """dc = dy * gelu'(c)."""
+    dy, c = _c(dy), _c(c)
+    dc = torch.empty_like(c)
+    check(lib.b200asr_gelu_bwd(_p(dy), _p(c), _p(dc), c.numel(), dt(c), _st()), "gelu_bwd")
+    return dc
+
+
 # ----------------------------------------------------------------------------- GEMM
 def gemm_raw(A, B, Cout, M, N, K, lda, ldb, ldc, a_kmajor=True, b_kmajor=True, bias=None, residual=None,
              aux_out=None, aux_in=None, act=ACT_NONE, mul_gelu_grad=False, alpha=1.0, batch0=1, batch1=1,

@@ -47,6 +47,47 @@ def test_plain_ctc_matches_hf(golden_dir, name, conv_bias):
         assert abs(float(sd[str(n)].grad.norm()) - v) <= 2e-4 * max(v, 1e-3), n
 
 
+# config-5 variants (finetune_ASRs.py:154-172).  The table mirrors tests/golden/make_golden.py::VARIANTS.
+VARIANTS = {
+    "w2v2_group_postln": ("tiny_wav2vec2", {}),
+    "w2v2_layer_stable": ("tiny_wav2vec2", dict(feat_extract_norm="layer", conv_bias=True, do_stable_layer_norm=True)),
+    "hubert_stable": ("tiny_hubert", {}),
+    "hubert_base_nomask": ("tiny_hubert", dict(feat_extract_norm="group", conv_bias=False, do_stable_layer_norm=False,
+                                               feat_proj_layer_norm=False)),
+}
+
+
+def variant_cfg(name):
+    fac, kw = VARIANTS[name]
+    return getattr(R.ArchConfig, fac)(**kw)
+
+
+@pytest.mark.parametrize("name", list(VARIANTS))
+def test_variant_ctc_matches_hf(golden_dir, name):
+    """Wav2Vec2ForCTC / HubertForCTC fixtures: GroupNorm conv stack, weight-normed positional conv, pre-LN blocks."""
+    g = _load(golden_dir, name)
+    cfg = variant_cfg(name)
+    seed, batch, samples, use_mask = int(g["seed"]), int(g["batch"]), int(g["samples"]), bool(g["use_mask"])
+    sd = R.init_state_dict(cfg, seed=seed, dacs=False)
+    sd = {k: v.clone().requires_grad_(not k.startswith(cfg.prefix + "feature_extractor")) for k, v in sd.items()}
+    b = R.synth_batch(cfg, batch, samples, seed=1234 + seed, ragged=use_mask, max_label=12)
+    collect = []
+    loss, logits = R.ctc_forward(sd, cfg, b["input_values"], b["attention_mask"] if use_mask else None, b["labels"], collect)
+    loss.backward()
+    np.testing.assert_allclose(collect[0].detach().numpy(), g["hidden_first"], rtol=0, atol=5e-5)
+    np.testing.assert_allclose(collect[-1].detach().numpy(), g["hidden_last"], rtol=0, atol=1e-4)
+    np.testing.assert_allclose(logits.detach().numpy(), g["logits"], rtol=0, atol=2e-4)
+    np.testing.assert_allclose(float(loss), float(g["loss"]), rtol=1e-5)
+    assert (logits.argmax(-1).numpy() == g["argmax"]).all()
+    for n in g["grad_names"]:
+        ref = g["grad:" + str(n)]
+        got = sd[str(n)].grad.numpy()
+        scale = max(np.abs(ref).max(), 1e-6)
+        assert np.abs(got - ref).max() / scale < 3e-4, n
+    for n, v in zip(g["gnorm_names"], g["gnorm_values"]):
+        assert abs(float(sd[str(n)].grad.norm()) - v) <= 3e-4 * max(v, 1e-3), n
+
+
 @pytest.mark.parametrize("name", ["dacs_stage0", "dacs_stage1", "dacs_stage2", "dacs_stage2_toggle", "dacs_stage2_f1"])
 def test_dacs_matches_reference(golden_dir, name):
     g = _load(golden_dir, name)
