@@ -159,7 +159,7 @@ def run_b200(args):
     import torch.distributed as dist
 
     from b200asr import _lib, modeling as M, ops
-    from b200asr.fedavg import fedavg_allreduce
+    from b200asr.fedavg import PeerFedAvg, fedavg_allreduce
     from b200asr.optim import FusedAdamW
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -178,7 +178,10 @@ def run_b200(args):
     model.freeze_feature_encoder()
     model.validate_labels = False  # the reference's labels.max() check costs a host sync per step; inputs are synthetic
     model.to(dev).train()
-    opt = FusedAdamW(model.named_parameters(), lr=1e-5, weight_decay=0.005, max_grad_norm=1.0, warmup_steps=1000)
+    use_peer = world > 1 and args.fedavg == "peer"
+    opt = FusedAdamW(model.named_parameters(), lr=1e-5, weight_decay=0.005, max_grad_norm=1.0, warmup_steps=1000,
+                     peer=use_peer)
+    peer_agg = PeerFedAvg([g["fp"] for g in opt.groups]) if use_peer else None
     n_train = sum(g["fp"].numel for g in opt.groups)
     samples = SECONDS * SR
     frames = int(M.conv_out_lengths(cfg, torch.tensor(samples)))
@@ -202,11 +205,17 @@ def run_b200(args):
     def local_step(batch):
         return graphed(batch) if graphed is not None else eager_step(batch)
 
+    def fedavg_nccl():
+        for g in opt.groups:
+            fedavg_allreduce(g["fp"].flat)
+            g["fp"].mark_updated()
+
     def fedavg():
         if world > 1:
-            for g in opt.groups:
-                fedavg_allreduce(g["fp"].flat)
-                g["fp"].mark_updated()
+            if peer_agg is not None:   # fused peer-memory kernel: scale + reduce-scatter + all-gather over NVLink
+                peer_agg()
+            else:                      # our scale kernel + NCCL all-reduce
+                fedavg_nccl()
 
     def barrier():
         if world > 1:
@@ -254,6 +263,26 @@ def run_b200(args):
     clk = clocks.stop() if clocks else None
     ms_e2e, _, last_loss = timed(args.steps, e2e=True)
 
+    # ---- the other FedAvg implementation, timed alone on identical buffers (every rank holds the same average by now)
+    agg_alone = {}
+    if world > 1:
+        def time_alone(fn, iters=5):
+            barrier()
+            fn(); barrier()
+            o0, o1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            o0.record()
+            for _ in range(iters):
+                fn()
+            o1.record()
+            barrier()
+            t = torch.tensor([o0.elapsed_time(o1) / iters], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t)
+        agg_alone["nccl_allreduce_ms"] = time_alone(fedavg_nccl)
+        if peer_agg is not None:
+            agg_alone["peer_kernel_ms"] = time_alone(peer_agg)
+            peer_agg.check()
+
     # ---- host enqueue time of one step (no synchronisation inside: pure Python + launch cost; the GPU queue holds a step)
     torch.cuda.synchronize()
     h0 = time.perf_counter()
@@ -266,6 +295,8 @@ def run_b200(args):
     torch.cuda.synchronize()
 
     # ---- roofline leg: one extra instrumented step, every GEMM / attention call bracketed by CUDA events
+    eager_step(resident[0])  # untimed: the eager path's workspaces are allocated here, not inside an event bracket
+    torch.cuda.synchronize()
     ops.PROFILE = []
     eager_step(resident[0])
     torch.cuda.synchronize()
@@ -278,8 +309,14 @@ def run_b200(args):
     gm = kinds.get("gemm", [0, 1e-9, 0.0])
     achieved = gm[2] / (gm[1] * 1e-3) / 1e12
     peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1400.0)))
+    traffic = None
+    try:  # per-launch DRAM traffic of this kernel from the committed ncu capture of this same command (profiles/)
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_gemm_traffic_v9.json")))["dram_bytes_per_launch"]
+    except Exception:
+        pass
     roofline = {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05 bf16 GEMM: QKV/O/FFN linears fwd+dgrad+wgrad, conv layers 1-6)",
-                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
+                "traffic_source": "profiles/r01_ncu_gemm_traffic_v9.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, mean over one step's launches)",
                 "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({src})", "launches": gm[0],
                 "avg_launch_us": gm[1] * 1e3 / max(1, gm[0]), "share_of_step": gm[1] / ms_step,
                 "other": {k: {"launches": v[0], "ms": v[1], "tflops": v[2] / (v[1] * 1e-3) / 1e12} for k, v in kinds.items()
@@ -296,7 +333,10 @@ def run_b200(args):
             "config": {"workload": WORKLOAD, "global_batch": BATCH * world, "audio_s_per_step": audio_s,
                        "clients": world, "trainable_params": n_train, "frames_per_utt": frames,
                        "l2_policy": "inputs+weights+saved activations per step (>3 GB) exceed the 126 MB L2; no flush",
-                       "fedavg": "uniform FedAvg of all trainable params after every local step (NCCL all-reduce)" if world > 1 else "n/a at 1 GPU"},
+                       "fedavg": (("uniform FedAvg of all trainable params after every local step: fused peer-memory kernel "
+                                   "(scale + reduce-scatter + all-gather over NVLink, no NCCL on the data path)") if use_peer else
+                                  "uniform FedAvg of all trainable params after every local step (scale kernel + NCCL all-reduce)")
+                                 if world > 1 else "n/a at 1 GPU"},
             "e2e": {"value": audio_s / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": sum(v.numel() * v.element_size() for v in host[0].values()),
                     "d2h_bytes_per_step": 4, "last_loss": last_loss},
@@ -307,6 +347,9 @@ def run_b200(args):
             "step_tflops": algo_tflop * world / (ms_step * 1e-3),
             "step_frac_of_tensor_peak": algo_tflop / (ms_step * 1e-3) / peak,
             "fedavg_round_s": ms_step * 1e-3, "fedavg_agg_ms": agg_ms if world > 1 else None,
+            "fedavg_agg_alone": agg_alone or None,  # each implementation timed back to back without the local step
+            "fedavg_nvlink_gbs_per_dir": (4 * n_train * (world - 1) / world / (agg_alone["peer_kernel_ms"] * 1e-3) / 1e9)
+                                         if agg_alone.get("peer_kernel_ms") else None,
             "fedavg_bytes_per_client": 4 * n_train,
             "clocks": clk, "roofline": roofline,
         }
@@ -324,6 +367,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--fedavg", default="peer", choices=["peer", "nccl"], help="N>1 aggregation: fused peer-memory kernel or NCCL")
     ap.add_argument("--eager", action="store_true", help="issue every launch from Python instead of replaying the CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":

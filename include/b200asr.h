@@ -291,6 +291,20 @@ int b200asr_fedavg_prescale(float* buf, float w, long long n, void* stream);
 int b200asr_fedavg_peer_reduce(float* const* peer_bufs, const float* weights, int world, int rank, long long n,
                                void* stream);
 
+/* Cross-rank barrier over peer memory for the fused kernel above: every rank passes the HOST array of the `world`
+ * ranks' flag buffers (>= world unsigned each, zero-initialised, peer-mapped) and a barrier number `epoch` that grows
+ * by one per call on every rank.  Stream-ordered; bounded spin (sets *timeout_flag, a device int, instead of hanging). */
+int b200asr_fedavg_peer_barrier(unsigned* const* peer_flags, int world, int rank, unsigned epoch, int* timeout_flag,
+                                void* stream);
+/* Peer-visible device allocations (zero-filled cudaMalloc, exportable through CUDA IPC) and the IPC plumbing that
+ * replaces the reference's pickle / deepcopy hops of the weights between client processes and the server
+ * (federated/src/federated_main.py:124-141, federated/src/update.py:246-283).  Explicit create / destroy pairs. */
+int b200asr_peer_alloc(void** ptr, size_t bytes);
+int b200asr_peer_free(void* ptr);
+int b200asr_ipc_export(const void* ptr, unsigned char handle[64]);
+int b200asr_ipc_open(const unsigned char handle[64], void** ptr);
+int b200asr_ipc_close(void* ptr);
+
 /* ------------------------------------------------------------------------------------------------
  * Fused AdamW on flat fp32 buffers (HF Trainer "adamw_hf" semantics = transformers.AdamW with
  * correct_bias=True, configured at centralized/finetune_ASRs.py:202-220, federated/src/update.py:657-678):

@@ -84,6 +84,12 @@ SIGNATURES = {
     "b200asr_fedavg_scale_accum": (i32, [C.POINTER(vp), C.POINTER(f32), vp, i32, i64, vp]),
     "b200asr_fedavg_prescale": (i32, [vp, f32, i64, vp]),
     "b200asr_fedavg_peer_reduce": (i32, [C.POINTER(vp), C.POINTER(f32), i32, i32, i64, vp]),
+    "b200asr_fedavg_peer_barrier": (i32, [C.POINTER(vp), i32, i32, C.c_uint, vp, vp]),
+    "b200asr_peer_alloc": (i32, [C.POINTER(vp), sz]),
+    "b200asr_peer_free": (i32, [vp]),
+    "b200asr_ipc_export": (i32, [vp, C.c_char_p]),
+    "b200asr_ipc_open": (i32, [C.c_char_p, C.POINTER(vp)]),
+    "b200asr_ipc_close": (i32, [vp]),
     "b200asr_adamw_step": (i32, [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i32, vp, f32, vp]),
     "b200asr_adamw_step_dev": (i32, [vp, vp, vp, vp, vp, i64, vp, f32, f32, f32, f32, vp, f32, vp]),
     "b200asr_sumsq": (i32, [vp, i64, vp, vp]),

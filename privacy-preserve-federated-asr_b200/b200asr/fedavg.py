@@ -55,7 +55,10 @@ class FlatParams:
         cast or QKV concat.  `epoch` counts raw-pointer updates of `flat`; the shadow is valid iff it was refreshed
         at the current epoch."""
 
-    def __init__(self, named_params: Iterable, device=None, with_shadow: bool = False, direct_grads: bool = True):
+    def __init__(self, named_params: Iterable, device=None, with_shadow: bool = False, direct_grads: bool = True,
+                 peer: bool = False):
+        """peer=True places `flat` in a peer-visible allocation (PeerBuffer) so that PeerFedAvg can reduce it straight
+        out of the other clients' HBM."""
         named = [(n, p) for n, p in named_params]
         if not named:
             raise ValueError("FlatParams: no parameters")
@@ -67,7 +70,8 @@ class FlatParams:
             self.offsets.append(off)
             off += (p.numel() + 3) // 4 * 4
         self.numel = off
-        self.flat = torch.zeros(off, dtype=torch.float32, device=device)
+        self.peer_buffer = PeerBuffer(off * 4, device) if peer else None
+        self.flat = self.peer_buffer.as_tensor(torch.float32, off) if peer else torch.zeros(off, dtype=torch.float32, device=device)
         self.grad = torch.zeros(off, dtype=torch.float32, device=device)
         self.shadow = torch.zeros(off, dtype=torch.bfloat16, device=device) if with_shadow else None
         self.epoch = 0
@@ -126,6 +130,127 @@ def fedavg_allreduce(flat: torch.Tensor, weight: Optional[float] = None, group=N
     ops.fedavg_prescale_(flat, w)
     dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
     return flat
+
+
+class PeerBuffer:
+    """A zero-filled device allocation made by the library (plain cudaMalloc, so CUDA IPC can export it) and viewed as
+    a torch tensor.  `export()` gives the 64-byte IPC handle another process opens with `PeerBuffer.open`."""
+
+    def __init__(self, nbytes: int, device=None, _ptr=None, _opened=False):
+        import ctypes as C
+        from ._lib import check, lib
+        self.nbytes = int(nbytes)
+        self.device = torch.device(device if device is not None else torch.device("cuda", torch.cuda.current_device()))
+        self.opened = _opened
+        if _ptr is None:
+            with torch.cuda.device(self.device):
+                p = C.c_void_p()
+                check(lib.b200asr_peer_alloc(C.byref(p), self.nbytes), "peer_alloc")
+                _ptr = p.value
+        self.ptr = int(_ptr)
+
+    def as_tensor(self, dtype=torch.float32, numel=None) -> torch.Tensor:
+        item = torch.empty(0, dtype=dtype).element_size()
+        n = self.nbytes // item if numel is None else int(numel)
+        typestr = {torch.float32: "<f4", torch.int32: "<i4", torch.uint8: "|u1"}[dtype]
+        holder = type("_PeerView", (), {})()
+        holder.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (self.ptr, False), "version": 2}
+        holder._owner = self  # keeps the allocation alive as long as the tensor
+        return torch.as_tensor(holder, device=self.device)
+
+    def export(self) -> bytes:
+        import ctypes as C
+        from ._lib import check, lib
+        buf = C.create_string_buffer(64)
+        check(lib.b200asr_ipc_export(self.ptr, buf), "ipc_export")
+        return buf.raw
+
+    @staticmethod
+    def open(handle: bytes, nbytes: int, device=None) -> "PeerBuffer":
+        import ctypes as C
+        from ._lib import check, lib
+        p = C.c_void_p()
+        check(lib.b200asr_ipc_open(C.create_string_buffer(handle, 64), C.byref(p)), "ipc_open")
+        return PeerBuffer(nbytes, device, _ptr=p.value, _opened=True)
+
+    def close(self):
+        from ._lib import lib
+        if self.ptr:
+            (lib.b200asr_ipc_close if self.opened else lib.b200asr_peer_free)(self.ptr)
+            self.ptr = 0
+
+
+class PeerFedAvg:
+    """The fused multi-GPU FedAvg (one federated client per rank / GPU, federated_main.py:138-141): every rank reduces
+    its slice of each flat buffer straight out of the peers' HBM over NVLink and writes the average back into every
+    peer -- scale, reduce-scatter and all-gather in one kernel (`b200asr_fedavg_peer_reduce`), bracketed by the
+    peer-memory barrier kernel.  No NCCL on the data path; torch.distributed only carries the IPC handles once.
+
+      agg = PeerFedAvg([g["fp"] for g in opt.groups])      # FlatParams built with peer=True
+      agg()                                                # after the local step, on every rank
+    """
+
+    def __init__(self, flats: Sequence["FlatParams"], group=None):
+        import torch.distributed as dist
+        self.flats = list(flats)
+        for fp in self.flats:
+            if fp.peer_buffer is None:
+                raise ValueError("PeerFedAvg needs FlatParams(..., peer=True)")
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        dev = self.flats[0].flat.device
+        self.sync = PeerBuffer(4096, dev)
+        self.timeout = torch.zeros(1, dtype=torch.int32, device=dev)
+        mine = {"flats": [(fp.peer_buffer.export(), fp.peer_buffer.nbytes, fp.numel) for fp in self.flats],
+                "sync": self.sync.export()}
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, mine, group=group)
+        self._opened = []
+        self.flag_ptrs, self.flat_ptrs = [], [[] for _ in self.flats]
+        for r, info in enumerate(everyone):
+            if [n for _, _, n in info["flats"]] != [fp.numel for fp in self.flats]:
+                raise ValueError(f"PeerFedAvg: rank {r} holds differently sized flat buffers")
+            if r == self.rank:
+                self.flag_ptrs.append(self.sync.ptr)
+                for i, fp in enumerate(self.flats):
+                    self.flat_ptrs[i].append(fp.peer_buffer.ptr)
+                continue
+            sb = PeerBuffer.open(info["sync"], 4096, dev)
+            self._opened.append(sb)
+            self.flag_ptrs.append(sb.ptr)
+            for i, (h, nbytes, _) in enumerate(info["flats"]):
+                pb = PeerBuffer.open(h, nbytes, dev)
+                self._opened.append(pb)
+                self.flat_ptrs[i].append(pb.ptr)
+        self.epoch = 0
+        dist.barrier(group=group)  # every rank has mapped every peer before the first kernel touches them
+
+    def _barrier(self):
+        import ctypes as C
+        from ._lib import check, lib
+        self.epoch += 1
+        ptrs = (C.c_void_p * self.world)(*self.flag_ptrs)
+        check(lib.b200asr_fedavg_peer_barrier(ptrs, self.world, self.rank, self.epoch, self.timeout.data_ptr(),
+                                              torch.cuda.current_stream().cuda_stream), "fedavg_peer_barrier")
+
+    def __call__(self, weights: Optional[Sequence[float]] = None):
+        """weights: per-rank FedAvg weights (None = the reference's uniform 1/N, sequential sum then divide)."""
+        self._barrier()   # every client's local update is complete and visible
+        for fp, ptrs in zip(self.flats, self.flat_ptrs):
+            ops.fedavg_peer_reduce(ptrs, weights, self.rank, fp.numel)
+        self._barrier()   # every slice has been written back everywhere
+        for fp in self.flats:
+            fp.mark_updated()
+
+    def check(self):
+        """Host-synchronising: raises if a barrier ever timed out (a peer never arrived)."""
+        if int(self.timeout.item()) != 0:
+            raise RuntimeError("PeerFedAvg: cross-rank barrier timed out")
+
+    def close(self):
+        for pb in self._opened:
+            pb.close()
+        self._opened = []
 
 
 def fedavg_shard_plan(n: int, world: int):

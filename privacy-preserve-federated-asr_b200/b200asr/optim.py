@@ -21,7 +21,7 @@ def _no_decay(name: str) -> bool:
 class FusedAdamW:
     def __init__(self, named_params: Iterable, lr=1e-5, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.005,
                  max_grad_norm: Optional[float] = 1.0, warmup_steps: int = 0, total_steps: Optional[int] = None,
-                 bf16_shadow: bool = True):
+                 bf16_shadow: bool = True, peer: bool = False):
         """bf16_shadow: keep a flat bf16 copy of the decayed group (the GEMM weights) current inside the update
         kernel, which the bf16 compute path then reads directly (functional.ShadowCache)."""
         wd_shadow = bf16_shadow
@@ -31,7 +31,7 @@ class FusedAdamW:
         self.groups = []
         for items, wd in ((dec, weight_decay), (nod, 0.0)):
             if items:
-                fp = FlatParams(items, with_shadow=(wd_shadow and items is dec))
+                fp = FlatParams(items, with_shadow=(wd_shadow and items is dec), peer=peer)
                 self.groups.append(dict(fp=fp, wd=wd, m=torch.zeros_like(fp.flat), v=torch.zeros_like(fp.flat)))
         self.lr, self.betas, self.eps = lr, betas, eps
         self.max_grad_norm = max_grad_norm

@@ -1,5 +1,7 @@
 // FedAvg on flat fp32 parameter buffers (federated/src/utils.py:240-249) and the fused AdamW step that shares
 // the flat layout.  HBM-bound streaming kernels: 128-bit loads, grid = multiple of the SM count, one pass.
+#include <string.h>
+
 #include "common.cuh"
 
 namespace b200asr {
@@ -66,20 +68,42 @@ template <int UNIFORM>
 __global__ void __launch_bounds__(256) fedavg_peer_kernel(const PeerPtrs p, int world, long long lo, long long hi) {
     const float kf = (float)world;
     const long long nvec = (hi - lo) / 4;  // lo, hi are multiples of 4 except the global tail handled by the last rank
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
-        const long long e = lo + 4 * i;
-        float4 acc = *reinterpret_cast<const float4*>(p.buf[0] + e);
-        if (!UNIFORM) { acc.x *= p.w[0]; acc.y *= p.w[0]; acc.z *= p.w[0]; acc.w *= p.w[0]; }
+    constexpr int U = 4;                   // independent 16-byte loads per peer in flight per thread (NVLink latency)
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < nvec; i0 += U * stride) {
+        float4 acc[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long i = i0 + u * stride;
+            acc[u] = (i < nvec) ? __ldcs(reinterpret_cast<const float4*>(p.buf[0] + lo + 4 * i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            if (!UNIFORM) { acc[u].x *= p.w[0]; acc[u].y *= p.w[0]; acc[u].z *= p.w[0]; acc[u].w *= p.w[0]; }
+        }
         for (int j = 1; j < world; ++j) {
-            const float4 v = *reinterpret_cast<const float4*>(p.buf[j] + e);
-            if (UNIFORM) { acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w; }
-            else {
-                acc.x = fmaf(p.w[j], v.x, acc.x); acc.y = fmaf(p.w[j], v.y, acc.y);
-                acc.z = fmaf(p.w[j], v.z, acc.z); acc.w = fmaf(p.w[j], v.w, acc.w);
+            float4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const long long i = i0 + u * stride;
+                v[u] = (i < nvec) ? __ldcs(reinterpret_cast<const float4*>(p.buf[j] + lo + 4 * i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (UNIFORM) { acc[u].x += v[u].x; acc[u].y += v[u].y; acc[u].z += v[u].z; acc[u].w += v[u].w; }
+                else {
+                    acc[u].x = fmaf(p.w[j], v[u].x, acc[u].x); acc[u].y = fmaf(p.w[j], v[u].y, acc[u].y);
+                    acc[u].z = fmaf(p.w[j], v[u].z, acc[u].z); acc[u].w = fmaf(p.w[j], v[u].w, acc[u].w);
+                }
             }
         }
-        if (UNIFORM) { acc.x = __fdiv_rn(acc.x, kf); acc.y = __fdiv_rn(acc.y, kf); acc.z = __fdiv_rn(acc.z, kf); acc.w = __fdiv_rn(acc.w, kf); }
-        for (int j = 0; j < world; ++j) *reinterpret_cast<float4*>(p.buf[j] + e) = acc;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long i = i0 + u * stride;
+            if (i >= nvec) continue;
+            if (UNIFORM) {
+                acc[u].x = __fdiv_rn(acc[u].x, kf); acc[u].y = __fdiv_rn(acc[u].y, kf);
+                acc[u].z = __fdiv_rn(acc[u].z, kf); acc[u].w = __fdiv_rn(acc[u].w, kf);
+            }
+            for (int j = 0; j < world; ++j) __stcs(reinterpret_cast<float4*>(p.buf[j] + lo + 4 * i), acc[u]);
+        }
     }
     for (long long e = lo + nvec * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; e < hi; e += (long long)gridDim.x * blockDim.x) {
         float acc = UNIFORM ? p.buf[0][e] : p.w[0] * p.buf[0][e];
@@ -87,6 +111,35 @@ __global__ void __launch_bounds__(256) fedavg_peer_kernel(const PeerPtrs p, int 
         if (UNIFORM) acc = __fdiv_rn(acc, kf);
         for (int j = 0; j < world; ++j) p.buf[j][e] = acc;
     }
+}
+
+// Cross-rank barrier over peer memory (one tiny block): thread t publishes `epoch` into peer t's flag slot [rank]
+// (NVLink store, release at system scope) and spins on the local slot [t] until peer t has published the same epoch.
+// Stream order on each rank + this barrier = "every rank's preceding kernels are complete and visible".  The spin is
+// bounded (~2 s of SM clock): on expiry *timeout is set and the kernel returns instead of hanging the GPU.
+struct PeerFlags {
+    unsigned* f[FEDAVG_MAX_K];
+};
+
+__global__ void fedavg_peer_barrier_kernel(const PeerFlags s, int world, int rank, unsigned epoch, int* timeout) {
+    const int t = threadIdx.x;
+    if (t >= world) return;
+    __threadfence_system();
+    unsigned* remote = s.f[t] + rank;
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(remote), "r"(epoch) : "memory");
+    const unsigned* local = s.f[rank] + t;
+    const long long t0 = clock64();
+    for (;;) {
+        unsigned v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(local) : "memory");
+        if ((int)(v - epoch) >= 0) break;
+        if (clock64() - t0 > 4000000000LL) {
+            if (timeout) *timeout = 1;
+            break;
+        }
+        __nanosleep(200);
+    }
+    __threadfence_system();
 }
 
 // ---------------------------------------------------------------- AdamW (transformers.AdamW, correct_bias=True)
@@ -237,6 +290,81 @@ int b200asr_fedavg_peer_reduce(float* const* peer_bufs, const float* weights, in
     if (weights) fedavg_peer_kernel<0><<<stream_grid(hi - lo), 256, 0, as_stream(stream)>>>(p, world, lo, hi);
     else fedavg_peer_kernel<1><<<stream_grid(hi - lo), 256, 0, as_stream(stream)>>>(p, world, lo, hi);
     return check_launch("fedavg_peer_reduce");
+}
+
+int b200asr_fedavg_peer_barrier(unsigned* const* peer_flags, int world, int rank, unsigned epoch, int* timeout_flag,
+                                void* stream) {
+    B200_REQUIRE(peer_flags, "fedavg_peer_barrier: null pointer");
+    B200_REQUIRE(world >= 1 && world <= FEDAVG_MAX_K && rank >= 0 && rank < world, "fedavg_peer_barrier: bad world/rank");
+    PeerFlags s;
+    for (int j = 0; j < FEDAVG_MAX_K; ++j) {
+        s.f[j] = j < world ? peer_flags[j] : nullptr;
+        if (j < world) B200_REQUIRE(peer_flags[j], "fedavg_peer_barrier: null flag pointer for rank %d", j);
+    }
+    fedavg_peer_barrier_kernel<<<1, 32, 0, as_stream(stream)>>>(s, world, rank, epoch, timeout_flag);
+    return check_launch("fedavg_peer_barrier");
+}
+
+// ---- peer-visible allocations + CUDA IPC plumbing (one federated client per process / GPU)
+int b200asr_peer_alloc(void** ptr, size_t bytes) {
+    B200_REQUIRE(ptr && bytes > 0, "peer_alloc: bad argument");
+    cudaError_t e = cudaMalloc(ptr, bytes);
+    if (e == cudaSuccess) e = cudaMemset(*ptr, 0, bytes);
+    if (e != cudaSuccess) {
+        set_error("peer_alloc(%zu): %s", bytes, cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return B200ASR_ERR_CUDA;
+    }
+    return B200ASR_OK;
+}
+
+int b200asr_peer_free(void* ptr) {
+    if (!ptr) return B200ASR_OK;
+    cudaError_t e = cudaFree(ptr);
+    if (e != cudaSuccess) {
+        set_error("peer_free: %s", cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return B200ASR_ERR_CUDA;
+    }
+    return B200ASR_OK;
+}
+
+int b200asr_ipc_export(const void* ptr, unsigned char handle[64]) {
+    B200_REQUIRE(ptr && handle, "ipc_export: null pointer");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, const_cast<void*>(ptr));
+    if (e != cudaSuccess) {
+        set_error("ipc_export: %s", cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return B200ASR_ERR_CUDA;
+    }
+    memcpy(handle, &h, 64);
+    return B200ASR_OK;
+}
+
+int b200asr_ipc_open(const unsigned char handle[64], void** ptr) {
+    B200_REQUIRE(ptr && handle, "ipc_open: null pointer");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    cudaError_t e = cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+        set_error("ipc_open: %s", cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return B200ASR_ERR_CUDA;
+    }
+    return B200ASR_OK;
+}
+
+int b200asr_ipc_close(void* ptr) {
+    if (!ptr) return B200ASR_OK;
+    cudaError_t e = cudaIpcCloseMemHandle(ptr);
+    if (e != cudaSuccess) {
+        set_error("ipc_close: %s", cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return B200ASR_ERR_CUDA;
+    }
+    return B200ASR_OK;
 }
 
 int b200asr_adamw_step(float* p, const float* grad, float* m, float* v, void* shadow_bf16, long long n, float lr, float beta1,

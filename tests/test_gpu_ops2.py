@@ -113,7 +113,8 @@ def test_mha_bf16_fused_vs_composed(fused, B, T, H, klens):
 
 # ----------------------------------------------------------------------------- positional conv
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-@pytest.mark.parametrize("C,groups,k,T", [(128, 2, 19, 50), (1024, 16, 19, 77), (128, 2, 128, 150), (1024, 16, 19, 499), (64, 2, 19, 70)])
+@pytest.mark.parametrize("C,groups,k,T", [(128, 2, 19, 50), (1024, 16, 19, 77), (128, 2, 128, 150), (1024, 16, 19, 499), (64, 2, 19, 70),
+                                       (1024, 16, 128, 499), (1280, 16, 128, 200)])  # wav2vec2/hubert-large, hubert-xlarge (Cg=80)
 def test_posconv_fwd_bwd(dtype, C, groups, k, T):
     g = torch.Generator().manual_seed(5)
     B = 2
