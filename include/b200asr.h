@@ -37,6 +37,7 @@ extern "C" {
 /* activation codes */
 #define B200ASR_ACT_NONE 0
 #define B200ASR_ACT_GELU 1
+#define B200ASR_ACT_GELU_SAVE_GRAD 2 /* GELU, and aux_out receives gelu'(pre-activation) instead of the pre-activation */
 
 const char* b200asr_last_error(void);
 int b200asr_abi_version(void);
@@ -104,6 +105,8 @@ int b200asr_conv0_ln_gelu_fwd(const float* x, const float* w, const float* bias,
  *   B(n, k) = b_kmajor ? B[n*ldb + k] : B[k*ldb + n]
  *   epi(v)  = v*alpha (+ bias[n]) -> (aux_out = that, if given) -> (GELU if act) (* gelu'(aux_in[m,n]) if
  *             mul_gelu_grad) (+ residual[m, n])
+ *   act = B200ASR_ACT_GELU_SAVE_GRAD stores gelu'(v) in aux_out (both come out of one erf evaluation) and
+ *   mul_gelu_grad = 2 multiplies by aux_in as it is: the backward GEMM epilogue then carries no transcendental math.
  * Two batch dims (batch0 fastest) with element strides per operand; batch counts of 1 for a plain GEMM.
  * dtype = storage of A and B (both the same).  BF16 runs on tcgen05 tensor cores (TMA -> smem -> UMMA ->
  * TMEM), F32 runs on FP32 FMA pipes (parity mode; no TF32).  c_dtype = storage of C, residual, aux.
@@ -121,7 +124,7 @@ typedef struct b200asr_gemm_args {
     int lda, ldb, ldc;
     int a_kmajor, b_kmajor;
     int act;            /* B200ASR_ACT_* */
-    int mul_gelu_grad;  /* 0/1 */
+    int mul_gelu_grad;  /* 0; 1: * gelu'(aux_in); 2: * aux_in (already a derivative) */
     float alpha;
     int batch0, batch1;
     long long sa0, sa1, sb0, sb1, sc0, sc1; /* element strides of the batch dims */

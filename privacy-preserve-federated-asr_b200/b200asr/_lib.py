@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200asr.so")
 
 F32, BF16 = 0, 1
-ACT_NONE, ACT_GELU = 0, 1
+ACT_NONE, ACT_GELU, ACT_GELU_SAVE_GRAD = 0, 1, 2
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(

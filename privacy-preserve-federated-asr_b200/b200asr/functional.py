@@ -11,7 +11,7 @@ from typing import List, Optional
 import torch
 
 from . import ops
-from ._lib import ACT_GELU, ACT_NONE
+from ._lib import ACT_GELU, ACT_GELU_SAVE_GRAD, ACT_NONE
 
 
 # ----------------------------------------------------------------------------- weight shadows
@@ -351,7 +351,7 @@ class EncoderLayerFn(torch.autograd.Function):
         attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale)
         s1, _ = ops.linear_fwd(attn, wo, o_b, residual=x)
         x1, _, m1, r1 = ops.layernorm_fwd(s1, ln1_w, ln1_b, eps)
-        g, u = ops.linear_fwd(x1, w1s, b1, act=ACT_GELU, want_preact=True)
+        g, u = ops.linear_fwd(x1, w1s, b1, act=ACT_GELU_SAVE_GRAD)  # u = gelu'(pre-activation), from the same erf evaluation
         s2, _ = ops.linear_fwd(g, w2s, b2, residual=x1)
         y, _, m2, r2 = ops.layernorm_fwd(s2, ln2_w, ln2_b, eps)
         ctx.save_for_backward(x, qkv, attn, lse, s1, m1, r1, x1, u, g, s2, m2, r2, wqkv, wo, w1s, w2s)
@@ -369,7 +369,7 @@ class EncoderLayerFn(torch.autograd.Function):
         wg = any(ctx.needs_input_grad[4:])  # parameter gradients wanted?
         ds2, dln2w, dln2b, db2 = _ln_bwd(dy, s2, ln2_w, ln2_b, m2, r2, wg, in_bias=b2)
         dw2 = _wgrad(w2, wg, ds2, g)
-        du = ops.linear_dgrad(ds2, w2s, gelu_preact=u)            # (ds2 W2) * gelu'(u)
+        du = ops.linear_dgrad(ds2, w2s, gelu_grad=u)              # (ds2 W2) * gelu'(pre-activation)
         db1 = _bgrad(b1, wg, du)
         dw1 = _wgrad(w1, wg, du, x1)
         dx1 = ops.linear_dgrad(du, w1s, residual=ds2)            # + residual path of s2 = x1 + ...
@@ -494,7 +494,7 @@ class EncoderLayerStableFn(torch.autograd.Function):
         attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale)
         s1, _ = ops.linear_fwd(attn, wo, o_b, residual=x)
         n2, _, m2, r2 = ops.layernorm_fwd(s1, ln2_w, ln2_b, eps)
-        g, u = ops.linear_fwd(n2, w1s, b1, act=ACT_GELU, want_preact=True)
+        g, u = ops.linear_fwd(n2, w1s, b1, act=ACT_GELU_SAVE_GRAD)
         y, _ = ops.linear_fwd(g, w2s, b2, residual=s1)
         ctx.save_for_backward(x, m1, r1, n1, qkv, attn, lse, s1, m2, r2, n2, u, g, wqkv, wo, w1s, w2s)
         ctx.params = P
@@ -513,7 +513,7 @@ class EncoderLayerStableFn(torch.autograd.Function):
             dy = dy.contiguous()
         db2 = _bgrad(b2, wg, dy)
         dw2 = _wgrad(w2, wg, dy, g)
-        du = ops.linear_dgrad(dy, w2s, gelu_preact=u)
+        du = ops.linear_dgrad(dy, w2s, gelu_grad=u)
         db1 = _bgrad(b1, wg, du)
         dw1 = _wgrad(w1, wg, du, n2)
         dn2 = ops.linear_dgrad(du, w1s)

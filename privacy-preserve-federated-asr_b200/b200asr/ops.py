@@ -11,7 +11,7 @@ from typing import Optional, Sequence
 import torch
 
 from . import _lib
-from ._lib import ACT_GELU, ACT_NONE, BF16, F32, GemmArgs, check, lib
+from ._lib import ACT_GELU, ACT_GELU_SAVE_GRAD, ACT_NONE, BF16, F32, GemmArgs, check, lib
 
 _DT = {torch.float32: F32, torch.bfloat16: BF16}
 
@@ -319,7 +319,7 @@ def gemm_raw(A, B, Cout, M, N, K, lda, ldb, ldc, a_kmajor=True, b_kmajor=True, b
     g.M, g.N, g.K = M, N, K
     g.lda, g.ldb, g.ldc = lda, ldb, ldc
     g.a_kmajor, g.b_kmajor = int(a_kmajor), int(b_kmajor)
-    g.act, g.mul_gelu_grad, g.alpha = act, int(mul_gelu_grad), float(alpha)
+    g.act, g.mul_gelu_grad, g.alpha = act, int(mul_gelu_grad), float(alpha)  # mul_gelu_grad: 0 | 1 (gelu'(aux_in)) | 2 (aux_in)
     g.batch0, g.batch1 = batch0, batch1
     g.sa0, g.sa1 = sa
     g.sb0, g.sb1 = sb
@@ -338,7 +338,10 @@ def gemm_raw(A, B, Cout, M, N, K, lda, ldb, ldc, a_kmajor=True, b_kmajor=True, b
 
 
 def linear_fwd(x, w, bias=None, act=ACT_NONE, residual=None, want_preact=False, out_dtype=None):
-    """y = act(x @ w.T + bias) (+ residual).  x [M, K], w [N, K] (same dtype).  Returns (y, preact_or_None)."""
+    """y = act(x @ w.T + bias) (+ residual).  x [M, K], w [N, K] (same dtype).  Returns (y, preact_or_None);
+    with act=ACT_GELU_SAVE_GRAD the second tensor holds gelu'(pre-activation) (feed it to linear_dgrad(gelu_grad=))."""
+    if act == ACT_GELU_SAVE_GRAD:
+        want_preact = True
     x = _c(x)
     M, K = x.shape
     N = w.shape[0]
@@ -348,14 +351,15 @@ def linear_fwd(x, w, bias=None, act=ACT_NONE, residual=None, want_preact=False, 
     return y, pre
 
 
-def linear_dgrad(dy, w, residual=None, gelu_preact=None):
-    """dx = dy @ w  (* gelu'(preact)) (+ residual).  dy [M, N], w [N, K] -> [M, K]."""
+def linear_dgrad(dy, w, residual=None, gelu_preact=None, gelu_grad=None):
+    """dx = dy @ w  (* gelu'(preact) | * gelu_grad) (+ residual).  dy [M, N], w [N, K] -> [M, K]."""
     dy = _c(dy)
     M, N = dy.shape
     K = w.shape[1]
     dx = torch.empty(M, K, dtype=dy.dtype, device=dy.device)
-    gemm_raw(dy, w, dx, M, K, N, N, K, K, True, False, residual=residual, aux_in=gelu_preact,
-             mul_gelu_grad=gelu_preact is not None)
+    aux = gelu_grad if gelu_grad is not None else gelu_preact
+    gemm_raw(dy, w, dx, M, K, N, N, K, K, True, False, residual=residual, aux_in=aux,
+             mul_gelu_grad=2 if gelu_grad is not None else int(gelu_preact is not None))
     return dx
 
 

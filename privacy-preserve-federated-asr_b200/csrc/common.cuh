@@ -98,6 +98,56 @@ __device__ __forceinline__ float gelu_grad_fast(float x) {
     return fmaf(x * 0.39894228040143267794f, e, 0.5f * (1.0f + er));
 }
 
+// Two-at-a-time forms on the packed fp32 pipe of sm_100 (FFMA2 / FMUL2 / FADD2: one issue slot for two lanes' worth of
+// work) -- same arithmetic as erf_fast_parts, evaluated for an (x.x, x.y) pair.  The GEMM epilogues are issue-slot bound
+// on their K = 1024 shapes (profiles/r01_gemm_epilogue_ablation.txt), which is what this halves.
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ void erf_fast_parts2(float2 x, float2& erfv, float2& e) {
+    const float2 ax = make_float2(fabsf(x.x), fabsf(x.y));
+    const float2 z = __fmul2_rn(ax, make_float2(0.70710678118654752440f, 0.70710678118654752440f));
+    const float2 den = __ffma2_rn(make_float2(0.3275911f, 0.3275911f), z, make_float2(1.0f, 1.0f));
+    const float2 t = make_float2(rcp_approx(den.x), rcp_approx(den.y));
+    const float2 arg = __fmul2_rn(__fmul2_rn(z, make_float2(-1.4426950408889634f, -1.4426950408889634f)), z);
+    e = make_float2(ex2_approx(arg.x), ex2_approx(arg.y));  // = exp(-x^2 / 2)
+    float2 poly = __ffma2_rn(make_float2(1.061405429f, 1.061405429f), t, make_float2(-1.453152027f, -1.453152027f));
+    poly = __ffma2_rn(poly, t, make_float2(1.421413741f, 1.421413741f));
+    poly = __ffma2_rn(poly, t, make_float2(-0.284496736f, -0.284496736f));
+    poly = __ffma2_rn(poly, t, make_float2(0.254829592f, 0.254829592f));
+    poly = __fmul2_rn(poly, t);
+    const float2 er = __ffma2_rn(make_float2(-poly.x, -poly.y), e, make_float2(1.0f, 1.0f));
+    erfv = make_float2(copysignf(er.x, x.x), copysignf(er.y, x.y));
+}
+__device__ __forceinline__ float2 gelu_fast2(float2 x) {
+    float2 er, e;
+    erf_fast_parts2(x, er, e);
+    const float2 h = __fmul2_rn(x, make_float2(0.5f, 0.5f));
+    return __ffma2_rn(h, er, h);
+}
+// value and derivative from one erf evaluation
+__device__ __forceinline__ void gelu_both_fast2(float2 x, float2& g, float2& gp) {
+    float2 er, e;
+    erf_fast_parts2(x, er, e);
+    const float2 h = __fmul2_rn(x, make_float2(0.5f, 0.5f));
+    g = __ffma2_rn(h, er, h);
+    const float2 cdf = __ffma2_rn(er, make_float2(0.5f, 0.5f), make_float2(0.5f, 0.5f));
+    gp = __ffma2_rn(__fmul2_rn(x, make_float2(0.39894228040143267794f, 0.39894228040143267794f)), e, cdf);
+}
+__device__ __forceinline__ float2 gelu_grad_fast2(float2 x) {
+    float2 er, e;
+    erf_fast_parts2(x, er, e);
+    const float2 cdf = __ffma2_rn(er, make_float2(0.5f, 0.5f), make_float2(0.5f, 0.5f));
+    return __ffma2_rn(__fmul2_rn(x, make_float2(0.39894228040143267794f, 0.39894228040143267794f)), e, cdf);
+}
+
 // storage-type dispatch: bf16 outputs take the MUFU-based approximation (error far below bf16 rounding), fp32
 // (parity mode) keeps the libm erff / expf forms
 template <typename T> __device__ __forceinline__ float gelu_for(float x) {

@@ -94,9 +94,9 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const b200asr_gemm_args 
             const long long idx = (long long)m * a.ldc + n;
             float v = acc[i][j] * a.alpha;
             if (a.bias) v += a.bias[n];
-            if (AO) AO[idx] = from_f<TC>(v);
-            if (a.act == B200ASR_ACT_GELU) v = gelu_erf(v);
-            if (a.mul_gelu_grad) v *= gelu_erf_grad(to_f<TC>(AI[idx]));
+            if (AO) AO[idx] = from_f<TC>(a.act == B200ASR_ACT_GELU_SAVE_GRAD ? gelu_erf_grad(v) : v);
+            if (a.act != B200ASR_ACT_NONE) v = gelu_erf(v);
+            if (a.mul_gelu_grad) v *= (a.mul_gelu_grad == 2) ? to_f<TC>(AI[idx]) : gelu_erf_grad(to_f<TC>(AI[idx]));
             if (R) v += to_f<TC>(R[idx]);
             C[idx] = from_f<TC>(v);
         }

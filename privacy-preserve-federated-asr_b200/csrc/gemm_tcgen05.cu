@@ -4,6 +4,8 @@
 // epilogue (one TMEM lane quarter each).  Either operand may be K-major or MN-major in memory, so that
 // nn.Linear forward (NT), dgrad (NN) and wgrad (TN) all run without materialised transposes.
 #include <cuda.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include <mutex>
 
@@ -28,9 +30,20 @@ constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
 template <int BN, int NCTA = 1> struct Cfg {
     static constexpr int B_STAGE_BYTES = (BN / NCTA) * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-    static constexpr int STAGES = (NCTA == 2) ? (BN == 256 ? 6 : 8) : ((BN == 256) ? 4 : (BN == 128 ? 6 : 8));
+    // Staged epilogue: every epilogue warp owns 8 KB of shared memory -- two 32x32 output chunks (TMA-stored, so the
+    // global writes are full coalesced rows and asynchronous) and two chunks of the second epilogue tensor (the GELU
+    // pre-activation written next to the output, or the residual / gelu' operand TMA-prefetched two chunks ahead).
+    // Measured before this (profiles/r01_gemm_epilogue_ablation.txt): the row-per-thread global accesses cost
+    // 9 us of a 34 us QKV GEMM and 19 us of a 52 us FFN data-gradient GEMM.
+    static constexpr bool EPI_TMA = !(NCTA == 1 && BN == 256);  // 48 KB stages leave no room there
+    static constexpr int EPI_WARP_BYTES = 8192;
+    static constexpr int EPI_BYTES = EPI_TMA ? 8 * EPI_WARP_BYTES : 0;
+    static constexpr int STAGES = (NCTA == 2) ? (BN == 256 ? 5 : 6) : ((BN == 256) ? 4 : (BN == 128 ? 5 : 6));
     static constexpr int TMEM_COLS = (NCTA == 2) ? 512 : ((2 * BN < 32) ? 32 : 2 * BN);  // two accumulator buffers
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int BAR_BYTES = 512;  // full/empty[STAGES], tmem_full/empty[2], tmem slot, epilogue in-barriers[16]
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 /*align slack*/ + BAR_BYTES;
+    static_assert(SMEM_BYTES <= 232448, "shared memory budget");
+    static_assert(8 * (2 * STAGES + 4) + 8 + 16 * 8 <= BAR_BYTES, "barrier area");
 };
 
 struct Params {
@@ -56,6 +69,9 @@ struct Params {
     //      filter tap nb, whose B rows are the activation frames t0 + nb - tap_pad
     int mode, tap_pad, tblocks, num_kb;
     long long bias_sb0;  // bias element stride per batch0 index (grouped conv: channels per group)
+    int epi_tma;         // 1: staged epilogue (TMA store of C [+ second tensor]); 0: direct row-per-thread accesses
+    int x_kind;          // second epilogue tensor of the staged path: 0 none, 1 aux_out (store), 2 residual, 3 aux_in (gelu')
+    int dbg;             // experiment knobs (B200ASR_GEMM_DBG): 1 skip GELU math, 2 skip aux/residual traffic, 4 skip the C store
 };
 
 template <typename TC> __device__ __forceinline__ void store_row_chunk(TC* dst, const float* v, int ncols_valid, bool vec_ok);
@@ -117,7 +133,8 @@ template <> __device__ __forceinline__ void load_row_chunk<__nv_bfloat16>(const 
 
 template <int BN, typename TC, int NCTA>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const Params p) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+               const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_x, const Params p) {
     using C_ = Cfg<BN, NCTA>;
     constexpr int TILE_M = BLOCK_M * NCTA;  // rows of one (pair) tile
     constexpr int BNH = BN / NCTA;          // B rows staged by this CTA
@@ -127,15 +144,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     extern __shared__ uint8_t smem_raw[];
     // 1024-byte alignment: the 128B swizzle pattern is a function of the absolute shared address
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t bars = smem_base + C_::STAGES * C_::STAGE_BYTES;
+    const uint32_t epi_smem = smem_base + C_::STAGES * C_::STAGE_BYTES;
+    const uint32_t bars = epi_smem + C_::EPI_BYTES;
     // barrier layout (8 bytes each): full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2], then tmem ptr
     auto full_bar = [&](int s) { return bars + 8u * s; };
     auto empty_bar = [&](int s) { return bars + 8u * (C_::STAGES + s); };
     auto tfull_bar = [&](int s) { return bars + 8u * (2 * C_::STAGES + s); };
     auto tempty_bar = [&](int s) { return bars + 8u * (2 * C_::STAGES + 2 + s); };
     const uint32_t tmem_slot = bars + 8u * (2 * C_::STAGES + 4);
+    auto in_bar = [&](int ew, int i) { return bars + 8u * (2 * C_::STAGES + 5) + 8u * (2 * ew + i); };
     uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
-    volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(smem_gen + C_::STAGES * C_::STAGE_BYTES + 8 * (2 * C_::STAGES + 4));
+    volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(smem_gen + C_::STAGES * C_::STAGE_BYTES + C_::EPI_BYTES + 8 * (2 * C_::STAGES + 4));
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -150,6 +169,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         for (int s = 0; s < 2; ++s) {
             mbar_init(tfull_bar(s), 1);
             mbar_init(tempty_bar(s), 8 * NCTA);  // one arrival per epilogue warp (of both CTAs of a pair)
+        }
+        for (int s = 0; s < 16; ++s) mbar_init(in_bar(s >> 1, s & 1), 1);
+        if (p.epi_tma) {
+            tma_prefetch_desc(&tma_c);
+            if (p.x_kind) tma_prefetch_desc(&tma_x);
         }
         fence_barrier_init();
     }
@@ -296,69 +320,263 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                             (!p.residual || (reinterpret_cast<uintptr_t>(p.residual) & 15) == 0) &&
                             (!p.aux_out || (reinterpret_cast<uintptr_t>(p.aux_out) & 15) == 0) &&
                             (!p.aux_in || (reinterpret_cast<uintptr_t>(p.aux_in) & 15) == 0);
-        for (long long tile = worker; tile < p.num_tiles; tile += nworkers) {
-            const int z = (int)(tile / tiles_per_batch);
-            const int rem = (int)(tile % tiles_per_batch);
-            const int mb = rem / p.tiles_n, nb = rem % p.tiles_n;
-            const int b0 = z % p.batch0, b1 = z / p.batch0;
-            const int m = mb * TILE_M + (int)rank * BLOCK_M + quarter * 32 + lane;
-            const int n0 = nb * BN;
-            const long long row_off = (long long)b0 * p.sc0 + (long long)b1 * p.sc1 + (long long)m * p.ldc;
-            mbar_wait(tfull_bar(acc), acc_phase);
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+        bool staged = false;
+        if constexpr (C_::EPI_TMA) staged = p.epi_tma != 0;
+        if (staged) {
+            if constexpr (C_::EPI_TMA) {
+                // ---------- staged epilogue: TMEM -> registers -> swizzled shared chunk -> TMA store ----------
+                constexpr int ES = (int)sizeof(TC);
+                constexpr int CHUNK_BYTES = 32 * 32 * ES;          // 2 KB (bf16) / 4 KB (fp32)
+                constexpr int V16 = 32 * ES / 16;                   // 16-byte vectors per chunk row
+                constexpr int SWZ = V16 - 1;                        // swizzle-64B (bf16) / swizzle-128B (fp32) XOR mask
+                constexpr int ROW_SHIFT = (ES == 2) ? 1 : 0;        // 64-byte rows: two rows share a 128-byte line
+                const int ew = warp - 2;
+                const uint32_t my = epi_smem + (uint32_t)ew * C_::EPI_WARP_BYTES;
+                // bf16: x0, x1, out0, out1 (2 KB each); fp32: out0, out1 (4 KB each, no second tensor)
+                const uint32_t xbuf = my, obuf = (ES == 2) ? my + 2 * CHUNK_BYTES : my;
+                uint8_t* my_gen = smem_gen + C_::STAGES * C_::STAGE_BYTES + ew * C_::EPI_WARP_BYTES;
+                uint8_t* xgen = my_gen;
+                uint8_t* ogen = (ES == 2) ? my_gen + 2 * CHUNK_BYTES : my_gen;
+                const int x_kind = (ES == 2) ? p.x_kind : 0;
+                const bool has_in = x_kind >= 2;
+                const int sw = (lane >> ROW_SHIFT) & SWZ;           // this lane's (row's) swizzle term
+                const uint32_t row_off_s = (uint32_t)lane * (32 * ES);
+
+                // work item = (tile, 32-column chunk of this warp's half); coordinates of item `it`
+                auto coords = [&](long long it, int& m0w, int& n, int& b0, int& b1) -> bool {
+                    const long long tile = worker + (it / CHUNKS) * nworkers;
+                    if (tile >= p.num_tiles) return false;
+                    const int cc = (int)(it % CHUNKS);
+                    const int z = (int)(tile / tiles_per_batch);
+                    const int rem = (int)(tile % tiles_per_batch);
+                    const int mb = rem / p.tiles_n, nb = rem % p.tiles_n;
+                    b0 = z % p.batch0; b1 = z / p.batch0;
+                    m0w = mb * TILE_M + (int)rank * BLOCK_M + quarter * 32;
+                    n = nb * BN + (chalf * CHUNKS + cc) * 32;
+                    return n < p.N && m0w < p.M;
+                };
+                auto issue_in = [&](long long it) {
+                    int m0w, n, b0, b1;
+                    if (!coords(it, m0w, n, b0, b1)) return;
+                    if (lane == 0) {
+                        const int i = (int)(it & 1);
+                        mbar_expect_tx(in_bar(ew, i), CHUNK_BYTES);
+                        tma_load_4d(xbuf + i * CHUNK_BYTES, &tma_x, in_bar(ew, i), n, m0w, b0, b1);
+                    }
+                };
+                uint32_t in_phase0 = 0, in_phase1 = 0;
+                if (has_in) { issue_in(0); issue_in(1); }
+                long long item = 0;
+                for (long long tile = worker; tile < p.num_tiles; tile += nworkers) {
+                    mbar_wait(tfull_bar(acc), acc_phase);
+                    tc_fence_after();
+                    const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
 #pragma unroll 1
-            for (int c = chalf * CHUNKS; c < (chalf + 1) * CHUNKS; ++c) {
-                uint32_t r[32];
-                tmem_ld_32x32(taddr + c * 32, r);
-                tmem_ld_wait();
-                const int n = n0 + c * 32;
-                const int nvalid = p.N - n;  // may be <= 0 or > 32
-                if (m < p.M && nvalid > 0) {
-                    float v[32];
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
-                    if (p.bias) {
-                        const float* bp = p.bias + (long long)b0 * p.bias_sb0 + n;
-                        if (nvalid >= 32 && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
+                    for (int cc = 0; cc < CHUNKS; ++cc, ++item) {
+                        int m0w, n, b0, b1;
+                        if (!coords(item, m0w, n, b0, b1)) {  // chunk entirely outside C: nothing staged, nothing waited for
+                            if (has_in) issue_in(item + 2);
+                            continue;
+                        }
+                        const int i = (int)(item & 1);
+                        uint32_t r[32];
+                        tmem_ld_32x32(taddr + (chalf * CHUNKS + cc) * 32, r);
+                        tmem_ld_wait();
+                        if (lane == 0) bulk_wait_group_read<1>();   // the stores that last read buffer i are done with it
+                        __syncwarp();
+                        float2 v2[16];   // the 32 accumulator columns of this lane's row, as pairs for the packed fp32 pipe
+                        float* v = reinterpret_cast<float*>(v2);
+                        const float2 al = make_float2(p.alpha, p.alpha);
+                        const float* bp = p.bias ? p.bias + (long long)b0 * p.bias_sb0 + n : nullptr;
+                        if (bp && p.N - n >= 32 && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
 #pragma unroll
                             for (int j = 0; j < 32; j += 4) {
                                 const float4 bv = __ldg(reinterpret_cast<const float4*>(bp + j));
-                                v[j] += bv.x; v[j + 1] += bv.y; v[j + 2] += bv.z; v[j + 3] += bv.w;
+                                v2[j / 2] = __ffma2_rn(make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])), al, make_float2(bv.x, bv.y));
+                                v2[j / 2 + 1] = __ffma2_rn(make_float2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3])), al, make_float2(bv.z, bv.w));
                             }
                         } else {
 #pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (j < nvalid) v[j] += __ldg(bp + j);
+                            for (int j = 0; j < 32; j += 2)
+                                v2[j / 2] = __fmul2_rn(make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])), al);
+                            if (bp) {
+                                const int nvalid = p.N - n;
+#pragma unroll
+                                for (int j = 0; j < 32; ++j)
+                                    if (j < nvalid) v[j] += __ldg(bp + j);
+                            }
                         }
-                    }
-                    if (AOb) store_row_chunk<TC>(AOb + row_off + n, v, nvalid, vec_ok);
-                    if (p.act == B200ASR_ACT_GELU) {
+                        if constexpr (ES == 2) {
+                            uint8_t* xrow = xgen + i * CHUNK_BYTES + row_off_s;
+                            if (x_kind == 1) {  // second output next to the result: the pre-activation, or gelu'(it)
+                                float2 g2[16];
+                                const float2* src = v2;
+                                if (p.act == B200ASR_ACT_GELU_SAVE_GRAD) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);
-                    }
-                    if (p.mul_gelu_grad) {
-                        float u[32];
-                        load_row_chunk<TC>(AIb + row_off + n, u, nvalid, vec_ok);
+                                    for (int j = 0; j < 16; ++j) {
+                                        float2 gv;
+                                        gelu_both_fast2(v2[j], gv, g2[j]);
+                                        v2[j] = gv;
+                                    }
+                                    src = g2;
+                                }
+                                const float* sf = reinterpret_cast<const float*>(src);
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] *= gelu_grad_fast(u[j]);
-                    }
-                    if (Rb) {
-                        float u[32];
-                        load_row_chunk<TC>(Rb + row_off + n, u, nvalid, vec_ok);
+                                for (int q = 0; q < V16; ++q) {
+                                    uint4 o;
+                                    o.x = bf2_pack(sf[8 * q], sf[8 * q + 1]); o.y = bf2_pack(sf[8 * q + 2], sf[8 * q + 3]);
+                                    o.z = bf2_pack(sf[8 * q + 4], sf[8 * q + 5]); o.w = bf2_pack(sf[8 * q + 6], sf[8 * q + 7]);
+                                    *reinterpret_cast<uint4*>(xrow + ((q ^ sw) << 4)) = o;
+                                }
+                            }
+                            if ((p.act == B200ASR_ACT_GELU || (p.act == B200ASR_ACT_GELU_SAVE_GRAD && x_kind != 1)) && !(p.dbg & 32)) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] += u[j];
+                                for (int j = 0; j < 16; ++j) v2[j] = gelu_fast2(v2[j]);
+                            }
+                            if (has_in) {
+                                mbar_wait(in_bar(ew, i), i ? in_phase1 : in_phase0);
+                                if (i) in_phase1 ^= 1u; else in_phase0 ^= 1u;
+#pragma unroll
+                                for (int q = 0; q < V16; ++q) {
+                                    const uint4 t = *reinterpret_cast<const uint4*>(xrow + ((q ^ sw) << 4));
+                                    float u[8];
+                                    bf2_unpack(t.x, u[0], u[1]); bf2_unpack(t.y, u[2], u[3]);
+                                    bf2_unpack(t.z, u[4], u[5]); bf2_unpack(t.w, u[6], u[7]);
+                                    if (x_kind == 3 && p.mul_gelu_grad == 2) {
+#pragma unroll
+                                        for (int e = 0; e < 8; e += 2)
+                                            v2[4 * q + e / 2] = __fmul2_rn(v2[4 * q + e / 2], make_float2(u[e], u[e + 1]));
+                                    } else if (x_kind == 3 && !(p.dbg & 32)) {
+#pragma unroll
+                                        for (int e = 0; e < 8; e += 2)
+                                            v2[4 * q + e / 2] = __fmul2_rn(v2[4 * q + e / 2], gelu_grad_fast2(make_float2(u[e], u[e + 1])));
+                                    } else {
+#pragma unroll
+                                        for (int e = 0; e < 8; e += 2)
+                                            v2[4 * q + e / 2] = __fadd2_rn(v2[4 * q + e / 2], make_float2(u[e], u[e + 1]));
+                                    }
+                                }
+                            }
+                            uint8_t* orow = ogen + i * CHUNK_BYTES + row_off_s;
+#pragma unroll
+                            for (int q = 0; q < V16; ++q) {
+                                uint4 o;
+                                o.x = bf2_pack(v[8 * q], v[8 * q + 1]); o.y = bf2_pack(v[8 * q + 2], v[8 * q + 3]);
+                                o.z = bf2_pack(v[8 * q + 4], v[8 * q + 5]); o.w = bf2_pack(v[8 * q + 6], v[8 * q + 7]);
+                                *reinterpret_cast<uint4*>(orow + ((q ^ sw) << 4)) = o;
+                            }
+                        } else {
+                            if (p.act != B200ASR_ACT_NONE) {
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) v2[j] = gelu_fast2(v2[j]);
+                            }
+                            uint8_t* orow = ogen + i * CHUNK_BYTES + row_off_s;
+#pragma unroll
+                            for (int q = 0; q < V16; ++q)
+                                *reinterpret_cast<float4*>(orow + ((q ^ sw) << 4)) =
+                                    make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                        }
+                        fence_proxy_async();
+                        __syncwarp();
+                        if (lane == 0 && !(p.dbg & 16)) {
+                            tma_store_4d(&tma_c, obuf + i * CHUNK_BYTES, n, m0w, b0, b1);
+                            if (x_kind == 1 && !(p.dbg & 64)) tma_store_4d(&tma_x, xbuf + i * CHUNK_BYTES, n, m0w, b0, b1);
+                            bulk_commit_group();
+                        }
+                        if (has_in) issue_in(item + 2);   // buffer i has been consumed by every lane (syncwarp above)
                     }
-                    store_row_chunk<TC>(Cb + row_off + n, v, nvalid, vec_ok);
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if constexpr (NCTA == 2) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0));
+                        else mbar_arrive(tempty_bar(acc));
+                    }
+                    if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
                 }
+                if (lane == 0) bulk_wait_group<0>();
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) {
-                if constexpr (NCTA == 2) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0));
-                else mbar_arrive(tempty_bar(acc));
+        } else {
+        for (long long tile = worker; tile < p.num_tiles; tile += nworkers) {
+                const int z = (int)(tile / tiles_per_batch);
+                const int rem = (int)(tile % tiles_per_batch);
+                const int mb = rem / p.tiles_n, nb = rem % p.tiles_n;
+                const int b0 = z % p.batch0, b1 = z / p.batch0;
+                const int m = mb * TILE_M + (int)rank * BLOCK_M + quarter * 32 + lane;
+                const int n0 = nb * BN;
+                const long long row_off = (long long)b0 * p.sc0 + (long long)b1 * p.sc1 + (long long)m * p.ldc;
+                mbar_wait(tfull_bar(acc), acc_phase);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+    #pragma unroll 1
+                for (int c = chalf * CHUNKS; c < (chalf + 1) * CHUNKS; ++c) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(taddr + c * 32, r);
+                    tmem_ld_wait();
+                    const int n = n0 + c * 32;
+                    const int nvalid = p.N - n;  // may be <= 0 or > 32
+                    if (m < p.M && nvalid > 0) {
+                        float v[32];
+    #pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+                        if (p.bias) {
+                            const float* bp = p.bias + (long long)b0 * p.bias_sb0 + n;
+                            if (nvalid >= 32 && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
+    #pragma unroll
+                                for (int j = 0; j < 32; j += 4) {
+                                    const float4 bv = __ldg(reinterpret_cast<const float4*>(bp + j));
+                                    v[j] += bv.x; v[j + 1] += bv.y; v[j + 2] += bv.z; v[j + 3] += bv.w;
+                                }
+                            } else {
+    #pragma unroll
+                                for (int j = 0; j < 32; ++j)
+                                    if (j < nvalid) v[j] += __ldg(bp + j);
+                            }
+                        }
+                        if (AOb && !(p.dbg & 2)) {
+                            if (p.act == B200ASR_ACT_GELU_SAVE_GRAD) {
+                                float gp[32];
+    #pragma unroll
+                                for (int j = 0; j < 32; ++j) gp[j] = gelu_grad_fast(v[j]);
+                                store_row_chunk<TC>(AOb + row_off + n, gp, nvalid, vec_ok);
+                            } else {
+                                store_row_chunk<TC>(AOb + row_off + n, v, nvalid, vec_ok);
+                            }
+                        }
+                        if (p.act != B200ASR_ACT_NONE && !(p.dbg & 1)) {
+    #pragma unroll
+                            for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);
+                        }
+                        if (p.mul_gelu_grad && !(p.dbg & 2)) {
+                            float u[32];
+                            load_row_chunk<TC>(AIb + row_off + n, u, nvalid, vec_ok);
+                            if (p.mul_gelu_grad == 2) {
+    #pragma unroll
+                                for (int j = 0; j < 32; ++j) v[j] *= u[j];
+                            } else if (!(p.dbg & 1)) {
+    #pragma unroll
+                                for (int j = 0; j < 32; ++j) v[j] *= gelu_grad_fast(u[j]);
+                            } else {
+    #pragma unroll
+                                for (int j = 0; j < 32; ++j) v[j] += u[j];
+                            }
+                        }
+                        if (Rb && !(p.dbg & 2)) {
+                            float u[32];
+                            load_row_chunk<TC>(Rb + row_off + n, u, nvalid, vec_ok);
+    #pragma unroll
+                            for (int j = 0; j < 32; ++j) v[j] += u[j];
+                        }
+                        if (!(p.dbg & 4) || v[0] == 123.456f) store_row_chunk<TC>(Cb + row_off + n, v, nvalid, vec_ok);
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    if constexpr (NCTA == 2) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0));
+                    else mbar_arrive(tempty_bar(acc));
+                }
+                if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
             }
-            if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
         }
     }
     tc_fence_before();
@@ -444,7 +662,8 @@ static int make_operand_map(CUtensorMap* map, const void* base, int R, int K, in
 }
 
 template <int BN, typename TC, int NCTA = 1>
-static int launch_kernel(const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, cudaStream_t st) {
+static int launch_kernel(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mx,
+                         const Params& p, cudaStream_t st) {
     using C_ = Cfg<BN, NCTA>;
     static bool attr_set = false;  // per instantiation
     if (!attr_set) {
@@ -459,7 +678,7 @@ static int launch_kernel(const CUtensorMap& ma, const CUtensorMap& mb, const Par
     const long long workers = num_sms() / NCTA;
     const long long grid = (p.num_tiles < workers ? p.num_tiles : workers) * NCTA;
     if constexpr (NCTA == 1) {
-        gemm_tc_kernel<BN, TC, 1><<<(int)grid, NUM_THREADS, C_::SMEM_BYTES, st>>>(ma, mb, p);
+        gemm_tc_kernel<BN, TC, 1><<<(int)grid, NUM_THREADS, C_::SMEM_BYTES, st>>>(ma, mb, mc, mx, p);
     } else {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)grid);
@@ -473,7 +692,7 @@ static int launch_kernel(const CUtensorMap& ma, const CUtensorMap& mb, const Par
         attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
-        cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, TC, NCTA>, ma, mb, p);
+        cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, TC, NCTA>, ma, mb, mc, mx, p);
         if (e != cudaSuccess) {
             set_error("gemm(tcgen05, cta pair): launch failed: %s", cudaGetErrorString(e));
             (void)cudaGetLastError();
@@ -483,9 +702,33 @@ static int launch_kernel(const CUtensorMap& ma, const CUtensorMap& mb, const Par
     return check_launch("gemm_tcgen05");
 }
 
+// 32 x 32 chunk map over an epilogue tensor X[b1][b0][m][n] (strides sc1, sc0, ld; same geometry as C).  Returns false
+// when TMA cannot address it (alignment), in which case the launch falls back to the direct epilogue.
+template <typename TC>
+static bool make_epilogue_map(CUtensorMap* map, const void* base, int M, int N, int ld, int batch0, int batch1, long long s0,
+                              long long s1) {
+    EncodeTiledFn enc = get_encode_fn();
+    constexpr int ES = (int)sizeof(TC);
+    if (!enc || !base || ((uintptr_t)base & 15) || ((long long)ld * ES) % 16) return false;
+    if ((batch0 > 1 && (s0 * ES) % 16) || (batch1 > 1 && (s1 * ES) % 16)) return false;
+    const cuuint64_t dims[4] = {(cuuint64_t)N, (cuuint64_t)M, (cuuint64_t)batch0, (cuuint64_t)batch1};
+    // unit batch dims still need a legal (multiple-of-16-byte) stride
+    const cuuint64_t strides[3] = {(cuuint64_t)ld * ES, (cuuint64_t)(batch0 > 1 ? s0 * ES : 16),
+                                   (cuuint64_t)(batch1 > 1 ? s1 * ES : 16)};
+    const cuuint32_t box[4] = {32, 32, 1, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(map, ES == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4,
+                     const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     ES == 2 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS;
+}
+
 template <int BN, typename TC, int NCTA = 1>
 static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
-    CUtensorMap ma, mb;
+    CUtensorMap ma, mb, mc, mx;
+    memset(&mc, 0, sizeof(mc));
+    memset(&mx, 0, sizeof(mx));
     int rc = make_operand_map(&ma, a.A, a.M, a.K, a.lda, a.a_kmajor, BLOCK_M, a.batch0, a.batch1, a.sa0, a.sa1);
     if (rc) return rc;
     rc = make_operand_map(&mb, a.B, a.N, a.K, a.ldb, a.b_kmajor, BN / NCTA, a.batch0, a.batch1, a.sb0, a.sb1);
@@ -500,7 +743,23 @@ static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
     p.tiles_n = ceil_div(a.N, BN);
     p.num_tiles = (long long)p.tiles_m * p.tiles_n * a.batch0 * a.batch1;
     p.mode = 0; p.tap_pad = 0; p.tblocks = 1; p.num_kb = ceil_div(a.K, BLOCK_K); p.bias_sb0 = 0;
-    return launch_kernel<BN, TC, NCTA>(ma, mb, p, st);
+    static const int dbg = getenv("B200ASR_GEMM_DBG") ? atoi(getenv("B200ASR_GEMM_DBG")) : 0;
+    p.dbg = dbg;
+    // staged epilogue when the kernel variant has the shared memory for it and at most ONE second tensor is involved
+    p.epi_tma = 0; p.x_kind = 0;
+    if (Cfg<BN, NCTA>::EPI_TMA && !(dbg & 8)) {
+        const void* xs[3] = {a.aux_out, a.residual, a.mul_gelu_grad ? a.aux_in : nullptr};
+        int nx = 0, kind = 0;
+        for (int i = 0; i < 3; ++i)
+            if (xs[i]) { ++nx; kind = i + 1; }
+        const bool f32c = sizeof(TC) == 4;
+        if (nx <= 1 && !(f32c && nx) && make_epilogue_map<TC>(&mc, a.C, a.M, a.N, a.ldc, a.batch0, a.batch1, a.sc0, a.sc1) &&
+            (nx == 0 || make_epilogue_map<TC>(&mx, xs[kind - 1], a.M, a.N, a.ldc, a.batch0, a.batch1, a.sc0, a.sc1))) {
+            p.epi_tma = 1;
+            p.x_kind = kind;
+        }
+    }
+    return launch_kernel<BN, TC, NCTA>(ma, mb, mc, mx, p, st);
 }
 
 // ---------------------------------------------------------------- grouped positional conv on the same kernel
@@ -530,7 +789,7 @@ static int posconv_taps_launch(const void* x, const void* w_pack, const float* b
     p.tiles_m = ceil_div(T, BLOCK_M); p.tiles_n = 1;
     p.num_tiles = (long long)p.tiles_m * groups * B;
     p.mode = 1; p.tap_pad = tap_pad; p.tblocks = 1; p.num_kb = k; p.bias_sb0 = 64;
-    return launch_kernel<64, __nv_bfloat16>(ma, mb, p, st);
+    return launch_kernel<64, __nv_bfloat16>(ma, mb, ma, ma, p, st);  // epi_tma = 0: the epilogue maps are unused
 }
 
 // dwt[g*64+o][j][i] = sum_{b,t} dy[b,t,g*64+o] * x[b, t+j-pad, g*64+i]   (fp32, tap-major; permuted by the caller)
@@ -551,7 +810,7 @@ static int posconv_wgrad_launch(const void* x, const void* dy, float* dwt, int B
     p.tiles_m = 1; p.tiles_n = k;
     p.num_tiles = (long long)k * groups;
     p.mode = 2; p.tap_pad = pad; p.tblocks = ceil_div(T, BLOCK_K); p.num_kb = B * p.tblocks; p.bias_sb0 = 0;
-    return launch_kernel<64, float>(ma, mb, p, st);
+    return launch_kernel<64, float>(ma, mb, ma, ma, p, st);  // epi_tma = 0
 }
 
 }  // namespace tc

@@ -212,3 +212,28 @@ def test_gemm_tcgen05_overlapping_rows_conv_view():
     ops.gemm_raw(h.to(DEV), wf, y, Tout, Co, k * Cc, s * Cc, k * Cc, Co, True, True, batch0=1, batch1=B,
                  sa=(0, Tin * Cc), sb=(0, 0), sc=(0, Tout * Co), backend=1)
     assert rel(y, ref) < 1e-2
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("M,N,K", [(300, 264, 192), (3992, 4096, 256), (77, 40, 64)])
+def test_gemm_gelu_save_grad_modes(dtype, M, N, K):
+    """act = GELU_SAVE_GRAD writes gelu'(pre-activation) next to gelu(pre-activation); mul_gelu_grad = 2 multiplies the
+    data-gradient GEMM by that saved derivative (HF:330-343 backward without transcendental math in the epilogue)."""
+    from b200asr._lib import ACT_GELU_SAVE_GRAD
+    g = torch.Generator().manual_seed(M + N)
+    x = torch.randn(M, K, generator=g).to(dtype)
+    w = (torch.randn(N, K, generator=g) / math.sqrt(K)).to(dtype)
+    b = torch.randn(N, generator=g) * 0.3
+    pre = (x.float() @ w.float().t() + b).requires_grad_()
+    ref = F.gelu(pre)
+    (gp_ref,) = torch.autograd.grad(ref.sum(), pre)
+    y, gp = ops.linear_fwd(x.to(DEV), w.to(DEV), b.to(DEV), act=ACT_GELU_SAVE_GRAD)
+    t = 2e-5 if dtype == torch.float32 else 1e-2
+    assert rel(y, ref.detach()) < t
+    assert rel(gp, gp_ref) < t
+    dy = torch.randn(M, N, generator=g).to(dtype)
+    w2 = (torch.randn(N, K, generator=g) / math.sqrt(N)).to(dtype)       # [N, K]: dx[M, K] = dy @ w2
+    gsave = torch.rand(M, K, generator=g).to(dtype)
+    dref = (dy.float() @ w2.float()) * gsave.float()
+    dx = ops.linear_dgrad(dy.to(DEV), w2.to(DEV), gelu_grad=gsave.to(DEV))
+    assert rel(dx, dref) < t
