@@ -251,6 +251,12 @@ int b200asr_dacs_mask_fwd(const void* scores, const void* h, const float* noise_
                           void* lm_masked, void* ad_masked, void* soft_lm, void* soft_ad, void* lm_mask,
                           void* ad_mask, long long M, int d, float tau, float toggle_ratio,
                           unsigned long long seed, unsigned long long offset, int dtype, void* stream);
+/* Same, with the Philox offset advanced by *dev_offset (device u64, may be NULL): the launch can be captured in a CUDA
+ * graph and still draw fresh Gumbel noise on every replay (the caller bumps the counter with a device-side add). */
+int b200asr_dacs_mask_fwd_ctr(const void* scores, const void* h, const float* noise_lm, const float* noise_ad,
+                              void* lm_masked, void* ad_masked, void* soft_lm, void* soft_ad, void* lm_mask, void* ad_mask,
+                              long long M, int d, float tau, float toggle_ratio, unsigned long long seed,
+                              unsigned long long offset, const unsigned long long* dev_offset, int dtype, void* stream);
 /* Straight-through backward: d_scores [M, 4d] from d_lm_masked, d_ad_masked; dh [M, d] or NULL. */
 int b200asr_dacs_mask_bwd(const void* d_lm_masked, const void* d_ad_masked, const void* h, const void* soft_lm,
                           const void* soft_ad, const void* lm_mask, const void* ad_mask, void* d_scores, void* dh,

@@ -76,6 +76,7 @@ SIGNATURES = {
     "b200asr_ctc_fwd_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, sz, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "b200asr_greedy_decode": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]),
     "b200asr_dacs_mask_fwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, f32, u64, u64, i32, vp]),
+    "b200asr_dacs_mask_fwd_ctr": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, f32, u64, u64, vp, i32, vp]),
     "b200asr_dacs_mask_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, f32, i32, vp]),
     "b200asr_mean_time_fwd": (i32, [vp, vp, i32, i32, i32, i32, vp]),
     "b200asr_mean_time_bwd": (i32, [vp, vp, i32, i32, i32, f32, i32, vp]),

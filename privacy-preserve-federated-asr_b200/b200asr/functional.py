@@ -615,9 +615,12 @@ class DacsMaskFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, scores, h, tau, ratio, noise_lm, noise_ad, seed, offset):
+        """offset: host int, or a device int64 counter tensor (graph-replayable draws)."""
         d = h.shape[-1]
         s2, h2 = scores.reshape(-1, 4 * d), h.reshape(-1, d)
-        lm, ad, sl, sa, ml, ma = ops.dacs_mask_fwd(s2, h2, tau, ratio, noise_lm, noise_ad, seed, offset)
+        dev_off = offset if isinstance(offset, torch.Tensor) else None
+        lm, ad, sl, sa, ml, ma = ops.dacs_mask_fwd(s2, h2, tau, ratio, noise_lm, noise_ad, seed,
+                                                   0 if dev_off is not None else offset, dev_offset=dev_off)
         ctx.save_for_backward(h2, sl, sa, ml, ma)
         ctx.cfg = (tau, ratio, scores.shape, h.shape)
         ctx.mark_non_differentiable(ml, ma)

@@ -417,6 +417,9 @@ class DacsData2VecAudioForCTC(_CTCBase):
                 p.requires_grad = False
         self.gumbel_seed = 0
         self._gumbel_calls = 0
+        # Philox offset of the in-kernel Gumbel draws, kept on the device and advanced by a device-side add, so that a
+        # forward captured in a CUDA graph draws fresh noise on every replay (the reference draws fresh noise per call)
+        self.register_buffer("gumbel_counter", torch.zeros(1, dtype=torch.int64), persistent=False)
 
     def _ad_weights(self):
         if self.AD_loss == "recall":
@@ -444,11 +447,12 @@ class DacsData2VecAudioForCTC(_CTCBase):
         stage = self.STAGE
         g_lm, g_ad = gumbel_noise if gumbel_noise is not None else (None, None)
         self._gumbel_calls += 1
+        self.gumbel_counter.add_(1)
         # stages 0/1 only report the masked logits (their loss never touches the toggling branch): no graph needed
         with (contextlib.nullcontext() if stage == 2 else torch.no_grad()):
             score = lin(h, self.arbitrator)
             lm_masked, ad_masked, lm_mask, ad_mask = Fn.DacsMaskFn.apply(
-                score, h, self.GS_TAU, self.TOGGLE_RATIO, g_lm, g_ad, self.gumbel_seed, self._gumbel_calls)
+                score, h, self.GS_TAU, self.TOGGLE_RATIO, g_lm, g_ad, self.gumbel_seed, self.gumbel_counter)
             logits = lin(lm_masked, self.lm_head)  # the returned logits are always the lm-masked ones (:629-631)
         final_loss = None
         if labels is not None:

@@ -464,7 +464,8 @@ def greedy_decode(logits, in_len=None, blank=0):
 
 
 # ----------------------------------------------------------------------------- DACS
-def dacs_mask_fwd(scores, h, tau, toggle_ratio, noise_lm=None, noise_ad=None, seed=0, offset=0, want_masks=True):
+def dacs_mask_fwd(scores, h, tau, toggle_ratio, noise_lm=None, noise_ad=None, seed=0, offset=0, want_masks=True,
+                  dev_offset=None):
     """scores [M, 4d], h [M, d] -> (lm_masked, ad_masked, soft_lm, soft_ad, lm_mask, ad_mask)."""
     scores, h = _c(scores), _c(h)
     M, d = h.shape
@@ -473,9 +474,11 @@ def dacs_mask_fwd(scores, h, tau, toggle_ratio, noise_lm=None, noise_ad=None, se
     if noise_lm is not None:
         assert noise_lm.dtype == torch.float32 and noise_ad.dtype == torch.float32
         noise_lm, noise_ad = _c(noise_lm), _c(noise_ad)
-    check(lib.b200asr_dacs_mask_fwd(_p(scores), _p(h), _p(noise_lm), _p(noise_ad), _p(outs[0]), _p(outs[1]), _p(outs[2]),
-                                    _p(outs[3]), _p(lm_mask), _p(ad_mask), M, d, float(tau), float(toggle_ratio),
-                                    int(seed), int(offset), dt(h), _st()), "dacs_mask_fwd")
+    if dev_offset is not None:
+        assert dev_offset.dtype == torch.int64 and dev_offset.numel() == 1 and dev_offset.is_cuda
+    check(lib.b200asr_dacs_mask_fwd_ctr(_p(scores), _p(h), _p(noise_lm), _p(noise_ad), _p(outs[0]), _p(outs[1]), _p(outs[2]),
+                                        _p(outs[3]), _p(lm_mask), _p(ad_mask), M, d, float(tau), float(toggle_ratio),
+                                        int(seed), int(offset), _p(dev_offset), dt(h), _st()), "dacs_mask_fwd")
     return outs[0], outs[1], outs[2], outs[3], lm_mask, ad_mask
 
 

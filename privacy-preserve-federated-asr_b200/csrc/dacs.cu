@@ -43,8 +43,10 @@ __global__ void __launch_bounds__(256) dacs_mask_fwd_kernel(const T* __restrict_
                                                             T* __restrict__ soft_ad, T* __restrict__ lm_mask,
                                                             T* __restrict__ ad_mask, long long M, int d, float inv_tau,
                                                             float ratio, unsigned long long seed,
-                                                            unsigned long long offset) {
+                                                            unsigned long long offset,
+                                                            const unsigned long long* __restrict__ dev_offset) {
     constexpr int N = Vec16<T>::N;
+    if (dev_offset) offset += *dev_offset;  // per-call counter kept on the device: a captured launch draws fresh noise
     const int vec_per_row = d / N;
     const long long total = M * vec_per_row;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -294,10 +296,23 @@ using namespace b200asr;
 
 extern "C" {
 
+int b200asr_dacs_mask_fwd_ctr(const void* scores, const void* h, const float* noise_lm, const float* noise_ad,
+                              void* lm_masked, void* ad_masked, void* soft_lm, void* soft_ad, void* lm_mask, void* ad_mask,
+                              long long M, int d, float tau, float toggle_ratio, unsigned long long seed,
+                              unsigned long long offset, const unsigned long long* dev_offset, int dtype, void* stream);
+
 int b200asr_dacs_mask_fwd(const void* scores, const void* h, const float* noise_lm, const float* noise_ad, void* lm_masked,
                           void* ad_masked, void* soft_lm, void* soft_ad, void* lm_mask, void* ad_mask, long long M, int d,
                           float tau, float toggle_ratio, unsigned long long seed, unsigned long long offset, int dtype,
                           void* stream) {
+    return b200asr_dacs_mask_fwd_ctr(scores, h, noise_lm, noise_ad, lm_masked, ad_masked, soft_lm, soft_ad, lm_mask, ad_mask, M,
+                                     d, tau, toggle_ratio, seed, offset, nullptr, dtype, stream);
+}
+
+int b200asr_dacs_mask_fwd_ctr(const void* scores, const void* h, const float* noise_lm, const float* noise_ad,
+                              void* lm_masked, void* ad_masked, void* soft_lm, void* soft_ad, void* lm_mask, void* ad_mask,
+                              long long M, int d, float tau, float toggle_ratio, unsigned long long seed,
+                              unsigned long long offset, const unsigned long long* dev_offset, int dtype, void* stream) {
     B200_REQUIRE(scores && h && lm_masked && ad_masked && soft_lm && soft_ad, "dacs_mask_fwd: null pointer");
     B200_REQUIRE((noise_lm == nullptr) == (noise_ad == nullptr), "dacs_mask_fwd: give both noise tensors or neither");
     B200_REQUIRE(M > 0 && d > 0 && d % (dtype == B200ASR_BF16 ? 8 : 4) == 0, "dacs_mask_fwd: bad shape M=%lld d=%d", M, d);
@@ -306,7 +321,7 @@ int b200asr_dacs_mask_fwd(const void* scores, const void* h, const float* noise_
         const long long total = M * (d / Vec16<T>::N);
         dacs_mask_fwd_kernel<T><<<ew_grid(total, 256), 256, 0, as_stream(stream)>>>(
             (const T*)scores, (const T*)h, noise_lm, noise_ad, (T*)lm_masked, (T*)ad_masked, (T*)soft_lm, (T*)soft_ad,
-            (T*)lm_mask, (T*)ad_mask, M, d, 1.0f / tau, toggle_ratio, seed, offset);
+            (T*)lm_mask, (T*)ad_mask, M, d, 1.0f / tau, toggle_ratio, seed, offset, dev_offset);
     });
     return check_launch("dacs_mask_fwd");
 }

@@ -93,8 +93,17 @@ def main():
         step, ntrain = train_step_fn(model, b, extra=("dementia_labels",))
         ms = timed(step, a.steps, a.warmup)
         emit("C3", "DACS stage-2 toggling network (gumbel_softmax GS_TAU=1, GRL AD head, 2 x CTC, CosFace), batch 8 x 10 s, "
-                   "frozen encoder forward + arbitrator update", ms, 80.0, trainable_params=ntrain, frames=frames)
-        del model, step
+                   "frozen encoder forward + arbitrator update", ms, 80.0, trainable_params=ntrain, frames=frames, mode="eager")
+        from b200asr.graph import GraphedTrainStep
+        opt = FusedAdamW(model.named_parameters(), lr=1e-5, weight_decay=0.005, max_grad_norm=1.0)
+        gb = {k: b[k] for k in ("input_values", "attention_mask", "labels", "dementia_labels")}
+        gstep = GraphedTrainStep(model, opt, gb, max_label_len=120)
+        c0 = int(model.gumbel_counter)
+        ms = timed(lambda: gstep(gb), a.steps * 2, a.warmup)
+        assert int(model.gumbel_counter) == c0 + a.steps * 2 + a.warmup  # every replay advanced the noise counter
+        emit("C3", "same, the whole update replayed as one CUDA graph (Gumbel noise offset read from a device counter)",
+             ms, 80.0, trainable_params=ntrain, frames=frames, mode="cuda_graph")
+        del model, step, gstep
 
     for key, cls, name, kw in (
             ("c5w", M.Wav2Vec2ForCTC, "wav2vec2-large-960h-lv60 arch (layer-norm conv stack + bias, stable LayerNorm, weight-normed pos conv k=128)",
