@@ -5,13 +5,19 @@
 
 namespace b200asr {
 
+// FR consecutive frames per warp iteration: every filter tap pair read from shared memory feeds FR accumulators (the
+// one-frame version re-read the whole 20 KB filter bank per frame and was shared-memory-bandwidth bound at 14% of
+// the HBM peak); the arithmetic runs on the packed fp32 pipe (FFMA2), two channels per instruction.
+constexpr int CONV0_FR = 4;
+
 template <typename T, int NP>
 __global__ void __launch_bounds__(256) conv0_ln_gelu_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                             const float* __restrict__ bias,
                                                             const float* __restrict__ ln_w,
                                                             const float* __restrict__ ln_b, T* __restrict__ y,
-                                                            long long frames, int L, int Tout, int C, int k,
+                                                            long long ngroups, int L, int Tout, int C, int k,
                                                             int stride, float eps) {
+    constexpr int FR = CONV0_FR;
     extern __shared__ float smem[];
     float* w_s = smem;              // [k][C]  (transposed so that a warp reads consecutive channels)
     float* bias_s = w_s + k * C;    // [C]
@@ -31,47 +37,62 @@ __global__ void __launch_bounds__(256) conv0_ln_gelu_kernel(const float* __restr
     const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
     const float inv_c = 1.0f / (float)C;
-    for (long long f = warp; f < frames; f += nwarps) {
-        const int b = (int)(f / Tout), t = (int)(f % Tout);
-        const float* xp = x + (long long)b * L + (long long)t * stride;
-        const float xv = (lane < k) ? __ldg(xp + lane) : 0.f;
-        float acc[NP][2];
+    const int gpu_ = (Tout + FR - 1) / FR;  // frame groups per utterance
+    const int span = (FR - 1) * stride + k; // waveform samples one group touches (<= 32, checked by the host)
+    for (long long gi = warp; gi < ngroups; gi += nwarps) {
+        const int b = (int)(gi / gpu_), t0 = (int)(gi % gpu_) * FR;
+        const long long xo = (long long)b * L + (long long)t0 * stride;
+        const float xv = (lane < span && xo + lane < (long long)(b + 1) * L) ? __ldg(x + xo + lane) : 0.f;
+        float2 acc[FR][NP];
 #pragma unroll
         for (int i = 0; i < NP; ++i) {
             const float2 bb = *reinterpret_cast<const float2*>(bias_s + 2 * lane + 64 * i);
-            acc[i][0] = bb.x;
-            acc[i][1] = bb.y;
+#pragma unroll
+            for (int f = 0; f < FR; ++f) acc[f][i] = bb;
         }
         for (int j = 0; j < k; ++j) {
-            const float xj = __shfl_sync(0xffffffffu, xv, j);
+            float2 xf[FR];
+#pragma unroll
+            for (int f = 0; f < FR; ++f) {
+                const float xj = __shfl_sync(0xffffffffu, xv, f * stride + j);
+                xf[f] = make_float2(xj, xj);
+            }
 #pragma unroll
             for (int i = 0; i < NP; ++i) {
                 const float2 ww = *reinterpret_cast<const float2*>(w_s + j * C + 2 * lane + 64 * i);
-                acc[i][0] = fmaf(ww.x, xj, acc[i][0]);
-                acc[i][1] = fmaf(ww.y, xj, acc[i][1]);
+#pragma unroll
+                for (int f = 0; f < FR; ++f) acc[f][i] = __ffma2_rn(ww, xf[f], acc[f][i]);
             }
         }
-        float sum = 0.f;
 #pragma unroll
-        for (int i = 0; i < NP; ++i) sum += acc[i][0] + acc[i][1];
-        const float mean = warp_sum(sum) * inv_c;
-        float sq = 0.f;
+        for (int f = 0; f < FR; ++f) {
+            const int t = t0 + f;
+            float2 s2 = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int i = 0; i < NP; ++i) {
-            const float d0 = acc[i][0] - mean, d1 = acc[i][1] - mean;
-            sq += d0 * d0 + d1 * d1;
-        }
-        const float rstd = rsqrtf(warp_sum(sq) * inv_c + eps);
-        T* yp = y + f * C;
+            for (int i = 0; i < NP; ++i) s2 = __fadd2_rn(s2, acc[f][i]);
+            const float mean = warp_sum(s2.x + s2.y) * inv_c;
+            const float2 nm = make_float2(-mean, -mean);
+            float2 q2 = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int i = 0; i < NP; ++i) {
-            const int c = 2 * lane + 64 * i;
-            const float o0 = gelu_for<T>((acc[i][0] - mean) * rstd * lnw_s[c] + lnb_s[c]);
-            const float o1 = gelu_for<T>((acc[i][1] - mean) * rstd * lnw_s[c + 1] + lnb_s[c + 1]);
-            if constexpr (sizeof(T) == 2) {
-                *reinterpret_cast<uint32_t*>(yp + c) = bf2_pack(o0, o1);
-            } else {
-                *reinterpret_cast<float2*>(yp + c) = make_float2(o0, o1);
+            for (int i = 0; i < NP; ++i) {
+                acc[f][i] = __fadd2_rn(acc[f][i], nm);
+                q2 = __ffma2_rn(acc[f][i], acc[f][i], q2);
+            }
+            const float rstd = rsqrtf(warp_sum(q2.x + q2.y) * inv_c + eps);
+            if (t >= Tout) continue;  // warp-uniform
+            const float2 r2 = make_float2(rstd, rstd);
+            T* yp = y + ((long long)b * Tout + t) * C;
+#pragma unroll
+            for (int i = 0; i < NP; ++i) {
+                const int c = 2 * lane + 64 * i;
+                const float2 gw = __fmul2_rn(*reinterpret_cast<const float2*>(lnw_s + c), r2);
+                float2 o = __ffma2_rn(acc[f][i], gw, *reinterpret_cast<const float2*>(lnb_s + c));
+                if constexpr (sizeof(T) == 2) {
+                    o = gelu_fast2(o);
+                    *reinterpret_cast<uint32_t*>(yp + c) = bf2_pack(o.x, o.y);
+                } else {
+                    *reinterpret_cast<float2*>(yp + c) = make_float2(gelu_erf(o.x), gelu_erf(o.y));
+                }
             }
         }
     }
@@ -88,7 +109,9 @@ extern "C" int b200asr_conv0_ln_gelu_fwd(const float* x, const float* w, const f
     B200_REQUIRE(B > 0 && L >= k && k >= 1 && k <= 32 && stride >= 1, "conv0: bad shape B=%d L=%d k=%d", B, L, k);
     B200_REQUIRE(C % 64 == 0 && C <= 1024, "conv0: C=%d must be a multiple of 64 and <= 1024", C);
     const int Tout = (L - k) / stride + 1;
-    const long long frames = (long long)B * Tout;
+    B200_REQUIRE((CONV0_FR - 1) * stride + k <= 32, "conv0: (FR-1)*stride + k = %d exceeds one warp of samples",
+                 (CONV0_FR - 1) * stride + k);
+    const long long frames = (long long)B * ((Tout + CONV0_FR - 1) / CONV0_FR);  // frame groups
     const size_t smem = (size_t)(k * C + 3 * C) * sizeof(float);
     const int np = C / 64;
     long long want = (frames + 7) / 8;

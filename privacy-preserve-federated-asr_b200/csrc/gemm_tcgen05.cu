@@ -186,6 +186,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     if constexpr (NCTA == 2) cluster_sync_all();  // the peer's barriers are initialised before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_gen;
+    // Programmatic dependent launch: everything above (barrier init, TMEM allocation, descriptor prefetch) may overlap the
+    // tail of the kernel this one depends on; nothing below may touch global memory before that kernel has completed.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 
     const int num_kb = p.num_kb;
     const long long tiles_per_batch = (long long)p.tiles_m * p.tiles_n;
@@ -677,27 +681,33 @@ static int launch_kernel(const CUtensorMap& ma, const CUtensorMap& mb, const CUt
     }
     const long long workers = num_sms() / NCTA;
     const long long grid = (p.num_tiles < workers ? p.num_tiles : workers) * NCTA;
-    if constexpr (NCTA == 1) {
-        gemm_tc_kernel<BN, TC, 1><<<(int)grid, NUM_THREADS, C_::SMEM_BYTES, st>>>(ma, mb, mc, mx, p);
-    } else {
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)grid);
-        cfg.blockDim = dim3(NUM_THREADS);
-        cfg.dynamicSmemBytes = C_::SMEM_BYTES;
-        cfg.stream = st;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = NCTA;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, TC, NCTA>, ma, mb, mc, mx, p);
-        if (e != cudaSuccess) {
-            set_error("gemm(tcgen05, cta pair): launch failed: %s", cudaGetErrorString(e));
-            (void)cudaGetLastError();
-            return B200ASR_ERR_CUDA;
-        }
+    static const int use_pdl = getenv("B200ASR_PDL") ? atoi(getenv("B200ASR_PDL")) : 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = C_::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (NCTA > 1) {
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = NCTA;
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = 1;
+        ++na;
+    }
+    if (use_pdl) {  // the kernel's prologue may start while its predecessor on the stream drains (griddepcontrol.wait inside)
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, TC, NCTA>, ma, mb, mc, mx, p);
+    if (e != cudaSuccess) {
+        set_error("gemm(tcgen05): launch failed: %s", cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return B200ASR_ERR_CUDA;
     }
     return check_launch("gemm_tcgen05");
 }

@@ -143,23 +143,42 @@ __global__ void __launch_bounds__(512, 1) ln_bwd_kernel(const T* __restrict__ dy
     }
     const int ngroups = gridDim.x * G;
     int row = blockIdx.x * G + g;
-    Vec16<T> a_nxt, g_nxt;
-    a_nxt.raw = make_uint4(0, 0, 0, 0);
-    g_nxt.raw = make_uint4(0, 0, 0, 0);
-    if (row < rows && active) {
-        a_nxt.load(s + (long long)row * cols + c0);
-        g_nxt.load(dy + (long long)row * cols + c0);
+    // PF rows of this group in flight (operands + row statistics): with one block per SM the HBM pipe needs ~45 KB
+    // outstanding per SM; one row ahead (16 KB per block) left the kernel latency-bound at ~20% of the HBM peak.
+    constexpr int PF = 3;
+    Vec16<T> a_q[PF], g_q[PF];
+    float m_q[PF], r_q[PF];
+#pragma unroll
+    for (int d = 0; d < PF; ++d) {
+        a_q[d].raw = make_uint4(0, 0, 0, 0);
+        g_q[d].raw = make_uint4(0, 0, 0, 0);
+        m_q[d] = 0.f; r_q[d] = 0.f;
+        const int r = row + d * ngroups;
+        if (r < rows) {
+            m_q[d] = __ldg(mean_in + r);
+            r_q[d] = __ldg(rstd_in + r);
+            if (active) {
+                a_q[d].load(s + (long long)r * cols + c0);
+                g_q[d].load(dy + (long long)r * cols + c0);
+            }
+        }
     }
     int parity = 0;
     for (; row < rows; row += ngroups, parity ^= 1) {
         const long long base = (long long)row * cols + c0;
-        Vec16<T> a = a_nxt, gg = g_nxt;
-        const int nrow = row + ngroups;
-        if (nrow < rows && active) {
-            a_nxt.load(s + (long long)nrow * cols + c0);
-            g_nxt.load(dy + (long long)nrow * cols + c0);
+        Vec16<T> a = a_q[0], gg = g_q[0];
+        const float mean = m_q[0], rstd = r_q[0];
+#pragma unroll
+        for (int d = 0; d + 1 < PF; ++d) { a_q[d] = a_q[d + 1]; g_q[d] = g_q[d + 1]; m_q[d] = m_q[d + 1]; r_q[d] = r_q[d + 1]; }
+        const int nrow = row + PF * ngroups;
+        if (nrow < rows) {
+            m_q[PF - 1] = __ldg(mean_in + nrow);
+            r_q[PF - 1] = __ldg(rstd_in + nrow);
+            if (active) {
+                a_q[PF - 1].load(s + (long long)nrow * cols + c0);
+                g_q[PF - 1].load(dy + (long long)nrow * cols + c0);
+            }
         }
-        const float mean = mean_in[row], rstd = rstd_in[row];
         float xh[N], dz[N];
         a.unpack(xh);
         gg.unpack(dz);

@@ -19,3 +19,9 @@ for _ in range(4):
     ops.layernorm_bwd(dy, x, w, b, mean, rstd, dw_out=dw, db_out=db, dxsum_out=dxs)
 torch.cuda.synchronize()
 print("ok")
+wav = torch.randn(8, 160000, device="cuda")
+cw, lw, lb = torch.randn(512, 1, 10, device="cuda") * 0.4, torch.ones(512, device="cuda"), torch.zeros(512, device="cuda")
+for _ in range(3):
+    ops.conv0_ln_gelu(wav, cw, None, lw, lb, 5, 1e-5, bf)
+torch.cuda.synchronize()
+print("ok2")
