@@ -54,6 +54,7 @@ struct FwdParams {
 __global__ void __launch_bounds__(F_THREADS, 2)
 mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                   const __grid_constant__ CUtensorMap map_v, const FwdParams p) {
+    pdl_enter();  // launched with programmatic stream serialization: wait for the producers before touching global memory
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
@@ -285,6 +286,7 @@ __global__ void __launch_bounds__(B_THREADS, 1)
 mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
                   const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_do,
                   const BwdParams p) {
+    pdl_enter();  // launched with programmatic stream serialization: wait for the producers before touching global memory
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
@@ -524,6 +526,7 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
 __global__ void __launch_bounds__(256) mha_bwd_dsum_kernel(const __nv_bfloat16* __restrict__ o,
                                                            const __nv_bfloat16* __restrict__ dout,
                                                            float* __restrict__ dsum, int B, int T, int H) {
+    pdl_enter();  // launched with programmatic stream serialization: wait for the producers before touching global memory
     const int lane = threadIdx.x & 31;
     const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
@@ -592,7 +595,7 @@ int mha_fwd_tc_launch(const void* qkv, void* out, float* lse, const int* klen, i
     p.out = (__nv_bfloat16*)out; p.lse = lse; p.klen = klen; p.B = B; p.T = T; p.H = H;
     p.scale_log2 = scale * LOG2E;
     dim3 grid(ceil_div(T, FQ), H, B);
-    mha_fwd_tc_kernel<<<grid, F_THREADS, F_SMEM, st>>>(mq, mk, mv, p);
+    launch_pdl(mha_fwd_tc_kernel, grid, dim3(F_THREADS), (size_t)F_SMEM, st, mq, mk, mv, p);
     return check_launch("mha_fwd_tcgen05");
 }
 
@@ -613,7 +616,7 @@ int mha_bwd_tc_launch(const void* qkv, const void* out, const void* dout, const 
         long long frames = (long long)B * T;
         long long g = (frames + 7) / 8;
         if (g > (long long)num_sms() * 8) g = (long long)num_sms() * 8;
-        mha_bwd_dsum_kernel<<<(int)g, 256, 0, st>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, dsum, B, T, H);
+        launch_pdl(mha_bwd_dsum_kernel, dim3((unsigned)g), dim3(256), 0, st, (const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, dsum, B, T, H);
         int rc = check_launch("mha_bwd_dsum");
         if (rc) return rc;
     }
@@ -645,7 +648,7 @@ int mha_bwd_tc_launch(const void* qkv, const void* out, const void* dout, const 
         set_error("mha_bwd(tcgen05): T=%d too long for the staged softmax statistics", T);
         return B200ASR_ERR_UNSUPPORTED;
     }
-    mha_bwd_tc_kernel<<<grid, B_THREADS, smem, st>>>(mk, mv, mq, mdo, p);
+    launch_pdl(mha_bwd_tc_kernel, grid, dim3(B_THREADS), smem, st, mk, mv, mq, mdo, p);
     rc = check_launch("mha_bwd_tcgen05");
     if (rc) return rc;
     // dQ[q, n] = sum_key dS^T[key, q] K[key, n]   (dS already carries the softmax scale)

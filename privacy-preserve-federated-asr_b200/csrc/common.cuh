@@ -192,6 +192,32 @@ __device__ __forceinline__ float block_max(float v, float* red) {
     return r;
 }
 
+// ---- programmatic dependent launch ------------------------------------------------------------------------------
+// A kernel launched through launch_pdl may be scheduled while its predecessor on the stream is still draining (its
+// launch latency and prologue overlap the predecessor's tail).  Such a kernel MUST call pdl_wait() before its first
+// access to global memory written by earlier work; pdl_trigger() lets ITS dependents be scheduled early in turn.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() { pdl_trigger(); pdl_wait(); }
+
+bool pdl_enabled();  // B200ASR_PDL=0 disables (A/B measurements)
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                     Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 #define B200_DISPATCH_DTYPE(dtype, ...)                                        \
     do {                                                                       \
         if ((dtype) == B200ASR_F32) { using T = float; __VA_ARGS__ }           \

@@ -29,6 +29,7 @@ __global__ void __launch_bounds__(128) ln_fwd_kernel(const T* __restrict__ x, co
                                                      float* __restrict__ mean_out, float* __restrict__ rstd_out,
                                                      int rows, int cols, float eps, int act) {
     constexpr int N = Vec16<T>::N;
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -123,6 +124,7 @@ __global__ void __launch_bounds__(512, 1) ln_bwd_kernel(const T* __restrict__ dy
                                                         float* __restrict__ partial, int rows, int cols, int act, int GS,
                                                         int G) {
     constexpr int N = Vec16<T>::N;
+    pdl_enter();
     extern __shared__ float sm[];
     float* sacc = sm;                 // [3][cols] block sums (when partial != nullptr)
     float* xch = sm + 3 * cols;       // [2][G][16][2] per-warp row statistics, double buffered by row parity
@@ -256,6 +258,7 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __res
                                                               float* __restrict__ out1, float* __restrict__ out2,
                                                               int nparts, int cols, int ncols_total, int stride) {
     __shared__ float red[8][33];
+    pdl_enter();
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + lane;
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
@@ -285,6 +288,7 @@ template <typename T>
 __global__ void colsum_partial_kernel(const T* __restrict__ x, float* __restrict__ partial, int rows, int cols,
                                       int ld, int rows_per_chunk) {
     // thread = one column; blockIdx.y = row chunk.  Warps read 32 consecutive columns: coalesced.
+    pdl_enter();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= cols) return;
     const int r0 = blockIdx.y * rows_per_chunk;
@@ -308,6 +312,7 @@ __global__ void __launch_bounds__(256) colsum_partial_vec_kernel(const T* __rest
                                                                  int rows, int cols, int ld, int rows_per_chunk) {
     constexpr int N = Vec16<T>::N;
     __shared__ float red[8][32][N + 1];
+    pdl_enter();
     const int cv = threadIdx.x & 31, rl = threadIdx.x >> 5;
     const int c = (blockIdx.x * 32 + cv) * N;
     const int r0 = blockIdx.y * rows_per_chunk;
@@ -361,8 +366,8 @@ static int launch_ln_fwd(const void* x, const void* res, const float* w, const f
     const int cap = num_sms() * 16;
     if (grid > cap) grid = cap;
 #define LN_FWD_CASE(NVV)                                                                                      \
-    ln_fwd_kernel<T, NVV><<<grid, 128, 0, st>>>((const T*)x, (const T*)res, w, b, (T*)y, (T*)sum_out, mean,   \
-                                                 rstd, rows, cols, eps, act)
+    launch_pdl(ln_fwd_kernel<T, NVV>, dim3(grid), dim3(128), 0, st, (const T*)x, (const T*)res, w, b, (T*)y,  \
+               (T*)sum_out, mean, rstd, rows, cols, eps, act)
     if (nv <= 1) LN_FWD_CASE(1);
     else if (nv <= 2) LN_FWD_CASE(2);
     else if (nv <= 4) LN_FWD_CASE(4);
@@ -387,11 +392,11 @@ static int launch_ln_bwd(const void* dy, const void* s, const float* w, const fl
     if (partial) grid = LN_BWD_BLOCKS;  // finalize sums exactly LN_BWD_BLOCKS partials
     const size_t smem = ((size_t)3 * cols + 2 * 8 * 16 * 2) * sizeof(float);
     if (colsum)
-        ln_bwd_kernel<T, true><<<grid, G * GS, smem, st>>>((const T*)dy, (const T*)s, w, b, mean, rstd, (const T*)dres, (T*)dx,
-                                                           partial, rows, cols, act, GS, G);
+        launch_pdl(ln_bwd_kernel<T, true>, dim3(grid), dim3(G * GS), smem, st, (const T*)dy, (const T*)s, w, b, mean, rstd,
+                   (const T*)dres, (T*)dx, partial, rows, cols, act, GS, G);
     else
-        ln_bwd_kernel<T, false><<<grid, G * GS, smem, st>>>((const T*)dy, (const T*)s, w, b, mean, rstd, (const T*)dres, (T*)dx,
-                                                            partial, rows, cols, act, GS, G);
+        launch_pdl(ln_bwd_kernel<T, false>, dim3(grid), dim3(G * GS), smem, st, (const T*)dy, (const T*)s, w, b, mean, rstd,
+                   (const T*)dres, (T*)dx, partial, rows, cols, act, GS, G);
     return check_launch("layernorm_bwd");
 }
 
@@ -441,8 +446,8 @@ int b200asr_layernorm_bwd(const void* dy, const void* s, const float* w, const f
     if (rc != B200ASR_OK) return rc;
     if (partial) {
         const int total = dx_colsum ? 3 * cols : 2 * cols;
-        reduce_partials_kernel<<<ceil_div(total, 32), 256, 0, as_stream(stream)>>>(partial, dw, db, dx_colsum, LN_BWD_BLOCKS,
-                                                                                   cols, total, 3 * cols);
+        launch_pdl(reduce_partials_kernel, dim3(ceil_div(total, 32)), dim3(256), 0, as_stream(stream), (const float*)partial, dw,
+                   db, dx_colsum, (int)LN_BWD_BLOCKS, cols, total, 3 * cols);
         return check_launch("layernorm_bwd_reduce");
     }
     return B200ASR_OK;
@@ -467,7 +472,7 @@ int b200asr_colsum(const void* x, float* out, void* workspace, size_t workspace_
         nchunks = ceil_div(rows, rpc);
         dim3 grid(gx, nchunks);
         B200_DISPATCH_DTYPE(dtype, {
-            colsum_partial_vec_kernel<T><<<grid, 256, 0, as_stream(stream)>>>((const T*)x, (float*)workspace, rows, cols, ld, rpc);
+            launch_pdl(colsum_partial_vec_kernel<T>, grid, dim3(256), 0, as_stream(stream), (const T*)x, (float*)workspace, rows, cols, ld, rpc);
         });
     } else {
         const int chunks = rows < COLSUM_CHUNKS ? rows : COLSUM_CHUNKS;
@@ -475,13 +480,13 @@ int b200asr_colsum(const void* x, float* out, void* workspace, size_t workspace_
         nchunks = ceil_div(rows, rpc);
         dim3 grid(ceil_div(cols, 128), nchunks);
         B200_DISPATCH_DTYPE(dtype, {
-            colsum_partial_kernel<T><<<grid, 128, 0, as_stream(stream)>>>((const T*)x, (float*)workspace, rows, cols, ld, rpc);
+            launch_pdl(colsum_partial_kernel<T>, grid, dim3(128), 0, as_stream(stream), (const T*)x, (float*)workspace, rows, cols, ld, rpc);
         });
     }
     int rc = check_launch("colsum_partial");
     if (rc != B200ASR_OK) return rc;
-    reduce_partials_kernel<<<ceil_div(cols, 32), 256, 0, as_stream(stream)>>>((const float*)workspace, out, nullptr, nullptr,
-                                                                              nchunks, cols, cols, cols);
+    launch_pdl(reduce_partials_kernel, dim3(ceil_div(cols, 32)), dim3(256), 0, as_stream(stream), (const float*)workspace, out,
+               (float*)nullptr, (float*)nullptr, nchunks, cols, cols, cols);
     return check_launch("colsum_reduce");
 }
 

@@ -1,5 +1,6 @@
 // Error plumbing + small elementwise helpers of the C ABI.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 #include <atomic>
 
@@ -25,6 +26,11 @@ int check_launch(const char* what) {
         return B200ASR_ERR_CUDA;
     }
     return B200ASR_OK;
+}
+
+bool pdl_enabled() {
+    static const bool on = !(getenv("B200ASR_PDL") && atoi(getenv("B200ASR_PDL")) == 0);
+    return on;
 }
 
 int num_sms() {

@@ -143,7 +143,8 @@ def _gemm_case(backend, dtype, M, N, K, a_k, b_k, epi, c_dtype=None, batch=(1, 1
                  sa=((M if a_k else Mp) * K, b0 * (M if a_k else Mp) * K),
                  sb=((N if b_k else Np) * K, b0 * (N if b_k else Np) * K), sc=(M * N, b0 * M * N), backend=backend)
     torch.cuda.synchronize()
-    t = 3e-5 if (dtype == torch.float32 and c_dtype == torch.float32) else (1e-2 if c_dtype == torch.bfloat16 else 2e-5)
+    # fp32: 1e-4 (BASELINE asks for 1e-3); the CPU reference's own summation order varies between host CPUs by a few 1e-5
+    t = 1e-4 if (dtype == torch.float32 and c_dtype == torch.float32) else (1e-2 if c_dtype == torch.bfloat16 else 2e-5)
     assert rel(Cd, ref) < t, (rel(Cd, ref), M, N, K, a_k, b_k, epi)
     if aux_out is not None:
         assert rel(aux_out, pre) < t

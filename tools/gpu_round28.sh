@@ -1,7 +1,7 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_kernels.py -q -x -k "gemm or linear" > gpurun_out/t_gemm.log 2>&1; echo "gemm tests rc=$?"; tail -n 3 gpurun_out/t_gemm.log | cut -c1-200
-for pdl in 0 1; do
+timeout 900 python -m pytest tests -q -m gpu > gpurun_out/t_all.log 2>&1; echo "all tests rc=$?"; tail -n 3 gpurun_out/t_all.log | cut -c1-200
+for pdl in 1; do
 B200ASR_PDL=$pdl timeout 600 python bench.py --no-cpu-baseline > gpurun_out/bench28_$pdl.json 2> gpurun_out/bench28_$pdl.err; echo "bench pdl=$pdl rc=$?"; tail -n 3 gpurun_out/bench28_$pdl.err
 python - <<PY
 import json
