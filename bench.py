@@ -178,7 +178,7 @@ def run_b200(args):
     model.freeze_feature_encoder()
     model.validate_labels = False  # the reference's labels.max() check costs a host sync per step; inputs are synthetic
     model.to(dev).train()
-    use_peer = world > 1 and args.fedavg == "peer"
+    use_peer = world > 1 and args.fedavg in ("peer", "auto")
     opt = FusedAdamW(model.named_parameters(), lr=1e-5, weight_decay=0.005, max_grad_norm=1.0, warmup_steps=1000,
                      peer=use_peer)
     peer_agg = PeerFedAvg([g["fp"] for g in opt.groups]) if use_peer else None
@@ -210,11 +210,13 @@ def run_b200(args):
             fedavg_allreduce(g["fp"].flat)
             g["fp"].mark_updated()
 
+    chosen = {"impl": "peer" if use_peer else "nccl"}
+
     def fedavg():
         if world > 1:
-            if peer_agg is not None:   # fused peer-memory kernel: scale + reduce-scatter + all-gather over NVLink
+            if chosen["impl"] == "peer":   # fused peer-memory kernel: scale + reduce-scatter + all-gather over NVLink
                 peer_agg()
-            else:                      # our scale kernel + NCCL all-reduce
+            else:                          # our scale kernel + NCCL all-reduce (NVLS in-switch reduction at 8 GPUs)
                 fedavg_nccl()
 
     def barrier():
@@ -251,9 +253,30 @@ def run_b200(args):
             dist.all_reduce(agg_ms, op=dist.ReduceOp.MAX)
         return float(ms) / nsteps, float(agg_ms), last
 
+    def time_alone(fn, iters=5):
+        barrier()
+        fn(); barrier()
+        o0, o1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        o0.record()
+        for _ in range(iters):
+            fn()
+        o1.record()
+        barrier()
+        t = torch.tensor([o0.elapsed_time(o1) / iters], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+
     for i in range(args.warmup):
         local_step(resident[i % len(resident)])
         fedavg()
+    agg_alone = {}
+    if world > 1:  # both aggregation paths timed alone on the real buffers (max over ranks: every rank sees the same numbers)
+        agg_alone["nccl_allreduce_ms"] = time_alone(fedavg_nccl)
+        if peer_agg is not None:
+            agg_alone["peer_kernel_ms"] = time_alone(peer_agg)
+            peer_agg.check()
+            if args.fedavg == "auto":
+                chosen["impl"] = "peer" if agg_alone["peer_kernel_ms"] <= agg_alone["nccl_allreduce_ms"] else "nccl"
     clocks = ClockSampler(local_rank) if rank == 0 else None
     n0 = _lib.launch_count()
     ms_step, agg_ms, _ = timed(args.steps, e2e=False)
@@ -264,25 +287,6 @@ def run_b200(args):
     ms_e2e, _, last_loss = timed(args.steps, e2e=True)
 
     # ---- the other FedAvg implementation, timed alone on identical buffers (every rank holds the same average by now)
-    agg_alone = {}
-    if world > 1:
-        def time_alone(fn, iters=5):
-            barrier()
-            fn(); barrier()
-            o0, o1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            o0.record()
-            for _ in range(iters):
-                fn()
-            o1.record()
-            barrier()
-            t = torch.tensor([o0.elapsed_time(o1) / iters], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            return float(t)
-        agg_alone["nccl_allreduce_ms"] = time_alone(fedavg_nccl)
-        if peer_agg is not None:
-            agg_alone["peer_kernel_ms"] = time_alone(peer_agg)
-            peer_agg.check()
-
     # ---- host enqueue time of one step (no synchronisation inside: pure Python + launch cost; the GPU queue holds a step)
     torch.cuda.synchronize()
     h0 = time.perf_counter()
@@ -333,8 +337,9 @@ def run_b200(args):
             "config": {"workload": WORKLOAD, "global_batch": BATCH * world, "audio_s_per_step": audio_s,
                        "clients": world, "trainable_params": n_train, "frames_per_utt": frames,
                        "l2_policy": "inputs+weights+saved activations per step (>3 GB) exceed the 126 MB L2; no flush",
+                       "fedavg_impl": chosen["impl"] if world > 1 else None,
                        "fedavg": (("uniform FedAvg of all trainable params after every local step: fused peer-memory kernel "
-                                   "(scale + reduce-scatter + all-gather over NVLink, no NCCL on the data path)") if use_peer else
+                                   "(scale + reduce-scatter + all-gather over NVLink, no NCCL on the data path)") if chosen["impl"] == "peer" else
                                   "uniform FedAvg of all trainable params after every local step (scale kernel + NCCL all-reduce)")
                                  if world > 1 else "n/a at 1 GPU"},
             "e2e": {"value": audio_s / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
@@ -348,7 +353,8 @@ def run_b200(args):
             "step_frac_of_tensor_peak": algo_tflop / (ms_step * 1e-3) / peak,
             "fedavg_round_s": ms_step * 1e-3, "fedavg_agg_ms": agg_ms if world > 1 else None,
             "fedavg_agg_alone": agg_alone or None,  # each implementation timed back to back without the local step
-            "fedavg_nvlink_gbs_per_dir": (4 * n_train * (world - 1) / world / (agg_alone["peer_kernel_ms"] * 1e-3) / 1e9)
+            # per GPU and direction: its own remote reads + the peers' writes into it = 2 * 4P (N-1)/N bytes
+            "fedavg_nvlink_gbs_per_dir": (2 * 4 * n_train * (world - 1) / world / (agg_alone["peer_kernel_ms"] * 1e-3) / 1e9)
                                          if agg_alone.get("peer_kernel_ms") else None,
             "fedavg_bytes_per_client": 4 * n_train,
             "clocks": clk, "roofline": roofline,
@@ -367,7 +373,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--fedavg", default="peer", choices=["peer", "nccl"], help="N>1 aggregation: fused peer-memory kernel or NCCL")
+    ap.add_argument("--fedavg", default="auto", choices=["auto", "peer", "nccl"],
+                    help="N>1 aggregation: fused peer-memory kernel, scale kernel + NCCL all-reduce, or whichever measures faster in warm-up")
     ap.add_argument("--eager", action="store_true", help="issue every launch from Python instead of replaying the CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":
