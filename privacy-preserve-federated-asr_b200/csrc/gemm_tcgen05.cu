@@ -27,8 +27,12 @@ constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
 // CTA stages its own 128 rows of A and HALF of the B tile, so the L2 -> shared-memory traffic per FLOP drops by 1.5x
 // (BN = 256) against the single-CTA 128 x 256 tile -- the measured limiter of this kernel (profiles/: ~6.3 KB/clk chip
 // wide L2 read cap reached at ~950 TFLOP/s).
+// NCTA = 4: a cluster of TWO pairs on vertically adjacent 256 x BN tiles (a 512 x BN super tile).  Both pairs need the same
+// B tile: every CTA loads one quarter of it and TMA-multicasts it to the CTA of the other pair that holds the same B half,
+// so the L2 -> shared-memory traffic per FLOP drops by another 25% (A 16 KB + B 8 KB per CTA and 64-deep K block).
 template <int BN, int NCTA = 1> struct Cfg {
-    static constexpr int B_STAGE_BYTES = (BN / NCTA) * BLOCK_K * 2;
+    static constexpr int NP = NCTA >= 2 ? 2 : 1;  // CTAs per MMA (cta_group)
+    static constexpr int B_STAGE_BYTES = (BN / NP) * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
     // Staged epilogue: every epilogue warp owns 8 KB of shared memory -- two 32x32 output chunks (TMA-stored, so the
     // global writes are full coalesced rows and asynchronous) and two chunks of the second epilogue tensor (the GELU
@@ -38,8 +42,8 @@ template <int BN, int NCTA = 1> struct Cfg {
     static constexpr bool EPI_TMA = !(NCTA == 1 && BN == 256);  // 48 KB stages leave no room there
     static constexpr int EPI_WARP_BYTES = 8192;
     static constexpr int EPI_BYTES = EPI_TMA ? 8 * EPI_WARP_BYTES : 0;
-    static constexpr int STAGES = (NCTA == 2) ? (BN == 256 ? 5 : 6) : ((BN == 256) ? 4 : (BN == 128 ? 5 : 6));
-    static constexpr int TMEM_COLS = (NCTA == 2) ? 512 : ((2 * BN < 32) ? 32 : 2 * BN);  // two accumulator buffers
+    static constexpr int STAGES = (NCTA >= 2) ? (BN == 256 ? 5 : 6) : ((BN == 256) ? 4 : (BN == 128 ? 5 : 6));
+    static constexpr int TMEM_COLS = (NCTA >= 2) ? 512 : ((2 * BN < 32) ? 32 : 2 * BN);  // two accumulator buffers
     static constexpr int BAR_BYTES = 512;  // full/empty[STAGES], tmem_full/empty[2], tmem slot, epilogue in-barriers[16]
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 /*align slack*/ + BAR_BYTES;
     static_assert(SMEM_BYTES <= 232448, "shared memory budget");
@@ -136,11 +140,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_x, const Params p) {
     using C_ = Cfg<BN, NCTA>;
-    constexpr int TILE_M = BLOCK_M * NCTA;  // rows of one (pair) tile
-    constexpr int BNH = BN / NCTA;          // B rows staged by this CTA
-    const uint32_t rank = (NCTA == 2) ? cluster_ctarank() : 0u;   // 0 = pair leader (issues the MMAs)
-    const int worker = (NCTA == 2) ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
-    const int nworkers = (NCTA == 2) ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    constexpr int NP = C_::NP;
+    constexpr bool PAIR = NCTA >= 2;        // tcgen05 cta_group::2
+    constexpr bool MC = NCTA == 4;          // two pairs per cluster sharing the B tile by TMA multicast
+    constexpr int TILE_M = BLOCK_M * NP;    // rows of one (pair) tile
+    constexpr int BNH = BN / NP;            // B rows held by this CTA
+    const uint32_t crank = PAIR ? cluster_ctarank() : 0u;  // rank in the cluster
+    const uint32_t rank = crank & 1u;       // rank in the pair: 0 = pair leader (issues the MMAs)
+    const uint32_t pair = crank >> 1;       // which pair of the cluster (NCTA = 4)
+    const uint32_t leader = crank & ~1u;    // cluster rank of this pair's leader
+    // worker = the unit that walks the tile list: a CTA, a pair, or (NCTA = 4) a cluster of two pairs whose "tile" is the
+    // vertical pair of 256-row tiles (pair p takes the p-th); tiles_m then counts super rows
+    const int worker = (NCTA == 4) ? (int)(blockIdx.x >> 2) : PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int nworkers = (NCTA == 4) ? (int)(gridDim.x >> 2) : PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
     extern __shared__ uint8_t smem_raw[];
     // 1024-byte alignment: the 128B swizzle pattern is a function of the absolute shared address
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -164,11 +176,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         tma_prefetch_desc(&tma_b);
         for (int s = 0; s < C_::STAGES; ++s) {
             mbar_init(full_bar(s), 1);
-            mbar_init(empty_bar(s), 1);
+            mbar_init(empty_bar(s), MC ? 2 : 1);  // NCTA = 4: both pairs' MMAs must have drained the slot (multicast target)
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(tfull_bar(s), 1);
-            mbar_init(tempty_bar(s), 8 * NCTA);  // one arrival per epilogue warp (of both CTAs of a pair)
+            mbar_init(tempty_bar(s), 8 * NP);  // one arrival per epilogue warp (of both CTAs of a pair)
         }
         for (int s = 0; s < 16; ++s) mbar_init(in_bar(s >> 1, s & 1), 1);
         if (p.epi_tma) {
@@ -178,12 +190,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         fence_barrier_init();
     }
     if (warp == 1) {
-        if constexpr (NCTA == 2) tmem_alloc_2sm(tmem_slot, C_::TMEM_COLS);
+        if constexpr (PAIR) tmem_alloc_2sm(tmem_slot, C_::TMEM_COLS);
         else tmem_alloc(tmem_slot, C_::TMEM_COLS);
     }
     tc_fence_before();
     __syncthreads();
-    if constexpr (NCTA == 2) cluster_sync_all();  // the peer's barriers are initialised before anyone signals them
+    if constexpr (PAIR) cluster_sync_all();  // the peers' barriers are initialised before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_gen;
     // Programmatic dependent launch: everything above (barrier init, TMEM allocation, descriptor prefetch) may overlap the
@@ -204,15 +216,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                 const int rem = (int)(tile % tiles_per_batch);
                 const int mb = rem / p.tiles_n, nb = rem % p.tiles_n;  // n fastest: neighbours share the A tile in L2
                 const int b0 = z % p.batch0, b1 = z / p.batch0;
-                const int m0 = mb * TILE_M + (int)rank * BLOCK_M, n0 = nb * BN + (int)rank * BNH;
+                const int m0 = (MC ? (2 * mb + (int)pair) : mb) * TILE_M + (int)rank * BLOCK_M, n0 = nb * BN + (int)rank * BNH;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(empty_bar(stage), phase ^ 1u);
                     const uint32_t sa = smem_base + stage * C_::STAGE_BYTES;
                     const uint32_t sb = sa + A_STAGE_BYTES;
                     const int k0 = kb * BLOCK_K;
-                    if constexpr (NCTA == 2) {
-                        // both CTAs' loads complete on the LEADER's full barrier, which expects the bytes of the pair
-                        const uint32_t fb = mapa_shared(full_bar(stage), 0);
+                    if constexpr (PAIR) {
+                        // the loads of both CTAs complete on the pair LEADER's full barrier, which expects the pair's bytes
+                        const uint32_t fb = mapa_shared(full_bar(stage), leader);
                         if (rank == 0) mbar_expect_tx(full_bar(stage), 2 * C_::STAGE_BYTES);
                         if (!p.a_mn) {
                             tma_load_4d_2sm(sa, &tma_a, fb, k0, m0, b0, b1);
@@ -221,7 +233,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                             for (int c = 0; c < BLOCK_M / 64; ++c)
                                 tma_load_4d_2sm(sa + c * (64 * BLOCK_K * 2), &tma_a, fb, m0 + 64 * c, k0, b0, b1);
                         }
-                        if (!p.b_mn) {
+                        if constexpr (MC) {
+                            // this CTA fetches quarter `pair` (64 of the BNH = 128 rows) of its B half and multicasts it to
+                            // the CTA holding the same half in the other pair (cluster ranks rank and rank + 2); the bytes
+                            // are credited to the leader of each destination's pair (peer bit of the barrier address cleared)
+                            static_assert(!MC || BNH == 128, "multicast variant: 256-wide tiles");
+                            const uint16_t mask = (uint16_t)((1u << rank) | (1u << (rank + 2)));
+                            const uint32_t fbm = full_bar(stage) & 0xFEFFFFFFu;
+                            const uint32_t dst = sb + pair * (64 * BLOCK_K * 2);
+                            if (!p.b_mn) tma_load_4d_2sm_mc(dst, &tma_b, fbm, mask, k0, n0 + 64 * (int)pair, b0, b1);
+                            else tma_load_4d_2sm_mc(dst, &tma_b, fbm, mask, n0 + 64 * (int)pair, k0, b0, b1);
+                        } else if (!p.b_mn) {
                             tma_load_4d_2sm(sb, &tma_b, fb, k0, n0, b0, b1);
                         } else {
 #pragma unroll
@@ -294,16 +316,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                     for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
                         const uint64_t adesc = make_smem_desc(sa + k * a_kstep, a_lbo, a_sbo);
                         const uint64_t bdesc = make_smem_desc(sb + k * b_kstep, b_lbo, b_sbo);
-                        if constexpr (NCTA == 2) umma_bf16_2sm(tmem_d, adesc, bdesc, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                        if constexpr (PAIR) umma_bf16_2sm(tmem_d, adesc, bdesc, idesc, (kb > 0 || k > 0) ? 1u : 0u);
                         else umma_bf16(tmem_d, adesc, bdesc, idesc, (kb > 0 || k > 0) ? 1u : 0u);
                     }
                     // frees the smem slot (in both CTAs of a pair) once these MMAs have read it
-                    if constexpr (NCTA == 2) umma_commit_2sm(empty_bar(stage), 3);
+                    if constexpr (MC) umma_commit_2sm(empty_bar(stage), 0xF);   // all four CTAs: the slot is a multicast target
+                    else if constexpr (PAIR) umma_commit_2sm(empty_bar(stage), 3);
                     else umma_commit(empty_bar(stage));
                     if (++stage == C_::STAGES) { stage = 0; phase ^= 1u; }
                 }
                 // accumulator complete -> epilogue warps (of both CTAs)
-                if constexpr (NCTA == 2) umma_commit_2sm(tfull_bar(acc), 3);
+                if constexpr (PAIR) umma_commit_2sm(tfull_bar(acc), (uint16_t)(3u << leader));
                 else umma_commit(tfull_bar(acc));
                 if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
             }
@@ -355,7 +378,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                     const int rem = (int)(tile % tiles_per_batch);
                     const int mb = rem / p.tiles_n, nb = rem % p.tiles_n;
                     b0 = z % p.batch0; b1 = z / p.batch0;
-                    m0w = mb * TILE_M + (int)rank * BLOCK_M + quarter * 32;
+                    m0w = (MC ? (2 * mb + (int)pair) : mb) * TILE_M + (int)rank * BLOCK_M + quarter * 32;
                     n = nb * BN + (chalf * CHUNKS + cc) * 32;
                     return n < p.N && m0w < p.M;
                 };
@@ -492,7 +515,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) {
-                        if constexpr (NCTA == 2) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0));
+                        if constexpr (PAIR) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), leader));
                         else mbar_arrive(tempty_bar(acc));
                     }
                     if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
@@ -505,7 +528,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                 const int rem = (int)(tile % tiles_per_batch);
                 const int mb = rem / p.tiles_n, nb = rem % p.tiles_n;
                 const int b0 = z % p.batch0, b1 = z / p.batch0;
-                const int m = mb * TILE_M + (int)rank * BLOCK_M + quarter * 32 + lane;
+                const int m = (MC ? (2 * mb + (int)pair) : mb) * TILE_M + (int)rank * BLOCK_M + quarter * 32 + lane;
                 const int n0 = nb * BN;
                 const long long row_off = (long long)b0 * p.sc0 + (long long)b1 * p.sc1 + (long long)m * p.ldc;
                 mbar_wait(tfull_bar(acc), acc_phase);
@@ -576,7 +599,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
-                    if constexpr (NCTA == 2) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0));
+                    if constexpr (PAIR) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), leader));
                     else mbar_arrive(tempty_bar(acc));
                 }
                 if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
@@ -585,10 +608,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     }
     tc_fence_before();
     __syncthreads();
-    if constexpr (NCTA == 2) cluster_sync_all();  // no CTA of the pair exits while its peer may still signal / read it
+    if constexpr (PAIR) cluster_sync_all();  // no CTA of the cluster exits while a peer may still signal / read it
     if (warp == 1) {
         tc_fence_after();
-        if constexpr (NCTA == 2) tmem_dealloc_2sm(tmem_base, C_::TMEM_COLS);
+        if constexpr (PAIR) tmem_dealloc_2sm(tmem_base, C_::TMEM_COLS);
         else tmem_dealloc(tmem_base, C_::TMEM_COLS);
     }
 }
@@ -679,7 +702,27 @@ static int launch_kernel(const CUtensorMap& ma, const CUtensorMap& mb, const CUt
         }
         attr_set = true;
     }
-    const long long workers = num_sms() / NCTA;
+    long long workers = num_sms() / NCTA;
+    if (NCTA == 4) {  // clusters of 4 must fit inside a GPC: ask how many can be co-resident (persistent kernel, one wave)
+        static int max_clusters = -1;
+        if (max_clusters < 0) {
+            cudaLaunchConfig_t q = {};
+            q.gridDim = dim3(NCTA * (num_sms() / NCTA));
+            q.blockDim = dim3(NUM_THREADS);
+            q.dynamicSmemBytes = C_::SMEM_BYTES;
+            cudaLaunchAttribute qa[1];
+            qa[0].id = cudaLaunchAttributeClusterDimension;
+            qa[0].val.clusterDim.x = NCTA; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+            q.attrs = qa; q.numAttrs = 1;
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<BN, TC, NCTA>, &q) != cudaSuccess || n <= 0) {
+                (void)cudaGetLastError();
+                n = num_sms() / NCTA;
+            }
+            max_clusters = n;
+        }
+        if (workers > max_clusters) workers = max_clusters;
+    }
     const long long grid = (p.num_tiles < workers ? p.num_tiles : workers) * NCTA;
     static const int use_pdl = getenv("B200ASR_PDL") ? atoi(getenv("B200ASR_PDL")) : 1;
     cudaLaunchConfig_t cfg = {};
@@ -741,7 +784,8 @@ static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
     memset(&mx, 0, sizeof(mx));
     int rc = make_operand_map(&ma, a.A, a.M, a.K, a.lda, a.a_kmajor, BLOCK_M, a.batch0, a.batch1, a.sa0, a.sa1);
     if (rc) return rc;
-    rc = make_operand_map(&mb, a.B, a.N, a.K, a.ldb, a.b_kmajor, BN / NCTA, a.batch0, a.batch1, a.sb0, a.sb1);
+    // B box rows: the whole tile (single CTA), this CTA's half (pair), or one multicast quarter (two pairs)
+    rc = make_operand_map(&mb, a.B, a.N, a.K, a.ldb, a.b_kmajor, NCTA == 4 ? 64 : BN / NCTA, a.batch0, a.batch1, a.sb0, a.sb1);
     if (rc) return rc;
     Params p;
     p.C = a.C; p.bias = a.bias; p.residual = a.residual; p.aux_out = a.aux_out; p.aux_in = a.aux_in;
@@ -749,7 +793,7 @@ static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
     p.a_mn = a.a_kmajor ? 0 : 1; p.b_mn = a.b_kmajor ? 0 : 1;
     p.act = a.act; p.mul_gelu_grad = a.mul_gelu_grad; p.alpha = a.alpha;
     p.batch0 = a.batch0; p.batch1 = a.batch1; p.sc0 = a.sc0; p.sc1 = a.sc1;
-    p.tiles_m = ceil_div(a.M, BLOCK_M * NCTA);
+    p.tiles_m = ceil_div(a.M, BLOCK_M * NCTA);  // NCTA = 4: super rows of 512 (two vertically adjacent pair tiles)
     p.tiles_n = ceil_div(a.N, BN);
     p.num_tiles = (long long)p.tiles_m * p.tiles_n * a.batch0 * a.batch1;
     p.mode = 0; p.tap_pad = 0; p.tblocks = 1; p.num_kb = ceil_div(a.K, BLOCK_K); p.bias_sb0 = 0;
@@ -853,15 +897,23 @@ static void choose_config(const b200asr_gemm_args& a, int* ncta_out, int* bn_out
     const int sms = num_sms();
     double best = 1e30;
     int best_ncta = 1, best_bn = 128;
-    for (int ncta = 1; ncta <= 2; ++ncta) {
-        if (ncta == 2 && a.M <= 128) continue;
+    // The multicast cluster variant (NCTA = 4) is correct on every operand layout (tests force it) but measured no faster
+    // than the pair tile on the model's shapes and 0.8% slower in the full step (profiles/r01_gemm_multicast_ab.txt): the
+    // pair kernel is not bound by L2 read traffic after all.  Opt-in via B200ASR_GEMM_MC=1.
+    static const int allow4 = getenv("B200ASR_GEMM_MC") ? atoi(getenv("B200ASR_GEMM_MC")) : 0;
+    for (int ncta = 1; ncta <= 4; ncta *= 2) {
+        if (ncta >= 2 && a.M <= 128) continue;
+        if (ncta == 4 && (!allow4 || a.M <= 256)) continue;
         for (int bn = 64; bn <= 256; bn *= 2) {
-            if (ncta == 2 && bn == 64) continue;
+            if (ncta >= 2 && bn == 64) continue;
+            if (ncta == 4 && bn != 256) continue;
             if (bn > 64 && a.N <= bn / 2) continue;  // more than half of the tile would be padding
             const long long tiles = (long long)ceil_div(a.M, 128 * ncta) * ceil_div(a.N, bn) * batches;
-            const long long workers = sms / ncta;
+            const long long workers = ncta == 4 ? 32 : sms / ncta;  // clusters of 4: GPC granularity leaves ~32 co-resident
             const long long waves = (tiles + workers - 1) / workers;
             const double mma = (double)waves * 2.0 * bn * num_kb;
+            // bytes fetched from L2 per CTA and K block: its 128 A rows + its share of the B tile (half of it in a pair,
+            // a quarter in the multicast cluster of two pairs)
             const double bytes = (double)tiles * ncta * (128.0 + (double)bn / ncta) * 128.0 * num_kb;
             const double l2 = bytes / 6300.0;
             const double epi = (double)waves * (600.0 + 8.0 * bn);
@@ -878,6 +930,7 @@ int gemm_tc_launch(const b200asr_gemm_args& a, cudaStream_t st) {
     choose_config(a, &ncta, &bn);
     if (g_force_cfg) { ncta = g_force_cfg / 1000; bn = g_force_cfg % 1000; }
     const bool f32c = a.c_dtype == B200ASR_F32;
+    if (ncta == 4) return f32c ? tc::launch<256, float, 4>(a, st) : tc::launch<256, __nv_bfloat16, 4>(a, st);
     if (ncta == 2) {
         if (bn == 256) return f32c ? tc::launch<256, float, 2>(a, st) : tc::launch<256, __nv_bfloat16, 2>(a, st);
         return f32c ? tc::launch<128, float, 2>(a, st) : tc::launch<128, __nv_bfloat16, 2>(a, st);

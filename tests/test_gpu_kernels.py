@@ -182,7 +182,7 @@ def test_gemm_tcgen05_batched_and_persistent():
     _gemm_case(1, torch.bfloat16, 128 * 40, 256 * 5, 128, True, True, "bias", seed=7)  # > 148 tiles: several per CTA
 
 
-@pytest.mark.parametrize("cfg", [2256, 2128, 1256, 1128, 1064])
+@pytest.mark.parametrize("cfg", [4256, 2256, 2128, 1256, 1128, 1064])
 @pytest.mark.parametrize("a_k,b_k", [(True, True), (True, False), (False, False), (False, True)])
 def test_gemm_tcgen05_forced_tile_configs(cfg, a_k, b_k):
     """Every tile configuration of the tcgen05 kernel (ncta*1000 + bn: single CTA 128 x {64,128,256}, CTA pair =

@@ -96,7 +96,7 @@ for name, mk, fl, mult in [
     us = bench(name, mk, fl)
     tot += us * mult
     if SWEEP:
-        for cfg in (1128, 1256, 2128, 2256):
+        for cfg in (2256, 4256):
             lib.b200asr_gemm_force_config(cfg)
             bench(f"    forced {cfg}", mk, fl)
         lib.b200asr_gemm_force_config(0)
