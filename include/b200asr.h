@@ -315,6 +315,28 @@ int b200asr_ipc_open(const unsigned char handle[64], void** ptr);
 int b200asr_ipc_close(void* ptr);
 
 /* ------------------------------------------------------------------------------------------------
+ * Input pipeline on the device.  Replaces Wav2Vec2Processor's zero-mean / unit-variance normalisation
+ * (centralized/finetune_ASRs.py:88-96: (x - mean) / sqrt(var + 1e-7) per utterance) and DataCollatorCTCWithPadding's
+ * padding + attention mask (finetune_ASRs.py:59-86) on ONE packed buffer of raw utterances.
+ *   packed fp32: the B utterances back to back; offsets int64 [B+1] (device) their boundaries
+ *   input_values fp32 [B, Lmax] (zero padded), attention_mask int32 [B, Lmax] or NULL,
+ *   frame_lengths int32 [B] or NULL = _get_feat_extract_output_lengths (conv_kernel / conv_stride: DEVICE int32 [n_conv])
+ */
+size_t b200asr_normalize_pad_workspace_bytes(int B, long long max_len);
+int b200asr_normalize_pad(const float* packed, const long long* offsets, float* input_values, int* attention_mask,
+                          int* frame_lengths, void* workspace, size_t workspace_bytes, int B, int Lmax,
+                          const int* conv_kernel, const int* conv_stride, int n_conv, void* stream);
+/* Word error rate on the device (federated/src/update.py:36-50 compute_metrics -> jiwer.wer on the decoded
+ * strings).  words_from_ids: ids int32 [B, ld] (negative = padding), len [B] or NULL; a word is a maximal run of
+ * ids != delim and is represented by a 64-bit hash (delim < 0: every id is a token = character error rate);
+ * words u64 [B, ldw], nwords [B].  edit_distance: Levenshtein distance per pair of token rows -> dist int32 [B];
+ * WER = sum(dist) / sum(ref word counts). */
+int b200asr_words_from_ids(const int* ids, const int* len, int B, int ld, int delim, unsigned long long* words, int* nwords,
+                           int ldw, void* stream);
+int b200asr_edit_distance(const unsigned long long* hyp, const int* hyp_len, const unsigned long long* ref, const int* ref_len,
+                          int* dist, int B, int ld_hyp, int ld_ref, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Fused AdamW on flat fp32 buffers (HF Trainer "adamw_hf" semantics = transformers.AdamW with
  * correct_bias=True, configured at centralized/finetune_ASRs.py:202-220, federated/src/update.py:657-678):
  *   g = grad * clip_coef,  clip_coef = min(1, max_norm / (sqrt(*gnorm_sq) + 1e-6)) (gnorm_sq NULL -> 1)
