@@ -135,6 +135,10 @@ int b200asr_gemm(const b200asr_gemm_args* args, void* stream);
 /* test / tuning hook: force the tcgen05 tile configuration: 0 = built-in cost model, else ncta * 1000 + bn
  * (1064, 1128, 1256 single CTA; 2128, 2256 CTA pair = cluster of 2 with cta_group::2 MMA).  Returns the old value. */
 int b200asr_gemm_force_config(int cfg);
+/* diagnostics: while `buf` (device memory, >= 148 * 20 * 8 bytes) is set, every tensor-core GEMM launch records 20 u64
+ * time stamps per CTA (entry, set-up done, dependency wait done, first operands landed, last MMA issued, last
+ * accumulator complete, epilogue done, exit; SM clock cycles, slots 0 / 9 = %globaltimer ns); NULL stops. */
+int b200asr_gemm_set_trace(void* buf);
 /* test hook: run b200asr_gemm on a forced back end (0 = fp32 FMA pipes, 1 = tcgen05 tensor cores). */
 int b200asr_gemm_backend(const b200asr_gemm_args* args, int backend, void* stream);
 

@@ -17,6 +17,8 @@ namespace b200asr {
 
 namespace tc {
 
+static unsigned long long* g_gemm_trace = nullptr;  // b200asr_gemm_set_trace
+
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;   // 64 bf16 = 128 bytes = one swizzle-128B row
 constexpr int UMMA_K = 16;
@@ -44,10 +46,10 @@ template <int BN, int NCTA = 1> struct Cfg {
     static constexpr int EPI_BYTES = EPI_TMA ? 8 * EPI_WARP_BYTES : 0;
     static constexpr int STAGES = (NCTA >= 2) ? (BN == 256 ? 5 : 6) : ((BN == 256) ? 4 : (BN == 128 ? 5 : 6));
     static constexpr int TMEM_COLS = (NCTA >= 2) ? 512 : ((2 * BN < 32) ? 32 : 2 * BN);  // two accumulator buffers
-    static constexpr int BAR_BYTES = 512;  // full/empty[STAGES], tmem_full/empty[2], tmem slot, epilogue in-barriers[16]
+    static constexpr int BAR_BYTES = 512;  // full/empty[STAGES], tmem_full/empty[2], tmem slot, epilogue in-barriers[32]
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 /*align slack*/ + BAR_BYTES;
     static_assert(SMEM_BYTES <= 232448, "shared memory budget");
-    static_assert(8 * (2 * STAGES + 4) + 8 + 16 * 8 <= BAR_BYTES, "barrier area");
+    static_assert(8 * (2 * STAGES + 4) + 8 + 32 * 8 <= BAR_BYTES, "barrier area");
 };
 
 struct Params {
@@ -76,7 +78,18 @@ struct Params {
     int epi_tma;         // 1: staged epilogue (TMA store of C [+ second tensor]); 0: direct row-per-thread accesses
     int x_kind;          // second epilogue tensor of the staged path: 0 none, 1 aux_out (store), 2 residual, 3 aux_in (gelu')
     int dbg;             // experiment knobs (B200ASR_GEMM_DBG): 1 skip GELU math, 2 skip aux/residual traffic, 4 skip the C store
+    unsigned long long* trace;  // diagnostics (b200asr_gemm_set_trace): 12 time stamps per CTA, null in normal use
 };
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+// slot layout: 0 globaltimer at entry, 1 clock at entry, 2 after set-up, 3 after griddepcontrol.wait, 4 first operand stage
+// landed (MMA issuer), 5 last MMA issued, 6 last accumulator complete (epilogue warp 2), 7 epilogue warp 2 done, 8 clock at
+// exit, 9 globaltimer at exit
+#define TRACE(slot) do { if (p.trace) p.trace[(long long)blockIdx.x * 20 + (slot)] = (unsigned long long)clock64(); } while (0)
 
 template <typename TC> __device__ __forceinline__ void store_row_chunk(TC* dst, const float* v, int ncols_valid, bool vec_ok);
 template <> __device__ __forceinline__ void store_row_chunk<float>(float* dst, const float* v, int n, bool vec_ok) {
@@ -164,12 +177,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     auto tfull_bar = [&](int s) { return bars + 8u * (2 * C_::STAGES + s); };
     auto tempty_bar = [&](int s) { return bars + 8u * (2 * C_::STAGES + 2 + s); };
     const uint32_t tmem_slot = bars + 8u * (2 * C_::STAGES + 4);
-    auto in_bar = [&](int ew, int i) { return bars + 8u * (2 * C_::STAGES + 5) + 8u * (2 * ew + i); };
+    auto in_bar = [&](int ew, int i) { return bars + 8u * (2 * C_::STAGES + 5) + 8u * (4 * ew + i); };
     uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
     volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(smem_gen + C_::STAGES * C_::STAGE_BYTES + C_::EPI_BYTES + 8 * (2 * C_::STAGES + 4));
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    if (p.trace && threadIdx.x == 0) { p.trace[(long long)blockIdx.x * 20] = globaltimer_ns(); TRACE(1); }
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tma_a);
@@ -182,7 +196,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
             mbar_init(tfull_bar(s), 1);
             mbar_init(tempty_bar(s), 8 * NP);  // one arrival per epilogue warp (of both CTAs of a pair)
         }
-        for (int s = 0; s < 16; ++s) mbar_init(in_bar(s >> 1, s & 1), 1);
+        for (int s = 0; s < 32; ++s) mbar_init(in_bar(s >> 2, s & 3), 1);
         if (p.epi_tma) {
             tma_prefetch_desc(&tma_c);
             if (p.x_kind) tma_prefetch_desc(&tma_x);
@@ -200,8 +214,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     const uint32_t tmem_base = *tmem_slot_gen;
     // Programmatic dependent launch: everything above (barrier init, TMEM allocation, descriptor prefetch) may overlap the
     // tail of the kernel this one depends on; nothing below may touch global memory before that kernel has completed.
+    if (threadIdx.x == 0) TRACE(2);
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (threadIdx.x == 0) TRACE(3);
 
     const int num_kb = p.num_kb;
     const long long tiles_per_batch = (long long)p.tiles_m * p.tiles_n;
@@ -310,6 +326,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(full_bar(stage), phase);
                     tc_fence_after();
+                    if (kb == 0 && tile == worker) TRACE(4);
                     const uint32_t sa = smem_base + stage * C_::STAGE_BYTES;
                     const uint32_t sb = sa + A_STAGE_BYTES;
 #pragma unroll
@@ -328,6 +345,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                 // accumulator complete -> epilogue warps (of both CTAs)
                 if constexpr (PAIR) umma_commit_2sm(tfull_bar(acc), (uint16_t)(3u << leader));
                 else umma_commit(tfull_bar(acc));
+                TRACE(5);
                 if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
             }
         }
@@ -359,62 +377,96 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                 constexpr int ROW_SHIFT = (ES == 2) ? 1 : 0;        // 64-byte rows: two rows share a 128-byte line
                 const int ew = warp - 2;
                 const uint32_t my = epi_smem + (uint32_t)ew * C_::EPI_WARP_BYTES;
-                // bf16: x0, x1, out0, out1 (2 KB each); fp32: out0, out1 (4 KB each, no second tensor)
-                const uint32_t xbuf = my, obuf = (ES == 2) ? my + 2 * CHUNK_BYTES : my;
                 uint8_t* my_gen = smem_gen + C_::STAGES * C_::STAGE_BYTES + ew * C_::EPI_WARP_BYTES;
-                uint8_t* xgen = my_gen;
-                uint8_t* ogen = (ES == 2) ? my_gen + 2 * CHUNK_BYTES : my_gen;
+                // Per warp NSLOT staging chunks (bf16: 4 x 2 KB, fp32: 2 x 4 KB).  Chunk `item` uses
+                //   no second tensor:       slot item % NSLOT for the result;
+                //   residual / gelu' input: slot item % 4, TMA-loaded up to three chunks (a whole tile) ahead, the result is
+                //                           written IN PLACE over the operand (each lane owns its row) and stored from there;
+                //   second output (aux):    slots 2 (item % 2) (result) and 2 (item % 2) + 1 (pre-activation / gelu').
+                constexpr int NSLOT = C_::EPI_WARP_BYTES / CHUNK_BYTES;
+                static_assert(NSLOT == (ES == 2 ? 4 : 2), "staging chunks per epilogue warp");
                 const int x_kind = (ES == 2) ? p.x_kind : 0;
                 const bool has_in = x_kind >= 2;
                 const int sw = (lane >> ROW_SHIFT) & SWZ;           // this lane's (row's) swizzle term
                 const uint32_t row_off_s = (uint32_t)lane * (32 * ES);
+                const int ntiles = (int)p.num_tiles, tpb = (int)tiles_per_batch;
 
-                // work item = (tile, 32-column chunk of this warp's half); coordinates of item `it`
-                auto coords = [&](long long it, int& m0w, int& n, int& b0, int& b1) -> bool {
-                    const long long tile = worker + (it / CHUNKS) * nworkers;
-                    if (tile >= p.num_tiles) return false;
-                    const int cc = (int)(it % CHUNKS);
-                    const int z = (int)(tile / tiles_per_batch);
-                    const int rem = (int)(tile % tiles_per_batch);
-                    const int mb = rem / p.tiles_n, nb = rem % p.tiles_n;
-                    b0 = z % p.batch0; b1 = z / p.batch0;
+                // first row / first column of this warp's part of a tile (32-bit arithmetic: this runs once per tile on
+                // the accumulator-drain critical path)
+                auto tile_coords = [&](int tile, int& m0w, int& nbase, int& b0, int& b1) {
+                    const int z = tile / tpb, rem = tile - z * tpb;
+                    const int mb = rem / p.tiles_n, nb = rem - mb * p.tiles_n;
+                    b1 = z / p.batch0; b0 = z - b1 * p.batch0;
                     m0w = (MC ? (2 * mb + (int)pair) : mb) * TILE_M + (int)rank * BLOCK_M + quarter * 32;
-                    n = nb * BN + (chalf * CHUNKS + cc) * 32;
-                    return n < p.N && m0w < p.M;
+                    nbase = nb * BN + chalf * CHUNKS * 32;
                 };
-                auto issue_in = [&](long long it) {
-                    int m0w, n, b0, b1;
-                    if (!coords(it, m0w, n, b0, b1)) return;
-                    if (lane == 0) {
-                        const int i = (int)(it & 1);
-                        mbar_expect_tx(in_bar(ew, i), CHUNK_BYTES);
-                        tma_load_4d(xbuf + i * CHUNK_BYTES, &tma_x, in_bar(ew, i), n, m0w, b0, b1);
-                    }
+                // lane 0: fetch the second-tensor chunk of work item `it` (= CHUNKS * tile ordinal + chunk) into its slot
+                auto issue_in = [&](int it) {
+                    const int tile = worker + (it / CHUNKS) * nworkers;
+                    if (tile >= ntiles) return;
+                    int m0w, nbase, b0, b1;
+                    tile_coords(tile, m0w, nbase, b0, b1);
+                    const int n = nbase + (it % CHUNKS) * 32;
+                    if (n >= p.N || m0w >= p.M) return;
+                    const int sl = it & 3;
+                    mbar_expect_tx(in_bar(ew, sl), CHUNK_BYTES);
+                    tma_load_4d(my + sl * CHUNK_BYTES, &tma_x, in_bar(ew, sl), n, m0w, b0, b1);
                 };
-                uint32_t in_phase0 = 0, in_phase1 = 0;
-                if (has_in) { issue_in(0); issue_in(1); }
-                long long item = 0;
-                for (long long tile = worker; tile < p.num_tiles; tile += nworkers) {
+                uint32_t in_phase = 0;   // bit s: parity of slot s's load barrier
+                if (has_in && lane == 0) {
+#pragma unroll 1
+                    for (int it = 0; it < 4; ++it) issue_in(it);
+                }
+                int item = 0;
+                for (int tile = worker; tile < ntiles; tile += nworkers) {
+                    int m0w, nbase, b0, b1;
+                    tile_coords(tile, m0w, nbase, b0, b1);
+                    const float* bpt = p.bias ? p.bias + (long long)b0 * p.bias_sb0 + nbase : nullptr;
+                    // the tile's bias slice into L1 while the accumulator is still being computed
+                    if (bpt && lane * 4 < CHUNKS * 32 && nbase + lane * 4 < p.N)
+                        asm volatile("prefetch.global.L1 [%0];" ::"l"(bpt + lane * 4));
                     mbar_wait(tfull_bar(acc), acc_phase);
                     tc_fence_after();
+                    if (threadIdx.x == 64) TRACE(6);
                     const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+                    auto release_acc = [&]() {   // this warp has read its part of the accumulator: the MMA issuer may reuse it
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) {
+                            if constexpr (PAIR) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), leader));
+                            else mbar_arrive(tempty_bar(acc));
+                        }
+                    };
 #pragma unroll 1
                     for (int cc = 0; cc < CHUNKS; ++cc, ++item) {
-                        int m0w, n, b0, b1;
-                        if (!coords(item, m0w, n, b0, b1)) {  // chunk entirely outside C: nothing staged, nothing waited for
-                            if (has_in) issue_in(item + 2);
+                        const int n = nbase + cc * 32;
+                        if (n >= p.N || m0w >= p.M) {  // chunk entirely outside C: nothing staged, nothing waited for
+                            if (cc == CHUNKS - 1) release_acc();
+                            if (has_in && item >= 1 && lane == 0) {
+                                bulk_wait_group_read<0>();
+                                issue_in(item + 3);
+                            }
                             continue;
                         }
-                        const int i = (int)(item & 1);
+                        const int sl = (x_kind == 1) ? 2 * (item & 1) : (item & (NSLOT - 1));
                         uint32_t r[32];
                         tmem_ld_32x32(taddr + (chalf * CHUNKS + cc) * 32, r);
                         tmem_ld_wait();
-                        if (lane == 0) bulk_wait_group_read<1>();   // the stores that last read buffer i are done with it
-                        __syncwarp();
+                        if (cc == CHUNKS - 1) release_acc();
+                        const bool trc = cc == 1 && threadIdx.x == 64;
+                        if (trc) TRACE(12);
+                        if (!has_in) {   // the stores that last read this chunk's slot(s) are done with them
+                            if (lane == 0) {
+                                if (ES == 2 && x_kind == 0) bulk_wait_group_read<3>();
+                                else bulk_wait_group_read<1>();
+                            }
+                            __syncwarp();
+                        }
+                        if (trc) TRACE(13);
                         float2 v2[16];   // the 32 accumulator columns of this lane's row, as pairs for the packed fp32 pipe
                         float* v = reinterpret_cast<float*>(v2);
                         const float2 al = make_float2(p.alpha, p.alpha);
-                        const float* bp = p.bias ? p.bias + (long long)b0 * p.bias_sb0 + n : nullptr;
+                        const float* bp = bpt ? bpt + cc * 32 : nullptr;
                         if (bp && p.N - n >= 32 && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
 #pragma unroll
                             for (int j = 0; j < 32; j += 4) {
@@ -433,8 +485,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                                     if (j < nvalid) v[j] += __ldg(bp + j);
                             }
                         }
+                        if (trc) TRACE(14);
                         if constexpr (ES == 2) {
-                            uint8_t* xrow = xgen + i * CHUNK_BYTES + row_off_s;
+                            uint8_t* xrow = my_gen + (sl + (x_kind == 1 ? 1 : 0)) * CHUNK_BYTES + row_off_s;
                             if (x_kind == 1) {  // second output next to the result: the pre-activation, or gelu'(it)
                                 float2 g2[16];
                                 const float2* src = v2;
@@ -461,8 +514,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                                 for (int j = 0; j < 16; ++j) v2[j] = gelu_fast2(v2[j]);
                             }
                             if (has_in) {
-                                mbar_wait(in_bar(ew, i), i ? in_phase1 : in_phase0);
-                                if (i) in_phase1 ^= 1u; else in_phase0 ^= 1u;
+                                mbar_wait(in_bar(ew, sl), (in_phase >> sl) & 1u);
+                                in_phase ^= 1u << sl;
+                                if (trc) TRACE(15);
 #pragma unroll
                                 for (int q = 0; q < V16; ++q) {
                                     const uint4 t = *reinterpret_cast<const uint4*>(xrow + ((q ^ sw) << 4));
@@ -484,7 +538,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                                     }
                                 }
                             }
-                            uint8_t* orow = ogen + i * CHUNK_BYTES + row_off_s;
+                            uint8_t* orow = my_gen + sl * CHUNK_BYTES + row_off_s;   // (in place over the operand when has_in)
 #pragma unroll
                             for (int q = 0; q < V16; ++q) {
                                 uint4 o;
@@ -497,30 +551,35 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 #pragma unroll
                                 for (int j = 0; j < 16; ++j) v2[j] = gelu_fast2(v2[j]);
                             }
-                            uint8_t* orow = ogen + i * CHUNK_BYTES + row_off_s;
+                            uint8_t* orow = my_gen + sl * CHUNK_BYTES + row_off_s;
 #pragma unroll
                             for (int q = 0; q < V16; ++q)
                                 *reinterpret_cast<float4*>(orow + ((q ^ sw) << 4)) =
                                     make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
                         }
+                        if (trc) TRACE(16);
                         fence_proxy_async();
                         __syncwarp();
+                        if (trc) TRACE(17);
                         if (lane == 0 && !(p.dbg & 16)) {
-                            tma_store_4d(&tma_c, obuf + i * CHUNK_BYTES, n, m0w, b0, b1);
-                            if (x_kind == 1 && !(p.dbg & 64)) tma_store_4d(&tma_x, xbuf + i * CHUNK_BYTES, n, m0w, b0, b1);
+                            tma_store_4d(&tma_c, my + sl * CHUNK_BYTES, n, m0w, b0, b1);
+                            if (x_kind == 1 && !(p.dbg & 64)) tma_store_4d(&tma_x, my + (sl + 1) * CHUNK_BYTES, n, m0w, b0, b1);
                             bulk_commit_group();
                         }
-                        if (has_in) issue_in(item + 2);   // buffer i has been consumed by every lane (syncwarp above)
-                    }
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) {
-                        if constexpr (PAIR) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), leader));
-                        else mbar_arrive(tempty_bar(acc));
+                        if (trc) TRACE(18);
+                        if (has_in && item >= 1 && lane == 0) {
+                            // the store of chunk item-1 has read its slot: refill it with the operand of chunk item+3
+                            bulk_wait_group_read<1>();
+                            issue_in(item + 3);
+                        }
+                        if (trc) TRACE(19);
+                        if (cc == 0 && threadIdx.x == 64) TRACE(10);
                     }
                     if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
                 }
-                if (lane == 0) bulk_wait_group<0>();
+                if (threadIdx.x == 64) TRACE(11);
+                if (lane == 0) bulk_wait_group_read<0>();   // shared memory may be released; the writes complete with the grid
+                if (threadIdx.x == 64) TRACE(7);
             }
         } else {
         for (long long tile = worker; tile < p.num_tiles; tile += nworkers) {
@@ -614,6 +673,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         if constexpr (PAIR) tmem_dealloc_2sm(tmem_base, C_::TMEM_COLS);
         else tmem_dealloc(tmem_base, C_::TMEM_COLS);
     }
+    if (p.trace && threadIdx.x == 0) { TRACE(8); p.trace[(long long)blockIdx.x * 20 + 9] = globaltimer_ns(); }
 }
 
 // ---------------------------------------------------------------- host side
@@ -799,6 +859,7 @@ static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
     p.mode = 0; p.tap_pad = 0; p.tblocks = 1; p.num_kb = ceil_div(a.K, BLOCK_K); p.bias_sb0 = 0;
     static const int dbg = getenv("B200ASR_GEMM_DBG") ? atoi(getenv("B200ASR_GEMM_DBG")) : 0;
     p.dbg = dbg;
+    p.trace = g_gemm_trace;
     // staged epilogue when the kernel variant has the shared memory for it and at most ONE second tensor is involved
     p.epi_tma = 0; p.x_kind = 0;
     if (Cfg<BN, NCTA>::EPI_TMA && !(dbg & 8)) {
@@ -954,3 +1015,10 @@ int posconv_tc_wgrad(const void* x, const void* dy, float* dwt, int B, int T, in
     return tc::posconv_wgrad_launch(x, dy, dwt, B, T, C, groups, k, pad, st);
 }
 }  // namespace b200asr
+
+// diagnostics: while `buf` (device memory, 20 u64 per CTA of the largest grid = 148 * 20 * 8 bytes) is set, every tcgen05 GEMM
+// launch records per-CTA time stamps (slot layout next to TRACE above); pass null to stop
+extern "C" int b200asr_gemm_set_trace(void* buf) {
+    b200asr::tc::g_gemm_trace = (unsigned long long*)buf;
+    return 0;
+}
