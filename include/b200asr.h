@@ -139,6 +139,9 @@ int b200asr_gemm_force_config(int cfg);
  * time stamps per CTA (entry, set-up done, dependency wait done, first operands landed, last MMA issued, last
  * accumulator complete, epilogue done, exit; SM clock cycles, slots 0 / 9 = %globaltimer ns); NULL stops. */
 int b200asr_gemm_set_trace(void* buf);
+/* diagnostics, same idea for the attention backward kernel: 24 u64 SM-clock stamps per CTA of its grid
+ * (ceil(T/128) x H x B CTAs), slot layout next to the function in csrc/attn_tc.cu; NULL stops. */
+int b200asr_attn_set_trace(void* buf);
 /* test hook: run b200asr_gemm on a forced back end (0 = fp32 FMA pipes, 1 = tcgen05 tensor cores). */
 int b200asr_gemm_backend(const b200asr_gemm_args* args, int backend, void* stream);
 

@@ -119,7 +119,7 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
     const uint32_t tmem_o = tmem_base + 128;
 
     if (warp == 0) {
-        if (lane == 0) {
+        if (elect_one_sync()) {
             mbar_expect_tx(q_full, F_Q_BYTES);
             tma_load_4d(sQ, &map_q, q_full, 0, q0, h, b);
             for (int j = 0; j < nkb; ++j) {
@@ -131,7 +131,7 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        if (elect_one_sync()) {
             const uint32_t idesc_s = make_idesc_bf16(FQ, FK, 0, 0);
             const uint32_t idesc_pv = make_idesc_bf16(FQ, DH, 0, 1);
             auto issue_s = [&](int j) {
@@ -265,7 +265,9 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
 constexpr int BK = 128;       // keys per CTA (= TMEM lanes)
 constexpr int BQ = 64;        // queries per block
 constexpr int B_STAGES = 3;
-constexpr int B_THREADS = 320;  // TMA warp, MMA warp, 8 element-wise warps
+constexpr int B_EW = 16;        // element-wise warps: four per TMEM lane quarter, 16 query columns each (the per-block chain
+                                // of one thread is latency bound; twice the warps of the first version hide twice the latency)
+constexpr int B_THREADS = 96 + 32 * B_EW;  // TMA warp, MMA warp, element-wise warps, dS^T store warp
 constexpr int B_KV_BYTES = 2 * BK * DH * 2;   // K_j + V_j: 32 KB
 constexpr int B_QD_BYTES = 2 * BQ * DH * 2;   // Q_i + dO_i: 16 KB
 constexpr int B_PT_BYTES = BK * BQ * 2;       // one P^T (or dS^T) operand tile: 16 KB
@@ -280,13 +282,18 @@ struct BwdParams {
     __nv_bfloat16* dst;   // dS^T [B,H,T(key),ldq] (scaled by `scale`)
     int B, T, H, ldq;
     float scale, scale_log2;
+    unsigned long long* trace;   // diagnostics (b200asr_attn_set_trace): 24 time stamps per CTA, null in normal use
 };
+static unsigned long long* g_attn_trace = nullptr;
+#define ATRACE(slot) do { if (p.trace) p.trace[(long long)((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 24 + (slot)] = (unsigned long long)clock64(); } while (0)
 
 __global__ void __launch_bounds__(B_THREADS, 1)
 mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
                   const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_do,
-                  const BwdParams p) {
+                  const __grid_constant__ CUtensorMap map_dst, const BwdParams p) {
+    if (threadIdx.x == 0) ATRACE(0);
     pdl_enter();  // launched with programmatic stream serialization: wait for the producers before touching global memory
+    if (threadIdx.x == 0) ATRACE(1);
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
@@ -322,9 +329,9 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
 
     if (k0 >= kl) {  // fully masked key block: dK = dV = 0, dS^T rows = 0
         if (warp >= 2) {
-            const int et = threadIdx.x - 64;  // 0..255: two threads per key row
+            const int et = threadIdx.x - 64;  // first 256: two threads per key row
             const int row = et >> 1, half = et & 1, key = k0 + row;
-            if (key < T) {
+            if (et < 2 * BK && key < T) {
                 __nv_bfloat16* dk = p.dqkv + (((long long)b * T + key) * 3 + 1) * D + h * DH + half * 32;
                 __nv_bfloat16* dv = dk + D;
 #pragma unroll
@@ -344,6 +351,7 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
         tma_prefetch_desc(&map_v);
         tma_prefetch_desc(&map_q);
         tma_prefetch_desc(&map_do);
+        tma_prefetch_desc(&map_dst);
         mbar_init(kv_full, 1);
         for (int s = 0; s < B_STAGES; ++s) {
             mbar_init(qd_full(s), 1);
@@ -351,9 +359,9 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(sdp_full(s), 1);
-            mbar_init(sdp_free(s), 8);
-            mbar_init(pds_ready(s), 8);
-            mbar_init(pds_free(s), 1);
+            mbar_init(sdp_free(s), B_EW);
+            mbar_init(pds_ready(s), B_EW);
+            mbar_init(pds_free(s), 2);   // the MMAs that read P^T / dS^T have completed + the dS^T tile has been stored
         }
         mbar_init(dkv_done, 1);
         fence_barrier_init();
@@ -368,11 +376,12 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
         dsum_s[q] = (q < T) ? p.dsum[bh * T + q] : 0.f;
     }
     __syncthreads();
+    if (threadIdx.x == 0) ATRACE(2);
     // TMEM columns: S^T[s] at 64 s, dP^T[s] at 128 + 64 s, dV at 256, dK at 320
     const uint32_t tm_dv = tmem_base + 256, tm_dk = tmem_base + 320;
 
     if (warp == 0) {
-        if (lane == 0) {
+        if (elect_one_sync()) {
             mbar_expect_tx(kv_full, B_KV_BYTES);
             tma_load_4d(sK, &map_k, kv_full, 0, k0, h, b);
             tma_load_4d(sV, &map_v, kv_full, 0, k0, h, b);
@@ -385,9 +394,10 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        if (elect_one_sync()) {
             const uint32_t idesc_kk = make_idesc_bf16(BK, BQ, 0, 0);  // S^T, dP^T: both operands K-major
             const uint32_t idesc_km = make_idesc_bf16(BK, DH, 0, 1);  // dV, dK: B operand MN-major
+            const uint64_t desc_k = make_smem_desc(sK, 16, 1024), desc_v = make_smem_desc(sV, 16, 1024);
             auto issue_sdp = [&](int i) {
                 const int s = i % B_STAGES;
                 mbar_wait(qd_full(s), (i / B_STAGES) & 1);
@@ -395,63 +405,83 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
                 tc_fence_after();
                 const uint32_t sq = sQD + s * B_QD_BYTES, sdo = sq + BQ * DH * 2;
                 const uint32_t t_st = tmem_base + (uint32_t)((i & 1) * BQ), t_dp = tmem_base + 128 + (uint32_t)((i & 1) * BQ);
+                const uint64_t dq = make_smem_desc(sq, 16, 1024), ddo = make_smem_desc(sdo, 16, 1024);
 #pragma unroll
-                for (int k = 0; k < DH / 16; ++k)
-                    umma_bf16(t_st, make_smem_desc(sK + k * 32, 16, 1024), make_smem_desc(sq + k * 32, 16, 1024), idesc_kk,
-                              k > 0 ? 1u : 0u);
-#pragma unroll
-                for (int k = 0; k < DH / 16; ++k)
-                    umma_bf16(t_dp, make_smem_desc(sV + k * 32, 16, 1024), make_smem_desc(sdo + k * 32, 16, 1024), idesc_kk,
-                              k > 0 ? 1u : 0u);
+                for (int k = 0; k < DH / 16; ++k) {
+                    umma_bf16(t_st, smem_desc_advance(desc_k, 2 * k), smem_desc_advance(dq, 2 * k), idesc_kk, k > 0 ? 1u : 0u);
+                    umma_bf16(t_dp, smem_desc_advance(desc_v, 2 * k), smem_desc_advance(ddo, 2 * k), idesc_kk, k > 0 ? 1u : 0u);
+                }
                 umma_commit(sdp_full(i & 1));
             };
             mbar_wait(kv_full, 0);
+            ATRACE(3);
             issue_sdp(0);
             for (int i = 0; i < nqb; ++i) {
                 if (i + 1 < nqb) issue_sdp(i + 1);
+                if (i == 2) ATRACE(16);
                 mbar_wait(pds_ready(i & 1), (i >> 1) & 1);
                 tc_fence_after();
+                if (i == 2) ATRACE(17);
                 const int s = i % B_STAGES;
                 const uint32_t sq = sQD + s * B_QD_BYTES, sdo = sq + BQ * DH * 2;
                 const uint32_t spt = sPT + (i & 1) * B_PT_BYTES, sdst = sPT + (2 + (i & 1)) * B_PT_BYTES;
+                const uint64_t dpt = make_smem_desc(spt, 16, 1024), ddst = make_smem_desc(sdst, 16, 1024);
+                const uint64_t ddo = make_smem_desc(sdo, 8192, 1024), dq = make_smem_desc(sq, 8192, 1024);   // MN-major B
 #pragma unroll
-                for (int k = 0; k < BQ / 16; ++k)
-                    umma_bf16(tm_dv, make_smem_desc(spt + k * 32, 16, 1024), make_smem_desc(sdo + k * 2048, 8192, 1024),
-                              idesc_km, (i > 0 || k > 0) ? 1u : 0u);
-#pragma unroll
-                for (int k = 0; k < BQ / 16; ++k)
-                    umma_bf16(tm_dk, make_smem_desc(sdst + k * 32, 16, 1024), make_smem_desc(sq + k * 2048, 8192, 1024),
-                              idesc_km, (i > 0 || k > 0) ? 1u : 0u);
+                for (int k = 0; k < BQ / 16; ++k) {
+                    umma_bf16(tm_dv, smem_desc_advance(dpt, 2 * k), smem_desc_advance(ddo, 128 * k), idesc_km, (i > 0 || k > 0) ? 1u : 0u);
+                    umma_bf16(tm_dk, smem_desc_advance(ddst, 2 * k), smem_desc_advance(dq, 128 * k), idesc_km, (i > 0 || k > 0) ? 1u : 0u);
+                }
                 umma_commit(qd_empty(s));
                 umma_commit(pds_free(i & 1));
+                if (i == 2) ATRACE(18);
             }
             umma_commit(dkv_done);
+            ATRACE(4);
+        }
+    } else if (warp == 2 + B_EW) {
+        // dS^T (the A operand tile the element-wise warps just built, 128 keys x 64 queries, swizzle-128B) -> HBM as ONE TMA
+        // store per query block.  Row-per-thread global stores from the element-wise warps touched 32 lines per instruction
+        // and cost ~800 clk of every ~2500 clk block (tools/attn_trace.py).
+        if (elect_one_sync()) {
+            for (int i = 0; i < nqb; ++i) {
+                const int slot = i & 1;
+                mbar_wait(pds_ready(slot), (i >> 1) & 1);
+                tma_store_4d(&map_dst, sPT + (2 + slot) * B_PT_BYTES, i * BQ, k0, (int)bh, 0);
+                bulk_commit_group();
+                bulk_wait_group_read<0>();
+                mbar_arrive(pds_free(slot));
+            }
         }
     } else {
-        const int quarter = warp & 3, half = (warp - 2) >> 2;
+        constexpr int CG = 4 * BQ / B_EW;   // query columns per thread and block (16)
+        static_assert(CG == 16 && DH == 64, "element-wise layout");
+        const int quarter = warp & 3, cg = (warp - 2) >> 2;   // TMEM lane quarter, column group
         const int row = quarter * 32 + lane;
         const int key = k0 + row;
         const bool key_valid = key < kl;
-        const int et = threadIdx.x - 64;  // 0..255
         const uint32_t tlane = tmem_base + ((uint32_t)(quarter * 32) << 16);
         const float c2 = p.scale_log2, sc = p.scale;
-        __nv_bfloat16* dst_row = p.dst + (bh * T + key) * ldq;
         for (int i = 0; i < nqb; ++i) {
             const int slot = i & 1;
+            const bool trc = threadIdx.x == 64 && (i == 2 || i == 3);
+            if (trc && i == 2) ATRACE(8);
             mbar_wait(sdp_full(slot), (i >> 1) & 1);
             tc_fence_after();
-            uint32_t s[32], dp[32];
-            tmem_ld_32x32(tlane + (uint32_t)(slot * BQ + half * 32), s);
-            tmem_ld_32x32(tlane + 128 + (uint32_t)(slot * BQ + half * 32), dp);
+            if (trc) ATRACE(i == 2 ? 9 : 15);
+            uint32_t s[CG], dp[CG];
+            tmem_ld_32x16(tlane + (uint32_t)(slot * BQ + cg * CG), s);
+            tmem_ld_32x16(tlane + 128 + (uint32_t)(slot * BQ + cg * CG), dp);
             tmem_ld_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(sdp_free(slot));
-            uint32_t pp[16], dd[16];
-            const float4* l2v = reinterpret_cast<const float4*>(lse2_s + i * BQ + half * 32);  // broadcast 16-byte reads
-            const float4* dqv = reinterpret_cast<const float4*>(dsum_s + i * BQ + half * 32);
+            if (trc && i == 2) ATRACE(10);
+            uint32_t pp[CG / 2], dd[CG / 2];
+            const float4* l2v = reinterpret_cast<const float4*>(lse2_s + i * BQ + cg * CG);  // broadcast 16-byte reads
+            const float4* dqv = reinterpret_cast<const float4*>(dsum_s + i * BQ + cg * CG);
 #pragma unroll
-            for (int c = 0; c < 32; c += 4) {
+            for (int c = 0; c < CG; c += 4) {
                 const float4 l4 = l2v[c >> 2], d4 = dqv[c >> 2];
                 float p0 = fast_exp2(fmaf(__uint_as_float(s[c]), c2, -l4.x));
                 float p1 = fast_exp2(fmaf(__uint_as_float(s[c + 1]), c2, -l4.y));
@@ -467,39 +497,37 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
                 dd[c >> 1] = bf2_pack(d0, d1);
                 dd[(c >> 1) + 1] = bf2_pack(d2, d3);
             }
+            if (trc && i == 2) ATRACE(11);
             if (i >= 2) mbar_wait(pds_free(slot), ((i >> 1) - 1) & 1);
+            if (trc && i == 2) ATRACE(12);
             uint8_t* gpt = genPT + slot * B_PT_BYTES;
             uint8_t* gds = genPT + (2 + slot) * B_PT_BYTES;
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const uint32_t off = sw128_offset(row, half * 4 + c);
+            for (int c = 0; c < CG / 8; ++c) {
+                const uint32_t off = sw128_offset(row, cg * (CG / 8) + c);
                 *reinterpret_cast<uint4*>(gpt + off) = make_uint4(pp[4 * c], pp[4 * c + 1], pp[4 * c + 2], pp[4 * c + 3]);
                 *reinterpret_cast<uint4*>(gds + off) = make_uint4(dd[4 * c], dd[4 * c + 1], dd[4 * c + 2], dd[4 * c + 3]);
             }
-            if (key < T) {
-                const int qb = i * BQ + half * 32;
-#pragma unroll
-                for (int c = 0; c < 4; ++c)
-                    if (qb + 8 * c + 8 <= ldq)
-                        *reinterpret_cast<uint4*>(dst_row + qb + 8 * c) =
-                            make_uint4(dd[4 * c], dd[4 * c + 1], dd[4 * c + 2], dd[4 * c + 3]);
-            }
+            if (trc && i == 2) ATRACE(13);
             fence_proxy_async();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(pds_ready(slot));
+            if (trc && i == 2) ATRACE(14);
         }
+        if (threadIdx.x == 64) ATRACE(5);
         mbar_wait(dkv_done, 0);
         tc_fence_after();
-        uint32_t a[32], c_[32];
-        tmem_ld_32x32(tlane + 256 + (uint32_t)(half * 32), a);   // dV
-        tmem_ld_32x32(tlane + 320 + (uint32_t)(half * 32), c_);  // dK
+        if (threadIdx.x == 64) ATRACE(6);
+        uint32_t a[CG], c_[CG];   // this thread's 16 of the 64 head-dim columns of dV / dK
+        tmem_ld_32x16(tlane + 256 + (uint32_t)(cg * CG), a);   // dV
+        tmem_ld_32x16(tlane + 320 + (uint32_t)(cg * CG), c_);  // dK
         tmem_ld_wait();
         if (key < T) {
-            __nv_bfloat16* dk = p.dqkv + (((long long)b * T + key) * 3 + 1) * D + h * DH + half * 32;
+            __nv_bfloat16* dk = p.dqkv + (((long long)b * T + key) * 3 + 1) * D + h * DH + cg * CG;
             __nv_bfloat16* dv = dk + D;
 #pragma unroll
-            for (int c = 0; c < 32; c += 8) {
+            for (int c = 0; c < CG; c += 8) {
                 uint4 v;
                 v.x = bf2_pack(__uint_as_float(a[c]), __uint_as_float(a[c + 1]));
                 v.y = bf2_pack(__uint_as_float(a[c + 2]), __uint_as_float(a[c + 3]));
@@ -520,6 +548,7 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
         tc_fence_after();
         tmem_dealloc(tmem_base, B_TMEM_COLS);
     }
+    if (threadIdx.x == 0) ATRACE(7);
 }
 
 // D[b,h,t] = sum_c dO[b,t,h,c] * O[b,t,h,c]   (one warp per frame, 8 lanes per head per 256-column sweep)
@@ -641,6 +670,7 @@ int mha_bwd_tc_launch(const void* qkv, const void* out, const void* dout, const 
     BwdParams p;
     p.lse = lse; p.dsum = dsum; p.klen = klen; p.dqkv = (__nv_bfloat16*)dqkv; p.dst = dst;
     p.B = B; p.T = T; p.H = H; p.ldq = ldq; p.scale = scale; p.scale_log2 = scale * LOG2E;
+    p.trace = g_attn_trace;
     dim3 grid(ceil_div(T, BK), H, B);
     const int Tpad = ceil_div(T, BQ) * BQ;
     const size_t smem = (size_t)B_SMEM_FIXED + 2 * (size_t)Tpad * sizeof(float);
@@ -648,7 +678,15 @@ int mha_bwd_tc_launch(const void* qkv, const void* out, const void* dout, const 
         set_error("mha_bwd(tcgen05): T=%d too long for the staged softmax statistics", T);
         return B200ASR_ERR_UNSUPPORTED;
     }
-    launch_pdl(mha_bwd_tc_kernel, grid, dim3(B_THREADS), smem, st, mk, mv, mq, mdo, p);
+    CUtensorMap mdst;
+    {
+        const cuuint64_t dims[4] = {(cuuint64_t)ldq, (cuuint64_t)T, (cuuint64_t)B * H, 1};
+        const cuuint64_t strides[3] = {(cuuint64_t)ldq * 2, (cuuint64_t)T * ldq * 2, (cuuint64_t)B * H * T * ldq * 2};
+        const cuuint32_t box[4] = {BQ, BK, 1, 1};
+        rc = encode_map_bf16_4d(&mdst, dst, dims, strides, box, "mha_bwd(tcgen05) dS^T");
+        if (rc) return rc;
+    }
+    launch_pdl(mha_bwd_tc_kernel, grid, dim3(B_THREADS), smem, st, mk, mv, mq, mdo, mdst, p);
     rc = check_launch("mha_bwd_tcgen05");
     if (rc) return rc;
     // dQ[q, n] = sum_key dS^T[key, q] K[key, n]   (dS already carries the softmax scale)
@@ -662,3 +700,11 @@ int mha_bwd_tc_launch(const void* qkv, const void* out, const void* dout, const 
 }
 
 }  // namespace b200asr
+
+// diagnostics: while `buf` (device memory, 24 u64 per CTA of the backward grid) is set, mha_bwd records per-CTA SM-clock
+// time stamps: 0 entry, 1 dependency wait done, 2 set-up done, 3 K/V landed, 4 last MMA issued, 5 element-wise loop done,
+// 6 dK/dV complete, 7 exit; query block 2: 8..14 element-wise phases, 15 block 3 ready, 16..18 MMA issuer
+extern "C" int b200asr_attn_set_trace(void* buf) {
+    b200asr::attn::g_attn_trace = (unsigned long long*)buf;
+    return 0;
+}

@@ -8,6 +8,7 @@
 #include <string.h>
 
 #include <mutex>
+#include <type_traits>
 
 #include "common.cuh"
 #include "gemm.h"
@@ -36,11 +37,14 @@ template <int BN, int NCTA = 1> struct Cfg {
     static constexpr int NP = NCTA >= 2 ? 2 : 1;  // CTAs per MMA (cta_group)
     static constexpr int B_STAGE_BYTES = (BN / NP) * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-    // Staged epilogue: every epilogue warp owns 8 KB of shared memory -- two 32x32 output chunks (TMA-stored, so the
-    // global writes are full coalesced rows and asynchronous) and two chunks of the second epilogue tensor (the GELU
-    // pre-activation written next to the output, or the residual / gelu' operand TMA-prefetched two chunks ahead).
-    // Measured before this (profiles/r01_gemm_epilogue_ablation.txt): the row-per-thread global accesses cost
-    // 9 us of a 34 us QKV GEMM and 19 us of a 52 us FFN data-gradient GEMM.
+    // Staged epilogue: every epilogue warp owns 8 KB of shared memory -- two chunks of 32 rows x 128 bytes (64 bf16 / 32 fp32
+    // columns, swizzle-128B).  Results are TMA-stored from there (full coalesced rows, asynchronous); a residual / gelu'
+    // operand is TMA-prefetched into the same chunk a whole tile ahead and overwritten in place by the result; the
+    // forward FFN GEMM uses the pair as (result, gelu').  Measured before the staging (profiles/
+    // r01_gemm_epilogue_ablation.txt): the row-per-thread global accesses cost 9 us of a 34 us QKV GEMM and 19 us of a
+    // 52 us FFN data-gradient GEMM; per-CTA time stamps (tools/gemm_trace.py, profiles/r01_gemm_trace.txt) then showed the
+    // accumulator drain itself at 25% of a single-tile GEMM, which is what the 64-column chunks, the compile-time
+    // epilogue modes and the register-held bias slice are for.
     static constexpr bool EPI_TMA = !(NCTA == 1 && BN == 256);  // 48 KB stages leave no room there
     static constexpr int EPI_WARP_BYTES = 8192;
     static constexpr int EPI_BYTES = EPI_TMA ? 8 * EPI_WARP_BYTES : 0;
@@ -77,6 +81,7 @@ struct Params {
     long long bias_sb0;  // bias element stride per batch0 index (grouped conv: channels per group)
     int epi_tma;         // 1: staged epilogue (TMA store of C [+ second tensor]); 0: direct row-per-thread accesses
     int x_kind;          // second epilogue tensor of the staged path: 0 none, 1 aux_out (store), 2 residual, 3 aux_in (gelu')
+    int epi_mode;        // staged path: 8 * ACTM + XK (see the epilogue)
     int dbg;             // experiment knobs (B200ASR_GEMM_DBG): 1 skip GELU math, 2 skip aux/residual traffic, 4 skip the C store
     unsigned long long* trace;  // diagnostics (b200asr_gemm_set_trace): 12 time stamps per CTA, null in normal use
 };
@@ -196,11 +201,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
             mbar_init(tfull_bar(s), 1);
             mbar_init(tempty_bar(s), 8 * NP);  // one arrival per epilogue warp (of both CTAs of a pair)
         }
-        for (int s = 0; s < 32; ++s) mbar_init(in_bar(s >> 2, s & 3), 1);
         if (p.epi_tma) {
             tma_prefetch_desc(&tma_c);
             if (p.x_kind) tma_prefetch_desc(&tma_x);
         }
+        fence_barrier_init();
+    }
+    if (warp == 2) {   // the epilogue warps' operand-load barriers, one per lane
+        mbar_init(in_bar(lane >> 2, lane & 3), 1);
         fence_barrier_init();
     }
     if (warp == 1) {
@@ -224,7 +232,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 
     if (warp == 0) {
         // ===================== TMA producer =====================
-        if (lane == 0) {
+        if (elect_one_sync()) {   // (not `lane == 0`: elect.sync keeps the region warp-uniform for the compiler, so the
+            // TMA / MMA instructions take their uniform-register operands without a per-instruction election loop)
             int stage = 0;
             uint32_t phase = 0;
             for (long long tile = worker; tile < p.num_tiles; tile += nworkers) {
@@ -304,7 +313,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0 && rank == 0) {
+        if (rank == 0 && elect_one_sync()) {
             // instruction descriptor: D fp32, A/B bf16, majors, N>>3, M>>4 (cute::UMMA::InstrDescriptor)
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
                                    ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
@@ -370,212 +379,236 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         if (staged) {
             if constexpr (C_::EPI_TMA) {
                 // ---------- staged epilogue: TMEM -> registers -> swizzled shared chunk -> TMA store ----------
+                // A chunk is 32 rows x 128 bytes (64 bf16 / 32 fp32 columns, swizzle-128B): two (bf16) or one (fp32)
+                // 32-column TMEM reads feed one fence + one TMA store.  The math is specialised at compile time per
+                // epilogue mode (ACTM, XK) so that every chunk is straight-line code:
+                //   ACTM 1: GELU on the result.   XK 0: no second tensor, 1: second output = the pre-activation,
+                //   2: result GELU, second output gelu' (forward of the FFN), 3: + residual, 4: * stored gelu',
+                //   5: * gelu'(stored pre-activation).
                 constexpr int ES = (int)sizeof(TC);
-                constexpr int CHUNK_BYTES = 32 * 32 * ES;          // 2 KB (bf16) / 4 KB (fp32)
-                constexpr int V16 = 32 * ES / 16;                   // 16-byte vectors per chunk row
-                constexpr int SWZ = V16 - 1;                        // swizzle-64B (bf16) / swizzle-128B (fp32) XOR mask
-                constexpr int ROW_SHIFT = (ES == 2) ? 1 : 0;        // 64-byte rows: two rows share a 128-byte line
+                constexpr int GC = (ES == 2) ? 2 : 1;              // 32-column accumulator groups per chunk
+                constexpr int CW = 32 * GC;                         // chunk width in columns
+                constexpr int CHUNK_BYTES = 4096;
+                constexpr bool SOLO = (BN / 2) < CW;                // BN = 64, bf16: the tile is one chunk wide
+                constexpr int CPT = SOLO ? 1 : (BN / 2) / CW;       // chunks per tile drained by this warp
+                constexpr int NSLOT = C_::EPI_WARP_BYTES / CHUNK_BYTES;
+                static_assert(NSLOT == 2, "two staging chunks per epilogue warp");
                 const int ew = warp - 2;
                 const uint32_t my = epi_smem + (uint32_t)ew * C_::EPI_WARP_BYTES;
                 uint8_t* my_gen = smem_gen + C_::STAGES * C_::STAGE_BYTES + ew * C_::EPI_WARP_BYTES;
-                // Per warp NSLOT staging chunks (bf16: 4 x 2 KB, fp32: 2 x 4 KB).  Chunk `item` uses
-                //   no second tensor:       slot item % NSLOT for the result;
-                //   residual / gelu' input: slot item % 4, TMA-loaded up to three chunks (a whole tile) ahead, the result is
-                //                           written IN PLACE over the operand (each lane owns its row) and stored from there;
-                //   second output (aux):    slots 2 (item % 2) (result) and 2 (item % 2) + 1 (pre-activation / gelu').
-                constexpr int NSLOT = C_::EPI_WARP_BYTES / CHUNK_BYTES;
-                static_assert(NSLOT == (ES == 2 ? 4 : 2), "staging chunks per epilogue warp");
-                const int x_kind = (ES == 2) ? p.x_kind : 0;
-                const bool has_in = x_kind >= 2;
-                const int sw = (lane >> ROW_SHIFT) & SWZ;           // this lane's (row's) swizzle term
-                const uint32_t row_off_s = (uint32_t)lane * (32 * ES);
+                const int sw = lane & 7;                            // swizzle-128B: 16-byte unit u of row r sits at u ^ (r & 7)
                 const int ntiles = (int)p.num_tiles, tpb = (int)tiles_per_batch;
+                const int col0 = SOLO ? 0 : chalf * CPT * CW;       // first tile column of this warp's part
+                const bool works = !SOLO || chalf == 0;
 
-                // first row / first column of this warp's part of a tile (32-bit arithmetic: this runs once per tile on
-                // the accumulator-drain critical path)
+                // first row / first column of this warp's part of a tile (32-bit arithmetic: once per tile)
                 auto tile_coords = [&](int tile, int& m0w, int& nbase, int& b0, int& b1) {
                     const int z = tile / tpb, rem = tile - z * tpb;
                     const int mb = rem / p.tiles_n, nb = rem - mb * p.tiles_n;
                     b1 = z / p.batch0; b0 = z - b1 * p.batch0;
                     m0w = (MC ? (2 * mb + (int)pair) : mb) * TILE_M + (int)rank * BLOCK_M + quarter * 32;
-                    nbase = nb * BN + chalf * CHUNKS * 32;
+                    nbase = nb * BN + col0;
                 };
-                // lane 0: fetch the second-tensor chunk of work item `it` (= CHUNKS * tile ordinal + chunk) into its slot
+                // lane 0: fetch the second-tensor chunk of work item `it` (= CPT * tile ordinal + chunk) into slot it & 1
                 auto issue_in = [&](int it) {
-                    const int tile = worker + (it / CHUNKS) * nworkers;
+                    const int tile = worker + (it / CPT) * nworkers;
                     if (tile >= ntiles) return;
                     int m0w, nbase, b0, b1;
                     tile_coords(tile, m0w, nbase, b0, b1);
-                    const int n = nbase + (it % CHUNKS) * 32;
+                    const int n = nbase + (it % CPT) * CW;
                     if (n >= p.N || m0w >= p.M) return;
-                    const int sl = it & 3;
+                    const int sl = it & 1;
                     mbar_expect_tx(in_bar(ew, sl), CHUNK_BYTES);
                     tma_load_4d(my + sl * CHUNK_BYTES, &tma_x, in_bar(ew, sl), n, m0w, b0, b1);
                 };
-                uint32_t in_phase = 0;   // bit s: parity of slot s's load barrier
-                if (has_in && lane == 0) {
-#pragma unroll 1
-                    for (int it = 0; it < 4; ++it) issue_in(it);
-                }
-                int item = 0;
-                for (int tile = worker; tile < ntiles; tile += nworkers) {
-                    int m0w, nbase, b0, b1;
-                    tile_coords(tile, m0w, nbase, b0, b1);
-                    const float* bpt = p.bias ? p.bias + (long long)b0 * p.bias_sb0 + nbase : nullptr;
-                    // the tile's bias slice into L1 while the accumulator is still being computed
-                    if (bpt && lane * 4 < CHUNKS * 32 && nbase + lane * 4 < p.N)
-                        asm volatile("prefetch.global.L1 [%0];" ::"l"(bpt + lane * 4));
-                    mbar_wait(tfull_bar(acc), acc_phase);
-                    tc_fence_after();
-                    if (threadIdx.x == 64) TRACE(6);
-                    const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
-                    auto release_acc = [&]() {   // this warp has read its part of the accumulator: the MMA issuer may reuse it
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) {
-                            if constexpr (PAIR) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), leader));
-                            else mbar_arrive(tempty_bar(acc));
-                        }
-                    };
-#pragma unroll 1
-                    for (int cc = 0; cc < CHUNKS; ++cc, ++item) {
-                        const int n = nbase + cc * 32;
-                        if (n >= p.N || m0w >= p.M) {  // chunk entirely outside C: nothing staged, nothing waited for
-                            if (cc == CHUNKS - 1) release_acc();
-                            if (has_in && item >= 1 && lane == 0) {
-                                bulk_wait_group_read<0>();
-                                issue_in(item + 3);
+
+                auto run = [&](auto actm_c, auto xk_c) {
+                    constexpr int ACTM = decltype(actm_c)::value;
+                    constexpr int XK = decltype(xk_c)::value;
+                    constexpr bool HAS_IN = XK >= 3;      // operand chunk TMA-loaded into the slot, result written in place
+                    constexpr bool TWO_OUT = XK == 1 || XK == 2;   // result in slot 0, second output in slot 1
+                    int acc = 0;
+                    uint32_t acc_phase = 0, in_phase = 0;
+                    if (HAS_IN && works && elect_one_sync()) { issue_in(0); issue_in(1); }
+                    int item = 0;
+                    for (int tile = worker; tile < ntiles; tile += nworkers) {
+                        int m0w, nbase, b0, b1;
+                        tile_coords(tile, m0w, nbase, b0, b1);
+                        // this warp's bias slice: four columns per lane, broadcast by shuffles chunk by chunk (a global
+                        // load per chunk costs an L2 round trip on the critical path of the accumulator drain)
+                        const float* bpt = p.bias ? p.bias + (long long)b0 * p.bias_sb0 + nbase : nullptr;
+                        const bool bias_fast = bpt && works && (p.N - nbase >= CPT * CW) && (reinterpret_cast<uintptr_t>(bpt) & 15) == 0;
+                        float4 bq = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (bias_fast && lane * 4 < CPT * CW) bq = __ldg(reinterpret_cast<const float4*>(bpt) + lane);
+                        mbar_wait(tfull_bar(acc), acc_phase);
+                        tc_fence_after();
+                        if (threadIdx.x == 64) TRACE(6);
+                        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + col0);
+                        auto release_acc = [&]() {   // this warp has read its part of the accumulator: the MMA issuer may reuse it
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) {
+                                if constexpr (PAIR) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), leader));
+                                else mbar_arrive(tempty_bar(acc));
                             }
+                        };
+                        if (!works) {
+                            release_acc();
+                            if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
                             continue;
                         }
-                        const int sl = (x_kind == 1) ? 2 * (item & 1) : (item & (NSLOT - 1));
-                        uint32_t r[32];
-                        tmem_ld_32x32(taddr + (chalf * CHUNKS + cc) * 32, r);
-                        tmem_ld_wait();
-                        if (cc == CHUNKS - 1) release_acc();
-                        const bool trc = cc == 1 && threadIdx.x == 64;
-                        if (trc) TRACE(12);
-                        if (!has_in) {   // the stores that last read this chunk's slot(s) are done with them
-                            if (lane == 0) {
-                                if (ES == 2 && x_kind == 0) bulk_wait_group_read<3>();
-                                else bulk_wait_group_read<1>();
-                            }
-                            __syncwarp();
-                        }
-                        if (trc) TRACE(13);
-                        float2 v2[16];   // the 32 accumulator columns of this lane's row, as pairs for the packed fp32 pipe
-                        float* v = reinterpret_cast<float*>(v2);
-                        const float2 al = make_float2(p.alpha, p.alpha);
-                        const float* bp = bpt ? bpt + cc * 32 : nullptr;
-                        if (bp && p.N - n >= 32 && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
-#pragma unroll
-                            for (int j = 0; j < 32; j += 4) {
-                                const float4 bv = __ldg(reinterpret_cast<const float4*>(bp + j));
-                                v2[j / 2] = __ffma2_rn(make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])), al, make_float2(bv.x, bv.y));
-                                v2[j / 2 + 1] = __ffma2_rn(make_float2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3])), al, make_float2(bv.z, bv.w));
-                            }
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; j += 2)
-                                v2[j / 2] = __fmul2_rn(make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])), al);
-                            if (bp) {
-                                const int nvalid = p.N - n;
-#pragma unroll
-                                for (int j = 0; j < 32; ++j)
-                                    if (j < nvalid) v[j] += __ldg(bp + j);
-                            }
-                        }
-                        if (trc) TRACE(14);
-                        if constexpr (ES == 2) {
-                            uint8_t* xrow = my_gen + (sl + (x_kind == 1 ? 1 : 0)) * CHUNK_BYTES + row_off_s;
-                            if (x_kind == 1) {  // second output next to the result: the pre-activation, or gelu'(it)
-                                float2 g2[16];
-                                const float2* src = v2;
-                                if (p.act == B200ASR_ACT_GELU_SAVE_GRAD) {
-#pragma unroll
-                                    for (int j = 0; j < 16; ++j) {
-                                        float2 gv;
-                                        gelu_both_fast2(v2[j], gv, g2[j]);
-                                        v2[j] = gv;
-                                    }
-                                    src = g2;
+#pragma unroll 1
+                        for (int cc = 0; cc < CPT; ++cc, ++item) {
+                            const int n = nbase + cc * CW;
+                            if (n >= p.N || m0w >= p.M) {  // chunk entirely outside C: nothing staged, nothing waited for
+                                if (cc == CPT - 1) release_acc();
+                                if (HAS_IN && item >= 1 && elect_one_sync()) {
+                                    bulk_wait_group_read<0>();
+                                    issue_in(item + 1);
                                 }
-                                const float* sf = reinterpret_cast<const float*>(src);
-#pragma unroll
-                                for (int q = 0; q < V16; ++q) {
-                                    uint4 o;
-                                    o.x = bf2_pack(sf[8 * q], sf[8 * q + 1]); o.y = bf2_pack(sf[8 * q + 2], sf[8 * q + 3]);
-                                    o.z = bf2_pack(sf[8 * q + 4], sf[8 * q + 5]); o.w = bf2_pack(sf[8 * q + 6], sf[8 * q + 7]);
-                                    *reinterpret_cast<uint4*>(xrow + ((q ^ sw) << 4)) = o;
-                                }
+                                continue;
                             }
-                            if ((p.act == B200ASR_ACT_GELU || (p.act == B200ASR_ACT_GELU_SAVE_GRAD && x_kind != 1)) && !(p.dbg & 32)) {
-#pragma unroll
-                                for (int j = 0; j < 16; ++j) v2[j] = gelu_fast2(v2[j]);
-                            }
-                            if (has_in) {
-                                mbar_wait(in_bar(ew, sl), (in_phase >> sl) & 1u);
+                            const int sl = TWO_OUT ? 0 : (item & 1);
+                            uint8_t* orow = my_gen + sl * CHUNK_BYTES + lane * 128;      // result row (= operand row when HAS_IN)
+                            [[maybe_unused]] uint8_t* xrow = my_gen + (TWO_OUT ? 1 : sl) * CHUNK_BYTES + lane * 128;
+                            if constexpr (HAS_IN) {
+                                mbar_wait(in_bar(ew, sl), (in_phase >> sl) & 1u);   // operand landed (issued after the slot's last store)
                                 in_phase ^= 1u << sl;
-                                if (trc) TRACE(15);
+                            } else {
+                                if (lane == 0) {   // the stores that last read this chunk's slot(s) are done with them
+                                    if (TWO_OUT) bulk_wait_group_read<0>();
+                                    else bulk_wait_group_read<1>();
+                                }
+                                __syncwarp();
+                            }
+                            uint32_t rr[GC][32];   // the chunk's accumulator columns: all TMEM reads in flight, one wait
 #pragma unroll
-                                for (int q = 0; q < V16; ++q) {
-                                    const uint4 t = *reinterpret_cast<const uint4*>(xrow + ((q ^ sw) << 4));
-                                    float u[8];
-                                    bf2_unpack(t.x, u[0], u[1]); bf2_unpack(t.y, u[2], u[3]);
-                                    bf2_unpack(t.z, u[4], u[5]); bf2_unpack(t.w, u[6], u[7]);
-                                    if (x_kind == 3 && p.mul_gelu_grad == 2) {
+                            for (int g = 0; g < GC; ++g) tmem_ld_32x32(taddr + cc * CW + g * 32, rr[g]);
+                            tmem_ld_wait();
+                            if (cc == CPT - 1) release_acc();
 #pragma unroll
-                                        for (int e = 0; e < 8; e += 2)
-                                            v2[4 * q + e / 2] = __fmul2_rn(v2[4 * q + e / 2], make_float2(u[e], u[e + 1]));
-                                    } else if (x_kind == 3 && !(p.dbg & 32)) {
+                            for (int g = 0; g < GC; ++g) {
+                                const uint32_t* r = rr[g];
+                                float2 v2[16];   // the 32 accumulator columns of this lane's row, as pairs for the packed fp32 pipe
+                                float* v = reinterpret_cast<float*>(v2);
+                                const float2 al = make_float2(p.alpha, p.alpha);
+                                if (bias_fast) {
+                                    const int src0 = (cc * CW + g * 32) >> 2;
 #pragma unroll
-                                        for (int e = 0; e < 8; e += 2)
-                                            v2[4 * q + e / 2] = __fmul2_rn(v2[4 * q + e / 2], gelu_grad_fast2(make_float2(u[e], u[e + 1])));
-                                    } else {
+                                    for (int j = 0; j < 32; j += 4) {
+                                        const int src = src0 + (j >> 2);
+                                        const float2 b01 = make_float2(__shfl_sync(0xffffffffu, bq.x, src), __shfl_sync(0xffffffffu, bq.y, src));
+                                        const float2 b23 = make_float2(__shfl_sync(0xffffffffu, bq.z, src), __shfl_sync(0xffffffffu, bq.w, src));
+                                        v2[j / 2] = __ffma2_rn(make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])), al, b01);
+                                        v2[j / 2 + 1] = __ffma2_rn(make_float2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3])), al, b23);
+                                    }
+                                } else {
 #pragma unroll
-                                        for (int e = 0; e < 8; e += 2)
-                                            v2[4 * q + e / 2] = __fadd2_rn(v2[4 * q + e / 2], make_float2(u[e], u[e + 1]));
+                                    for (int j = 0; j < 32; j += 2)
+                                        v2[j / 2] = __fmul2_rn(make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])), al);
+                                    if (bpt) {
+                                        const int nvalid = p.N - (n + g * 32);
+                                        const float* bp = bpt + cc * CW + g * 32;
+#pragma unroll
+                                        for (int j = 0; j < 32; ++j)
+                                            if (j < nvalid) v[j] += __ldg(bp + j);
                                     }
                                 }
-                            }
-                            uint8_t* orow = my_gen + sl * CHUNK_BYTES + row_off_s;   // (in place over the operand when has_in)
+                                if constexpr (ES == 2) {
+                                    auto pack8 = [](const float* f) {
+                                        uint4 o;
+                                        o.x = bf2_pack(f[0], f[1]); o.y = bf2_pack(f[2], f[3]);
+                                        o.z = bf2_pack(f[4], f[5]); o.w = bf2_pack(f[6], f[7]);
+                                        return o;
+                                    };
+                                    if constexpr (XK == 1) {          // second output: the pre-activation
 #pragma unroll
-                            for (int q = 0; q < V16; ++q) {
-                                uint4 o;
-                                o.x = bf2_pack(v[8 * q], v[8 * q + 1]); o.y = bf2_pack(v[8 * q + 2], v[8 * q + 3]);
-                                o.z = bf2_pack(v[8 * q + 4], v[8 * q + 5]); o.w = bf2_pack(v[8 * q + 6], v[8 * q + 7]);
-                                *reinterpret_cast<uint4*>(orow + ((q ^ sw) << 4)) = o;
-                            }
-                        } else {
-                            if (p.act != B200ASR_ACT_NONE) {
+                                        for (int q = 0; q < 4; ++q)
+                                            *reinterpret_cast<uint4*>(xrow + (((g * 4 + q) ^ sw) << 4)) = pack8(v + 8 * q);
+                                    }
+                                    if constexpr (XK == 2) {          // result gelu, second output gelu'
+                                        float2 g2[16];
 #pragma unroll
-                                for (int j = 0; j < 16; ++j) v2[j] = gelu_fast2(v2[j]);
-                            }
-                            uint8_t* orow = my_gen + sl * CHUNK_BYTES + row_off_s;
+                                        for (int j = 0; j < 16; ++j) {
+                                            float2 gv;
+                                            gelu_both_fast2(v2[j], gv, g2[j]);
+                                            v2[j] = gv;
+                                        }
+                                        const float* gf = reinterpret_cast<const float*>(g2);
 #pragma unroll
-                            for (int q = 0; q < V16; ++q)
-                                *reinterpret_cast<float4*>(orow + ((q ^ sw) << 4)) =
-                                    make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                                        for (int q = 0; q < 4; ++q)
+                                            *reinterpret_cast<uint4*>(xrow + (((g * 4 + q) ^ sw) << 4)) = pack8(gf + 8 * q);
+                                    } else if constexpr (ACTM == 1) {
+#pragma unroll
+                                        for (int j = 0; j < 16; ++j) v2[j] = gelu_fast2(v2[j]);
+                                    }
+                                    if constexpr (HAS_IN) {
+                                        uint4 t[4];
+#pragma unroll
+                                        for (int q = 0; q < 4; ++q) t[q] = *reinterpret_cast<const uint4*>(xrow + (((g * 4 + q) ^ sw) << 4));
+#pragma unroll
+                                        for (int q = 0; q < 4; ++q) {
+                                            float u[8];
+                                            bf2_unpack(t[q].x, u[0], u[1]); bf2_unpack(t[q].y, u[2], u[3]);
+                                            bf2_unpack(t[q].z, u[4], u[5]); bf2_unpack(t[q].w, u[6], u[7]);
+#pragma unroll
+                                            for (int e = 0; e < 8; e += 2) {
+                                                const float2 uu = make_float2(u[e], u[e + 1]);
+                                                float2& d = v2[4 * q + e / 2];
+                                                if constexpr (XK == 3) d = __fadd2_rn(d, uu);
+                                                else if constexpr (XK == 4) d = __fmul2_rn(d, uu);
+                                                else d = __fmul2_rn(d, gelu_grad_fast2(uu));
+                                            }
+                                        }
+                                    }
+#pragma unroll
+                                    for (int q = 0; q < 4; ++q)
+                                        *reinterpret_cast<uint4*>(orow + (((g * 4 + q) ^ sw) << 4)) = pack8(v + 8 * q);
+                                } else {
+                                    if constexpr (ACTM == 1) {
+#pragma unroll
+                                        for (int j = 0; j < 16; ++j) v2[j] = gelu_fast2(v2[j]);
+                                    }
+#pragma unroll
+                                    for (int q = 0; q < 8; ++q)
+                                        *reinterpret_cast<float4*>(orow + ((q ^ sw) << 4)) =
+                                            make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                                }
+                            }
+                            fence_proxy_async();
+                            __syncwarp();
+                            if (elect_one_sync()) {
+                                tma_store_4d(&tma_c, my + sl * CHUNK_BYTES, n, m0w, b0, b1);
+                                if constexpr (TWO_OUT) tma_store_4d(&tma_x, my + CHUNK_BYTES, n, m0w, b0, b1);
+                                bulk_commit_group();
+                                if (HAS_IN && item >= 1) {
+                                    // the store of chunk item-1 has read its slot: refill it with the operand of chunk item+1
+                                    bulk_wait_group_read<1>();
+                                    issue_in(item + 1);
+                                }
+                            }
+                            if (cc == 0 && threadIdx.x == 64) TRACE(10);
                         }
-                        if (trc) TRACE(16);
-                        fence_proxy_async();
-                        __syncwarp();
-                        if (trc) TRACE(17);
-                        if (lane == 0 && !(p.dbg & 16)) {
-                            tma_store_4d(&tma_c, my + sl * CHUNK_BYTES, n, m0w, b0, b1);
-                            if (x_kind == 1 && !(p.dbg & 64)) tma_store_4d(&tma_x, my + (sl + 1) * CHUNK_BYTES, n, m0w, b0, b1);
-                            bulk_commit_group();
-                        }
-                        if (trc) TRACE(18);
-                        if (has_in && item >= 1 && lane == 0) {
-                            // the store of chunk item-1 has read its slot: refill it with the operand of chunk item+3
-                            bulk_wait_group_read<1>();
-                            issue_in(item + 3);
-                        }
-                        if (trc) TRACE(19);
-                        if (cc == 0 && threadIdx.x == 64) TRACE(10);
+                        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
                     }
-                    if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+                };
+                using I0 = std::integral_constant<int, 0>;
+                using I1 = std::integral_constant<int, 1>;
+                if constexpr (ES == 4) {
+                    if (p.epi_mode & 8) run(I1{}, I0{});
+                    else run(I0{}, I0{});
+                } else {
+                    switch (p.epi_mode) {
+                        case 0: run(I0{}, I0{}); break;
+                        case 8: run(I1{}, I0{}); break;
+                        case 1: run(I0{}, I1{}); break;
+                        case 9: run(I1{}, I1{}); break;
+                        case 2: run(I0{}, std::integral_constant<int, 2>{}); break;
+                        case 3: run(I0{}, std::integral_constant<int, 3>{}); break;
+                        case 11: run(I1{}, std::integral_constant<int, 3>{}); break;
+                        case 4: run(I0{}, std::integral_constant<int, 4>{}); break;
+                        default: run(I0{}, std::integral_constant<int, 5>{}); break;
+                    }
                 }
                 if (threadIdx.x == 64) TRACE(11);
                 if (lane == 0) bulk_wait_group_read<0>();   // shared memory may be released; the writes complete with the grid
@@ -828,12 +861,11 @@ static bool make_epilogue_map(CUtensorMap* map, const void* base, int M, int N, 
     // unit batch dims still need a legal (multiple-of-16-byte) stride
     const cuuint64_t strides[3] = {(cuuint64_t)ld * ES, (cuuint64_t)(batch0 > 1 ? s0 * ES : 16),
                                    (cuuint64_t)(batch1 > 1 ? s1 * ES : 16)};
-    const cuuint32_t box[4] = {32, 32, 1, 1};
+    const cuuint32_t box[4] = {(cuuint32_t)(128 / ES), 32, 1, 1};   // one staged chunk: 32 rows of 128 bytes
     const cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = enc(map, ES == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4,
                      const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     ES == 2 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS;
 }
 
@@ -861,14 +893,22 @@ static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
     p.dbg = dbg;
     p.trace = g_gemm_trace;
     // staged epilogue when the kernel variant has the shared memory for it and at most ONE second tensor is involved
-    p.epi_tma = 0; p.x_kind = 0;
+    p.epi_tma = 0; p.x_kind = 0; p.epi_mode = 0;
     if (Cfg<BN, NCTA>::EPI_TMA && !(dbg & 8)) {
         const void* xs[3] = {a.aux_out, a.residual, a.mul_gelu_grad ? a.aux_in : nullptr};
         int nx = 0, kind = 0;
         for (int i = 0; i < 3; ++i)
             if (xs[i]) { ++nx; kind = i + 1; }
         const bool f32c = sizeof(TC) == 4;
-        if (nx <= 1 && !(f32c && nx) && make_epilogue_map<TC>(&mc, a.C, a.M, a.N, a.ldc, a.batch0, a.batch1, a.sc0, a.sc1) &&
+        // epilogue mode 8 * ACTM + XK; combinations outside the specialised list take the direct path
+        const bool gelu = a.act == B200ASR_ACT_GELU || a.act == B200ASR_ACT_GELU_SAVE_GRAD;
+        int mode = -1;
+        if (nx == 0) mode = gelu ? 8 : 0;
+        else if (nx == 1 && kind == 1) mode = a.act == B200ASR_ACT_GELU_SAVE_GRAD ? 2 : (a.act == B200ASR_ACT_GELU ? 9 : 1);
+        else if (nx == 1 && kind == 2) mode = gelu ? 11 : 3;
+        else if (nx == 1 && kind == 3 && !gelu) mode = a.mul_gelu_grad == 2 ? 4 : 5;
+        p.epi_mode = mode < 0 ? 0 : mode;
+        if (mode >= 0 && nx <= 1 && !(f32c && nx) && make_epilogue_map<TC>(&mc, a.C, a.M, a.N, a.ldc, a.batch0, a.batch1, a.sc0, a.sc1) &&
             (nx == 0 || make_epilogue_map<TC>(&mx, xs[kind - 1], a.M, a.N, a.ldc, a.batch0, a.batch1, a.sc0, a.sc1))) {
             p.epi_tma = 1;
             p.x_kind = kind;

@@ -46,9 +46,6 @@ for r in (reps // 2, reps - 1):
     print(f"   CTA lifetime median {(a[:, 8] - a[:, 1]).median():.0f} clk")
     print(f"   epilogue split: first chunk {(a[:, 10] - a[:, 6]).median():.0f}, chunks 2.. {(a[:, 11] - a[:, 10]).median():.0f}, "
           f"final store wait {(a[:, 7] - a[:, 11]).median():.0f} clk (medians)")
-    ph = ["tmem ld+wait", "store-read wait", "bias math", "residual wait", "math + smem write", "fence + syncwarp", "store issue", "next load issue"]
-    pts = [10, 12, 13, 14, 15, 16, 17, 18, 19]
-    print("   chunk 1 phases (medians): " + ", ".join(f"{n} {(a[:, pts[k + 1]] - a[:, pts[k]]).median():.0f}" for k, n in enumerate(ph)))
     for j, n in enumerate(names):
         col = seg[:, j]
         if j in (2, 3, 4):
