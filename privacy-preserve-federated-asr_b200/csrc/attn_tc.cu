@@ -110,6 +110,14 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
         mbar_init(p_ready, 4);
         mbar_init(pv_done, 1);
         fence_barrier_init();
+        // the operand loads start now and overlap the TMEM allocation
+        mbar_expect_tx(q_full, F_Q_BYTES);
+        tma_load_4d(sQ, &map_q, q_full, 0, q0, h, b);
+        for (int j = 0; j < nkb && j < F_STAGES; ++j) {
+            mbar_expect_tx(kv_full(j), F_KV_BYTES);
+            tma_load_4d(sKV + j * F_KV_BYTES, &map_k, kv_full(j), 0, j * FK, h, b);
+            tma_load_4d(sKV + j * F_KV_BYTES + FK * DH * 2, &map_v, kv_full(j), 0, j * FK, h, b);
+        }
     }
     if (warp == 1) tmem_alloc(tmem_slot, F_TMEM_COLS);
     tc_fence_before();
@@ -120,9 +128,7 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
 
     if (warp == 0) {
         if (elect_one_sync()) {
-            mbar_expect_tx(q_full, F_Q_BYTES);
-            tma_load_4d(sQ, &map_q, q_full, 0, q0, h, b);
-            for (int j = 0; j < nkb; ++j) {
+            for (int j = F_STAGES; j < nkb; ++j) {   // (Q and the first F_STAGES key blocks were requested during set-up)
                 const int s = j % F_STAGES;
                 mbar_wait(kv_empty(s), ((j / F_STAGES) & 1) ^ 1u);
                 mbar_expect_tx(kv_full(s), F_KV_BYTES);
@@ -365,6 +371,15 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
         }
         mbar_init(dkv_done, 1);
         fence_barrier_init();
+        // the operand loads start now: they overlap the TMEM allocation and the staging of the softmax statistics below
+        mbar_expect_tx(kv_full, B_KV_BYTES);
+        tma_load_4d(sK, &map_k, kv_full, 0, k0, h, b);
+        tma_load_4d(sV, &map_v, kv_full, 0, k0, h, b);
+        for (int i = 0; i < nqb && i < B_STAGES; ++i) {
+            mbar_expect_tx(qd_full(i), B_QD_BYTES);
+            tma_load_4d(sQD + i * B_QD_BYTES, &map_q, qd_full(i), 0, i * BQ, h, b);
+            tma_load_4d(sQD + i * B_QD_BYTES + BQ * DH * 2, &map_do, qd_full(i), 0, i * BQ, h, b);
+        }
     }
     if (warp == 1) tmem_alloc(tmem_slot, B_TMEM_COLS);
     tc_fence_before();
@@ -382,10 +397,7 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
 
     if (warp == 0) {
         if (elect_one_sync()) {
-            mbar_expect_tx(kv_full, B_KV_BYTES);
-            tma_load_4d(sK, &map_k, kv_full, 0, k0, h, b);
-            tma_load_4d(sV, &map_v, kv_full, 0, k0, h, b);
-            for (int i = 0; i < nqb; ++i) {
+            for (int i = B_STAGES; i < nqb; ++i) {   // (K, V and the first B_STAGES blocks were requested during set-up)
                 const int s = i % B_STAGES;
                 mbar_wait(qd_empty(s), ((i / B_STAGES) & 1) ^ 1u);
                 mbar_expect_tx(qd_full(s), B_QD_BYTES);

@@ -13,7 +13,7 @@
 namespace b200asr {
 
 namespace {
-constexpr int CTC_THREADS = 256;
+constexpr int CTC_THREADS = 512;  // lattice kernel: all warps build the posteriors, warps 0 / 1 run the recursions
 constexpr float NEG_INF = -INFINITY;
 constexpr int E_EMPTY = -(1 << 28);  // exponent of a lane whose states are all zero
 
@@ -142,6 +142,50 @@ __device__ void lattice_dispatch(int spl, const float* pr, int V, const int* tgt
 }
 }  // namespace
 
+// fp32 softmax of one frame by one warp (same operation order wherever it is used: the lattice kernel and the gradient
+// kernel must see bit-identical posteriors).  Up to 4 values per lane stay in registers: one global read of the row.
+template <typename T, typename F>
+__device__ __forceinline__ void frame_softmax(const T* __restrict__ xr, int V, int lane, F&& emit) {
+    float xv[4];
+    const bool cached = V <= 128;
+    float mx = NEG_INF;
+    if (cached) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int v = lane + 32 * k;
+            xv[k] = v < V ? to_f<T>(xr[v]) : NEG_INF;
+            mx = fmaxf(mx, xv[k]);
+        }
+    } else {
+        for (int v = lane; v < V; v += 32) mx = fmaxf(mx, to_f<T>(xr[v]));
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+    if (cached) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (lane + 32 * k < V) sum += expf(xv[k] - mx);
+    } else {
+        for (int v = lane; v < V; v += 32) sum += expf(to_f<T>(xr[v]) - mx);
+    }
+    sum = warp_sum(sum);
+    const float lz = mx + logf(sum);
+    if (cached) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (lane + 32 * k < V) emit(lane + 32 * k, expf(xv[k] - lz));
+    } else {
+        for (int v = lane; v < V; v += 32) emit(v, expf(to_f<T>(xr[v]) - lz));
+    }
+}
+
+// workspace per (head, utterance), in floats: alpha, beta mantissas [T][Sld], their lane exponents [T][32] int32 each,
+// then 8 floats of scalars (0: the raw negative log-likelihood for the gradient kernel)
+__host__ __device__ inline long long ctc_ws_stride(int T_, int Sld) { return 2LL * T_ * Sld + 2LL * T_ * 32 + 8; }
+
+// Lattice kernel: one CTA per (head, utterance).  Phase 1: posteriors of the utterance into shared memory (all warps);
+// phase 2: alpha (warp 0) and beta (warp 1) concurrently; then the loss.  The gradient is a separate, frame-parallel
+// kernel: inside this CTA it took 350 of 510 us (8 utterances = 8 busy SMs) at the sizes of the path.
 template <typename T>
 __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ logits, const int* __restrict__ targets,
                                                           const int* __restrict__ tgt_off, const int* __restrict__ tgt_len,
@@ -158,28 +202,17 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     const int Tb = max(0, min(in_len[b], T_));
     float* pr = sm;                                  // [T][V] softmax probabilities
     int* tgt_s = (int*)(pr + (size_t)T_ * V);        // [max_tgt + 1]
-    // [nwarps][V] occupancy sums in 2^-40 fixed point: integer atomics commute, so the gradient is reproducible
-    unsigned long long* acc_s = (unsigned long long*)(((uintptr_t)(tgt_s + max_tgt + 1) + 7) & ~(uintptr_t)7);
     const long long hb = (long long)head * B + b;
     const T* x = logits + hb * T_ * V;
-    // workspace per (head, utterance): alpha, beta mantissas [T][Sld] fp32, then their lane exponents [T][32] int32
-    float* alpha = ws + hb * (2LL * T_ * Sld + 2LL * T_ * 32);
+    float* alpha = ws + hb * ctc_ws_stride(T_, Sld);
     float* beta = alpha + (long long)T_ * Sld;
     int* ea = reinterpret_cast<int*>(beta + (long long)T_ * Sld);
     int* eb = ea + (long long)T_ * 32;
 
     for (int i = threadIdx.x; i < L; i += blockDim.x) tgt_s[i] = targets[tgt_off[b] + i];
     // ---- phase 1: fp32 softmax of the valid frames
-    for (int t = warp; t < Tb; t += nwarps) {
-        float mx = NEG_INF;
-        for (int v = lane; v < V; v += 32) mx = fmaxf(mx, to_f<T>(x[(long long)t * V + v]));
-        mx = warp_max(mx);
-        float sum = 0.f;
-        for (int v = lane; v < V; v += 32) sum += expf(to_f<T>(x[(long long)t * V + v]) - mx);
-        sum = warp_sum(sum);
-        const float lz = mx + logf(sum);
-        for (int v = lane; v < V; v += 32) pr[t * V + v] = expf(to_f<T>(x[(long long)t * V + v]) - lz);
-    }
+    for (int t = warp; t < Tb; t += nwarps)
+        frame_softmax<T>(x + (long long)t * V, V, lane, [&](int v, float pv) { pr[t * V + v] = pv; });
     __syncthreads();
     // ---- phase 2: alpha (warp 0) and beta (warp 1) concurrently
     if (Tb > 0) {
@@ -189,7 +222,7 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     __threadfence_block();
     __syncthreads();
     // ---- phase 3: loss and gradient
-    constexpr float LN2 = 0.6931471805599453f, LOG2E = 1.4426950408889634f;
+    constexpr float LN2 = 0.6931471805599453f;
     float nll = INFINITY;
     if (Tb > 0) {
         const long long r = (long long)(Tb - 1);
@@ -203,50 +236,81 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     }
     if (Tb == 0 && L == 0) nll = 0.f;  // empty input, empty target (torch convention)
     const bool infeasible = !(nll < INFINITY);
-    if (threadIdx.x == 0) loss[hb] = (infeasible && zero_infinity) ? 0.f : nll;
-    if (!grad) return;
-    const float gs = grad_scale ? grad_scale[hb] : 1.f;
+    if (threadIdx.x == 0) {
+        loss[hb] = (infeasible && zero_infinity) ? 0.f : nll;
+        reinterpret_cast<float*>(eb + (long long)T_ * 32)[0] = nll;   // raw value for the gradient kernel
+    }
+}
+
+// Gradient kernel: one warp per frame of one (head, utterance); reads alpha / beta of that frame, recomputes the frame's
+// posteriors (bit-identical to the lattice kernel's), accumulates the label occupancies in 2^-40 fixed point (integer
+// atomics commute: reproducible) and writes d nll / d logits.
+template <typename T>
+__global__ void __launch_bounds__(256) ctc_grad_kernel(const T* __restrict__ logits, const int* __restrict__ targets,
+                                                       const int* __restrict__ tgt_off, const int* __restrict__ tgt_len,
+                                                       const int* __restrict__ in_len, const float* __restrict__ grad_scale,
+                                                       T* __restrict__ grad, const float* __restrict__ ws, int n_heads,
+                                                       int B, int T_, int V, int max_tgt, int blank, int zero_infinity,
+                                                       int spl) {
+    extern __shared__ unsigned long long acc_all[];   // [8 warps][V] occupancy sums + [8][V] floats of posteriors
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long frame = (long long)blockIdx.x * 8 + warp;
+    if (frame >= (long long)n_heads * B * T_) return;
+    const long long hb = frame / T_;
+    const int t = (int)(frame - hb * T_);
+    const int b = (int)(hb % B);
+    const int Sld = 2 * max_tgt + 1;
+    const int L = min(tgt_len[b], max_tgt);
+    const int S = 2 * L + 1;
+    const int Tb = max(0, min(in_len[b], T_));
+    const float* alpha = ws + hb * ctc_ws_stride(T_, Sld);
+    const float* beta = alpha + (long long)T_ * Sld;
+    const int* ea = reinterpret_cast<const int*>(beta + (long long)T_ * Sld);
+    const int* eb = ea + (long long)T_ * 32;
+    const float nll = reinterpret_cast<const float*>(eb + (long long)T_ * 32)[0];
+    const bool infeasible = !(nll < INFINITY);
+    constexpr float LOG2E = 1.4426950408889634f;
     T* g = grad + hb * T_ * V;
-    unsigned long long* acc = acc_s + warp * V;
-    for (int t = warp; t < T_; t += nwarps) {
-        if (t >= Tb || infeasible) {
-            // torch: gradient of padded frames is 0; zero_infinity zeroes infeasible utterances (NaN otherwise)
-            for (int v = lane; v < V; v += 32)
-                g[(long long)t * V + v] = from_f<T>((t < Tb && !zero_infinity) ? NAN : 0.f);
-            continue;
+    if (t >= Tb || infeasible) {
+        // torch: gradient of padded frames is 0; zero_infinity zeroes infeasible utterances (NaN otherwise)
+        for (int v = lane; v < V; v += 32) g[(long long)t * V + v] = from_f<T>((t < Tb && !zero_infinity) ? NAN : 0.f);
+        return;
+    }
+    unsigned long long* acc = acc_all + warp * V;
+    float* pr = reinterpret_cast<float*>(acc_all + 8 * V) + warp * V;
+    const int* tgt = targets + tgt_off[b];
+    const float gs = grad_scale ? grad_scale[hb] : 1.f;
+    frame_softmax<T>(logits + (hb * T_ + t) * V, V, lane, [&](int v, float pv) { pr[v] = pv; });
+    const float* ar = alpha + (long long)t * Sld;
+    const float* br = beta + (long long)t * Sld;
+    const int* ear = ea + (long long)t * 32;
+    const int* ebr = eb + (long long)t * 32;
+    // log2 of alpha_t(s) * beta_t(s): mantissa product + the two lane exponents (the only logs of the kernel)
+    float mx = NEG_INF;
+    for (int s = lane; s < S; s += 32) {
+        const float ab = ar[s] * br[s];
+        if (ab > 0.f) mx = fmaxf(mx, log2f(ab) + (float)(ear[s / spl] + ebr[s / spl]));
+    }
+    mx = warp_max(mx);
+    for (int v = lane; v < V; v += 32) acc[v] = 0ull;
+    __syncwarp();
+    for (int s = lane; s < S; s += 32) {
+        const float ab = ar[s] * br[s];
+        if (ab > 0.f) {
+            const int l = (s & 1) ? tgt[(s - 1) >> 1] : blank;
+            const float rel2 = log2f(ab) + (float)(ear[s / spl] + ebr[s / spl]) - mx;  // <= 0
+            atomicAdd(&acc[l], (unsigned long long)(exp2f(rel2) * 1099511627776.0f));  // in [0, 2^40]
         }
-        const float* ar = alpha + (long long)t * Sld;
-        const float* br = beta + (long long)t * Sld;
-        const int* ear = ea + (long long)t * 32;
-        const int* ebr = eb + (long long)t * 32;
-        // log2 of alpha_t(s) * beta_t(s): mantissa product + the two lane exponents (the only logs of the kernel)
-        float mx = NEG_INF;
-        for (int s = lane; s < S; s += 32) {
-            const float ab = ar[s] * br[s];
-            if (ab > 0.f) mx = fmaxf(mx, log2f(ab) + (float)(ear[s / spl] + ebr[s / spl]));
-        }
-        mx = warp_max(mx);
-        for (int v = lane; v < V; v += 32) acc[v] = 0ull;
-        __syncwarp();
-        for (int s = lane; s < S; s += 32) {
-            const float ab = ar[s] * br[s];
-            if (ab > 0.f) {
-                const int l = (s & 1) ? tgt_s[(s - 1) >> 1] : blank;
-                const float rel2 = log2f(ab) + (float)(ear[s / spl] + ebr[s / spl]) - mx;  // <= 0
-                atomicAdd(&acc[l], (unsigned long long)(exp2f(rel2) * 1099511627776.0f));  // in [0, 2^40]
-            }
-        }
-        __syncwarp();
-        // d nll / d logit = softmax - sum_{s: lab = v} alpha_t(s) beta_t(s) / (P p_t(v)),  P = exp(-nll)
-        // (ATen ctc_loss backward form)
-        const float fac = exp2f(mx + nll * LOG2E) * (1.0f / 1099511627776.0f);
-        for (int v = lane; v < V; v += 32) {
-            const float pv = pr[t * V + v];
-            const float a = (float)acc[v];
-            const float occ = a > 0.f ? a * fac / fmaxf(pv, 1e-37f) : 0.f;
-            g[(long long)t * V + v] = from_f<T>((pv - occ) * gs);
-        }
-        __syncwarp();
+    }
+    __syncwarp();
+    // d nll / d logit = softmax - sum_{s: lab = v} alpha_t(s) beta_t(s) / (P p_t(v)),  P = exp(-nll)
+    // (ATen ctc_loss backward form)
+    const float fac = exp2f(mx + nll * LOG2E) * (1.0f / 1099511627776.0f);
+    for (int v = lane; v < V; v += 32) {
+        const float pv = pr[v];
+        const float a = (float)acc[v];
+        const float occ = a > 0.f ? a * fac / fmaxf(pv, 1e-37f) : 0.f;
+        g[(long long)t * V + v] = from_f<T>((pv - occ) * gs);
     }
 }
 
@@ -294,7 +358,7 @@ using namespace b200asr;
 extern "C" {
 
 size_t b200asr_ctc_workspace_bytes(int n_heads, int B, int T, int max_tgt_len) {
-    return (size_t)n_heads * B * (2 * (size_t)T * (2 * max_tgt_len + 1) + 2 * (size_t)T * 32) * sizeof(float);
+    return (size_t)n_heads * B * (size_t)ctc_ws_stride(T, 2 * max_tgt_len + 1) * sizeof(float);
 }
 
 int b200asr_ctc_fwd_bwd(const void* logits, const int* targets, const int* tgt_off, const int* tgt_len,
@@ -313,8 +377,7 @@ int b200asr_ctc_fwd_bwd(const void* logits, const int* targets, const int* tgt_o
         set_error("ctc: target length %d exceeds the supported 255", max_tgt_len);
         return B200ASR_ERR_UNSUPPORTED;
     }
-    const size_t smem = ((size_t)T_ * V + (max_tgt_len + 1)) * sizeof(float) + 8 +
-                        (size_t)(CTC_THREADS / 32) * V * sizeof(unsigned long long);
+    const size_t smem = ((size_t)T_ * V + (max_tgt_len + 1)) * sizeof(float) + 8;
     if (smem > 227 * 1024) {
         set_error("ctc: T*V=%d*%d log-probabilities do not fit in shared memory", T_, V);
         return B200ASR_ERR_UNSUPPORTED;
@@ -332,6 +395,18 @@ int b200asr_ctc_fwd_bwd(const void* logits, const int* targets, const int* tgt_o
         ctc_kernel<T><<<grid, CTC_THREADS, smem, st>>>((const T*)logits, targets, tgt_off, tgt_len, in_len, grad_scale, loss,
                                                         (T*)grad, (float*)workspace, B, T_, V, max_tgt_len, blank,
                                                         zero_infinity, spl);
+        if (grad) {
+            const long long frames = (long long)n_heads * B * T_;
+            const size_t gsm = (size_t)8 * V * (sizeof(unsigned long long) + sizeof(float));
+            if (gsm > 48 * 1024) {
+                set_error("ctc: vocabulary %d too large for the gradient kernel", V);
+                return B200ASR_ERR_UNSUPPORTED;
+            }
+            ctc_grad_kernel<T><<<(unsigned)((frames + 7) / 8), 256, gsm, st>>>((const T*)logits, targets, tgt_off, tgt_len, in_len,
+                                                                            grad_scale, (T*)grad, (const float*)workspace,
+                                                                            n_heads, B, T_, V, max_tgt_len, blank,
+                                                                            zero_infinity, spl);
+        }
     });
     return check_launch("ctc_fwd_bwd");
 }
