@@ -140,7 +140,7 @@ def _wgrad(ps, need, dy, x):
     sink, fresh = grad_sink(ps)
     if sink is None:
         return ops.linear_wgrad(dy, x)
-    with ops.on_side_stream(dy, x):
+    with ops.on_side_stream(dy, x, ordered=not fresh):
         ops.linear_wgrad(dy, x, out=sink.view(dy.shape[1], x.shape[1]), accumulate=not fresh)
     return None
 
@@ -156,6 +156,7 @@ def _bgrad(ps, need, dy):
         with ops.on_side_stream(dy):
             ops.colsum(dy, out=sink)
     else:
+        ops.join_side_stream()   # the sink's first write may still be in flight on a side stream
         ops.axpy_(sink, ops.colsum(dy))
     return None
 

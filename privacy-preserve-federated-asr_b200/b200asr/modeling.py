@@ -313,6 +313,17 @@ class _CTCBase(nn.Module):
 
     freeze_feature_extractor = freeze_feature_encoder
 
+    def save_pretrained(self, save_directory, state_dict=None):
+        """`pytorch_model.bin` + `config.json`, the files the reference's clients and server exchange (checkpoint.py)."""
+        from .checkpoint import save_pretrained
+        save_pretrained(self, save_directory, state_dict)
+
+    @classmethod
+    def from_pretrained(cls, directory, *model_args, **kw):
+        """Open a directory written by HF `save_pretrained` (or by `save_pretrained` above); see checkpoint.from_pretrained."""
+        from .checkpoint import from_pretrained
+        return from_pretrained(cls, directory, *model_args, **kw)
+
     def _ctc(self, logits, idx):
         c = self.config
         targets, tgt_off, tgt_len, in_len, lmax = idx
