@@ -252,32 +252,33 @@ __global__ void __launch_bounds__(512, 1) ln_bwd_kernel(const T* __restrict__ dy
 }
 
 // out[c] = sum_{p < nparts} partial[p * stride + c] for c < ncols_total; columns [0, cols) go to out0, [cols, 2 cols)
-// to out1, [2 cols, 3 cols) to out2.  One block = 32 columns x 8 warps; warp w sums partials w, w+8, ... (coalesced 128-byte rows, 4 loads
-// in flight per thread), then a fixed-order shared-memory combine: deterministic.
-__global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ partial, float* __restrict__ out0,
-                                                              float* __restrict__ out1, float* __restrict__ out2,
-                                                              int nparts, int cols, int ncols_total, int stride) {
-    __shared__ float red[8][33];
+// to out1, [2 cols, 3 cols) to out2.  One block = 32 columns x 32 warps; warp w sums partials w, w+32, ... (coalesced 128-byte
+// rows, all loads of a thread in flight together), then a fixed-order shared-memory combine: deterministic.
+__global__ void __launch_bounds__(1024) reduce_partials_kernel(const float* __restrict__ partial, float* __restrict__ out0,
+                                                               float* __restrict__ out1, float* __restrict__ out2,
+                                                               int nparts, int cols, int ncols_total, int stride) {
+    __shared__ float red[32][33];
     pdl_enter();
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + lane;
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    // 32 warps: warp w owns partials w, w+32, ...; at the 148 partials of this library that is one batch of <= 5 independent
+    // loads (one L2 round trip) where 8 warps needed five dependent batches -- this kernel is pure latency
+    float a[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
     if (c < ncols_total) {
-        int p = w;
-        for (; p + 24 < nparts; p += 32) {
-            a0 += partial[(long long)p * stride + c];
-            a1 += partial[(long long)(p + 8) * stride + c];
-            a2 += partial[(long long)(p + 16) * stride + c];
-            a3 += partial[(long long)(p + 24) * stride + c];
+        for (int p0 = w; p0 < nparts; p0 += 160) {
+#pragma unroll
+            for (int k = 0; k < 5; ++k) {
+                const int p = p0 + 32 * k;
+                if (p < nparts) a[k] += partial[(long long)p * stride + c];
+            }
         }
-        for (; p < nparts; p += 8) a0 += partial[(long long)p * stride + c];
     }
-    red[w][lane] = (a0 + a1) + (a2 + a3);
+    red[w][lane] = ((a[0] + a[1]) + (a[2] + a[3])) + a[4];
     __syncthreads();
     if (w == 0 && c < ncols_total) {
         float t = 0.f;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) t += red[i][lane];
+        for (int i = 0; i < 32; ++i) t += red[i][lane];
         if (c < cols) { if (out0) out0[c] = t; }
         else if (c < 2 * cols) { if (out1) out1[c - cols] = t; }
         else if (out2) out2[c - 2 * cols] = t;
@@ -446,7 +447,7 @@ int b200asr_layernorm_bwd(const void* dy, const void* s, const float* w, const f
     if (rc != B200ASR_OK) return rc;
     if (partial) {
         const int total = dx_colsum ? 3 * cols : 2 * cols;
-        launch_pdl(reduce_partials_kernel, dim3(ceil_div(total, 32)), dim3(256), 0, as_stream(stream), (const float*)partial, dw,
+        launch_pdl(reduce_partials_kernel, dim3(ceil_div(total, 32)), dim3(1024), 0, as_stream(stream), (const float*)partial, dw,
                    db, dx_colsum, (int)LN_BWD_BLOCKS, cols, total, 3 * cols);
         return check_launch("layernorm_bwd_reduce");
     }
@@ -485,7 +486,7 @@ int b200asr_colsum(const void* x, float* out, void* workspace, size_t workspace_
     }
     int rc = check_launch("colsum_partial");
     if (rc != B200ASR_OK) return rc;
-    launch_pdl(reduce_partials_kernel, dim3(ceil_div(cols, 32)), dim3(256), 0, as_stream(stream), (const float*)workspace, out,
+    launch_pdl(reduce_partials_kernel, dim3(ceil_div(cols, 32)), dim3(1024), 0, as_stream(stream), (const float*)workspace, out,
                (float*)nullptr, (float*)nullptr, nchunks, cols, cols, cols);
     return check_launch("colsum_reduce");
 }

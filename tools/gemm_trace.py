@@ -9,25 +9,32 @@ import torch
 from b200asr import ops
 from b200asr._lib import lib, check
 
-N, K = int(sys.argv[1]), int(sys.argv[2])
-M = int(sys.argv[3]) if len(sys.argv) > 3 else 3992
-reps = int(sys.argv[4]) if len(sys.argv) > 4 else 20
+WGRAD = "--wgrad" in sys.argv   # fp32 weight-gradient GEMM dW[N, K] = dy[M, N]^T x[M, K] instead of the bf16 linear
+argv = [a for a in sys.argv if a != "--wgrad"]
+N, K = int(argv[1]), int(argv[2])
+M = int(argv[3]) if len(argv) > 3 else 3992
+reps = int(argv[4]) if len(argv) > 4 else 20
 x = (torch.randn(M, K, device="cuda") * 0.1).bfloat16(); w = (torch.randn(N, K, device="cuda") * 0.1).bfloat16()
 b = torch.zeros(N, device="cuda"); y = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
 res = torch.randn(M, N, device="cuda").bfloat16()
 tr = torch.zeros(reps, 148 * 20, dtype=torch.int64, device="cuda")
+if WGRAD:
+    dy = (torch.randn(M, N, device="cuda") * 0.1).bfloat16(); dw = torch.empty(N, K, device="cuda")
+    run = lambda: ops.linear_wgrad(dy, x, out=dw)
+else:
+    run = lambda: ops.gemm_raw(x, w, y, M, N, K, K, K, N, True, True, bias=b, residual=res)
 for _ in range(5):
-    ops.gemm_raw(x, w, y, M, N, K, K, K, N, True, True, bias=b, residual=res)
+    run()
 torch.cuda.synchronize()
 t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 t0.record()
 for i in range(reps):
     check(lib.b200asr_gemm_set_trace(tr[i].data_ptr()), "set_trace")
-    ops.gemm_raw(x, w, y, M, N, K, K, K, N, True, True, bias=b, residual=res)
+    run()
 t1.record()
 check(lib.b200asr_gemm_set_trace(None), "set_trace")
 torch.cuda.synchronize()
-print(f"N={N} K={K} M={M}: {t0.elapsed_time(t1) / reps * 1e3:.1f} us per launch (back to back)")
+print(f"{'wgrad fp32 ' if WGRAD else ''}N={N} K={K} M={M}: {t0.elapsed_time(t1) / reps * 1e3:.1f} us per launch (back to back)")
 t = tr.cpu().view(reps, 148, 20)
 names = ["setup", "dep wait", "first stage landed", "mainloop issue", "acc complete after last issue", "epilogue", "teardown"]
 for r in (reps // 2, reps - 1):
