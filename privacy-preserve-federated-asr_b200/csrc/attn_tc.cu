@@ -11,7 +11,7 @@
 //               log2 domain, P_j -> bf16 -> swizzled shared memory (the A operand of the P V product),
 //               O rescale in TMEM only when a row maximum moved, final O / l -> bf16 -> HBM, log-sum-exp saved.
 // Backward (one CTA = 128 keys of one (utterance, head); queries stream through in blocks of 64):
-//   S^T = K_j Q_i^T and dP^T = V_j dO_i^T land in TMEM (double buffered); 8 element-wise warps rebuild
+//   S^T = K_j Q_i^T and dP^T = V_j dO_i^T land in TMEM (three accumulator pairs: two blocks ahead of the element-wise warps); 8 element-wise warps rebuild
 //   P^T = exp2(S^T c - lse) and dS^T = P^T (dP^T - D) scale, one key row per thread (no cross-thread reduction
 //   is needed in this orientation), write both as bf16 A operands into swizzled shared memory and dS^T to HBM;
 //   dV += P^T dO_i and dK += dS^T Q_i accumulate in TMEM over the whole query loop.  dQ = dS K is one batched
@@ -94,7 +94,7 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
         return;
     }
 
-    if (warp == 0 && lane == 0) {
+    if (warp == 0 && elect_one_sync()) {
         tma_prefetch_desc(&map_q);
         tma_prefetch_desc(&map_k);
         tma_prefetch_desc(&map_v);
@@ -270,7 +270,8 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
 // ------------------------------------------------------------------------------------------ backward
 constexpr int BK = 128;       // keys per CTA (= TMEM lanes)
 constexpr int BQ = 64;        // queries per block
-constexpr int B_STAGES = 3;
+constexpr int B_STAGES = 5;    // Q_i + dO_i ring: S^T / dP^T run two blocks ahead of dV / dK, which still reads block i
+constexpr int B_SDP = 3;       // S^T / dP^T accumulator pairs in TMEM
 constexpr int B_EW = 16;        // element-wise warps: four per TMEM lane quarter, 16 query columns each (the per-block chain
                                 // of one thread is latency bound; twice the warps of the first version hide twice the latency)
 constexpr int B_THREADS = 96 + 32 * B_EW;  // TMA warp, MMA warp, element-wise warps, dS^T store warp
@@ -278,7 +279,7 @@ constexpr int B_KV_BYTES = 2 * BK * DH * 2;   // K_j + V_j: 32 KB
 constexpr int B_QD_BYTES = 2 * BQ * DH * 2;   // Q_i + dO_i: 16 KB
 constexpr int B_PT_BYTES = BK * BQ * 2;       // one P^T (or dS^T) operand tile: 16 KB
 constexpr int B_SMEM_FIXED = B_KV_BYTES + B_STAGES * B_QD_BYTES + 4 * B_PT_BYTES + 1024 + 256;  // + 2 * Tpad floats (lse, D)
-constexpr int B_TMEM_COLS = 512;  // S^T[2], dP^T[2] (4 x 64) + dV (64) + dK (64)
+constexpr int B_TMEM_COLS = 512;  // S^T[3], dP^T[3] (6 x 64) + dV (64) + dK (64)
 
 struct BwdParams {
     const float* lse;   // [B,H,T] natural-log sum-exp of the scaled logits
@@ -312,13 +313,14 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
     auto qd_full = [&](int s) { return bars + 8u * (1 + s); };
     auto qd_empty = [&](int s) { return bars + 8u * (1 + B_STAGES + s); };
     auto sdp_full = [&](int s) { return bars + 8u * (1 + 2 * B_STAGES + s); };
-    auto sdp_free = [&](int s) { return bars + 8u * (3 + 2 * B_STAGES + s); };
-    auto pds_ready = [&](int s) { return bars + 8u * (5 + 2 * B_STAGES + s); };
-    auto pds_free = [&](int s) { return bars + 8u * (7 + 2 * B_STAGES + s); };
-    const uint32_t dkv_done = bars + 8u * (9 + 2 * B_STAGES);
-    const uint32_t tmem_slot = bars + 8u * (10 + 2 * B_STAGES);
+    auto sdp_free = [&](int s) { return bars + 8u * (1 + B_SDP + 2 * B_STAGES + s); };
+    auto pds_ready = [&](int s) { return bars + 8u * (1 + 2 * B_SDP + 2 * B_STAGES + s); };
+    auto pds_free = [&](int s) { return bars + 8u * (3 + 2 * B_SDP + 2 * B_STAGES + s); };
+    const uint32_t dkv_done = bars + 8u * (5 + 2 * B_SDP + 2 * B_STAGES);
+    const uint32_t tmem_slot = bars + 8u * (6 + 2 * B_SDP + 2 * B_STAGES);
+    static_assert(8 * (7 + 2 * B_SDP + 2 * B_STAGES) <= 256, "barrier area");
     volatile uint32_t* tmem_slot_gen =
-        reinterpret_cast<volatile uint32_t*>(genPT + 4 * B_PT_BYTES + 8 * (10 + 2 * B_STAGES));
+        reinterpret_cast<volatile uint32_t*>(genPT + 4 * B_PT_BYTES + 8 * (6 + 2 * B_SDP + 2 * B_STAGES));
     // whole-row softmax statistics of this (utterance, head), staged once: lse * log2(e) then D, Tpad floats each
     // (Tpad = T rounded up to the 64-query block; the padding holds +inf / 0 so that out-of-range queries give P = 0)
     const int Tpad = ((p.T + BQ - 1) / BQ) * BQ;
@@ -352,7 +354,7 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
         return;
     }
 
-    if (warp == 0 && lane == 0) {
+    if (warp == 0 && elect_one_sync()) {
         tma_prefetch_desc(&map_k);
         tma_prefetch_desc(&map_v);
         tma_prefetch_desc(&map_q);
@@ -363,9 +365,11 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
             mbar_init(qd_full(s), 1);
             mbar_init(qd_empty(s), 1);
         }
-        for (int s = 0; s < 2; ++s) {
+        for (int s = 0; s < B_SDP; ++s) {
             mbar_init(sdp_full(s), 1);
             mbar_init(sdp_free(s), B_EW);
+        }
+        for (int s = 0; s < 2; ++s) {
             mbar_init(pds_ready(s), B_EW);
             mbar_init(pds_free(s), 2);   // the MMAs that read P^T / dS^T have completed + the dS^T tile has been stored
         }
@@ -392,8 +396,8 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
     }
     __syncthreads();
     if (threadIdx.x == 0) ATRACE(2);
-    // TMEM columns: S^T[s] at 64 s, dP^T[s] at 128 + 64 s, dV at 256, dK at 320
-    const uint32_t tm_dv = tmem_base + 256, tm_dk = tmem_base + 320;
+    // TMEM columns: S^T[s] at 64 s, dP^T[s] at 192 + 64 s (s < 3), dV at 384, dK at 448
+    const uint32_t tm_dv = tmem_base + 384, tm_dk = tmem_base + 448;
 
     if (warp == 0) {
         if (elect_one_sync()) {
@@ -412,24 +416,28 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
             const uint64_t desc_k = make_smem_desc(sK, 16, 1024), desc_v = make_smem_desc(sV, 16, 1024);
             auto issue_sdp = [&](int i) {
                 const int s = i % B_STAGES;
+                const int a3 = i % B_SDP;
                 mbar_wait(qd_full(s), (i / B_STAGES) & 1);
-                if (i >= 2) mbar_wait(sdp_free(i & 1), ((i >> 1) - 1) & 1);
+                if (i >= B_SDP) mbar_wait(sdp_free(a3), ((i / B_SDP) - 1) & 1);
                 tc_fence_after();
                 const uint32_t sq = sQD + s * B_QD_BYTES, sdo = sq + BQ * DH * 2;
-                const uint32_t t_st = tmem_base + (uint32_t)((i & 1) * BQ), t_dp = tmem_base + 128 + (uint32_t)((i & 1) * BQ);
+                const uint32_t t_st = tmem_base + (uint32_t)(a3 * BQ), t_dp = tmem_base + 192 + (uint32_t)(a3 * BQ);
                 const uint64_t dq = make_smem_desc(sq, 16, 1024), ddo = make_smem_desc(sdo, 16, 1024);
 #pragma unroll
                 for (int k = 0; k < DH / 16; ++k) {
                     umma_bf16(t_st, smem_desc_advance(desc_k, 2 * k), smem_desc_advance(dq, 2 * k), idesc_kk, k > 0 ? 1u : 0u);
                     umma_bf16(t_dp, smem_desc_advance(desc_v, 2 * k), smem_desc_advance(ddo, 2 * k), idesc_kk, k > 0 ? 1u : 0u);
                 }
-                umma_commit(sdp_full(i & 1));
+                umma_commit(sdp_full(a3));
             };
             mbar_wait(kv_full, 0);
             ATRACE(3);
+            // S^T / dP^T of block i+2 are queued before this thread waits for the element-wise warps of block i: the
+            // tensor pipe always has the next block's logits ready when they come back (three accumulator pairs)
             issue_sdp(0);
+            if (nqb > 1) issue_sdp(1);
             for (int i = 0; i < nqb; ++i) {
-                if (i + 1 < nqb) issue_sdp(i + 1);
+                if (i + 2 < nqb) issue_sdp(i + 2);
                 if (i == 2) ATRACE(16);
                 mbar_wait(pds_ready(i & 1), (i >> 1) & 1);
                 tc_fence_after();
@@ -475,19 +483,19 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
         const uint32_t tlane = tmem_base + ((uint32_t)(quarter * 32) << 16);
         const float c2 = p.scale_log2, sc = p.scale;
         for (int i = 0; i < nqb; ++i) {
-            const int slot = i & 1;
+            const int slot = i & 1, a3 = i % B_SDP;
             const bool trc = threadIdx.x == 64 && (i == 2 || i == 3);
             if (trc && i == 2) ATRACE(8);
-            mbar_wait(sdp_full(slot), (i >> 1) & 1);
+            mbar_wait(sdp_full(a3), (i / B_SDP) & 1);
             tc_fence_after();
             if (trc) ATRACE(i == 2 ? 9 : 15);
             uint32_t s[CG], dp[CG];
-            tmem_ld_32x16(tlane + (uint32_t)(slot * BQ + cg * CG), s);
-            tmem_ld_32x16(tlane + 128 + (uint32_t)(slot * BQ + cg * CG), dp);
+            tmem_ld_32x16(tlane + (uint32_t)(a3 * BQ + cg * CG), s);
+            tmem_ld_32x16(tlane + 192 + (uint32_t)(a3 * BQ + cg * CG), dp);
             tmem_ld_wait();
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(sdp_free(slot));
+            if (lane == 0) mbar_arrive(sdp_free(a3));
             if (trc && i == 2) ATRACE(10);
             uint32_t pp[CG / 2], dd[CG / 2];
             const float4* l2v = reinterpret_cast<const float4*>(lse2_s + i * BQ + cg * CG);  // broadcast 16-byte reads
@@ -532,8 +540,8 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
         tc_fence_after();
         if (threadIdx.x == 64) ATRACE(6);
         uint32_t a[CG], c_[CG];   // this thread's 16 of the 64 head-dim columns of dV / dK
-        tmem_ld_32x16(tlane + 256 + (uint32_t)(cg * CG), a);   // dV
-        tmem_ld_32x16(tlane + 320 + (uint32_t)(cg * CG), c_);  // dK
+        tmem_ld_32x16(tlane + 384 + (uint32_t)(cg * CG), a);   // dV
+        tmem_ld_32x16(tlane + 448 + (uint32_t)(cg * CG), c_);  // dK
         tmem_ld_wait();
         if (key < T) {
             __nv_bfloat16* dk = p.dqkv + (((long long)b * T + key) * 3 + 1) * D + h * DH + cg * CG;
