@@ -36,11 +36,14 @@ constexpr float LN2 = 0.6931471805599453f;
 constexpr int FQ = 128;       // queries per CTA (= TMEM lanes)
 constexpr int FK = 64;        // keys per block
 constexpr int F_STAGES = 3;
-constexpr int F_THREADS = 192;
+constexpr int F_SW = 8;         // softmax warps: two per TMEM lane quarter, each thread owns HALF a query row (32 of the
+                                // block's 64 keys): the per-block chain (max, exp2, sum, pack) of a thread is latency bound
+constexpr int F_THREADS = 64 + 32 * F_SW;
 constexpr int F_Q_BYTES = FQ * DH * 2;        // 16 KB
 constexpr int F_KV_BYTES = 2 * FK * DH * 2;   // K + V: 16 KB
 constexpr int F_P_BYTES = FQ * FK * 2;        // 16 KB
-constexpr int F_SMEM = F_Q_BYTES + F_STAGES * F_KV_BYTES + F_P_BYTES + 1024 + 256;
+constexpr int F_XCH_BYTES = 2 * FQ * 2 * 4;   // row maxima of the two half-row threads, double buffered by block parity
+constexpr int F_SMEM = F_Q_BYTES + F_STAGES * F_KV_BYTES + F_P_BYTES + 1024 + 256 + F_XCH_BYTES;
 constexpr int F_TMEM_COLS = 256;              // S[2] (2 x 64) + O (64) -> next power of two
 
 struct FwdParams {
@@ -49,12 +52,17 @@ struct FwdParams {
     const int* klen;
     int B, T, H;
     float scale_log2;  // softmax scale * log2(e)
+    unsigned long long* trace;   // diagnostics (b200asr_attn_set_trace): 24 time stamps per CTA, null in normal use
 };
+static unsigned long long* g_attn_trace = nullptr;
+#define ATRACE(slot) do { if (p.trace) p.trace[(long long)((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 24 + (slot)] = (unsigned long long)clock64(); } while (0)
 
 __global__ void __launch_bounds__(F_THREADS, 2)
 mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                   const __grid_constant__ CUtensorMap map_v, const FwdParams p) {
-    pdl_enter();  // launched with programmatic stream serialization: wait for the producers before touching global memory
+    if (threadIdx.x == 0) ATRACE(0);
+    pdl_enter();
+    if (threadIdx.x == 0) ATRACE(1);  // launched with programmatic stream serialization: wait for the producers before touching global memory
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
@@ -82,7 +90,7 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
     const int D = H * DH;
 
     if (nkb == 0) {  // no valid key: probabilities are all zero (softmax_rows_kernel convention), lse = -inf
-        if (warp >= 2) {
+        if (warp >= 2 && warp < 6) {
             const int row = (warp & 3) * 32 + lane, t = q0 + row;
             if (t < T) {
                 uint4* o = reinterpret_cast<uint4*>(p.out + ((long long)b * T + t) * D + h * DH);
@@ -105,9 +113,9 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(s_full(s), 1);
-            mbar_init(s_free(s), 4);
+            mbar_init(s_free(s), F_SW);
         }
-        mbar_init(p_ready, 4);
+        mbar_init(p_ready, F_SW);
         mbar_init(pv_done, 1);
         fence_barrier_init();
         // the operand loads start now and overlap the TMEM allocation
@@ -125,6 +133,7 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_gen;
     const uint32_t tmem_o = tmem_base + 128;
+    if (threadIdx.x == 0) ATRACE(2);
 
     if (warp == 0) {
         if (elect_one_sync()) {
@@ -153,6 +162,7 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
                 umma_commit(s_full(j & 1));
             };
             mbar_wait(q_full, 0);
+            ATRACE(3);
             issue_s(0);
             for (int j = 0; j < nkb; ++j) {
                 if (j + 1 < nkb) issue_s(j + 1);
@@ -167,83 +177,108 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
                 umma_commit(kv_empty(s));
                 umma_commit(pv_done);
             }
+            ATRACE(4);
         }
     } else {
-        const int quarter = warp & 3;
+        constexpr int HC = FK / 2;   // key columns per thread and block (32)
+        const int quarter = warp & 3, half = (warp - 2) >> 2;
         const int row = quarter * 32 + lane;
         const uint32_t tlane = tmem_base + ((uint32_t)(quarter * 32) << 16);
-        const uint32_t tlane_o = tlane + 128;
-        float m = -INFINITY, l = 0.f;
+        const uint32_t tlane_o = tlane + 128 + (uint32_t)(half * 32);   // this thread's 32 of the 64 output columns
+        float* xch = reinterpret_cast<float*>(genP + F_P_BYTES + 256);  // [parity][row][half]
+        float m = -INFINITY, l = 0.f;   // running row maximum (common to both halves), this half's running sum
         const float c2 = p.scale_log2;
         for (int j = 0; j < nkb; ++j) {
+            const bool trc = threadIdx.x == 64 && j == 2;
+            if (trc) ATRACE(8);
             mbar_wait(s_full(j & 1), (j >> 1) & 1);
             tc_fence_after();
-            uint32_t r[64];
-            tmem_ld_32x32(tlane + (uint32_t)((j & 1) * FK), r);
-            tmem_ld_32x32(tlane + (uint32_t)((j & 1) * FK + 32), r + 32);
+            if (threadIdx.x == 64 && j == 3) ATRACE(15);
+            if (trc) ATRACE(9);
+            uint32_t r[HC];
+            tmem_ld_32x32(tlane + (uint32_t)((j & 1) * FK + half * HC), r);
             tmem_ld_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(s_free(j & 1));
-            const int nvalid = kl - j * FK;  // >= 1
-            float mx = -INFINITY;
-            if (nvalid >= FK) {
+            if (trc) ATRACE(10);
+            const int nvalid = kl - j * FK - half * HC;  // valid keys among this thread's columns (may be <= 0)
+            float mx0 = -INFINITY, mx1 = -INFINITY;
+            if (nvalid >= HC) {
 #pragma unroll
-                for (int c = 0; c < FK; ++c) mx = fmaxf(mx, __uint_as_float(r[c]));
+                for (int c = 0; c < HC; c += 2) {
+                    mx0 = fmaxf(mx0, __uint_as_float(r[c]));
+                    mx1 = fmaxf(mx1, __uint_as_float(r[c + 1]));
+                }
             } else {
 #pragma unroll
-                for (int c = 0; c < FK; ++c) {
+                for (int c = 0; c < HC; ++c) {
                     if (c >= nvalid) r[c] = __float_as_uint(-INFINITY);
-                    mx = fmaxf(mx, __uint_as_float(r[c]));
+                    mx0 = fmaxf(mx0, __uint_as_float(r[c]));
                 }
             }
-            const float m_new = fmaxf(m, mx * c2);
+            // the other half of the row lives in the warp four further on (same lane): exchange the block maxima
+            float* xr = xch + ((j & 1) * FQ + row) * 2;
+            xr[half] = fmaxf(mx0, mx1);
+            named_bar_sync(1 + quarter, 64);
+            if (trc) ATRACE(11);
+            const float mx = fmaxf(xr[0], xr[1]);   // >= one valid key in the block: finite
+            // lazy rescaling: the reference maximum only moves when the block maximum exceeds it by more than 2^8 (the
+            // probabilities then stay <= 256, exact enough in fp32 sums and bf16 operands); O in TMEM is rescaled only then
+            const float mb = mx * c2;
+            const float m_new = (mb > m + 8.0f) ? mb : m;
             const float alpha = fast_exp2(m - m_new);
-            float sum = 0.f;
-            uint32_t pk[32];
+            float sum0 = 0.f, sum1 = 0.f;
+            uint32_t pk[HC / 2];
 #pragma unroll
-            for (int c = 0; c < FK; c += 2) {
+            for (int c = 0; c < HC; c += 2) {
                 const float p0 = fast_exp2(fmaf(__uint_as_float(r[c]), c2, -m_new));
                 const float p1 = fast_exp2(fmaf(__uint_as_float(r[c + 1]), c2, -m_new));
-                sum += p0 + p1;
+                sum0 += p0;
+                sum1 += p1;
                 pk[c >> 1] = bf2_pack(p0, p1);
             }
-            l = fmaf(l, alpha, sum);
+            l = fmaf(l, alpha, sum0 + sum1);
             m = m_new;
+            if (trc) ATRACE(12);
             if (j > 0) {
                 mbar_wait(pv_done, (j - 1) & 1);
                 tc_fence_after();
             }
+            if (trc) ATRACE(13);
 #pragma unroll
-            for (int c = 0; c < 8; ++c)
-                *reinterpret_cast<uint4*>(genP + sw128_offset(row, c)) =
+            for (int c = 0; c < HC / 8; ++c)
+                *reinterpret_cast<uint4*>(genP + sw128_offset(row, half * (HC / 8) + c)) =
                     make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
-            if (j > 0 && __any_sync(0xffffffffu, alpha != 1.0f)) {
+            if (j > 0 && __any_sync(0xffffffffu, alpha != 1.0f)) {   // (both halves see the same alpha)
+                uint32_t o[32];
+                tmem_ld_32x32(tlane_o, o);
+                tmem_ld_wait();
 #pragma unroll
-                for (int hh = 0; hh < 2; ++hh) {
-                    uint32_t o[32];
-                    tmem_ld_32x32(tlane_o + hh * 32, o);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * alpha);
-                    tmem_st_32x32(tlane_o + hh * 32, o);
-                }
+                for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * alpha);
+                tmem_st_32x32(tlane_o, o);
                 tmem_st_wait();
             }
             fence_proxy_async();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(p_ready);
+            if (trc) ATRACE(14);
         }
+        if (threadIdx.x == 64) ATRACE(5);
+        // row sum = the two halves' sums (same running maximum)
+        float* xl = xch + ((nkb & 1) * FQ + row) * 2;
+        xl[half] = l;
+        named_bar_sync(1 + quarter, 64);
+        const float lt = xl[0] + xl[1];
         mbar_wait(pv_done, (nkb - 1) & 1);
         tc_fence_after();
         const int t = q0 + row;
-        const float inv = 1.0f / l;
-        __nv_bfloat16* orow = p.out + ((long long)b * T + t) * D + h * DH;
-#pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
+        const float inv = 1.0f / lt;
+        __nv_bfloat16* orow = p.out + ((long long)b * T + t) * D + h * DH + half * 32;
+        {
             uint32_t o[32];
-            tmem_ld_32x32(tlane_o + hh * 32, o);
+            tmem_ld_32x32(tlane_o, o);
             tmem_ld_wait();
             if (t < T) {
 #pragma unroll
@@ -253,11 +288,12 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
                     v.y = bf2_pack(__uint_as_float(o[c + 2]) * inv, __uint_as_float(o[c + 3]) * inv);
                     v.z = bf2_pack(__uint_as_float(o[c + 4]) * inv, __uint_as_float(o[c + 5]) * inv);
                     v.w = bf2_pack(__uint_as_float(o[c + 6]) * inv, __uint_as_float(o[c + 7]) * inv);
-                    *reinterpret_cast<uint4*>(orow + hh * 32 + c) = v;
+                    *reinterpret_cast<uint4*>(orow + c) = v;
                 }
             }
         }
-        if (t < T) p.lse[((long long)b * H + h) * T + t] = (m + log2f(l)) * LN2;
+        if (half == 0 && t < T) p.lse[((long long)b * H + h) * T + t] = (m + log2f(lt)) * LN2;
+        if (threadIdx.x == 64) ATRACE(6);
     }
     tc_fence_before();
     __syncthreads();
@@ -265,6 +301,7 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
         tc_fence_after();
         tmem_dealloc(tmem_base, F_TMEM_COLS);
     }
+    if (threadIdx.x == 0) ATRACE(7);
 }
 
 // ------------------------------------------------------------------------------------------ backward
@@ -291,8 +328,6 @@ struct BwdParams {
     float scale, scale_log2;
     unsigned long long* trace;   // diagnostics (b200asr_attn_set_trace): 24 time stamps per CTA, null in normal use
 };
-static unsigned long long* g_attn_trace = nullptr;
-#define ATRACE(slot) do { if (p.trace) p.trace[(long long)((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 24 + (slot)] = (unsigned long long)clock64(); } while (0)
 
 __global__ void __launch_bounds__(B_THREADS, 1)
 mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
@@ -643,6 +678,7 @@ int mha_fwd_tc_launch(const void* qkv, void* out, float* lse, const int* klen, i
     FwdParams p;
     p.out = (__nv_bfloat16*)out; p.lse = lse; p.klen = klen; p.B = B; p.T = T; p.H = H;
     p.scale_log2 = scale * LOG2E;
+    p.trace = g_attn_trace;
     dim3 grid(ceil_div(T, FQ), H, B);
     launch_pdl(mha_fwd_tc_kernel, grid, dim3(F_THREADS), (size_t)F_SMEM, st, mq, mk, mv, p);
     return check_launch("mha_fwd_tcgen05");
