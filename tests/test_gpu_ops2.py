@@ -173,6 +173,48 @@ def test_ctc_matches_torch(dtype):
     _ctc_case(dtype, 4, 499, 32, [499, 450, 300, 499], [120, 60, 20, 100], 2)  # config-2 shape: S up to 241
     _ctc_case(dtype, 2, 40, 8, [40, 10], [5, 9], 3)                          # utterance 1 infeasible -> zero_infinity
     _ctc_case(dtype, 2, 30, 40, [30, 30], [3, 0], 4)                         # empty target, V > 32
+    _ctc_case(dtype, 2, 25, 150, [25, 20], [4, 6], 5)                        # V > 128: the re-reading softmax path
+
+
+def test_kernel_traces_record_and_do_not_change_results():
+    """b200asr_gemm_set_trace / b200asr_attn_set_trace (diagnostics): stamps are written for the CTAs of the launch, the
+    results are bit-identical with and without them, NULL stops the recording."""
+    from b200asr._lib import check, lib
+    g = torch.Generator().manual_seed(3)
+    M, N, K = 1000, 512, 512
+    x = (torch.randn(M, K, generator=g) * 0.2).bfloat16().to(DEV)
+    w = (torch.randn(N, K, generator=g) * 0.2).bfloat16().to(DEV)
+    b = torch.randn(N, generator=g).to(DEV)
+    y0 = ops.linear_fwd(x, w, b)
+    y0 = y0[0] if isinstance(y0, tuple) else y0
+    tr = torch.zeros(148 * 20, dtype=torch.int64, device=DEV)
+    check(lib.b200asr_gemm_set_trace(tr.data_ptr()), "set_trace")
+    y1 = ops.linear_fwd(x, w, b)
+    check(lib.b200asr_gemm_set_trace(None), "set_trace")
+    y1 = y1[0] if isinstance(y1, tuple) else y1
+    torch.cuda.synchronize()
+    assert torch.equal(y0, y1)
+    t = tr.view(148, 20).cpu()
+    used = t[:, 1] != 0
+    assert int(used.sum()) >= 1 and bool((t[used, 8] > t[used, 1]).all())   # exit after entry (SM clock)
+    tr.zero_()
+    ops.linear_fwd(x, w, b)
+    torch.cuda.synchronize()
+    assert int(tr.abs().sum()) == 0
+    B, T, H = 2, 150, 2
+    qkv = (torch.randn(B * T, 3 * H * 64, generator=g) * 0.5).bfloat16().to(DEV)
+    do = (torch.randn(B * T, H * 64, generator=g) * 0.1).bfloat16().to(DEV)
+    out, lse = ops.mha_fwd(qkv, None, B, T, H, 64, 0.125)
+    d0 = ops.mha_bwd(qkv, out, do, lse, None, B, T, H, 64, 0.125)
+    nc = ((T + 127) // 128) * H * B
+    tra = torch.zeros(nc * 24, dtype=torch.int64, device=DEV)
+    check(lib.b200asr_attn_set_trace(tra.data_ptr()), "set_trace")
+    d1 = ops.mha_bwd(qkv, out, do, lse, None, B, T, H, 64, 0.125)
+    check(lib.b200asr_attn_set_trace(None), "set_trace")
+    torch.cuda.synchronize()
+    assert torch.equal(d0, d1)
+    ta = tra.view(nc, 24).cpu()
+    assert bool((ta[:, 7] > ta[:, 0]).all())
 
 
 def test_ctc_third_opinion_fp64():
