@@ -370,6 +370,15 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
     const int D = H * DH;
     const long long bh = (long long)b * H + h;
 
+    // this thread's share of the softmax statistics: the loads fly while the barriers / TMEM are set up
+    float pre_lse = INFINITY, pre_d = 0.f;
+    {
+        const int q = threadIdx.x - 64;
+        if (q >= 0 && q < T && k0 < kl) {
+            pre_lse = __ldg(p.lse + bh * T + q) * LOG2E;
+            pre_d = __ldg(p.dsum + bh * T + q);
+        }
+    }
     if (k0 >= kl) {  // fully masked key block: dK = dV = 0, dS^T rows = 0
         if (warp >= 2) {
             const int et = threadIdx.x - 64;  // first 256: two threads per key row
@@ -389,27 +398,25 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
         return;
     }
 
+    if (warp == 0) {   // one barrier per lane (they are laid out back to back), then one lane starts the operand loads
+        constexpr int NBAR = 6 + 2 * B_SDP + 2 * B_STAGES;
+        static_assert(NBAR <= 32, "one barrier per lane");
+        if (lane < NBAR) {
+            const int first_ew = 1 + B_SDP + 2 * B_STAGES, first_pf = 3 + 2 * B_SDP + 2 * B_STAGES;   // sdp_free, pds_free
+            // sdp_free / pds_ready: one arrival per element-wise warp; pds_free: the MMAs that read P^T / dS^T have
+            // completed + the dS^T tile has been stored; everything else: one arrival (+ transaction bytes)
+            const uint32_t cnt = (lane >= first_ew && lane < first_pf) ? B_EW : (lane >= first_pf && lane < first_pf + 2) ? 2 : 1;
+            mbar_init(bars + 8u * lane, cnt);
+        }
+        fence_barrier_init();
+        __syncwarp();
+    }
     if (warp == 0 && elect_one_sync()) {
         tma_prefetch_desc(&map_k);
         tma_prefetch_desc(&map_v);
         tma_prefetch_desc(&map_q);
         tma_prefetch_desc(&map_do);
         tma_prefetch_desc(&map_dst);
-        mbar_init(kv_full, 1);
-        for (int s = 0; s < B_STAGES; ++s) {
-            mbar_init(qd_full(s), 1);
-            mbar_init(qd_empty(s), 1);
-        }
-        for (int s = 0; s < B_SDP; ++s) {
-            mbar_init(sdp_full(s), 1);
-            mbar_init(sdp_free(s), B_EW);
-        }
-        for (int s = 0; s < 2; ++s) {
-            mbar_init(pds_ready(s), B_EW);
-            mbar_init(pds_free(s), 2);   // the MMAs that read P^T / dS^T have completed + the dS^T tile has been stored
-        }
-        mbar_init(dkv_done, 1);
-        fence_barrier_init();
         // the operand loads start now: they overlap the TMEM allocation and the staging of the softmax statistics below
         mbar_expect_tx(kv_full, B_KV_BYTES);
         tma_load_4d(sK, &map_k, kv_full, 0, k0, h, b);
@@ -425,12 +432,18 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_gen;
-    for (int q = threadIdx.x; q < Tpad; q += blockDim.x) {
-        lse2_s[q] = (q < T) ? p.lse[bh * T + q] * LOG2E : INFINITY;
-        dsum_s[q] = (q < T) ? p.dsum[bh * T + q] : 0.f;
+    // the softmax statistics are only read by the element-wise warps: they stage them among themselves (named barrier)
+    // while the MMA issuer already queues the first S^T / dP^T products
+    if (warp >= 2 && warp < 2 + B_EW) {
+        const int q0s = threadIdx.x - 64;
+        if (q0s < Tpad) { lse2_s[q0s] = pre_lse; dsum_s[q0s] = pre_d; }   // (requested before the set-up barrier)
+        for (int q = q0s + 32 * B_EW; q < Tpad; q += 32 * B_EW) {
+            lse2_s[q] = (q < T) ? p.lse[bh * T + q] * LOG2E : INFINITY;
+            dsum_s[q] = (q < T) ? p.dsum[bh * T + q] : 0.f;
+        }
+        named_bar_sync(1, 32 * B_EW);
     }
-    __syncthreads();
-    if (threadIdx.x == 0) ATRACE(2);
+    if (threadIdx.x == 64) ATRACE(2);
     // TMEM columns: S^T[s] at 64 s, dP^T[s] at 192 + 64 s (s < 3), dV at 384, dK at 448
     const uint32_t tm_dv = tmem_base + 384, tm_dk = tmem_base + 448;
 
