@@ -190,22 +190,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     const int lane = threadIdx.x & 31;
     if (p.trace && threadIdx.x == 0) { p.trace[(long long)blockIdx.x * 20] = globaltimer_ns(); TRACE(1); }
 
-    if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&tma_a);
-        tma_prefetch_desc(&tma_b);
-        for (int s = 0; s < C_::STAGES; ++s) {
-            mbar_init(full_bar(s), 1);
-            mbar_init(empty_bar(s), MC ? 2 : 1);  // NCTA = 4: both pairs' MMAs must have drained the slot (multicast target)
-        }
-        for (int s = 0; s < 2; ++s) {
-            mbar_init(tfull_bar(s), 1);
-            mbar_init(tempty_bar(s), 8 * NP);  // one arrival per epilogue warp (of both CTAs of a pair)
-        }
-        if (p.epi_tma) {
-            tma_prefetch_desc(&tma_c);
-            if (p.x_kind) tma_prefetch_desc(&tma_x);
+    if (warp == 0) {   // one pipeline barrier per lane: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2] lie back to back
+        static_assert(2 * C_::STAGES + 4 <= 32, "one barrier per lane");
+        if (lane < 2 * C_::STAGES + 4) {
+            // empty (NCTA = 4): both pairs' MMAs must have drained the slot (multicast target);
+            // tmem_empty: one arrival per epilogue warp (of both CTAs of a pair)
+            const uint32_t cnt = (lane >= C_::STAGES && lane < 2 * C_::STAGES) ? (MC ? 2u : 1u)
+                                 : (lane >= 2 * C_::STAGES + 2) ? (uint32_t)(8 * NP) : 1u;
+            mbar_init(bars + 8u * lane, cnt);
         }
         fence_barrier_init();
+        if (lane == 0) {
+            tma_prefetch_desc(&tma_a);
+            tma_prefetch_desc(&tma_b);
+            if (p.epi_tma) {
+                tma_prefetch_desc(&tma_c);
+                if (p.x_kind) tma_prefetch_desc(&tma_x);
+            }
+        }
     }
     if (warp == 2) {   // the epilogue warps' operand-load barriers, one per lane
         mbar_init(in_bar(lane >> 2, lane & 3), 1);
@@ -228,7 +230,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     if (threadIdx.x == 0) TRACE(3);
 
     const int num_kb = p.num_kb;
-    const long long tiles_per_batch = (long long)p.tiles_m * p.tiles_n;
+    const int tiles_per_batch = p.tiles_m * p.tiles_n;   // (32-bit tile arithmetic: the host rejects tile counts beyond 2^31)
+    const int num_tiles_i = (int)p.num_tiles;
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -236,9 +239,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
             // TMA / MMA instructions take their uniform-register operands without a per-instruction election loop)
             int stage = 0;
             uint32_t phase = 0;
-            for (long long tile = worker; tile < p.num_tiles; tile += nworkers) {
-                const int z = (int)(tile / tiles_per_batch);
-                const int rem = (int)(tile % tiles_per_batch);
+            for (int tile = worker; tile < num_tiles_i; tile += nworkers) {
+                const int z = tile / tiles_per_batch;
+                const int rem = tile - z * tiles_per_batch;
                 const int mb = rem / p.tiles_n, nb = rem % p.tiles_n;  // n fastest: neighbours share the A tile in L2
                 const int b0 = z % p.batch0, b1 = z / p.batch0;
                 const int m0 = (MC ? (2 * mb + (int)pair) : mb) * TILE_M + (int)rank * BLOCK_M, n0 = nb * BN + (int)rank * BNH;
@@ -328,7 +331,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (long long tile = worker; tile < p.num_tiles; tile += nworkers) {
+            for (int tile = worker; tile < num_tiles_i; tile += nworkers) {
                 mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
@@ -397,7 +400,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                 const uint32_t my = epi_smem + (uint32_t)ew * C_::EPI_WARP_BYTES;
                 uint8_t* my_gen = smem_gen + C_::STAGES * C_::STAGE_BYTES + ew * C_::EPI_WARP_BYTES;
                 const int sw = lane & 7;                            // swizzle-128B: 16-byte unit u of row r sits at u ^ (r & 7)
-                const int ntiles = (int)p.num_tiles, tpb = (int)tiles_per_batch;
+                const int ntiles = num_tiles_i, tpb = tiles_per_batch;
                 const int col0 = SOLO ? 0 : chalf * CPT * CW;       // first tile column of this warp's part
                 const bool works = !SOLO || chalf == 0;
 
@@ -615,9 +618,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                 if (threadIdx.x == 64) TRACE(7);
             }
         } else {
-        for (long long tile = worker; tile < p.num_tiles; tile += nworkers) {
-                const int z = (int)(tile / tiles_per_batch);
-                const int rem = (int)(tile % tiles_per_batch);
+        for (int tile = worker; tile < num_tiles_i; tile += nworkers) {
+                const int z = tile / tiles_per_batch;
+                const int rem = tile - z * tiles_per_batch;
                 const int mb = rem / p.tiles_n, nb = rem % p.tiles_n;
                 const int b0 = z % p.batch0, b1 = z / p.batch0;
                 const int m = (MC ? (2 * mb + (int)pair) : mb) * TILE_M + (int)rank * BLOCK_M + quarter * 32 + lane;
@@ -785,6 +788,10 @@ template <int BN, typename TC, int NCTA = 1>
 static int launch_kernel(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mx,
                          const Params& p, cudaStream_t st) {
     using C_ = Cfg<BN, NCTA>;
+    if (p.num_tiles <= 0 || p.num_tiles > 0x7fffffffLL / 8) {   // the kernel walks the tile list with 32-bit indices
+        set_error("gemm(tcgen05): %lld tiles are outside the supported range", p.num_tiles);
+        return B200ASR_ERR_UNSUPPORTED;
+    }
     static bool attr_set = false;  // per instantiation
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, TC, NCTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
