@@ -142,6 +142,8 @@ int b200asr_gemm_set_trace(void* buf);
 /* diagnostics, same idea for the attention backward kernel: 24 u64 SM-clock stamps per CTA of its grid
  * (ceil(T/128) x H x B CTAs), slot layout next to the function in csrc/attn_tc.cu; NULL stops. */
 int b200asr_attn_set_trace(void* buf);
+/* diagnostics: 8 u64 SM-clock stamps of thread 0 per block of the LayerNorm backward grid (148 blocks); NULL stops. */
+int b200asr_ln_set_trace(void* buf);
 /* test hook: run b200asr_gemm on a forced back end (0 = fp32 FMA pipes, 1 = tcgen05 tensor cores). */
 int b200asr_gemm_backend(const b200asr_gemm_args* args, int backend, void* stream);
 

@@ -55,6 +55,7 @@ SIGNATURES = {
     "b200asr_gemm_force_config": (i32, [i32]),
     "b200asr_gemm_set_trace": (i32, [vp]),
     "b200asr_attn_set_trace": (i32, [vp]),
+    "b200asr_ln_set_trace": (i32, [vp]),
     "b200asr_gemm_backend": (i32, [C.POINTER(GemmArgs), i32, vp]),
     "b200asr_softmax_rows": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]),
     "b200asr_softmax_rows_bwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]),

@@ -115,6 +115,9 @@ __global__ void __launch_bounds__(128) ln_fwd_kernel(const T* __restrict__ x, co
 // next row of a group is prefetched while the current one is reduced.  The row statistics cross the warps of a group
 // through shared memory + a named barrier.  Groups add their accumulators into the block's shared sums in a fixed
 // order, blocks write partials, reduce_partials_kernel finishes: deterministic, no floating-point atomics.
+static __device__ unsigned long long* g_ln_trace_dev = nullptr;   // diagnostics (b200asr_ln_set_trace): 8 stamps per block
+#define LTRACE(slot) do { if (g_ln_trace_dev && threadIdx.x == 0) g_ln_trace_dev[blockIdx.x * 8 + (slot)] = (unsigned long long)clock64(); } while (0)
+
 template <typename T, bool CS>
 __global__ void __launch_bounds__(512, 1) ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ s,
                                                         const float* __restrict__ w, const float* __restrict__ b,
@@ -124,18 +127,17 @@ __global__ void __launch_bounds__(512, 1) ln_bwd_kernel(const T* __restrict__ dy
                                                         float* __restrict__ partial, int rows, int cols, int act, int GS,
                                                         int G) {
     constexpr int N = Vec16<T>::N;
+    LTRACE(0);
     pdl_enter();
+    LTRACE(1);
     extern __shared__ float sm[];
-    float* sacc = sm;                 // [3][cols] block sums (when partial != nullptr)
-    float* xch = sm + 3 * cols;       // [2][G][16][2] per-warp row statistics, double buffered by row parity
+    float* xch = sm;                    // [2][G][16][2] per-warp row statistics, double buffered by row parity
+    float* sacc = sm + 2 * 8 * 16 * 2;  // [G][3][N][GS] accumulators of the groups (end phase)
     const int g = threadIdx.x / GS, tg = threadIdx.x - g * GS;
     const int lane = threadIdx.x & 31, wg = tg >> 5, nwg = GS >> 5;
     const int c0 = tg * N;
     const bool active = c0 < cols;
     const float inv_cols = 1.0f / (float)cols;
-    if (partial) {
-        for (int i = threadIdx.x; i < 3 * cols; i += blockDim.x) sacc[i] = 0.f;
-    }
     float aw[N], ab[N], ac[N], wv[N], bv[N];
 #pragma unroll
     for (int j = 0; j < N; ++j) { aw[j] = ab[j] = ac[j] = 0.f; wv[j] = 1.f; bv[j] = 0.f; }
@@ -165,7 +167,8 @@ __global__ void __launch_bounds__(512, 1) ln_bwd_kernel(const T* __restrict__ dy
             }
         }
     }
-    int parity = 0;
+    LTRACE(2);
+    int parity = 0, nrows_done = 0;
     for (; row < rows; row += ngroups, parity ^= 1) {
         const long long base = (long long)row * cols + c0;
         Vec16<T> a = a_q[0], gg = g_q[0];
@@ -200,6 +203,7 @@ __global__ void __launch_bounds__(512, 1) ln_bwd_kernel(const T* __restrict__ dy
                 s2 = fmaf(d, h, s2);
             }
         }
+        if (nrows_done++ == 0) LTRACE(3);
         s1 = warp_sum(s1);
         s2 = warp_sum(s2);
         if (nwg > 1) {
@@ -233,22 +237,34 @@ __global__ void __launch_bounds__(512, 1) ln_bwd_kernel(const T* __restrict__ dy
             }
         }
     }
+    LTRACE(4);
     if (partial) {
-        __syncthreads();
-        for (int turn = 0; turn < G; ++turn) {
-            if (g == turn && active) {
+        // every group parks its accumulators in its own region, element (k, column c0 + j) at [((g * 3 + k) * N + j) * GS + tg]:
+        // consecutive threads hit consecutive banks (the first version added group after group into [3][cols] with an
+        // 8-way bank conflict on every access and G block barriers: 7.2K of the block's 23K clk, tools/ln_trace.py)
+        float* mine = sacc + (long long)g * 3 * N * GS;
 #pragma unroll
-                for (int j = 0; j < N; ++j) {
-                    sacc[c0 + j] += aw[j];
-                    sacc[cols + c0 + j] += ab[j];
-                    if (CS) sacc[2 * cols + c0 + j] += ac[j];
-                }
-            }
-            __syncthreads();
+        for (int j = 0; j < N; ++j) {
+            mine[(0 * N + j) * GS + tg] = aw[j];
+            mine[(1 * N + j) * GS + tg] = ab[j];
+            mine[(2 * N + j) * GS + tg] = CS ? ac[j] : 0.f;
         }
+        __syncthreads();
+        LTRACE(5);
         float* out = partial + (long long)blockIdx.x * 3 * cols;
-        for (int i = threadIdx.x; i < 3 * cols; i += blockDim.x) out[i] = sacc[i];
+        // walk the staging layout itself (consecutive lanes = consecutive banks); the 32-byte-strided global stores of the
+        // 12 KB partial are cheaper than an 8-way conflict on every shared read
+        for (int kj = g; kj < 3 * N; kj += G) {   // thread (g, tg) takes rows g, g + G, ... of the [3 N][GS] staging layout
+            const int i = kj * GS + tg;
+            const int k = kj / N, j = kj - k * N;
+            const int c = tg * N + j;
+            if (c >= cols) continue;
+            float v = 0.f;
+            for (int gg = 0; gg < G; ++gg) v += sacc[gg * 3 * N * GS + i];   // fixed order: deterministic
+            out[k * cols + c] = v;
+        }
     }
+    LTRACE(6);
 }
 
 // out[c] = sum_{p < nparts} partial[p * stride + c] for c < ncols_total; columns [0, cols) go to out0, [cols, 2 cols)
@@ -391,7 +407,17 @@ static int launch_ln_bwd(const void* dy, const void* s, const float* w, const fl
     int grid = ceil_div(rows, G);
     if (grid > LN_BWD_BLOCKS) grid = LN_BWD_BLOCKS;
     if (partial) grid = LN_BWD_BLOCKS;  // finalize sums exactly LN_BWD_BLOCKS partials
-    const size_t smem = ((size_t)3 * cols + 2 * 8 * 16 * 2) * sizeof(float);
+    const size_t smem = ((size_t)G * 3 * N * GS + 2 * 8 * 16 * 2) * sizeof(float);   // 50 KB at 512 threads (bf16)
+    static bool attr_set = false;   // per instantiation
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(ln_bwd_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(ln_bwd_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        if (e != cudaSuccess) {
+            set_error("layernorm_bwd: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+            return B200ASR_ERR_CUDA;
+        }
+        attr_set = true;
+    }
     if (colsum)
         launch_pdl(ln_bwd_kernel<T, true>, dim3(grid), dim3(G * GS), smem, st, (const T*)dy, (const T*)s, w, b, mean, rstd,
                    (const T*)dres, (T*)dx, partial, rows, cols, act, GS, G);
@@ -492,3 +518,16 @@ int b200asr_colsum(const void* x, float* out, void* workspace, size_t workspace_
 }
 
 }  // extern "C"
+
+// diagnostics: while `buf` (device memory, 8 u64 per block of the LayerNorm backward grid = 148 * 8 * 8 bytes) is set,
+// ln_bwd_kernel records SM-clock stamps of thread 0: 0 entry, 1 dependency wait done, 2 first rows requested, 3 first row
+// reduced, 4 row loop done, 5 block barrier passed, 6 partials written; NULL stops
+extern "C" int b200asr_ln_set_trace(void* buf) {
+    unsigned long long* p = (unsigned long long*)buf;
+    cudaError_t e = cudaMemcpyToSymbol(b200asr::g_ln_trace_dev, &p, sizeof(p));
+    if (e != cudaSuccess) {
+        b200asr::set_error("ln_set_trace: %s", cudaGetErrorString(e));
+        return B200ASR_ERR_CUDA;
+    }
+    return 0;
+}
