@@ -333,12 +333,12 @@ def run_b200(args):
     peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1400.0)))
     traffic = None
     try:  # per-launch DRAM traffic of this kernel from the committed ncu capture of this same command (profiles/)
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_gemm_traffic_v15.json")))["dram_bytes_per_launch"]
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_gemm_traffic_v16.json")))["dram_bytes_per_launch"]
     except Exception:
         pass
     roofline = {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05 bf16 GEMM: QKV/O/FFN linears fwd+dgrad+wgrad, conv layers 1-6)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "profiles/r01_ncu_gemm_traffic_v15.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, mean over one step's launches)",
+                "traffic_source": "profiles/r01_ncu_gemm_traffic_v16.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, mean over one step's launches)",
                 "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({src})", "launches": gm[0],
                 "avg_launch_us": gm[1] * 1e3 / max(1, gm[0]), "share_of_step": gm[1] / ms_step,
                 "other": {k: {"launches": v[0], "ms": v[1], "tflops": v[2] / (v[1] * 1e-3) / 1e12} for k, v in kinds.items()

@@ -25,6 +25,9 @@ class GraphedTrainStep:
     def __init__(self, model, opt, example_batch: Dict[str, torch.Tensor], max_label_len: Optional[int] = None,
                  warmup: int = 3):
         self.model, self.opt = model, opt
+        if model.training and float(getattr(getattr(model, "config", None), "layerdrop", 0.0) or 0.0) > 0.0:
+            raise NotImplementedError("GraphedTrainStep: LayerDrop changes the launch sequence from step to step "
+                                      "(HF:392-404); set config.layerdrop = 0 or run the update eagerly")
         self.max_label_len = int(max_label_len or example_batch["labels"].shape[1])
         if hasattr(model, "validate_labels"):
             model.validate_labels = False  # the reference's host-side range check would synchronise (models.py:483)

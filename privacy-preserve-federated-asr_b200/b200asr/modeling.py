@@ -195,6 +195,10 @@ class Data2VecAudioModel(nn.Module):
             self.masked_spec_embed = nn.Parameter(torch.empty(config.hidden_size).uniform_())
         self.cache = Fn.ShadowCache(compute_dtype)
         self._warned = False
+        # LayerDrop coins (HF:392-404) are host RNG draws: "numpy" = np.random.uniform(0, 1) as in the pinned
+        # transformers 4.17, "torch" = torch.rand([]) on the CPU generator as in transformers >= 4.3x.
+        self.layerdrop_rng = "numpy"
+        self.last_skipped_layers = ()
 
     @property
     def compute_dtype(self):
@@ -207,9 +211,10 @@ class Data2VecAudioModel(nn.Module):
         c = self.config
         if self.training and not self._warned:
             drops = [_cfg(c, n, 0.0) for n in ("hidden_dropout", "attention_dropout", "activation_dropout",
-                                               "feat_proj_dropout", "layerdrop")]
+                                               "feat_proj_dropout")]
             if any(d > 0 for d in drops):
-                warnings.warn("b200asr: dropout / LayerDrop are not applied by this build (treated as 0)")
+                warnings.warn("b200asr: element dropout is not applied by this build (treated as 0); "
+                              "LayerDrop is applied")
             self._warned = True
         if self.training and _cfg(c, "mask_time_prob", 0.0) > 0.0 and _cfg(c, "apply_spec_augment", True):
             raise NotImplementedError("SpecAugment (mask_time_prob > 0) is not supported; every reference entry "
@@ -224,6 +229,25 @@ class Data2VecAudioModel(nn.Module):
             raise NotImplementedError("Data2VecAudio has no GroupNorm / stable-LayerNorm variant (HF:51-157, 359-418)")
         if _cfg(c, "conv_pos_batch_norm", False):
             raise NotImplementedError("hubert conv_pos_batch_norm is not supported")
+
+    def _layerdrop_coins(self, n_layers):
+        """HF:392-404: one uniform draw per block, every step, in block order; the block is skipped when
+        training and the draw is below config.layerdrop.  Host RNG, no device sync.  Under stream capture the
+        outcome would be frozen into the graph, so that combination is refused."""
+        p = float(_cfg(self.config, "layerdrop", 0.0) or 0.0)
+        if not self.training or p <= 0.0:
+            return ()
+        if torch.cuda.is_current_stream_capturing():
+            raise NotImplementedError("LayerDrop draws a fresh coin per block every step; a captured CUDA graph "
+                                      "would replay one outcome: set config.layerdrop = 0 or run eagerly")
+        if self.layerdrop_rng == "torch":
+            coins = [float(torch.rand([])) for _ in range(n_layers)]
+        elif self.layerdrop_rng == "numpy":
+            import numpy as np
+            coins = [float(np.random.uniform(0, 1)) for _ in range(n_layers)]
+        else:
+            raise ValueError(f"layerdrop_rng must be 'numpy' or 'torch', got {self.layerdrop_rng!r}")
+        return tuple(l for l, u in enumerate(coins) if u < p)
 
     def forward(self, input_values, attention_mask=None, output_hidden_states=False):
         """Returns (hidden [B,T,d] in compute dtype, frame_lengths int32 [B] or None, hidden_states tuple|None)."""
@@ -263,8 +287,11 @@ class Data2VecAudioModel(nn.Module):
         collected = [h] if output_hidden_states else None
         meta = (B, T, int(c.num_attention_heads), eps)
         block = Fn.EncoderLayerStableFn if stable else Fn.EncoderLayerFn
+        skipped = self._layerdrop_coins(len(enc.layers))
+        self.last_skipped_layers = skipped
         for li, layer in enumerate(enc.layers):
-            x = block.apply(x, klen, meta, cache, *layer.params())
+            if li not in skipped:  # a dropped block is the identity and its parameters get no gradient
+                x = block.apply(x, klen, meta, cache, *layer.params())
             if collected is not None and not (stable and li + 1 == len(enc.layers)):
                 collected.append(x.view(B, T, d))
         if stable:  # Wav2Vec2EncoderStableLayerNorm: one LayerNorm after the last block

@@ -57,13 +57,19 @@ class FusedAdamW:
                 p._b200_fresh = True
 
     def _gather_stray_grads(self):
+        """Returns, per group, the indices of the parameters that received no gradient in this step (a block
+        dropped by LayerDrop, an unused head): their slice of the flat gradient is zeroed so the global norm is
+        unaffected, and step() leaves them alone as transformers.AdamW does (`if p.grad is None: continue`)."""
+        untouched = []
         for g in self.groups:
             fp = g["fp"]
-            for p in fp.params:
+            idle = []
+            for i, p in enumerate(fp.params):
                 if p.grad is None:
                     if p._b200_fresh:  # untouched this step
                         p._b200_grad.zero_()
                         p._b200_fresh = False
+                        idle.append(i)
                     p.grad = p._b200_grad
                 elif p.grad.data_ptr() != p._b200_grad.data_ptr():  # autograd delivered its own tensor
                     if p._b200_fresh:
@@ -72,6 +78,33 @@ class FusedAdamW:
                     else:
                         p._b200_grad.add_(p.grad)
                     p.grad = p._b200_grad
+            untouched.append(idle)
+        return untouched
+
+    def _segments(self, g, idle):
+        """Per-parameter step counts (transformers.AdamW keeps `state["step"]` per parameter and only advances it
+        when the parameter has a gradient).  Yields (start, end, step) over the flat buffer: maximal runs of
+        consecutive parameters that are updated in this step with the same step number."""
+        fp = g["fp"]
+        steps = g.setdefault("param_steps", [self.step_count - 1] * len(fp.params))
+        idle = set(idle)
+        run = None
+        for i, (p, o) in enumerate(zip(fp.params, fp.offsets)):
+            if i in idle:
+                if run:
+                    yield run
+                run = None
+                continue
+            steps[i] += 1
+            end = o + (p.numel() + 3) // 4 * 4
+            if run and run[2] == steps[i]:
+                run = (run[0], end, run[2])
+            else:
+                if run:
+                    yield run
+                run = (o, end, steps[i])
+        if run:
+            yield run
 
     def _clip_norm(self):
         if self.max_grad_norm is None:
@@ -83,14 +116,20 @@ class FusedAdamW:
 
     def step(self):
         ops.join_side_stream()
-        self._gather_stray_grads()
+        untouched = self._gather_stray_grads()
         lr = self.current_lr()
         self.step_count += 1
         gn = self._clip_norm()
-        for g in self.groups:
+        for g, idle in zip(self.groups, untouched):
             fp = g["fp"]
-            ops.adamw_step_(fp.flat, fp.grad, g["m"], g["v"], fp.shadow, lr, self.betas[0], self.betas[1], self.eps, g["wd"],
-                            self.step_count, gn, self.max_grad_norm or 0.0)
+            if not idle and "param_steps" not in g:  # every parameter has always been updated: one launch per group
+                ops.adamw_step_(fp.flat, fp.grad, g["m"], g["v"], fp.shadow, lr, self.betas[0], self.betas[1], self.eps,
+                                g["wd"], self.step_count, gn, self.max_grad_norm or 0.0)
+            else:
+                for a, b, t in self._segments(g, idle):
+                    ops.adamw_step_(fp.flat[a:b], fp.grad[a:b], g["m"][a:b], g["v"][a:b],
+                                    None if fp.shadow is None else fp.shadow[a:b], lr, self.betas[0], self.betas[1],
+                                    self.eps, g["wd"], t, gn, self.max_grad_norm or 0.0)
             fp.mark_updated(shadow_written=fp.shadow is not None)
 
     # ---- CUDA-graph friendly split: per-step scalars live in device memory (graph.GraphedTrainStep)

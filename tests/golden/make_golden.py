@@ -80,6 +80,49 @@ def case_plain_ctc(tag, cfg, batch, samples, seed, use_mask):
     print(tag, "loss", float(out.loss), "logits", tuple(out.logits.shape))
 
 
+def case_layerdrop(tag, cfg, batch, samples, seed, layerdrop, coin_seed):
+    """HF Data2VecAudioForCTC in training mode with LayerDrop (HF:392-404; every dropout 0).  The per-layer coins
+    are host RNG draws (`torch.rand([])` in the image's transformers, `np.random.uniform` in the pinned 4.17); the
+    fixture stores the coins and which blocks were skipped (read off the hidden states: a skipped block leaves its
+    input unchanged) so the oracle and the CUDA path can be driven with the same outcome."""
+    from transformers import Data2VecAudioForCTC
+    sd = R.init_state_dict(cfg, seed=seed, dacs=False)
+    hc = hf_config(cfg)
+    hc.layerdrop = layerdrop
+    m = Data2VecAudioForCTC(hc)
+    m.load_state_dict(sd, strict=True)
+    m.freeze_feature_encoder()
+    m.train()
+    b = R.synth_batch(cfg, batch, samples, seed=1234 + seed, ragged=True, max_label=12)
+    torch.manual_seed(coin_seed)
+    coins = np.array([float(torch.rand([])) for _ in range(cfg.num_hidden_layers)])
+    torch.manual_seed(coin_seed)
+    out = m(input_values=b["input_values"], attention_mask=b["attention_mask"], labels=b["labels"],
+            output_hidden_states=True)
+    out.loss.backward()
+    hs = out.hidden_states
+    skipped = np.array([l for l in range(cfg.num_hidden_layers) if torch.equal(hs[l], hs[l + 1])], dtype=np.int64)
+    assert list(skipped) == [l for l in range(cfg.num_hidden_layers) if coins[l] < layerdrop], (skipped, coins)
+    assert 0 < len(skipped) < cfg.num_hidden_layers
+    g = {n: p.grad.detach().clone() for n, p in m.named_parameters() if p.grad is not None}
+    none_grad = [n for n, p in m.named_parameters() if p.requires_grad and p.grad is None]
+    keep = ["lm_head.weight", "data2vec_audio.feature_projection.projection.weight",
+            "data2vec_audio.encoder.pos_conv_embed.layers.0.conv.weight"]
+    kept_layers = [l for l in range(cfg.num_hidden_layers) if l not in set(skipped)]
+    keep += [f"data2vec_audio.encoder.layers.{l}.attention.q_proj.weight" for l in kept_layers]
+    keep += [f"data2vec_audio.encoder.layers.{l}.feed_forward.output_dense.bias" for l in kept_layers]
+    np.savez_compressed(
+        os.path.join(OUT, f"{tag}.npz"),
+        seed=seed, batch=batch, samples=samples, layerdrop=layerdrop, coin_seed=coin_seed, coins=coins,
+        skipped=skipped, num_hidden_layers=cfg.num_hidden_layers, none_grad_names=np.array(none_grad),
+        loss=out.loss.detach().numpy(), logits=out.logits.detach().numpy(), argmax=out.logits.argmax(-1).numpy(),
+        hidden_last=hs[-1].detach().numpy(),
+        grad_names=np.array(keep), **{"grad:" + k: g[k].numpy() for k in keep},
+        gnorm_names=np.array(list(g.keys())), gnorm_values=np.array([float(v.norm()) for v in g.values()]),
+    )
+    print(tag, "loss", float(out.loss), "skipped", skipped.tolist(), "coins", coins.round(3).tolist())
+
+
 def case_variant_ctc(tag, cfg, batch, samples, seed, use_mask):
     """Config-5 variants (centralized/finetune_ASRs.py:154-172): HF Wav2Vec2ForCTC / HubertForCTC, eager attention.
     The oracle state_dict uses the transformers-4.17 weight_norm key names (weight_g / weight_v, the reference's
@@ -223,6 +266,8 @@ def main():
     case_dacs("dacs_stage2_toggle", cfg, batch=2, samples=6000, seed=20, stage=2, toggle_ratio=0.3)
     case_dacs("dacs_stage2_f1", cfg, batch=2, samples=6000, seed=21, stage=2, ad_loss="f1")
     case_fedavg("fedavg")
+    case_layerdrop("plain_ctc_layerdrop", R.ArchConfig.tiny(num_hidden_layers=4), batch=2, samples=6000, seed=3,
+                   layerdrop=0.5, coin_seed=5)
     for tag, (_, _, batch, samples, seed, use_mask) in VARIANTS.items():
         case_variant_ctc(tag, variant_cfg(tag), batch, samples, seed, use_mask)
 
@@ -231,5 +276,8 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "variants":  # only (re)generate the config-5 variant fixtures
         for tag, (_, _, batch, samples, seed, use_mask) in VARIANTS.items():
             case_variant_ctc(tag, variant_cfg(tag), batch, samples, seed, use_mask)
+    elif len(sys.argv) > 1 and sys.argv[1] == "layerdrop":
+        case_layerdrop("plain_ctc_layerdrop", R.ArchConfig.tiny(num_hidden_layers=4), batch=2, samples=6000, seed=3,
+                       layerdrop=0.5, coin_seed=5)
     else:
         main()

@@ -196,6 +196,98 @@ def test_training_loop_flat_grads_shadows_vs_oracle(dtype):
             assert relinf(params[n].detach(), ref[n]) < 2e-3, n
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_layerdrop_vs_reference_golden(golden_dir, dtype):
+    """LayerDrop (HF:392-404): same coins as HF (torch.rand([]) after torch.manual_seed) -> same blocks skipped,
+    loss / logits / gradients within tolerance, no gradient for the skipped blocks' parameters."""
+    g = load(golden_dir, "plain_ctc_layerdrop")
+    cfg = R.ArchConfig.tiny(num_hidden_layers=int(g["num_hidden_layers"]))
+    seed, batch, samples = int(g["seed"]), int(g["batch"]), int(g["samples"])
+    c = ns(cfg)
+    c.layerdrop = float(g["layerdrop"])
+    model = M.Data2VecAudioForCTC(c, compute_dtype=dtype)
+    model.load_state_dict(R.init_state_dict(cfg, seed=seed, dacs=False), strict=True)
+    model.freeze_feature_encoder()
+    model.to(DEV).train()
+    model.backbone.layerdrop_rng = "torch"
+    b = R.synth_batch(cfg, batch, samples, seed=1234 + seed, ragged=True, max_label=12)
+    torch.manual_seed(int(g["coin_seed"]))
+    out = model(input_values=b["input_values"].to(DEV), attention_mask=b["attention_mask"].to(DEV),
+                labels=b["labels"].to(DEV), output_hidden_states=True)
+    out.loss.backward()
+    assert list(model.backbone.last_skipped_layers) == g["skipped"].tolist()
+    assert len(out.hidden_states) == cfg.num_hidden_layers + 1
+    tol = TOL[dtype]
+    assert relinf(out.hidden_states[-1], g["hidden_last"]) < tol
+    assert relinf(out.logits, g["logits"]) < tol
+    assert abs(float(out.loss) - float(g["loss"])) / abs(float(g["loss"])) < tol
+    if dtype == torch.float32:
+        assert (out.logits.argmax(-1).cpu().numpy() == g["argmax"]).all()
+    params = dict(model.named_parameters())
+    gt = 2e-3 if dtype == torch.float32 else 6e-2
+    for n in g["grad_names"]:
+        assert relinf(params[str(n)].grad, g["grad:" + str(n)]) < gt, n
+    for n in g["none_grad_names"]:
+        assert params[str(n)].grad is None, n
+    model.eval()  # no coin in eval mode: every block runs
+    with torch.no_grad():
+        model(input_values=b["input_values"].to(DEV), attention_mask=b["attention_mask"].to(DEV))
+    assert model.backbone.last_skipped_layers == ()
+
+
+def test_layerdrop_training_loop_skips_optimizer_state():
+    """Four updates with LayerDrop through FlatParams + FusedAdamW against the oracle stepping with
+    transformers.AdamW semantics: a parameter without a gradient is left alone and keeps its own step count
+    (`if p.grad is None: continue`, per-parameter state["step"])."""
+    from b200asr.optim import FusedAdamW, _no_decay
+    cfg = R.ArchConfig.tiny(num_hidden_layers=4)
+    sd = R.init_state_dict(cfg, seed=4, dacs=False)
+    c = ns(cfg)
+    c.layerdrop = 0.4
+    model = M.Data2VecAudioForCTC(c, compute_dtype=torch.float32)
+    model.load_state_dict(sd)
+    model.freeze_feature_encoder()
+    model.to(DEV).train()
+    lr, wd = 1e-3, 0.01
+    opt = FusedAdamW(model.named_parameters(), lr=lr, weight_decay=wd, max_grad_norm=1.0)
+    ref = {k: v.clone() for k, v in sd.items()}
+    trainable = [n for n, p in model.named_parameters() if p.requires_grad]
+    state, steps = {}, {n: 0 for n in trainable}
+    np.random.seed(11)  # default coin source = np.random.uniform, as in the pinned transformers 4.17
+    seen = set()
+    for it in range(4):
+        b = R.synth_batch(cfg, 2, 6000, seed=70 + it, ragged=True, max_label=12)
+        opt.zero_grad()
+        out = model(b["input_values"].to(DEV), b["attention_mask"].to(DEV), labels=b["labels"].to(DEV))
+        out.loss.backward()
+        skipped = set(model.backbone.last_skipped_layers)
+        seen.add(tuple(sorted(skipped)))
+        leaf = {k: v.clone().requires_grad_(k in trainable) for k, v in ref.items()}
+        loss_ref, _ = R.ctc_forward(leaf, cfg, b["input_values"], b["attention_mask"], b["labels"], skip_layers=skipped)
+        loss_ref.backward()
+        assert abs(float(out.loss) - float(loss_ref)) / abs(float(loss_ref)) < 3e-3, it
+        opt.step()
+        live = [n for n in trainable if leaf[n].grad is not None]
+        assert {int(n.split("layers.")[1].split(".")[0]) for n in trainable if n not in live
+                and ".encoder.layers." in n} == skipped
+        total = torch.sqrt(sum((leaf[n].grad.double() ** 2).sum() for n in live)).float()
+        clip = min(1.0, float(1.0 / (total + 1e-6)))
+        with torch.no_grad():
+            for n in live:  # transformers.AdamW, one parameter at a time with its own step count
+                steps[n] += 1
+                t = steps[n]
+                gr = leaf[n].grad * clip
+                m, v = state.setdefault(n, (torch.zeros_like(ref[n]), torch.zeros_like(ref[n])))
+                m.mul_(0.9).add_(gr, alpha=0.1)
+                v.mul_(0.999).addcmul_(gr, gr, value=0.001)
+                ref[n].addcdiv_(m, v.sqrt().add_(1e-8), value=-lr * (1 - 0.999 ** t) ** 0.5 / (1 - 0.9 ** t))
+                ref[n].add_(ref[n], alpha=-lr * (0.0 if _no_decay(n) else wd))
+    assert len(seen) > 1 and any(seen), seen  # the coins produced different patterns, at least one with a skip
+    params = dict(model.named_parameters())
+    for n in trainable:
+        assert relinf(params[n].detach(), ref[n]) < 2e-3, n
+
+
 def test_graphed_train_step_matches_eager():
     """The CUDA-graph replay of the whole update (graph.GraphedTrainStep) follows the eager path step for step,
     and building the graph leaves model / optimizer state untouched."""

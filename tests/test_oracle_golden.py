@@ -47,6 +47,34 @@ def test_plain_ctc_matches_hf(golden_dir, name, conv_bias):
         assert abs(float(sd[str(n)].grad.norm()) - v) <= 2e-4 * max(v, 1e-3), n
 
 
+def test_layerdrop_matches_hf(golden_dir):
+    """LayerDrop (HF:392-404): the blocks whose coin fell under config.layerdrop are the identity in that step and
+    their parameters get no gradient.  The fixture stores HF's coins; the oracle is driven with their outcome."""
+    g = _load(golden_dir, "plain_ctc_layerdrop")
+    cfg = R.ArchConfig.tiny(num_hidden_layers=int(g["num_hidden_layers"]))
+    seed, batch, samples = int(g["seed"]), int(g["batch"]), int(g["samples"])
+    skipped = [l for l, c in enumerate(g["coins"]) if c < float(g["layerdrop"])]
+    assert skipped == g["skipped"].tolist() and 0 < len(skipped) < cfg.num_hidden_layers
+    sd = R.init_state_dict(cfg, seed=seed, dacs=False)
+    sd = {k: v.clone().requires_grad_(not k.startswith("data2vec_audio.feature_extractor")) for k, v in sd.items()}
+    b = R.synth_batch(cfg, batch, samples, seed=1234 + seed, ragged=True, max_label=12)
+    collect = []
+    loss, logits = R.ctc_forward(sd, cfg, b["input_values"], b["attention_mask"], b["labels"], collect,
+                                 skip_layers=set(skipped))
+    loss.backward()
+    np.testing.assert_allclose(collect[-1].detach().numpy(), g["hidden_last"], rtol=0, atol=5e-5)
+    np.testing.assert_allclose(logits.detach().numpy(), g["logits"], rtol=0, atol=1e-4)
+    np.testing.assert_allclose(float(loss), float(g["loss"]), rtol=1e-5)
+    assert (logits.argmax(-1).numpy() == g["argmax"]).all()
+    for n in g["grad_names"]:
+        ref = g["grad:" + str(n)]
+        scale = max(np.abs(ref).max(), 1e-6)
+        assert np.abs(sd[str(n)].grad.numpy() - ref).max() / scale < 2e-4, n
+    for n in g["none_grad_names"]:  # parameters of the skipped blocks
+        assert sd[str(n)].grad is None, n
+    assert {int(str(n).split("layers.")[1].split(".")[0]) for n in g["none_grad_names"]} == set(skipped)
+
+
 # config-5 variants (finetune_ASRs.py:154-172).  The table mirrors tests/golden/make_golden.py::VARIANTS.
 VARIANTS = {
     "w2v2_group_postln": ("tiny_wav2vec2", {}),
