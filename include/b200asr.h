@@ -224,6 +224,16 @@ int b200asr_weight_norm_bwd(const float* dw, const float* v, const float* g, con
 int b200asr_gelu_add_fwd(const void* c, const void* res, void* y, long long n, int dtype, void* stream);
 int b200asr_gelu_bwd(const void* dy, const void* c, void* dc, long long n, int dtype, void* stream);
 
+/* Element dropout, torch.nn.functional.dropout(x, p, training=True) semantics (HF modeling_data2vec_audio.py
+ * hidden_dropout / activation_dropout / feat_proj_dropout :160-172, 300-346, 359-386; final_dropout
+ * federated/src/models.py:403):  y = res + keep(x) / (1 - p)   (res may be NULL; y may alias x).
+ * The mask is not stored: it is a pure function of (seed, site, offset + *dev_offset, element index), so the backward
+ * pass calls the same entry point on dy with the same keys.  `dev_offset` (device u64, may be NULL) lets a launch
+ * captured in a CUDA graph draw a fresh mask per replay.  n % (16/sizeof) == 0; P(drop) is p rounded to 1/65536. */
+int b200asr_dropout(const void* x, const void* res, void* y, long long n, float p, unsigned long long seed,
+                    unsigned long long site, unsigned long long offset, const unsigned long long* dev_offset, int dtype,
+                    void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * CTC: log_softmax(fp32) + alpha/beta recursions + gradient w.r.t. the logits, one launch for `n_heads`
  * logit tensors sharing targets.  Replaces nn.functional.log_softmax + nn.functional.ctc_loss at

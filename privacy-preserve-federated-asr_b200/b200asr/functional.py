@@ -391,6 +391,93 @@ class EncoderLayerFn(torch.autograd.Function):
                 dln2w, dln2b)
 
 
+class DropoutFn(torch.autograd.Function):
+    """nn.Dropout at a stand-alone site (after the encoder's first LayerNorm HF:380-381, feat_proj_dropout HF:171,
+    final_dropout federated/src/models.py:403): y = keep(x) / (1 - p); backward re-draws the same mask."""
+
+    @staticmethod
+    def forward(ctx, x, p, seed, site, counter):
+        ctx.key = (p, seed, site, counter)
+        return ops.dropout(x, p, seed, site, counter)
+
+    @staticmethod
+    def backward(ctx, dy):
+        p, seed, site, counter = ctx.key
+        return ops.dropout(dy, p, seed, site, counter), None, None, None, None
+
+
+class EncoderLayerDropoutFn(torch.autograd.Function):
+    """EncoderLayerFn with the block's element dropouts applied (HF:300-346):
+         a = O(attention(x));  x1 = LN1(x + drop_h(a));  f = drop_a(gelu(W1 x1));  y = LN2(x1 + drop_h(W2 f)).
+    Each dropout is one b200asr_dropout pass fused with the residual add that follows it; masks are re-drawn from
+    (seed, site, counter) in the backward pass, never stored.  Dropout on the attention probabilities
+    (attention_dropout) sits inside the fused attention kernel's softmax and is not applied.
+    drop = (p_hidden, p_act, seed, site0, counter): sites site0 .. site0+2."""
+
+    @staticmethod
+    def forward(ctx, x, klen, meta, cache: ShadowCache, drop, *P):
+        (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = P
+        B, T, H, eps = meta
+        ph, pa, seed, site, ctr = drop
+        M, d = x.shape
+        dh = d // H
+        scale = dh ** -0.5
+        wqkv = cache.qkv(q_w, k_w, v_w)
+        bqkv = cache.qkv_bias(q_b, k_b, v_b)
+        wo, w1s, w2s = cache.weight(o_w), cache.weight(w1), cache.weight(w2)
+        qkv, _ = ops.linear_fwd(x, wqkv, bqkv)
+        attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale)
+        o, _ = ops.linear_fwd(attn, wo, o_b)
+        s1 = ops.dropout(o, ph, seed, site, ctr, residual=x, out=o)
+        x1, _, m1, r1 = ops.layernorm_fwd(s1, ln1_w, ln1_b, eps)
+        g, u = ops.linear_fwd(x1, w1s, b1, act=ACT_GELU_SAVE_GRAD)
+        g = ops.dropout(g, pa, seed, site + 1, ctr, out=g)
+        o2, _ = ops.linear_fwd(g, w2s, b2)
+        s2 = ops.dropout(o2, ph, seed, site + 2, ctr, residual=x1, out=o2)
+        y, _, m2, r2 = ops.layernorm_fwd(s2, ln2_w, ln2_b, eps)
+        ctx.save_for_backward(x, qkv, attn, lse, s1, m1, r1, x1, u, g, s2, m2, r2, wqkv, wo, w1s, w2s)
+        ctx.params = P
+        ctx.klen = klen
+        ctx.meta = (B, T, H, dh, scale)
+        ctx.drop = drop
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x, qkv, attn, lse, s1, m1, r1, x1, u, g, s2, m2, r2, wqkv, wo, w1s, w2s) = ctx.saved_tensors
+        (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = ctx.params
+        B, T, H, dh, scale = ctx.meta
+        ph, pa, seed, site, ctr = ctx.drop
+        d = x.shape[1]
+        wg = any(ctx.needs_input_grad[5:])  # parameter gradients wanted?
+        ds2, dln2w, dln2b, _ = _ln_bwd(dy, s2, ln2_w, ln2_b, m2, r2, wg)
+        do2 = ops.dropout(ds2, ph, seed, site + 2, ctr)           # gradient of W2 f + b2 (ds2 itself is the residual path)
+        db2 = _bgrad(b2, wg, do2)
+        dw2 = _wgrad(w2, wg, do2, g)                              # g = the dropped activations W2 consumed
+        du = ops.linear_dgrad(do2, w2s, gelu_grad=u)              # (do2 W2) * gelu'
+        du = ops.dropout(du, pa, seed, site + 1, ctr, out=du)     # ... * mask_a / (1 - p_a) (the factors commute)
+        db1 = _bgrad(b1, wg, du)
+        dw1 = _wgrad(w1, wg, du, x1)
+        dx1 = ops.linear_dgrad(du, w1s, residual=ds2)
+        ds1, dln1w, dln1b, _ = _ln_bwd(dx1, s1, ln1_w, ln1_b, m1, r1, wg)
+        do = ops.dropout(ds1, ph, seed, site, ctr)
+        dbo = _bgrad(o_b, wg, do)
+        dwo = _wgrad(o_w, wg, do, attn)
+        dattn = ops.linear_dgrad(do, wo)
+        dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale)
+        dx = ops.linear_dgrad(dqkv, wqkv, residual=ds1) if ctx.needs_input_grad[0] else None
+        dqw = dkw = dvw = dqb = dkb = dvb = None
+        if wg:
+            dbqkv = _bgrad((q_b, k_b, v_b), True, dqkv)
+            dwqkv = _wgrad((q_w, k_w, v_w), True, dqkv, x)
+            if dwqkv is not None:
+                dqw, dkw, dvw = dwqkv[:d], dwqkv[d:2 * d], dwqkv[2 * d:]
+            if dbqkv is not None:
+                dqb, dkb, dvb = dbqkv[:d], dbqkv[d:2 * d], dbqkv[2 * d:]
+        return (dx, None, None, None, None, dqw, dqb, dkw, dkb, dvw, dvb, dwo, dbo, dln1w, dln1b, dw1, db1, dw2, db2,
+                dln2w, dln2b)
+
+
 def _deliver(p, grad):
     """Hand a finished fp32 gradient to p's flat-gradient sink (copy when fresh, add otherwise); returns what autograd
     should receive (None when delivered)."""
@@ -538,6 +625,81 @@ class EncoderLayerStableFn(torch.autograd.Function):
             if not ctx.needs_input_grad[0]:
                 dx = None
         return (dx, None, None, None, dqw, dqb, dkw, dkb, dvw, dvb, dwo, dbo, dln1w, dln1b, dw1, db1, dw2, db2,
+                dln2w, dln2b)
+
+
+class EncoderLayerStableDropoutFn(torch.autograd.Function):
+    """EncoderLayerStableFn with the block's element dropouts (Wav2Vec2EncoderLayerStableLayerNorm.forward):
+         s1 = x + drop_h(O(attn(LN1(x))));   y = s1 + drop_h(W2 drop_a(gelu(W1 LN2(s1)))).
+    drop = (p_hidden, p_act, seed, site0, counter) as in EncoderLayerDropoutFn; attention_dropout is not applied."""
+
+    @staticmethod
+    def forward(ctx, x, klen, meta, cache: ShadowCache, drop, *P):
+        (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = P
+        B, T, H, eps = meta
+        ph, pa, seed, site, ctr = drop
+        M, d = x.shape
+        dh = d // H
+        scale = dh ** -0.5
+        wqkv = cache.qkv(q_w, k_w, v_w)
+        bqkv = cache.qkv_bias(q_b, k_b, v_b)
+        wo, w1s, w2s = cache.weight(o_w), cache.weight(w1), cache.weight(w2)
+        n1, _, m1, r1 = ops.layernorm_fwd(x, ln1_w, ln1_b, eps)
+        qkv, _ = ops.linear_fwd(n1, wqkv, bqkv)
+        attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale)
+        o, _ = ops.linear_fwd(attn, wo, o_b)
+        s1 = ops.dropout(o, ph, seed, site, ctr, residual=x, out=o)
+        n2, _, m2, r2 = ops.layernorm_fwd(s1, ln2_w, ln2_b, eps)
+        g, u = ops.linear_fwd(n2, w1s, b1, act=ACT_GELU_SAVE_GRAD)
+        g = ops.dropout(g, pa, seed, site + 1, ctr, out=g)
+        o2, _ = ops.linear_fwd(g, w2s, b2)
+        y = ops.dropout(o2, ph, seed, site + 2, ctr, residual=s1, out=o2)
+        ctx.save_for_backward(x, m1, r1, n1, qkv, attn, lse, s1, m2, r2, n2, u, g, wqkv, wo, w1s, w2s)
+        ctx.params = P
+        ctx.klen = klen
+        ctx.meta = (B, T, H, dh, scale)
+        ctx.drop = drop
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x, m1, r1, n1, qkv, attn, lse, s1, m2, r2, n2, u, g, wqkv, wo, w1s, w2s) = ctx.saved_tensors
+        (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = ctx.params
+        B, T, H, dh, scale = ctx.meta
+        ph, pa, seed, site, ctr = ctx.drop
+        d = x.shape[1]
+        wg = any(ctx.needs_input_grad[5:])
+        if not dy.is_contiguous():
+            dy = dy.contiguous()
+        do2 = ops.dropout(dy, ph, seed, site + 2, ctr)
+        db2 = _bgrad(b2, wg, do2)
+        dw2 = _wgrad(w2, wg, do2, g)
+        du = ops.linear_dgrad(do2, w2s, gelu_grad=u)
+        du = ops.dropout(du, pa, seed, site + 1, ctr, out=du)
+        db1 = _bgrad(b1, wg, du)
+        dw1 = _wgrad(w1, wg, du, n2)
+        dn2 = ops.linear_dgrad(du, w1s)
+        ds1, dln2w, dln2b, _ = _ln_bwd(dn2, s1, ln2_w, ln2_b, m2, r2, wg, dres_add=dy)   # + residual path of y
+        do = ops.dropout(ds1, ph, seed, site, ctr)
+        dbo = _bgrad(o_b, wg, do)
+        dwo = _wgrad(o_w, wg, do, attn)
+        dattn = ops.linear_dgrad(do, wo)
+        dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale)
+        dqw = dkw = dvw = dqb = dkb = dvb = None
+        if wg:
+            dbqkv = _bgrad((q_b, k_b, v_b), True, dqkv)
+            dwqkv = _wgrad((q_w, k_w, v_w), True, dqkv, n1)
+            if dwqkv is not None:
+                dqw, dkw, dvw = dwqkv[:d], dwqkv[d:2 * d], dwqkv[2 * d:]
+            if dbqkv is not None:
+                dqb, dkb, dvb = dbqkv[:d], dbqkv[d:2 * d], dbqkv[2 * d:]
+        dx = dln1w = dln1b = None
+        if ctx.needs_input_grad[0] or wg:
+            dn1 = ops.linear_dgrad(dqkv, wqkv)
+            dx, dln1w, dln1b, _ = _ln_bwd(dn1, x, ln1_w, ln1_b, m1, r1, wg, dres_add=ds1)  # + residual path of s1
+            if not ctx.needs_input_grad[0]:
+                dx = None
+        return (dx, None, None, None, None, dqw, dqb, dkw, dkb, dvw, dvb, dwo, dbo, dln1w, dln1b, dw1, db1, dw2, db2,
                 dln2w, dln2b)
 
 

@@ -199,6 +199,11 @@ class Data2VecAudioModel(nn.Module):
         # transformers 4.17, "torch" = torch.rand([]) on the CPU generator as in transformers >= 4.3x.
         self.layerdrop_rng = "numpy"
         self.last_skipped_layers = ()
+        # element dropout: masks are a pure function of (dropout_seed, site, dropout_counter, element index); the
+        # counter lives on the device and is bumped once per training forward, so CUDA-graph replays draw fresh masks
+        self.dropout_seed = None  # None: torch.initial_seed() at first use (follows torch.manual_seed)
+        self.register_buffer("dropout_counter", torch.zeros(1, dtype=torch.int64), persistent=False)
+        self._drop_ctr = None
 
     @property
     def compute_dtype(self):
@@ -210,11 +215,10 @@ class Data2VecAudioModel(nn.Module):
     def _check_unsupported(self):
         c = self.config
         if self.training and not self._warned:
-            drops = [_cfg(c, n, 0.0) for n in ("hidden_dropout", "attention_dropout", "activation_dropout",
-                                               "feat_proj_dropout")]
-            if any(d > 0 for d in drops):
-                warnings.warn("b200asr: element dropout is not applied by this build (treated as 0); "
-                              "LayerDrop is applied")
+            if float(_cfg(c, "attention_dropout", 0.0) or 0.0) > 0:
+                warnings.warn("b200asr: attention_dropout (dropout on the softmax probabilities inside the fused "
+                              "attention kernel) is not applied (treated as 0); hidden / activation / feat_proj / "
+                              "final dropout and LayerDrop are applied")
             self._warned = True
         if self.training and _cfg(c, "mask_time_prob", 0.0) > 0.0 and _cfg(c, "apply_spec_augment", True):
             raise NotImplementedError("SpecAugment (mask_time_prob > 0) is not supported; every reference entry "
@@ -249,10 +253,34 @@ class Data2VecAudioModel(nn.Module):
             raise ValueError(f"layerdrop_rng must be 'numpy' or 'torch', got {self.layerdrop_rng!r}")
         return tuple(l for l, u in enumerate(coins) if u < p)
 
+    # dropout sites: 0 feat_proj_dropout, 1 encoder prologue (hidden_dropout), 2 final_dropout, 16 + 4 l + {0, 1, 2}
+    # = block l's {attention output, FFN activation, FFN output}
+    def _p_drop(self, name):
+        return float(_cfg(self.config, name, 0.0) or 0.0) if self.training else 0.0
+
+    def _begin_dropout_step(self):
+        """One counter value per training forward; the clone is what this forward's autograd nodes keep, so a second
+        forward before the backward (gradient accumulation) cannot shift the first one's masks."""
+        self._drop_ctr = None
+        if self.training and any(self._p_drop(n) > 0 for n in ("hidden_dropout", "activation_dropout",
+                                                               "feat_proj_dropout", "final_dropout")):
+            if self.dropout_seed is None:
+                self.dropout_seed = int(torch.initial_seed()) & (2 ** 63 - 1)
+            self.dropout_counter.add_(1)
+            self._drop_ctr = self.dropout_counter.clone()
+
+    def apply_dropout(self, x, name, site):
+        """nn.Dropout(config.<name>) at a stand-alone site (training mode only)."""
+        p = self._p_drop(name)
+        if p <= 0.0 or self._drop_ctr is None:
+            return x
+        return Fn.DropoutFn.apply(x, p, self.dropout_seed, site, self._drop_ctr)
+
     def forward(self, input_values, attention_mask=None, output_hidden_states=False):
         """Returns (hidden [B,T,d] in compute dtype, frame_lengths int32 [B] or None, hidden_states tuple|None)."""
         c = self.config
         self._check_unsupported()
+        self._begin_dropout_step()
         cache = self.cache
         fe = self.feature_extractor.conv_layers
         lns = [getattr(l, "layer_norm", None) for l in fe]
@@ -269,6 +297,7 @@ class Data2VecAudioModel(nn.Module):
         fln = getattr(fp, "layer_norm", None)
         h = Fn.FeatureProjectionFn.apply(feats, None if fln is None else fln.weight, None if fln is None else fln.bias,
                                          fp.projection.weight, fp.projection.bias, eps, cache, klen)
+        h = self.apply_dropout(h, "feat_proj_dropout", 0)  # HF:171 (commutes with zeroing the padded frames)
         enc = self.encoder
         stable = bool(_cfg(c, "do_stable_layer_norm", False))
         if self.family == "data2vec":
@@ -282,15 +311,25 @@ class Data2VecAudioModel(nn.Module):
                                              None if stable else enc.layer_norm.bias, eps,
                                              int(c.num_conv_pos_embedding_groups), int(c.num_conv_pos_embeddings), cache,
                                              pc.weight_g, pc.weight_v, pc.bias)
+        h = self.apply_dropout(h, "hidden_dropout", 1)  # HF:380-381 (after the LayerNorm; pre-LN encoders: after the add)
         d = h.shape[-1]
         x = h.view(B * T, d)
         collected = [h] if output_hidden_states else None
         meta = (B, T, int(c.num_attention_heads), eps)
         block = Fn.EncoderLayerStableFn if stable else Fn.EncoderLayerFn
+        ph, pa = self._p_drop("hidden_dropout"), self._p_drop("activation_dropout")
+        drop_block = None
+        if self._drop_ctr is not None and (ph > 0 or pa > 0):
+            drop_block = Fn.EncoderLayerStableDropoutFn if stable else Fn.EncoderLayerDropoutFn
         skipped = self._layerdrop_coins(len(enc.layers))
         self.last_skipped_layers = skipped
         for li, layer in enumerate(enc.layers):
-            if li not in skipped:  # a dropped block is the identity and its parameters get no gradient
+            if li in skipped:  # a dropped block is the identity and its parameters get no gradient
+                pass
+            elif drop_block is not None:
+                x = drop_block.apply(x, klen, meta, cache, (ph, pa, self.dropout_seed, 16 + 4 * li, self._drop_ctr),
+                                     *layer.params())
+            else:
                 x = block.apply(x, klen, meta, cache, *layer.params())
             if collected is not None and not (stable and li + 1 == len(enc.layers)):
                 collected.append(x.view(B, T, d))
@@ -390,6 +429,7 @@ class Data2VecAudioForCTC(_CTCBase):
         if labels is not None:
             self._check_labels(labels)
         h, klen, hs = self.backbone(input_values, attention_mask, bool(output_hidden_states))
+        h = self.backbone.apply_dropout(h, "final_dropout", 2)  # HF:877-878
         logits = Fn.LinearFn.apply(h, self.lm_head.weight, self.lm_head.bias, self.backbone.cache)
         loss = None
         if labels is not None:
@@ -481,6 +521,7 @@ class DacsData2VecAudioForCTC(_CTCBase):
         if labels is not None:
             self._check_labels(labels)
         h, klen, hs = self.data2vec_audio(input_values, attention_mask, bool(output_hidden_states))
+        h = self.data2vec_audio.apply_dropout(h, "final_dropout", 2)  # models.py:403
         lin = lambda x, m: Fn.LinearFn.apply(x, m.weight, m.bias, cache)
         stage = self.STAGE
         g_lm, g_ad = gumbel_noise if gumbel_noise is not None else (None, None)

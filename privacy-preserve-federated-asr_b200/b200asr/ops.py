@@ -314,6 +314,23 @@ def gelu_bwd(dy: torch.Tensor, c: torch.Tensor) -> torch.Tensor:
     return dc
 
 
+def dropout(x: torch.Tensor, p: float, seed: int, site: int, counter=None, residual: Optional[torch.Tensor] = None,
+            out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """y = residual + keep(x) / (1 - p) (torch.nn.functional.dropout semantics, b200asr_dropout).  The mask is a pure
+    function of (seed, site, counter, element index): the backward pass calls this again on dy with the same keys.
+    counter: host int, or a device int64 tensor [1] (graph-replayable draws)."""
+    x = _c(x)
+    if residual is not None:
+        residual = _c(residual)
+        assert residual.shape == x.shape and residual.dtype == x.dtype
+    y = torch.empty_like(x) if out is None else out
+    dev = counter if isinstance(counter, torch.Tensor) else None
+    host = 0 if dev is not None or counter is None else int(counter)
+    check(lib.b200asr_dropout(_p(x), _p(residual), _p(y), x.numel(), float(p), int(seed) & (2 ** 64 - 1), int(site),
+                              host, _p(dev), dt(x), _st()), "dropout")
+    return y
+
+
 # ----------------------------------------------------------------------------- GEMM
 def gemm_raw(A, B, Cout, M, N, K, lda, ldb, ldc, a_kmajor=True, b_kmajor=True, bias=None, residual=None,
              aux_out=None, aux_in=None, act=ACT_NONE, mul_gelu_grad=False, alpha=1.0, batch0=1, batch1=1,

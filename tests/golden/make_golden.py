@@ -123,6 +123,57 @@ def case_layerdrop(tag, cfg, batch, samples, seed, layerdrop, coin_seed):
     print(tag, "loss", float(out.loss), "skipped", skipped.tolist(), "coins", coins.round(3).tolist())
 
 
+def case_dropout(tag, cfg, batch, samples, seed, ps, mask_seed):
+    """HF Data2VecAudioForCTC in training mode with element dropout (attention_dropout 0).  torch.nn.Dropout.forward
+    is replaced by oracle.data2vec_ref.call_order_mask (k-th call -> generator seeded mask_seed + k), so the fixture
+    pins WHERE each dropout sits and with which probability; the oracle replays the same rule."""
+    from transformers import Data2VecAudioForCTC
+    sd = R.init_state_dict(cfg, seed=seed, dacs=False)
+    hc = hf_config(cfg)
+    for k, v in ps.items():
+        setattr(hc, k, v)
+    m = Data2VecAudioForCTC(hc)
+    m.load_state_dict(sd, strict=True)
+    m.freeze_feature_encoder()
+    m.train()
+    b = R.synth_batch(cfg, batch, samples, seed=1234 + seed, ragged=True, max_label=12)
+    calls = {"k": 0, "ps": []}
+    orig = torch.nn.Dropout.forward
+
+    def patched(self, x):
+        k = calls["k"]
+        calls["k"] += 1
+        calls["ps"].append(self.p)
+        return R.call_order_mask(x, self.p, mask_seed, k)
+
+    torch.nn.Dropout.forward = patched
+    try:
+        out = m(input_values=b["input_values"], attention_mask=b["attention_mask"], labels=b["labels"],
+                output_hidden_states=True)
+    finally:
+        torch.nn.Dropout.forward = orig
+    out.loss.backward()
+    g = {n: p.grad.detach().clone() for n, p in m.named_parameters() if p.grad is not None}
+    keep = ["lm_head.weight", "data2vec_audio.feature_projection.projection.weight",
+            "data2vec_audio.encoder.layers.0.attention.out_proj.bias",
+            "data2vec_audio.encoder.layers.0.feed_forward.intermediate_dense.weight",
+            "data2vec_audio.encoder.layers.1.feed_forward.output_dense.bias",
+            "data2vec_audio.encoder.layers.1.attention.q_proj.weight"]
+    np.savez_compressed(
+        os.path.join(OUT, f"{tag}.npz"),
+        seed=seed, batch=batch, samples=samples, mask_seed=mask_seed, n_dropout_calls=calls["k"],
+        dropout_call_ps=np.array(calls["ps"]), p_names=np.array(list(ps.keys())), p_values=np.array(list(ps.values())),
+        loss=out.loss.detach().numpy(), logits=out.logits.detach().numpy(),
+        hidden_last=out.hidden_states[-1].detach().numpy(),
+        grad_names=np.array(keep), **{"grad:" + k: g[k].numpy() for k in keep},
+        gnorm_names=np.array(list(g.keys())), gnorm_values=np.array([float(v.norm()) for v in g.values()]),
+    )
+    print(tag, "loss", float(out.loss.detach()), "dropout calls", calls["k"], calls["ps"])
+
+
+DROPOUT_PS = dict(hidden_dropout=0.1, activation_dropout=0.15, feat_proj_dropout=0.05, final_dropout=0.2)
+
+
 def case_variant_ctc(tag, cfg, batch, samples, seed, use_mask):
     """Config-5 variants (centralized/finetune_ASRs.py:154-172): HF Wav2Vec2ForCTC / HubertForCTC, eager attention.
     The oracle state_dict uses the transformers-4.17 weight_norm key names (weight_g / weight_v, the reference's
@@ -268,6 +319,7 @@ def main():
     case_fedavg("fedavg")
     case_layerdrop("plain_ctc_layerdrop", R.ArchConfig.tiny(num_hidden_layers=4), batch=2, samples=6000, seed=3,
                    layerdrop=0.5, coin_seed=5)
+    case_dropout("plain_ctc_dropout", R.ArchConfig.tiny(), batch=2, samples=6000, seed=5, ps=DROPOUT_PS, mask_seed=900)
     for tag, (_, _, batch, samples, seed, use_mask) in VARIANTS.items():
         case_variant_ctc(tag, variant_cfg(tag), batch, samples, seed, use_mask)
 
@@ -276,6 +328,8 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "variants":  # only (re)generate the config-5 variant fixtures
         for tag, (_, _, batch, samples, seed, use_mask) in VARIANTS.items():
             case_variant_ctc(tag, variant_cfg(tag), batch, samples, seed, use_mask)
+    elif len(sys.argv) > 1 and sys.argv[1] == "dropout":
+        case_dropout("plain_ctc_dropout", R.ArchConfig.tiny(), batch=2, samples=6000, seed=5, ps=DROPOUT_PS, mask_seed=900)
     elif len(sys.argv) > 1 and sys.argv[1] == "layerdrop":
         case_layerdrop("plain_ctc_layerdrop", R.ArchConfig.tiny(num_hidden_layers=4), batch=2, samples=6000, seed=3,
                        layerdrop=0.5, coin_seed=5)

@@ -1,0 +1,158 @@
+"""GPU: element dropout on the product path (b200asr_dropout + the dropout variants of the encoder blocks).
+
+torch's dropout RNG stream cannot be reproduced by another kernel, so parity is defined GIVEN the masks: the masks the
+library drew in a training step are read back (the same entry point applied to a tensor of ones with the same keys),
+handed to the CPU oracle through its `drop(site, x)` hook -- whose dropout placement is pinned against HF by
+tests/golden/plain_ctc_dropout.npz (tests/test_oracle_golden.py) -- and loss / logits / every gradient are compared."""
+from types import SimpleNamespace
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+if not torch.cuda.is_available():
+    pytest.skip("needs a CUDA device", allow_module_level=True)
+
+from b200asr import modeling as M  # noqa: E402
+from b200asr import ops  # noqa: E402
+from oracle import data2vec_ref as R  # noqa: E402
+
+DEV = "cuda"
+TOL = {torch.float32: 1e-3, torch.bfloat16: 2e-2}  # BASELINE.json: loss / logits relative tolerance
+PS = dict(hidden_dropout=0.1, activation_dropout=0.15, feat_proj_dropout=0.05, final_dropout=0.2)
+
+
+def relinf(a, b):
+    a = torch.as_tensor(a).float().cpu()
+    b = torch.as_tensor(b).float().cpu()
+    return float((a - b).abs().max() / max(float(b.abs().max()), 1e-6))
+
+
+@pytest.mark.parametrize("p", [0.1, 0.5])
+def test_dropout_kernel_mask_properties(p):
+    n = 1 << 20
+    ones32 = torch.ones(n, device=DEV)
+    y = ops.dropout(ones32, p, seed=1234, site=7, counter=3)
+    vals = torch.unique(y)
+    assert vals.numel() == 2 and float(vals[0]) == 0.0 and abs(float(vals[1]) - 1.0 / (1.0 - p)) < 1e-6
+    keep = float((y != 0).float().mean())
+    p_q = round(p * 65536) / 65536  # the drop probability is p rounded to 1/65536
+    assert abs(keep - (1.0 - p_q)) < 5 * (p_q * (1 - p_q) / n) ** 0.5
+    # deterministic in its keys; dtype-independent; device counter == host counter; other keys -> other masks
+    assert torch.equal(y, ops.dropout(ones32, p, seed=1234, site=7, counter=3))
+    yb = ops.dropout(torch.ones(n, device=DEV, dtype=torch.bfloat16), p, seed=1234, site=7, counter=3)
+    assert torch.equal(yb != 0, y != 0)
+    ctr = torch.tensor([3], dtype=torch.int64, device=DEV)
+    assert torch.equal(y, ops.dropout(ones32, p, seed=1234, site=7, counter=ctr))
+    for other in (dict(seed=1235, site=7, counter=3), dict(seed=1234, site=8, counter=3), dict(seed=1234, site=7, counter=4)):
+        z = ops.dropout(ones32, p, **other)
+        agree = float(((z != 0) == (y != 0)).float().mean())
+        assert abs(agree - (p_q ** 2 + (1 - p_q) ** 2)) < 0.01, other  # independent masks
+    # residual add and in-place use
+    x = torch.randn(n, device=DEV)
+    r = torch.randn(n, device=DEV)
+    ref = r + x * y
+    got = ops.dropout(x, p, seed=1234, site=7, counter=3, residual=r)
+    assert torch.allclose(got, ref, rtol=1e-6, atol=1e-6)
+    x2 = x.clone()
+    assert ops.dropout(x2, p, seed=1234, site=7, counter=3, residual=r, out=x2).data_ptr() == x2.data_ptr()
+    assert torch.equal(x2, got)
+    # no long runs: neighbouring elements are not correlated
+    k = (y != 0).float()
+    corr = float(((k[1:] - k.mean()) * (k[:-1] - k.mean())).mean() / k.var())
+    assert abs(corr) < 0.01
+
+
+def _masks_from_library(backbone, cfg, B, T, ps):
+    """Read the masks of the last training forward back: dropout(ones) with that forward's keys."""
+    seed, ctr = backbone.dropout_seed, backbone._drop_ctr
+    d, inter = cfg.hidden_size, cfg.intermediate_size
+
+    def mask(site, cols, p):
+        if p <= 0:
+            return None
+        return ops.dropout(torch.ones(B * T * cols, device=DEV), p, seed, site, ctr).view(B, T, cols).cpu()
+
+    masks = {0: mask(0, d, ps["feat_proj_dropout"]), 1: mask(1, d, ps["hidden_dropout"]), 2: mask(2, d, ps["final_dropout"])}
+    for l in range(cfg.num_hidden_layers):
+        masks[16 + 4 * l] = mask(16 + 4 * l, d, ps["hidden_dropout"])
+        masks[16 + 4 * l + 1] = mask(16 + 4 * l + 1, inter, ps["activation_dropout"])
+        masks[16 + 4 * l + 2] = mask(16 + 4 * l + 2, d, ps["hidden_dropout"])
+    return masks
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("family", ["data2vec_postln", "hubert_stable"])
+def test_dropout_training_step_vs_oracle_given_masks(family, dtype):
+    if family == "data2vec_postln":
+        cfg, cls = R.ArchConfig.tiny(), M.Data2VecAudioForCTC
+        c = SimpleNamespace(**{k: (tuple(v) if isinstance(v, (list, tuple)) else v) for k, v in cfg.__dict__.items()})
+    else:
+        cfg, cls = R.ArchConfig.tiny_hubert(), M.HubertForCTC
+        c = SimpleNamespace(**cfg.to_hf_kwargs())
+    for k, v in PS.items():
+        setattr(c, k, v)
+    c.attention_dropout = 0.0
+    sd = R.init_state_dict(cfg, seed=6, dacs=False)
+    model = cls(c, compute_dtype=dtype)
+    model.load_state_dict(sd, strict=True)
+    model.freeze_feature_encoder()
+    model.to(DEV).train()
+    model.backbone.dropout_seed = 4242
+    b = R.synth_batch(cfg, 2, 6000, seed=77, ragged=True, max_label=12)
+    out = model(input_values=b["input_values"].to(DEV), attention_mask=b["attention_mask"].to(DEV), labels=b["labels"].to(DEV))
+    out.loss.backward()
+    B, T = out.logits.shape[:2]
+    masks = _masks_from_library(model.backbone, cfg, B, T, PS)
+    assert all(m is not None and 0 < float((m != 0).float().mean()) < 1 for m in masks.values())
+    trainable = {n for n, p in model.named_parameters() if p.requires_grad}
+    leaf = {k: v.clone().requires_grad_(k in trainable) for k, v in sd.items()}
+    loss_ref, logits_ref = R.ctc_forward(leaf, cfg, b["input_values"], b["attention_mask"], b["labels"],
+                                         drop=lambda site, x: x * masks[site])
+    loss_ref.backward()
+    tol = TOL[dtype]
+    assert abs(float(out.loss) - float(loss_ref)) / abs(float(loss_ref)) < tol
+    assert relinf(out.logits, logits_ref.detach()) < tol
+    gt = 2e-3 if dtype == torch.float32 else 6e-2
+    params = dict(model.named_parameters())
+    for n in sorted(trainable):
+        if n.endswith("k_proj.bias"):
+            continue  # zero in exact arithmetic (softmax shift invariance)
+        ref = leaf[n].grad
+        got = params[n].grad
+        assert got is not None, n
+        assert abs(float(got.float().norm()) - float(ref.norm())) <= gt * max(float(ref.norm()), 1e-3), n
+        if dtype == torch.float32:
+            assert relinf(got, ref) < gt, n
+    # a second forward draws other masks; eval mode applies none (deterministic, equals the dropout-free oracle)
+    out2 = model(input_values=b["input_values"].to(DEV), attention_mask=b["attention_mask"].to(DEV), labels=b["labels"].to(DEV))
+    assert float(out2.loss) != float(out.loss)
+    model.eval()
+    with torch.no_grad():
+        e1 = model(input_values=b["input_values"].to(DEV), attention_mask=b["attention_mask"].to(DEV))
+    _, logits_eval = R.ctc_forward(sd, cfg, b["input_values"], b["attention_mask"])
+    assert relinf(e1.logits, logits_eval) < tol
+
+
+def test_dropout_graphed_step_draws_fresh_masks():
+    """The device counter is bumped inside the captured step: every replay of the CUDA graph draws new masks."""
+    from b200asr.graph import GraphedTrainStep
+    from b200asr.optim import FusedAdamW
+    cfg = R.ArchConfig.tiny()
+    c = SimpleNamespace(**{k: (tuple(v) if isinstance(v, (list, tuple)) else v) for k, v in cfg.__dict__.items()})
+    c.hidden_dropout, c.activation_dropout, c.final_dropout = 0.1, 0.1, 0.1
+    model = M.Data2VecAudioForCTC(c, compute_dtype=torch.bfloat16)
+    model.load_state_dict(R.init_state_dict(cfg, seed=8, dacs=False))
+    model.freeze_feature_encoder()
+    model.to(DEV).train()
+    opt = FusedAdamW(model.named_parameters(), lr=0.0, weight_decay=0.0)  # lr 0: the weights never move
+    b = {k: v.to(DEV) for k, v in R.synth_batch(cfg, 2, 6000, seed=78, ragged=True, max_label=12).items()
+         if k in ("input_values", "attention_mask", "labels")}
+    step = GraphedTrainStep(model, opt, b)
+    c0 = int(model.backbone.dropout_counter)
+    losses = [float(step(b)) for _ in range(4)]
+    assert int(model.backbone.dropout_counter) == c0 + 4
+    assert len(set(losses)) == 4, losses  # same weights, same batch, different masks
+    assert max(losses) / min(losses) < 1.5
