@@ -172,7 +172,9 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    cfg = large_config()
+    pd = float(args.dropout)
+    cfg = large_config(hidden_dropout=pd, activation_dropout=pd, final_dropout=pd, feat_proj_dropout=0.0,
+                       attention_dropout=0.0, layerdrop=0.0)
     torch.manual_seed(0)  # identical initial weights on every client
     model = M.Data2VecAudioForCTC(cfg, compute_dtype=torch.bfloat16)
     model.freeze_feature_encoder()
@@ -354,6 +356,10 @@ def run_b200(args):
             "dtype": "bf16", "data": "synthetic",
             "config": {"workload": WORKLOAD, "global_batch": BATCH * world, "audio_s_per_step": audio_s,
                        "clients": world, "trainable_params": n_train, "frames_per_utt": frames,
+                       "regularisation": (f"hidden / activation / final dropout {pd:g} applied in the timed step (masks drawn "
+                                          "in-kernel, fresh per CUDA-graph replay); " if pd > 0 else "element dropout 0; ")
+                                         + "attention-probability dropout not applied; layerdrop 0 = all 24 blocks run "
+                                           "every step (the reference default 0.1 would skip 10% of them)",
                        "l2_policy": "inputs+weights+saved activations per step (>3 GB) exceed the 126 MB L2; no flush",
                        "e2e_input_pipeline": "each step's pinned-host -> device copy runs on a copy stream, issued while the previous step computes; the loss is read back every step",
                        "fedavg_impl": chosen["impl"] if world > 1 else None,
@@ -394,6 +400,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--fedavg", default="auto", choices=["auto", "peer", "nccl"],
                     help="N>1 aggregation: fused peer-memory kernel, scale kernel + NCCL all-reduce, or whichever measures faster in warm-up")
+    ap.add_argument("--dropout", type=float, default=0.1,
+                    help="hidden_dropout = activation_dropout = final_dropout = P in the timed training step "
+                         "(0.1 = the Data2VecAudioConfig defaults the reference fine-tunes with; 0 = the parity setting)")
     ap.add_argument("--eager", action="store_true", help="issue every launch from Python instead of replaying the CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -89,6 +89,14 @@ def colsum(cols):
     return mk
 
 
+def dropout(cols, res):
+    def mk():
+        x = rnd(M, cols); r = rnd(M, cols) if res else None
+        y = torch.empty_like(x)
+        return lambda: ops.dropout(x, 0.1, 1234, 16, 7, residual=r, out=y)
+    return mk
+
+
 def mha_f():
     def mk():
         qkv = rnd(M, 3 * D)
@@ -155,6 +163,9 @@ tot += 48 * bench("ln_bwd   [3992,1024] affine + colsum  (x48)", ln_bwd(D, M, Tr
 tot += 5 * bench("ln_bwd   [3992,1024] no affine gelu cs (x5)", ln_bwd(D, M, False, True, ACT_GELU), nbytes=3 * M * D * e)
 tot += 24 * bench("colsum   [3992,4096]                 (x24)", colsum(F), nbytes=M * F * e)
 tot += 24 * bench("colsum   [3992,3072]                 (x24)", colsum(3 * D), nbytes=M * 3 * D * e)
+bench("dropout [3992,1024] + residual (x96 when p > 0)", dropout(D, True), nbytes=3 * M * D * e)
+bench("dropout [3992,1024]            (x52 when p > 0)", dropout(D, False), nbytes=2 * M * D * e)
+bench("dropout [3992,4096] activation (x48 when p > 0)", dropout(F, False), nbytes=2 * M * F * e)
 tot += 24 * bench("mha_fwd  B8 T499 H16 dh64            (x24)", mha_f(), flops=4.0 * B * H * T * T * 64)
 tot += 24 * bench("mha_bwd  B8 T499 H16 dh64 (+dsum,dQ) (x24)", mha_b(), flops=10.0 * B * H * T * T * 64)
 tot += bench("ctc      B8 T499 V32 L<=120 fwd+bwd   (x1)", ctc(), iters=10)
