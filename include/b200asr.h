@@ -224,6 +224,16 @@ int b200asr_weight_norm_bwd(const float* dw, const float* v, const float* g, con
 int b200asr_gelu_add_fwd(const void* c, const void* res, void* y, long long n, int dtype, void* stream);
 int b200asr_gelu_bwd(const void* dy, const void* c, void* dc, long long n, int dtype, void* stream);
 
+/* b200asr_layernorm_fwd with an inverted dropout applied to x before the residual add:
+ *   sum_out = res + dropout(x),  y = act(LN(sum_out) * w + b)
+ * = `hidden_states = attn_residual + self.dropout(hidden_states); hidden_states = self.layer_norm(hidden_states)`
+ * (HF modeling_data2vec_audio.py:321-324, 327-328) in one pass.  Mask keys as b200asr_dropout (below): the same
+ * (seed, site, offset) give the same mask there, which is how the backward pass re-draws it.  cols % 8 == 0. */
+int b200asr_layernorm_dropout_fwd(const void* x, const void* res, const float* w, const float* b, void* y, void* sum_out,
+                                  float* mean, float* rstd, int rows, int cols, float eps, int act, float p,
+                                  unsigned long long seed, unsigned long long site, unsigned long long offset,
+                                  const unsigned long long* dev_offset, int dtype, void* stream);
+
 /* Element dropout, torch.nn.functional.dropout(x, p, training=True) semantics (HF modeling_data2vec_audio.py
  * hidden_dropout / activation_dropout / feat_proj_dropout :160-172, 300-346, 359-386; final_dropout
  * federated/src/models.py:403):  y = res + keep(x) / (1 - p)   (res may be NULL; y may alias x).

@@ -428,13 +428,12 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
         qkv, _ = ops.linear_fwd(x, wqkv, bqkv)
         attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale)
         o, _ = ops.linear_fwd(attn, wo, o_b)
-        s1 = ops.dropout(o, ph, seed, site, ctr, residual=x, out=o)
-        x1, _, m1, r1 = ops.layernorm_fwd(s1, ln1_w, ln1_b, eps)
+        # s1 = x + drop_h(o) and LN1 in one pass (b200asr_layernorm_dropout_fwd)
+        x1, s1, m1, r1 = ops.layernorm_fwd(o, ln1_w, ln1_b, eps, res=x, want_sum=True, drop=(ph, seed, site, ctr))
         g, u = ops.linear_fwd(x1, w1s, b1, act=ACT_GELU_SAVE_GRAD)
         g = ops.dropout(g, pa, seed, site + 1, ctr, out=g)
         o2, _ = ops.linear_fwd(g, w2s, b2)
-        s2 = ops.dropout(o2, ph, seed, site + 2, ctr, residual=x1, out=o2)
-        y, _, m2, r2 = ops.layernorm_fwd(s2, ln2_w, ln2_b, eps)
+        y, s2, m2, r2 = ops.layernorm_fwd(o2, ln2_w, ln2_b, eps, res=x1, want_sum=True, drop=(ph, seed, site + 2, ctr))
         ctx.save_for_backward(x, qkv, attn, lse, s1, m1, r1, x1, u, g, s2, m2, r2, wqkv, wo, w1s, w2s)
         ctx.params = P
         ctx.klen = klen

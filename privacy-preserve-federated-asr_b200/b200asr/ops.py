@@ -147,8 +147,10 @@ class on_side_stream:
 
 
 # ----------------------------------------------------------------------------- norm / elementwise
-def layernorm_fwd(x, w, b, eps, res=None, act=ACT_NONE, want_sum=False, want_stats=True):
-    """y = act(LN(x (+res)) * w + b) over the last dim.  Returns (y, s_or_None, mean, rstd)."""
+def layernorm_fwd(x, w, b, eps, res=None, act=ACT_NONE, want_sum=False, want_stats=True, drop=None):
+    """y = act(LN(x (+res)) * w + b) over the last dim.  Returns (y, s_or_None, mean, rstd).
+    drop = (p, seed, site, counter): x goes through an inverted dropout first (keys as ops.dropout), i.e.
+    s = res + dropout(x), in the same pass."""
     x = _c(x)
     cols = x.shape[-1]
     rows = x.numel() // cols
@@ -158,6 +160,14 @@ def layernorm_fwd(x, w, b, eps, res=None, act=ACT_NONE, want_sum=False, want_sta
     rstd = torch.empty(rows, dtype=torch.float32, device=x.device) if want_stats else None
     if res is not None:
         res = _c(res)
+    if drop is not None:
+        p, seed, site, counter = drop
+        dev = counter if isinstance(counter, torch.Tensor) else None
+        host = 0 if dev is not None or counter is None else int(counter)
+        check(lib.b200asr_layernorm_dropout_fwd(_p(x), _p(res), _p(w), _p(b), _p(y), _p(s), _p(mean), _p(rstd), rows, cols,
+                                                float(eps), act, float(p), int(seed) & (2 ** 64 - 1), int(site), host,
+                                                _p(dev), dt(x), _st()), "layernorm_dropout_fwd")
+        return y, s, mean, rstd
     check(lib.b200asr_layernorm_fwd(_p(x), _p(res), _p(w), _p(b), _p(y), _p(s), _p(mean), _p(rstd), rows, cols,
                                     float(eps), act, dt(x), _st()), "layernorm_fwd")
     return y, s, mean, rstd

@@ -218,6 +218,53 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 b
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
+// ---- counter-based dropout masks (dropout.cu, LayerNorm forward with a fused dropout + residual add) ----------------
+// Philox4x32-10 keyed by (seed, site) over the counter (element index / 8, step): one call = the 16-bit uniforms of 8
+// consecutive elements, so an element's keep decision does not depend on the dtype's vector width.
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        k.x += 0x9E3779B9u;
+        k.y += 0xBB67AE85u;
+    }
+    return c;
+}
+struct DropKeys {
+    uint2 key;
+    uint32_t thresh16;  // keep iff u16 >= thresh16
+    float scale;        // 1 / (1 - p)
+    unsigned long long offset;
+    const unsigned long long* dev_offset;  // optional device-side step counter added to offset
+};
+static inline DropKeys make_drop_keys(float p, unsigned long long seed, unsigned long long site, unsigned long long offset,
+                                      const unsigned long long* dev_offset) {
+    DropKeys k;
+    const unsigned long long kk = seed ^ (site * 0x9E3779B97F4A7C15ull);
+    k.key = make_uint2((uint32_t)kk, (uint32_t)(kk >> 32));
+    k.thresh16 = (uint32_t)lrintf(p * 65536.f);
+    k.scale = 1.0f / (1.0f - p);
+    k.offset = offset;
+    k.dev_offset = dev_offset;
+    return k;
+}
+// 16-bit uniforms of the N (4 or 8) consecutive elements starting at element e0 (e0 % N == 0)
+template <int N>
+__device__ __forceinline__ void dropout_uniforms(unsigned long long e0, uint2 key, unsigned long long offset, uint32_t* u) {
+    const unsigned long long blk = e0 >> 3;
+    const uint4 r = philox4x32_10(make_uint4((uint32_t)blk, (uint32_t)(blk >> 32), (uint32_t)offset, (uint32_t)(offset >> 32)), key);
+    if constexpr (N == 8) {
+        u[0] = r.x & 0xffffu; u[1] = r.x >> 16; u[2] = r.y & 0xffffu; u[3] = r.y >> 16;
+        u[4] = r.z & 0xffffu; u[5] = r.z >> 16; u[6] = r.w & 0xffffu; u[7] = r.w >> 16;
+    } else {  // fp32: 4 elements per vector = the low or the high half of the 8-element block
+        const bool hi = (e0 & 4) != 0;
+        const uint32_t a = hi ? r.z : r.x, b = hi ? r.w : r.y;
+        u[0] = a & 0xffffu; u[1] = a >> 16; u[2] = b & 0xffffu; u[3] = b >> 16;
+    }
+}
+
 #define B200_DISPATCH_DTYPE(dtype, ...)                                        \
     do {                                                                       \
         if ((dtype) == B200ASR_F32) { using T = float; __VA_ARGS__ }           \

@@ -22,14 +22,18 @@ template <int N> __device__ __forceinline__ void load_params(const float* __rest
     }
 }
 
-template <typename T, int NV>
+// DROP: x is first passed through an inverted dropout (mask from DropKeys, see common.cuh) -- y = LN(res + drop(x)),
+// sum_out = res + drop(x): the hidden_dropout + residual add + LayerNorm of a post-LN encoder block in one pass.
+template <typename T, int NV, bool DROP>
 __global__ void __launch_bounds__(128) ln_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res,
                                                      const float* __restrict__ w, const float* __restrict__ b,
                                                      T* __restrict__ y, T* __restrict__ sum_out,
                                                      float* __restrict__ mean_out, float* __restrict__ rstd_out,
-                                                     int rows, int cols, float eps, int act) {
+                                                     int rows, int cols, float eps, int act, DropKeys dk) {
     constexpr int N = Vec16<T>::N;
     pdl_enter();
+    unsigned long long drop_offset = 0;
+    if (DROP) drop_offset = dk.offset + (dk.dev_offset ? *dk.dev_offset : 0ull);
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -46,6 +50,12 @@ __global__ void __launch_bounds__(128) ln_fwd_kernel(const T* __restrict__ x, co
                 Vec16<T> a;
                 a.load(x + base + (long long)vi * N);
                 a.unpack(v[i]);
+                if (DROP) {
+                    uint32_t u[N];
+                    dropout_uniforms<N>((unsigned long long)(base + (long long)vi * N), dk.key, drop_offset, u);
+#pragma unroll
+                    for (int j = 0; j < N; ++j) v[i][j] = (u[j] >= dk.thresh16) ? v[i][j] * dk.scale : 0.f;
+                }
                 if (res) {
                     Vec16<T> r;
                     float rf[N];
@@ -374,7 +384,8 @@ __global__ void __launch_bounds__(256) colsum_partial_vec_kernel(const T* __rest
 
 template <typename T>
 static int launch_ln_fwd(const void* x, const void* res, const float* w, const float* b, void* y, void* sum_out,
-                         float* mean, float* rstd, int rows, int cols, float eps, int act, cudaStream_t st) {
+                         float* mean, float* rstd, int rows, int cols, float eps, int act, cudaStream_t st,
+                         const DropKeys* drop = nullptr) {
     constexpr int N = Vec16<T>::N;
     const int nvec = cols / N;
     const int nv = ceil_div(nvec, 32);
@@ -382,9 +393,16 @@ static int launch_ln_fwd(const void* x, const void* res, const float* w, const f
     int grid = ceil_div(rows, warps_per_block);
     const int cap = num_sms() * 16;
     if (grid > cap) grid = cap;
-#define LN_FWD_CASE(NVV)                                                                                      \
-    launch_pdl(ln_fwd_kernel<T, NVV>, dim3(grid), dim3(128), 0, st, (const T*)x, (const T*)res, w, b, (T*)y,  \
-               (T*)sum_out, mean, rstd, rows, cols, eps, act)
+    const DropKeys dk = drop ? *drop : DropKeys{};
+#define LN_FWD_CASE(NVV)                                                                                              \
+    do {                                                                                                              \
+        if (drop)                                                                                                     \
+            launch_pdl(ln_fwd_kernel<T, NVV, true>, dim3(grid), dim3(128), 0, st, (const T*)x, (const T*)res, w, b,   \
+                       (T*)y, (T*)sum_out, mean, rstd, rows, cols, eps, act, dk);                                     \
+        else                                                                                                          \
+            launch_pdl(ln_fwd_kernel<T, NVV, false>, dim3(grid), dim3(128), 0, st, (const T*)x, (const T*)res, w, b,  \
+                       (T*)y, (T*)sum_out, mean, rstd, rows, cols, eps, act, dk);                                     \
+    } while (0)
     if (nv <= 1) LN_FWD_CASE(1);
     else if (nv <= 2) LN_FWD_CASE(2);
     else if (nv <= 4) LN_FWD_CASE(4);
@@ -444,6 +462,23 @@ int b200asr_layernorm_fwd(const void* x, const void* res, const float* w, const 
     B200_REQUIRE(!w || (((uintptr_t)w | (uintptr_t)b) & 15) == 0, "layernorm_fwd: w/b must be 16-byte aligned");
     B200_DISPATCH_DTYPE(dtype, {
         return launch_ln_fwd<T>(x, res, w, b, y, sum_out, mean, rstd, rows, cols, eps, act, as_stream(stream));
+    });
+    return B200ASR_OK;
+}
+
+int b200asr_layernorm_dropout_fwd(const void* x, const void* res, const float* w, const float* b, void* y, void* sum_out,
+                                  float* mean, float* rstd, int rows, int cols, float eps, int act, float p,
+                                  unsigned long long seed, unsigned long long site, unsigned long long offset,
+                                  const unsigned long long* dev_offset, int dtype, void* stream) {
+    if (rows <= 0) return B200ASR_OK;
+    B200_REQUIRE(x && y, "layernorm_dropout_fwd: null pointer");
+    B200_REQUIRE((w == nullptr) == (b == nullptr), "layernorm_dropout_fwd: w and b must both be given or both NULL");
+    B200_REQUIRE(cols > 0 && cols % 8 == 0, "layernorm_dropout_fwd: cols=%d must be a multiple of 8", cols);
+    B200_REQUIRE(!w || (((uintptr_t)w | (uintptr_t)b) & 15) == 0, "layernorm_dropout_fwd: w/b must be 16-byte aligned");
+    B200_REQUIRE(p >= 0.f && p < 1.f, "layernorm_dropout_fwd: p=%f must be in [0, 1)", (double)p);
+    const DropKeys dk = make_drop_keys(p, seed, site, offset, dev_offset);
+    B200_DISPATCH_DTYPE(dtype, {
+        return launch_ln_fwd<T>(x, res, w, b, y, sum_out, mean, rstd, rows, cols, eps, act, as_stream(stream), &dk);
     });
     return B200ASR_OK;
 }
