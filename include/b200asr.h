@@ -234,6 +234,13 @@ int b200asr_layernorm_dropout_fwd(const void* x, const void* res, const float* w
                                   unsigned long long seed, unsigned long long site, unsigned long long offset,
                                   const unsigned long long* dev_offset, int dtype, void* stream);
 
+/* y = dropout(x) and out[cols] = column sums of y in one pass over x [rows, cols] (contiguous): the backward of a
+ * Linear whose output went through a dropout -- `d_out = dropout(ds)` feeds the data / weight gradients, its column sums
+ * are the bias gradient.  Keys as b200asr_dropout; workspace as b200asr_colsum.  cols % 8 == 0. */
+int b200asr_dropout_colsum(const void* x, void* y, float* out, void* workspace, size_t workspace_bytes, int rows, int cols,
+                           float p, unsigned long long seed, unsigned long long site, unsigned long long offset,
+                           const unsigned long long* dev_offset, int dtype, void* stream);
+
 /* Element dropout, torch.nn.functional.dropout(x, p, training=True) semantics (HF modeling_data2vec_audio.py
  * hidden_dropout / activation_dropout / feat_proj_dropout :160-172, 300-346, 359-386; final_dropout
  * federated/src/models.py:403):  y = res + keep(x) / (1 - p)   (res may be NULL; y may alias x).

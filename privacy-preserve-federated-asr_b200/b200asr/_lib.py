@@ -76,6 +76,7 @@ SIGNATURES = {
     "b200asr_gelu_add_fwd": (i32, [vp, vp, vp, i64, i32, vp]),
     "b200asr_gelu_bwd": (i32, [vp, vp, vp, i64, i32, vp]),
     "b200asr_layernorm_dropout_fwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, f32, i32, f32, u64, u64, u64, vp, i32, vp]),
+    "b200asr_dropout_colsum": (i32, [vp, vp, vp, vp, sz, i32, i32, f32, u64, u64, u64, vp, i32, vp]),
     "b200asr_dropout": (i32, [vp, vp, vp, i64, f32, u64, u64, u64, vp, i32, vp]),
     "b200asr_ctc_workspace_bytes": (sz, [i32, i32, i32, i32]),
     "b200asr_ctc_fwd_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, sz, i32, i32, i32, i32, i32, i32, i32, i32, vp]),

@@ -161,6 +161,33 @@ def _bgrad(ps, need, dy):
     return None
 
 
+import os as _os
+# A/B on one B200 (profiles/r01_dropout_bgrad_ab_v17.txt): the fused pass saves 48 launches per step but puts the column
+# sums on the main stream's critical path (14.86-14.90 ms vs 14.79-14.80 ms with the sums on the side stream) -> opt-in.
+FUSED_DROPOUT_BGRAD = _os.environ.get("B200ASR_FUSED_DROPOUT_BGRAD", "0") != "0"
+
+
+def _dropout_bgrad(ps, need, dy, p, seed, site, ctr):
+    """do = dropout(dy) (the mask the forward drew at `site`) and the bias gradient colsum(do) of the Linear whose
+    output was dropped, in one pass over dy (b200asr_dropout_colsum).  Returns (do, dbias or None if delivered)."""
+    if not need:
+        return ops.dropout(dy, p, seed, site, ctr), None
+    if not FUSED_DROPOUT_BGRAD:  # dropout on the main stream, column sums on the side stream
+        do = ops.dropout(dy, p, seed, site, ctr)
+        return do, _bgrad(ps, need, do)
+    ps = ps if isinstance(ps, tuple) else (ps,)
+    sink, fresh = grad_sink(ps)
+    if sink is None:
+        return ops.dropout_colsum(dy, p, seed, site, ctr)
+    if fresh:
+        do, _ = ops.dropout_colsum(dy, p, seed, site, ctr, out=sink)
+        return do, None
+    ops.join_side_stream()   # the sink's first write may still be in flight on a side stream
+    do, cs = ops.dropout_colsum(dy, p, seed, site, ctr)
+    ops.axpy_(sink, cs)
+    return do, None
+
+
 def _ln_bwd(dy, s, w, b, mean, rstd, need, in_bias=None, **kw):
     """LayerNorm backward.  Affine gradients go straight to their sinks when fresh.  `in_bias` = the bias parameter
     of the Linear / conv whose output fed this LayerNorm: its gradient is the column sum of dx, which the kernel
@@ -450,8 +477,7 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
         d = x.shape[1]
         wg = any(ctx.needs_input_grad[5:])  # parameter gradients wanted?
         ds2, dln2w, dln2b, _ = _ln_bwd(dy, s2, ln2_w, ln2_b, m2, r2, wg)
-        do2 = ops.dropout(ds2, ph, seed, site + 2, ctr)           # gradient of W2 f + b2 (ds2 itself is the residual path)
-        db2 = _bgrad(b2, wg, do2)
+        do2, db2 = _dropout_bgrad(b2, wg, ds2, ph, seed, site + 2, ctr)   # gradient of W2 f + b2 (ds2 itself is the residual path)
         dw2 = _wgrad(w2, wg, do2, g)                              # g = the dropped activations W2 consumed
         du = ops.linear_dgrad(do2, w2s, gelu_grad=u)              # (do2 W2) * gelu'
         du = ops.dropout(du, pa, seed, site + 1, ctr, out=du)     # ... * mask_a / (1 - p_a) (the factors commute)
@@ -459,8 +485,7 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
         dw1 = _wgrad(w1, wg, du, x1)
         dx1 = ops.linear_dgrad(du, w1s, residual=ds2)
         ds1, dln1w, dln1b, _ = _ln_bwd(dx1, s1, ln1_w, ln1_b, m1, r1, wg)
-        do = ops.dropout(ds1, ph, seed, site, ctr)
-        dbo = _bgrad(o_b, wg, do)
+        do, dbo = _dropout_bgrad(o_b, wg, ds1, ph, seed, site, ctr)
         dwo = _wgrad(o_w, wg, do, attn)
         dattn = ops.linear_dgrad(do, wo)
         dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale)
@@ -670,8 +695,7 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
         wg = any(ctx.needs_input_grad[5:])
         if not dy.is_contiguous():
             dy = dy.contiguous()
-        do2 = ops.dropout(dy, ph, seed, site + 2, ctr)
-        db2 = _bgrad(b2, wg, do2)
+        do2, db2 = _dropout_bgrad(b2, wg, dy, ph, seed, site + 2, ctr)
         dw2 = _wgrad(w2, wg, do2, g)
         du = ops.linear_dgrad(do2, w2s, gelu_grad=u)
         du = ops.dropout(du, pa, seed, site + 1, ctr, out=du)
@@ -679,8 +703,7 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
         dw1 = _wgrad(w1, wg, du, n2)
         dn2 = ops.linear_dgrad(du, w1s)
         ds1, dln2w, dln2b, _ = _ln_bwd(dn2, s1, ln2_w, ln2_b, m2, r2, wg, dres_add=dy)   # + residual path of y
-        do = ops.dropout(ds1, ph, seed, site, ctr)
-        dbo = _bgrad(o_b, wg, do)
+        do, dbo = _dropout_bgrad(o_b, wg, ds1, ph, seed, site, ctr)
         dwo = _wgrad(o_w, wg, do, attn)
         dattn = ops.linear_dgrad(do, wo)
         dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale)

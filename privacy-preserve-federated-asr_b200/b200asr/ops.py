@@ -209,6 +209,23 @@ def colsum(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     return out
 
 
+def dropout_colsum(x: torch.Tensor, p: float, seed: int, site: int, counter=None, out: Optional[torch.Tensor] = None):
+    """(y, colsum): y = dropout(x) (keys as ops.dropout) and the fp32 column sums of y, one pass over x [rows, cols]."""
+    x = _c(x)
+    cols = x.shape[-1]
+    rows = x.numel() // cols
+    y = torch.empty_like(x)
+    if out is None:
+        out = torch.empty(cols, dtype=torch.float32, device=x.device)
+    dev = counter if isinstance(counter, torch.Tensor) else None
+    host = 0 if dev is not None or counter is None else int(counter)
+    nws = lib.b200asr_colsum_workspace_bytes(cols)
+    ws = workspace(nws, x.device)
+    check(lib.b200asr_dropout_colsum(_p(x), _p(y), _p(out), _p(ws), nws, rows, cols, float(p), int(seed) & (2 ** 64 - 1),
+                                     int(site), host, _p(dev), dt(x), _st()), "dropout_colsum")
+    return y, out
+
+
 def mask_frames_(x: torch.Tensor, lengths: torch.Tensor) -> torch.Tensor:
     """x [B, T, C]: zero frames t >= lengths[b] in place."""
     B, T, Cc = x.shape

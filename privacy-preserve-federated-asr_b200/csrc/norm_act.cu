@@ -334,12 +334,36 @@ __global__ void colsum_partial_kernel(const T* __restrict__ x, float* __restrict
 
 // vectorised variant: a block = 32 column vectors (16 B each) x 8 row lanes; needs cols % N == 0, ld % N == 0 and a
 // 16-byte aligned base.  partial[chunk][cols].
-template <typename T>
+// DROP: x first goes through an inverted dropout (DropKeys, common.cuh; needs ld == cols so that the element index is
+// r * cols + c); the dropped values are written to y and it is their (rounded) column sums that are accumulated --
+// `do = dropout(ds); db = colsum(do)` of a block's backward in one pass over ds.
+template <typename T, bool DROP>
+__device__ __forceinline__ void colsum_load(const T* __restrict__ x, T* __restrict__ y, long long e0, float* f,
+                                            const DropKeys& dk, unsigned long long drop_offset) {
+    constexpr int N = Vec16<T>::N;
+    Vec16<T> a;
+    a.load(x + e0);
+    a.unpack(f);
+    if (DROP) {
+        uint32_t u[N];
+        dropout_uniforms<N>((unsigned long long)e0, dk.key, drop_offset, u);
+#pragma unroll
+        for (int j = 0; j < N; ++j) f[j] = (u[j] >= dk.thresh16) ? f[j] * dk.scale : 0.f;
+        a.pack(f);
+        a.store(y + e0);
+        a.unpack(f);  // sum what was stored
+    }
+}
+
+template <typename T, bool DROP>
 __global__ void __launch_bounds__(256) colsum_partial_vec_kernel(const T* __restrict__ x, float* __restrict__ partial,
-                                                                 int rows, int cols, int ld, int rows_per_chunk) {
+                                                                 int rows, int cols, int ld, int rows_per_chunk,
+                                                                 T* __restrict__ y, DropKeys dk) {
     constexpr int N = Vec16<T>::N;
     __shared__ float red[8][32][N + 1];
     pdl_enter();
+    unsigned long long drop_offset = 0;
+    if (DROP) drop_offset = dk.offset + (dk.dev_offset ? *dk.dev_offset : 0ull);
     const int cv = threadIdx.x & 31, rl = threadIdx.x >> 5;
     const int c = (blockIdx.x * 32 + cv) * N;
     const int r0 = blockIdx.y * rows_per_chunk;
@@ -350,20 +374,15 @@ __global__ void __launch_bounds__(256) colsum_partial_vec_kernel(const T* __rest
     if (c < cols) {
         int r = r0 + rl;
         for (; r + 8 < r1; r += 16) {
-            Vec16<T> a, b;
             float af[N], bf[N];
-            a.load(x + (long long)r * ld + c);
-            b.load(x + (long long)(r + 8) * ld + c);
-            a.unpack(af);
-            b.unpack(bf);
+            colsum_load<T, DROP>(x, y, (long long)r * ld + c, af, dk, drop_offset);
+            colsum_load<T, DROP>(x, y, (long long)(r + 8) * ld + c, bf, dk, drop_offset);
 #pragma unroll
             for (int j = 0; j < N; ++j) { acc[j] += af[j]; acc2[j] += bf[j]; }
         }
         for (; r < r1; r += 8) {
-            Vec16<T> a;
             float af[N];
-            a.load(x + (long long)r * ld + c);
-            a.unpack(af);
+            colsum_load<T, DROP>(x, y, (long long)r * ld + c, af, dk, drop_offset);
 #pragma unroll
             for (int j = 0; j < N; ++j) acc[j] += af[j];
         }
@@ -534,7 +553,8 @@ int b200asr_colsum(const void* x, float* out, void* workspace, size_t workspace_
         nchunks = ceil_div(rows, rpc);
         dim3 grid(gx, nchunks);
         B200_DISPATCH_DTYPE(dtype, {
-            launch_pdl(colsum_partial_vec_kernel<T>, grid, dim3(256), 0, as_stream(stream), (const T*)x, (float*)workspace, rows, cols, ld, rpc);
+            launch_pdl(colsum_partial_vec_kernel<T, false>, grid, dim3(256), 0, as_stream(stream), (const T*)x, (float*)workspace, rows, cols, ld, rpc,
+                       (T*)nullptr, DropKeys{});
         });
     } else {
         const int chunks = rows < COLSUM_CHUNKS ? rows : COLSUM_CHUNKS;
@@ -550,6 +570,35 @@ int b200asr_colsum(const void* x, float* out, void* workspace, size_t workspace_
     launch_pdl(reduce_partials_kernel, dim3(ceil_div(cols, 32)), dim3(1024), 0, as_stream(stream), (const float*)workspace, out,
                (float*)nullptr, (float*)nullptr, nchunks, cols, cols, cols);
     return check_launch("colsum_reduce");
+}
+
+int b200asr_dropout_colsum(const void* x, void* y, float* out, void* workspace, size_t workspace_bytes, int rows, int cols,
+                           float p, unsigned long long seed, unsigned long long site, unsigned long long offset,
+                           const unsigned long long* dev_offset, int dtype, void* stream) {
+    B200_REQUIRE(x && y && out && workspace, "dropout_colsum: null pointer");
+    B200_REQUIRE(rows > 0 && cols > 0 && cols % 8 == 0, "dropout_colsum: bad shape rows=%d cols=%d (cols %% 8 == 0)", rows, cols);
+    B200_REQUIRE((((uintptr_t)x | (uintptr_t)y) & 15) == 0, "dropout_colsum: buffers must be 16-byte aligned");
+    B200_REQUIRE(workspace_bytes >= b200asr_colsum_workspace_bytes(cols), "dropout_colsum: workspace too small");
+    B200_REQUIRE(p >= 0.f && p < 1.f, "dropout_colsum: p=%f must be in [0, 1)", (double)p);
+    const DropKeys dk = make_drop_keys(p, seed, site, offset, dev_offset);
+    const int nvec = dtype == B200ASR_BF16 ? 8 : 4;
+    const int gx = ceil_div(cols, 32 * nvec);
+    int chunks = (4 * num_sms()) / gx;
+    if (chunks > COLSUM_CHUNKS) chunks = COLSUM_CHUNKS;
+    if (chunks > ceil_div(rows, 8)) chunks = ceil_div(rows, 8);
+    if (chunks < 1) chunks = 1;
+    const int rpc = ceil_div(rows, chunks);
+    const int nchunks = ceil_div(rows, rpc);
+    dim3 grid(gx, nchunks);
+    B200_DISPATCH_DTYPE(dtype, {
+        launch_pdl(colsum_partial_vec_kernel<T, true>, grid, dim3(256), 0, as_stream(stream), (const T*)x, (float*)workspace, rows, cols,
+                   cols, rpc, (T*)y, dk);
+    });
+    int rc = check_launch("dropout_colsum_partial");
+    if (rc != B200ASR_OK) return rc;
+    launch_pdl(reduce_partials_kernel, dim3(ceil_div(cols, 32)), dim3(1024), 0, as_stream(stream), (const float*)workspace, out,
+               (float*)nullptr, (float*)nullptr, nchunks, cols, cols, cols);
+    return check_launch("dropout_colsum_reduce");
 }
 
 }  // extern "C"

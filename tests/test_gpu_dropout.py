@@ -65,6 +65,30 @@ def test_dropout_kernel_mask_properties(p):
     assert abs(corr) < 0.01
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("rows,cols", [(3992, 1024), (37, 128), (8, 2048)])
+def test_fused_dropout_entry_points_equal_the_composition(rows, cols, dtype):
+    """b200asr_layernorm_dropout_fwd == dropout(+residual) then layernorm; b200asr_dropout_colsum == dropout then colsum
+    (bit-exact: same mask keys, same rounding points)."""
+    g = torch.Generator().manual_seed(rows + cols)
+    x = torch.randn(rows, cols, generator=g).to(DEV).to(dtype)
+    r = torch.randn(rows, cols, generator=g).to(DEV).to(dtype)
+    w = (1 + 0.1 * torch.randn(cols, generator=g)).to(DEV)
+    b = (0.1 * torch.randn(cols, generator=g)).to(DEV)
+    ctr = torch.tensor([5], dtype=torch.int64, device=DEV)
+    keys = (0.2, 99, 21, ctr)
+    s_ref = ops.dropout(x, *keys, residual=r)
+    y_ref, _, m_ref, r_ref = ops.layernorm_fwd(s_ref, w, b, 1e-5)
+    y, s, m, rs = ops.layernorm_fwd(x, w, b, 1e-5, res=r, want_sum=True, drop=keys)
+    assert torch.equal(s, s_ref) and torch.equal(y, y_ref) and torch.equal(m, m_ref) and torch.equal(rs, r_ref)
+    do_ref = ops.dropout(x, *keys)
+    cs_ref = ops.colsum(do_ref)
+    do, cs = ops.dropout_colsum(x, *keys)
+    assert torch.equal(do, do_ref) and torch.equal(cs, cs_ref)
+    ref64 = do_ref.double().sum(0)
+    assert float((cs.double() - ref64).abs().max()) <= 1e-3 * max(1.0, float(ref64.abs().max()))
+
+
 def _masks_from_library(backbone, cfg, B, T, ps):
     """Read the masks of the last training forward back: dropout(ones) with that forward's keys."""
     seed, ctr = backbone.dropout_seed, backbone._drop_ctr
