@@ -672,8 +672,8 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
         qkv, _ = ops.linear_fwd(n1, wqkv, bqkv)
         attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale)
         o, _ = ops.linear_fwd(attn, wo, o_b)
-        s1 = ops.dropout(o, ph, seed, site, ctr, residual=x, out=o)
-        n2, _, m2, r2 = ops.layernorm_fwd(s1, ln2_w, ln2_b, eps)
+        # s1 = x + drop_h(o) and LN2 in one pass (b200asr_layernorm_dropout_fwd)
+        n2, s1, m2, r2 = ops.layernorm_fwd(o, ln2_w, ln2_b, eps, res=x, want_sum=True, drop=(ph, seed, site, ctr))
         g, u = ops.linear_fwd(n2, w1s, b1, act=ACT_GELU_SAVE_GRAD)
         g = ops.dropout(g, pa, seed, site + 1, ctr, out=g)
         o2, _ = ops.linear_fwd(g, w2s, b2)
