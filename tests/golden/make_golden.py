@@ -172,6 +172,62 @@ def case_dropout(tag, cfg, batch, samples, seed, ps, mask_seed):
 
 
 DROPOUT_PS = dict(hidden_dropout=0.1, activation_dropout=0.15, feat_proj_dropout=0.05, final_dropout=0.2)
+ATTN_DROPOUT_PS = dict(DROPOUT_PS, attention_dropout=0.25)
+
+
+def case_attn_dropout(tag, cfg, batch, samples, seed, ps, mask_seed):
+    """As case_dropout, with attention_dropout > 0 as well.  HF's eager attention calls `nn.functional.dropout` on the
+    softmax probabilities (HF:189-197) and nn.Dropout.forward calls it too, so `torch.nn.functional.dropout` itself is
+    replaced by the call-order rule: the fixture pins the position of EVERY dropout of the training forward, the
+    attention-probability one included (first call of each block)."""
+    from transformers import Data2VecAudioForCTC
+    import torch.nn.functional as TF
+    sd = R.init_state_dict(cfg, seed=seed, dacs=False)
+    hc = hf_config(cfg)
+    for k, v in ps.items():
+        setattr(hc, k, v)
+    m = Data2VecAudioForCTC(hc)
+    m.load_state_dict(sd, strict=True)
+    m.freeze_feature_encoder()
+    m.train()
+    b = R.synth_batch(cfg, batch, samples, seed=1234 + seed, ragged=True, max_label=12)
+    calls = {"k": 0, "ps": [], "shapes": []}
+    orig = TF.dropout
+
+    def patched(x, p=0.5, training=True, inplace=False):
+        if not training:
+            return x
+        k = calls["k"]
+        calls["k"] += 1
+        calls["ps"].append(p)
+        calls["shapes"].append(tuple(x.shape))
+        return R.call_order_mask(x, p, mask_seed, k)
+
+    TF.dropout = patched
+    try:
+        out = m(input_values=b["input_values"], attention_mask=b["attention_mask"], labels=b["labels"],
+                output_hidden_states=True)
+    finally:
+        TF.dropout = orig
+    out.loss.backward()
+    assert calls["k"] == 3 + 4 * cfg.num_hidden_layers, calls
+    g = {n: p.grad.detach().clone() for n, p in m.named_parameters() if p.grad is not None}
+    keep = ["lm_head.weight", "data2vec_audio.feature_projection.projection.weight",
+            "data2vec_audio.encoder.layers.0.attention.out_proj.bias",
+            "data2vec_audio.encoder.layers.0.attention.v_proj.weight",
+            "data2vec_audio.encoder.layers.0.attention.q_proj.weight",
+            "data2vec_audio.encoder.layers.1.attention.k_proj.weight",
+            "data2vec_audio.encoder.layers.1.feed_forward.output_dense.bias"]
+    np.savez_compressed(
+        os.path.join(OUT, f"{tag}.npz"),
+        seed=seed, batch=batch, samples=samples, mask_seed=mask_seed, n_dropout_calls=calls["k"],
+        dropout_call_ps=np.array(calls["ps"]), p_names=np.array(list(ps.keys())), p_values=np.array(list(ps.values())),
+        loss=out.loss.detach().numpy(), logits=out.logits.detach().numpy(),
+        hidden_last=out.hidden_states[-1].detach().numpy(),
+        grad_names=np.array(keep), **{"grad:" + k: g[k].numpy() for k in keep},
+        gnorm_names=np.array(list(g.keys())), gnorm_values=np.array([float(v.norm()) for v in g.values()]),
+    )
+    print(tag, "loss", float(out.loss.detach()), "dropout calls", calls["k"], calls["ps"], calls["shapes"][:6])
 
 
 def case_variant_ctc(tag, cfg, batch, samples, seed, use_mask):
@@ -320,6 +376,8 @@ def main():
     case_layerdrop("plain_ctc_layerdrop", R.ArchConfig.tiny(num_hidden_layers=4), batch=2, samples=6000, seed=3,
                    layerdrop=0.5, coin_seed=5)
     case_dropout("plain_ctc_dropout", R.ArchConfig.tiny(), batch=2, samples=6000, seed=5, ps=DROPOUT_PS, mask_seed=900)
+    case_attn_dropout("plain_ctc_attn_dropout", R.ArchConfig.tiny(), batch=2, samples=6000, seed=6, ps=ATTN_DROPOUT_PS,
+                      mask_seed=901)
     for tag, (_, _, batch, samples, seed, use_mask) in VARIANTS.items():
         case_variant_ctc(tag, variant_cfg(tag), batch, samples, seed, use_mask)
 
@@ -328,6 +386,9 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "variants":  # only (re)generate the config-5 variant fixtures
         for tag, (_, _, batch, samples, seed, use_mask) in VARIANTS.items():
             case_variant_ctc(tag, variant_cfg(tag), batch, samples, seed, use_mask)
+    elif len(sys.argv) > 1 and sys.argv[1] == "attn_dropout":
+        case_attn_dropout("plain_ctc_attn_dropout", R.ArchConfig.tiny(), batch=2, samples=6000, seed=6, ps=ATTN_DROPOUT_PS,
+                          mask_seed=901)
     elif len(sys.argv) > 1 and sys.argv[1] == "dropout":
         case_dropout("plain_ctc_dropout", R.ArchConfig.tiny(), batch=2, samples=6000, seed=5, ps=DROPOUT_PS, mask_seed=900)
     elif len(sys.argv) > 1 and sys.argv[1] == "layerdrop":

@@ -102,6 +102,35 @@ def test_dropout_placement_matches_hf(golden_dir):
         assert abs(float(sd[str(n)].grad.norm()) - v) <= 2e-4 * max(v, 1e-3), n
 
 
+def test_attention_dropout_placement_matches_hf(golden_dir):
+    """attention_dropout sits on the softmax probabilities, before the P V product (HF:189-197): HF ran with
+    torch.nn.functional.dropout replaced by the call-order rule (every dropout of the forward, attention included)."""
+    g = _load(golden_dir, "plain_ctc_attn_dropout")
+    cfg = R.ArchConfig.tiny()
+    seed, batch, samples = int(g["seed"]), int(g["batch"]), int(g["samples"])
+    ps = {str(k): float(v) for k, v in zip(g["p_names"], g["p_values"])}
+    assert ps["attention_dropout"] > 0
+    sd = R.init_state_dict(cfg, seed=seed, dacs=False)
+    sd = {k: v.clone().requires_grad_(not k.startswith("data2vec_audio.feature_extractor")) for k, v in sd.items()}
+    b = R.synth_batch(cfg, batch, samples, seed=1234 + seed, ragged=True, max_label=12)
+    collect = []
+    loss, logits = R.ctc_forward(sd, cfg, b["input_values"], b["attention_mask"], b["labels"], collect,
+                                 drop=R.seeded_call_order_dropout(ps, int(g["mask_seed"])))
+    loss.backward()
+    assert int(g["n_dropout_calls"]) == 3 + 4 * cfg.num_hidden_layers
+    np.testing.assert_allclose(collect[-1].detach().numpy(), g["hidden_last"], rtol=0, atol=5e-5)
+    np.testing.assert_allclose(logits.detach().numpy(), g["logits"], rtol=0, atol=1e-4)
+    np.testing.assert_allclose(float(loss), float(g["loss"]), rtol=1e-5)
+    for n in g["grad_names"]:
+        ref = g["grad:" + str(n)]
+        scale = max(np.abs(ref).max(), 1e-6)
+        assert np.abs(sd[str(n)].grad.numpy() - ref).max() / scale < 2e-4, n
+    for n, v in zip(g["gnorm_names"], g["gnorm_values"]):
+        if str(n).endswith("k_proj.bias"):
+            continue
+        assert abs(float(sd[str(n)].grad.norm()) - v) <= 2e-4 * max(v, 1e-3), n
+
+
 # config-5 variants (finetune_ASRs.py:154-172).  The table mirrors tests/golden/make_golden.py::VARIANTS.
 VARIANTS = {
     "w2v2_group_postln": ("tiny_wav2vec2", {}),
