@@ -31,10 +31,15 @@ class _GRL(torch.autograd.Function):
         return -ctx.lam * g, None
 
 
-def gumbel_hard_mask(score2: torch.Tensor, gumbels: torch.Tensor, tau: float) -> torch.Tensor:
+def gumbel_hard_mask(score2: torch.Tensor, gumbels: torch.Tensor, tau: float, hard0: Optional[torch.Tensor] = None) -> torch.Tensor:
     """federated/src/models.py:75-129 with hard=True, then `[..., 0]`.
-    score2, gumbels: [..., 2]."""
+    score2, gumbels: [..., 2].  hard0 (bool [...]): take these hard decisions instead of the argmax (parity "given the
+    masks": the decisions sit behind a comparison that another implementation's rounding may flip at near-ties); the
+    straight-through gradient still flows through y_soft."""
     y_soft = ((score2 + gumbels) / tau).softmax(-1)
+    if hard0 is not None:
+        h0 = hard0.to(y_soft.dtype)
+        return h0 - y_soft[..., 0].detach() + y_soft[..., 0]
     index = y_soft.max(-1, keepdim=True)[1]
     y_hard = torch.zeros_like(score2).scatter_(-1, index, 1.0)
     return (y_hard - y_soft.detach() + y_soft)[..., 0]
@@ -42,12 +47,12 @@ def gumbel_hard_mask(score2: torch.Tensor, gumbels: torch.Tensor, tau: float) ->
 
 def recall_loss(logits2: torch.Tensor, target: torch.Tensor, weight, kind: str = "recall") -> torch.Tensor:
     """federated/src/models.py:187-260 on [N, C] logits (last_size == 1)."""
-    w = torch.tensor(weight, dtype=torch.float32)
+    w = torch.tensor(weight, dtype=torch.float32, device=logits2.device)
     w = w / w.sum()
     x = logits2.float()
     N, C = x.shape
     pt = F.log_softmax(x, dim=1).exp()
-    onehot = torch.zeros(N, C).scatter_(1, target.view(N, 1).long(), 1.0)
+    onehot = torch.zeros(N, C, device=x.device).scatter_(1, target.view(N, 1).long(), 1.0)
     tp = pt * onehot
     recall = (tp + 1e-5) / (onehot + 1e-5)
     precision = (tp + 1e-5) / (pt + 1e-5)
@@ -76,7 +81,8 @@ def cosface_loss(x: torch.Tensor, labels: torch.Tensor, fc_weight: torch.Tensor,
 
 
 def dacs_forward(sd, cfg: R.ArchConfig, args, input_values, attention_mask, labels, dementia_labels,
-                 gumbels_lm: torch.Tensor, gumbels_ad: torch.Tensor, hidden: Optional[torch.Tensor] = None):
+                 gumbels_lm: torch.Tensor, gumbels_ad: torch.Tensor, hidden: Optional[torch.Tensor] = None,
+                 hard_lm: Optional[torch.Tensor] = None, hard_ad: Optional[torch.Tensor] = None):
     """federated/src/models.py:375-631 with dropout = 0.  Returns a dict with every loss term, the
     stage-selected `loss` and the returned (lm-masked) `logits`.  `hidden` may be supplied to skip
     the encoder (used when only the heads are under test)."""
@@ -93,8 +99,8 @@ def dacs_forward(sd, cfg: R.ArchConfig, args, input_values, attention_mask, labe
         r = args.TOGGLE_RATIO
         lm_score = torch.stack(((lm_score[..., 1] - lm_score[..., 0]) * r + lm_score[..., 0], lm_score[..., 1]), -1)
         ad_score = torch.stack(((ad_score[..., 1] - ad_score[..., 0]) * r + ad_score[..., 0], ad_score[..., 1]), -1)
-    lm_mask = gumbel_hard_mask(lm_score, gumbels_lm, args.GS_TAU)
-    ad_mask = gumbel_hard_mask(ad_score, gumbels_ad, args.GS_TAU)
+    lm_mask = gumbel_hard_mask(lm_score, gumbels_lm, args.GS_TAU, hard_lm)
+    ad_mask = gumbel_hard_mask(ad_score, gumbels_ad, args.GS_TAU, hard_ad)
     lm_masked = lm_mask * h
     ad_masked = ad_mask * h
     lin = lambda x, n: F.linear(x, sd[n + ".weight"], sd[n + ".bias"])
@@ -127,7 +133,7 @@ def dacs_forward(sd, cfg: R.ArchConfig, args, input_values, attention_mask, labe
     out["ad_rev"] = lf(ad_mean_r)
     n = lm_masked.shape[0] * lm_masked.shape[1]
     scores = torch.cat((lm_masked.reshape(n, d), ad_masked.reshape(n, d)), 0)
-    am_labels = torch.cat((torch.zeros(n, dtype=torch.long), torch.ones(n, dtype=torch.long)))
+    am_labels = torch.cat((torch.zeros(n, dtype=torch.long, device=scores.device), torch.ones(n, dtype=torch.long, device=scores.device)))
     out["cosface"] = cosface_loss(scores, am_labels, sd["criterion_similar.fc.weight"])
     if args.STAGE == 0:
         out["loss"] = out["ctc_unmask"]
