@@ -177,6 +177,33 @@ size_t b200asr_mha_bwd_workspace_bytes(int B, int T, int H, int dh, int dtype);
 int b200asr_mha_bwd(const void* qkv, const void* out, const void* dout, const float* lse, const int* klen,
                     void* dqkv, void* workspace, size_t workspace_bytes, int B, int T, int H, int dh, float scale,
                     int dtype, void* stream);
+/* Where dQ of the fused backward is formed.  1 (default): inside the backward kernel -- dQ_i += dS_i K_j is a fifth MMA of
+ * the query-block loop, the partial tiles are added into an fp32 accumulator with bulk reduce-add and converted once; no
+ * dS^T round trip through HBM.  The key blocks of a head add in arrival order: reproducible to fp32 rounding, not bit for bit.
+ * 0: the kernel stores dS^T and dQ = dS K is a batched GEMM (fixed summation order, bit-reproducible).  Returns the old setting. */
+int b200asr_mha_set_dq_fused(int on);
+
+/* Attention-probability dropout: `nn.functional.dropout(attn_weights, p=config.attention_dropout)` between the softmax and
+ * the P V product (HF:189-197; Data2VecAudioConfig.attention_dropout = 0.1 in every reference training run, also inside the
+ * frozen encoder of DACS stages 1-2, federated/src/update.py:433,650).
+ * The keep decisions are data independent, so they are drawn OFF the attention kernels' critical path, for all blocks of a
+ * step in one launch: keep[site][((b H + h) KW + key / 32) TQ + query] bit (key & 31), 1 = keep; KW = ceil(T / 32),
+ * TQ = T rounded up to 128; b200asr_attn_keep_words(B, T, H) uint32 words per site.  Philox4x32-10 keyed by
+ * (seed, site0 + site_stride * s) over (word, step = offset + *dev_offset); P(drop) = p rounded to 1 / 65536.
+ * The fused kernels read one word per 32 probabilities; the forward keeps the softmax normalisation and the saved
+ * log-sum-exp of the UNDROPPED probabilities, drops P before P V and scales the output by 1 / (1 - p); the backward
+ * applies the same bits to P (for dV) and to dP (for dS).  The composed path applies them to the materialised planes. */
+size_t b200asr_attn_keep_words(int B, int T, int H);
+int b200asr_attn_dropout_mask(unsigned* keep, int n_sites, int B, int T, int H, float p, unsigned long long seed,
+                              unsigned long long site0, unsigned long long site_stride, unsigned long long offset,
+                              const unsigned long long* dev_offset, void* stream);
+/* b200asr_mha_fwd / b200asr_mha_bwd with the keep bits of one site (keep == NULL: no dropout). */
+int b200asr_mha_fwd_dropout(const void* qkv, void* out, float* lse, const int* klen, const unsigned* keep, float p_drop,
+                            void* workspace, size_t workspace_bytes, int B, int T, int H, int dh, float scale, int dtype,
+                            void* stream);
+int b200asr_mha_bwd_dropout(const void* qkv, const void* out, const void* dout, const float* lse, const int* klen,
+                            const unsigned* keep, float p_drop, void* dqkv, void* workspace, size_t workspace_bytes, int B,
+                            int T, int H, int dh, float scale, int dtype, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Grouped positional convolution (HF:89-128): y[b,t,g*Cg+o] = bias + sum_{j,i} W[g*Cg+o, i, j] *
@@ -335,12 +362,19 @@ int b200asr_fedavg_prescale(float* buf, float w, long long n, void* stream);
  * peer memory) and writes the result back into every peer's slice.  Caller brackets with cross-rank barriers. */
 int b200asr_fedavg_peer_reduce(float* const* peer_bufs, const float* weights, int world, int rank, long long n,
                                void* stream);
+/* Same, but the kernel returns without touching any buffer when *abort_flag (device int, the barrier's timeout flag)
+ * is non-zero: a straggler that missed the barrier must not receive -- or contribute to -- a torn average. */
+int b200asr_fedavg_peer_reduce_guarded(float* const* peer_bufs, const float* weights, int world, int rank, long long n,
+                                       const int* abort_flag, void* stream);
 
 /* Cross-rank barrier over peer memory for the fused kernel above: every rank passes the HOST array of the `world`
  * ranks' flag buffers (>= world unsigned each, zero-initialised, peer-mapped) and a barrier number `epoch` that grows
  * by one per call on every rank.  Stream-ordered; bounded spin (sets *timeout_flag, a device int, instead of hanging). */
 int b200asr_fedavg_peer_barrier(unsigned* const* peer_flags, int world, int rank, unsigned epoch, int* timeout_flag,
                                 void* stream);
+/* Spin limit of the barrier in seconds of SM clock (default ~2 s).  A rank whose flag is already set publishes a poison
+ * value at its next barrier, which sets the flag on every peer that meets it (the failure is visible on all ranks). */
+int b200asr_fedavg_peer_barrier_set_timeout(double seconds);
 /* Peer-visible device allocations (zero-filled cudaMalloc, exportable through CUDA IPC) and the IPC plumbing that
  * replaces the reference's pickle / deepcopy hops of the weights between client processes and the server
  * (federated/src/federated_main.py:124-141, federated/src/update.py:246-283).  Explicit create / destroy pairs. */
@@ -388,8 +422,20 @@ int b200asr_adamw_step(float* p, const float* grad, float* m, float* v, void* sh
 int b200asr_adamw_step_dev(float* p, const float* grad, float* m, float* v, void* shadow_bf16, long long n,
                            const float* hyper, float beta1, float beta2, float eps, float weight_decay,
                            const float* gnorm_sq, float max_norm, void* stream);
-/* out[0] += sum(x^2)  (out must be zeroed by the caller for a fresh norm) */
+/* Same update with PER-PARAMETER scalars (transformers.AdamW keeps state["step"] per parameter and skips parameters
+ * whose grad is None -- a block dropped by LayerDrop (HF:392-404), an unused head): the flat buffer is described by
+ * `chunks` (device int32 [nchunks, 4] = {first float4 index, float4 count, parameter index, 0}; a chunk never straddles
+ * a parameter) and `hyper` (device fp32 [n_params, 2] = {lr, lr * sqrt(1-b2^t_p) / (1-b1^t_p)}); a NEGATIVE second entry
+ * marks the parameter idle in this step: p / m / v / shadow are left untouched.  Graph-capturable. */
+int b200asr_adamw_step_chunks(float* p, const float* grad, float* m, float* v, void* shadow_bf16, const int* chunks,
+                              int nchunks, const float* hyper, float beta1, float beta2, float eps, float weight_decay,
+                              const float* gnorm_sq, float max_norm, void* stream);
+/* out[0] += sum(x^2)  (out must be zeroed by the caller for a fresh norm).  Deterministic (fixed-order combine).
+ * b200asr_sumsq parks its per-block partials in module-global device memory: one launch in flight per device.
+ * b200asr_sumsq_ws takes a caller-owned workspace (zero-initialised once) and may run on any number of streams. */
 int b200asr_sumsq(const float* x, long long n, float* out, void* stream);
+size_t b200asr_sumsq_workspace_bytes(void);
+int b200asr_sumsq_ws(const float* x, long long n, float* out, void* workspace, size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

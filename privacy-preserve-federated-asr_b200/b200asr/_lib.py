@@ -62,6 +62,11 @@ SIGNATURES = {
     "b200asr_mha_fwd_workspace_bytes": (sz, [i32, i32, i32, i32, i32]),
     "b200asr_mha_fwd": (i32, [vp, vp, vp, vp, vp, sz, i32, i32, i32, i32, f32, i32, vp]),
     "b200asr_mha_set_fused": (i32, [i32]),
+    "b200asr_mha_set_dq_fused": (i32, [i32]),
+    "b200asr_attn_keep_words": (sz, [i32, i32, i32]),
+    "b200asr_attn_dropout_mask": (i32, [vp, i32, i32, i32, i32, f32, u64, u64, u64, u64, vp, vp]),
+    "b200asr_mha_fwd_dropout": (i32, [vp, vp, vp, vp, vp, f32, vp, sz, i32, i32, i32, i32, f32, i32, vp]),
+    "b200asr_mha_bwd_dropout": (i32, [vp, vp, vp, vp, vp, vp, f32, vp, vp, sz, i32, i32, i32, i32, f32, i32, vp]),
     "b200asr_mha_bwd_workspace_bytes": (sz, [i32, i32, i32, i32, i32]),
     "b200asr_mha_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, sz, i32, i32, i32, i32, f32, i32, vp]),
     "b200asr_posconv_pack_weight": (i32, [vp, vp, vp, i32, i32, i32, i32, vp]),
@@ -91,7 +96,9 @@ SIGNATURES = {
     "b200asr_fedavg_scale_accum": (i32, [C.POINTER(vp), C.POINTER(f32), vp, i32, i64, vp]),
     "b200asr_fedavg_prescale": (i32, [vp, f32, i64, vp]),
     "b200asr_fedavg_peer_reduce": (i32, [C.POINTER(vp), C.POINTER(f32), i32, i32, i64, vp]),
+    "b200asr_fedavg_peer_reduce_guarded": (i32, [C.POINTER(vp), C.POINTER(f32), i32, i32, i64, vp, vp]),
     "b200asr_fedavg_peer_barrier": (i32, [C.POINTER(vp), i32, i32, C.c_uint, vp, vp]),
+    "b200asr_fedavg_peer_barrier_set_timeout": (i32, [C.c_double]),
     "b200asr_peer_alloc": (i32, [C.POINTER(vp), sz]),
     "b200asr_peer_free": (i32, [vp]),
     "b200asr_ipc_export": (i32, [vp, C.c_char_p]),
@@ -103,7 +110,10 @@ SIGNATURES = {
     "b200asr_edit_distance": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, vp]),
     "b200asr_adamw_step": (i32, [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i32, vp, f32, vp]),
     "b200asr_adamw_step_dev": (i32, [vp, vp, vp, vp, vp, i64, vp, f32, f32, f32, f32, vp, f32, vp]),
+    "b200asr_adamw_step_chunks": (i32, [vp, vp, vp, vp, vp, vp, i32, vp, f32, f32, f32, f32, vp, f32, vp]),
     "b200asr_sumsq": (i32, [vp, i64, vp, vp]),
+    "b200asr_sumsq_workspace_bytes": (sz, []),
+    "b200asr_sumsq_ws": (i32, [vp, i64, vp, vp, sz, vp]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

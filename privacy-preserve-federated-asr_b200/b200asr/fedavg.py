@@ -102,6 +102,22 @@ class FlatParams:
             for p in self.params:
                 p._b200_pver = p._version
 
+    def sync_params(self) -> bool:
+        """Parameters were written through torch (`load_state_dict`, `p.copy_`, `p.data.mul_` ... bump `p._version`)
+        since the shadow was last refreshed -- the per-round "load the global weights" step of a federated client
+        (federated/src/update.py:228).  Refreshes the bf16 shadow and bumps the epoch so derived layouts are rebuilt.
+        Cheap when nothing changed (one integer compare per parameter); called by FusedAdamW.zero_grad and before every
+        CUDA-graph replay, whose captured kernels read the shadow through fixed pointers."""
+        if all(p._version == p._b200_pver for p in self.params):
+            return False
+        self.epoch += 1
+        if self.shadow is not None:
+            self.refresh_shadow()
+        else:
+            for p in self.params:
+                p._b200_pver = p._version
+        return True
+
     def mark_updated(self, shadow_written: bool = False):
         """A kernel wrote the flat buffer behind autograd's back: bump the epoch so cached weight shadows and derived
         layouts of THESE parameters are rebuilt (frozen parameters elsewhere keep theirs)."""
@@ -236,8 +252,8 @@ class PeerFedAvg:
     def __call__(self, weights: Optional[Sequence[float]] = None):
         """weights: per-rank FedAvg weights (None = the reference's uniform 1/N, sequential sum then divide)."""
         self._barrier()   # every client's local update is complete and visible
-        for fp, ptrs in zip(self.flats, self.flat_ptrs):
-            ops.fedavg_peer_reduce(ptrs, weights, self.rank, fp.numel)
+        for fp, ptrs in zip(self.flats, self.flat_ptrs):   # (a no-op on every rank that saw the barrier time out)
+            ops.fedavg_peer_reduce(ptrs, weights, self.rank, fp.numel, abort_flag=self.timeout)
         self._barrier()   # every slice has been written back everywhere
         for fp in self.flats:
             fp.mark_updated()

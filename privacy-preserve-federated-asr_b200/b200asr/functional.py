@@ -418,6 +418,26 @@ class EncoderLayerFn(torch.autograd.Function):
                 dln2w, dln2b)
 
 
+class SegmentMarkFn(torch.autograd.Function):
+    """Identity placed between encoder blocks while graph.GraphedTrainStep captures an update with LayerDrop: its
+    forward and its backward tell the recorder that a block boundary has been reached (the recorder closes the running
+    CUDA graph and opens the next one) and hand it the tensor / gradient that crosses the boundary, which a replay copies
+    across a skipped block."""
+
+    @staticmethod
+    def forward(ctx, x, idx, recorder):
+        ctx.idx, ctx.recorder = idx, recorder
+        recorder.fwd_mark(idx, x)
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        if not g.is_contiguous():
+            g = g.contiguous()
+        ctx.recorder.bwd_mark(ctx.idx, g)
+        return g, None, None
+
+
 class DropoutFn(torch.autograd.Function):
     """nn.Dropout at a stand-alone site (after the encoder's first LayerNorm HF:380-381, feat_proj_dropout HF:171,
     final_dropout federated/src/models.py:403): y = keep(x) / (1 - p); backward re-draws the same mask."""

@@ -1,16 +1,69 @@
-"""Whole client-local update as ONE CUDA graph (forward -> CTC -> backward -> clip -> fused AdamW).
+"""Whole client-local update as CUDA graphs (forward -> CTC -> backward -> clip -> fused AdamW).
 
 The update of a fixed-shape batch is a fixed sequence of ~700 kernel launches on two streams; issuing them from
 Python costs more host time than the B200 needs to execute them.  GraphedTrainStep captures the sequence once
-(torch.cuda.graph: stream capture of our C-ABI launches, including the side-stream fork/join of the weight-gradient
-kernels and the cluster launches of the CTA-pair GEMM) and replays it per step.  Per-step host values (learning
-rate, Adam bias correction) are read by the captured kernels from a small device tensor refreshed before each replay.
+(stream capture of our C-ABI launches, including the side-stream fork/join of the weight-gradient kernels and the
+cluster launches of the CTA-pair GEMM) and replays it per step.  Per-step host values (learning rate, per-parameter
+Adam bias correction, which parameters are idle) are read by the captured kernels from a small device table
+refreshed before each replay (optim.FusedAdamW.prepare_hyper).
+
+LayerDrop (HF:392-404, `config.layerdrop`, 0.1 in every reference training run) changes the launch sequence from step
+to step: every block is skipped with probability p by a host coin.  With layerdrop > 0 the update is therefore captured
+as 2 L + 3 graphs that share one memory pool -- prologue, one per block forward, head + loss + head backward, one per
+block backward, epilogue + optimizer -- cut at identity autograd nodes placed between the blocks (functional.SegmentMarkFn).
+A replay draws the coins on the host exactly as the eager path does, launches the graphs of the surviving blocks and
+replaces a skipped block by what it is: a copy of its input to its output (forward), of its output gradient to its input
+gradient (backward), zeroed parameter gradients and idle rows in the AdamW table (transformers.AdamW skips parameters
+without a gradient and does not advance their step count).
 """
 from __future__ import annotations
 
-from typing import Dict, Optional
+from typing import Dict, List, Optional
 
 import torch
+
+from . import ops
+
+
+def _layerdrop_p(model) -> float:
+    return float(getattr(getattr(model, "config", None), "layerdrop", 0.0) or 0.0) if model.training else 0.0
+
+
+class _SegmentRecorder:
+    """Cuts one captured update into graphs at the block boundaries.  `boundary()` is called from the forward pass (main
+    thread) and from the backward pass (autograd's device thread) with the capture stream current: it joins the side
+    streams, ends the running capture and begins the next one in the same memory pool (relaxed capture mode: the captures
+    begin and end on different threads)."""
+
+    def __init__(self, pool, n_layers: int):
+        self.pool = pool
+        self.L = n_layers
+        self.graphs: List[torch.cuda.CUDAGraph] = []
+        self.fwd_x: Dict[int, torch.Tensor] = {}   # tensor at mark l (block l's input = block l-1's output)
+        self.bwd_g: Dict[int, torch.Tensor] = {}   # gradient seen at mark l (d loss / d block l's input)
+        self.cur: Optional[torch.cuda.CUDAGraph] = None
+
+    def begin(self):
+        self.cur = torch.cuda.CUDAGraph()
+        self.cur.capture_begin(pool=self.pool, capture_error_mode="relaxed")
+
+    def end(self):
+        ops.join_side_stream()
+        self.cur.capture_end()
+        self.graphs.append(self.cur)
+        self.cur = None
+
+    def boundary(self):
+        self.end()
+        self.begin()
+
+    def fwd_mark(self, idx: int, x: torch.Tensor):
+        self.fwd_x[idx] = x
+        self.boundary()
+
+    def bwd_mark(self, idx: int, g: torch.Tensor):
+        self.bwd_g[idx] = g
+        self.boundary()
 
 
 class GraphedTrainStep:
@@ -18,22 +71,24 @@ class GraphedTrainStep:
 
     `example_batch`: dict of DEVICE tensors with the shapes every later batch will have (`input_values` [B, L],
     optional `attention_mask` [B, L], `labels` [B, <= max_label_len] padded with -100, optional `dementia_labels`).
-    Construction runs `warmup` eager updates and one capture; model, optimizer state and step counter are restored
+    Construction runs `warmup` eager updates and one capture; model, optimizer state and step counters are restored
     afterwards, so building the graph has no training side effect.  The returned loss is a device tensor that the
-    next call overwrites."""
+    next call overwrites.  `last_skipped_layers` holds the blocks LayerDrop skipped in the latest call."""
 
     def __init__(self, model, opt, example_batch: Dict[str, torch.Tensor], max_label_len: Optional[int] = None,
                  warmup: int = 3):
         self.model, self.opt = model, opt
-        if model.training and float(getattr(getattr(model, "config", None), "layerdrop", 0.0) or 0.0) > 0.0:
-            raise NotImplementedError("GraphedTrainStep: LayerDrop changes the launch sequence from step to step "
-                                      "(HF:392-404); set config.layerdrop = 0 or run the update eagerly")
         self.max_label_len = int(max_label_len or example_batch["labels"].shape[1])
         if hasattr(model, "validate_labels"):
             model.validate_labels = False  # the reference's host-side range check would synchronise (models.py:483)
+        self.backbone = getattr(model, "backbone", None)
+        self.layerdrop = _layerdrop_p(model)
+        self.segmented = self.layerdrop > 0.0
+        if self.segmented and self.backbone is None:
+            raise ValueError("GraphedTrainStep: LayerDrop needs a model with a `backbone` (Data2VecAudioModel)")
         self.static = {k: self._fit(k, v).clone() for k, v in example_batch.items()}
         saved = [t.clone() for t in opt.state_tensors()]
-        step_count = opt.step_count
+        host = opt.host_state()
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
@@ -43,14 +98,20 @@ class GraphedTrainStep:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         from . import _lib
-        self.graph = torch.cuda.CUDAGraph()
         n0 = _lib.launch_count()
-        with torch.cuda.graph(self.graph):
-            self.loss = self._body()
-        self.launches_per_replay = _lib.launch_count() - n0  # library kernels captured = launched by every replay
+        self.last_skipped_layers = ()
+        if self.segmented:
+            self._capture_segmented()
+        else:
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                self.loss = self._body()
+        self.launches_per_replay = _lib.launch_count() - n0  # library kernels captured = launched by a replay of everything
         for t, s in zip(opt.state_tensors(), saved):
             t.copy_(s)
-        opt.step_count = step_count
+        opt.load_host_state(host)
+        for g in opt.groups:
+            g["fp"].sync_params()
         torch.cuda.synchronize()
 
     def _fit(self, key, v):
@@ -67,6 +128,73 @@ class GraphedTrainStep:
         self.opt.step_captured()
         return out.loss.detach()
 
+    # ------------------------------------------------------------------ LayerDrop: one graph per block and direction
+    def _capture_segmented(self):
+        bb = self.backbone
+        L = len(bb.encoder.layers)
+        torch.cuda.synchronize()
+        pool = torch.cuda.graph_pool_handle()
+        rec = _SegmentRecorder(pool, L)
+        stream = torch.cuda.Stream()
+        stream.wait_stream(torch.cuda.current_stream())
+        bb._segment_recorder = rec      # modeling.forward places a SegmentMarkFn before every block and after the last
+        bb._force_no_layerdrop = True   # the capture holds every block; the coins are drawn per replay
+        try:
+            with torch.cuda.stream(stream):
+                rec.begin()
+                self.loss = self._body()
+                rec.end()
+        finally:
+            bb._segment_recorder = None
+            bb._force_no_layerdrop = False
+        torch.cuda.current_stream().wait_stream(stream)
+        if len(rec.graphs) != 2 * L + 3 or len(rec.fwd_x) != L + 1 or len(rec.bwd_g) != L + 1:
+            raise RuntimeError(f"GraphedTrainStep: expected {2 * L + 3} segments, captured {len(rec.graphs)} "
+                               f"({len(rec.fwd_x)} forward / {len(rec.bwd_g)} backward marks)")
+        self.L = L
+        self.graphs = rec.graphs
+        self.fwd_x, self.bwd_g = rec.fwd_x, rec.bwd_g
+        # per block: the parameters it owns (idle rows of the AdamW table when skipped) and their slices of the flat gradients
+        self.layer_idle, self.layer_grad_slices = [], []
+        for l in range(L):
+            tag = f"encoder.layers.{l}."
+            idx = self.opt.param_indices(lambda n, tag=tag: tag in n)
+            self.layer_idle.append(idx)
+            slices = []
+            for g, ii in zip(self.opt.groups, idx):
+                fp = g["fp"]
+                if ii:
+                    if ii != list(range(ii[0], ii[-1] + 1)):
+                        raise RuntimeError("GraphedTrainStep: a block's parameters are not adjacent in the flat buffer")
+                    a = fp.offsets[ii[0]]
+                    b = fp.offsets[ii[-1]] + (fp.params[ii[-1]].numel() + 3) // 4 * 4
+                    slices.append(fp.grad[a:b])
+            self.layer_grad_slices.append(slices)
+
+    def _replay_segmented(self):
+        L = self.L
+        skipped = set(self.backbone._layerdrop_coins(L))
+        self.last_skipped_layers = tuple(sorted(skipped))
+        self.backbone.last_skipped_layers = self.last_skipped_layers
+        idle = [[i for l in skipped for i in self.layer_idle[l][gi]] for gi in range(len(self.opt.groups))]
+        self.opt.prepare_hyper(idle)
+        g = self.graphs
+        g[0].replay()                                       # conv stack, projection, positional conv
+        for l in range(L):
+            if l in skipped:
+                self.fwd_x[l + 1].copy_(self.fwd_x[l])      # a dropped block is the identity
+            else:
+                g[1 + l].replay()
+        g[1 + L].replay()                                   # head, CTC, head backward
+        for l in range(L - 1, -1, -1):
+            if l in skipped:
+                self.bwd_g[l].copy_(self.bwd_g[l + 1])
+                for s in self.layer_grad_slices[l]:         # no gradient: zero for the global norm, idle in AdamW
+                    s.zero_()
+            else:
+                g[2 + L + (L - 1 - l)].replay()
+        g[2 + 2 * L].replay()                               # positional conv / projection backward, clip, AdamW
+
     def __call__(self, batch: Dict[str, torch.Tensor]) -> torch.Tensor:
         for k, dst in self.static.items():
             src = batch[k]
@@ -75,6 +203,11 @@ class GraphedTrainStep:
                 dst[:, : src.shape[1]].copy_(src, non_blocking=True)
             else:
                 dst.copy_(src, non_blocking=True)
-        self.opt.prepare_hyper()
-        self.graph.replay()
+        for g in self.opt.groups:   # weights replaced through torch since the last step (load_state_dict of the global
+            g["fp"].sync_params()   # model at the start of a federated round): the captured kernels read the bf16 shadow
+        if self.segmented:
+            self._replay_segmented()
+        else:
+            self.opt.prepare_hyper()
+            self.graph.replay()
         return self.loss

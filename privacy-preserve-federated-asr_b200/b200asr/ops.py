@@ -111,10 +111,11 @@ class on_side_stream:
     the operands read inside (their memory must not be recycled by the caching allocator until the side stream is
     done with them).  Outputs must be long-lived buffers (the flat gradient)."""
 
-    def __init__(self, *tensors, ordered=False):
+    def __init__(self, *tensors, ordered=False, manual_join=False):
         self.tensors = tensors
         self.ctx = None
         self.ordered = ordered   # the launches update a buffer an earlier side-stream launch wrote: order after all of them
+        self.manual_join = manual_join   # the caller joins (join_side_stream) before it consumes the results
 
     def __enter__(self):
         if not SIDE_STREAM_ENABLED:
@@ -137,6 +138,8 @@ class on_side_stream:
             return False
         self.ctx.__exit__(*exc)
         _SIDE_DIRTY.add(torch.cuda.current_device())
+        if self.manual_join:
+            return False
         if not _SIDE_CB_QUEUED[0]:
             try:  # joined automatically when the running backward pass ends
                 torch.autograd.Variable._execution_engine.queue_callback(join_side_stream)
@@ -432,28 +435,55 @@ def linear_wgrad(dy, x, out=None, accumulate=False):
 
 
 # ----------------------------------------------------------------------------- attention
-def mha_fwd(qkv, klen, B, T, H, dh, scale):
-    """qkv [B*T, 3*H*dh] packed; returns (ctx [B*T, H*dh], lse [B, H, T])."""
+def attn_keep_words(B, T, H) -> int:
+    return int(lib.b200asr_attn_keep_words(B, T, H))
+
+
+def attn_dropout_mask(n_sites, B, T, H, p, seed, site0, site_stride, counter=None, out=None) -> torch.Tensor:
+    """Keep bits of the attention-probability dropout for `n_sites` sites (encoder blocks) in one launch:
+    int32 [n_sites, words] (b200asr_attn_dropout_mask layout).  counter: host int or device int64 [1] step counter."""
+    words = attn_keep_words(B, T, H)
+    if out is None:
+        out = torch.empty(n_sites, words, dtype=torch.int32, device="cuda")
+    assert out.dtype == torch.int32 and out.is_contiguous() and out.numel() >= n_sites * words
+    dev = counter if isinstance(counter, torch.Tensor) else None
+    host = 0 if dev is not None or counter is None else int(counter)
+    check(lib.b200asr_attn_dropout_mask(_p(out), n_sites, B, T, H, float(p), int(seed) & (2 ** 64 - 1), int(site0),
+                                        int(site_stride), host, _p(dev), _st()), "attn_dropout_mask")
+    return out
+
+
+def attn_keep_dense(keep: torch.Tensor, B, T, H) -> torch.Tensor:
+    """Test helper: the keep bits of one site as a bool tensor [B, H, T(query), T(key)]."""
+    KW, TQ = (T + 31) // 32, (T + 127) // 128 * 128
+    w = keep.view(B, H, KW, TQ)[..., :T].to(torch.int64) & 0xffffffff       # [B, H, KW, Tq]
+    bits = (w.unsqueeze(-1) >> torch.arange(32, device=keep.device)) & 1    # [B, H, KW, Tq, 32]
+    return bits.permute(0, 1, 3, 2, 4).reshape(B, H, T, KW * 32)[..., :T].bool()
+
+
+def mha_fwd(qkv, klen, B, T, H, dh, scale, keep=None, p_drop=0.0):
+    """qkv [B*T, 3*H*dh] packed; returns (ctx [B*T, H*dh], lse [B, H, T]).  keep: int32 keep bits of this site
+    (attn_dropout_mask) -> dropout with probability p_drop on the softmax probabilities."""
     assert qkv.is_contiguous()
     out = torch.empty(B * T, H * dh, dtype=qkv.dtype, device=qkv.device)
     lse = torch.empty(B, H, T, dtype=torch.float32, device=qkv.device)
     nws = lib.b200asr_mha_fwd_workspace_bytes(B, T, H, dh, dt(qkv))
     ws = workspace(nws, qkv.device)
     e0 = _prof_begin()
-    check(lib.b200asr_mha_fwd(_p(qkv), _p(out), _p(lse), _p(klen), _p(ws), nws, B, T, H, dh, float(scale), dt(qkv),
-                              _st()), "mha_fwd")
+    check(lib.b200asr_mha_fwd_dropout(_p(qkv), _p(out), _p(lse), _p(klen), _p(keep), float(p_drop), _p(ws), nws, B, T, H, dh,
+                                      float(scale), dt(qkv), _st()), "mha_fwd")
     _prof_end("mha_fwd", e0, 4.0 * B * H * T * T * dh)
     return out, lse
 
 
-def mha_bwd(qkv, out, dout, lse, klen, B, T, H, dh, scale):
+def mha_bwd(qkv, out, dout, lse, klen, B, T, H, dh, scale, keep=None, p_drop=0.0):
     dout = _c(dout)
     dqkv = torch.empty_like(qkv)
     nws = lib.b200asr_mha_bwd_workspace_bytes(B, T, H, dh, dt(qkv))
     ws = workspace(nws, qkv.device)
     e0 = _prof_begin()
-    check(lib.b200asr_mha_bwd(_p(qkv), _p(out), _p(dout), _p(lse), _p(klen), _p(dqkv), _p(ws), nws, B, T, H, dh,
-                              float(scale), dt(qkv), _st()), "mha_bwd")
+    check(lib.b200asr_mha_bwd_dropout(_p(qkv), _p(out), _p(dout), _p(lse), _p(klen), _p(keep), float(p_drop), _p(dqkv),
+                                      _p(ws), nws, B, T, H, dh, float(scale), dt(qkv), _st()), "mha_bwd")
     _prof_end("mha_bwd", e0, 10.0 * B * H * T * T * dh)
     return dqkv
 
@@ -611,11 +641,13 @@ def fedavg_prescale_(buf: torch.Tensor, w: float):
     return buf
 
 
-def fedavg_peer_reduce(peer_ptrs: Sequence[int], weights: Optional[Sequence[float]], rank: int, n: int):
+def fedavg_peer_reduce(peer_ptrs: Sequence[int], weights: Optional[Sequence[float]], rank: int, n: int,
+                       abort_flag: Optional[torch.Tensor] = None):
+    """abort_flag: device int32 [1] (the barrier's timeout flag): when set, the kernel leaves every buffer untouched."""
     world = len(peer_ptrs)
     ptrs = (C.c_void_p * world)(*[int(p) for p in peer_ptrs])
     w = (C.c_float * world)(*[float(v) for v in weights]) if weights is not None else None
-    check(lib.b200asr_fedavg_peer_reduce(ptrs, w, world, rank, n, _st()), "fedavg_peer_reduce")
+    check(lib.b200asr_fedavg_peer_reduce_guarded(ptrs, w, world, rank, n, _p(abort_flag), _st()), "fedavg_peer_reduce")
 
 
 def adamw_step_(p, grad, m, v, shadow, lr, beta1, beta2, eps, weight_decay, step, gnorm_sq=None, max_norm=1.0):
@@ -635,7 +667,22 @@ def adamw_step_dev_(p, grad, m, v, shadow, hyper, beta1, beta2, eps, weight_deca
           "adamw_step_dev")
 
 
-def sumsq_(x: torch.Tensor, out: torch.Tensor):
+def adamw_step_chunks_(p, grad, m, v, shadow, chunks, hyper, beta1, beta2, eps, weight_decay, gnorm_sq=None, max_norm=1.0):
+    """AdamW with per-parameter {lr, step size} rows in the device table `hyper` [n_params, 2] (a negative step size =
+    the parameter is idle in this step) over the chunk table `chunks` int32 [n_chunks, 4] (b200asr_adamw_step_chunks)."""
+    for t in (p, grad, m, v, hyper):
+        assert t.dtype == torch.float32 and t.is_contiguous()
+    assert chunks.dtype == torch.int32 and chunks.is_contiguous() and chunks.shape[1] == 4
+    check(lib.b200asr_adamw_step_chunks(_p(p), _p(grad), _p(m), _p(v), _p(shadow), _p(chunks), chunks.shape[0], _p(hyper),
+                                        float(beta1), float(beta2), float(eps), float(weight_decay), _p(gnorm_sq),
+                                        float(max_norm), _st()), "adamw_step_chunks")
+
+
+def sumsq_(x: torch.Tensor, out: torch.Tensor, ws: Optional[torch.Tensor] = None):
+    """out[0] += sum(x^2); `ws` = caller-owned zero-initialised workspace (uint8, >= b200asr_sumsq_workspace_bytes())."""
     assert x.dtype == torch.float32 and x.is_contiguous() and out.dtype == torch.float32
-    check(lib.b200asr_sumsq(_p(x), x.numel(), _p(out), _st()), "sumsq")
+    if ws is None:
+        check(lib.b200asr_sumsq(_p(x), x.numel(), _p(out), _st()), "sumsq")
+    else:
+        check(lib.b200asr_sumsq_ws(_p(x), x.numel(), _p(out), _p(ws), ws.numel() * ws.element_size(), _st()), "sumsq_ws")
     return out

@@ -3,15 +3,25 @@
 Semantics of the reference's optimizer = HF Trainer "adamw_hf" (transformers.AdamW, correct_bias=True) with
 max_grad_norm clipping, weight decay on everything except biases and LayerNorm weights, linear warm-up then
 linear decay (centralized/finetune_ASRs.py:202-220, federated/src/update.py:651-678).
+
+transformers.AdamW keeps `state["step"]` PER PARAMETER and skips parameters whose `grad is None` (a block dropped by
+LayerDrop, an unused head, `masked_spec_embed` without SpecAugment).  Here that is a device table: one {lr, bias-corrected
+step size} row per parameter (negative step size = idle in this step) consumed by `b200asr_adamw_step_chunks` -- the same
+launch serves every pattern of idle parameters, so it can be captured in a CUDA graph; the eager step() and the captured
+step_captured() go through the same arithmetic and agree bit for bit.
 """
 from __future__ import annotations
 
-from typing import Iterable, Optional
+from typing import Dict, Iterable, List, Optional, Sequence
 
+import numpy as np
 import torch
 
 from . import ops
+from ._lib import lib
 from .fedavg import FlatParams
+
+CHUNK_VECS = 2048  # float4 per chunk of the AdamW chunk table (8192 parameters: one 256-thread block, 8 float4 per thread)
 
 
 def _no_decay(name: str) -> bool:
@@ -39,6 +49,9 @@ class FusedAdamW:
         self.step_count = 0
         dev = self.groups[0]["fp"].flat.device
         self.gnorm_sq = torch.zeros(1, dtype=torch.float32, device=dev)
+        # caller-owned partials + arrival counter of the deterministic sum of squares: two optimizers (two clients on one
+        # GPU, a side stream) never share reduction state
+        self.sumsq_ws = torch.zeros(int(lib.b200asr_sumsq_workspace_bytes()), dtype=torch.uint8, device=dev)
 
     def current_lr(self) -> float:
         s = self.step_count
@@ -52,6 +65,7 @@ class FusedAdamW:
         """No memset: every parameter is marked fresh, the backward kernels overwrite their slice of the flat
         gradient (functional.grad_sink); parameters that end up with no gradient are zeroed in step()."""
         for g in self.groups:
+            g["fp"].sync_params()   # weights replaced through torch since the last step (load_state_dict): refresh the shadow
             for p in g["fp"].params:
                 p.grad = None
                 p._b200_fresh = True
@@ -81,37 +95,56 @@ class FusedAdamW:
             untouched.append(idle)
         return untouched
 
-    def _segments(self, g, idle):
-        """Per-parameter step counts (transformers.AdamW keeps `state["step"]` per parameter and only advances it
-        when the parameter has a gradient).  Yields (start, end, step) over the flat buffer: maximal runs of
-        consecutive parameters that are updated in this step with the same step number."""
+    # ---- per-parameter step table
+    def _table(self, g):
+        """(chunks int32 [n, 4] on the device, hyper fp32 [n_params, 2] on the device) of one group, built once."""
+        if "chunks" not in g:
+            fp = g["fp"]
+            rows = []
+            for i, (p, o) in enumerate(zip(fp.params, fp.offsets)):
+                v0, nv = o // 4, (p.numel() + 3) // 4
+                for c in range(0, nv, CHUNK_VECS):
+                    rows.append((v0 + c, min(CHUNK_VECS, nv - c), i, 0))
+            g["chunks"] = torch.tensor(rows, dtype=torch.int32, device=fp.flat.device)
+            g["hyper_dev"] = torch.zeros(len(fp.params), 2, dtype=torch.float32, device=fp.flat.device)
+        return g["chunks"], g["hyper_dev"]
+
+    def _upload_hyper(self, g, idle: Sequence[int], lr: float):
+        """Advance the step count of every non-idle parameter of the group and upload its {lr, step size} rows
+        (same arithmetic as b200asr_adamw_step: lr and betas rounded to fp32 first, bias correction in double)."""
         fp = g["fp"]
-        steps = g.setdefault("param_steps", [self.step_count - 1] * len(fp.params))
-        idle = set(idle)
-        run = None
-        for i, (p, o) in enumerate(zip(fp.params, fp.offsets)):
-            if i in idle:
-                if run:
-                    yield run
-                run = None
+        _, hyper_dev = self._table(g)
+        n = len(fp.params)
+        steps = g.get("param_steps")
+        if steps is None:
+            steps = g["param_steps"] = np.full(n, self.step_count - 1, dtype=np.int64)
+        active = np.ones(n, dtype=bool)
+        if len(idle):
+            active[np.asarray(list(idle), dtype=np.int64)] = False
+        steps[active] += 1
+        lr32 = float(np.float32(lr))
+        b1, b2 = float(np.float32(self.betas[0])), float(np.float32(self.betas[1]))
+        rows = np.empty((n, 2), dtype=np.float32)
+        rows[:, 0] = lr32
+        cache: Dict[int, float] = {}
+        for i in range(n):   # (C pow through Python floats: bit-identical to b200asr_adamw_step's double arithmetic)
+            if not active[i]:
+                rows[i, 1] = -1.0
                 continue
-            steps[i] += 1
-            end = o + (p.numel() + 3) // 4 * 4
-            if run and run[2] == steps[i]:
-                run = (run[0], end, run[2])
-            else:
-                if run:
-                    yield run
-                run = (o, end, steps[i])
-        if run:
-            yield run
+            t = int(max(steps[i], 1))
+            if t not in cache:
+                cache[t] = lr32 * (1.0 - b2 ** t) ** 0.5 / (1.0 - b1 ** t)
+            rows[i, 1] = cache[t]
+        # a fresh pageable tensor per step: the copy is staged before the call returns, so the next step's values can
+        # never overtake this one in the stream
+        hyper_dev.copy_(torch.from_numpy(rows))
 
     def _clip_norm(self):
         if self.max_grad_norm is None:
             return None
         self.gnorm_sq.zero_()
         for g in self.groups:
-            ops.sumsq_(g["fp"].grad, self.gnorm_sq)
+            ops.sumsq_(g["fp"].grad, self.gnorm_sq, self.sumsq_ws)
         return self.gnorm_sq
 
     def step(self):
@@ -122,47 +155,64 @@ class FusedAdamW:
         gn = self._clip_norm()
         for g, idle in zip(self.groups, untouched):
             fp = g["fp"]
-            if not idle and "param_steps" not in g:  # every parameter has always been updated: one launch per group
+            if not idle and "param_steps" not in g:  # every parameter has always been updated: one scalar launch per group
                 ops.adamw_step_(fp.flat, fp.grad, g["m"], g["v"], fp.shadow, lr, self.betas[0], self.betas[1], self.eps,
                                 g["wd"], self.step_count, gn, self.max_grad_norm or 0.0)
             else:
-                for a, b, t in self._segments(g, idle):
-                    ops.adamw_step_(fp.flat[a:b], fp.grad[a:b], g["m"][a:b], g["v"][a:b],
-                                    None if fp.shadow is None else fp.shadow[a:b], lr, self.betas[0], self.betas[1],
-                                    self.eps, g["wd"], t, gn, self.max_grad_norm or 0.0)
+                self._upload_hyper(g, idle, lr)
+                chunks, hyper = self._table(g)
+                ops.adamw_step_chunks_(fp.flat, fp.grad, g["m"], g["v"], fp.shadow, chunks, hyper, self.betas[0],
+                                       self.betas[1], self.eps, g["wd"], gn, self.max_grad_norm or 0.0)
             fp.mark_updated(shadow_written=fp.shadow is not None)
 
     # ---- CUDA-graph friendly split: per-step scalars live in device memory (graph.GraphedTrainStep)
-    def prepare_hyper(self):
-        """Host side of the next update: advances the step counter and uploads {lr, lr*sqrt(1-b2^t)/(1-b1^t)} to the
-        device tensor the captured AdamW launch reads.  Call once before every replay (outside the graph)."""
-        if not hasattr(self, "hyper_dev"):
-            dev = self.groups[0]["fp"].flat.device
-            self.hyper_dev = torch.zeros(2, dtype=torch.float32, device=dev)
+    def prepare_hyper(self, idle: Optional[Sequence[Sequence[int]]] = None):
+        """Host side of the next captured update: advances the step counters and uploads the per-parameter
+        {lr, lr*sqrt(1-b2^t)/(1-b1^t)} table the captured AdamW launch reads.  Call once before every replay (outside the
+        graph).  `idle`: per group, the indices of the parameters without a gradient in THIS step (blocks LayerDrop
+        skipped) in addition to the ones that never get one (`static_idle`, found when the update was captured)."""
         lr = self.current_lr()
         self.step_count += 1
-        t = self.step_count
-        # a fresh pageable tensor per step: the copy is staged before the call returns, so the next step's values
-        # can never overtake this one in the stream
-        # (same arithmetic as b200asr_adamw_step: lr rounded to fp32 first, bias correction in double -> bit-identical
-        # to the eager path)
-        lr32 = float(torch.tensor(lr, dtype=torch.float32))
-        b1, b2 = float(torch.tensor(self.betas[0], dtype=torch.float32)), float(torch.tensor(self.betas[1], dtype=torch.float32))
-        self.hyper_dev.copy_(torch.tensor([lr32, lr32 * (1.0 - b2 ** t) ** 0.5 / (1.0 - b1 ** t)], dtype=torch.float32))
+        for gi, g in enumerate(self.groups):
+            skip = set(g.get("static_idle", ()))
+            if idle is not None:
+                skip |= set(idle[gi])
+            self._upload_hyper(g, sorted(skip), lr)
 
     def step_captured(self):
         """Device side of the update, with no host-dependent scalar: what a CUDA graph captures."""
         ops.join_side_stream()
-        self._gather_stray_grads()
+        untouched = self._gather_stray_grads()
         gn = self._clip_norm()
-        for g in self.groups:
+        for g, idle in zip(self.groups, untouched):
             fp = g["fp"]
-            ops.adamw_step_dev_(fp.flat, fp.grad, g["m"], g["v"], fp.shadow, self.hyper_dev, self.betas[0], self.betas[1],
-                                self.eps, g["wd"], gn, self.max_grad_norm or 0.0)
+            # parameters that get no gradient from this (fixed) launch sequence never will in a replay either: from now
+            # on prepare_hyper marks them idle, as the eager step() does
+            g["static_idle"] = tuple(idle)
+            chunks, hyper = self._table(g)
+            ops.adamw_step_chunks_(fp.flat, fp.grad, g["m"], g["v"], fp.shadow, chunks, hyper, self.betas[0], self.betas[1],
+                                   self.eps, g["wd"], gn, self.max_grad_norm or 0.0)
             fp.mark_updated(shadow_written=fp.shadow is not None)
+
+    def param_indices(self, predicate) -> List[List[int]]:
+        """Per group, the indices of the parameters whose name satisfies `predicate` (e.g. one encoder block)."""
+        return [[i for i, n in enumerate(g["fp"].names) if predicate(n)] for g in self.groups]
 
     def state_tensors(self):
         out = []
         for g in self.groups:
             out += [g["fp"].flat, g["m"], g["v"]] + ([g["fp"].shadow] if g["fp"].shadow is not None else [])
         return out
+
+    def host_state(self) -> Dict:
+        """Host-side counters (restored together with state_tensors() after a graph capture's warm-up steps)."""
+        return dict(step_count=self.step_count,
+                    param_steps=[None if g.get("param_steps") is None else g["param_steps"].copy() for g in self.groups])
+
+    def load_host_state(self, st: Dict):
+        self.step_count = st["step_count"]
+        for g, ps in zip(self.groups, st["param_steps"]):
+            if ps is None:
+                g.pop("param_steps", None)
+            else:
+                g["param_steps"] = ps.copy()

@@ -65,7 +65,11 @@ __global__ void __launch_bounds__(256) prescale_kernel(float* __restrict__ x, fl
 // Rank `rank` owns slice [lo, hi): reads that slice from every peer (NVLink loads), reduces, writes the result
 // into every peer's slice (NVLink stores).  One kernel = reduce-scatter + all-gather with the scaling fused in.
 template <int UNIFORM>
-__global__ void __launch_bounds__(256) fedavg_peer_kernel(const PeerPtrs p, int world, long long lo, long long hi) {
+__global__ void __launch_bounds__(256) fedavg_peer_kernel(const PeerPtrs p, int world, long long lo, long long hi,
+                                                          const int* __restrict__ abort_flag) {
+    // the barrier in front of this kernel gave up on a peer (straggler / dead client): leave every buffer untouched --
+    // a partial average written into the peers would be silently wrong on all ranks (PeerFedAvg.check() raises)
+    if (abort_flag && *abort_flag) return;
     const float kf = (float)world;
     const long long nvec = (hi - lo) / 4;  // lo, hi are multiples of 4 except the global tail handled by the last rank
     constexpr int U = 4;                   // independent 16-byte loads per peer in flight per thread (NVLink latency)
@@ -121,19 +125,30 @@ struct PeerFlags {
     unsigned* f[FEDAVG_MAX_K];
 };
 
-__global__ void fedavg_peer_barrier_kernel(const PeerFlags s, int world, int rank, unsigned epoch, int* timeout) {
+static long long g_barrier_spin_clocks = 4000000000LL;  // ~2 s of SM clock (b200asr_fedavg_peer_barrier_set_timeout)
+
+__global__ void fedavg_peer_barrier_kernel(const PeerFlags s, int world, int rank, unsigned epoch, int* timeout,
+                                           long long spin_clocks) {
     const int t = threadIdx.x;
     if (t >= world) return;
     __threadfence_system();
+    // a rank whose earlier barrier gave up publishes POISON instead of the epoch: every peer that meets it marks its own
+    // timeout flag as well, so a torn round is reported by PeerFedAvg.check() on ALL ranks, not only on the straggler's
+    constexpr unsigned POISON = 0xffffffffu;
+    const bool poisoned = timeout && *reinterpret_cast<volatile int*>(timeout) != 0;
     unsigned* remote = s.f[t] + rank;
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(remote), "r"(epoch) : "memory");
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(remote), "r"(poisoned ? POISON : epoch) : "memory");
     const unsigned* local = s.f[rank] + t;
     const long long t0 = clock64();
     for (;;) {
         unsigned v;
         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(local) : "memory");
+        if (v == POISON) {
+            if (timeout) *timeout = 1;
+            break;
+        }
         if ((int)(v - epoch) >= 0) break;
-        if (clock64() - t0 > 4000000000LL) {
+        if (clock64() - t0 > spin_clocks) {
             if (timeout) *timeout = 1;
             break;
         }
@@ -196,13 +211,69 @@ __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, const
     }
 }
 
+// Per-parameter hyper-parameters (transformers.AdamW keeps state["step"] per parameter and skips parameters without a
+// gradient): the flat buffer is cut into chunks that never straddle a parameter, `chunks[c] = {first vec4, vec4 count,
+// parameter index, 0}`; `hyper[2 * param] = {lr, lr * sqrt(1 - b2^t) / (1 - b1^t)}` with a NEGATIVE step size meaning
+// "no gradient this step: leave p / m / v / shadow alone" (a block dropped by LayerDrop, an unused head).  One block per
+// chunk (grid-stride), so a launch captured in a CUDA graph serves every pattern of idle parameters.
+__global__ void __launch_bounds__(256) adamw_chunks_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                           float* __restrict__ m, float* __restrict__ v,
+                                                           __nv_bfloat16* __restrict__ shadow,
+                                                           const int4* __restrict__ chunks, int nchunks,
+                                                           const float* __restrict__ hyper, float b1, float b2, float eps,
+                                                           float wd, const float* __restrict__ gnorm_sq, float max_norm) {
+    float clip = 1.f;
+    if (gnorm_sq) {
+        const float nrm = sqrtf(*gnorm_sq);
+        clip = fminf(1.f, max_norm / (nrm + 1e-6f));
+    }
+    for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
+        const int4 ch = __ldg(chunks + c);
+        const float lr = __ldg(hyper + 2 * ch.z), step_size = __ldg(hyper + 2 * ch.z + 1);
+        if (step_size < 0.f) continue;
+        for (int j = threadIdx.x; j < ch.y; j += blockDim.x) {
+            const long long i = (long long)ch.x + j;
+            float4 pv = *reinterpret_cast<float4*>(p + 4 * i);
+            const float4 gv = *reinterpret_cast<const float4*>(g + 4 * i);
+            float4 mv = *reinterpret_cast<float4*>(m + 4 * i);
+            float4 vv = *reinterpret_cast<float4*>(v + 4 * i);
+            float pa[4] = {pv.x, pv.y, pv.z, pv.w};
+            const float ga[4] = {gv.x, gv.y, gv.z, gv.w};
+            float ma[4] = {mv.x, mv.y, mv.z, mv.w};
+            float va[4] = {vv.x, vv.y, vv.z, vv.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {   // same arithmetic, in the same order, as adamw_kernel
+                const float gg = ga[k] * clip;
+                ma[k] = b1 * ma[k] + (1.f - b1) * gg;
+                va[k] = b2 * va[k] + (1.f - b2) * gg * gg;
+                pa[k] -= step_size * ma[k] / (sqrtf(va[k]) + eps);
+                pa[k] -= lr * wd * pa[k];
+            }
+            *reinterpret_cast<float4*>(p + 4 * i) = make_float4(pa[0], pa[1], pa[2], pa[3]);
+            *reinterpret_cast<float4*>(m + 4 * i) = make_float4(ma[0], ma[1], ma[2], ma[3]);
+            *reinterpret_cast<float4*>(v + 4 * i) = make_float4(va[0], va[1], va[2], va[3]);
+            if (shadow) {
+                uint2 o;
+                o.x = bf2_pack(pa[0], pa[1]);
+                o.y = bf2_pack(pa[2], pa[3]);
+                *reinterpret_cast<uint2*>(shadow + 4 * i) = o;
+            }
+        }
+    }
+}
+
 // Deterministic: every block parks its partial sum, the last block to finish adds them in block order (no
 // floating-point atomics, so the clipping coefficient -- and with it the whole update -- is reproducible bit for bit).
 constexpr int SUMSQ_MAX_BLOCKS = 1024;
 __device__ float g_sumsq_partial[SUMSQ_MAX_BLOCKS];
 __device__ unsigned int g_sumsq_arrived = 0;
 
-__global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ x, long long n, float* __restrict__ out) {
+__global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ x, long long n, float* __restrict__ out,
+                                                    float* __restrict__ ws_partial, unsigned int* __restrict__ ws_arrived) {
+    // ws_*: caller-owned partials + arrival counter (b200asr_sumsq_ws); the module-global pair serves b200asr_sumsq,
+    // which is therefore limited to one launch in flight per device
+    float* partial = ws_partial ? ws_partial : g_sumsq_partial;
+    unsigned int* arrived = ws_arrived ? ws_arrived : &g_sumsq_arrived;
     __shared__ float red[32];
     __shared__ bool is_last;
     float s = 0.f;
@@ -215,19 +286,19 @@ __global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ x,
         s += x[i] * x[i];
     s = block_sum(s, red);
     if (threadIdx.x == 0) {
-        g_sumsq_partial[blockIdx.x] = s;
+        partial[blockIdx.x] = s;
         __threadfence();
-        is_last = (atomicAdd(&g_sumsq_arrived, 1u) == gridDim.x - 1);
+        is_last = (atomicAdd(arrived, 1u) == gridDim.x - 1);
     }
     __syncthreads();
     if (is_last) {
         __threadfence();
         float t = 0.f;
-        for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) t += __ldcg(&g_sumsq_partial[i]);
+        for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) t += __ldcg(&partial[i]);
         t = block_sum(t, red);
         if (threadIdx.x == 0) {
             out[0] += t;
-            g_sumsq_arrived = 0;
+            *arrived = 0;
         }
     }
 }
@@ -271,8 +342,8 @@ int b200asr_fedavg_prescale(float* buf, float w, long long n, void* stream) {
     return check_launch("fedavg_prescale");
 }
 
-int b200asr_fedavg_peer_reduce(float* const* peer_bufs, const float* weights, int world, int rank, long long n,
-                               void* stream) {
+static int fedavg_peer_reduce_impl(float* const* peer_bufs, const float* weights, int world, int rank, long long n,
+                                   const int* abort_flag, void* stream) {
     B200_REQUIRE(peer_bufs, "fedavg_peer_reduce: null pointer");
     B200_REQUIRE(world >= 1 && world <= FEDAVG_MAX_K && rank >= 0 && rank < world, "fedavg_peer_reduce: bad world/rank");
     if (n <= 0) return B200ASR_OK;
@@ -287,9 +358,19 @@ int b200asr_fedavg_peer_reduce(float* const* peer_bufs, const float* weights, in
     const long long lo = per * rank;
     const long long hi = (rank == world - 1) ? n : per * (rank + 1);
     if (hi <= lo) return B200ASR_OK;
-    if (weights) fedavg_peer_kernel<0><<<stream_grid(hi - lo), 256, 0, as_stream(stream)>>>(p, world, lo, hi);
-    else fedavg_peer_kernel<1><<<stream_grid(hi - lo), 256, 0, as_stream(stream)>>>(p, world, lo, hi);
+    if (weights) fedavg_peer_kernel<0><<<stream_grid(hi - lo), 256, 0, as_stream(stream)>>>(p, world, lo, hi, abort_flag);
+    else fedavg_peer_kernel<1><<<stream_grid(hi - lo), 256, 0, as_stream(stream)>>>(p, world, lo, hi, abort_flag);
     return check_launch("fedavg_peer_reduce");
+}
+
+int b200asr_fedavg_peer_reduce(float* const* peer_bufs, const float* weights, int world, int rank, long long n,
+                               void* stream) {
+    return fedavg_peer_reduce_impl(peer_bufs, weights, world, rank, n, nullptr, stream);
+}
+
+int b200asr_fedavg_peer_reduce_guarded(float* const* peer_bufs, const float* weights, int world, int rank, long long n,
+                                       const int* abort_flag, void* stream) {
+    return fedavg_peer_reduce_impl(peer_bufs, weights, world, rank, n, abort_flag, stream);
 }
 
 int b200asr_fedavg_peer_barrier(unsigned* const* peer_flags, int world, int rank, unsigned epoch, int* timeout_flag,
@@ -301,8 +382,14 @@ int b200asr_fedavg_peer_barrier(unsigned* const* peer_flags, int world, int rank
         s.f[j] = j < world ? peer_flags[j] : nullptr;
         if (j < world) B200_REQUIRE(peer_flags[j], "fedavg_peer_barrier: null flag pointer for rank %d", j);
     }
-    fedavg_peer_barrier_kernel<<<1, 32, 0, as_stream(stream)>>>(s, world, rank, epoch, timeout_flag);
+    fedavg_peer_barrier_kernel<<<1, 32, 0, as_stream(stream)>>>(s, world, rank, epoch, timeout_flag, g_barrier_spin_clocks);
     return check_launch("fedavg_peer_barrier");
+}
+
+int b200asr_fedavg_peer_barrier_set_timeout(double seconds) {
+    B200_REQUIRE(seconds > 0.0 && seconds < 600.0, "fedavg_peer_barrier_set_timeout: seconds out of range");
+    g_barrier_spin_clocks = (long long)(seconds * 1.9e9);
+    return B200ASR_OK;
 }
 
 // ---- peer-visible allocations + CUDA IPC plumbing (one federated client per process / GPU)
@@ -395,15 +482,48 @@ int b200asr_adamw_step_dev(float* p, const float* grad, float* m, float* v, void
     return check_launch("adamw_step_dev");
 }
 
+static int sumsq_grid(long long n) {
+    long long g = (n / 4 + 255) / 256;
+    long long cap = (long long)num_sms() * 4;
+    if (cap > SUMSQ_MAX_BLOCKS) cap = SUMSQ_MAX_BLOCKS;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
 int b200asr_sumsq(const float* x, long long n, float* out, void* stream) {
     B200_REQUIRE(x && out && ((uintptr_t)x & 15) == 0, "sumsq: bad pointer");
     if (n <= 0) return B200ASR_OK;
-    long long g = (n / 4 + 255) / 256;
-    const long long cap = (long long)num_sms() * 4;
-    if (g > cap) g = cap;
-    if (g < 1) g = 1;
-    sumsq_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(x, n, out);
+    sumsq_kernel<<<sumsq_grid(n), 256, 0, as_stream(stream)>>>(x, n, out, nullptr, nullptr);
     return check_launch("sumsq");
+}
+
+size_t b200asr_sumsq_workspace_bytes(void) { return (size_t)(SUMSQ_MAX_BLOCKS + 4) * sizeof(float); }
+
+int b200asr_sumsq_ws(const float* x, long long n, float* out, void* workspace, size_t workspace_bytes, void* stream) {
+    B200_REQUIRE(x && out && workspace && ((uintptr_t)x & 15) == 0, "sumsq_ws: bad pointer");
+    B200_REQUIRE(workspace_bytes >= b200asr_sumsq_workspace_bytes(), "sumsq_ws: workspace too small");
+    if (n <= 0) return B200ASR_OK;
+    float* partial = (float*)workspace;
+    unsigned int* arrived = (unsigned int*)(partial + SUMSQ_MAX_BLOCKS);   // must be zero before the first use
+    sumsq_kernel<<<sumsq_grid(n), 256, 0, as_stream(stream)>>>(x, n, out, partial, arrived);
+    return check_launch("sumsq_ws");
+}
+
+int b200asr_adamw_step_chunks(float* p, const float* grad, float* m, float* v, void* shadow_bf16, const int* chunks,
+                              int nchunks, const float* hyper, float beta1, float beta2, float eps, float weight_decay,
+                              const float* gnorm_sq, float max_norm, void* stream) {
+    B200_REQUIRE(p && grad && m && v && chunks && hyper, "adamw_chunks: null pointer");
+    B200_REQUIRE((((uintptr_t)p | (uintptr_t)grad | (uintptr_t)m | (uintptr_t)v | (uintptr_t)chunks) & 15) == 0,
+                 "adamw_chunks: buffers must be 16-byte aligned");
+    B200_REQUIRE(!shadow_bf16 || ((uintptr_t)shadow_bf16 & 7) == 0, "adamw_chunks: shadow must be 8-byte aligned");
+    if (nchunks <= 0) return B200ASR_OK;
+    int grid = nchunks;
+    const int cap = num_sms() * 8;
+    if (grid > cap) grid = cap;
+    adamw_chunks_kernel<<<grid, 256, 0, as_stream(stream)>>>(p, grad, m, v, (__nv_bfloat16*)shadow_bf16, (const int4*)chunks,
+                                                             nchunks, hyper, beta1, beta2, eps, weight_decay, gnorm_sq, max_norm);
+    return check_launch("adamw_step_chunks");
 }
 
 }  // extern "C"
