@@ -71,6 +71,28 @@ __global__ void __launch_bounds__(256) softmax_rows_bwd_kernel(T* __restrict__ p
     }
 }
 
+// Composed path: x[b,h,q,k] = keep(b,h,q,k) ? x * inv_keep : 0 on a [B,H,T,ldk] plane (probabilities in the forward,
+// dP and then P in the backward), keep bits in the layout of the fused kernels (attn.h).
+template <typename T>
+__global__ void __launch_bounds__(256) apply_keep_kernel(T* __restrict__ x, const unsigned* __restrict__ keep, int Tq, int Tk,
+                                                         int ldk, int KW, int TQ, float inv_keep, long long rows) {
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long row = warp; row < rows; row += nwarps) {
+        const long long bh = row / Tq;
+        const int q = (int)(row - bh * Tq);
+        T* xr = x + row * ldk;
+        for (int k0 = 0; k0 < Tk; k0 += 32) {
+            const unsigned w = keep[(bh * KW + (k0 >> 5)) * (long long)TQ + q];
+            const int k = k0 + lane;
+            if (k < Tk) xr[k] = from_f<T>((w >> lane) & 1u ? to_f<T>(xr[k]) * inv_keep : 0.f);
+        }
+    }
+}
+
+static int apply_keep(void* x, const unsigned* keep, int B, int H, int Tn, int ldk, float p_drop, int dtype, cudaStream_t st);
+
 static int softmax_grid(long long rows) {
     long long g = (rows + 7) / 8;
     const long long cap = (long long)num_sms() * 8;
@@ -101,6 +123,15 @@ static int gemm_qk(const void* qkv, void* S, int B, int T, int H, int dh, int ld
     g.sa1 = (long long)T * 3 * D; g.sb1 = (long long)T * 3 * D; g.sc1 = (long long)H * T * ldk;
     g.dtype = dtype; g.c_dtype = dtype;
     return gemm_dispatch(g, st);
+}
+
+static int apply_keep(void* x, const unsigned* keep, int B, int H, int Tn, int ldk, float p_drop, int dtype, cudaStream_t st) {
+    const long long rows = (long long)B * H * Tn;
+    const int kw = attn_keep_kw(Tn), tq = attn_keep_tq(Tn);
+    B200_DISPATCH_DTYPE(dtype, {
+        apply_keep_kernel<T><<<softmax_grid(rows), 256, 0, st>>>((T*)x, keep, Tn, Tn, ldk, kw, tq, 1.0f / (1.0f - p_drop), rows);
+    });
+    return check_launch("attn_apply_keep");
 }
 
 }  // namespace b200asr
@@ -144,19 +175,44 @@ size_t b200asr_mha_fwd_workspace_bytes(int B, int T, int H, int dh, int dtype) {
     return (size_t)B * H * T * round_up8(T) * elem_size(dtype);
 }
 
+size_t b200asr_attn_keep_words(int B, int T, int H) {
+    return (size_t)B * H * attn_keep_kw(T) * attn_keep_tq(T);
+}
+
+int b200asr_attn_dropout_mask(unsigned* keep, int n_sites, int B, int T, int H, float p, unsigned long long seed,
+                              unsigned long long site0, unsigned long long site_stride, unsigned long long offset,
+                              const unsigned long long* dev_offset, void* stream) {
+    B200_REQUIRE(keep && n_sites > 0 && B > 0 && T > 0 && H > 0, "attn_dropout_mask: bad argument");
+    B200_REQUIRE(p >= 0.f && p < 1.f, "attn_dropout_mask: p=%f must be in [0, 1)", (double)p);
+    return attn_keep_mask_launch(keep, n_sites, B, T, H, p, seed, site0, site_stride, offset, dev_offset, as_stream(stream));
+}
+
 int b200asr_mha_fwd(const void* qkv, void* out, float* lse, const int* klen, void* workspace, size_t workspace_bytes,
                     int B, int T, int H, int dh, float scale, int dtype, void* stream) {
+    return b200asr_mha_fwd_dropout(qkv, out, lse, klen, nullptr, 0.f, workspace, workspace_bytes, B, T, H, dh, scale, dtype,
+                                   stream);
+}
+
+int b200asr_mha_fwd_dropout(const void* qkv, void* out, float* lse, const int* klen, const unsigned* keep, float p_drop,
+                            void* workspace, size_t workspace_bytes, int B, int T, int H, int dh, float scale, int dtype,
+                            void* stream) {
     B200_REQUIRE(qkv && out && lse && workspace, "mha_fwd: null pointer");
     B200_REQUIRE(B > 0 && T > 0 && H > 0 && dh > 0 && dh % 8 == 0, "mha_fwd: bad shape");
     B200_REQUIRE(workspace_bytes >= b200asr_mha_fwd_workspace_bytes(B, T, H, dh, dtype), "mha_fwd: workspace too small");
+    B200_REQUIRE(!keep || (p_drop >= 0.f && p_drop < 1.f), "mha_fwd: p_drop=%f must be in [0, 1)", (double)p_drop);
     cudaStream_t st = as_stream(stream);
-    if (g_mha_fused && mha_tc_eligible(dtype, dh, qkv)) return mha_fwd_tc_launch(qkv, out, lse, klen, B, T, H, scale, st);
+    if (g_mha_fused && mha_tc_eligible(dtype, dh, qkv))
+        return mha_fwd_tc_launch(qkv, out, lse, klen, keep, p_drop, B, T, H, scale, st);
     const int D = H * dh, ldk = round_up8(T);
     const size_t es = elem_size(dtype);
     int rc = gemm_qk(qkv, workspace, B, T, H, dh, ldk, scale, dtype, st);
     if (rc) return rc;
     rc = b200asr_softmax_rows(workspace, klen, lse, B, H, T, T, ldk, dtype, stream);
     if (rc) return rc;
+    if (keep) {   // dropout on the probabilities (HF:189-197); the log-sum-exp stays that of the undropped softmax
+        rc = apply_keep(workspace, keep, B, H, T, ldk, p_drop, dtype, st);
+        if (rc) return rc;
+    }
     // out[b, t, h*dh + n] = sum_k P[b,h,t,k] V[b,k,h,n]
     b200asr_gemm_args g = {};
     g.A = workspace;
@@ -174,13 +230,21 @@ int b200asr_mha_fwd(const void* qkv, void* out, float* lse, const int* klen, voi
 }
 
 size_t b200asr_mha_bwd_workspace_bytes(int B, int T, int H, int dh, int dtype) {
-    (void)dh;
-    return 2 * (size_t)B * H * T * round_up8(T) * elem_size(dtype) + 512;
+    const size_t composed = 2 * (size_t)B * H * T * round_up8(T) * elem_size(dtype) + 512;
+    const size_t fused = (dtype == B200ASR_BF16 && dh == 64) ? mha_bwd_tc_workspace_bytes(B, T, H) : 0;
+    return composed > fused ? composed : fused;
 }
 
 int b200asr_mha_bwd(const void* qkv, const void* out, const void* dout, const float* lse, const int* klen, void* dqkv,
                     void* workspace, size_t workspace_bytes, int B, int T, int H, int dh, float scale, int dtype,
                     void* stream) {
+    return b200asr_mha_bwd_dropout(qkv, out, dout, lse, klen, nullptr, 0.f, dqkv, workspace, workspace_bytes, B, T, H, dh,
+                                   scale, dtype, stream);
+}
+
+int b200asr_mha_bwd_dropout(const void* qkv, const void* out, const void* dout, const float* lse, const int* klen,
+                            const unsigned* keep, float p_drop, void* dqkv, void* workspace, size_t workspace_bytes, int B,
+                            int T, int H, int dh, float scale, int dtype, void* stream) {
     (void)out;
     B200_REQUIRE(qkv && dout && lse && dqkv && workspace, "mha_bwd: null pointer");
     B200_REQUIRE(B > 0 && T > 0 && H > 0 && dh > 0 && dh % 8 == 0, "mha_bwd: bad shape");
@@ -188,7 +252,7 @@ int b200asr_mha_bwd(const void* qkv, const void* out, const void* dout, const fl
     cudaStream_t st = as_stream(stream);
     if (g_mha_fused && mha_tc_eligible(dtype, dh, qkv) && ((reinterpret_cast<uintptr_t>(dout) | reinterpret_cast<uintptr_t>(dqkv)) & 15) == 0) {
         B200_REQUIRE(out, "mha_bwd: the fused path needs the forward output");
-        return mha_bwd_tc_launch(qkv, out, dout, lse, klen, dqkv, workspace, B, T, H, scale, st);
+        return mha_bwd_tc_launch(qkv, out, dout, lse, klen, keep, p_drop, dqkv, workspace, B, T, H, scale, st);
     }
     const int D = H * dh, ldk = round_up8(T);
     const size_t es = elem_size(dtype);
@@ -214,6 +278,10 @@ int b200asr_mha_bwd(const void* qkv, const void* out, const void* dout, const fl
     g.sa0 = dh; g.sa1 = sO1; g.sb0 = dh; g.sb1 = sQ1; g.sc0 = sS0; g.sc1 = sS1;
     rc = gemm_dispatch(g, st);
     if (rc) return rc;
+    if (keep) {   // dP = dP_drop o M / (1 - p): the softmax backward below then sees the gradient w.r.t. the undropped P
+        rc = apply_keep(dP, keep, B, H, T, ldk, p_drop, dtype, st);
+        if (rc) return rc;
+    }
     rc = b200asr_softmax_rows_bwd(P, dP, lse, klen, B, H, T, T, ldk, dtype, stream);  // P, dS
     if (rc) return rc;
     // dQ[t, n] = scale * sum_key dS[t, key] K[key, n]
@@ -227,7 +295,11 @@ int b200asr_mha_bwd(const void* qkv, const void* out, const void* dout, const fl
     g.a_kmajor = 0; g.b_kmajor = 0;
     rc = gemm_dispatch(g, st);
     if (rc) return rc;
-    // dV[key, n] = sum_t P[t, key] dO[t, n]
+    // dV[key, n] = sum_t P_drop[t, key] dO[t, n]
+    if (keep) {
+        rc = apply_keep(P, keep, B, H, T, ldk, p_drop, dtype, st);
+        if (rc) return rc;
+    }
     g.A = P; g.B = dout; g.C = dv; g.alpha = 1.f;
     g.ldb = D; g.sb0 = dh; g.sb1 = sO1;
     return gemm_dispatch(g, st);
