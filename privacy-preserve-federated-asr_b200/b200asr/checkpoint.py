@@ -107,17 +107,25 @@ def load_config(directory: str):
         return config_from_dict(json.load(f))
 
 
-def from_pretrained(cls, directory: str, *model_args, config=None, strict: bool = True, device=None, **model_kwargs):
+def from_pretrained(cls, directory: str, *model_args, config=None, strict: bool = False, device=None, **model_kwargs):
     """cls(config, *model_args, **model_kwargs) with the weights of `directory` (the reference's
     `Data2VecAudioForCTC.from_pretrained(path)`; for DacsData2VecAudioForCTC pass `args` as the reference does).
     Keys of the reference's weight-normed positional conv (`weight_g` / `weight_v` or `parametrizations.*`) are
-    accepted either way (modeling._WeightNormConv)."""
+    accepted either way (modeling._WeightNormConv).
+    strict=False (default) is HF's behaviour, which the reference's main flow relies on: `Data2VecAudioForCTC.from_pretrained(
+    pretrain_name, config, args)` opens a plain CTC checkpoint and leaves arbitrator / dementia_head / criterion_similar
+    freshly initialised (federated/src/update.py:228); missing and unexpected keys are reported by a warning.  strict=True
+    raises instead."""
     config = config if config is not None else load_config(directory)
     model = cls(config, *model_args, **model_kwargs)
     sd = load_state_dict_file(directory)
     missing, unexpected = model.load_state_dict(sd, strict=False)
     if strict and (missing or unexpected):
         raise RuntimeError(f"from_pretrained({directory}): missing keys {list(missing)[:5]}..., unexpected {list(unexpected)[:5]}...")
+    if missing or unexpected:
+        import warnings
+        warnings.warn(f"from_pretrained({directory}): newly initialised (not in the checkpoint): {sorted(missing)}; "
+                      f"unused checkpoint keys: {sorted(unexpected)}")
     if device is not None:
         model.to(device)
     return model

@@ -458,14 +458,15 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
          a = O(attention(x));  x1 = LN1(x + drop_h(a));  f = drop_a(gelu(W1 x1));  y = LN2(x1 + drop_h(W2 f)).
     Each dropout is one b200asr_dropout pass fused with the residual add that follows it; masks are re-drawn from
     (seed, site, counter) in the backward pass, never stored.  Dropout on the attention probabilities
-    (attention_dropout) sits inside the fused attention kernel's softmax and is not applied.
-    drop = (p_hidden, p_act, seed, site0, counter): sites site0 .. site0+2."""
+    (attention_dropout, HF:189-197) is applied inside the attention kernels from keep bits drawn ahead of time
+    (site0 + 3, ops.attn_dropout_mask): `keep` int32 bits of this block or None, `p_attn` its probability.
+    drop = (p_hidden, p_act, seed, site0, counter, keep, p_attn): sites site0 .. site0+3."""
 
     @staticmethod
     def forward(ctx, x, klen, meta, cache: ShadowCache, drop, *P):
         (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = P
         B, T, H, eps = meta
-        ph, pa, seed, site, ctr = drop
+        ph, pa, seed, site, ctr, keep, pt = drop
         M, d = x.shape
         dh = d // H
         scale = dh ** -0.5
@@ -473,7 +474,7 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
         bqkv = cache.qkv_bias(q_b, k_b, v_b)
         wo, w1s, w2s = cache.weight(o_w), cache.weight(w1), cache.weight(w2)
         qkv, _ = ops.linear_fwd(x, wqkv, bqkv)
-        attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale)
+        attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale, keep=keep, p_drop=pt)
         o, _ = ops.linear_fwd(attn, wo, o_b)
         # s1 = x + drop_h(o) and LN1 in one pass (b200asr_layernorm_dropout_fwd)
         x1, s1, m1, r1 = ops.layernorm_fwd(o, ln1_w, ln1_b, eps, res=x, want_sum=True, drop=(ph, seed, site, ctr))
@@ -493,7 +494,7 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
         (x, qkv, attn, lse, s1, m1, r1, x1, u, g, s2, m2, r2, wqkv, wo, w1s, w2s) = ctx.saved_tensors
         (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = ctx.params
         B, T, H, dh, scale = ctx.meta
-        ph, pa, seed, site, ctr = ctx.drop
+        ph, pa, seed, site, ctr, keep, pt = ctx.drop
         d = x.shape[1]
         wg = any(ctx.needs_input_grad[5:])  # parameter gradients wanted?
         ds2, dln2w, dln2b, _ = _ln_bwd(dy, s2, ln2_w, ln2_b, m2, r2, wg)
@@ -508,7 +509,7 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
         do, dbo = _dropout_bgrad(o_b, wg, ds1, ph, seed, site, ctr)
         dwo = _wgrad(o_w, wg, do, attn)
         dattn = ops.linear_dgrad(do, wo)
-        dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale)
+        dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale, keep=keep, p_drop=pt)
         dx = ops.linear_dgrad(dqkv, wqkv, residual=ds1) if ctx.needs_input_grad[0] else None
         dqw = dkw = dvw = dqb = dkb = dvb = None
         if wg:
@@ -675,13 +676,13 @@ class EncoderLayerStableFn(torch.autograd.Function):
 class EncoderLayerStableDropoutFn(torch.autograd.Function):
     """EncoderLayerStableFn with the block's element dropouts (Wav2Vec2EncoderLayerStableLayerNorm.forward):
          s1 = x + drop_h(O(attn(LN1(x))));   y = s1 + drop_h(W2 drop_a(gelu(W1 LN2(s1)))).
-    drop = (p_hidden, p_act, seed, site0, counter) as in EncoderLayerDropoutFn; attention_dropout is not applied."""
+    drop = (p_hidden, p_act, seed, site0, counter, keep, p_attn) as in EncoderLayerDropoutFn."""
 
     @staticmethod
     def forward(ctx, x, klen, meta, cache: ShadowCache, drop, *P):
         (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = P
         B, T, H, eps = meta
-        ph, pa, seed, site, ctr = drop
+        ph, pa, seed, site, ctr, keep, pt = drop
         M, d = x.shape
         dh = d // H
         scale = dh ** -0.5
@@ -690,7 +691,7 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
         wo, w1s, w2s = cache.weight(o_w), cache.weight(w1), cache.weight(w2)
         n1, _, m1, r1 = ops.layernorm_fwd(x, ln1_w, ln1_b, eps)
         qkv, _ = ops.linear_fwd(n1, wqkv, bqkv)
-        attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale)
+        attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale, keep=keep, p_drop=pt)
         o, _ = ops.linear_fwd(attn, wo, o_b)
         # s1 = x + drop_h(o) and LN2 in one pass (b200asr_layernorm_dropout_fwd)
         n2, s1, m2, r2 = ops.layernorm_fwd(o, ln2_w, ln2_b, eps, res=x, want_sum=True, drop=(ph, seed, site, ctr))
@@ -710,7 +711,7 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
         (x, m1, r1, n1, qkv, attn, lse, s1, m2, r2, n2, u, g, wqkv, wo, w1s, w2s) = ctx.saved_tensors
         (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = ctx.params
         B, T, H, dh, scale = ctx.meta
-        ph, pa, seed, site, ctr = ctx.drop
+        ph, pa, seed, site, ctr, keep, pt = ctx.drop
         d = x.shape[1]
         wg = any(ctx.needs_input_grad[5:])
         if not dy.is_contiguous():
@@ -726,7 +727,7 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
         do, dbo = _dropout_bgrad(o_b, wg, ds1, ph, seed, site, ctr)
         dwo = _wgrad(o_w, wg, do, attn)
         dattn = ops.linear_dgrad(do, wo)
-        dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale)
+        dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale, keep=keep, p_drop=pt)
         dqw = dkw = dvw = dqb = dkb = dvb = None
         if wg:
             dbqkv = _bgrad((q_b, k_b, v_b), True, dqkv)

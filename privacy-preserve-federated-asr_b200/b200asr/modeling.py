@@ -204,6 +204,9 @@ class Data2VecAudioModel(nn.Module):
         self.dropout_seed = None  # None: torch.initial_seed() at first use (follows torch.manual_seed)
         self.register_buffer("dropout_counter", torch.zeros(1, dtype=torch.int64), persistent=False)
         self._drop_ctr = None
+        self._attn_keep = None            # keep bits of this forward's attention-probability dropout, one row per block
+        self._segment_recorder = None     # set by graph.GraphedTrainStep while it captures an update with LayerDrop
+        self._force_no_layerdrop = False
 
     @property
     def compute_dtype(self):
@@ -214,12 +217,6 @@ class Data2VecAudioModel(nn.Module):
 
     def _check_unsupported(self):
         c = self.config
-        if self.training and not self._warned:
-            if float(_cfg(c, "attention_dropout", 0.0) or 0.0) > 0:
-                warnings.warn("b200asr: attention_dropout (dropout on the softmax probabilities inside the fused "
-                              "attention kernel) is not applied (treated as 0); hidden / activation / feat_proj / "
-                              "final dropout and LayerDrop are applied")
-            self._warned = True
         if self.training and _cfg(c, "mask_time_prob", 0.0) > 0.0 and _cfg(c, "apply_spec_augment", True):
             raise NotImplementedError("SpecAugment (mask_time_prob > 0) is not supported; every reference entry "
                                       "point sets mask_time_prob=0 (finetune_ASRs.py:162-163)")
@@ -239,11 +236,12 @@ class Data2VecAudioModel(nn.Module):
         training and the draw is below config.layerdrop.  Host RNG, no device sync.  Under stream capture the
         outcome would be frozen into the graph, so that combination is refused."""
         p = float(_cfg(self.config, "layerdrop", 0.0) or 0.0)
-        if not self.training or p <= 0.0:
+        if not self.training or p <= 0.0 or self._force_no_layerdrop:
             return ()
         if torch.cuda.is_current_stream_capturing():
-            raise NotImplementedError("LayerDrop draws a fresh coin per block every step; a captured CUDA graph "
-                                      "would replay one outcome: set config.layerdrop = 0 or run eagerly")
+            raise NotImplementedError("LayerDrop draws a fresh coin per block every step; a single captured CUDA graph "
+                                      "would replay one outcome: use graph.GraphedTrainStep (one graph per block, coins "
+                                      "drawn per replay), set config.layerdrop = 0, or run eagerly")
         if self.layerdrop_rng == "torch":
             coins = [float(torch.rand([])) for _ in range(n_layers)]
         elif self.layerdrop_rng == "numpy":
@@ -253,8 +251,8 @@ class Data2VecAudioModel(nn.Module):
             raise ValueError(f"layerdrop_rng must be 'numpy' or 'torch', got {self.layerdrop_rng!r}")
         return tuple(l for l, u in enumerate(coins) if u < p)
 
-    # dropout sites: 0 feat_proj_dropout, 1 encoder prologue (hidden_dropout), 2 final_dropout, 16 + 4 l + {0, 1, 2}
-    # = block l's {attention output, FFN activation, FFN output}
+    # dropout sites: 0 feat_proj_dropout, 1 encoder prologue (hidden_dropout), 2 final_dropout, 16 + 4 l + {0, 1, 2, 3}
+    # = block l's {attention output, FFN activation, FFN output, attention probabilities}
     def _p_drop(self, name):
         return float(_cfg(self.config, name, 0.0) or 0.0) if self.training else 0.0
 
@@ -262,12 +260,27 @@ class Data2VecAudioModel(nn.Module):
         """One counter value per training forward; the clone is what this forward's autograd nodes keep, so a second
         forward before the backward (gradient accumulation) cannot shift the first one's masks."""
         self._drop_ctr = None
-        if self.training and any(self._p_drop(n) > 0 for n in ("hidden_dropout", "activation_dropout",
+        self._attn_keep = None
+        if self.training and any(self._p_drop(n) > 0 for n in ("hidden_dropout", "activation_dropout", "attention_dropout",
                                                                "feat_proj_dropout", "final_dropout")):
             if self.dropout_seed is None:
                 self.dropout_seed = int(torch.initial_seed()) & (2 ** 63 - 1)
             self.dropout_counter.add_(1)
             self._drop_ctr = self.dropout_counter.clone()
+
+    def _draw_attention_keep(self, B, T):
+        """Keep bits of the attention-probability dropout (HF:189-197) for every block of this forward, drawn by ONE
+        launch on the side stream while the conv stack runs (the decisions are data independent); the encoder loop
+        joins the side stream before its first attention.  [n_layers, words] int32, held by the blocks' autograd nodes."""
+        p = self._p_drop("attention_dropout")
+        if p <= 0.0 or self._drop_ctr is None:
+            return
+        n = len(self.encoder.layers)
+        H = int(self.config.num_attention_heads)
+        keep = torch.empty(n, ops.attn_keep_words(B, T, H), dtype=torch.int32, device=self._drop_ctr.device)
+        with ops.on_side_stream(keep, self._drop_ctr, manual_join=True):
+            ops.attn_dropout_mask(n, B, T, H, p, self.dropout_seed, 16 + 3, 4, self._drop_ctr, out=keep)
+        self._attn_keep = keep
 
     def apply_dropout(self, x, name, site):
         """nn.Dropout(config.<name>) at a stand-alone site (training mode only)."""
@@ -282,6 +295,9 @@ class Data2VecAudioModel(nn.Module):
         self._check_unsupported()
         self._begin_dropout_step()
         cache = self.cache
+        if self._drop_ctr is not None and self._p_drop("attention_dropout") > 0:
+            L_in = int(input_values.shape[-1])
+            self._draw_attention_keep(int(input_values.shape[0]), int(conv_out_lengths(c, torch.tensor(L_in))))
         fe = self.feature_extractor.conv_layers
         lns = [getattr(l, "layer_norm", None) for l in fe]
         feats = Fn.feature_extractor_fwd(
@@ -318,21 +334,31 @@ class Data2VecAudioModel(nn.Module):
         meta = (B, T, int(c.num_attention_heads), eps)
         block = Fn.EncoderLayerStableFn if stable else Fn.EncoderLayerFn
         ph, pa = self._p_drop("hidden_dropout"), self._p_drop("activation_dropout")
+        pt = self._p_drop("attention_dropout") if self._attn_keep is not None else 0.0
         drop_block = None
-        if self._drop_ctr is not None and (ph > 0 or pa > 0):
+        if self._drop_ctr is not None and (ph > 0 or pa > 0 or pt > 0):
             drop_block = Fn.EncoderLayerStableDropoutFn if stable else Fn.EncoderLayerDropoutFn
+        if self._attn_keep is not None:
+            ops.join_side_stream()   # the keep bits were drawn on the side stream while the conv stack ran
         skipped = self._layerdrop_coins(len(enc.layers))
         self.last_skipped_layers = skipped
+        rec = self._segment_recorder
         for li, layer in enumerate(enc.layers):
+            if rec is not None:   # graph capture with LayerDrop: one CUDA graph per block (graph.GraphedTrainStep)
+                x = Fn.SegmentMarkFn.apply(x, li, rec)
             if li in skipped:  # a dropped block is the identity and its parameters get no gradient
                 pass
             elif drop_block is not None:
-                x = drop_block.apply(x, klen, meta, cache, (ph, pa, self.dropout_seed, 16 + 4 * li, self._drop_ctr),
+                x = drop_block.apply(x, klen, meta, cache,
+                                     (ph, pa, self.dropout_seed, 16 + 4 * li, self._drop_ctr,
+                                      None if self._attn_keep is None else self._attn_keep[li], pt),
                                      *layer.params())
             else:
                 x = block.apply(x, klen, meta, cache, *layer.params())
             if collected is not None and not (stable and li + 1 == len(enc.layers)):
                 collected.append(x.view(B, T, d))
+        if rec is not None:
+            x = Fn.SegmentMarkFn.apply(x, len(enc.layers), rec)
         if stable:  # Wav2Vec2EncoderStableLayerNorm: one LayerNorm after the last block
             x = Fn.LayerNormFn.apply(x, enc.layer_norm.weight, enc.layer_norm.bias, eps)
             if collected is not None:

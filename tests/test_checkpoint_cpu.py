@@ -81,3 +81,28 @@ def test_config_json_fields(tmp_path):
     assert c.model_type == "data2vec-audio" and c.hidden_size == cfg.hidden_size and list(c.conv_kernel) == list(cfg.conv_kernel)
     with pytest.raises(FileNotFoundError):
         ck.load_state_dict_file(str(tmp_path / "nothing"))
+
+
+def test_plain_ctc_checkpoint_opens_in_the_dacs_class(tmp_path):
+    """The reference's main flow: `Data2VecAudioForCTC.from_pretrained(pretrain_name, config=config, args=args)` on a
+    plain HF CTC checkpoint (federated/src/update.py:228) -- HF initialises the heads the checkpoint lacks (arbitrator,
+    dementia_head, criterion_similar) and reports them; strict=True is the opt-in that raises."""
+    from types import SimpleNamespace
+    cfg = ArchConfig.tiny()
+    hcfg, hcls = hf_config("data2vec", cfg)
+    torch.manual_seed(1)
+    hf = hcls(hcfg).eval()
+    d = str(tmp_path / "ctc")
+    os.makedirs(d)
+    hf.config.save_pretrained(d)
+    torch.save(hf.state_dict(), os.path.join(d, ck.WEIGHTS_NAME))
+    args = SimpleNamespace(LAMBDA=0.5, TOGGLE_RATIO=0, GS_TAU=1, AD_loss="recall", W_LOSS=None, STAGE=2)
+    with pytest.warns(UserWarning, match="newly initialised"):
+        m = M.DacsData2VecAudioForCTC.from_pretrained(d, args, compute_dtype=torch.float32)
+    ref = hf.state_dict()
+    for k, v in m.state_dict().items():
+        if k in ref:
+            assert torch.equal(v, ref[k]), k
+    assert m.arbitrator.weight.shape == (4 * cfg.hidden_size, cfg.hidden_size)
+    with pytest.raises(RuntimeError, match="missing keys"):
+        M.DacsData2VecAudioForCTC.from_pretrained(d, args, compute_dtype=torch.float32, strict=True)
