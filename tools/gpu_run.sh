@@ -1,0 +1,23 @@
+#!/bin/bash
+# One parameterised GPU-box script (replaces the per-round scratch scripts):  tools/gpu_run.sh TAG STAGE [STAGE ...]
+# Stages write their logs to gpurun_out/<TAG>_<stage>.*; every stage runs under its own timeout so that a hung kernel
+# cannot hold the box.
+TAG=$1; shift
+mkdir -p gpurun_out
+for stage in "$@"; do
+  case $stage in
+    newtests)  timeout 900 python -m pytest tests/test_gpu_attn_dropout.py tests/test_gpu_graph_layerdrop.py -q -x -s > gpurun_out/${TAG}_newtests.log 2>&1; echo "newtests rc=$?";;
+    newtests_all)  timeout 1200 python -m pytest tests/test_gpu_attn_dropout.py tests/test_gpu_graph_layerdrop.py -q -s > gpurun_out/${TAG}_newtests.log 2>&1; echo "newtests rc=$?";;
+    large)     timeout 1500 python -m pytest tests/test_gpu_large.py -q -s > gpurun_out/${TAG}_large.log 2>&1; echo "large rc=$?";;
+    alltests)  timeout 2400 python -m pytest tests -m gpu -q -x > gpurun_out/${TAG}_alltests.log 2>&1; echo "alltests rc=$?";;
+    alltests_noexit)  timeout 2400 python -m pytest tests -m gpu -q > gpurun_out/${TAG}_alltests.log 2>&1; echo "alltests rc=$?";;
+    smoke)     timeout 600 python __graft_entry__.py smoke > gpurun_out/${TAG}_smoke.log 2>&1; echo "smoke rc=$?";;
+    bench)     timeout 900 python bench.py --steps 20 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; echo "bench rc=$?";;
+    bench_p0)  timeout 900 python bench.py --steps 20 --warmup 3 --dropout 0 --layerdrop 0 --no-cpu-baseline > gpurun_out/${TAG}_bench_p0.json 2> gpurun_out/${TAG}_bench_p0.err; echo "bench_p0 rc=$?";;
+    bench_ref) timeout 1500 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${TAG}_bench_ref.json 2> gpurun_out/${TAG}_bench_ref.err; echo "bench_ref rc=$?";;
+    opbench)   timeout 900 python tools/op_bench.py > gpurun_out/${TAG}_op_bench.txt 2>&1; echo "opbench rc=$?";;
+    launches)  timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extras > gpurun_out/${TAG}_ncu.log 2>&1; echo "launches rc=$?";;
+    *) echo "unknown stage $stage";;
+  esac
+done
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/${TAG}_smi.txt 2>&1

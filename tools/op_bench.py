@@ -112,6 +112,54 @@ def mha_b():
     return mk
 
 
+def mha_drop(kind, dq_fused=1):
+    """attention with attention_dropout 0.1 keep bits; kind = "fwd" | "bwd" | "mask" (the keep-bit draw for 24 blocks)."""
+    from b200asr._lib import lib
+
+    def mk():
+        if kind == "mask":
+            keep24 = torch.empty(24, ops.attn_keep_words(B, T, H), dtype=torch.int32, device=dev)
+            return lambda: ops.attn_dropout_mask(24, B, T, H, 0.1, 1234, 19, 4, 5, out=keep24)
+        qkv = rnd(M, 3 * D); do = rnd(M, D, scale=0.1)
+        keep = ops.attn_dropout_mask(1, B, T, H, 0.1, 1234, 19, 4, 5)[0]
+        if kind == "fwd":
+            return lambda: ops.mha_fwd(qkv, None, B, T, H, 64, 0.125, keep=keep, p_drop=0.1)
+        out, lse = ops.mha_fwd(qkv, None, B, T, H, 64, 0.125, keep=keep, p_drop=0.1)
+
+        def run():
+            old = lib.b200asr_mha_set_dq_fused(dq_fused)
+            ops.mha_bwd(qkv, out, do, lse, None, B, T, H, 64, 0.125, keep=keep, p_drop=0.1)
+            lib.b200asr_mha_set_dq_fused(old)
+        return run
+    return mk
+
+
+def mha_b_mode(dq_fused):
+    from b200asr._lib import lib
+
+    def mk():
+        qkv = rnd(M, 3 * D); do = rnd(M, D, scale=0.1)
+        out, lse = ops.mha_fwd(qkv, None, B, T, H, 64, 0.125)
+
+        def run():
+            old = lib.b200asr_mha_set_dq_fused(dq_fused)
+            ops.mha_bwd(qkv, out, do, lse, None, B, T, H, 64, 0.125)
+            lib.b200asr_mha_set_dq_fused(old)
+        return run
+    return mk
+
+
+def dacs(kind):
+    def mk():
+        scores = rnd(M, 4 * D); h = rnd(M, D)
+        if kind == "fwd":
+            return lambda: ops.dacs_mask_fwd(scores, h, 1.0, 0.0, seed=1, offset=3)
+        lm, ad, sl, sa, ml, ma = ops.dacs_mask_fwd(scores, h, 1.0, 0.0, seed=1, offset=3)
+        dl, da = rnd(M, D), rnd(M, D)
+        return lambda: ops.dacs_mask_bwd(dl, da, h, sl, sa, ml, ma, 1.0, 0.0, want_dh=False)
+    return mk
+
+
 def ctc():
     def mk():
         logits = rnd(1, B, T, 32)
@@ -168,6 +216,13 @@ bench("dropout [3992,1024]            (x52 when p > 0)", dropout(D, False), nbyt
 bench("dropout [3992,4096] activation (x48 when p > 0)", dropout(F, False), nbytes=2 * M * F * e)
 tot += 24 * bench("mha_fwd  B8 T499 H16 dh64            (x24)", mha_f(), flops=4.0 * B * H * T * T * 64)
 tot += 24 * bench("mha_bwd  B8 T499 H16 dh64 (+dsum,dQ) (x24)", mha_b(), flops=10.0 * B * H * T * T * 64)
+bench("mha_bwd  ... dQ via dS^T + GEMM (deterministic)", mha_b_mode(0), flops=10.0 * B * H * T * T * 64)
+bench("mha_fwd  ... + attention dropout 0.1 keep bits", mha_drop("fwd"), flops=4.0 * B * H * T * T * 64)
+bench("mha_bwd  ... + attention dropout 0.1 keep bits", mha_drop("bwd"), flops=10.0 * B * H * T * T * 64)
+bench("attn keep bits, 24 blocks in one launch (x1)", mha_drop("mask"), nbytes=24 * 4.0 * B * H * 16 * 512, iters=6)
+# DACS toggling network (configs[2]): read scores [M,4d] + h, write 2 masked states + 2 soft + 2 masks = 18 KB / token fwd
+bench("dacs_mask_fwd [3992,1024] in-kernel gumbel (x1)", dacs("fwd"), nbytes=M * D * e * (4 + 1 + 6), iters=10)
+bench("dacs_mask_bwd [3992,1024]                  (x1)", dacs("bwd"), nbytes=M * D * e * (2 + 1 + 4 + 4), iters=10)
 tot += bench("ctc      B8 T499 V32 L<=120 fwd+bwd   (x1)", ctc(), iters=10)
 tot += bench("adamw    309M params (+clip,+shadow)  (x1)", adamw(309_101_600 // 4 * 4), nbytes=309_101_600 * 30.0, iters=6)
 tot += bench("conv0    B8 x 160000 -> [8,31999,512] (x1)", conv0(), nbytes=8 * 160000 * 4 + 8 * 31999 * 512 * e, iters=10)
