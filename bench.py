@@ -4,14 +4,26 @@ CTC client-local update on B200, and the FedAvg round at 1/2/4/8 GPUs (one feder
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
 
-A "step" = one client-local update on one batch of synthetic audio (configs[1]: batch 8 x 10 s at 16 kHz, bf16):
-zero_grad -> forward (frozen conv stack, 24-layer encoder, lm_head, CTC) -> backward -> fused AdamW; with N > 1 every
-step ends with the FedAvg of the trainable parameters across the N clients (NCCL all-reduce over NVLink).
-Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for what every key means.
+A "step" = one client-local update on one batch of synthetic audio (configs[1]: batch 8 x 10 s at 16 kHz, bf16) with the
+reference's real training configuration (Data2VecAudioConfig defaults, which centralized/finetune_ASRs.py:160-164 keeps:
+hidden / activation / attention / final dropout 0.1, layerdrop 0.1): zero_grad -> forward (frozen conv stack, 24-layer
+encoder, lm_head, CTC) -> backward -> fused AdamW; with N > 1 every step ends with the FedAvg of the trainable parameters
+across the N clients.  Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for what every key means.
+
+Legs of the b200 line (all measured in this process, on this box):
+  value / ms_per_step   inputs resident in HBM, CUDA events, max over ranks
+  e2e                   pinned host batch -> device copy and loss read-back inside the timed region
+  roofline              the dominant kernel (tcgen05 GEMM): algorithmic FLOPs / CUDA-event time per launch
+  torch_gpu_baseline    the oracle port (the reference's model restated on stock PyTorch ops) on THIS GPU under bf16
+                        autocast + torch.optim.AdamW(fused=True), same batch, same regularisation: "the real bar"
+  cpu_baseline          the oracle port on the host cores, bounded sample
+  other_configs         C1 greedy inference / C3 DACS stage 2 / C5 wav2vec2-large 16 x 30 s at full size
+`--impl reference` times the reference's CPU path (oracle port, all host cores) at the metric's own configuration.
 """
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import statistics
@@ -32,17 +44,24 @@ METRIC = "train audio-sec/sec (data2vec-large CTC) + FedAvg round s at 1/2/4/8 B
 UNIT = "audio-s/s"
 BATCH, SECONDS, SR = 8, 10, 16000
 WORKLOAD = "data2vec-audio-large CTC fine-tune step, batch 8 x 10 s synthetic 16 kHz audio, bf16 (BASELINE configs[1])"
+N_LAYERS = 24
+COIN_SEED = 20260  # host LayerDrop coins (np.random.uniform, as the pinned transformers 4.17): same stream in every arm
 
 
 def large_config(**kw):
     from types import SimpleNamespace
-    c = dict(vocab_size=32, hidden_size=1024, num_hidden_layers=24, num_attention_heads=16, intermediate_size=4096,
+    c = dict(vocab_size=32, hidden_size=1024, num_hidden_layers=N_LAYERS, num_attention_heads=16, intermediate_size=4096,
              conv_dim=(512,) * 7, conv_kernel=(10, 3, 3, 3, 3, 2, 2), conv_stride=(5, 2, 2, 2, 2, 2, 2), conv_bias=False,
              num_conv_pos_embeddings=5, conv_pos_kernel_size=19, num_conv_pos_embedding_groups=16, layer_norm_eps=1e-5,
              pad_token_id=0, ctc_loss_reduction="sum", ctc_zero_infinity=True, mask_time_prob=0.0,
              feat_extract_norm="layer", do_stable_layer_norm=False)
     c.update(kw)
     return SimpleNamespace(**c)
+
+
+def regularisation(pd: float, ld: float) -> dict:
+    return dict(hidden_dropout=pd, activation_dropout=pd, attention_dropout=pd, final_dropout=pd, feat_proj_dropout=0.0,
+                layerdrop=ld)
 
 
 def synth_batch(batch, samples, seed, frames, pin=True):
@@ -110,52 +129,171 @@ def measured_peaks():
         return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
-# ======================================================================================= CPU reference arm
-def cpu_reference_step_time(steps, warmup, seconds=2.0, batch=1):
-    """The reference's CPU path for this metric: the oracle port (oracle/data2vec_ref.py, a restatement of
-    HF Data2VecAudioForCTC + F.ctc_loss as the reference runs them) doing forward + backward + AdamW in fp32 on all
-    host cores, on a BOUNDED sample of the workload (full-size model, `batch` x `seconds` s of audio)."""
+def coin_stream(steps, p, seed=COIN_SEED):
+    """Per step, the blocks LayerDrop skips (HF:392-404: one uniform per block per step, skipped below p)."""
+    import numpy as np
+    rs = np.random.RandomState(seed)
+    return [tuple(l for l in range(N_LAYERS) if rs.uniform(0, 1) < p) if p > 0 else () for _ in range(steps)]
+
+
+# ======================================================================================= the oracle port as a baseline
+def oracle_step_time(device, batch, seconds, steps, warmup, pd, ld, autocast):
+    """forward + backward + clip + AdamW of the full-size model through the oracle port (oracle/data2vec_ref.py: the HF
+    Data2VecAudioForCTC arithmetic on stock torch ops).  CPU: fp32 on all host cores.  cuda: bf16 autocast, fused AdamW,
+    CUDA-event timing.  Same regularisation as the product arm: torch dropout at the HF sites, LayerDrop coins."""
+    import torch.nn.functional as F
     from oracle import data2vec_ref as R
-    torch.set_num_threads(os.cpu_count() or 1)
     cfg = R.ArchConfig()
     sd = R.init_state_dict(cfg, seed=0, dacs=False)
-    params = {k: v.requires_grad_(not k.startswith("data2vec_audio.feature_extractor")) for k, v in sd.items()}
-    opt = torch.optim.AdamW([p for p in params.values() if p.requires_grad], lr=1e-5, weight_decay=0.005)
+    params = {k: v.to(device).requires_grad_(not k.startswith("data2vec_audio.feature_extractor")) for k, v in sd.items()}
+    train = [p for p in params.values() if p.requires_grad]
+    opt = torch.optim.AdamW(train, lr=1e-5, weight_decay=0.005, fused=(device != "cpu"))
     samples = int(seconds * SR)
-    b = R.synth_batch(cfg, batch, samples, seed=1234, ragged=False, max_label=120)
+    frames = int(R.conv_out_lengths(cfg, torch.tensor([samples]))[0])
+    hb = synth_batch(batch, samples, 1234, frames, pin=False)
+    x, am, lab = hb["input_values"].to(device), hb["attention_mask"].long().to(device), hb["labels"].to(device)
+    coins = coin_stream(warmup + steps, ld)
+    drop = (lambda site, t: F.dropout(t, pd)) if pd > 0 else (lambda site, t: t)
     times = []
     for i in range(warmup + steps):
-        t0 = time.perf_counter()
+        if device == "cpu":
+            t0 = time.perf_counter()
+        else:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
         opt.zero_grad(set_to_none=True)
-        loss, _ = R.ctc_forward(params, cfg, b["input_values"], b["attention_mask"], b["labels"])
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+            loss, _ = R.ctc_forward(params, cfg, x, am, lab, skip_layers=set(coins[i]), drop=drop)
         loss.backward()
-        torch.nn.utils.clip_grad_norm_([p for p in params.values() if p.requires_grad], 1.0)
+        torch.nn.utils.clip_grad_norm_(train, 1.0)
         opt.step()
+        if device == "cpu":
+            dt = time.perf_counter() - t0
+        else:
+            e1.record()
+            torch.cuda.synchronize()
+            dt = e0.elapsed_time(e1) * 1e-3
         if i >= warmup:
-            times.append(time.perf_counter() - t0)
+            times.append(dt)
     t = statistics.median(times)
-    return dict(value=batch * seconds / t, unit=UNIT, cores=os.cpu_count() or 1, kind="port",
-                sample=f"full-size model, batch {batch} x {seconds:g} s, fp32 fwd+bwd+AdamW, median of {steps} step(s), "
-                       f"{t:.2f} s/step", ms_per_step=t * 1e3)
+    return dict(value=batch * seconds / t, ms_per_step=t * 1e3, last_loss=float(loss.detach()), steps=steps, warmup=warmup)
+
+
+def cpu_reference(steps, warmup, batch, seconds, pd, ld):
+    torch.set_num_threads(os.cpu_count() or 1)
+    r = oracle_step_time("cpu", batch, seconds, steps, warmup, 0.0, ld, autocast=False)
+    r.update(unit=UNIT, cores=os.cpu_count() or 1, kind="port",
+             sample=f"full-size model, batch {batch} x {seconds:g} s, fp32 fwd+bwd+clip+AdamW, layerdrop {ld:g} (same coin stream), "
+                    f"element dropout not applied (cost-neutral on the CPU), {warmup} warm-up + median of {steps} step(s), "
+                    f"{r['ms_per_step'] / 1e3:.2f} s/step")
+    return r
 
 
 def run_reference(args):
+    """The reference arm: the reference's CPU implementation of the path (oracle port -- the reference has no native code
+    and is not a package) on all host cores AT THE METRIC'S CONFIGURATION (batch 8 x 10 s), 1 warm-up +
+    up to 3 timed steps (~0.5 min each on 16 cores)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps, warmup = max(1, min(args.steps, 3)), max(0, min(args.warmup, 1))
-    cb = cpu_reference_step_time(steps, warmup)
+    steps, warmup = max(1, min(args.steps, 3)), 1
+    cb = cpu_reference(steps, warmup, args.ref_batch, args.ref_seconds, args.dropout, args.layerdrop)
+    same = args.ref_batch == BATCH and args.ref_seconds == SECONDS
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
             "warmup": warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample": cb["sample"]},
+            "config": {"workload": WORKLOAD if same else WORKLOAD + f" -- BOUNDED SAMPLE batch {args.ref_batch} x {args.ref_seconds:g} s",
+                       "global_batch": args.ref_batch, "audio_s_per_step": args.ref_batch * args.ref_seconds,
+                       "sample": cb["sample"]},
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
+# ======================================================================================= other configurations (N = 1)
+def other_configs(dev, steps=4, warmup=2):
+    """C1 / C3 / C5 of BASELINE.json at full size, measured by the same process (tools/config_bench.py holds the longer
+    version).  Parity-test cases, not the headline: a few steps each."""
+    from types import SimpleNamespace
+
+    from b200asr import modeling as M
+    from b200asr.graph import GraphedTrainStep
+    from b200asr.optim import FusedAdamW
+    out = {}
+
+    def timed(fn, n, w):
+        for _ in range(w):
+            fn()
+        torch.cuda.synchronize()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(n):
+            fn()
+        t1.record()
+        torch.cuda.synchronize()
+        return t0.elapsed_time(t1) / n
+
+    def batch_of(cfg, B, seconds):
+        frames = int(M.conv_out_lengths(cfg, torch.tensor(seconds * SR)))
+        hb = synth_batch(B, seconds * SR, 1234, frames, pin=False)
+        hb["dementia_labels"] = (torch.rand(B, generator=torch.Generator().manual_seed(1237)) < 0.5).long()
+        return {k: v.to(dev) for k, v in hb.items()}
+
+    torch.manual_seed(0)
+    cfg = large_config()
+    model = M.Data2VecAudioForCTC(cfg, compute_dtype=torch.bfloat16).to(dev).eval()
+    b = batch_of(cfg, 1, 5)
+
+    @torch.no_grad()
+    def infer():
+        o = model(b["input_values"])
+        return model.greedy_decode(o.logits)
+    ms = timed(infer, 4 * steps, warmup)
+    out["C1"] = dict(workload="greedy CTC inference, batch 1 x 5 s (forward + argmax / collapse on device, id lists on host)",
+                     ms_per_step=ms, audio_s_per_s=5.0 / (ms * 1e-3))
+    del model
+
+    cfg = large_config(**regularisation(0.1, 0.0))
+    args = SimpleNamespace(LAMBDA=0.5, TOGGLE_RATIO=0, GS_TAU=1, AD_loss="recall", W_LOSS=None, STAGE=2)
+    model = M.DacsData2VecAudioForCTC(cfg, args, compute_dtype=torch.bfloat16)
+    model.validate_labels = False
+    model.to(dev).train()
+    b = batch_of(cfg, 8, 10)
+    opt = FusedAdamW(model.named_parameters(), lr=1e-5, weight_decay=0.005, max_grad_norm=1.0)
+    gstep = GraphedTrainStep(model, opt, b, max_label_len=120)
+    ms = timed(lambda: gstep(b), 2 * steps, warmup)
+    out["C3"] = dict(workload="DACS stage-2 step (gumbel_softmax GS_TAU=1, GRL AD head, 2 x CTC, CosFace), batch 8 x 10 s, frozen "
+                              "encoder forward in training mode (dropouts 0.1 incl. attention) + arbitrator update, one CUDA graph",
+                     ms_per_step=ms, audio_s_per_s=80.0 / (ms * 1e-3))
+    del model, opt, gstep
+    torch.cuda.empty_cache()
+
+    cfg = large_config(feat_extract_norm="layer", conv_bias=True, do_stable_layer_norm=True, num_conv_pos_embeddings=128,
+                       **regularisation(0.1, 0.0))
+    model = M.Wav2Vec2ForCTC(cfg, compute_dtype=torch.bfloat16)
+    model.freeze_feature_encoder()
+    model.validate_labels = False
+    model.to(dev).train()
+    b = batch_of(cfg, 16, 30)
+    b.pop("dementia_labels")
+    opt = FusedAdamW(model.named_parameters(), lr=1e-5, weight_decay=0.005, max_grad_norm=1.0)
+
+    def step():
+        opt.zero_grad()
+        model(**b).loss.backward()
+        opt.step()
+    ms = timed(step, steps, warmup)
+    out["C5"] = dict(workload="wav2vec2-large-960h-lv60 architecture CTC step, batch 16 x 30 s (T = 1499), dropouts 0.1 incl. attention, "
+                              "eager launches", ms_per_step=ms, audio_s_per_s=480.0 / (ms * 1e-3),
+                     peak_mem_gb=torch.cuda.max_memory_allocated() / 2 ** 30)
+    del model, opt
+    torch.cuda.empty_cache()
+    return out
+
+
 # ======================================================================================= B200 arm
 def run_b200(args):
+    import numpy as np
     import torch.distributed as dist
 
     from b200asr import _lib, modeling as M, ops
@@ -172,9 +310,8 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    pd = float(args.dropout)
-    cfg = large_config(hidden_dropout=pd, activation_dropout=pd, final_dropout=pd, feat_proj_dropout=0.0,
-                       attention_dropout=0.0, layerdrop=0.0)
+    pd, ld = float(args.dropout), float(args.layerdrop)
+    cfg = large_config(**regularisation(pd, ld))
     torch.manual_seed(0)  # identical initial weights on every client
     model = M.Data2VecAudioForCTC(cfg, compute_dtype=torch.bfloat16)
     model.freeze_feature_encoder()
@@ -190,6 +327,7 @@ def run_b200(args):
     # a few distinct host batches per client (seed offset by rank: every client has its own shard)
     host = [synth_batch(BATCH, samples, 1234 + 100 * rank + i, frames) for i in range(4)]
     resident = [{k: v.to(dev) for k, v in hb.items()} for hb in host]
+    np.random.seed(COIN_SEED + rank)   # LayerDrop coins of this client
 
     def eager_step(batch):
         opt.zero_grad()
@@ -198,14 +336,20 @@ def run_b200(args):
         opt.step()
         return out.loss
 
-    # the call a user makes: the whole update captured once as a CUDA graph, replayed per batch (b200asr/graph.py)
+    # the call a user makes: the whole update captured once as CUDA graphs, replayed per batch (b200asr/graph.py)
     graphed = None
     if not args.eager:
         from b200asr.graph import GraphedTrainStep
         graphed = GraphedTrainStep(model, opt, resident[0], max_label_len=120)
+    skipped_blocks = [0]
 
     def local_step(batch):
-        return graphed(batch) if graphed is not None else eager_step(batch)
+        if graphed is None:
+            loss = eager_step(batch)
+        else:
+            loss = graphed(batch)
+        skipped_blocks[0] += len(model.backbone.last_skipped_layers)
+        return loss
 
     def fedavg_nccl():
         for g in opt.groups:
@@ -233,6 +377,8 @@ def run_b200(args):
         barrier()
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         agg = []
+        launches = 0
+        skipped_blocks[0] = 0
         t0.record()
         last = None
         main = torch.cuda.current_stream()
@@ -256,6 +402,8 @@ def run_b200(args):
             else:
                 batch = resident[i % len(resident)]
             loss = local_step(batch)
+            if graphed is not None:
+                launches += graphed.launches_last_replay if graphed.segmented else graphed.launches_per_replay
             if world > 1:
                 a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a0.record(); fedavg(); a1.record()
@@ -266,12 +414,14 @@ def run_b200(args):
                 last = float(loss)  # device -> host read of the step's result
         t1.record()
         barrier()
+        if peer_agg is not None:
+            peer_agg.check()   # a barrier that timed out inside the timed region voids the round: raise, do not report
         ms = torch.tensor([t0.elapsed_time(t1)], device=dev)
         agg_ms = torch.tensor([sum(a.elapsed_time(b) for a, b in agg) / max(1, len(agg))], device=dev)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
             dist.all_reduce(agg_ms, op=dist.ReduceOp.MAX)
-        return float(ms) / nsteps, float(agg_ms), last
+        return float(ms) / nsteps, float(agg_ms), last, launches, skipped_blocks[0]
 
     def time_alone(fn, iters=5):
         barrier()
@@ -299,14 +449,12 @@ def run_b200(args):
                 chosen["impl"] = "peer" if agg_alone["peer_kernel_ms"] <= agg_alone["nccl_allreduce_ms"] else "nccl"
     clocks = ClockSampler(local_rank) if rank == 0 else None
     n0 = _lib.launch_count()
-    ms_step, agg_ms, _ = timed(args.steps, e2e=False)
-    launches = (_lib.launch_count() - n0) // args.steps
-    if graphed is not None:  # replays launch the captured kernels without passing through the host wrappers
-        launches = graphed.launches_per_replay
+    ms_step, agg_ms, _, launches, skipped = timed(args.steps, e2e=False)
+    if graphed is None:
+        launches = _lib.launch_count() - n0
     clk = clocks.stop() if clocks else None
-    ms_e2e, _, last_loss = timed(args.steps, e2e=True)
+    ms_e2e, _, last_loss, _, skipped_e2e = timed(args.steps, e2e=True)
 
-    # ---- the other FedAvg implementation, timed alone on identical buffers (every rank holds the same average by now)
     # ---- host enqueue time of one step (no synchronisation inside: pure Python + launch cost; the GPU queue holds a step)
     torch.cuda.synchronize()
     h0 = time.perf_counter()
@@ -333,33 +481,42 @@ def run_b200(args):
     gm = kinds.get("gemm", [0, 1e-9, 0.0])
     achieved = gm[2] / (gm[1] * 1e-3) / 1e12
     peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1400.0)))
-    traffic = None
-    try:  # per-launch DRAM traffic of this kernel from the committed ncu capture of this same command (profiles/)
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_gemm_traffic_v16.json")))["dram_bytes_per_launch"]
+    # per-launch DRAM traffic of this kernel: ncu capture of THIS build (the JSON records the sha of the GEMM source it was
+    # taken from; a capture of another build is not reported)
+    traffic, traffic_src = None, "no ncu capture of this build (profiles/r02_ncu_gemm_traffic.json absent or from another source sha)"
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_gemm_traffic.json")))
+        sha = hashlib.sha256(open(os.path.join(PKG, "csrc", "gemm_tcgen05.cu"), "rb").read()).hexdigest()[:16]
+        if tj.get("gemm_source_sha16") == sha:
+            traffic = tj["dram_bytes_per_launch"]
+            traffic_src = ("profiles/r02_ncu_gemm_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, mean over one "
+                           f"step's launches, GEMM source sha {sha})")
     except Exception:
         pass
     roofline = {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05 bf16 GEMM: QKV/O/FFN linears fwd+dgrad+wgrad, conv layers 1-6)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "profiles/r01_ncu_gemm_traffic_v16.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, mean over one step's launches)",
+                "traffic_source": traffic_src,
                 "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({src})", "launches": gm[0],
-                "avg_launch_us": gm[1] * 1e3 / max(1, gm[0]), "share_of_step": gm[1] / ms_step,
+                "avg_launch_us": gm[1] * 1e3 / max(1, gm[0]),
                 "other": {k: {"launches": v[0], "ms": v[1], "tflops": v[2] / (v[1] * 1e-3) / 1e12} for k, v in kinds.items()
                           if k != "gemm"}}
 
     if rank == 0:
         audio_s = BATCH * SECONDS * world
-        cb = cpu_reference_step_time(steps=1, warmup=0) if world == 1 and not args.no_cpu_baseline else None
-        algo_tflop = 8.376  # conv + 3 x rest, B=8 x 10 s, frozen conv stack, no recompute
+        # algorithmic work: 8.376 TFLOP with all 24 blocks; a block = 3 x its forward linears + 3.5 x attention
+        blk = (3 * 2 * frames * BATCH * (4 * 1024 ** 2 + 2 * 1024 * 4096) + 3.5 * 4 * BATCH * 16 * frames ** 2 * 64) * 1e-12
+        frac_run = 1.0 - skipped / (args.steps * N_LAYERS)
+        algo_tflop = 8.376 - N_LAYERS * blk * (1.0 - frac_run)
         line = {
             "metric": METRIC, "value": audio_s / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
             "config": {"workload": WORKLOAD, "global_batch": BATCH * world, "audio_s_per_step": audio_s,
                        "clients": world, "trainable_params": n_train, "frames_per_utt": frames,
-                       "regularisation": (f"hidden / activation / final dropout {pd:g} applied in the timed step (masks drawn "
-                                          "in-kernel, fresh per CUDA-graph replay); " if pd > 0 else "element dropout 0; ")
-                                         + "attention-probability dropout not applied; layerdrop 0 = all 24 blocks run "
-                                           "every step (the reference default 0.1 would skip 10% of them)",
+                       "regularisation": (f"the reference's training configuration (Data2VecAudioConfig defaults kept by finetune_ASRs.py:160-164): "
+                                          f"hidden / activation / attention / final dropout {pd:g} (masks drawn on the device, fresh per "
+                                          f"replay), feat_proj_dropout 0, layerdrop {ld:g} (host coin per block per step: "
+                                          f"{skipped} of {args.steps * N_LAYERS} blocks skipped in the timed steps)"),
                        "l2_policy": "inputs+weights+saved activations per step (>3 GB) exceed the 126 MB L2; no flush",
                        "e2e_input_pipeline": "each step's pinned-host -> device copy runs on a copy stream, issued while the previous step computes; the loss is read back every step",
                        "fedavg_impl": chosen["impl"] if world > 1 else None,
@@ -369,13 +526,15 @@ def run_b200(args):
                                  if world > 1 else "n/a at 1 GPU"},
             "e2e": {"value": audio_s / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": sum(v.numel() * v.element_size() for v in host[0].values()),
-                    "d2h_bytes_per_step": 4, "last_loss": last_loss},
-            "gpu_launches": int(launches) * args.steps,
-            "gpu_launches_per_step": int(launches),
+                    "d2h_bytes_per_step": 4, "last_loss": last_loss, "blocks_skipped": skipped_e2e},
+            "gpu_launches": int(launches),
+            "gpu_launches_per_step": int(launches) / args.steps,
             "host_enqueue_ms_per_step": host_ms, "host_enqueue_ms_per_step_eager": host_eager_ms,
-            "step_mode": "cuda_graph" if graphed is not None else "eager",
+            "step_mode": ("cuda_graph" + (" (one graph per block and direction: LayerDrop)" if graphed.segmented else ""))
+                         if graphed is not None else "eager",
             "step_tflops": algo_tflop * world / (ms_step * 1e-3),
             "step_frac_of_tensor_peak": algo_tflop / (ms_step * 1e-3) / peak,
+            "algorithmic_tflop_per_step": algo_tflop,
             "fedavg_round_s": ms_step * 1e-3, "fedavg_agg_ms": agg_ms if world > 1 else None,
             "fedavg_agg_alone": agg_alone or None,  # each implementation timed back to back without the local step
             # per GPU and direction: its own remote reads + the peers' writes into it = 2 * 4P (N-1)/N bytes
@@ -384,7 +543,28 @@ def run_b200(args):
             "fedavg_bytes_per_client": 4 * n_train,
             "clocks": clk, "roofline": roofline,
         }
-        if cb is not None:
+        if world == 1 and not args.no_extras:
+            del graphed
+            model.to("cpu")
+            torch.cuda.empty_cache()
+            # "the real bar" (BASELINE.md 3): the same model through stock PyTorch kernels on this GPU
+            try:
+                tb = oracle_step_time("cuda", BATCH, SECONDS, steps=6, warmup=2, pd=pd, ld=ld, autocast=True)
+                line["torch_gpu_baseline"] = dict(
+                    value=tb["value"], unit=UNIT, ms_per_step=tb["ms_per_step"], ratio=tb["ms_per_step"] / ms_step,
+                    what=("oracle port (HF Data2VecAudioForCTC arithmetic on stock torch ops: cuDNN conv, cuBLAS, eager softmax "
+                          "attention, F.ctc_loss) under torch.autocast(bfloat16) + clip_grad_norm_ + torch.optim.AdamW(fused=True), same "
+                          "batch 8 x 10 s, same dropouts and LayerDrop coin stream, CUDA events, 2 warm-up + median of 6 steps"),
+                    last_loss=tb["last_loss"])
+            except Exception as e:  # the baseline leg must never take the product's number down with it
+                line["torch_gpu_baseline"] = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
+            torch.cuda.empty_cache()
+            try:
+                line["other_configs"] = other_configs(dev)
+            except Exception as e:
+                line["other_configs"] = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
+        if world == 1 and not args.no_cpu_baseline:
+            cb = cpu_reference(steps=2, warmup=1, batch=2, seconds=SECONDS, pd=pd, ld=ld)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
         print(json.dumps(line))
     if world > 1:
@@ -394,15 +574,19 @@ def run_b200(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the torch_gpu_baseline and other_configs legs (profiling runs)")
     ap.add_argument("--fedavg", default="auto", choices=["auto", "peer", "nccl"],
                     help="N>1 aggregation: fused peer-memory kernel, scale kernel + NCCL all-reduce, or whichever measures faster in warm-up")
     ap.add_argument("--dropout", type=float, default=0.1,
-                    help="hidden_dropout = activation_dropout = final_dropout = P in the timed training step "
-                         "(0.1 = the Data2VecAudioConfig defaults the reference fine-tunes with; 0 = the parity setting)")
+                    help="hidden = activation = attention = final dropout P in the timed training step (0.1 = the "
+                         "Data2VecAudioConfig defaults the reference fine-tunes with; 0 = the parity setting)")
+    ap.add_argument("--layerdrop", type=float, default=0.1, help="LayerDrop probability (0.1 = the reference's default)")
+    ap.add_argument("--ref-batch", type=int, default=BATCH, help="--impl reference: utterances per step (8 = the metric's config)")
+    ap.add_argument("--ref-seconds", type=float, default=SECONDS)
     ap.add_argument("--eager", action="store_true", help="issue every launch from Python instead of replaying the CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -42,14 +42,20 @@ class _SegmentRecorder:
         self.fwd_x: Dict[int, torch.Tensor] = {}   # tensor at mark l (block l's input = block l-1's output)
         self.bwd_g: Dict[int, torch.Tensor] = {}   # gradient seen at mark l (d loss / d block l's input)
         self.cur: Optional[torch.cuda.CUDAGraph] = None
+        self.launches: List[int] = []              # library kernels captured per graph
+        self._n0 = 0
 
     def begin(self):
+        from . import _lib
+        self._n0 = _lib.launch_count()
         self.cur = torch.cuda.CUDAGraph()
         self.cur.capture_begin(pool=self.pool, capture_error_mode="relaxed")
 
     def end(self):
         ops.join_side_stream()
         self.cur.capture_end()
+        from . import _lib
+        self.launches.append(_lib.launch_count() - self._n0)
         self.graphs.append(self.cur)
         self.cur = None
 
@@ -154,6 +160,8 @@ class GraphedTrainStep:
         self.L = L
         self.graphs = rec.graphs
         self.fwd_x, self.bwd_g = rec.fwd_x, rec.bwd_g
+        self.graph_launches = rec.launches
+        self.launches_last_replay = sum(rec.launches)
         # per block: the parameters it owns (idle rows of the AdamW table when skipped) and their slices of the flat gradients
         self.layer_idle, self.layer_grad_slices = [], []
         for l in range(L):
@@ -179,6 +187,8 @@ class GraphedTrainStep:
         idle = [[i for l in skipped for i in self.layer_idle[l][gi]] for gi in range(len(self.opt.groups))]
         self.opt.prepare_hyper(idle)
         g = self.graphs
+        gl = self.graph_launches
+        self.launches_last_replay = sum(gl) - sum(gl[1 + l] + gl[2 + L + (L - 1 - l)] for l in skipped)
         g[0].replay()                                       # conv stack, projection, positional conv
         for l in range(L):
             if l in skipped:
