@@ -48,8 +48,28 @@ class ShadowCache:
             return hit[1]
         with torch.no_grad():
             val = make()
-        self._cache[key] = (ver, val)
+        self._cache[key] = (ver, val, ps, make)
         return val
+
+    def refresh_in_place(self) -> int:
+        """Derived copies of parameters that no FlatParams owns (the frozen conv stack: bf16 / flattened filters) whose
+        source was rewritten through torch (load_state_dict) are recomputed INTO the cached tensors, so that kernels
+        captured in a CUDA graph -- which hold those pointers -- see the new values.  Returns the number refreshed.
+        (Flat-owned parameters are refreshed through FlatParams.sync_params / the in-graph layout kernels.)"""
+        n = 0
+        for key, (ver, val, ps, make) in list(self._cache.items()):
+            if any(hasattr(p, "_b200_flat") for p in ps) or self._ver(ps) == ver:
+                continue
+            with torch.no_grad():
+                new = make()
+            olds = val if isinstance(val, (tuple, list)) else (val,)
+            news = new if isinstance(new, (tuple, list)) else (new,)
+            for o, nw in zip(olds, news):
+                if o.data_ptr() != nw.data_ptr():
+                    o.copy_(nw)
+            self._cache[key] = (self._ver(ps), val, ps, make)
+            n += 1
+        return n
 
     def _cast(self, t: torch.Tensor) -> torch.Tensor:
         t = t.detach()

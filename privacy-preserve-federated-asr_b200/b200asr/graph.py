@@ -215,6 +215,8 @@ class GraphedTrainStep:
                 dst.copy_(src, non_blocking=True)
         for g in self.opt.groups:   # weights replaced through torch since the last step (load_state_dict of the global
             g["fp"].sync_params()   # model at the start of a federated round): the captured kernels read the bf16 shadow
+        if self.backbone is not None:
+            self.backbone.cache.refresh_in_place()   # ... and the cached copies of the frozen conv stack's filters
         if self.segmented:
             self._replay_segmented()
         else:
