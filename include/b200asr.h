@@ -177,10 +177,13 @@ size_t b200asr_mha_bwd_workspace_bytes(int B, int T, int H, int dh, int dtype);
 int b200asr_mha_bwd(const void* qkv, const void* out, const void* dout, const float* lse, const int* klen,
                     void* dqkv, void* workspace, size_t workspace_bytes, int B, int T, int H, int dh, float scale,
                     int dtype, void* stream);
-/* Where dQ of the fused backward is formed.  1 (default): inside the backward kernel -- dQ_i += dS_i K_j is a fifth MMA of
- * the query-block loop, the partial tiles are added into an fp32 accumulator with bulk reduce-add and converted once; no
- * dS^T round trip through HBM.  The key blocks of a head add in arrival order: reproducible to fp32 rounding, not bit for bit.
- * 0: the kernel stores dS^T and dQ = dS K is a batched GEMM (fixed summation order, bit-reproducible).  Returns the old setting. */
+/* Where dQ of the fused backward is formed.  0 (default): the kernel stores dS^T (one TMA store per query block; the tile
+ * stays L2-resident) and dQ = dS K is a batched GEMM -- fixed summation order, bit-reproducible, and the faster of the two
+ * on B200 (72 vs 85 us per layer at B=8 x 10 s: the fp32 reduce-adds of the alternative are bound by the L2 atomic rate).
+ * 1: inside the backward kernel -- dQ_i += dS_i K_j is a fifth MMA of the query-block loop, the partial tiles are added
+ * into an fp32 accumulator with bulk reduce-add (cp.reduce.async.bulk .add.f32) and converted once; no dS^T round trip
+ * through HBM; the key blocks of a head add in arrival order: reproducible to fp32 rounding, not bit for bit.
+ * 2: measurement hook (as 1 without the reduce-adds: dQ is wrong).  Returns the old setting. */
 int b200asr_mha_set_dq_fused(int on);
 
 /* Attention-probability dropout: `nn.functional.dropout(attn_weights, p=config.attention_dropout)` between the softmax and

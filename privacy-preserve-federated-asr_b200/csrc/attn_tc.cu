@@ -366,6 +366,7 @@ struct BwdParams {
     const uint32_t* keep;   // attention-probability dropout keep bits (see FwdParams) or unused
     int KW, TQ;
     float inv_keep;
+    int skip_reduce;        // measurement hook (b200asr_mha_set_dq_fused(2)): run the fused-dQ kernel without its reduce-adds
     unsigned long long* trace;   // diagnostics (b200asr_attn_set_trace): 24 time stamps per CTA, null in normal use
 };
 
@@ -625,7 +626,7 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
             }
             fence_proxy_async();
             named_bar_sync(2, 64);
-            if (issuer) {
+            if (issuer && !p.skip_reduce) {
                 const int rows = min(BQ, T - i * BQ);
                 bulk_reduce_add_f32(p.dq_acc + (bh * T + (long long)i * BQ) * DH, sDQS, (uint32_t)rows * DH * 4u);
                 bulk_commit_group();
@@ -856,7 +857,9 @@ static int make_head_map(CUtensorMap* map, const void* base, int T, int H, int B
     return encode_map_bf16_4d(map, base, dims, strides, box, what);
 }
 
-static int g_dq_fused = 1;   // b200asr_mha_set_dq_fused: 1 = dQ inside the backward kernel (fp32 reduce-add), 0 = dS^T + GEMM
+// b200asr_mha_set_dq_fused: 0 (default) = dS^T + batched GEMM, 1 = dQ inside the backward kernel (fp32 bulk reduce-add),
+// 2 = as 1 with the reduce-adds skipped (wrong dQ; isolates the cost of the reduction in measurements)
+static int g_dq_fused = 0;
 
 template <typename K>
 static int set_max_smem(K kernel, int bytes, const char* what) {
@@ -973,6 +976,7 @@ int mha_bwd_tc_launch(const void* qkv, const void* out, const void* dout, const 
     p.lse = lse; p.dsum = dsum; p.klen = klen; p.dqkv = (__nv_bfloat16*)dqkv; p.dst = dst; p.dq_acc = dq_acc;
     p.B = B; p.T = T; p.H = H; p.ldq = ldq; p.scale = scale; p.scale_log2 = scale * LOG2E;
     p.keep = keep; p.KW = attn_keep_kw(T); p.TQ = attn_keep_tq(T); p.inv_keep = keep ? 1.0f / (1.0f - p_drop) : 1.0f;
+    p.skip_reduce = g_dq_fused == 2;
     p.trace = g_attn_trace;
     dim3 grid(ceil_div(T, BK), H, B);
     const int Tpad = ceil_div(T, BQ) * BQ;
@@ -1022,10 +1026,11 @@ extern "C" int b200asr_attn_set_trace(void* buf) {
     return 0;
 }
 
-// 1 (default): dQ is accumulated inside the fused backward kernel (fp32 reduce-add, reproducible to rounding);
-// 0: the backward stores dS^T and a batched GEMM produces dQ (bit-reproducible).  Returns the previous setting.
+// 0 (default): the backward stores dS^T and a batched GEMM produces dQ (bit-reproducible; measured faster);
+// 1: dQ is accumulated inside the backward kernel (fp32 bulk reduce-add, reproducible to rounding); 2: measurement hook.
+// Returns the previous setting.
 extern "C" int b200asr_mha_set_dq_fused(int on) {
     const int old = b200asr::attn::g_dq_fused;
-    b200asr::attn::g_dq_fused = on ? 1 : 0;
+    b200asr::attn::g_dq_fused = (on < 0 || on > 2) ? 0 : on;
     return old;
 }

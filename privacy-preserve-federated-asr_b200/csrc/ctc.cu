@@ -2,12 +2,12 @@
 // One CTA per (head, utterance).  The frame posteriors of the utterance live in shared memory (T*V*4 bytes);
 // warp 0 runs the alpha recursion while warp 1 runs beta concurrently (one warp per recursion: each lane owns
 // SPL consecutive lattice states, the two neighbour states come from the previous lane by shuffle).
-// The recursions run in the linear domain in BLOCK FLOATING POINT: every lane keeps fp32 mantissas for its states
-// plus one integer exponent (true value = mantissa * 2^E), renormalised every frame by exact power-of-two
-// scalings -- a step is a handful of FADD/FMUL and integer ops, no exp/log on the T-step critical path and no
-// warp-wide reduction, yet the dynamic range is unbounded (a single per-frame scale underflows fp32 on wide lattices:
-// the frontier states of a 241-state lattice sit hundreds of binades below the bulk).  Logs are taken once, in
-// parallel, when all warps combine alpha*beta into the gradient.  Latency-bound (T sequential steps).
+// The recursions run in the linear domain with a SOFTWARE EXPONENT PER STATE: every state is an fp32 mantissa in [1, 2)
+// plus an integer exponent (true value = mantissa * 2^E), renormalised every frame by exact power-of-two scalings -- a
+// step is FADD/FMUL and integer ops, no exp/log on the T-step critical path and no warp-wide reduction, the mantissa
+// keeps 24 bits whatever the magnitude (torch's log-space fp32 recursion loses bits as |log p| grows) and the dynamic range
+// is unbounded.  Logs are taken once, in parallel, when all warps combine alpha*beta into the gradient.
+// Latency-bound (T sequential steps).
 #include "common.cuh"
 
 namespace b200asr {
@@ -22,10 +22,13 @@ __device__ __forceinline__ float pow2i(int d) { return d < -126 ? 0.f : __int_as
 
 // forward (DIR=+1) or backward (DIR=-1) lattice recursion by one warp.
 // state s of lane: s = lane*SPL + i.  ext[s] = blank (s even) or target[(s-1)/2] (s odd).
-// out[t][s] = mantissa, eout[t][lane] = exponent of that lane at frame t.
+// Every state carries its OWN exponent: value = out[t][s] * 2^eout[t][s], mantissa in [1, 2) (or 0 with E_EMPTY).
+// (Round 1 shared one exponent per lane: with peaked posteriors -- emission ratios of 2^-60 per frame -- two states of a
+// lane drift more than the 2^-126 fp32 range apart within a few frames and the smaller one, which may carry the whole
+// posterior mass once multiplied with the opposite recursion, was flushed to zero: wrong gradients at full-size configs.)
 template <int SPL, int DIR>
 __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __restrict__ tgt, int L, int Tb, int blank,
-                             float* __restrict__ out /* [T][Sld] */, int Sld, int* __restrict__ eout /* [T][32] */) {
+                             float* __restrict__ out /* [T][Sld] */, int Sld, int* __restrict__ eout /* [T][Sld] */) {
     const int lane = threadIdx.x & 31;
     const int S = 2 * L + 1;
     int lab[SPL];
@@ -43,90 +46,91 @@ __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __r
         }
     }
     float a[SPL];
-    int E = E_EMPTY;
+    int E[SPL];
+    auto normalise = [](float v, int base, float& m, int& e) {   // v >= 0 -> mantissa in [1, 2) and exponent (base + k)
+        if (v > 0.f) {
+            const int k = ((__float_as_int(v) >> 23) & 0xff) - 127;
+            m = v * pow2i(-k);
+            e = base + k;
+        } else {
+            m = 0.f;
+            e = E_EMPTY;
+        }
+    };
     const int t0 = DIR > 0 ? 0 : Tb - 1;
-    {
-        float m = 0.f;
 #pragma unroll
-        for (int i = 0; i < SPL; ++i) {
-            const int s = lane * SPL + i;
-            bool init;
-            if (DIR > 0) init = (s == 0) || (s == 1 && S > 1);
-            else init = (s == S - 1) || (s == S - 2 && S > 1);
-            a[i] = (init && s < S) ? pr[t0 * V + lab[i]] : 0.f;
-            m = fmaxf(m, a[i]);
+    for (int i = 0; i < SPL; ++i) {
+        const int s = lane * SPL + i;
+        bool init;
+        if (DIR > 0) init = (s == 0) || (s == 1 && S > 1);
+        else init = (s == S - 1) || (s == S - 2 && S > 1);
+        if (init && s < S) {   // pr holds log2-probabilities: mantissa 2^frac in [1, 2), exponent floor(l2)
+            const float l2 = pr[t0 * V + lab[i]];
+            const float fl = fmaxf(floorf(l2), -1.0e8f);   // (-inf logits: probability 0)
+            a[i] = exp2f(l2 - fl);
+            E[i] = a[i] > 0.f ? (int)fl : E_EMPTY;
+        } else {
+            a[i] = 0.f;
+            E[i] = E_EMPTY;
         }
-        if (m > 0.f) {
-            const int k = ((__float_as_int(m) >> 23) & 0xff) - 127;
-            const float sc = pow2i(-k);
-#pragma unroll
-            for (int i = 0; i < SPL; ++i) a[i] *= sc;
-            E = k;
+        if (s < S) {
+            out[(long long)t0 * Sld + s] = a[i];
+            eout[(long long)t0 * Sld + s] = E[i];
         }
-#pragma unroll
-        for (int i = 0; i < SPL; ++i) {
-            const int s = lane * SPL + i;
-            if (s < S) out[(long long)t0 * Sld + s] = a[i];
-        }
-        eout[t0 * 32 + lane] = E;
     }
     for (int step = 1; step < Tb; ++step) {
         const int t = DIR > 0 ? step : Tb - 1 - step;
-        float e[SPL];  // emission probabilities of this frame: independent of the recursion, issued first
+        float e[SPL];  // emission probabilities of this frame (mantissa, exponent): independent of the recursion, issued first
+        int ee[SPL];   // (log2-domain storage: no posterior underflows, whatever the logit range -- as torch's log-space lattice)
 #pragma unroll
-        for (int i = 0; i < SPL; ++i) e[i] = pr[t * V + lab[i]];
-        float n1, n2;  // neighbour lane's two boundary states and its exponent
-        int En;
+        for (int i = 0; i < SPL; ++i) {
+            const float l2 = pr[t * V + lab[i]];
+            const float fl = fmaxf(floorf(l2), -1.0e8f);   // (-inf logits: probability 0)
+            e[i] = exp2f(l2 - fl);
+            ee[i] = (int)fl;
+        }
+        // the neighbour lane's two boundary states
+        float n1, n2;
+        int En1, En2;
         if (DIR > 0) {
             n1 = __shfl_up_sync(0xffffffffu, a[SPL - 1], 1);
             n2 = __shfl_up_sync(0xffffffffu, a[SPL - 2], 1);
-            En = __shfl_up_sync(0xffffffffu, E, 1);
-            if (lane == 0) { n1 = n2 = 0.f; En = E_EMPTY; }
+            En1 = __shfl_up_sync(0xffffffffu, E[SPL - 1], 1);
+            En2 = __shfl_up_sync(0xffffffffu, E[SPL - 2], 1);
+            if (lane == 0) { n1 = n2 = 0.f; En1 = En2 = E_EMPTY; }
         } else {
             n1 = __shfl_down_sync(0xffffffffu, a[0], 1);
             n2 = __shfl_down_sync(0xffffffffu, a[1], 1);
-            En = __shfl_down_sync(0xffffffffu, E, 1);
-            if (lane == 31) { n1 = n2 = 0.f; En = E_EMPTY; }
+            En1 = __shfl_down_sync(0xffffffffu, E[0], 1);
+            En2 = __shfl_down_sync(0xffffffffu, E[1], 1);
+            if (lane == 31) { n1 = n2 = 0.f; En1 = En2 = E_EMPTY; }
         }
-        const int Ec = max(E, En);  // common exponent of this step's operands
-        const float fo = pow2i(E - Ec), fn = pow2i(En - Ec);  // E_EMPTY - Ec underflows to 0 (the values are 0 anyway)
-        n1 *= fn;
-        n2 *= fn;
-        float as[SPL];
+        float ao[SPL];
+        int Eo[SPL];
 #pragma unroll
-        for (int i = 0; i < SPL; ++i) as[i] = a[i] * fo;
-        float m = 0.f;
+        for (int i = 0; i < SPL; ++i) { ao[i] = a[i]; Eo[i] = E[i]; }
 #pragma unroll
         for (int i = 0; i < SPL; ++i) {
-            float p1, p2;
+            float m1, m2;
+            int e1, e2;
             if (DIR > 0) {
-                p1 = (i >= 1) ? as[i - 1] : n1;
-                p2 = (i >= 2) ? as[i - 2] : (i == 1 ? n1 : n2);
-                if (i == 0) { p1 = n1; p2 = n2; }
+                if (i >= 1) { m1 = ao[i - 1]; e1 = Eo[i - 1]; } else { m1 = n1; e1 = En1; }
+                if (i >= 2) { m2 = ao[i - 2]; e2 = Eo[i - 2]; } else if (i == 1) { m2 = n1; e2 = En1; } else { m2 = n2; e2 = En2; }
             } else {
-                p1 = (i + 1 < SPL) ? as[i + 1] : n1;
-                p2 = (i + 2 < SPL) ? as[i + 2] : (i + 2 == SPL ? n1 : n2);
+                if (i + 1 < SPL) { m1 = ao[i + 1]; e1 = Eo[i + 1]; } else { m1 = n1; e1 = En1; }
+                if (i + 2 < SPL) { m2 = ao[i + 2]; e2 = Eo[i + 2]; } else if (i + 2 == SPL) { m2 = n1; e2 = En1; } else { m2 = n2; e2 = En2; }
             }
+            if (!skip[i]) { m2 = 0.f; e2 = E_EMPTY; }
             const int s = lane * SPL + i;
-            const float v = (as[i] + p1 + (skip[i] ? p2 : 0.f)) * e[i];
-            a[i] = (s < S) ? v : 0.f;
-            m = fmaxf(m, a[i]);
+            const int Ec = max(Eo[i], max(e1, e2));   // common exponent of this state's operands
+            // (an empty operand has mantissa 0 and E_EMPTY - Ec underflows to a factor 0; all empty: 0 * 1 = 0)
+            const float v = (ao[i] * pow2i(Eo[i] - Ec) + m1 * pow2i(e1 - Ec) + m2 * pow2i(e2 - Ec)) * e[i];
+            normalise(s < S ? v : 0.f, Ec + ee[i], a[i], E[i]);
+            if (s < S) {
+                out[(long long)t * Sld + s] = a[i];
+                eout[(long long)t * Sld + s] = E[i];
+            }
         }
-        if (m > 0.f) {
-            const int k = ((__float_as_int(m) >> 23) & 0xff) - 127;
-            const float sc = pow2i(-k);
-#pragma unroll
-            for (int i = 0; i < SPL; ++i) a[i] *= sc;
-            E = Ec + k;
-        } else {
-            E = E_EMPTY;
-        }
-#pragma unroll
-        for (int i = 0; i < SPL; ++i) {
-            const int s = lane * SPL + i;
-            if (s < S) out[(long long)t * Sld + s] = a[i];
-        }
-        eout[t * 32 + lane] = E;
     }
 }
 
@@ -170,18 +174,19 @@ __device__ __forceinline__ void frame_softmax(const T* __restrict__ xr, int V, i
     }
     sum = warp_sum(sum);
     const float lz = mx + logf(sum);
+    constexpr float LOG2E_ = 1.4426950408889634f;
     if (cached) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-            if (lane + 32 * k < V) emit(lane + 32 * k, expf(xv[k] - lz));
+            if (lane + 32 * k < V) emit(lane + 32 * k, expf(xv[k] - lz), (xv[k] - lz) * LOG2E_);
     } else {
-        for (int v = lane; v < V; v += 32) emit(v, expf(to_f<T>(xr[v]) - lz));
+        for (int v = lane; v < V; v += 32) emit(v, expf(to_f<T>(xr[v]) - lz), (to_f<T>(xr[v]) - lz) * LOG2E_);
     }
 }
 
-// workspace per (head, utterance), in floats: alpha, beta mantissas [T][Sld], their lane exponents [T][32] int32 each,
+// workspace per (head, utterance), in floats: alpha, beta mantissas [T][Sld], their per-state exponents [T][Sld] int32 each,
 // then 8 floats of scalars (0: the raw negative log-likelihood for the gradient kernel)
-__host__ __device__ inline long long ctc_ws_stride(int T_, int Sld) { return 2LL * T_ * Sld + 2LL * T_ * 32 + 8; }
+__host__ __device__ inline long long ctc_ws_stride(int T_, int Sld) { return 4LL * T_ * Sld + 8; }
 
 // Lattice kernel: one CTA per (head, utterance).  Phase 1: posteriors of the utterance into shared memory (all warps);
 // phase 2: alpha (warp 0) and beta (warp 1) concurrently; then the loss.  The gradient is a separate, frame-parallel
@@ -200,19 +205,19 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     const int L = min(tgt_len[b], max_tgt);
     const int S = 2 * L + 1;
     const int Tb = max(0, min(in_len[b], T_));
-    float* pr = sm;                                  // [T][V] softmax probabilities
+    float* pr = sm;                                  // [T][V] log2 of the softmax probabilities
     int* tgt_s = (int*)(pr + (size_t)T_ * V);        // [max_tgt + 1]
     const long long hb = (long long)head * B + b;
     const T* x = logits + hb * T_ * V;
     float* alpha = ws + hb * ctc_ws_stride(T_, Sld);
     float* beta = alpha + (long long)T_ * Sld;
     int* ea = reinterpret_cast<int*>(beta + (long long)T_ * Sld);
-    int* eb = ea + (long long)T_ * 32;
+    int* eb = ea + (long long)T_ * Sld;
 
     for (int i = threadIdx.x; i < L; i += blockDim.x) tgt_s[i] = targets[tgt_off[b] + i];
     // ---- phase 1: fp32 softmax of the valid frames
     for (int t = warp; t < Tb; t += nwarps)
-        frame_softmax<T>(x + (long long)t * V, V, lane, [&](int v, float pv) { pr[t * V + v] = pv; });
+        frame_softmax<T>(x + (long long)t * V, V, lane, [&](int v, float, float l2v) { pr[t * V + v] = l2v; });
     __syncthreads();
     // ---- phase 2: alpha (warp 0) and beta (warp 1) concurrently
     if (Tb > 0) {
@@ -227,9 +232,9 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     if (Tb > 0) {
         const long long r = (long long)(Tb - 1);
         const float a1 = alpha[r * Sld + S - 1];
-        const int e1 = ea[r * 32 + (S - 1) / spl];
+        const int e1 = ea[r * Sld + S - 1];
         const float a2 = S > 1 ? alpha[r * Sld + S - 2] : 0.f;
-        const int e2 = S > 1 ? ea[r * 32 + (S - 2) / spl] : E_EMPTY;
+        const int e2 = S > 1 ? ea[r * Sld + S - 2] : E_EMPTY;
         const int em = max(e1, e2);
         const float tot = a1 * pow2i(e1 - em) + a2 * pow2i(e2 - em);
         if (tot > 0.f) nll = -(logf(tot) + (float)em * LN2);
@@ -238,7 +243,7 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     const bool infeasible = !(nll < INFINITY);
     if (threadIdx.x == 0) {
         loss[hb] = (infeasible && zero_infinity) ? 0.f : nll;
-        reinterpret_cast<float*>(eb + (long long)T_ * 32)[0] = nll;   // raw value for the gradient kernel
+        reinterpret_cast<float*>(eb + (long long)T_ * Sld)[0] = nll;   // raw value for the gradient kernel
     }
 }
 
@@ -252,7 +257,7 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const T* __restrict__ log
                                                        T* __restrict__ grad, const float* __restrict__ ws, int n_heads,
                                                        int B, int T_, int V, int max_tgt, int blank, int zero_infinity,
                                                        int spl) {
-    extern __shared__ unsigned long long acc_all[];   // [8 warps][V] occupancy sums + [8][V] floats of posteriors
+    extern __shared__ unsigned long long acc_all[];   // [8 warps][V] occupancy sums + [8][2][V] floats: posteriors and their log2
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long long frame = (long long)blockIdx.x * 8 + warp;
     if (frame >= (long long)n_heads * B * T_) return;
@@ -266,8 +271,8 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const T* __restrict__ log
     const float* alpha = ws + hb * ctc_ws_stride(T_, Sld);
     const float* beta = alpha + (long long)T_ * Sld;
     const int* ea = reinterpret_cast<const int*>(beta + (long long)T_ * Sld);
-    const int* eb = ea + (long long)T_ * 32;
-    const float nll = reinterpret_cast<const float*>(eb + (long long)T_ * 32)[0];
+    const int* eb = ea + (long long)T_ * Sld;
+    const float nll = reinterpret_cast<const float*>(eb + (long long)T_ * Sld)[0];
     const bool infeasible = !(nll < INFINITY);
     constexpr float LOG2E = 1.4426950408889634f;
     T* g = grad + hb * T_ * V;
@@ -277,19 +282,20 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const T* __restrict__ log
         return;
     }
     unsigned long long* acc = acc_all + warp * V;
-    float* pr = reinterpret_cast<float*>(acc_all + 8 * V) + warp * V;
+    float* pr = reinterpret_cast<float*>(acc_all + 8 * V) + warp * 2 * V;   // [V] probabilities, [V] their log2
+    float* pl2 = pr + V;
     const int* tgt = targets + tgt_off[b];
     const float gs = grad_scale ? grad_scale[hb] : 1.f;
-    frame_softmax<T>(logits + (hb * T_ + t) * V, V, lane, [&](int v, float pv) { pr[v] = pv; });
+    frame_softmax<T>(logits + (hb * T_ + t) * V, V, lane, [&](int v, float pv, float l2v) { pr[v] = pv; pl2[v] = l2v; });
     const float* ar = alpha + (long long)t * Sld;
     const float* br = beta + (long long)t * Sld;
-    const int* ear = ea + (long long)t * 32;
-    const int* ebr = eb + (long long)t * 32;
+    const int* ear = ea + (long long)t * Sld;
+    const int* ebr = eb + (long long)t * Sld;
     // log2 of alpha_t(s) * beta_t(s): mantissa product + the two lane exponents (the only logs of the kernel)
     float mx = NEG_INF;
     for (int s = lane; s < S; s += 32) {
         const float ab = ar[s] * br[s];
-        if (ab > 0.f) mx = fmaxf(mx, log2f(ab) + (float)(ear[s / spl] + ebr[s / spl]));
+        if (ab > 0.f) mx = fmaxf(mx, log2f(ab) + (float)(ear[s] + ebr[s]));
     }
     mx = warp_max(mx);
     for (int v = lane; v < V; v += 32) acc[v] = 0ull;
@@ -298,18 +304,19 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const T* __restrict__ log
         const float ab = ar[s] * br[s];
         if (ab > 0.f) {
             const int l = (s & 1) ? tgt[(s - 1) >> 1] : blank;
-            const float rel2 = log2f(ab) + (float)(ear[s / spl] + ebr[s / spl]) - mx;  // <= 0
+            const float rel2 = log2f(ab) + (float)(ear[s] + ebr[s]) - mx;  // <= 0
             atomicAdd(&acc[l], (unsigned long long)(exp2f(rel2) * 1099511627776.0f));  // in [0, 2^40]
         }
     }
     __syncwarp();
     // d nll / d logit = softmax - sum_{s: lab = v} alpha_t(s) beta_t(s) / (P p_t(v)),  P = exp(-nll)
     // (ATen ctc_loss backward form)
-    const float fac = exp2f(mx + nll * LOG2E) * (1.0f / 1099511627776.0f);
+    // (combined in the log2 domain: p_t(v) may lie below the fp32 range while the occupancy it divides is of order 1)
+    const float lfac = mx + nll * LOG2E - 40.0f;
     for (int v = lane; v < V; v += 32) {
         const float pv = pr[v];
         const float a = (float)acc[v];
-        const float occ = a > 0.f ? a * fac / fmaxf(pv, 1e-37f) : 0.f;
+        const float occ = a > 0.f ? exp2f(log2f(a) + lfac - pl2[v]) : 0.f;
         g[(long long)t * V + v] = from_f<T>((pv - occ) * gs);
     }
 }
@@ -397,7 +404,7 @@ int b200asr_ctc_fwd_bwd(const void* logits, const int* targets, const int* tgt_o
                                                         zero_infinity, spl);
         if (grad) {
             const long long frames = (long long)n_heads * B * T_;
-            const size_t gsm = (size_t)8 * V * (sizeof(unsigned long long) + sizeof(float));
+            const size_t gsm = (size_t)8 * V * (sizeof(unsigned long long) + 2 * sizeof(float));
             if (gsm > 48 * 1024) {
                 set_error("ctc: vocabulary %d too large for the gradient kernel", V);
                 return B200ASR_ERR_UNSUPPORTED;

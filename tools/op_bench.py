@@ -216,7 +216,8 @@ bench("dropout [3992,1024]            (x52 when p > 0)", dropout(D, False), nbyt
 bench("dropout [3992,4096] activation (x48 when p > 0)", dropout(F, False), nbytes=2 * M * F * e)
 tot += 24 * bench("mha_fwd  B8 T499 H16 dh64            (x24)", mha_f(), flops=4.0 * B * H * T * T * 64)
 tot += 24 * bench("mha_bwd  B8 T499 H16 dh64 (+dsum,dQ) (x24)", mha_b(), flops=10.0 * B * H * T * T * 64)
-bench("mha_bwd  ... dQ via dS^T + GEMM (deterministic)", mha_b_mode(0), flops=10.0 * B * H * T * T * 64)
+bench("mha_bwd  ... dQ in-kernel, fp32 bulk reduce-add", mha_b_mode(1), flops=10.0 * B * H * T * T * 64)
+bench("mha_bwd  ... dQ in-kernel, reduce-adds skipped (hook)", mha_b_mode(2), flops=10.0 * B * H * T * T * 64)
 bench("mha_fwd  ... + attention dropout 0.1 keep bits", mha_drop("fwd"), flops=4.0 * B * H * T * T * 64)
 bench("mha_bwd  ... + attention dropout 0.1 keep bits", mha_drop("bwd"), flops=10.0 * B * H * T * T * 64)
 bench("attn keep bits, 24 blocks in one launch (x1)", mha_drop("mask"), nbytes=24 * 4.0 * B * H * 16 * 512, iters=6)
