@@ -73,3 +73,10 @@ def relinf(a, b):
     a = torch.as_tensor(np.asarray(a) if not torch.is_tensor(a) else a).float().cpu()
     b = torch.as_tensor(np.asarray(b) if not torch.is_tensor(b) else b).float().cpu()
     return float((a - b).abs().max() / max(float(b.abs().max()), 1e-12))
+
+
+def rel2(a, b):
+    """relative L2 (Frobenius) error ||a - b|| / ||b||."""
+    a = torch.as_tensor(np.asarray(a) if not torch.is_tensor(a) else a).double().cpu()
+    b = torch.as_tensor(np.asarray(b) if not torch.is_tensor(b) else b).double().cpu()
+    return float((a - b).norm() / max(float(b.norm()), 1e-30))
