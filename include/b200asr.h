@@ -370,6 +370,15 @@ int b200asr_fedavg_peer_reduce(float* const* peer_bufs, const float* weights, in
 int b200asr_fedavg_peer_reduce_guarded(float* const* peer_bufs, const float* weights, int world, int rank, long long n,
                                        const int* abort_flag, void* stream);
 
+/* NVLS form of the same exchange (uniform weights): `multicast_buf` is the multicast address of the ranks' flat buffers
+ * (one NVSwitch multicast object bound to every rank's allocation, e.g. torch symmetric memory's multicast_ptr).  Rank r
+ * reduces slice r IN THE SWITCH (multimem.ld_reduce.add.v4.f32), divides by `world` and multicasts the result into every
+ * rank's buffer (multimem.st): 4P/N bytes in + 4P/N bytes out per GPU at any N.  Same bracketing barriers as above;
+ * equal to the sequential reference sum to fp32 rounding (the switch fixes the order), not bit for bit.
+ * max_blocks > 0 caps the grid (leaves SMs free for work overlapped with the exchange). */
+int b200asr_fedavg_nvls_reduce(float* multicast_buf, int world, int rank, long long n, const int* abort_flag, int max_blocks,
+                               void* stream);
+
 /* Cross-rank barrier over peer memory for the fused kernel above: every rank passes the HOST array of the `world`
  * ranks' flag buffers (>= world unsigned each, zero-initialised, peer-mapped) and a barrier number `epoch` that grows
  * by one per call on every rank.  Stream-ordered; bounded spin (sets *timeout_flag, a device int, instead of hanging). */

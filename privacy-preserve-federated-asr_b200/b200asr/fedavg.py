@@ -70,8 +70,19 @@ class FlatParams:
             self.offsets.append(off)
             off += (p.numel() + 3) // 4 * 4
         self.numel = off
-        self.peer_buffer = PeerBuffer(off * 4, device) if peer else None
-        self.flat = self.peer_buffer.as_tensor(torch.float32, off) if peer else torch.zeros(off, dtype=torch.float32, device=device)
+        # peer=True: plain cudaMalloc exported through CUDA IPC (PeerFedAvg); peer="symm": torch symmetric memory, whose
+        # allocation can be bound to an NVSwitch multicast object as well (SymmFedAvg: NVLS in-switch reduction)
+        self.peer_buffer = PeerBuffer(off * 4, device) if peer is True else None
+        self.symm = None
+        if peer == "symm":
+            import torch.distributed._symmetric_memory as symm_mem
+            self.symm = symm_mem.empty(off, dtype=torch.float32, device=device)
+            self.symm.zero_()
+            self.flat = self.symm
+        elif peer:
+            self.flat = self.peer_buffer.as_tensor(torch.float32, off)
+        else:
+            self.flat = torch.zeros(off, dtype=torch.float32, device=device)
         self.grad = torch.zeros(off, dtype=torch.float32, device=device)
         self.shadow = torch.zeros(off, dtype=torch.bfloat16, device=device) if with_shadow else None
         self.epoch = 0
@@ -267,6 +278,74 @@ class PeerFedAvg:
         for pb in self._opened:
             pb.close()
         self._opened = []
+
+
+class SymmFedAvg:
+    """Multi-GPU FedAvg over torch symmetric memory (FlatParams(..., peer="symm")): the same flat buffers are reachable
+    both through peer pointers (the fused peer-memory kernel, bit-exact left-to-right sum) and through ONE NVSwitch
+    multicast address (`b200asr_fedavg_nvls_reduce`: the switch sums the ranks' slices and multicasts the average back --
+    4P/N bytes each way per GPU at any N).  torch.distributed only does the rendezvous; every byte of the exchange is moved
+    by our kernels, bracketed by our peer-memory barrier kernel.
+
+      agg = SymmFedAvg([g["fp"] for g in opt.groups]); agg()            # impl="nvls" (default) | "peer"
+    """
+
+    def __init__(self, flats: Sequence["FlatParams"], group=None):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        group = group if group is not None else dist.group.WORLD
+        self.flats = list(flats)
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        dev = self.flats[0].flat.device
+        self.mc_ptrs, self.flat_ptrs, self._handles = [], [], []
+        for fp in self.flats:
+            if fp.symm is None:
+                raise ValueError('SymmFedAvg needs FlatParams(..., peer="symm")')
+            h = symm_mem.rendezvous(fp.symm, group)
+            self._handles.append(h)
+            off = fp.symm.data_ptr() - int(h.buffer_ptrs[self.rank])
+            self.flat_ptrs.append([int(p) + off for p in h.buffer_ptrs])
+            self.mc_ptrs.append(int(h.multicast_ptr) + off if int(h.multicast_ptr) else 0)
+        self._flags = symm_mem.empty(1024, dtype=torch.int32, device=dev)
+        self._flags.zero_()
+        fh = symm_mem.rendezvous(self._flags, group)
+        self._handles.append(fh)
+        foff = self._flags.data_ptr() - int(fh.buffer_ptrs[self.rank])
+        self.flag_ptrs = [int(p) + foff for p in fh.buffer_ptrs]
+        self.timeout = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.has_multicast = all(self.mc_ptrs)
+        self.epoch = 0
+        torch.cuda.synchronize()
+        dist.barrier(group=group)
+
+    def _barrier(self):
+        import ctypes as C
+        from ._lib import check, lib
+        self.epoch += 1
+        ptrs = (C.c_void_p * self.world)(*self.flag_ptrs)
+        check(lib.b200asr_fedavg_peer_barrier(ptrs, self.world, self.rank, self.epoch, self.timeout.data_ptr(),
+                                              torch.cuda.current_stream().cuda_stream), "fedavg_peer_barrier")
+
+    def __call__(self, weights: Optional[Sequence[float]] = None, impl: str = "nvls", max_blocks: int = 0, mark: bool = True):
+        from ._lib import check, lib
+        if impl == "nvls" and (weights is not None or not self.has_multicast):
+            impl = "peer"   # per-client weights need the scale-accumulate form; no multicast object on this fabric
+        self._barrier()   # every client's local update is complete and visible
+        for fp, ptrs, mc in zip(self.flats, self.flat_ptrs, self.mc_ptrs):
+            if impl == "nvls":
+                check(lib.b200asr_fedavg_nvls_reduce(mc, self.world, self.rank, fp.numel, self.timeout.data_ptr(), int(max_blocks),
+                                                     torch.cuda.current_stream().cuda_stream), "fedavg_nvls_reduce")
+            else:
+                ops.fedavg_peer_reduce(ptrs, weights, self.rank, fp.numel, abort_flag=self.timeout)
+        self._barrier()   # every slice has been written back everywhere
+        if mark:
+            for fp in self.flats:
+                fp.mark_updated()
+
+    def check(self):
+        """Host-synchronising: raises if a barrier ever timed out (a peer never arrived)."""
+        if int(self.timeout.item()) != 0:
+            raise RuntimeError("SymmFedAvg: cross-rank barrier timed out")
 
 
 def fedavg_shard_plan(n: int, world: int):

@@ -117,6 +117,43 @@ __global__ void __launch_bounds__(256) fedavg_peer_kernel(const PeerPtrs p, int 
     }
 }
 
+// NVLS variant: the flat buffers of all ranks are bound to ONE multicast object (NVSwitch); rank r owns slice [lo, hi):
+//   multimem.ld_reduce  -- the switch fetches the slice from every GPU and returns the SUM (in-switch reduction)
+//   multimem.st         -- the switch writes the averaged value into every GPU's buffer
+// so each rank moves 4P/N bytes in and 4P/N bytes out over its own links, whatever N is (the peer kernel above moves
+// 4P (N-1)/N each way).  The reduction order inside the switch is fixed by the fabric, not left-to-right: equal to the
+// reference's sequential sum to fp32 rounding (<= 1e-6 relative), not bit for bit -- the peer kernel stays the bit-exact path.
+__global__ void __launch_bounds__(256) fedavg_nvls_kernel(float* __restrict__ mc, int world, long long lo, long long hi,
+                                                          const int* __restrict__ abort_flag) {
+    if (abort_flag && *abort_flag) return;
+    const float kf = (float)world;
+    const long long nvec = (hi - lo) / 4;
+    constexpr int U = 4;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < nvec; i0 += U * stride) {
+        float4 acc[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long i = i0 + u * stride;
+            acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (i < nvec)
+                asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                             : "=f"(acc[u].x), "=f"(acc[u].y), "=f"(acc[u].z), "=f"(acc[u].w)
+                             : "l"(mc + lo + 4 * i) : "memory");
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long i = i0 + u * stride;
+            if (i >= nvec) continue;
+            acc[u].x = __fdiv_rn(acc[u].x, kf); acc[u].y = __fdiv_rn(acc[u].y, kf);
+            acc[u].z = __fdiv_rn(acc[u].z, kf); acc[u].w = __fdiv_rn(acc[u].w, kf);
+            asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                         ::"l"(mc + lo + 4 * i), "f"(acc[u].x), "f"(acc[u].y), "f"(acc[u].z), "f"(acc[u].w) : "memory");
+        }
+    }
+    __threadfence_system();
+}
+
 // Cross-rank barrier over peer memory (one tiny block): thread t publishes `epoch` into peer t's flag slot [rank]
 // (NVLink store, release at system scope) and spins on the local slot [t] until peer t has published the same epoch.
 // Stream order on each rank + this barrier = "every rank's preceding kernels are complete and visible".  The spin is
@@ -371,6 +408,22 @@ int b200asr_fedavg_peer_reduce(float* const* peer_bufs, const float* weights, in
 int b200asr_fedavg_peer_reduce_guarded(float* const* peer_bufs, const float* weights, int world, int rank, long long n,
                                        const int* abort_flag, void* stream) {
     return fedavg_peer_reduce_impl(peer_bufs, weights, world, rank, n, abort_flag, stream);
+}
+
+int b200asr_fedavg_nvls_reduce(float* multicast_buf, int world, int rank, long long n, const int* abort_flag, int max_blocks,
+                               void* stream) {
+    B200_REQUIRE(multicast_buf && ((uintptr_t)multicast_buf & 15) == 0, "fedavg_nvls_reduce: bad multicast pointer");
+    B200_REQUIRE(world >= 1 && world <= FEDAVG_MAX_K && rank >= 0 && rank < world, "fedavg_nvls_reduce: bad world/rank");
+    B200_REQUIRE(n % 4 == 0, "fedavg_nvls_reduce: n must be a multiple of 4 (FlatParams pads every segment)");
+    if (n <= 0) return B200ASR_OK;
+    const long long per = ((n / world) / 4) * 4;
+    const long long lo = per * rank;
+    const long long hi = (rank == world - 1) ? n : per * (rank + 1);
+    if (hi <= lo) return B200ASR_OK;
+    int grid = stream_grid(hi - lo);
+    if (max_blocks > 0 && grid > max_blocks) grid = max_blocks;   // leave SMs to work overlapped with the exchange
+    fedavg_nvls_kernel<<<grid, 256, 0, as_stream(stream)>>>(multicast_buf, world, lo, hi, abort_flag);
+    return check_launch("fedavg_nvls_reduce");
 }
 
 int b200asr_fedavg_peer_barrier(unsigned* const* peer_flags, int world, int rank, unsigned epoch, int* timeout_flag,
