@@ -394,6 +394,10 @@ def run_b200(args):
                 v.record_stream(main)
             return b, ev
 
+        # loss read-back (e2e): every step's loss goes device -> pinned host inside the timed region, asynchronously; the host
+        # looks at it one step later, so that it never stalls the launch of the next step (what a logging training loop does)
+        pinned = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)] if e2e else None
+        pending = None
         nxt = stage(0) if e2e else None
         for i in range(nsteps):
             if e2e:  # the call a user makes: pinned host batch -> device, update, loss read back
@@ -411,7 +415,16 @@ def run_b200(args):
             if e2e:
                 if i + 1 < nsteps:
                     nxt = stage(i + 1)
-                last = float(loss)  # device -> host read of the step's result
+                pinned[i & 1].copy_(loss.detach().reshape(1), non_blocking=True)   # device -> host read of the step's result
+                ev = torch.cuda.Event()
+                ev.record()
+                if pending is not None:
+                    pending[0].synchronize()
+                    last = float(pending[1])
+                pending = (ev, pinned[i & 1])
+        if e2e and pending is not None:
+            pending[0].synchronize()
+            last = float(pending[1])
         t1.record()
         barrier()
         if peer_agg is not None:
@@ -518,7 +531,7 @@ def run_b200(args):
                                           f"replay), feat_proj_dropout 0, layerdrop {ld:g} (host coin per block per step: "
                                           f"{skipped} of {args.steps * N_LAYERS} blocks skipped in the timed steps)"),
                        "l2_policy": "inputs+weights+saved activations per step (>3 GB) exceed the 126 MB L2; no flush",
-                       "e2e_input_pipeline": "each step's pinned-host -> device copy runs on a copy stream, issued while the previous step computes; the loss is read back every step",
+                       "e2e_input_pipeline": "each step's pinned-host -> device copy runs on a copy stream, issued while the previous step computes; every step's loss is copied to pinned host memory inside the timed region and read by the host one step later",
                        "fedavg_impl": chosen["impl"] if world > 1 else None,
                        "fedavg": (("uniform FedAvg of all trainable params after every local step: fused peer-memory kernel "
                                    "(scale + reduce-scatter + all-gather over NVLink, no NCCL on the data path)") if chosen["impl"] == "peer" else

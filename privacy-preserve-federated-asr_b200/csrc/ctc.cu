@@ -229,6 +229,8 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     // ---- phase 3: loss and gradient
     constexpr float LN2 = 0.6931471805599453f;
     float nll = INFINITY;
+    float lp_frac = 0.f;   // log2 P(y) = lp_frac + lp_exp, kept split: the gradient kernel subtracts the integer parts exactly
+    int lp_exp = 0;
     if (Tb > 0) {
         const long long r = (long long)(Tb - 1);
         const float a1 = alpha[r * Sld + S - 1];
@@ -237,13 +239,20 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
         const int e2 = S > 1 ? ea[r * Sld + S - 2] : E_EMPTY;
         const int em = max(e1, e2);
         const float tot = a1 * pow2i(e1 - em) + a2 * pow2i(e2 - em);
-        if (tot > 0.f) nll = -(logf(tot) + (float)em * LN2);
+        if (tot > 0.f) {
+            nll = -(logf(tot) + (float)em * LN2);
+            lp_frac = log2f(tot);
+            lp_exp = em;
+        }
     }
     if (Tb == 0 && L == 0) nll = 0.f;  // empty input, empty target (torch convention)
     const bool infeasible = !(nll < INFINITY);
     if (threadIdx.x == 0) {
         loss[hb] = (infeasible && zero_infinity) ? 0.f : nll;
-        reinterpret_cast<float*>(eb + (long long)T_ * Sld)[0] = nll;   // raw value for the gradient kernel
+        float* sc = reinterpret_cast<float*>(eb + (long long)T_ * Sld);   // scalars for the gradient kernel
+        sc[0] = nll;
+        sc[1] = lp_frac;
+        reinterpret_cast<int*>(sc)[2] = lp_exp;
     }
 }
 
@@ -272,7 +281,9 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const T* __restrict__ log
     const float* beta = alpha + (long long)T_ * Sld;
     const int* ea = reinterpret_cast<const int*>(beta + (long long)T_ * Sld);
     const int* eb = ea + (long long)T_ * Sld;
-    const float nll = reinterpret_cast<const float*>(eb + (long long)T_ * Sld)[0];
+    const float* scal = reinterpret_cast<const float*>(eb + (long long)T_ * Sld);
+    const float nll = scal[0], lp_frac = scal[1];
+    const int lp_exp = reinterpret_cast<const int*>(scal)[2];
     const bool infeasible = !(nll < INFINITY);
     constexpr float LOG2E = 1.4426950408889634f;
     T* g = grad + hb * T_ * V;
@@ -291,11 +302,18 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const T* __restrict__ log
     const float* br = beta + (long long)t * Sld;
     const int* ear = ea + (long long)t * Sld;
     const int* ebr = eb + (long long)t * Sld;
-    // log2 of alpha_t(s) * beta_t(s): mantissa product + the two lane exponents (the only logs of the kernel)
+    __syncwarp();   // pl2[] of the other lanes' labels is read below
+    // q(s) = log2( alpha_t(s) beta_t(s) / (p_t(label_s) P(y)) ) = log2 of the state posterior: mantissa product + the two state
+    // exponents - log2 p - log2 P (integer parts subtracted exactly: the result is a small number, whatever |log P| is).  The division by p comes FIRST: with peaked posteriors a state whose label has p = 2^-60 carries
+    // alpha beta = 2^-60 of the frame's largest product and still holds the whole posterior mass of its label (a fixed-point
+    // sum relative to max alpha beta, as in round 1, drops exactly those states).
     float mx = NEG_INF;
     for (int s = lane; s < S; s += 32) {
         const float ab = ar[s] * br[s];
-        if (ab > 0.f) mx = fmaxf(mx, log2f(ab) + (float)(ear[s] + ebr[s]));
+        if (ab > 0.f) {
+            const int l = (s & 1) ? tgt[(s - 1) >> 1] : blank;
+            mx = fmaxf(mx, (log2f(ab) - pl2[l] - lp_frac) + (float)(ear[s] + ebr[s] - lp_exp));
+        }
     }
     mx = warp_max(mx);
     for (int v = lane; v < V; v += 32) acc[v] = 0ull;
@@ -304,19 +322,17 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const T* __restrict__ log
         const float ab = ar[s] * br[s];
         if (ab > 0.f) {
             const int l = (s & 1) ? tgt[(s - 1) >> 1] : blank;
-            const float rel2 = log2f(ab) + (float)(ear[s] + ebr[s]) - mx;  // <= 0
-            atomicAdd(&acc[l], (unsigned long long)(exp2f(rel2) * 1099511627776.0f));  // in [0, 2^40]
+            const float rel2 = (log2f(ab) - pl2[l] - lp_frac) + (float)(ear[s] + ebr[s] - lp_exp) - mx;  // <= 0
+            atomicAdd(&acc[l], (unsigned long long)(exp2f(rel2) * 1099511627776.0f));  // in [0, 2^40]: integer sums commute
         }
     }
     __syncwarp();
-    // d nll / d logit = softmax - sum_{s: lab = v} alpha_t(s) beta_t(s) / (P p_t(v)),  P = exp(-nll)
+    // d nll / d logit = softmax - occupancy,  occupancy_t(v) = sum_{s: lab = v} alpha_t(s) beta_t(s) / (P p_t(v)),  P = exp(-nll)
     // (ATen ctc_loss backward form)
-    // (combined in the log2 domain: p_t(v) may lie below the fp32 range while the occupancy it divides is of order 1)
-    const float lfac = mx + nll * LOG2E - 40.0f;
+    const float fac = exp2f(mx - 40.0f);   // (mx = log2 of the frame's largest state posterior: <= 0 up to rounding)
     for (int v = lane; v < V; v += 32) {
         const float pv = pr[v];
-        const float a = (float)acc[v];
-        const float occ = a > 0.f ? exp2f(log2f(a) + lfac - pl2[v]) : 0.f;
+        const float occ = (float)acc[v] * fac;
         g[(long long)t * V + v] = from_f<T>((pv - occ) * gs);
     }
 }
