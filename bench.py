@@ -297,7 +297,7 @@ def run_b200(args):
     import torch.distributed as dist
 
     from b200asr import _lib, modeling as M, ops
-    from b200asr.fedavg import PeerFedAvg, fedavg_allreduce
+    from b200asr.fedavg import PeerFedAvg, SymmFedAvg, fedavg_allreduce
     from b200asr.optim import FusedAdamW
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -317,10 +317,25 @@ def run_b200(args):
     model.freeze_feature_encoder()
     model.validate_labels = False  # the reference's labels.max() check costs a host sync per step; inputs are synthetic
     model.to(dev).train()
-    use_peer = world > 1 and args.fedavg in ("peer", "auto")
-    opt = FusedAdamW(model.named_parameters(), lr=1e-5, weight_decay=0.005, max_grad_norm=1.0, warmup_steps=1000,
-                     peer=use_peer)
-    peer_agg = PeerFedAvg([g["fp"] for g in opt.groups]) if use_peer else None
+    # N > 1: the flat parameter buffers live in memory every client can reach.  Preferred: torch symmetric memory (peer
+    # pointers AND one NVSwitch multicast address: our NVLS kernel + our peer kernel on the same buffers); fallback: plain
+    # cudaMalloc exported over CUDA IPC (peer kernel only); "nccl": ordinary allocations.
+    use_peer = world > 1 and args.fedavg in ("peer", "auto", "nvls")
+    opt, peer_agg, symm_note = None, None, None
+    if use_peer and args.fedavg in ("auto", "nvls") and not args.no_symm:
+        try:
+            opt = FusedAdamW(model.named_parameters(), lr=1e-5, weight_decay=0.005, max_grad_norm=1.0, warmup_steps=1000,
+                             peer="symm")
+            peer_agg = SymmFedAvg([g["fp"] for g in opt.groups])
+            symm_note = "symmetric memory, multicast " + ("available" if peer_agg.has_multicast else "NOT available")
+        except Exception as e:   # no symmetric-memory support on this box: CUDA IPC buffers + the peer kernel
+            symm_note = f"symmetric memory unavailable ({type(e).__name__}: {str(e)[:120]})"
+            opt, peer_agg = None, None
+    if opt is None:
+        opt = FusedAdamW(model.named_parameters(), lr=1e-5, weight_decay=0.005, max_grad_norm=1.0, warmup_steps=1000,
+                         peer=use_peer)
+        peer_agg = PeerFedAvg([g["fp"] for g in opt.groups]) if use_peer else None
+    is_symm = isinstance(peer_agg, SymmFedAvg)
     n_train = sum(g["fp"].numel for g in opt.groups)
     samples = SECONDS * SR
     frames = int(M.conv_out_lengths(cfg, torch.tensor(samples)))
@@ -340,7 +355,8 @@ def run_b200(args):
     graphed = None
     if not args.eager:
         from b200asr.graph import GraphedTrainStep
-        graphed = GraphedTrainStep(model, opt, resident[0], max_label_len=120)
+        # N > 1: the frozen conv stack is a graph of its own, so that the next round's begin() can run under the aggregation
+        graphed = GraphedTrainStep(model, opt, resident[0], max_label_len=120, split_conv=(world > 1 and not args.no_overlap))
     skipped_blocks = [0]
 
     def local_step(batch):
@@ -356,14 +372,21 @@ def run_b200(args):
             fedavg_allreduce(g["fp"].flat)
             g["fp"].mark_updated()
 
-    chosen = {"impl": "peer" if use_peer else "nccl"}
+    chosen = {"impl": ("nvls" if (is_symm and peer_agg.has_multicast) else "peer") if use_peer else "nccl"}
+    if args.fedavg in ("peer", "nvls") and use_peer:
+        chosen["impl"] = args.fedavg if (args.fedavg == "peer" or (is_symm and peer_agg.has_multicast)) else "peer"
+
+    def fedavg_impl(impl):
+        if impl == "nccl":                 # our scale kernel + NCCL all-reduce
+            fedavg_nccl()
+        elif is_symm:                      # "nvls": in-switch reduction + multicast; "peer": fused peer-memory kernel
+            peer_agg(impl=impl, max_blocks=(args.nvls_blocks if impl == "nvls" else 0))
+        else:                              # fused peer-memory kernel over CUDA IPC buffers
+            peer_agg()
 
     def fedavg():
         if world > 1:
-            if chosen["impl"] == "peer":   # fused peer-memory kernel: scale + reduce-scatter + all-gather over NVLink
-                peer_agg()
-            else:                          # our scale kernel + NCCL all-reduce (NVLS in-switch reduction at 8 GPUs)
-                fedavg_nccl()
+            fedavg_impl(chosen["impl"])
 
     def barrier():
         if world > 1:
@@ -371,6 +394,7 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     copy_stream = torch.cuda.Stream()
+    comm_stream = torch.cuda.Stream()
 
     def timed(nsteps, e2e):
         """CUDA-event time of nsteps steps (max over ranks), barrier + synchronize on both sides."""
@@ -399,22 +423,43 @@ def run_b200(args):
         pinned = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)] if e2e else None
         pending = None
         nxt = stage(0) if e2e else None
-        for i in range(nsteps):
+        pipelined = world > 1 and graphed is not None and graphed.split_conv
+
+        def get_batch(i):
+            nonlocal nxt
             if e2e:  # the call a user makes: pinned host batch -> device, update, loss read back
-                batch, ev = nxt
+                b, ev = nxt
                 main.wait_event(ev)
-            else:
-                batch = resident[i % len(resident)]
-            loss = local_step(batch)
-            if graphed is not None:
-                launches += graphed.launches_last_replay if graphed.segmented else graphed.launches_per_replay
-            if world > 1:
-                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                a0.record(); fedavg(); a1.record()
-                agg.append((a0, a1))
-            if e2e:
                 if i + 1 < nsteps:
                     nxt = stage(i + 1)
+                return b
+            return resident[i % len(resident)]
+
+        if pipelined:
+            graphed.begin(get_batch(0))
+        for i in range(nsteps):
+            if pipelined:
+                # round i: the weight-dependent part of the update, then the aggregation on the comm stream while the main
+                # stream already runs the frozen conv stack of round i + 1; the main stream rejoins before it reads weights
+                loss = graphed.finish()
+                skipped_blocks[0] += len(model.backbone.last_skipped_layers)
+                comm_stream.wait_stream(main)
+                with torch.cuda.stream(comm_stream):
+                    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a0.record(comm_stream); fedavg(); a1.record(comm_stream)
+                agg.append((a0, a1))
+                if i + 1 < nsteps:
+                    graphed.begin(get_batch(i + 1))
+                main.wait_stream(comm_stream)
+            else:
+                loss = local_step(get_batch(i))
+                if world > 1:
+                    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a0.record(); fedavg(); a1.record()
+                    agg.append((a0, a1))
+            if graphed is not None:
+                launches += graphed.launches_last_replay if (graphed.segmented or graphed.split_conv) else graphed.launches_per_replay
+            if e2e:
                 pinned[i & 1].copy_(loss.detach().reshape(1), non_blocking=True)   # device -> host read of the step's result
                 ev = torch.cuda.Event()
                 ev.record()
@@ -456,10 +501,15 @@ def run_b200(args):
     if world > 1:  # both aggregation paths timed alone on the real buffers (max over ranks: every rank sees the same numbers)
         agg_alone["nccl_allreduce_ms"] = time_alone(fedavg_nccl)
         if peer_agg is not None:
-            agg_alone["peer_kernel_ms"] = time_alone(peer_agg)
+            agg_alone["peer_kernel_ms"] = time_alone(lambda: fedavg_impl("peer"))
+            if is_symm and peer_agg.has_multicast:
+                agg_alone["nvls_kernel_ms"] = time_alone(lambda: fedavg_impl("nvls"))
             peer_agg.check()
             if args.fedavg == "auto":
-                chosen["impl"] = "peer" if agg_alone["peer_kernel_ms"] <= agg_alone["nccl_allreduce_ms"] else "nccl"
+                cand = {"nccl": agg_alone["nccl_allreduce_ms"], "peer": agg_alone["peer_kernel_ms"]}
+                if "nvls_kernel_ms" in agg_alone:
+                    cand["nvls"] = agg_alone["nvls_kernel_ms"]
+                chosen["impl"] = min(cand, key=cand.get)
     clocks = ClockSampler(local_rank) if rank == 0 else None
     n0 = _lib.launch_count()
     ms_step, agg_ms, _, launches, skipped = timed(args.steps, e2e=False)
@@ -533,10 +583,15 @@ def run_b200(args):
                        "l2_policy": "inputs+weights+saved activations per step (>3 GB) exceed the 126 MB L2; no flush",
                        "e2e_input_pipeline": "each step's pinned-host -> device copy runs on a copy stream, issued while the previous step computes; every step's loss is copied to pinned host memory inside the timed region and read by the host one step later",
                        "fedavg_impl": chosen["impl"] if world > 1 else None,
-                       "fedavg": (("uniform FedAvg of all trainable params after every local step: fused peer-memory kernel "
-                                   "(scale + reduce-scatter + all-gather over NVLink, no NCCL on the data path)") if chosen["impl"] == "peer" else
-                                  "uniform FedAvg of all trainable params after every local step (scale kernel + NCCL all-reduce)")
-                                 if world > 1 else "n/a at 1 GPU"},
+                       "fedavg_buffers": symm_note if world > 1 else None,
+                       "fedavg_overlap": ("the aggregation runs on a comm stream while the main stream replays the next round's frozen "
+                                          "conv-stack graph" if (world > 1 and graphed is not None and graphed.split_conv) else None),
+                       "fedavg": ({"peer": "uniform FedAvg of all trainable params after every local step: fused peer-memory kernel "
+                                           "(scale + reduce-scatter + all-gather over NVLink, no NCCL on the data path)",
+                                   "nvls": "uniform FedAvg of all trainable params after every local step: own NVLS kernel (multimem.ld_reduce "
+                                           "in the NVSwitch + multimem.st multicast of the average, 4P/N bytes each way per GPU)",
+                                   "nccl": "uniform FedAvg of all trainable params after every local step (scale kernel + NCCL all-reduce)"}
+                                  [chosen["impl"]]) if world > 1 else "n/a at 1 GPU"},
             "e2e": {"value": audio_s / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": sum(v.numel() * v.element_size() for v in host[0].values()),
                     "d2h_bytes_per_step": 4, "last_loss": last_loss, "blocks_skipped": skipped_e2e},
@@ -592,8 +647,12 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the torch_gpu_baseline and other_configs legs (profiling runs)")
-    ap.add_argument("--fedavg", default="auto", choices=["auto", "peer", "nccl"],
-                    help="N>1 aggregation: fused peer-memory kernel, scale kernel + NCCL all-reduce, or whichever measures faster in warm-up")
+    ap.add_argument("--fedavg", default="auto", choices=["auto", "peer", "nccl", "nvls"],
+                    help="N>1 aggregation: own NVLS kernel (in-switch reduction), fused peer-memory kernel, scale kernel + NCCL "
+                         "all-reduce, or whichever measures fastest in warm-up")
+    ap.add_argument("--no-symm", action="store_true", help="do not try torch symmetric memory for the flat buffers (CUDA IPC + peer kernel)")
+    ap.add_argument("--no-overlap", action="store_true", help="N>1: do not overlap the aggregation with the next round's conv stack")
+    ap.add_argument("--nvls-blocks", type=int, default=0, help="cap of the NVLS kernel's grid (0 = full grid)")
     ap.add_argument("--dropout", type=float, default=0.1,
                     help="hidden = activation = attention = final dropout P in the timed training step (0.1 = the "
                          "Data2VecAudioConfig defaults the reference fine-tunes with; 0 = the parity setting)")

@@ -35,9 +35,11 @@ class _SegmentRecorder:
     streams, ends the running capture and begins the next one in the same memory pool (relaxed capture mode: the captures
     begin and end on different threads)."""
 
-    def __init__(self, pool, n_layers: int):
+    def __init__(self, pool, n_layers: int, block_marks: bool = True, split_conv: bool = False):
         self.pool = pool
         self.L = n_layers
+        self.block_marks = block_marks   # cut before every block and after the last one (LayerDrop)
+        self.split_conv = split_conv     # cut after the frozen conv stack (its graph may run while FedAvg is in flight)
         self.graphs: List[torch.cuda.CUDAGraph] = []
         self.fwd_x: Dict[int, torch.Tensor] = {}   # tensor at mark l (block l's input = block l-1's output)
         self.bwd_g: Dict[int, torch.Tensor] = {}   # gradient seen at mark l (d loss / d block l's input)
@@ -63,6 +65,9 @@ class _SegmentRecorder:
         self.end()
         self.begin()
 
+    def conv_mark(self):
+        self.boundary()
+
     def fwd_mark(self, idx: int, x: torch.Tensor):
         self.fwd_x[idx] = x
         self.boundary()
@@ -82,7 +87,10 @@ class GraphedTrainStep:
     next call overwrites.  `last_skipped_layers` holds the blocks LayerDrop skipped in the latest call."""
 
     def __init__(self, model, opt, example_batch: Dict[str, torch.Tensor], max_label_len: Optional[int] = None,
-                 warmup: int = 3):
+                 warmup: int = 3, split_conv: bool = False):
+        """split_conv: capture the frozen conv feature extractor as a graph of its own, replayed by `begin(batch)`; the
+        rest of the update is replayed by `finish()`.  The conv stack does not depend on the trainable weights, so a
+        federated client can run `begin(next batch)` while the FedAvg of the previous round is still in flight."""
         self.model, self.opt = model, opt
         self.max_label_len = int(max_label_len or example_batch["labels"].shape[1])
         if hasattr(model, "validate_labels"):
@@ -90,7 +98,8 @@ class GraphedTrainStep:
         self.backbone = getattr(model, "backbone", None)
         self.layerdrop = _layerdrop_p(model)
         self.segmented = self.layerdrop > 0.0
-        if self.segmented and self.backbone is None:
+        self.split_conv = bool(split_conv)
+        if (self.segmented or self.split_conv) and self.backbone is None:
             raise ValueError("GraphedTrainStep: LayerDrop needs a model with a `backbone` (Data2VecAudioModel)")
         self.static = {k: self._fit(k, v).clone() for k, v in example_batch.items()}
         saved = [t.clone() for t in opt.state_tensors()]
@@ -106,7 +115,8 @@ class GraphedTrainStep:
         from . import _lib
         n0 = _lib.launch_count()
         self.last_skipped_layers = ()
-        if self.segmented:
+        self.conv_graph, self.conv_launches = None, 0
+        if self.segmented or self.split_conv:
             self._capture_segmented()
         else:
             self.graph = torch.cuda.CUDAGraph()
@@ -140,7 +150,7 @@ class GraphedTrainStep:
         L = len(bb.encoder.layers)
         torch.cuda.synchronize()
         pool = torch.cuda.graph_pool_handle()
-        rec = _SegmentRecorder(pool, L)
+        rec = _SegmentRecorder(pool, L, block_marks=self.segmented, split_conv=self.split_conv)
         stream = torch.cuda.Stream()
         stream.wait_stream(torch.cuda.current_stream())
         bb._segment_recorder = rec      # modeling.forward places a SegmentMarkFn before every block and after the last
@@ -154,14 +164,20 @@ class GraphedTrainStep:
             bb._segment_recorder = None
             bb._force_no_layerdrop = False
         torch.cuda.current_stream().wait_stream(stream)
-        if len(rec.graphs) != 2 * L + 3 or len(rec.fwd_x) != L + 1 or len(rec.bwd_g) != L + 1:
-            raise RuntimeError(f"GraphedTrainStep: expected {2 * L + 3} segments, captured {len(rec.graphs)} "
+        c0 = 1 if self.split_conv else 0
+        want = c0 + (2 * L + 3 if self.segmented else 1)
+        nm = L + 1 if self.segmented else 0
+        if len(rec.graphs) != want or len(rec.fwd_x) != nm or len(rec.bwd_g) != nm:
+            raise RuntimeError(f"GraphedTrainStep: expected {want} segments, captured {len(rec.graphs)} "
                                f"({len(rec.fwd_x)} forward / {len(rec.bwd_g)} backward marks)")
         self.L = L
-        self.graphs = rec.graphs
+        self.conv_graph = rec.graphs[0] if self.split_conv else None
+        self.conv_launches = rec.launches[0] if self.split_conv else 0
+        self.graphs = rec.graphs[c0:]
+        rec.launches = rec.launches[c0:]
         self.fwd_x, self.bwd_g = rec.fwd_x, rec.bwd_g
         self.graph_launches = rec.launches
-        self.launches_last_replay = sum(rec.launches)
+        self.launches_last_replay = self.conv_launches + sum(rec.launches)
         # per block: the parameters it owns (idle rows of the AdamW table when skipped) and their slices of the flat gradients
         self.layer_idle, self.layer_grad_slices = [], []
         for l in range(L):
@@ -181,6 +197,11 @@ class GraphedTrainStep:
 
     def _replay_segmented(self):
         L = self.L
+        if not self.segmented:   # only the conv stack was split off
+            self.opt.prepare_hyper()
+            self.launches_last_replay = self.conv_launches + self.graph_launches[0]
+            self.graphs[0].replay()
+            return
         skipped = set(self.backbone._layerdrop_coins(L))
         self.last_skipped_layers = tuple(sorted(skipped))
         self.backbone.last_skipped_layers = self.last_skipped_layers
@@ -188,7 +209,7 @@ class GraphedTrainStep:
         self.opt.prepare_hyper(idle)
         g = self.graphs
         gl = self.graph_launches
-        self.launches_last_replay = sum(gl) - sum(gl[1 + l] + gl[2 + L + (L - 1 - l)] for l in skipped)
+        self.launches_last_replay = self.conv_launches + sum(gl) - sum(gl[1 + l] + gl[2 + L + (L - 1 - l)] for l in skipped)
         g[0].replay()                                       # conv stack, projection, positional conv
         for l in range(L):
             if l in skipped:
@@ -206,6 +227,12 @@ class GraphedTrainStep:
         g[2 + 2 * L].replay()                               # positional conv / projection backward, clip, AdamW
 
     def __call__(self, batch: Dict[str, torch.Tensor]) -> torch.Tensor:
+        self.begin(batch)
+        return self.finish()
+
+    def begin(self, batch: Dict[str, torch.Tensor]):
+        """Stage the batch and (split_conv) run the frozen conv feature extractor -- everything that does not depend on
+        the trainable weights."""
         for k, dst in self.static.items():
             src = batch[k]
             if k == "labels" and src.shape[1] != self.max_label_len:
@@ -213,11 +240,16 @@ class GraphedTrainStep:
                 dst[:, : src.shape[1]].copy_(src, non_blocking=True)
             else:
                 dst.copy_(src, non_blocking=True)
+        if self.backbone is not None:
+            self.backbone.cache.refresh_in_place()   # cached copies of the frozen conv stack's filters (load_state_dict)
+        if self.conv_graph is not None:
+            self.conv_graph.replay()
+
+    def finish(self) -> torch.Tensor:
+        """The rest of the update (reads the trainable weights: run after the aggregation of the previous round)."""
         for g in self.opt.groups:   # weights replaced through torch since the last step (load_state_dict of the global
             g["fp"].sync_params()   # model at the start of a federated round): the captured kernels read the bf16 shadow
-        if self.backbone is not None:
-            self.backbone.cache.refresh_in_place()   # ... and the cached copies of the frozen conv stack's filters
-        if self.segmented:
+        if self.segmented or self.split_conv:
             self._replay_segmented()
         else:
             self.opt.prepare_hyper()

@@ -305,6 +305,8 @@ class Data2VecAudioModel(nn.Module):
             [None if n is None else n.weight for n in lns], [None if n is None else n.bias for n in lns],
             list(c.conv_kernel), list(c.conv_stride), 1e-5, cache, norm=_cfg(c, "feat_extract_norm", "layer"))
         B, T, _ = feats.shape
+        if self._segment_recorder is not None and self._segment_recorder.split_conv:
+            self._segment_recorder.conv_mark()   # graph capture: the frozen conv stack becomes a graph of its own
         klen = None
         if attention_mask is not None:
             klen = conv_out_lengths(c, attention_mask.sum(-1)).to(torch.int32).contiguous()
@@ -344,7 +346,7 @@ class Data2VecAudioModel(nn.Module):
         self.last_skipped_layers = skipped
         rec = self._segment_recorder
         for li, layer in enumerate(enc.layers):
-            if rec is not None:   # graph capture with LayerDrop: one CUDA graph per block (graph.GraphedTrainStep)
+            if rec is not None and rec.block_marks:   # graph capture with LayerDrop: one CUDA graph per block
                 x = Fn.SegmentMarkFn.apply(x, li, rec)
             if li in skipped:  # a dropped block is the identity and its parameters get no gradient
                 pass
@@ -357,7 +359,7 @@ class Data2VecAudioModel(nn.Module):
                 x = block.apply(x, klen, meta, cache, *layer.params())
             if collected is not None and not (stable and li + 1 == len(enc.layers)):
                 collected.append(x.view(B, T, d))
-        if rec is not None:
+        if rec is not None and rec.block_marks:
             x = Fn.SegmentMarkFn.apply(x, len(enc.layers), rec)
         if stable:  # Wav2Vec2EncoderStableLayerNorm: one LayerNorm after the last block
             x = Fn.LayerNormFn.apply(x, enc.layer_norm.weight, enc.layer_norm.bias, eps)
