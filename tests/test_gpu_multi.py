@@ -81,3 +81,61 @@ def test_peer_fedavg_matches_average_weights(tmp_path, weighted):
             assert torch.equal(res[r]["first"][k], res[0]["first"][k])  # every client holds the same model
         if not weighted:  # averaging identical models is the identity
             assert torch.equal(res[0]["last"][k], res[0]["first"][k]), k
+
+
+def _symm_worker(rank, world, port, out_dir):
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for p in (root, os.path.join(root, "privacy-preserve-federated-asr_b200")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    from b200asr.fedavg import FlatParams, SymmFedAvg
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        params = {k: torch.nn.Parameter(v.cuda()) for k, v in _client_params(rank).items()}
+        fp = FlatParams(list(params.items()), peer="symm", with_shadow=True)
+        agg = SymmFedAvg([fp])
+        start = fp.flat.clone()
+        out = {"has_multicast": agg.has_multicast}
+        for impl in (["nvls"] if agg.has_multicast else []) + ["peer"]:
+            fp.flat.copy_(start)
+            torch.cuda.synchronize()
+            dist.barrier()
+            agg(impl=impl)
+            torch.cuda.synchronize()
+            agg.check()
+            out[impl] = {k: p.detach().cpu().clone() for k, p in params.items()}
+            out[impl + "_shadow_ok"] = bool(torch.equal(fp.shadow, fp.flat.to(torch.bfloat16)))   # refreshed by mark_updated
+            dist.barrier()
+        torch.save(out, os.path.join(out_dir, f"rank{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_symm_fedavg_nvls_and_peer_match_average_weights(tmp_path):
+    """FlatParams over torch symmetric memory: the own NVLS kernel (multimem.ld_reduce in the switch + multimem.st) equals
+    the reference's sequential mean to <= 1e-6 (BASELINE.json) on every rank, the peer kernel on the same buffers is
+    bit-exact; the bf16 shadow follows."""
+    world = min(torch.cuda.device_count(), 8)
+    port = 29100 + (os.getpid() % 500)
+    mp.spawn(_symm_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    clients = [_client_params(r) for r in range(world)]
+    res = [torch.load(os.path.join(tmp_path, f"rank{r}.pt")) for r in range(world)]
+    impls = (["nvls"] if res[0]["has_multicast"] else []) + ["peer"]
+    print(f"[symm fedavg] world {world}, multicast {res[0]['has_multicast']}, impls {impls}")
+    for k in clients[0]:
+        ref = clients[0][k].clone()
+        for c in clients[1:]:
+            ref += c[k]
+        ref = torch.div(ref, world)
+        for impl in impls:
+            for r in range(world):
+                got = res[r][impl][k]
+                if impl == "peer":
+                    assert torch.equal(got, ref), (k, r)
+                else:
+                    assert (got - ref).abs().max() <= 1e-6 * max(1.0, float(ref.abs().max())), (impl, k, r)
+                assert torch.equal(got, res[0][impl][k])   # every client holds the same bits
+                assert res[r][impl + "_shadow_ok"]
