@@ -19,8 +19,8 @@ for stage in "$@"; do
     launches)  timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extras > gpurun_out/${TAG}_ncu.log 2>&1; echo "launches rc=$?";;
     probe*)    N=${stage#probe}; timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29531 tools/nvls_probe.py > gpurun_out/${TAG}_probe${N}.json 2> gpurun_out/${TAG}_probe${N}.err; echo "probe$N rc=$?";;
     multitest) timeout 900 python -m pytest tests/test_gpu_multi.py -q -s > gpurun_out/${TAG}_multitest.log 2>&1; echo "multitest rc=$?";;
-    mbench*)   N=${stage#mbench}; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29541 bench.py --gpus $N --steps 20 --warmup 3 > gpurun_out/${TAG}_bench_n${N}.json 2> gpurun_out/${TAG}_bench_n${N}.err; echo "mbench$N rc=$?";;
     mbench_noov*) N=${stage#mbench_noov}; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29551 bench.py --gpus $N --steps 20 --warmup 3 --no-overlap > gpurun_out/${TAG}_bench_noov_n${N}.json 2> gpurun_out/${TAG}_bench_noov_n${N}.err; echo "mbench_noov$N rc=$?";;
+    mbench*)   N=${stage#mbench}; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29541 bench.py --gpus $N --steps 20 --warmup 3 > gpurun_out/${TAG}_bench_n${N}.json 2> gpurun_out/${TAG}_bench_n${N}.err; echo "mbench$N rc=$?";;
     *) echo "unknown stage $stage";;
   esac
 done
