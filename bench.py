@@ -207,7 +207,7 @@ def run_reference(args):
                        "sample": cb["sample"]},
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    args._emit(json.dumps(line))
 
 
 # ======================================================================================= other configurations (N = 1)
@@ -634,7 +634,7 @@ def run_b200(args):
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_reference(steps=2, warmup=1, batch=2, seconds=SECONDS, pd=pd, ld=ld)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
-        print(json.dumps(line))
+        args._emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
@@ -661,6 +661,12 @@ def main():
     ap.add_argument("--ref-seconds", type=float, default=SECONDS)
     ap.add_argument("--eager", action="store_true", help="issue every launch from Python instead of replaying the CUDA graph")
     args = ap.parse_args()
+    # stdout carries exactly ONE line, the JSON: anything a library prints on the way (NCCL's version banner, warnings) is
+    # sent to stderr by pointing fd 1 there until the line is ready
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    args._emit = lambda text: (sys.stdout.flush(), os.dup2(real_stdout, 1), print(text, flush=True))
     if args.impl == "reference":
         run_reference(args)
     else:

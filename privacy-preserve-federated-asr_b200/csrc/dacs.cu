@@ -1,8 +1,6 @@
 // DACS toggling network kernels: fused Gumbel-softmax hard mask (+ masked hidden states) forward/backward,
 // mean over time of AD logits, RecallLoss / CE on [B, C] logits, CosFace diversity term.  All HBM-bound
 // elementwise / reduction work: 128-bit loads, one pass over the data.
-#include <curand_kernel.h>
-
 #include "common.cuh"
 
 namespace b200asr {
@@ -31,8 +29,8 @@ __device__ __forceinline__ MaskOut gumbel_hard(float s0, float s1, float g0, flo
 __device__ __forceinline__ float gumbel_from_u32(uint32_t r) {
     // U in (0, 1]; E = -log(U) ~ Exp(1); g = -log(E)   (models.py:111-116)
     const float u = ((float)(r >> 8) + 1.0f) * (1.0f / 16777216.0f);
-    const float e = fmaxf(-logf(u), 1e-20f);
-    return -logf(e);
+    const float e = fmaxf(-__logf(u), 1e-20f);   // (MUFU lg2: the noise is random, its last bits do not matter)
+    return -__logf(e);
 }
 
 template <typename T>
@@ -70,9 +68,12 @@ __global__ void __launch_bounds__(256) dacs_mask_fwd_kernel(const T* __restrict_
                 g0 = noise_lm[2 * e]; g1 = noise_lm[2 * e + 1];
                 g2 = noise_ad[2 * e]; g3 = noise_ad[2 * e + 1];
             } else {
-                curandStatePhilox4_32_10_t st;
-                curand_init(seed, (unsigned long long)e, offset, &st);
-                const uint4 r = curand4(&st);
+                // one Philox4x32-10 call per element = its four uniforms (counter: element index and call offset, key: seed).
+                // (Round 1 went through curand_init per element: its 64-byte state and skip-ahead made the kernel ALU bound
+                // at 21 % of the HBM rate.)
+                const uint4 r = philox4x32_10(make_uint4((uint32_t)e, (uint32_t)((unsigned long long)e >> 32), (uint32_t)offset,
+                                                         (uint32_t)(offset >> 32)),
+                                              make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
                 g0 = gumbel_from_u32(r.x); g1 = gumbel_from_u32(r.y);
                 g2 = gumbel_from_u32(r.z); g3 = gumbel_from_u32(r.w);
             }
