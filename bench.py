@@ -297,7 +297,7 @@ def run_b200(args):
     import torch.distributed as dist
 
     from b200asr import _lib, modeling as M, ops
-    from b200asr.fedavg import PeerFedAvg, SymmFedAvg, fedavg_allreduce
+    from b200asr.fedavg import PeerFedAvg, PipelinedFedAvg, SymmFedAvg, fedavg_allreduce
     from b200asr.optim import FusedAdamW
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -358,6 +358,11 @@ def run_b200(args):
         # N > 1: the frozen conv stack is a graph of its own, so that the next round's begin() can run under the aggregation
         graphed = GraphedTrainStep(model, opt, resident[0], max_label_len=120, split_conv=(world > 1 and not args.no_overlap))
     skipped_blocks = [0]
+    # N > 1 with per-block graphs: layer-wise FedAvg on a comm stream, each block's graph of the NEXT round waits only for
+    # its own parameters (fedavg.PipelinedFedAvg) -- the aggregation hides behind the forward pass
+    pipe = None
+    if world > 1 and graphed is not None and graphed.segmented and not args.no_overlap and not args.no_layerwise:
+        pipe = PipelinedFedAvg([g["fp"] for g in opt.groups], graphed.fedavg_chunks(), agg=peer_agg, max_blocks=args.fedavg_blocks)
 
     def local_step(batch):
         if graphed is None:
@@ -437,8 +442,21 @@ def run_b200(args):
 
         if pipelined:
             graphed.begin(get_batch(0))
+        evs = None
         for i in range(nsteps):
-            if pipelined:
+            if pipe is not None:
+                # round i: every block's graph waits only for the average of ITS parameters from round i - 1; the
+                # aggregation of round i then starts on the comm stream and runs under the forward pass of round i + 1
+                loss = graphed.finish(wait_events=evs)
+                skipped_blocks[0] += len(model.backbone.last_skipped_layers)
+                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a0.record(main)
+                evs = pipe.launch(comm_stream, chosen["impl"])
+                a1.record(comm_stream)
+                agg.append((a0, a1))
+                if i + 1 < nsteps:
+                    graphed.begin(get_batch(i + 1))
+            elif pipelined:
                 # round i: the weight-dependent part of the update, then the aggregation on the comm stream while the main
                 # stream already runs the frozen conv stack of round i + 1; the main stream rejoins before it reads weights
                 loss = graphed.finish()
@@ -470,6 +488,7 @@ def run_b200(args):
         if e2e and pending is not None:
             pending[0].synchronize()
             last = float(pending[1])
+        main.wait_stream(comm_stream)   # the last round's aggregation is part of the timed region
         t1.record()
         barrier()
         if peer_agg is not None:
@@ -584,8 +603,12 @@ def run_b200(args):
                        "e2e_input_pipeline": "each step's pinned-host -> device copy runs on a copy stream, issued while the previous step computes; every step's loss is copied to pinned host memory inside the timed region and read by the host one step later",
                        "fedavg_impl": chosen["impl"] if world > 1 else None,
                        "fedavg_buffers": symm_note if world > 1 else None,
-                       "fedavg_overlap": ("the aggregation runs on a comm stream while the main stream replays the next round's frozen "
-                                          "conv-stack graph" if (world > 1 and graphed is not None and graphed.split_conv) else None),
+                       "fedavg_overlap": (("layer-wise pipelined: chunk = one encoder block, exchange + barrier + bf16 shadow refresh per chunk "
+                                           f"on a comm stream (exchange grid capped at {args.fedavg_blocks} blocks); every block's CUDA graph "
+                                           "of the next round waits only for its own chunk, so the aggregation runs under the next forward "
+                                           "pass; fedavg_agg_ms is the span of the aggregation, not its exposed part") if pipe is not None else
+                                          ("the aggregation runs on a comm stream while the main stream replays the next round's frozen "
+                                           "conv-stack graph" if (world > 1 and graphed is not None and graphed.split_conv) else None)),
                        "fedavg": ({"peer": "uniform FedAvg of all trainable params after every local step: fused peer-memory kernel "
                                            "(scale + reduce-scatter + all-gather over NVLink, no NCCL on the data path)",
                                    "nvls": "uniform FedAvg of all trainable params after every local step: own NVLS kernel (multimem.ld_reduce "
@@ -653,6 +676,8 @@ def main():
     ap.add_argument("--no-symm", action="store_true", help="do not try torch symmetric memory for the flat buffers (CUDA IPC + peer kernel)")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: do not overlap the aggregation with the next round's conv stack")
     ap.add_argument("--nvls-blocks", type=int, default=0, help="cap of the NVLS kernel's grid (0 = full grid)")
+    ap.add_argument("--no-layerwise", action="store_true", help="N>1: aggregate the whole buffer at once instead of block by block")
+    ap.add_argument("--fedavg-blocks", type=int, default=32, help="grid cap of the exchange kernels in the layer-wise pipelined FedAvg")
     ap.add_argument("--dropout", type=float, default=0.1,
                     help="hidden = activation = attention = final dropout P in the timed training step (0.1 = the "
                          "Data2VecAudioConfig defaults the reference fine-tunes with; 0 = the parity setting)")

@@ -379,6 +379,10 @@ int b200asr_fedavg_peer_reduce_guarded(float* const* peer_bufs, const float* wei
 int b200asr_fedavg_nvls_reduce(float* multicast_buf, int world, int rank, long long n, const int* abort_flag, int max_blocks,
                                void* stream);
 
+/* Grid cap (thread blocks) of the two exchange kernels above; 0 = full grid.  Returns the previous cap.  Used when the
+ * exchange is overlapped with compute (layer-wise pipelined FedAvg): the links saturate with a fraction of the SMs. */
+int b200asr_fedavg_set_max_blocks(int max_blocks);
+
 /* Cross-rank barrier over peer memory for the fused kernel above: every rank passes the HOST array of the `world`
  * ranks' flag buffers (>= world unsigned each, zero-initialised, peer-mapped) and a barrier number `epoch` that grows
  * by one per call on every rank.  Stream-ordered; bounded spin (sets *timeout_flag, a device int, instead of hanging). */

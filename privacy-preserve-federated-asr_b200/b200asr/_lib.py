@@ -98,6 +98,7 @@ SIGNATURES = {
     "b200asr_fedavg_peer_reduce": (i32, [C.POINTER(vp), C.POINTER(f32), i32, i32, i64, vp]),
     "b200asr_fedavg_peer_reduce_guarded": (i32, [C.POINTER(vp), C.POINTER(f32), i32, i32, i64, vp, vp]),
     "b200asr_fedavg_nvls_reduce": (i32, [vp, i32, i32, i64, vp, i32, vp]),
+    "b200asr_fedavg_set_max_blocks": (i32, [i32]),
     "b200asr_fedavg_peer_barrier": (i32, [C.POINTER(vp), i32, i32, C.c_uint, vp, vp]),
     "b200asr_fedavg_peer_barrier_set_timeout": (i32, [C.c_double]),
     "b200asr_peer_alloc": (i32, [C.POINTER(vp), sz]),

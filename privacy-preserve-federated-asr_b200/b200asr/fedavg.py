@@ -269,6 +269,13 @@ class PeerFedAvg:
         for fp in self.flats:
             fp.mark_updated()
 
+    def barrier(self):
+        self._barrier()
+
+    def reduce_range(self, gi: int, a: int, b: int, impl: str = "peer"):
+        """The exchange of elements [a, b) of flat buffer `gi` only (a, b multiples of 4), no barriers (PipelinedFedAvg)."""
+        ops.fedavg_peer_reduce([p + 4 * a for p in self.flat_ptrs[gi]], None, self.rank, b - a, abort_flag=self.timeout)
+
     def check(self):
         """Host-synchronising: raises if a barrier ever timed out (a peer never arrived)."""
         if int(self.timeout.item()) != 0:
@@ -342,10 +349,69 @@ class SymmFedAvg:
             for fp in self.flats:
                 fp.mark_updated()
 
+    def barrier(self):
+        self._barrier()
+
+    def reduce_range(self, gi: int, a: int, b: int, impl: str = "nvls"):
+        """The exchange of elements [a, b) of flat buffer `gi` only (a, b multiples of 4), no barriers (PipelinedFedAvg)."""
+        from ._lib import check, lib
+        if impl == "nvls" and self.has_multicast:
+            check(lib.b200asr_fedavg_nvls_reduce(self.mc_ptrs[gi] + 4 * a, self.world, self.rank, b - a, self.timeout.data_ptr(), 0,
+                                                 torch.cuda.current_stream().cuda_stream), "fedavg_nvls_reduce")
+        else:
+            ops.fedavg_peer_reduce([p + 4 * a for p in self.flat_ptrs[gi]], None, self.rank, b - a, abort_flag=self.timeout)
+
     def check(self):
         """Host-synchronising: raises if a barrier ever timed out (a peer never arrived)."""
         if int(self.timeout.item()) != 0:
             raise RuntimeError("SymmFedAvg: cross-rank barrier timed out")
+
+
+class PipelinedFedAvg:
+    """Layer-wise FedAvg that hides behind the next round's forward pass.
+
+    The flat buffers are cut into chunks in the order the forward pass consumes them (the non-block parameters, then block
+    0, 1, ...).  `launch()` enqueues, on a communication stream, for every chunk: exchange of its ranges -> cross-rank
+    barrier -> refresh of its slice of the bf16 weight shadow -> event.  The caller's forward pass waits for chunk c's
+    event right before the first kernel that reads chunk c (graph.GraphedTrainStep.finish(wait_events=...): one CUDA graph
+    per block), so the aggregation of block l+1.. overlaps the compute of block l.  The exchange kernels run with a capped
+    grid (`max_blocks`): they are NVLink bound with a fraction of the SMs and leave the rest to the forward pass.
+
+    `agg`: PeerFedAvg | SymmFedAvg | None (impl "nccl": scale kernel + NCCL all-reduce per range); uniform weights.
+    `chunks`: list of lists of (flat-buffer index, start, end) in elements."""
+
+    def __init__(self, flats: Sequence["FlatParams"], chunks, agg=None, max_blocks: int = 32):
+        self.flats, self.chunks, self.agg = list(flats), chunks, agg
+        self.max_blocks = int(max_blocks)
+        self.events = [torch.cuda.Event() for _ in chunks]
+
+    def launch(self, comm_stream, impl: str = "peer"):
+        """Returns the per-chunk events (valid until the next launch)."""
+        from ._lib import lib
+        comm_stream.wait_stream(torch.cuda.current_stream())   # the local update is complete
+        old = lib.b200asr_fedavg_set_max_blocks(self.max_blocks)
+        try:
+            with torch.cuda.stream(comm_stream):
+                if impl != "nccl":
+                    self.agg.barrier()   # every client's local update is complete and visible
+                for ev, ranges in zip(self.events, self.chunks):
+                    for gi, a, b in ranges:
+                        if impl == "nccl":
+                            fedavg_allreduce(self.flats[gi].flat[a:b])
+                        else:
+                            self.agg.reduce_range(gi, a, b, impl)
+                    if impl != "nccl":
+                        self.agg.barrier()   # every rank's slice of this chunk has landed everywhere
+                    for gi, a, b in ranges:
+                        fp = self.flats[gi]
+                        if fp.shadow is not None:
+                            ops.cast_from_f32(fp.flat[a:b], torch.bfloat16, out=fp.shadow[a:b])
+                    ev.record(comm_stream)
+        finally:
+            lib.b200asr_fedavg_set_max_blocks(old)
+        for fp in self.flats:
+            fp.mark_updated(shadow_written=True)   # (host bookkeeping: the shadow slices were refreshed chunk by chunk)
+        return self.events
 
 
 def fedavg_shard_plan(n: int, world: int):

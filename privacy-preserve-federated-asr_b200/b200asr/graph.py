@@ -195,8 +195,35 @@ class GraphedTrainStep:
                     slices.append(fp.grad[a:b])
             self.layer_grad_slices.append(slices)
 
-    def _replay_segmented(self):
+    def fedavg_chunks(self):
+        """The flat-buffer ranges in the order the forward pass reads them, for fedavg.PipelinedFedAvg: chunk 0 = every
+        parameter outside the encoder blocks (projection, positional conv, encoder LayerNorm, heads), chunk 1 + l = block l.
+        Each chunk is a list of (group index, start, end) in elements."""
+        if not self.segmented:
+            raise RuntimeError("fedavg_chunks: needs the per-block graphs (config.layerdrop > 0)")
+        chunks = [[] for _ in range(self.L + 1)]
+        for gi, g in enumerate(self.opt.groups):
+            fp = g["fp"]
+            pos = 0
+            for l in range(self.L):
+                ii = self.layer_idle[l][gi]
+                if not ii:
+                    continue
+                a = fp.offsets[ii[0]]
+                b = fp.offsets[ii[-1]] + (fp.params[ii[-1]].numel() + 3) // 4 * 4
+                if a > pos:
+                    chunks[0].append((gi, pos, a))
+                chunks[1 + l].append((gi, a, b))
+                pos = b
+            if fp.numel > pos:
+                chunks[0].append((gi, pos, fp.numel))
+        return chunks
+
+    def _replay_segmented(self, wait_events=None):
         L = self.L
+        main = torch.cuda.current_stream()
+        if wait_events is not None and not self.segmented:
+            main.wait_event(wait_events[-1])
         if not self.segmented:   # only the conv stack was split off
             self.opt.prepare_hyper()
             self.launches_last_replay = self.conv_launches + self.graph_launches[0]
@@ -210,12 +237,18 @@ class GraphedTrainStep:
         g = self.graphs
         gl = self.graph_launches
         self.launches_last_replay = self.conv_launches + sum(gl) - sum(gl[1 + l] + gl[2 + L + (L - 1 - l)] for l in skipped)
+        if wait_events is not None:
+            main.wait_event(wait_events[0])                 # (pipelined FedAvg: the non-block parameters have been averaged)
         g[0].replay()                                       # conv stack, projection, positional conv
         for l in range(L):
             if l in skipped:
                 self.fwd_x[l + 1].copy_(self.fwd_x[l])      # a dropped block is the identity
             else:
+                if wait_events is not None:
+                    main.wait_event(wait_events[1 + l])     # block l's parameters have been averaged
                 g[1 + l].replay()
+        if wait_events is not None:
+            main.wait_event(wait_events[-1])                # everything (skipped blocks included) before backward / AdamW
         g[1 + L].replay()                                   # head, CTC, head backward
         for l in range(L - 1, -1, -1):
             if l in skipped:
@@ -245,13 +278,17 @@ class GraphedTrainStep:
         if self.conv_graph is not None:
             self.conv_graph.replay()
 
-    def finish(self) -> torch.Tensor:
-        """The rest of the update (reads the trainable weights: run after the aggregation of the previous round)."""
+    def finish(self, wait_events=None) -> torch.Tensor:
+        """The rest of the update (reads the trainable weights: run after the aggregation of the previous round).
+        wait_events: the per-chunk events of fedavg.PipelinedFedAvg.launch() (chunks = self.fedavg_chunks()): each block's
+        graph then waits only for ITS parameters, the aggregation of the later blocks overlaps the forward pass."""
         for g in self.opt.groups:   # weights replaced through torch since the last step (load_state_dict of the global
             g["fp"].sync_params()   # model at the start of a federated round): the captured kernels read the bf16 shadow
         if self.segmented or self.split_conv:
-            self._replay_segmented()
+            self._replay_segmented(wait_events)
         else:
+            if wait_events is not None:
+                torch.cuda.current_stream().wait_event(wait_events[-1])
             self.opt.prepare_hyper()
             self.graph.replay()
         return self.loss

@@ -346,6 +346,16 @@ static int stream_grid(long long n) {
     return (int)(g < cap ? (g < 1 ? 1 : g) : cap);
 }
 
+// Grid cap of the multi-GPU exchange kernels (b200asr_fedavg_set_max_blocks; 0 = none).  An exchange that runs UNDER other
+// work (the layer-wise pipelined FedAvg overlaps the next round's forward) is link bound with a fraction of the SMs; the
+// cap leaves the rest to the compute kernels.
+static int g_fedavg_max_blocks = 0;
+static int exchange_grid(long long n) {
+    int g = stream_grid(n);
+    if (g_fedavg_max_blocks > 0 && g > g_fedavg_max_blocks) g = g_fedavg_max_blocks;
+    return g;
+}
+
 }  // namespace b200asr
 
 using namespace b200asr;
@@ -395,8 +405,8 @@ static int fedavg_peer_reduce_impl(float* const* peer_bufs, const float* weights
     const long long lo = per * rank;
     const long long hi = (rank == world - 1) ? n : per * (rank + 1);
     if (hi <= lo) return B200ASR_OK;
-    if (weights) fedavg_peer_kernel<0><<<stream_grid(hi - lo), 256, 0, as_stream(stream)>>>(p, world, lo, hi, abort_flag);
-    else fedavg_peer_kernel<1><<<stream_grid(hi - lo), 256, 0, as_stream(stream)>>>(p, world, lo, hi, abort_flag);
+    if (weights) fedavg_peer_kernel<0><<<exchange_grid(hi - lo), 256, 0, as_stream(stream)>>>(p, world, lo, hi, abort_flag);
+    else fedavg_peer_kernel<1><<<exchange_grid(hi - lo), 256, 0, as_stream(stream)>>>(p, world, lo, hi, abort_flag);
     return check_launch("fedavg_peer_reduce");
 }
 
@@ -420,7 +430,7 @@ int b200asr_fedavg_nvls_reduce(float* multicast_buf, int world, int rank, long l
     const long long lo = per * rank;
     const long long hi = (rank == world - 1) ? n : per * (rank + 1);
     if (hi <= lo) return B200ASR_OK;
-    int grid = stream_grid(hi - lo);
+    int grid = exchange_grid(hi - lo);
     if (max_blocks > 0 && grid > max_blocks) grid = max_blocks;   // leave SMs to work overlapped with the exchange
     fedavg_nvls_kernel<<<grid, 256, 0, as_stream(stream)>>>(multicast_buf, world, lo, hi, abort_flag);
     return check_launch("fedavg_nvls_reduce");
@@ -437,6 +447,12 @@ int b200asr_fedavg_peer_barrier(unsigned* const* peer_flags, int world, int rank
     }
     fedavg_peer_barrier_kernel<<<1, 32, 0, as_stream(stream)>>>(s, world, rank, epoch, timeout_flag, g_barrier_spin_clocks);
     return check_launch("fedavg_peer_barrier");
+}
+
+int b200asr_fedavg_set_max_blocks(int max_blocks) {
+    const int old = g_fedavg_max_blocks;
+    g_fedavg_max_blocks = max_blocks > 0 ? max_blocks : 0;
+    return old;
 }
 
 int b200asr_fedavg_peer_barrier_set_timeout(double seconds) {

@@ -109,6 +109,23 @@ def _symm_worker(rank, world, port, out_dir):
             out[impl] = {k: p.detach().cpu().clone() for k, p in params.items()}
             out[impl + "_shadow_ok"] = bool(torch.equal(fp.shadow, fp.flat.to(torch.bfloat16)))   # refreshed by mark_updated
             dist.barrier()
+            # the same exchange chunk by chunk on a comm stream (PipelinedFedAvg: capped grid, per-chunk barrier + shadow slice)
+            from b200asr.fedavg import PipelinedFedAvg
+            n = fp.numel
+            cuts = [0, (n // 3) // 4 * 4, (2 * n // 3) // 4 * 4, n]
+            pipe = PipelinedFedAvg([fp], [[(0, cuts[i], cuts[i + 1])] for i in range(3)], agg=agg, max_blocks=8)
+            fp.flat.copy_(start)
+            fp.shadow.zero_()
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm = torch.cuda.Stream()
+            evs = pipe.launch(comm, impl)
+            torch.cuda.current_stream().wait_event(evs[-1])
+            torch.cuda.synchronize()
+            agg.check()
+            out["pipe_" + impl] = {k: p.detach().cpu().clone() for k, p in params.items()}
+            out["pipe_" + impl + "_shadow_ok"] = bool(torch.equal(fp.shadow, fp.flat.to(torch.bfloat16)))
+            dist.barrier()
         torch.save(out, os.path.join(out_dir, f"rank{rank}.pt"))
     finally:
         dist.destroy_process_group()
@@ -139,3 +156,5 @@ def test_symm_fedavg_nvls_and_peer_match_average_weights(tmp_path):
                     assert (got - ref).abs().max() <= 1e-6 * max(1.0, float(ref.abs().max())), (impl, k, r)
                 assert torch.equal(got, res[0][impl][k])   # every client holds the same bits
                 assert res[r][impl + "_shadow_ok"]
+                assert torch.equal(res[r]["pipe_" + impl][k], got), (impl, k, r)   # chunked == whole-buffer exchange
+                assert res[r]["pipe_" + impl + "_shadow_ok"]
