@@ -531,7 +531,13 @@ def run_b200(args):
                 chosen["impl"] = min(cand, key=cand.get)
     clocks = ClockSampler(local_rank) if rank == 0 else None
     n0 = _lib.launch_count()
+    if args.profile_range:   # `ncu --profile-from-start off`: exactly the timed steps are captured
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
     ms_step, agg_ms, _, launches, skipped = timed(args.steps, e2e=False)
+    if args.profile_range:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     if graphed is None:
         launches = _lib.launch_count() - n0
     clk = clocks.stop() if clocks else None
@@ -676,6 +682,7 @@ def main():
     ap.add_argument("--no-symm", action="store_true", help="do not try torch symmetric memory for the flat buffers (CUDA IPC + peer kernel)")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: do not overlap the aggregation with the next round's conv stack")
     ap.add_argument("--nvls-blocks", type=int, default=0, help="cap of the NVLS kernel's grid (0 = full grid)")
+    ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around the timed steps (ncu --profile-from-start off)")
     ap.add_argument("--no-layerwise", action="store_true", help="N>1: aggregate the whole buffer at once instead of block by block")
     ap.add_argument("--fedavg-blocks", type=int, default=32, help="grid cap of the exchange kernels in the layer-wise pipelined FedAvg")
     ap.add_argument("--dropout", type=float, default=0.1,

@@ -2,7 +2,7 @@
 """Summarise an ncu per-launch capture of gemm_tc_kernel (gpu__time_duration, dram bytes read/write, tensor-pipe
 active %) into a table + a JSON blob bench.py reads for roofline.traffic.
 usage: gemm_traffic_summary.py capture.csv out.txt out.json"""
-import collections, csv, json, re, sys
+import collections, csv, hashlib, json, os, re, sys
 rows = [l for l in open(sys.argv[1]) if l.startswith('"')]
 per = collections.OrderedDict()
 for r in csv.DictReader(rows):
@@ -27,6 +27,8 @@ for key, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     out.append(f"{a[1]/1e6:7.3f} ms n={a[0]:3d} avg {a[1]/a[0]/1e3:6.1f} us  dram {a[2]/a[0]/1e6:6.1f} MB/launch {a[2]/a[1]:7.1f} GB/s  "
                f"tensor {a[3]/a[1]:5.1f}%  {key[0]} grid {key[1]}")
 open(sys.argv[2], "w").write("\n".join(out) + "\n")
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sha = hashlib.sha256(open(os.path.join(ROOT, "privacy-preserve-federated-asr_b200", "csrc", "gemm_tcgen05.cu"), "rb").read()).hexdigest()[:16]
 json.dump({"kernel": "gemm_tc_kernel", "launches": n, "dram_bytes_per_launch": Bt / n, "tensor_pipe_active_pct_time_weighted": tw,
-           "source": sys.argv[1]}, open(sys.argv[3], "w"))
+           "source": sys.argv[1], "gemm_source_sha16": sha}, open(sys.argv[3], "w"))
 print(out[1])

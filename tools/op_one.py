@@ -25,3 +25,22 @@ for _ in range(3):
     ops.conv0_ln_gelu(wav, cw, None, lw, lb, 5, 1e-5, bf)
 torch.cuda.synchronize()
 print("ok2")
+
+# CTC (B=8, T=499, V=32, <= 120 labels), DACS toggling masks (in-kernel Gumbel noise), dropout, attention with keep bits
+logits = r(1, B, T, 32)
+tl = torch.randint(20, 121, (B,), device="cuda", dtype=torch.int32)
+tg = torch.randint(1, 32, (B * 120,), device="cuda", dtype=torch.int32)
+off = torch.arange(B, device="cuda", dtype=torch.int32) * 120
+il = torch.full((B,), T, device="cuda", dtype=torch.int32)
+scores, hid = r(M, 4 * D), r(M, D)
+keep24 = ops.attn_dropout_mask(24, B, T, H, 0.1, 1234, 19, 4, 5)
+for _ in range(3):
+    ops.ctc_fwd_bwd(logits, tg, off, tl, il, 120, 0, True)
+    lm, ad, sl, sa, ml, ma = ops.dacs_mask_fwd(scores, hid, 1.0, 0.0, seed=1, offset=3)
+    ops.dacs_mask_bwd(x, dy, hid, sl, sa, ml, ma, 1.0, 0.0, want_dh=False)
+    ops.dropout(x, 0.1, 1234, 16, 7, residual=dy)
+    ops.attn_dropout_mask(24, B, T, H, 0.1, 1234, 19, 4, 5, out=keep24)
+    out, lse = ops.mha_fwd(qkv, None, B, T, H, 64, 0.125, keep=keep24[0], p_drop=0.1)
+    ops.mha_bwd(qkv, out, do, lse, None, B, T, H, 64, 0.125, keep=keep24[0], p_drop=0.1)
+torch.cuda.synchronize()
+print("ok3")
