@@ -362,7 +362,11 @@ def run_b200(args):
     # its own parameters (fedavg.PipelinedFedAvg) -- the aggregation hides behind the forward pass
     pipe = None
     if world > 1 and graphed is not None and graphed.segmented and not args.no_overlap and not args.no_layerwise:
-        pipe = PipelinedFedAvg([g["fp"] for g in opt.groups], graphed.fedavg_chunks(), agg=peer_agg, max_blocks=args.fedavg_blocks)
+        ch = graphed.fedavg_chunks()   # [non-block parameters, block 0, block 1, ...]; --fedavg-group blocks per exchange
+        G = max(1, args.fedavg_group)
+        grouped = [ch[0]] + [sum(ch[1 + i:1 + i + G], []) for i in range(0, len(ch) - 1, G)]
+        pipe = PipelinedFedAvg([g["fp"] for g in opt.groups], grouped, agg=peer_agg, max_blocks=args.fedavg_blocks)
+        pipe_event_of_block = [0] + [1 + i // G for i in range(len(ch) - 1)]   # chunk index per graph chunk
 
     def local_step(batch):
         if graphed is None:
@@ -399,7 +403,7 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     copy_stream = torch.cuda.Stream()
-    comm_stream = torch.cuda.Stream()
+    comm_stream = torch.cuda.Stream(priority=-1)   # high priority: the exchange kernels' blocks go first whenever an SM frees up
 
     def timed(nsteps, e2e):
         """CUDA-event time of nsteps steps (max over ranks), barrier + synchronize on both sides."""
@@ -451,7 +455,8 @@ def run_b200(args):
                 skipped_blocks[0] += len(model.backbone.last_skipped_layers)
                 a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a0.record(main)
-                evs = pipe.launch(comm_stream, chosen["impl"])
+                ge = pipe.launch(comm_stream, chosen["impl"])
+                evs = [ge[j] for j in pipe_event_of_block]   # one event per graph chunk (blocks of a group share theirs)
                 a1.record(comm_stream)
                 agg.append((a0, a1))
                 if i + 1 < nsteps:
@@ -684,7 +689,8 @@ def main():
     ap.add_argument("--nvls-blocks", type=int, default=0, help="cap of the NVLS kernel's grid (0 = full grid)")
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around the timed steps (ncu --profile-from-start off)")
     ap.add_argument("--no-layerwise", action="store_true", help="N>1: aggregate the whole buffer at once instead of block by block")
-    ap.add_argument("--fedavg-blocks", type=int, default=32, help="grid cap of the exchange kernels in the layer-wise pipelined FedAvg")
+    ap.add_argument("--fedavg-blocks", type=int, default=128, help="grid cap of the exchange kernels in the layer-wise pipelined FedAvg")
+    ap.add_argument("--fedavg-group", type=int, default=2, help="encoder blocks per exchange of the layer-wise pipelined FedAvg")
     ap.add_argument("--dropout", type=float, default=0.1,
                     help="hidden = activation = attention = final dropout P in the timed training step (0.1 = the "
                          "Data2VecAudioConfig defaults the reference fine-tunes with; 0 = the parity setting)")

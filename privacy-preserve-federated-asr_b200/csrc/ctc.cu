@@ -19,6 +19,16 @@ constexpr int E_EMPTY = -(1 << 28);  // exponent of a lane whose states are all 
 
 // 2^d for d <= 127 (0 below the normal range)
 __device__ __forceinline__ float pow2i(int d) { return d < -126 ? 0.f : __int_as_float((d + 127) << 23); }
+// m * 2^d for a mantissa m in [1, 2) (or 0) and d <= 0: the exponent field is rewritten by an integer add (no multiply on
+// the recursion's dependent chain); below 2^-100 the term is dropped (it is 2^-76 of an fp32 ulp of the sum it joins)
+__device__ __forceinline__ float scale_pow2(float m, int d) {
+    return (d < -100 || m == 0.f) ? 0.f : __int_as_float(__float_as_int(m) + (d << 23));
+}
+__device__ __forceinline__ float ex2_fast(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 
 // forward (DIR=+1) or backward (DIR=-1) lattice recursion by one warp.
 // state s of lane: s = lane*SPL + i.  ext[s] = blank (s even) or target[(s-1)/2] (s odd).
@@ -48,14 +58,10 @@ __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __r
     float a[SPL];
     int E[SPL];
     auto normalise = [](float v, int base, float& m, int& e) {   // v >= 0 -> mantissa in [1, 2) and exponent (base + k)
-        if (v > 0.f) {
-            const int k = ((__float_as_int(v) >> 23) & 0xff) - 127;
-            m = v * pow2i(-k);
-            e = base + k;
-        } else {
-            m = 0.f;
-            e = E_EMPTY;
-        }
+        const int bits = __float_as_int(v);
+        const bool live = v > 0.f;   // (v is a sum of [1, 2) mantissas times a [1, 2) emission: normal or exactly 0)
+        m = live ? __int_as_float((bits & 0x007fffff) | 0x3f800000) : 0.f;
+        e = live ? base + (bits >> 23) - 127 : E_EMPTY;
     };
     const int t0 = DIR > 0 ? 0 : Tb - 1;
 #pragma unroll
@@ -67,7 +73,7 @@ __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __r
         if (init && s < S) {   // pr holds log2-probabilities: mantissa 2^frac in [1, 2), exponent floor(l2)
             const float l2 = pr[t0 * V + lab[i]];
             const float fl = fmaxf(floorf(l2), -1.0e8f);   // (-inf logits: probability 0)
-            a[i] = exp2f(l2 - fl);
+            a[i] = ex2_fast(l2 - fl);
             E[i] = a[i] > 0.f ? (int)fl : E_EMPTY;
         } else {
             a[i] = 0.f;
@@ -86,7 +92,7 @@ __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __r
         for (int i = 0; i < SPL; ++i) {
             const float l2 = pr[t * V + lab[i]];
             const float fl = fmaxf(floorf(l2), -1.0e8f);   // (-inf logits: probability 0)
-            e[i] = exp2f(l2 - fl);
+            e[i] = ex2_fast(l2 - fl);
             ee[i] = (int)fl;
         }
         // the neighbour lane's two boundary states
@@ -124,7 +130,7 @@ __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __r
             const int s = lane * SPL + i;
             const int Ec = max(Eo[i], max(e1, e2));   // common exponent of this state's operands
             // (an empty operand has mantissa 0 and E_EMPTY - Ec underflows to a factor 0; all empty: 0 * 1 = 0)
-            const float v = (ao[i] * pow2i(Eo[i] - Ec) + m1 * pow2i(e1 - Ec) + m2 * pow2i(e2 - Ec)) * e[i];
+            const float v = (scale_pow2(ao[i], Eo[i] - Ec) + scale_pow2(m1, e1 - Ec) + scale_pow2(m2, e2 - Ec)) * e[i];
             normalise(s < S ? v : 0.f, Ec + ee[i], a[i], E[i]);
             if (s < S) {
                 out[(long long)t * Sld + s] = a[i];
