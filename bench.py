@@ -356,7 +356,9 @@ def run_b200(args):
     if not args.eager:
         from b200asr.graph import GraphedTrainStep
         # N > 1: the frozen conv stack is a graph of its own, so that the next round's begin() can run under the aggregation
-        graphed = GraphedTrainStep(model, opt, resident[0], max_label_len=120, split_conv=(world > 1 and not args.no_overlap))
+        layerwise = world > 1 and ld > 0 and not args.no_overlap and not args.no_layerwise
+        graphed = GraphedTrainStep(model, opt, resident[0], max_label_len=120, split_conv=(world > 1 and not args.no_overlap),
+                                   defer_adamw=(layerwise and not args.no_chunked_adamw))
     skipped_blocks = [0]
     # N > 1 with per-block graphs: layer-wise FedAvg on a comm stream, each block's graph of the NEXT round waits only for
     # its own parameters (fedavg.PipelinedFedAvg) -- the aggregation hides behind the forward pass
@@ -367,6 +369,12 @@ def run_b200(args):
         grouped = [ch[0]] + [sum(ch[1 + i:1 + i + G], []) for i in range(0, len(ch) - 1, G)]
         pipe = PipelinedFedAvg([g["fp"] for g in opt.groups], grouped, agg=peer_agg, max_blocks=args.fedavg_blocks)
         pipe_event_of_block = [0] + [1 + i // G for i in range(len(ch) - 1)]   # chunk index per graph chunk
+        cp = graphed.fedavg_chunk_params()
+        grouped_cp = [cp[0]] + [sum(cp[1 + i:1 + i + G], []) for i in range(0, len(cp) - 1, G)]
+
+        def update_chunk(c):   # the AdamW launch(es) of one exchange chunk, on the main stream
+            for gi, lo, hi in grouped_cp[c]:
+                opt.adamw_params(gi, lo, hi)
 
     def local_step(batch):
         if graphed is None:
@@ -451,11 +459,11 @@ def run_b200(args):
             if pipe is not None:
                 # round i: every block's graph waits only for the average of ITS parameters from round i - 1; the
                 # aggregation of round i then starts on the comm stream and runs under the forward pass of round i + 1
-                loss = graphed.finish(wait_events=evs)
+                loss = graphed.finish(wait_events=evs, adamw=not graphed.defer_adamw)
                 skipped_blocks[0] += len(model.backbone.last_skipped_layers)
                 a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a0.record(main)
-                ge = pipe.launch(comm_stream, chosen["impl"])
+                ge = pipe.launch(comm_stream, chosen["impl"], update_chunk=update_chunk if graphed.defer_adamw else None)
                 evs = [ge[j] for j in pipe_event_of_block]   # one event per graph chunk (blocks of a group share theirs)
                 a1.record(comm_stream)
                 agg.append((a0, a1))
@@ -617,7 +625,9 @@ def run_b200(args):
                        "fedavg_overlap": (("layer-wise pipelined: chunk = one encoder block, exchange + barrier + bf16 shadow refresh per chunk "
                                            f"on a comm stream (exchange grid capped at {args.fedavg_blocks} blocks); every block's CUDA graph "
                                            "of the next round waits only for its own chunk, so the aggregation runs under the next forward "
-                                           "pass; fedavg_agg_ms is the span of the aggregation, not its exposed part") if pipe is not None else
+                                           "pass" + ("; AdamW is launched chunk by chunk too and chunk c's exchange starts while chunk c + 1 "
+                                                     "is still being updated" if (graphed is not None and graphed.defer_adamw) else "")
+                                           + "; fedavg_agg_ms is the span of the aggregation, not its exposed part") if pipe is not None else
                                           ("the aggregation runs on a comm stream while the main stream replays the next round's frozen "
                                            "conv-stack graph" if (world > 1 and graphed is not None and graphed.split_conv) else None)),
                        "fedavg": ({"peer": "uniform FedAvg of all trainable params after every local step: fused peer-memory kernel "
@@ -688,6 +698,7 @@ def main():
     ap.add_argument("--no-overlap", action="store_true", help="N>1: do not overlap the aggregation with the next round's conv stack")
     ap.add_argument("--nvls-blocks", type=int, default=0, help="cap of the NVLS kernel's grid (0 = full grid)")
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around the timed steps (ncu --profile-from-start off)")
+    ap.add_argument("--no-chunked-adamw", action="store_true", help="layer-wise FedAvg: keep AdamW inside the last graph instead of chunk by chunk")
     ap.add_argument("--no-layerwise", action="store_true", help="N>1: aggregate the whole buffer at once instead of block by block")
     ap.add_argument("--fedavg-blocks", type=int, default=128, help="grid cap of the exchange kernels in the layer-wise pipelined FedAvg")
     ap.add_argument("--fedavg-group", type=int, default=2, help="encoder blocks per exchange of the layer-wise pipelined FedAvg")

@@ -385,16 +385,33 @@ class PipelinedFedAvg:
         self.max_blocks = int(max_blocks)
         self.events = [torch.cuda.Event() for _ in chunks]
 
-    def launch(self, comm_stream, impl: str = "peer"):
-        """Returns the per-chunk events (valid until the next launch)."""
+    def launch(self, comm_stream, impl: str = "peer", update_chunk=None):
+        """Returns the per-chunk events (valid until the next launch).
+        update_chunk(c): optional -- launches the optimizer update of chunk c on the CURRENT stream (graph.GraphedTrainStep(
+        defer_adamw=True) + FusedAdamW.adamw_params): the exchange of chunk c then starts as soon as ITS update is done, while
+        the update of chunk c + 1 is still running (HBM bound) -- the aggregation starts a whole AdamW pass earlier."""
         from ._lib import lib
-        comm_stream.wait_stream(torch.cuda.current_stream())   # the local update is complete
+        main = torch.cuda.current_stream()
+        ready = None
+        if update_chunk is None:
+            comm_stream.wait_stream(main)   # the local update is complete
+        else:
+            ready = []
+            for c in range(len(self.chunks)):
+                update_chunk(c)
+                e = torch.cuda.Event()
+                e.record(main)
+                ready.append(e)
         old = lib.b200asr_fedavg_set_max_blocks(self.max_blocks)
         try:
             with torch.cuda.stream(comm_stream):
-                if impl != "nccl":
+                if impl != "nccl" and ready is None:
                     self.agg.barrier()   # every client's local update is complete and visible
-                for ev, ranges in zip(self.events, self.chunks):
+                for c, (ev, ranges) in enumerate(zip(self.events, self.chunks)):
+                    if ready is not None:
+                        comm_stream.wait_event(ready[c])
+                        if impl != "nccl":
+                            self.agg.barrier()   # every client has updated chunk c (and chunk c - 1 has landed everywhere)
                     for gi, a, b in ranges:
                         if impl == "nccl":
                             fedavg_allreduce(self.flats[gi].flat[a:b])

@@ -87,11 +87,14 @@ class GraphedTrainStep:
     next call overwrites.  `last_skipped_layers` holds the blocks LayerDrop skipped in the latest call."""
 
     def __init__(self, model, opt, example_batch: Dict[str, torch.Tensor], max_label_len: Optional[int] = None,
-                 warmup: int = 3, split_conv: bool = False):
+                 warmup: int = 3, split_conv: bool = False, defer_adamw: bool = False):
         """split_conv: capture the frozen conv feature extractor as a graph of its own, replayed by `begin(batch)`; the
         rest of the update is replayed by `finish()`.  The conv stack does not depend on the trainable weights, so a
         federated client can run `begin(next batch)` while the FedAvg of the previous round is still in flight."""
         self.model, self.opt = model, opt
+        # defer_adamw: the graphs end with the global gradient norm; the AdamW launches are issued after the replay --
+        # by finish() (two launches) or, with finish(adamw=False), by the caller chunk by chunk (fedavg.PipelinedFedAvg)
+        self.defer_adamw = bool(defer_adamw)
         self.max_label_len = int(max_label_len or example_batch["labels"].shape[1])
         if hasattr(model, "validate_labels"):
             model.validate_labels = False  # the reference's host-side range check would synchronise (models.py:483)
@@ -141,7 +144,10 @@ class GraphedTrainStep:
         self.opt.zero_grad()
         out = self.model(**self.static)
         out.loss.backward()
-        self.opt.step_captured()
+        self.opt.step_captured(update=not self.defer_adamw)
+        if self.defer_adamw and not torch.cuda.is_current_stream_capturing():
+            for gi in range(len(self.opt.groups)):   # (eager warm-up steps: complete the update)
+                self.opt.adamw_params(gi)
         return out.loss.detach()
 
     # ------------------------------------------------------------------ LayerDrop: one graph per block and direction
@@ -194,6 +200,23 @@ class GraphedTrainStep:
                     b = fp.offsets[ii[-1]] + (fp.params[ii[-1]].numel() + 3) // 4 * 4
                     slices.append(fp.grad[a:b])
             self.layer_grad_slices.append(slices)
+
+    def fedavg_chunk_params(self):
+        """fedavg_chunks() in parameter indices: per chunk a list of (group index, first parameter, end parameter)."""
+        chunks = [[] for _ in range(self.L + 1)]
+        for gi, g in enumerate(self.opt.groups):
+            pos = 0
+            for l in range(self.L):
+                ii = self.layer_idle[l][gi]
+                if not ii:
+                    continue
+                if ii[0] > pos:
+                    chunks[0].append((gi, pos, ii[0]))
+                chunks[1 + l].append((gi, ii[0], ii[-1] + 1))
+                pos = ii[-1] + 1
+            if len(g["fp"].params) > pos:
+                chunks[0].append((gi, pos, len(g["fp"].params)))
+        return chunks
 
     def fedavg_chunks(self):
         """The flat-buffer ranges in the order the forward pass reads them, for fedavg.PipelinedFedAvg: chunk 0 = every
@@ -278,7 +301,7 @@ class GraphedTrainStep:
         if self.conv_graph is not None:
             self.conv_graph.replay()
 
-    def finish(self, wait_events=None) -> torch.Tensor:
+    def finish(self, wait_events=None, adamw: bool = True) -> torch.Tensor:
         """The rest of the update (reads the trainable weights: run after the aggregation of the previous round).
         wait_events: the per-chunk events of fedavg.PipelinedFedAvg.launch() (chunks = self.fedavg_chunks()): each block's
         graph then waits only for ITS parameters, the aggregation of the later blocks overlaps the forward pass."""
@@ -291,4 +314,7 @@ class GraphedTrainStep:
                 torch.cuda.current_stream().wait_event(wait_events[-1])
             self.opt.prepare_hyper()
             self.graph.replay()
+        if self.defer_adamw and adamw:
+            for gi in range(len(self.opt.groups)):
+                self.opt.adamw_params(gi)
         return self.loss

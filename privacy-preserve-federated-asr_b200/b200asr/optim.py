@@ -106,6 +106,12 @@ class FusedAdamW:
                 for c in range(0, nv, CHUNK_VECS):
                     rows.append((v0 + c, min(CHUNK_VECS, nv - c), i, 0))
             g["chunks"] = torch.tensor(rows, dtype=torch.int32, device=fp.flat.device)
+            # first chunk-table row of every parameter (+ the end): a run of parameters is a run of rows
+            first, r = [], 0
+            for p in fp.params:
+                first.append(r)
+                r += ((p.numel() + 3) // 4 + CHUNK_VECS - 1) // CHUNK_VECS
+            g["param_row"] = first + [r]
             g["hyper_dev"] = torch.zeros(len(fp.params), 2, dtype=torch.float32, device=fp.flat.device)
         return g["chunks"], g["hyper_dev"]
 
@@ -179,8 +185,10 @@ class FusedAdamW:
                 skip |= set(idle[gi])
             self._upload_hyper(g, sorted(skip), lr)
 
-    def step_captured(self):
-        """Device side of the update, with no host-dependent scalar: what a CUDA graph captures."""
+    def step_captured(self, update: bool = True):
+        """Device side of the update, with no host-dependent scalar: what a CUDA graph captures.
+        update=False: gradient bookkeeping and the global norm only; the AdamW launches follow outside the graph
+        (`adamw_params`), e.g. chunk by chunk, interleaved with the exchange of a pipelined FedAvg."""
         ops.join_side_stream()
         untouched = self._gather_stray_grads()
         gn = self._clip_norm()
@@ -190,9 +198,24 @@ class FusedAdamW:
             # on prepare_hyper marks them idle, as the eager step() does
             g["static_idle"] = tuple(idle)
             chunks, hyper = self._table(g)
+            if not update:
+                continue
             ops.adamw_step_chunks_(fp.flat, fp.grad, g["m"], g["v"], fp.shadow, chunks, hyper, self.betas[0], self.betas[1],
                                    self.eps, g["wd"], gn, self.max_grad_norm or 0.0)
             fp.mark_updated(shadow_written=fp.shadow is not None)
+
+    def adamw_params(self, gi: int, p_lo: int = 0, p_hi: Optional[int] = None):
+        """The AdamW launch for parameters [p_lo, p_hi) of group gi (default: the whole group) on the current stream, from
+        the per-parameter table prepare_hyper uploaded and the clip norm step_captured(update=False) left behind."""
+        g = self.groups[gi]
+        fp = g["fp"]
+        chunks, hyper = self._table(g)
+        p_hi = len(fp.params) if p_hi is None else p_hi
+        r0, r1 = g["param_row"][p_lo], g["param_row"][p_hi]
+        if r1 > r0:
+            ops.adamw_step_chunks_(fp.flat, fp.grad, g["m"], g["v"], fp.shadow, chunks[r0:r1], hyper, self.betas[0], self.betas[1],
+                                   self.eps, g["wd"], self.gnorm_sq if self.max_grad_norm is not None else None,
+                                   self.max_grad_norm or 0.0)
 
     def param_indices(self, predicate) -> List[List[int]]:
         """Per group, the indices of the parameters whose name satisfies `predicate` (e.g. one encoder block)."""
