@@ -45,8 +45,9 @@ def make(cfg, sd, dtype=torch.bfloat16, **cfg_kw):
     return m, FusedAdamW(m.named_parameters(), lr=1e-3, weight_decay=0.01, warmup_steps=2)
 
 
+@pytest.mark.parametrize("mode", ["plain", "split_conv+deferred_adamw"])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-def test_layerdrop_graph_matches_eager_with_the_same_coins(dtype):
+def test_layerdrop_graph_matches_eager_with_the_same_coins(dtype, mode):
     """Six updates with layerdrop 0.4 on a 4-block model: the segmented CUDA-graph replay and the eager path, driven by
     the same host coin stream (np.random.uniform, as the pinned transformers 4.17), skip the same blocks, report the same
     losses and end with the same parameters, Adam moments and per-parameter step counts."""
@@ -66,8 +67,17 @@ def test_layerdrop_graph_matches_eager_with_the_same_coins(dtype):
     assert any(eager_skips) and len(set(eager_skips)) > 1, eager_skips
     m2, o2 = make(cfg, sd, dtype, layerdrop=0.4)
     before = [t.clone() for t in o2.state_tensors()]
-    step = GraphedTrainStep(m2, o2, dev(batches[0]), max_label_len=16)
-    assert step.segmented and len(step.graphs) == 2 * 4 + 3
+    split = mode != "plain"   # conv stack as its own graph (begin / finish), AdamW launched after the graphs
+    step = GraphedTrainStep(m2, o2, dev(batches[0]), max_label_len=16, split_conv=split, defer_adamw=split)
+    assert step.segmented and len(step.graphs) == 2 * 4 + 3 and (step.conv_graph is not None) == split
+    if split:   # the chunk lists of the pipelined FedAvg cover every parameter exactly once
+        ch, cp = step.fedavg_chunks(), step.fedavg_chunk_params()
+        assert len(ch) == len(cp) == 4 + 1
+        for gi, g in enumerate(o2.groups):
+            covered = sorted((a, b) for c in ch for (i, a, b) in c if i == gi)
+            assert covered[0][0] == 0 and covered[-1][1] == g["fp"].numel
+            assert all(covered[k][1] == covered[k + 1][0] for k in range(len(covered) - 1))
+            assert sorted(p for c in cp for (i, lo, hi) in c if i == gi for p in range(lo, hi)) == list(range(len(g["fp"].params)))
     for t, b in zip(o2.state_tensors(), before):
         assert torch.equal(t, b)   # building the graphs left weights / moments alone
     assert o2.step_count == 0
