@@ -39,6 +39,7 @@ __device__ __forceinline__ float ex2_fast(float x) {
 template <int SPL, int DIR>
 __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __restrict__ tgt, int L, int Tb, int blank,
                              float* __restrict__ out /* [T][Sld] */, int Sld, int* __restrict__ eout /* [T][Sld] */) {
+    // Sld = 32 * SPL here; state s = lane * SPL + i lives at [t][i * 32 + lane]
     const int lane = threadIdx.x & 31;
     const int S = 2 * L + 1;
     int lab[SPL];
@@ -79,9 +80,9 @@ __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __r
             a[i] = 0.f;
             E[i] = E_EMPTY;
         }
-        if (s < S) {
-            out[(long long)t0 * Sld + s] = a[i];
-            eout[(long long)t0 * Sld + s] = E[i];
+        if (s < S) {   // lane-contiguous layout [t][i][lane]: every store of the warp is one 128-byte line
+            out[(long long)t0 * Sld + i * 32 + lane] = a[i];
+            eout[(long long)t0 * Sld + i * 32 + lane] = E[i];
         }
     }
     for (int step = 1; step < Tb; ++step) {
@@ -133,8 +134,8 @@ __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __r
             const float v = (scale_pow2(ao[i], Eo[i] - Ec) + scale_pow2(m1, e1 - Ec) + scale_pow2(m2, e2 - Ec)) * e[i];
             normalise(s < S ? v : 0.f, Ec + ee[i], a[i], E[i]);
             if (s < S) {
-                out[(long long)t * Sld + s] = a[i];
-                eout[(long long)t * Sld + s] = E[i];
+                out[(long long)t * Sld + i * 32 + lane] = a[i];
+                eout[(long long)t * Sld + i * 32 + lane] = E[i];
             }
         }
     }
@@ -207,7 +208,7 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     extern __shared__ float sm[];
     const int b = blockIdx.x, head = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const int Sld = 2 * max_tgt + 1;
+    const int Sld = 32 * spl;   // states per frame in the workspace: state s at [(s % spl) * 32 + s / spl]
     const int L = min(tgt_len[b], max_tgt);
     const int S = 2 * L + 1;
     const int Tb = max(0, min(in_len[b], T_));
@@ -239,10 +240,11 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     int lp_exp = 0;
     if (Tb > 0) {
         const long long r = (long long)(Tb - 1);
-        const float a1 = alpha[r * Sld + S - 1];
-        const int e1 = ea[r * Sld + S - 1];
-        const float a2 = S > 1 ? alpha[r * Sld + S - 2] : 0.f;
-        const int e2 = S > 1 ? ea[r * Sld + S - 2] : E_EMPTY;
+        auto at = [&](int st) { return r * Sld + (st % spl) * 32 + st / spl; };
+        const float a1 = alpha[at(S - 1)];
+        const int e1 = ea[at(S - 1)];
+        const float a2 = S > 1 ? alpha[at(S - 2)] : 0.f;
+        const int e2 = S > 1 ? ea[at(S - 2)] : E_EMPTY;
         const int em = max(e1, e2);
         const float tot = a1 * pow2i(e1 - em) + a2 * pow2i(e2 - em);
         if (tot > 0.f) {
@@ -279,7 +281,7 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const T* __restrict__ log
     const long long hb = frame / T_;
     const int t = (int)(frame - hb * T_);
     const int b = (int)(hb % B);
-    const int Sld = 2 * max_tgt + 1;
+    const int Sld = 32 * spl;
     const int L = min(tgt_len[b], max_tgt);
     const int S = 2 * L + 1;
     const int Tb = max(0, min(in_len[b], T_));
@@ -315,20 +317,22 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const T* __restrict__ log
     // sum relative to max alpha beta, as in round 1, drops exactly those states).
     float mx = NEG_INF;
     for (int s = lane; s < S; s += 32) {
-        const float ab = ar[s] * br[s];
+        const int ix = (s % spl) * 32 + s / spl;
+        const float ab = ar[ix] * br[ix];
         if (ab > 0.f) {
             const int l = (s & 1) ? tgt[(s - 1) >> 1] : blank;
-            mx = fmaxf(mx, (log2f(ab) - pl2[l] - lp_frac) + (float)(ear[s] + ebr[s] - lp_exp));
+            mx = fmaxf(mx, (log2f(ab) - pl2[l] - lp_frac) + (float)(ear[ix] + ebr[ix] - lp_exp));
         }
     }
     mx = warp_max(mx);
     for (int v = lane; v < V; v += 32) acc[v] = 0ull;
     __syncwarp();
     for (int s = lane; s < S; s += 32) {
-        const float ab = ar[s] * br[s];
+        const int ix = (s % spl) * 32 + s / spl;
+        const float ab = ar[ix] * br[ix];
         if (ab > 0.f) {
             const int l = (s & 1) ? tgt[(s - 1) >> 1] : blank;
-            const float rel2 = (log2f(ab) - pl2[l] - lp_frac) + (float)(ear[s] + ebr[s] - lp_exp) - mx;  // <= 0
+            const float rel2 = (log2f(ab) - pl2[l] - lp_frac) + (float)(ear[ix] + ebr[ix] - lp_exp) - mx;  // <= 0
             atomicAdd(&acc[l], (unsigned long long)(exp2f(rel2) * 1099511627776.0f));  // in [0, 2^40]: integer sums commute
         }
     }
@@ -386,8 +390,15 @@ using namespace b200asr;
 
 extern "C" {
 
+static int ctc_spl(int max_tgt_len) {   // lattice states per lane (2, 4, 8, 16; > 16: unsupported)
+    const int S = 2 * (max_tgt_len < 1 ? 1 : max_tgt_len) + 1;
+    int spl = 2;
+    while (spl * 32 < S) spl *= 2;
+    return spl;
+}
+
 size_t b200asr_ctc_workspace_bytes(int n_heads, int B, int T, int max_tgt_len) {
-    return (size_t)n_heads * B * (size_t)ctc_ws_stride(T, 2 * max_tgt_len + 1) * sizeof(float);
+    return (size_t)n_heads * B * (size_t)ctc_ws_stride(T, 32 * ctc_spl(max_tgt_len)) * sizeof(float);
 }
 
 int b200asr_ctc_fwd_bwd(const void* logits, const int* targets, const int* tgt_off, const int* tgt_len,
@@ -399,9 +410,7 @@ int b200asr_ctc_fwd_bwd(const void* logits, const int* targets, const int* tgt_o
     B200_REQUIRE(blank >= 0 && blank < V, "ctc: blank out of range");
     if (max_tgt_len < 1) max_tgt_len = 1;
     B200_REQUIRE(workspace_bytes >= b200asr_ctc_workspace_bytes(n_heads, B, T_, max_tgt_len), "ctc: workspace too small");
-    const int S = 2 * max_tgt_len + 1;
-    int spl = 2;
-    while (spl * 32 < S) spl *= 2;
+    const int spl = ctc_spl(max_tgt_len);
     if (spl > 16) {
         set_error("ctc: target length %d exceeds the supported 255", max_tgt_len);
         return B200ASR_ERR_UNSUPPORTED;
