@@ -216,6 +216,9 @@ class FusedAdamW:
             ops.adamw_step_chunks_(fp.flat, fp.grad, g["m"], g["v"], fp.shadow, chunks[r0:r1], hyper, self.betas[0], self.betas[1],
                                    self.eps, g["wd"], self.gnorm_sq if self.max_grad_norm is not None else None,
                                    self.max_grad_norm or 0.0)
+        # (also for a partial range: the epoch only has to differ from the one the derived layouts -- packed positional
+        # conv filters, fp32 QKV concat -- were cached at; a capture that hit those caches would replay stale weights)
+        fp.mark_updated(shadow_written=fp.shadow is not None)
 
     def param_indices(self, predicate) -> List[List[int]]:
         """Per group, the indices of the parameters whose name satisfies `predicate` (e.g. one encoder block)."""
