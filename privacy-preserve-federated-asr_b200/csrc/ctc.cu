@@ -1,7 +1,8 @@
 // CTC loss: fp32 softmax + alpha/beta recursions + gradient w.r.t. the logits, and greedy decode.
 // One CTA per (head, utterance).  The frame posteriors of the utterance live in shared memory (T*V*4 bytes);
-// warp 0 runs the alpha recursion while warp 1 runs beta concurrently (one warp per recursion: each lane owns
-// SPL consecutive lattice states, the two neighbour states come from the previous lane by shuffle).
+// warps 0..7 run the alpha recursion while warps 8..15 run beta concurrently (each thread owns SPL consecutive lattice
+// states -- one at the sizes of the path -- and the two neighbour states come from the previous thread through shared
+// memory, one named barrier per frame and direction).
 // The recursions run in the linear domain with a SOFTWARE EXPONENT PER STATE: every state is an fp32 mantissa in [1, 2)
 // plus an integer exponent (true value = mantissa * 2^E), renormalised every frame by exact power-of-two scalings -- a
 // step is FADD/FMUL and integer ops, no exp/log on the T-step critical path and no warp-wide reduction, the mantissa
@@ -13,16 +14,18 @@
 namespace b200asr {
 
 namespace {
-constexpr int CTC_THREADS = 512;  // lattice kernel: all warps build the posteriors, warps 0 / 1 run the recursions
+constexpr int CTC_THREADS = 512;  // lattice kernel: all warps build the posteriors, then 8 warps per recursion
+constexpr int LAT_THREADS = 256;  // threads per recursion (alpha: threads 0..255, beta: 256..511)
 constexpr float NEG_INF = -INFINITY;
 constexpr int E_EMPTY = -(1 << 28);  // exponent of a lane whose states are all zero
 
 // 2^d for d <= 127 (0 below the normal range)
 __device__ __forceinline__ float pow2i(int d) { return d < -126 ? 0.f : __int_as_float((d + 127) << 23); }
 // m * 2^d for a mantissa m in [1, 2) (or 0) and d <= 0: the exponent field is rewritten by an integer add (no multiply on
-// the recursion's dependent chain); below 2^-100 the term is dropped (it is 2^-76 of an fp32 ulp of the sum it joins)
+// the recursion's dependent chain); below 2^-100 the term is dropped (it is 2^-76 of an fp32 ulp of the sum it joins).
+// m == 0 comes with the exponent E_EMPTY: either d < -100, or every operand is empty and d = 0 keeps the zero bits.
 __device__ __forceinline__ float scale_pow2(float m, int d) {
-    return (d < -100 || m == 0.f) ? 0.f : __int_as_float(__float_as_int(m) + (d << 23));
+    return d < -100 ? 0.f : __int_as_float(__float_as_int(m) + (d << 23));
 }
 __device__ __forceinline__ float ex2_fast(float x) {
     float y;
@@ -30,23 +33,28 @@ __device__ __forceinline__ float ex2_fast(float x) {
     return y;
 }
 
-// forward (DIR=+1) or backward (DIR=-1) lattice recursion by one warp.
-// state s of lane: s = lane*SPL + i.  ext[s] = blank (s even) or target[(s-1)/2] (s odd).
+// forward (DIR=+1) or backward (DIR=-1) lattice recursion by LAT_THREADS threads (8 warps).
+// Thread `tid` owns the SPL consecutive states s = tid*SPL + i; ext[s] = blank (s even) or target[(s-1)/2] (s odd).  The
+// states next to a thread's range come from the neighbour thread through a double-buffered shared-memory exchange and ONE
+// named barrier per frame (one warp with 8 states per lane, as in round 1 / early round 2, issued ~360 instructions per
+// frame from a single warp: 0.7 us per frame, 340 us per utterance; spread over 8 warps a frame is the barrier plus one
+// state's ~40 instructions).
 // Every state carries its OWN exponent: value = out[t][s] * 2^eout[t][s], mantissa in [1, 2) (or 0 with E_EMPTY).
 // (Round 1 shared one exponent per lane: with peaked posteriors -- emission ratios of 2^-60 per frame -- two states of a
 // lane drift more than the 2^-126 fp32 range apart within a few frames and the smaller one, which may carry the whole
 // posterior mass once multiplied with the opposite recursion, was flushed to zero: wrong gradients at full-size configs.)
 template <int SPL, int DIR>
 __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __restrict__ tgt, int L, int Tb, int blank,
-                             float* __restrict__ out /* [T][Sld] */, int Sld, int* __restrict__ eout /* [T][Sld] */) {
-    // Sld = 32 * SPL here; state s = lane * SPL + i lives at [t][i * 32 + lane]
-    const int lane = threadIdx.x & 31;
+                             float* __restrict__ out /* [T][Sld] */, int Sld, int* __restrict__ eout /* [T][Sld] */,
+                             int2* __restrict__ xb /* [2][LAT_THREADS][2] */, int tid, int bar_id) {
+    // Sld = LAT_THREADS * SPL here; state s = tid * SPL + i lives at [t][i * LAT_THREADS + tid]
+    constexpr int NT = LAT_THREADS;
     const int S = 2 * L + 1;
     int lab[SPL];
     bool skip[SPL];  // may take the 2-step transition (from s-2 forward / from s+2 backward)
 #pragma unroll
     for (int i = 0; i < SPL; ++i) {
-        const int s = lane * SPL + i;
+        const int s = tid * SPL + i;
         lab[i] = blank;
         skip[i] = false;
         if (s < S && (s & 1)) {
@@ -64,10 +72,22 @@ __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __r
         m = live ? __int_as_float((bits & 0x007fffff) | 0x3f800000) : 0.f;
         e = live ? base + (bits >> 23) - 127 : E_EMPTY;
     };
+    // the two states a neighbour needs: slot 0 = the state next to its range, slot 1 = the one after (SPL == 1: the
+    // neighbour's neighbour publishes that one itself)
+    auto publish = [&](int buf) {
+        int2* x = xb + (buf * NT + tid) * 2;
+        if (DIR > 0) {
+            x[0] = make_int2(__float_as_int(a[SPL - 1]), E[SPL - 1]);
+            if (SPL > 1) x[1] = make_int2(__float_as_int(a[SPL > 1 ? SPL - 2 : 0]), E[SPL > 1 ? SPL - 2 : 0]);
+        } else {
+            x[0] = make_int2(__float_as_int(a[0]), E[0]);
+            if (SPL > 1) x[1] = make_int2(__float_as_int(a[SPL > 1 ? 1 : 0]), E[SPL > 1 ? 1 : 0]);
+        }
+    };
     const int t0 = DIR > 0 ? 0 : Tb - 1;
 #pragma unroll
     for (int i = 0; i < SPL; ++i) {
-        const int s = lane * SPL + i;
+        const int s = tid * SPL + i;
         bool init;
         if (DIR > 0) init = (s == 0) || (s == 1 && S > 1);
         else init = (s == S - 1) || (s == S - 2 && S > 1);
@@ -80,11 +100,15 @@ __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __r
             a[i] = 0.f;
             E[i] = E_EMPTY;
         }
-        if (s < S) {   // lane-contiguous layout [t][i][lane]: every store of the warp is one 128-byte line
-            out[(long long)t0 * Sld + i * 32 + lane] = a[i];
-            eout[(long long)t0 * Sld + i * 32 + lane] = E[i];
+        if (s < S) {   // thread-contiguous layout [t][i][tid]: every store of a warp is one 128-byte line
+            out[(long long)t0 * Sld + i * NT + tid] = a[i];
+            eout[(long long)t0 * Sld + i * NT + tid] = E[i];
         }
     }
+    publish(0);
+    const int nb = DIR > 0 ? tid - 1 : tid + 1;            // the neighbour thread whose states precede this range
+    const int nb2 = SPL > 1 ? nb : (DIR > 0 ? tid - 2 : tid + 2);
+    const bool has1 = nb >= 0 && nb < NT, has2 = nb2 >= 0 && nb2 < NT;
     for (int step = 1; step < Tb; ++step) {
         const int t = DIR > 0 ? step : Tb - 1 - step;
         float e[SPL];  // emission probabilities of this frame (mantissa, exponent): independent of the recursion, issued first
@@ -96,22 +120,14 @@ __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __r
             e[i] = ex2_fast(l2 - fl);
             ee[i] = (int)fl;
         }
-        // the neighbour lane's two boundary states
-        float n1, n2;
-        int En1, En2;
-        if (DIR > 0) {
-            n1 = __shfl_up_sync(0xffffffffu, a[SPL - 1], 1);
-            n2 = __shfl_up_sync(0xffffffffu, a[SPL - 2], 1);
-            En1 = __shfl_up_sync(0xffffffffu, E[SPL - 1], 1);
-            En2 = __shfl_up_sync(0xffffffffu, E[SPL - 2], 1);
-            if (lane == 0) { n1 = n2 = 0.f; En1 = En2 = E_EMPTY; }
-        } else {
-            n1 = __shfl_down_sync(0xffffffffu, a[0], 1);
-            n2 = __shfl_down_sync(0xffffffffu, a[1], 1);
-            En1 = __shfl_down_sync(0xffffffffu, E[0], 1);
-            En2 = __shfl_down_sync(0xffffffffu, E[1], 1);
-            if (lane == 31) { n1 = n2 = 0.f; En1 = En2 = E_EMPTY; }
-        }
+        // the previous frame's states of every thread of this direction are published
+        asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(NT) : "memory");
+        const int2* xp = xb + ((step - 1) & 1) * NT * 2;
+        int2 x1 = make_int2(0, E_EMPTY), x2 = make_int2(0, E_EMPTY);
+        if (has1) x1 = xp[nb * 2];
+        if (has2) x2 = xp[nb2 * 2 + (SPL > 1 ? 1 : 0)];
+        const float n1 = __int_as_float(x1.x), n2 = __int_as_float(x2.x);
+        const int En1 = x1.y, En2 = x2.y;
         float ao[SPL];
         int Eo[SPL];
 #pragma unroll
@@ -128,14 +144,18 @@ __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __r
                 if (i + 2 < SPL) { m2 = ao[i + 2]; e2 = Eo[i + 2]; } else if (i + 2 == SPL) { m2 = n1; e2 = En1; } else { m2 = n2; e2 = En2; }
             }
             if (!skip[i]) { m2 = 0.f; e2 = E_EMPTY; }
-            const int s = lane * SPL + i;
+            const int s = tid * SPL + i;
             const int Ec = max(Eo[i], max(e1, e2));   // common exponent of this state's operands
             // (an empty operand has mantissa 0 and E_EMPTY - Ec underflows to a factor 0; all empty: 0 * 1 = 0)
             const float v = (scale_pow2(ao[i], Eo[i] - Ec) + scale_pow2(m1, e1 - Ec) + scale_pow2(m2, e2 - Ec)) * e[i];
             normalise(s < S ? v : 0.f, Ec + ee[i], a[i], E[i]);
-            if (s < S) {
-                out[(long long)t * Sld + i * 32 + lane] = a[i];
-                eout[(long long)t * Sld + i * 32 + lane] = E[i];
+        }
+        publish(step & 1);
+#pragma unroll
+        for (int i = 0; i < SPL; ++i) {
+            if (tid * SPL + i < S) {
+                out[(long long)t * Sld + i * NT + tid] = a[i];
+                eout[(long long)t * Sld + i * NT + tid] = E[i];
             }
         }
     }
@@ -143,12 +163,11 @@ __device__ void lattice_pass(const float* __restrict__ pr, int V, const int* __r
 
 template <int DIR>
 __device__ void lattice_dispatch(int spl, const float* pr, int V, const int* tgt, int L, int Tb, int blank, float* out,
-                                 int Sld, int* eout) {
+                                 int Sld, int* eout, int2* xb, int tid, int bar_id) {
     switch (spl) {
-        case 2: lattice_pass<2, DIR>(pr, V, tgt, L, Tb, blank, out, Sld, eout); break;
-        case 4: lattice_pass<4, DIR>(pr, V, tgt, L, Tb, blank, out, Sld, eout); break;
-        case 8: lattice_pass<8, DIR>(pr, V, tgt, L, Tb, blank, out, Sld, eout); break;
-        default: lattice_pass<16, DIR>(pr, V, tgt, L, Tb, blank, out, Sld, eout); break;
+        case 1: lattice_pass<1, DIR>(pr, V, tgt, L, Tb, blank, out, Sld, eout, xb, tid, bar_id); break;
+        case 2: lattice_pass<2, DIR>(pr, V, tgt, L, Tb, blank, out, Sld, eout, xb, tid, bar_id); break;
+        default: lattice_pass<4, DIR>(pr, V, tgt, L, Tb, blank, out, Sld, eout, xb, tid, bar_id); break;
     }
 }
 }  // namespace
@@ -196,7 +215,7 @@ __device__ __forceinline__ void frame_softmax(const T* __restrict__ xr, int V, i
 __host__ __device__ inline long long ctc_ws_stride(int T_, int Sld) { return 4LL * T_ * Sld + 8; }
 
 // Lattice kernel: one CTA per (head, utterance).  Phase 1: posteriors of the utterance into shared memory (all warps);
-// phase 2: alpha (warp 0) and beta (warp 1) concurrently; then the loss.  The gradient is a separate, frame-parallel
+// phase 2: alpha (warps 0..7) and beta (warps 8..15) concurrently; then the loss.  The gradient is a separate, frame-parallel
 // kernel: inside this CTA it took 350 of 510 us (8 utterances = 8 busy SMs) at the sizes of the path.
 template <typename T>
 __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ logits, const int* __restrict__ targets,
@@ -208,11 +227,12 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     extern __shared__ float sm[];
     const int b = blockIdx.x, head = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const int Sld = 32 * spl;   // states per frame in the workspace: state s at [(s % spl) * 32 + s / spl]
+    const int Sld = LAT_THREADS * spl;   // states per frame in the workspace: state s at [(s % spl) * LAT_THREADS + s / spl]
     const int L = min(tgt_len[b], max_tgt);
     const int S = 2 * L + 1;
     const int Tb = max(0, min(in_len[b], T_));
-    float* pr = sm;                                  // [T][V] log2 of the softmax probabilities
+    int2* xb = reinterpret_cast<int2*>(sm);          // [2 directions][2 buffers][LAT_THREADS][2] boundary-state exchange
+    float* pr = sm + 2 * 2 * LAT_THREADS * 2 * 2;    // [T][V] log2 of the softmax probabilities
     int* tgt_s = (int*)(pr + (size_t)T_ * V);        // [max_tgt + 1]
     const long long hb = (long long)head * B + b;
     const T* x = logits + hb * T_ * V;
@@ -226,10 +246,13 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     for (int t = warp; t < Tb; t += nwarps)
         frame_softmax<T>(x + (long long)t * V, V, lane, [&](int v, float, float l2v) { pr[t * V + v] = l2v; });
     __syncthreads();
-    // ---- phase 2: alpha (warp 0) and beta (warp 1) concurrently
+    // ---- phase 2: alpha (warps 0..7) and beta (warps 8..15) concurrently, each with its own named barrier
     if (Tb > 0) {
-        if (warp == 0) lattice_dispatch<+1>(spl, pr, V, tgt_s, L, Tb, blank, alpha, Sld, ea);
-        else if (warp == 1) lattice_dispatch<-1>(spl, pr, V, tgt_s, L, Tb, blank, beta, Sld, eb);
+        if (threadIdx.x < LAT_THREADS)
+            lattice_dispatch<+1>(spl, pr, V, tgt_s, L, Tb, blank, alpha, Sld, ea, xb, threadIdx.x, 1);
+        else
+            lattice_dispatch<-1>(spl, pr, V, tgt_s, L, Tb, blank, beta, Sld, eb, xb + 2 * LAT_THREADS * 2,
+                                 threadIdx.x - LAT_THREADS, 2);
     }
     __threadfence_block();
     __syncthreads();
@@ -240,7 +263,7 @@ __global__ void __launch_bounds__(CTC_THREADS) ctc_kernel(const T* __restrict__ 
     int lp_exp = 0;
     if (Tb > 0) {
         const long long r = (long long)(Tb - 1);
-        auto at = [&](int st) { return r * Sld + (st % spl) * 32 + st / spl; };
+        auto at = [&](int st) { return r * Sld + (st % spl) * LAT_THREADS + st / spl; };
         const float a1 = alpha[at(S - 1)];
         const int e1 = ea[at(S - 1)];
         const float a2 = S > 1 ? alpha[at(S - 2)] : 0.f;
@@ -281,7 +304,7 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const T* __restrict__ log
     const long long hb = frame / T_;
     const int t = (int)(frame - hb * T_);
     const int b = (int)(hb % B);
-    const int Sld = 32 * spl;
+    const int Sld = LAT_THREADS * spl;
     const int L = min(tgt_len[b], max_tgt);
     const int S = 2 * L + 1;
     const int Tb = max(0, min(in_len[b], T_));
@@ -317,7 +340,7 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const T* __restrict__ log
     // sum relative to max alpha beta, as in round 1, drops exactly those states).
     float mx = NEG_INF;
     for (int s = lane; s < S; s += 32) {
-        const int ix = (s % spl) * 32 + s / spl;
+        const int ix = (s % spl) * LAT_THREADS + s / spl;
         const float ab = ar[ix] * br[ix];
         if (ab > 0.f) {
             const int l = (s & 1) ? tgt[(s - 1) >> 1] : blank;
@@ -328,7 +351,7 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const T* __restrict__ log
     for (int v = lane; v < V; v += 32) acc[v] = 0ull;
     __syncwarp();
     for (int s = lane; s < S; s += 32) {
-        const int ix = (s % spl) * 32 + s / spl;
+        const int ix = (s % spl) * LAT_THREADS + s / spl;
         const float ab = ar[ix] * br[ix];
         if (ab > 0.f) {
             const int l = (s & 1) ? tgt[(s - 1) >> 1] : blank;
@@ -390,15 +413,15 @@ using namespace b200asr;
 
 extern "C" {
 
-static int ctc_spl(int max_tgt_len) {   // lattice states per lane (2, 4, 8, 16; > 16: unsupported)
+static int ctc_spl(int max_tgt_len) {   // lattice states per thread (1, 2, 4; > 4: unsupported)
     const int S = 2 * (max_tgt_len < 1 ? 1 : max_tgt_len) + 1;
-    int spl = 2;
-    while (spl * 32 < S) spl *= 2;
+    int spl = 1;
+    while (spl * LAT_THREADS < S) spl *= 2;
     return spl;
 }
 
 size_t b200asr_ctc_workspace_bytes(int n_heads, int B, int T, int max_tgt_len) {
-    return (size_t)n_heads * B * (size_t)ctc_ws_stride(T, 32 * ctc_spl(max_tgt_len)) * sizeof(float);
+    return (size_t)n_heads * B * (size_t)ctc_ws_stride(T, LAT_THREADS * ctc_spl(max_tgt_len)) * sizeof(float);
 }
 
 int b200asr_ctc_fwd_bwd(const void* logits, const int* targets, const int* tgt_off, const int* tgt_len,
@@ -411,11 +434,11 @@ int b200asr_ctc_fwd_bwd(const void* logits, const int* targets, const int* tgt_o
     if (max_tgt_len < 1) max_tgt_len = 1;
     B200_REQUIRE(workspace_bytes >= b200asr_ctc_workspace_bytes(n_heads, B, T_, max_tgt_len), "ctc: workspace too small");
     const int spl = ctc_spl(max_tgt_len);
-    if (spl > 16) {
-        set_error("ctc: target length %d exceeds the supported 255", max_tgt_len);
+    if (spl > 4) {
+        set_error("ctc: target length %d exceeds the supported 511", max_tgt_len);
         return B200ASR_ERR_UNSUPPORTED;
     }
-    const size_t smem = ((size_t)T_ * V + (max_tgt_len + 1)) * sizeof(float) + 8;
+    const size_t smem = ((size_t)T_ * V + (max_tgt_len + 1) + 2 * 2 * LAT_THREADS * 2 * 2) * sizeof(float) + 8;
     if (smem > 227 * 1024) {
         set_error("ctc: T*V=%d*%d log-probabilities do not fit in shared memory", T_, V);
         return B200ASR_ERR_UNSUPPORTED;
