@@ -21,14 +21,17 @@ for stage in "$@"; do
     multitest) timeout 900 python -m pytest tests/test_gpu_multi.py -q -s > gpurun_out/${TAG}_multitest.log 2>&1; echo "multitest rc=$?";;
     mbench_noov*) N=${stage#mbench_noov}; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29551 bench.py --gpus $N --steps 20 --warmup 3 --no-overlap > gpurun_out/${TAG}_bench_noov_n${N}.json 2> gpurun_out/${TAG}_bench_noov_n${N}.err; echo "mbench_noov$N rc=$?";;
     mbench*)   N=${stage#mbench}; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29541 bench.py --gpus $N --steps 20 --warmup 3 > gpurun_out/${TAG}_bench_n${N}.json 2> gpurun_out/${TAG}_bench_n${N}.err; echo "mbench$N rc=$?";;
-    ncu)       # launch list of the bench's timed steps, GEMM traffic of one eager step, full sets of the memory-bound kernels
+    # one ncu use per box call, each after its own command exited 0 without ncu
+    ncu_launches)  # launch list of the bench's timed steps
                B="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extras --profile-range"
                timeout 600 $B > gpurun_out/${TAG}_ncu_plain1.log 2>&1 &&
                timeout 1500 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/${TAG}_launches.csv $B > gpurun_out/${TAG}_ncu1.log 2>&1
-               echo "ncu launches rc=$?"
+               echo "ncu launches rc=$?";;
+    ncu_gemm)  # DRAM traffic and tensor-pipe share of every GEMM launch of one eager step
                timeout 600 python tools/step_one.py > gpurun_out/${TAG}_ncu_plain2.log 2>&1 &&
                timeout 1500 ncu --profile-from-start off --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active -k regex:gemm_tc_kernel --clock-control none --csv --log-file gpurun_out/${TAG}_gemm_traffic.csv python tools/step_one.py > gpurun_out/${TAG}_ncu2.log 2>&1
-               echo "ncu gemm rc=$?"
+               echo "ncu gemm rc=$?";;
+    ncu_ops)   # full sets of the memory-bound / latency-bound kernels and of the attention kernels
                timeout 600 python tools/op_one.py > gpurun_out/${TAG}_ncu_plain3.log 2>&1 &&
                timeout 1500 ncu --set full --clock-control none --import-source on -k "regex:conv0_ln_gelu|ln_fwd|ln_bwd|ctc_kernel|ctc_grad|dacs_mask|mha_fwd_tc|mha_bwd_tc|attn_keep|dropout_kernel|dsum" -c 60 -o gpurun_out/${TAG}_prof_ops python tools/op_one.py > gpurun_out/${TAG}_ncu3.log 2>&1
                echo "ncu ops rc=$?";;

@@ -36,10 +36,57 @@ model = cls(ns, compute_dtype=dtype)
 model.load_state_dict(sd)
 model.freeze_feature_encoder()
 model.to(DEV).train()
-out = model(input_values=x, attention_mask=am, labels=lab, output_hidden_states=(len(sys.argv) > 3))
+out = model(input_values=x, attention_mask=am, labels=lab, output_hidden_states=True)
 out.logits.retain_grad()
+for h in out.hidden_states:
+    h.retain_grad()
 out.loss.backward()
 torch.cuda.synchronize()
+
+
+def l2(a, r):
+    a, r = a.double(), r.double()
+    return float((a - r).norm() / max(float(r.norm()), 1e-30))
+
+
+# the oracle's CTC on OUR logits: separates the loss kernel (bf16 in / out) from the deviation of the forward pass
+lg = out.logits.detach().float().requires_grad_(True)
+lens = R.conv_out_lengths(cfg, b["lengths"]).to(DEV)
+lp = torch.log_softmax(lg, -1).transpose(0, 1)
+tl = (lab >= 0).sum(-1)
+tg = torch.cat([lab[i, : int(tl[i])] for i in range(lab.shape[0])])
+l_own = torch.nn.functional.ctc_loss(lp, tg, lens, tl, blank=cfg.pad_token_id, reduction="sum", zero_infinity=False)
+l_own.backward()
+print("CTC on our logits (fp32 torch): loss", float(l_own), "ours", float(out.loss), " dlogits l2 (ours vs torch on the same logits)",
+      l2(out.logits.grad, lg.grad), " dlogits l2 (ours vs oracle end to end)", l2(out.logits.grad, logits_ref.grad))
+if dtype == torch.bfloat16:   # the yardstick: the oracle port under stock bf16 autocast
+    sdy = {k: v.detach().clone().requires_grad_(v.requires_grad) for k, v in sdg.items()}
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        loss_y, logits_y = R.ctc_forward(sdy, cfg, x, am.long(), lab)
+    logits_y.retain_grad()
+    loss_y.backward()
+    print("stock bf16 autocast: loss", float(loss_y), " logits l2 vs oracle", l2(logits_y.detach(), logits_ref.detach()),
+          " dlogits l2 vs oracle", l2(logits_y.grad, logits_ref.grad), " ours vs stock: logits", l2(out.logits.detach(), logits_y.detach()),
+          "dlogits", l2(out.logits.grad, logits_y.grad))
+    print("  |dlogits|: ours", float(out.logits.grad.float().norm()), "stock", float(logits_y.grad.float().norm()), "oracle", float(logits_ref.grad.norm()))
+    import numpy as np
+    pm = dict(model.named_parameters())
+    ro, ry, eo, ey = [], [], [], []
+    for k, v in sdg.items():
+        if v.grad is None or pm[k].grad is None or k.endswith("k_proj.bias"):
+            continue
+        n = float(v.grad.norm())
+        ro.append(float(pm[k].grad.float().norm()) / n); ry.append(float(sdy[k].grad.float().norm()) / n)
+        eo.append(l2(pm[k].grad, v.grad)); ey.append(l2(sdy[k].grad, v.grad))
+    q = lambda a: [round(float(np.quantile(a, t)), 4) for t in (0.1, 0.5, 0.9)]
+    print("  per-parameter |g| / |g_oracle| (10 / 50 / 90 %): ours", q(ro), "stock", q(ry))
+    print("  per-parameter l2 error of g (10 / 50 / 90 %): ours", q(eo), "stock", q(ey))
+if len(col) == len(out.hidden_states) and all(h.grad is not None for h in out.hidden_states):
+    for i in range(0, len(col), max(1, len(col) // 12)):
+        print(f"  d loss / d hidden[{i}]: l2 {l2(out.hidden_states[i].grad, col[i].grad):.3e}   hidden l2 {l2(out.hidden_states[i].detach(), col[i].detach()):.3e}"
+              f"   |h| rms {float(col[i].detach().pow(2).mean().sqrt()):.3e}  |dh| rms {float(col[i].grad.pow(2).mean().sqrt()):.3e}")
+else:
+    print("hidden state lists differ:", len(col), len(out.hidden_states))
 
 
 def rel(a, r):
