@@ -48,13 +48,15 @@ def test_large_training_step_matches_hf(golden_dir, name):
     for tag, i in (("first", 0), ("mid", L // 2), ("last", L)):
         assert LC.relinf(col[i][:, ::fs], g["hidden_" + tag]) < 2e-4, tag
     # gradients: two fp32 implementations (different summation orders in conv / matmul) drift apart through 24-48 layers
-    # of backward; measured up to 1.6e-3 on the earliest parameters of the pre-LN stacks
+    # of backward; measured up to 1.6e-3 on the earliest parameters of the pre-LN stacks with the thread count the fixture
+    # was written with and 7.4e-3 with another (torch's CPU reductions change their summation order with the number of
+    # threads; these posteriors are peaked: tools/grad_diag.py) -- the bound is the GPU test's fp32 gradient tolerance
     for n in g["grad_names"]:
-        assert LC.relinf(LC.grad_block(sd[str(n)].grad, blk), g["grad:" + str(n)]) < 3e-3, n
+        assert LC.relinf(LC.grad_block(sd[str(n)].grad, blk), g["grad:" + str(n)]) < 1.5e-2, n
     for n, v in zip(g["gnorm_names"], g["gnorm_values"]):
         if str(n).endswith("k_proj.bias"):
             continue  # exactly zero in exact arithmetic (softmax shift invariance): rounding noise on both sides
-        assert abs(float(sd[str(n)].grad.norm()) - v) <= 3e-3 * max(v, 1e-3), n
+        assert abs(float(sd[str(n)].grad.norm()) - v) <= 1.5e-2 * max(v, 1e-3), n
 
 
 def test_large_c3_dacs_stage2_matches_reference(golden_dir):
