@@ -318,3 +318,53 @@ class GraphedTrainStep:
             for gi in range(len(self.opt.groups)):
                 self.opt.adamw_params(gi)
         return self.loss
+
+
+class GraphedInference:
+    """Greedy CTC inference (finetune_ASRs.py:113-122: forward, argmax, repeat / blank collapse) of a fixed-shape batch as
+    ONE CUDA graph: infer = GraphedInference(model, input_values[, attention_mask]); logits, ids, seqs = infer(input_values).
+
+    At batch 1 x 5 s the ~330 launches of the forward pass execute faster than Python can issue them; the replay costs
+    one launch.  The model must be in eval mode (no dropout, no LayerDrop); weights replaced through torch
+    (`load_state_dict`) are picked up on the next call as in GraphedTrainStep."""
+
+    def __init__(self, model, input_values: torch.Tensor, attention_mask: Optional[torch.Tensor] = None, warmup: int = 2):
+        if model.training:
+            raise ValueError("GraphedInference: call model.eval() first")
+        self.model = model
+        self.backbone = getattr(model, "backbone", None)
+        self.x = input_values.clone()
+        self.am = None if attention_mask is None else attention_mask.clone()
+        self.blank = int(model.config.pad_token_id)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(max(1, warmup)):
+                self._body()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.no_grad(), torch.cuda.graph(self.graph):
+            self.logits, self.ids, self.collapsed, self.clen = self._body()
+
+    def _body(self):
+        out = self.model(self.x, self.am)
+        klen = None
+        if self.am is not None:   # frames beyond an utterance's length are not decoded (HF pads the logits there)
+            from .modeling import conv_out_lengths
+            klen = conv_out_lengths(self.model.config, self.am.sum(-1)).to(torch.int32).contiguous()
+        ids, col, clen = ops.greedy_decode(out.logits, klen, self.blank)
+        ops.join_side_stream()
+        return out.logits, ids, col, clen
+
+    def __call__(self, input_values: torch.Tensor, attention_mask: Optional[torch.Tensor] = None):
+        self.x.copy_(input_values, non_blocking=True)
+        if self.am is not None:
+            self.am.copy_(attention_mask, non_blocking=True)
+        for m in self.model.modules():
+            cache = getattr(m, "cache", None)
+            if cache is not None and hasattr(cache, "refresh_in_place"):
+                cache.refresh_in_place()
+        self.graph.replay()
+        col, clen = self.collapsed.cpu(), self.clen.cpu()
+        return self.logits, self.ids.long(), [col[b, : int(clen[b])].tolist() for b in range(col.shape[0])]

@@ -212,3 +212,39 @@ def test_adamw_chunk_table_equals_the_scalar_kernel():
     assert torch.equal(fp.flat, ref_p) and torch.equal(g["m"], ref_m) and torch.equal(g["v"], ref_v)
     assert torch.equal(fp.shadow, ref_s)
     assert list(g["param_steps"]) == [3, 1, 7, 2, 5]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("ragged", [False, True])
+def test_graphed_inference_matches_eager(dtype, ragged):
+    """graph.GraphedInference (forward + greedy decode as one CUDA graph) returns the eager path's logits, ids and collapsed
+    sequences -- for new inputs of the captured shape, and for new weights loaded after the capture."""
+    from b200asr.graph import GraphedInference
+    cfg = R.ArchConfig.tiny()
+    sd = R.init_state_dict(cfg, seed=31, dacs=False)
+    m = M.Data2VecAudioForCTC(ns(cfg), compute_dtype=dtype)
+    m.load_state_dict(sd)
+    m.to(DEV).eval()
+    b0 = dev(R.synth_batch(cfg, 3, 7000, seed=300, ragged=ragged, max_label=8))
+    am0 = b0["attention_mask"] if ragged else None
+    infer = GraphedInference(m, b0["input_values"], am0)
+
+    def eager(b):
+        with torch.no_grad():
+            am = b["attention_mask"] if ragged else None
+            o = m(b["input_values"], am)
+            klen = None if am is None else M.conv_out_lengths(m.config, am.sum(-1)).to(torch.int32)
+            return (o.logits,) + tuple(m.greedy_decode(o.logits, klen))
+
+    for seed in (301, 302):
+        b = dev(R.synth_batch(cfg, 3, 7000, seed=seed, ragged=ragged, max_label=8))
+        lg, ids, seqs = infer(b["input_values"], b["attention_mask"] if ragged else None)
+        lg_e, ids_e, seqs_e = eager(b)
+        assert torch.equal(lg, lg_e) and torch.equal(ids, ids_e) and seqs == seqs_e
+    with pytest.raises(ValueError):
+        GraphedInference(m.train(), b0["input_values"], am0)
+    m.eval()
+    m.load_state_dict(R.init_state_dict(cfg, seed=32, dacs=False))   # e.g. the next round's global model
+    lg, ids, seqs = infer(b["input_values"], b["attention_mask"] if ragged else None)
+    lg_e, ids_e, seqs_e = eager(b)
+    assert torch.equal(lg, lg_e) and torch.equal(ids, ids_e) and seqs == seqs_e

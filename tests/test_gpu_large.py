@@ -82,8 +82,10 @@ def stock_torch_bf16(cfg, sd, x, am, lab, want_grads=True):
         loss, logits = R.ctc_forward(sdg, cfg, x, None if am is None else am.long(), lab, collect=col)
     grads = {}
     if want_grads:
+        logits.retain_grad()
         loss.backward()
         grads = {k: v.grad for k, v in sdg.items() if v.grad is not None}
+        grads["d loss / d logits"] = logits.grad.float()
     return float(loss.detach()), logits.detach().float(), [h.detach().float() for h in col], grads
 
 
@@ -173,7 +175,6 @@ def _train_case(golden_dir, name, dtype):
         y_e_g, y_wg, y_gn, _ = grad_figures(None, g, blk, grads_of=y_grads)
         y_gb = y_e_g[y_wg]
         y_loss = abs(y_loss - float(g["loss"])) / abs(float(g["loss"]))
-        del y_grads
     figs = check(name, dtype, "logits", out.logits, g["logits"], y_logits)
     for tag, i in (("first", 0), ("mid", L // 2), ("last", L)):
         figs.update(check(name, dtype, "h_" + tag, out.hidden_states[i][:, ::fs], g["hidden_" + tag],
@@ -203,7 +204,9 @@ def _train_case(golden_dir, name, dtype):
     # gradient figures against the 2e-2 budget are therefore recorded for test_large_bf16_budget (an expected failure with
     # the measured numbers) and what is ASSERTED here is every kernel given its own inputs:
     #  (1) the CTC kernel on OUR logits vs torch's fp32 CTC on the same logits: loss and d loss / d logits,
-    #  (2) the backward pass: our parameter gradients vs the oracle's fp32 backward pass driven by OUR d loss / d logits.
+    #  (2) the backward pass: our parameter gradients vs the oracle's fp32 backward pass driven by OUR d loss / d logits
+    #      (the saved activations still carry the forward deviation -- 1e-1 at 48 blocks -- so the bound is the larger of the
+    #      bf16 gradient tolerance and YARD x the same figure of the stock-PyTorch bf16 run).
     del y_logits, y_h
     torch.cuda.empty_cache()
     own = dict(dlogits=out.logits.grad.detach().float() if out.logits.grad is not None else None)
@@ -219,15 +222,21 @@ def _train_case(golden_dir, name, dtype):
     fe = cfg.prefix + "feature_extractor"
     sdg = {k: v.to(DEV).requires_grad_(not k.startswith(fe)) for k, v in sd.items()}
     _, logits_ref = R.ctc_forward(sdg, cfg, x, am.long(), lab)
-    logits_ref.backward(own["dlogits"])
+    logits_ref.backward(own["dlogits"], retain_graph=True)
     errs = sorted((LC.rel2(params[k].grad, v.grad), k) for k, v in sdg.items()
                   if v.grad is not None and not k.endswith("k_proj.bias"))
     med, p90, worst = errs[len(errs) // 2][0], errs[int(0.9 * len(errs))][0], errs[-1]
+    for v in sdg.values():
+        v.grad = None
+    logits_ref.backward(y_grads["d loss / d logits"])   # the yardstick's own figure: stock bf16 gradients given ITS dlogits
+    y_errs = sorted(LC.rel2(y_grads[k], v.grad) for k, v in sdg.items() if v.grad is not None and not k.endswith("k_proj.bias"))
+    y_med, y_p90 = y_errs[len(y_errs) // 2], y_errs[int(0.9 * len(y_errs))]
     report(name, dtype, ctc_loss_on_own_logits=e_ctc_loss, ctc_dlogits_on_own_logits_l2=e_ctc_grad,
            backward_given_dlogits_median_l2=med, backward_given_dlogits_p90_l2=p90, backward_given_dlogits_worst_l2=worst[0],
-           backward_given_dlogits_worst_at=worst[1])
+           backward_given_dlogits_worst_at=worst[1], stock_torch_bf16_backward_given_dlogits_median_l2=y_med,
+           stock_torch_bf16_backward_given_dlogits_p90_l2=y_p90)
     assert e_ctc_loss < 1e-4 and e_ctc_grad < 1e-2, (e_ctc_loss, e_ctc_grad)   # (d loss / d logits is stored in bf16)
-    assert med < gtol and p90 < 2.5 * gtol, (med, p90, worst)
+    assert med < max(gtol, YARD * y_med) and p90 < max(2.5 * gtol, YARD * y_p90), (med, p90, worst, y_med, y_p90)
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
