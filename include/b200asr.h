@@ -132,6 +132,15 @@ typedef struct b200asr_gemm_args {
 } b200asr_gemm_args;
 int b200asr_gemm(const b200asr_gemm_args* args, void* stream);
 
+/* b200asr_gemm with act = B200ASR_ACT_GELU_SAVE_GRAD and the FFN's activation dropout (HF:335-339,
+ * `nn.Dropout(config.activation_dropout)` after the GELU) applied in the epilogue: C = drop(gelu(v)), aux_out =
+ * drop(gelu'(v)) with the SAME keep decisions, which are those of b200asr_dropout for (p, seed, site, offset, dev_offset)
+ * over the row-major [M, N] result.  The backward GEMM (mul_gelu_grad = 2 on aux_out) then needs no dropout pass either.
+ * bf16 operands and output on the tcgen05 back end only (B200ASR_ERR_UNSUPPORTED otherwise: use b200asr_gemm followed
+ * by b200asr_dropout); one batch, ldc = N, N % 8 == 0. */
+int b200asr_gemm_dropout(const b200asr_gemm_args* args, float p, unsigned long long seed, unsigned long long site,
+                         unsigned long long offset, const unsigned long long* dev_offset, void* stream);
+
 /* test / tuning hook: force the tcgen05 tile configuration: 0 = built-in cost model, else ncta * 1000 + bn
  * (1064, 1128, 1256 single CTA; 2128, 2256 CTA pair = cluster of 2 with cta_group::2 MMA).  Returns the old value. */
 int b200asr_gemm_force_config(int cfg);

@@ -498,8 +498,13 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
         o, _ = ops.linear_fwd(attn, wo, o_b)
         # s1 = x + drop_h(o) and LN1 in one pass (b200asr_layernorm_dropout_fwd)
         x1, s1, m1, r1 = ops.layernorm_fwd(o, ln1_w, ln1_b, eps, res=x, want_sum=True, drop=(ph, seed, site, ctr))
-        g, u = ops.linear_fwd(x1, w1s, b1, act=ACT_GELU_SAVE_GRAD)
-        g = ops.dropout(g, pa, seed, site + 1, ctr, out=g)
+        # activation dropout inside the W1 GEMM epilogue: g and the saved gelu' both carry mask_a / (1 - p_a), so the
+        # backward pass needs no dropout pass either (fp32 parity mode: separate passes, same mask)
+        fused_a = pa > 0.0 and ops.gemm_dropout_fusable(x1, w1s)
+        g, u = ops.linear_fwd(x1, w1s, b1, act=ACT_GELU_SAVE_GRAD, drop=(pa, seed, site + 1, ctr) if fused_a else None)
+        if not fused_a:
+            g = ops.dropout(g, pa, seed, site + 1, ctr, out=g)
+        ctx.fused_a = fused_a
         o2, _ = ops.linear_fwd(g, w2s, b2)
         y, s2, m2, r2 = ops.layernorm_fwd(o2, ln2_w, ln2_b, eps, res=x1, want_sum=True, drop=(ph, seed, site + 2, ctr))
         ctx.save_for_backward(x, qkv, attn, lse, s1, m1, r1, x1, u, g, s2, m2, r2, wqkv, wo, w1s, w2s)
@@ -521,7 +526,8 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
         do2, db2 = _dropout_bgrad(b2, wg, ds2, ph, seed, site + 2, ctr)   # gradient of W2 f + b2 (ds2 itself is the residual path)
         dw2 = _wgrad(w2, wg, do2, g)                              # g = the dropped activations W2 consumed
         du = ops.linear_dgrad(do2, w2s, gelu_grad=u)              # (do2 W2) * gelu'
-        du = ops.dropout(du, pa, seed, site + 1, ctr, out=du)     # ... * mask_a / (1 - p_a) (the factors commute)
+        if not ctx.fused_a:
+            du = ops.dropout(du, pa, seed, site + 1, ctr, out=du)     # ... * mask_a / (1 - p_a) (the factors commute)
         db1 = _bgrad(b1, wg, du)
         dw1 = _wgrad(w1, wg, du, x1)
         dx1 = ops.linear_dgrad(du, w1s, residual=ds2)
@@ -715,8 +721,13 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
         o, _ = ops.linear_fwd(attn, wo, o_b)
         # s1 = x + drop_h(o) and LN2 in one pass (b200asr_layernorm_dropout_fwd)
         n2, s1, m2, r2 = ops.layernorm_fwd(o, ln2_w, ln2_b, eps, res=x, want_sum=True, drop=(ph, seed, site, ctr))
-        g, u = ops.linear_fwd(n2, w1s, b1, act=ACT_GELU_SAVE_GRAD)
-        g = ops.dropout(g, pa, seed, site + 1, ctr, out=g)
+        # activation dropout inside the W1 GEMM epilogue: g and the saved gelu' both carry mask_a / (1 - p_a), so the
+        # backward pass needs no dropout pass either (fp32 parity mode: separate passes, same mask)
+        fused_a = pa > 0.0 and ops.gemm_dropout_fusable(n2, w1s)
+        g, u = ops.linear_fwd(n2, w1s, b1, act=ACT_GELU_SAVE_GRAD, drop=(pa, seed, site + 1, ctr) if fused_a else None)
+        if not fused_a:
+            g = ops.dropout(g, pa, seed, site + 1, ctr, out=g)
+        ctx.fused_a = fused_a
         o2, _ = ops.linear_fwd(g, w2s, b2)
         y = ops.dropout(o2, ph, seed, site + 2, ctr, residual=s1, out=o2)
         ctx.save_for_backward(x, m1, r1, n1, qkv, attn, lse, s1, m2, r2, n2, u, g, wqkv, wo, w1s, w2s)
@@ -739,7 +750,8 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
         do2, db2 = _dropout_bgrad(b2, wg, dy, ph, seed, site + 2, ctr)
         dw2 = _wgrad(w2, wg, do2, g)
         du = ops.linear_dgrad(do2, w2s, gelu_grad=u)
-        du = ops.dropout(du, pa, seed, site + 1, ctr, out=du)
+        if not ctx.fused_a:
+            du = ops.dropout(du, pa, seed, site + 1, ctr, out=du)
         db1 = _bgrad(b1, wg, du)
         dw1 = _wgrad(w1, wg, du, n2)
         dn2 = ops.linear_dgrad(du, w1s)

@@ -364,7 +364,7 @@ def dropout(x: torch.Tensor, p: float, seed: int, site: int, counter=None, resid
 # ----------------------------------------------------------------------------- GEMM
 def gemm_raw(A, B, Cout, M, N, K, lda, ldb, ldc, a_kmajor=True, b_kmajor=True, bias=None, residual=None,
              aux_out=None, aux_in=None, act=ACT_NONE, mul_gelu_grad=False, alpha=1.0, batch0=1, batch1=1,
-             sa=(0, 0), sb=(0, 0), sc=(0, 0), a_off=0, b_off=0, c_off=0, backend: Optional[int] = None):
+             sa=(0, 0), sb=(0, 0), sc=(0, 0), a_off=0, b_off=0, c_off=0, backend: Optional[int] = None, drop=None):
     """C[m,n] = epi(sum_k A(m,k) B(n,k)); offsets in elements.  See include/b200asr.h b200asr_gemm."""
     g = GemmArgs()
     esa, esc = A.element_size(), Cout.element_size()
@@ -388,7 +388,13 @@ def gemm_raw(A, B, Cout, M, N, K, lda, ldb, ldc, a_kmajor=True, b_kmajor=True, b
     if bias is not None:
         assert bias.dtype == torch.float32
     e0 = _prof_begin()
-    if backend is None:
+    if drop is not None:   # (p, seed, site, counter): element dropout on C and aux_out inside the GELU_SAVE_GRAD epilogue
+        pd, seed, site, counter = drop
+        dev = counter if isinstance(counter, torch.Tensor) else None
+        host = 0 if dev is not None or counter is None else int(counter)
+        check(lib.b200asr_gemm_dropout(C.byref(g), float(pd), int(seed) & (2 ** 64 - 1), int(site), host, _p(dev), _st()),
+              "gemm_dropout")
+    elif backend is None:
         check(lib.b200asr_gemm(C.byref(g), _st()), "gemm")
     else:
         check(lib.b200asr_gemm_backend(C.byref(g), backend, _st()), "gemm_backend")
@@ -396,9 +402,18 @@ def gemm_raw(A, B, Cout, M, N, K, lda, ldb, ldc, a_kmajor=True, b_kmajor=True, b
     return Cout
 
 
-def linear_fwd(x, w, bias=None, act=ACT_NONE, residual=None, want_preact=False, out_dtype=None):
+def gemm_dropout_fusable(x, w, out_dtype=None) -> bool:
+    """True when linear_fwd(..., act=ACT_GELU_SAVE_GRAD, drop=...) can apply the dropout in the GEMM epilogue (tcgen05
+    back end, bf16 in and out, aligned rows); otherwise the caller runs ops.dropout on the outputs."""
+    return (x.dtype == torch.bfloat16 and (out_dtype or x.dtype) == torch.bfloat16 and x.shape[-1] % 8 == 0
+            and w.shape[0] % 8 == 0 and x.data_ptr() % 16 == 0 and w.data_ptr() % 16 == 0)
+
+
+def linear_fwd(x, w, bias=None, act=ACT_NONE, residual=None, want_preact=False, out_dtype=None, drop=None):
     """y = act(x @ w.T + bias) (+ residual).  x [M, K], w [N, K] (same dtype).  Returns (y, preact_or_None);
-    with act=ACT_GELU_SAVE_GRAD the second tensor holds gelu'(pre-activation) (feed it to linear_dgrad(gelu_grad=))."""
+    with act=ACT_GELU_SAVE_GRAD the second tensor holds gelu'(pre-activation) (feed it to linear_dgrad(gelu_grad=)).
+    drop = (p, seed, site, counter) with ACT_GELU_SAVE_GRAD: y and the second tensor both come out multiplied by the
+    dropout mask / (1 - p) of ops.dropout's keys (b200asr_gemm_dropout; check gemm_dropout_fusable first)."""
     if act == ACT_GELU_SAVE_GRAD:
         want_preact = True
     x = _c(x)
@@ -406,7 +421,7 @@ def linear_fwd(x, w, bias=None, act=ACT_NONE, residual=None, want_preact=False, 
     N = w.shape[0]
     y = torch.empty(M, N, dtype=out_dtype or x.dtype, device=x.device)
     pre = torch.empty_like(y) if want_preact else None
-    gemm_raw(x, w, y, M, N, K, K, K, N, True, True, bias=bias, residual=residual, aux_out=pre, act=act)
+    gemm_raw(x, w, y, M, N, K, K, K, N, True, True, bias=bias, residual=residual, aux_out=pre, act=act, drop=drop)
     return y, pre
 
 

@@ -32,6 +32,31 @@ extern "C" int b200asr_gemm(const b200asr_gemm_args* args, void* stream) {
     return gemm_dispatch(a, as_stream(stream));
 }
 
+// y = drop(gelu(A B^T + bias)), aux_out = drop(gelu'(A B^T + bias)) with ONE mask: the FFN's activation dropout (HF:335-339)
+// inside the W1 GEMM epilogue.  The backward GEMM multiplies by aux_out as it is (mul_gelu_grad = 2), so neither direction
+// needs a dropout pass over the [M, 4 d] activations.  Mask = b200asr_dropout's for the same (p, seed, site, offset).
+extern "C" int b200asr_gemm_dropout(const b200asr_gemm_args* args, float p, unsigned long long seed, unsigned long long site,
+                                    unsigned long long offset, const unsigned long long* dev_offset, void* stream) {
+    B200_REQUIRE(args, "gemm_dropout: null args");
+    const b200asr_gemm_args& a = *args;
+    B200_REQUIRE(a.A && a.B && a.C && a.aux_out, "gemm_dropout: null operand (aux_out is required)");
+    B200_REQUIRE(a.act == B200ASR_ACT_GELU_SAVE_GRAD && !a.mul_gelu_grad && !a.residual,
+                 "gemm_dropout: only the GELU_SAVE_GRAD epilogue carries the fused dropout");
+    B200_REQUIRE(p >= 0.f && p < 1.f, "gemm_dropout: p=%f must be in [0, 1)", (double)p);
+    B200_REQUIRE(a.batch0 == 1 && a.batch1 == 1 && a.ldc == a.N && a.N % 8 == 0,
+                 "gemm_dropout: C must be one contiguous [M, N] matrix with N %% 8 == 0 (mask index = m * N + n)");
+    B200_REQUIRE(a.M >= 0 && a.N >= 0 && a.K >= 1, "gemm_dropout: bad shape M=%d N=%d K=%d", a.M, a.N, a.K);
+    const char* why = nullptr;
+    if (a.c_dtype != B200ASR_BF16 || !gemm_tc_eligible(a, &why)) {
+        set_error("gemm_dropout: needs the tcgen05 back end with bf16 output (%s); run b200asr_gemm + b200asr_dropout instead",
+                  why ? why : "c_dtype is not bf16");
+        return B200ASR_ERR_UNSUPPORTED;
+    }
+    if (a.M == 0 || a.N == 0) return B200ASR_OK;
+    const DropKeys k = make_drop_keys(p, seed, site, offset, dev_offset);
+    return gemm_tc_launch_dropout(a, k, as_stream(stream));
+}
+
 // test hook: force a back end (0 = simt, 1 = tcgen05) regardless of the dispatch rule
 extern "C" int b200asr_gemm_backend(const b200asr_gemm_args* args, int backend, void* stream) {
     B200_REQUIRE(args, "gemm: null args");

@@ -83,6 +83,15 @@ struct Params {
     int x_kind;          // second epilogue tensor of the staged path: 0 none, 1 aux_out (store), 2 residual, 3 aux_in (gelu')
     int epi_mode;        // staged path: 8 * ACTM + XK (see the epilogue)
     int dbg;             // experiment knobs (B200ASR_GEMM_DBG): 1 skip GELU math, 2 skip aux/residual traffic, 4 skip the C store
+    // element dropout fused into the GELU_SAVE_GRAD epilogue (b200asr_gemm_dropout): both outputs are multiplied by
+    // keep / (1 - p) with the keep decisions of dropout.cu (Philox keyed by (seed, site) over (element index / 8, step));
+    // drop_on = 0 otherwise
+    int drop_on;
+    uint32_t drop_thresh16;
+    float drop_scale;
+    uint2 drop_key;
+    unsigned long long drop_offset;
+    const unsigned long long* drop_dev_offset;
     unsigned long long* trace;  // diagnostics (b200asr_gemm_set_trace): 12 time stamps per CTA, null in normal use
 };
 
@@ -429,7 +438,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                     constexpr int ACTM = decltype(actm_c)::value;
                     constexpr int XK = decltype(xk_c)::value;
                     constexpr bool HAS_IN = XK >= 3;      // operand chunk TMA-loaded into the slot, result written in place
-                    constexpr bool TWO_OUT = XK == 1 || XK == 2;   // result in slot 0, second output in slot 1
+                    constexpr bool TWO_OUT = XK == 1 || XK == 2 || XK == 6;   // result in slot 0, second output in slot 1
+                    [[maybe_unused]] unsigned long long drop_off = 0;
+                    if constexpr (XK == 6) drop_off = p.drop_offset + (p.drop_dev_offset ? *p.drop_dev_offset : 0ull);
                     int acc = 0;
                     uint32_t acc_phase = 0, in_phase = 0;
                     if (HAS_IN && works && elect_one_sync()) { issue_in(0); issue_in(1); }
@@ -529,13 +540,31 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                                         for (int q = 0; q < 4; ++q)
                                             *reinterpret_cast<uint4*>(xrow + (((g * 4 + q) ^ sw) << 4)) = pack8(v + 8 * q);
                                     }
-                                    if constexpr (XK == 2) {          // result gelu, second output gelu'
+                                    if constexpr (XK == 2 || XK == 6) {   // result gelu, second output gelu' (6: both * keep / (1 - p))
                                         float2 g2[16];
 #pragma unroll
                                         for (int j = 0; j < 16; ++j) {
                                             float2 gv;
                                             gelu_both_fast2(v2[j], gv, g2[j]);
                                             v2[j] = gv;
+                                        }
+                                        if constexpr (XK == 6) {
+                                            // this lane's 32 columns of row m0w + lane = 4 Philox blocks of 8 elements of the
+                                            // row-major [M, N] result (ldc = N, N % 8 == 0: checked by the caller)
+                                            const unsigned long long e0 =
+                                                (unsigned long long)(m0w + lane) * (unsigned long long)p.ldc + (unsigned long long)(n + g * 32);
+#pragma unroll
+                                            for (int q = 0; q < 4; ++q) {
+                                                uint32_t u[8];
+                                                dropout_uniforms<8>(e0 + 8 * q, p.drop_key, drop_off, u);
+#pragma unroll
+                                                for (int e = 0; e < 8; e += 2) {
+                                                    const float2 mk = make_float2(u[e] >= p.drop_thresh16 ? p.drop_scale : 0.f,
+                                                                                  u[e + 1] >= p.drop_thresh16 ? p.drop_scale : 0.f);
+                                                    v2[4 * q + e / 2] = __fmul2_rn(v2[4 * q + e / 2], mk);
+                                                    g2[4 * q + e / 2] = __fmul2_rn(g2[4 * q + e / 2], mk);
+                                                }
+                                            }
                                         }
                                         const float* gf = reinterpret_cast<const float*>(g2);
 #pragma unroll
@@ -607,6 +636,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                         case 1: run(I0{}, I1{}); break;
                         case 9: run(I1{}, I1{}); break;
                         case 2: run(I0{}, std::integral_constant<int, 2>{}); break;
+                        case 6: run(I0{}, std::integral_constant<int, 6>{}); break;
                         case 3: run(I0{}, std::integral_constant<int, 3>{}); break;
                         case 11: run(I1{}, std::integral_constant<int, 3>{}); break;
                         case 4: run(I0{}, std::integral_constant<int, 4>{}); break;
@@ -654,11 +684,27 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                                     if (j < nvalid) v[j] += __ldg(bp + j);
                             }
                         }
+                        float mk[32];   // fused element dropout (drop_on): keep / (1 - p) per column of this row chunk
+                        if (p.drop_on) {
+                            const unsigned long long doff = p.drop_offset + (p.drop_dev_offset ? *p.drop_dev_offset : 0ull);
+                            const unsigned long long e0 = (unsigned long long)m * (unsigned long long)p.ldc + (unsigned long long)n;
+    #pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                uint32_t u[8];
+                                dropout_uniforms<8>(e0 + 8 * q, p.drop_key, doff, u);
+    #pragma unroll
+                                for (int e = 0; e < 8; ++e) mk[8 * q + e] = u[e] >= p.drop_thresh16 ? p.drop_scale : 0.f;
+                            }
+                        }
                         if (AOb && !(p.dbg & 2)) {
                             if (p.act == B200ASR_ACT_GELU_SAVE_GRAD) {
                                 float gp[32];
     #pragma unroll
                                 for (int j = 0; j < 32; ++j) gp[j] = gelu_grad_fast(v[j]);
+                                if (p.drop_on) {
+    #pragma unroll
+                                    for (int j = 0; j < 32; ++j) gp[j] *= mk[j];
+                                }
                                 store_row_chunk<TC>(AOb + row_off + n, gp, nvalid, vec_ok);
                             } else {
                                 store_row_chunk<TC>(AOb + row_off + n, v, nvalid, vec_ok);
@@ -667,6 +713,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                         if (p.act != B200ASR_ACT_NONE && !(p.dbg & 1)) {
     #pragma unroll
                             for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);
+                        }
+                        if (p.drop_on) {
+    #pragma unroll
+                            for (int j = 0; j < 32; ++j) v[j] *= mk[j];
                         }
                         if (p.mul_gelu_grad && !(p.dbg & 2)) {
                             float u[32];
@@ -876,6 +926,10 @@ static bool make_epilogue_map(CUtensorMap* map, const void* base, int M, int N, 
     return r == CUDA_SUCCESS;
 }
 
+// keys of the element dropout fused into the next launch's GELU_SAVE_GRAD epilogue (set by gemm_tc_launch_dropout around
+// its call; thread-local: the argument struct of the C ABI stays as it is)
+static thread_local const DropKeys* t_epi_drop = nullptr;
+
 template <int BN, typename TC, int NCTA = 1>
 static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
     CUtensorMap ma, mb, mc, mx;
@@ -901,6 +955,12 @@ static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
     p.trace = g_gemm_trace;
     // staged epilogue when the kernel variant has the shared memory for it and at most ONE second tensor is involved
     p.epi_tma = 0; p.x_kind = 0; p.epi_mode = 0;
+    p.drop_on = 0; p.drop_thresh16 = 0; p.drop_scale = 1.f; p.drop_key = make_uint2(0, 0); p.drop_offset = 0;
+    p.drop_dev_offset = nullptr;
+    if (t_epi_drop) {
+        p.drop_on = 1; p.drop_thresh16 = t_epi_drop->thresh16; p.drop_scale = t_epi_drop->scale; p.drop_key = t_epi_drop->key;
+        p.drop_offset = t_epi_drop->offset; p.drop_dev_offset = t_epi_drop->dev_offset;
+    }
     if (Cfg<BN, NCTA>::EPI_TMA && !(dbg & 8)) {
         const void* xs[3] = {a.aux_out, a.residual, a.mul_gelu_grad ? a.aux_in : nullptr};
         int nx = 0, kind = 0;
@@ -911,7 +971,7 @@ static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
         const bool gelu = a.act == B200ASR_ACT_GELU || a.act == B200ASR_ACT_GELU_SAVE_GRAD;
         int mode = -1;
         if (nx == 0) mode = gelu ? 8 : 0;
-        else if (nx == 1 && kind == 1) mode = a.act == B200ASR_ACT_GELU_SAVE_GRAD ? 2 : (a.act == B200ASR_ACT_GELU ? 9 : 1);
+        else if (nx == 1 && kind == 1) mode = a.act == B200ASR_ACT_GELU_SAVE_GRAD ? (p.drop_on ? 6 : 2) : (a.act == B200ASR_ACT_GELU ? 9 : 1);
         else if (nx == 1 && kind == 2) mode = gelu ? 11 : 3;
         else if (nx == 1 && kind == 3 && !gelu) mode = a.mul_gelu_grad == 2 ? 4 : 5;
         p.epi_mode = mode < 0 ? 0 : mode;
@@ -1048,6 +1108,13 @@ int gemm_tc_launch(const b200asr_gemm_args& a, cudaStream_t st) {
         case 256: return f32c ? tc::launch<256, float>(a, st) : tc::launch<256, __nv_bfloat16>(a, st);
         default: return f32c ? tc::launch<128, float>(a, st) : tc::launch<128, __nv_bfloat16>(a, st);
     }
+}
+
+int gemm_tc_launch_dropout(const b200asr_gemm_args& a, const DropKeys& k, cudaStream_t st) {
+    tc::t_epi_drop = &k;
+    const int rc = gemm_tc_launch(a, st);
+    tc::t_epi_drop = nullptr;
+    return rc;
 }
 
 }  // namespace b200asr

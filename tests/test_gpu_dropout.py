@@ -180,3 +180,42 @@ def test_dropout_graphed_step_draws_fresh_masks():
     assert int(model.backbone.dropout_counter) == c0 + 4
     assert len(set(losses)) == 4, losses  # same weights, same batch, different masks
     assert max(losses) / min(losses) < 1.5
+
+
+@pytest.mark.parametrize("cfg", [0, 1064, 1128, 1256, 2128, 2256])
+@pytest.mark.parametrize("shape", [(300, 256, 64), (1000, 512, 128), (3992, 4096, 1024)])
+def test_gemm_epilogue_dropout_equals_gemm_then_dropout(shape, cfg):
+    """b200asr_gemm_dropout (activation dropout inside the W1 GEMM's GELU_SAVE_GRAD epilogue): same keep decisions as
+    b200asr_dropout for the same keys, applied to BOTH outputs -- gelu(v) and the saved gelu'(v) -- on every tile
+    configuration (staged TMA-store epilogue and the direct one), host and device step counters."""
+    from b200asr._lib import ACT_GELU_SAVE_GRAD, lib
+    Mr, N, K = shape
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = (torch.randn(Mr, K, device="cuda", generator=g) * 0.5).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) * (K ** -0.5)).bfloat16()
+    b = torch.randn(N, device="cuda", generator=g) * 0.1
+    p, seed, site = 0.1, 99, 17
+    old = lib.b200asr_gemm_force_config(cfg)
+    try:
+        y0, u0 = ops.linear_fwd(x, w, b, act=ACT_GELU_SAVE_GRAD)
+        assert ops.gemm_dropout_fusable(x, w)
+        for counter in (3, torch.tensor([3], device="cuda", dtype=torch.int64)):
+            y1, u1 = ops.linear_fwd(x, w, b, act=ACT_GELU_SAVE_GRAD, drop=(p, seed, site, counter))
+            mask = ops.dropout(torch.ones(Mr, N, device="cuda", dtype=torch.bfloat16), p, seed, site, counter).float()
+            assert 0.85 < float((mask > 0).float().mean()) < 0.95
+            for got, plain in ((y1, y0), (u1, u0)):
+                want = plain.float() * mask          # (the separate pass rounds gelu to bf16 before scaling: one more rounding)
+                assert bool(((got.float() == 0) == (want == 0))[plain != 0].all())
+                err = (got.float() - want).abs().max() / want.abs().max()
+                assert float(err) < 1e-2, float(err)
+    finally:
+        lib.b200asr_gemm_force_config(old)
+
+
+def test_gemm_epilogue_dropout_rejects_what_it_cannot_fuse():
+    from b200asr._lib import ACT_GELU_SAVE_GRAD
+    x = torch.randn(64, 64, device="cuda")
+    w = torch.randn(64, 64, device="cuda")
+    assert not ops.gemm_dropout_fusable(x, w)
+    with pytest.raises(RuntimeError, match="gemm_dropout"):
+        ops.linear_fwd(x, w, None, act=ACT_GELU_SAVE_GRAD, drop=(0.1, 1, 2, 3))
