@@ -65,6 +65,15 @@ size_t b200asr_layernorm_bwd_workspace_bytes(int cols);
 int b200asr_layernorm_bwd(const void* dy, const void* s, const float* w, const float* b, const float* mean,
                           const float* rstd, const void* dres_add, void* dx, float* dw, float* db, float* dx_colsum,
                           void* workspace, size_t workspace_bytes, int rows, int cols, int act, int dtype, void* stream);
+/* The same with the hidden dropout that sits in front of the residual sum (HF:310-312, 344-345: s = res + drop(o)):
+ * dx continues along the residual path, dx_drop = dropout(dx) -- bit-identical to b200asr_dropout(dx) with the same
+ * (p, seed, site, offset, dev_offset) -- is the gradient of the dropped nn.Linear output o, and dx_drop_colsum its bias
+ * gradient.  Removes one pass over [rows, cols] and one column-sum launch per dropout site of the backward pass. */
+int b200asr_layernorm_bwd_dropout(const void* dy, const void* s, const float* w, const float* b, const float* mean,
+                                  const float* rstd, const void* dres_add, void* dx, void* dx_drop, float* dw, float* db,
+                                  float* dx_drop_colsum, void* workspace, size_t workspace_bytes, int rows, int cols, int act,
+                                  float p, unsigned long long seed, unsigned long long site, unsigned long long offset,
+                                  const unsigned long long* dev_offset, int dtype, void* stream);
 
 /* Column sums of a [rows, cols] matrix (bias gradients: what autograd does for nn.Linear.bias).
  * out fp32 [cols]; workspace >= b200asr_colsum_workspace_bytes(cols). */

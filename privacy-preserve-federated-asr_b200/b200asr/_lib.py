@@ -43,6 +43,8 @@ SIGNATURES = {
     "b200asr_layernorm_fwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, f32, i32, i32, vp]),
     "b200asr_layernorm_bwd_workspace_bytes": (sz, [i32]),
     "b200asr_layernorm_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, sz, i32, i32, i32, i32, vp]),
+    "b200asr_layernorm_bwd_dropout": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, sz, i32, i32, i32, f32, u64, u64,
+                                            u64, vp, i32, vp]),
     "b200asr_colsum_workspace_bytes": (sz, [i32]),
     "b200asr_colsum": (i32, [vp, vp, vp, sz, i32, i32, i32, i32, vp]),
     "b200asr_mask_frames": (i32, [vp, vp, i32, i32, i32, i32, vp]),

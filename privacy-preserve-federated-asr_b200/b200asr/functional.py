@@ -208,24 +208,34 @@ def _dropout_bgrad(ps, need, dy, p, seed, site, ctr):
     return do, None
 
 
-def _ln_bwd(dy, s, w, b, mean, rstd, need, in_bias=None, **kw):
+def _ln_bwd(dy, s, w, b, mean, rstd, need, in_bias=None, drop=None, **kw):
     """LayerNorm backward.  Affine gradients go straight to their sinks when fresh.  `in_bias` = the bias parameter
     of the Linear / conv whose output fed this LayerNorm: its gradient is the column sum of dx, which the kernel
-    emits in the same pass.  Returns (dx, dw, db, d_in_bias) with None for everything already delivered to a sink."""
+    emits in the same pass.  Returns (dx, dw, db, d_in_bias) with None for everything already delivered to a sink.
+    drop = (p, seed, site, counter): the Linear's output went through a hidden dropout before the residual sum; returns
+    (dx, dw, db, d_in_bias, dx_drop) with dx_drop = dropout(dx) from the same pass and d_in_bias = colsum(dx_drop)."""
     cols = s.shape[-1]
     dxsum = bias_sink = None
     bias_fresh = True
     if in_bias is not None and need:
         bias_sink, bias_fresh = grad_sink((in_bias,))
         dxsum = bias_sink if (bias_sink is not None and bias_fresh) else torch.empty(cols, dtype=torch.float32, device=s.device)
+    dropped = []
+
+    def run(**k):
+        out = ops.layernorm_bwd(dy, s, w, b, mean, rstd, dxsum_out=dxsum, drop=drop, **k, **kw)
+        if drop is not None:
+            dropped.append(out[3])
+        return out[:3]
+
     dw = db = None
     if need and w is not None:
         sw, fw = grad_sink((w,))
         sb, fb = grad_sink((b,))
         if sw is not None and sb is not None and fw and fb:
-            dx, _, _ = ops.layernorm_bwd(dy, s, w, b, mean, rstd, dw_out=sw, db_out=sb, dxsum_out=dxsum, **kw)
+            dx, _, _ = run(dw_out=sw, db_out=sb)
         else:
-            dx, dw, db = ops.layernorm_bwd(dy, s, w, b, mean, rstd, dxsum_out=dxsum, **kw)
+            dx, dw, db = run()
             if sw is not None:
                 if fw: sw.copy_(dw)
                 else: ops.axpy_(sw, dw)
@@ -235,13 +245,15 @@ def _ln_bwd(dy, s, w, b, mean, rstd, need, in_bias=None, **kw):
                 else: ops.axpy_(sb, db)
                 db = None
     else:
-        dx, _, _ = ops.layernorm_bwd(dy, s, w, b, mean, rstd, want_wgrad=False, dxsum_out=dxsum, **kw)
+        dx, _, _ = run(want_wgrad=False)
     d_in_bias = None
     if dxsum is not None and dxsum is not bias_sink:
         if bias_sink is not None:
             ops.axpy_(bias_sink, dxsum)
         else:
             d_in_bias = dxsum
+    if drop is not None:
+        return dx, dw, db, d_in_bias, dropped[0]
     return dx, dw, db, d_in_bias
 
 
@@ -522,8 +534,8 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
         ph, pa, seed, site, ctr, keep, pt = ctx.drop
         d = x.shape[1]
         wg = any(ctx.needs_input_grad[5:])  # parameter gradients wanted?
-        ds2, dln2w, dln2b, _ = _ln_bwd(dy, s2, ln2_w, ln2_b, m2, r2, wg)
-        do2, db2 = _dropout_bgrad(b2, wg, ds2, ph, seed, site + 2, ctr)   # gradient of W2 f + b2 (ds2 itself is the residual path)
+        # LN2 backward emits ds2 (residual path), do2 = hidden-dropout backward of it (gradient of W2 f + b2) and b2's gradient
+        ds2, dln2w, dln2b, db2, do2 = _ln_bwd(dy, s2, ln2_w, ln2_b, m2, r2, wg, in_bias=b2, drop=(ph, seed, site + 2, ctr))
         dw2 = _wgrad(w2, wg, do2, g)                              # g = the dropped activations W2 consumed
         du = ops.linear_dgrad(do2, w2s, gelu_grad=u)              # (do2 W2) * gelu'
         if not ctx.fused_a:
@@ -531,8 +543,7 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
         db1 = _bgrad(b1, wg, du)
         dw1 = _wgrad(w1, wg, du, x1)
         dx1 = ops.linear_dgrad(du, w1s, residual=ds2)
-        ds1, dln1w, dln1b, _ = _ln_bwd(dx1, s1, ln1_w, ln1_b, m1, r1, wg)
-        do, dbo = _dropout_bgrad(o_b, wg, ds1, ph, seed, site, ctr)
+        ds1, dln1w, dln1b, dbo, do = _ln_bwd(dx1, s1, ln1_w, ln1_b, m1, r1, wg, in_bias=o_b, drop=(ph, seed, site, ctr))
         dwo = _wgrad(o_w, wg, do, attn)
         dattn = ops.linear_dgrad(do, wo)
         dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale, keep=keep, p_drop=pt)
@@ -755,8 +766,10 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
         db1 = _bgrad(b1, wg, du)
         dw1 = _wgrad(w1, wg, du, n2)
         dn2 = ops.linear_dgrad(du, w1s)
-        ds1, dln2w, dln2b, _ = _ln_bwd(dn2, s1, ln2_w, ln2_b, m2, r2, wg, dres_add=dy)   # + residual path of y
-        do, dbo = _dropout_bgrad(o_b, wg, ds1, ph, seed, site, ctr)
+        # LN2 backward (+ the residual path of y) emits ds1, do = hidden-dropout backward of it (gradient of O attn + o_b) and
+        # o_b's gradient in one pass
+        ds1, dln2w, dln2b, dbo, do = _ln_bwd(dn2, s1, ln2_w, ln2_b, m2, r2, wg, in_bias=o_b, drop=(ph, seed, site, ctr),
+                                             dres_add=dy)
         dwo = _wgrad(o_w, wg, do, attn)
         dattn = ops.linear_dgrad(do, wo)
         dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale, keep=keep, p_drop=pt)

@@ -177,10 +177,12 @@ def layernorm_fwd(x, w, b, eps, res=None, act=ACT_NONE, want_sum=False, want_sta
 
 
 def layernorm_bwd(dy, s, w, b, mean, rstd, act=ACT_NONE, dres_add=None, want_wgrad=True, dw_out=None, db_out=None,
-                  dxsum_out=None):
+                  dxsum_out=None, drop=None):
     """Returns (dx, dw, db); dw/db are None when the LN has no affine or want_wgrad is False.
     dw_out/db_out: optional preallocated fp32 [cols] destinations (overwritten).
-    dxsum_out: optional fp32 [cols] receiving the column sums of dx (bias gradient of the producing Linear)."""
+    dxsum_out: optional fp32 [cols] receiving the column sums of dx (bias gradient of the producing Linear).
+    drop = (p, seed, site, counter): returns (dx, dw, db, dx_drop) with dx_drop = ops.dropout(dx, ...) written by the same
+    pass (b200asr_layernorm_bwd_dropout); dxsum_out then receives the column sums of dx_drop."""
     dy = _c(dy)
     s = _c(s)
     cols = s.shape[-1]
@@ -194,6 +196,16 @@ def layernorm_bwd(dy, s, w, b, mean, rstd, act=ACT_NONE, dres_add=None, want_wgr
     if dw is not None or dxsum_out is not None:
         nws = lib.b200asr_layernorm_bwd_workspace_bytes(cols)
         ws = workspace(nws, s.device)
+    if drop is not None:
+        pd, seed, site, counter = drop
+        dev = counter if isinstance(counter, torch.Tensor) else None
+        host = 0 if dev is not None or counter is None else int(counter)
+        dxd = torch.empty_like(s)
+        check(lib.b200asr_layernorm_bwd_dropout(_p(dy), _p(s), _p(w), _p(b), _p(mean), _p(rstd), _p(dres_add), _p(dx), _p(dxd),
+                                                _p(dw), _p(db), _p(dxsum_out), _p(ws), nws, rows, cols, act, float(pd),
+                                                int(seed) & (2 ** 64 - 1), int(site), host, _p(dev), dt(s), _st()),
+              "layernorm_bwd_dropout")
+        return dx, dw, db, dxd
     check(lib.b200asr_layernorm_bwd(_p(dy), _p(s), _p(w), _p(b), _p(mean), _p(rstd), _p(dres_add), _p(dx), _p(dw),
                                     _p(db), _p(dxsum_out), _p(ws), nws, rows, cols, act, dt(s), _st()), "layernorm_bwd")
     return dx, dw, db

@@ -437,7 +437,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                 auto run = [&](auto actm_c, auto xk_c) {
                     constexpr int ACTM = decltype(actm_c)::value;
                     constexpr int XK = decltype(xk_c)::value;
-                    constexpr bool HAS_IN = XK >= 3;      // operand chunk TMA-loaded into the slot, result written in place
+                    constexpr bool HAS_IN = XK >= 3 && XK <= 5;   // operand chunk TMA-loaded into the slot, result written in place
                     constexpr bool TWO_OUT = XK == 1 || XK == 2 || XK == 6;   // result in slot 0, second output in slot 1
                     [[maybe_unused]] unsigned long long drop_off = 0;
                     if constexpr (XK == 6) drop_off = p.drop_offset + (p.drop_dev_offset ? *p.drop_dev_offset : 0ull);

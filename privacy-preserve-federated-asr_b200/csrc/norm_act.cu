@@ -128,18 +128,24 @@ __global__ void __launch_bounds__(128) ln_fwd_kernel(const T* __restrict__ x, co
 static __device__ unsigned long long* g_ln_trace_dev = nullptr;   // diagnostics (b200asr_ln_set_trace): 8 stamps per block
 #define LTRACE(slot) do { if (g_ln_trace_dev && threadIdx.x == 0) g_ln_trace_dev[blockIdx.x * 8 + (slot)] = (unsigned long long)clock64(); } while (0)
 
-template <typename T, bool CS>
+// DR: a second output dx_drop = dropout(dx) with the keys `dk` (the hidden dropout in front of this LayerNorm's residual
+// sum, HF:310-312 / 344-345: dx continues along the residual path, dx_drop is the gradient of the dropped Linear output),
+// bit-identical to a b200asr_dropout pass over the stored dx; the CS column sums are then those of dx_drop (= that
+// Linear's bias gradient).
+template <typename T, bool CS, bool DR = false>
 __global__ void __launch_bounds__(512, 1) ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ s,
                                                         const float* __restrict__ w, const float* __restrict__ b,
                                                         const float* __restrict__ mean_in,
                                                         const float* __restrict__ rstd_in,
                                                         const T* __restrict__ dres_add, T* __restrict__ dx,
                                                         float* __restrict__ partial, int rows, int cols, int act, int GS,
-                                                        int G) {
+                                                        int G, T* __restrict__ dx_drop = nullptr, DropKeys dk = DropKeys{}) {
     constexpr int N = Vec16<T>::N;
+    [[maybe_unused]] unsigned long long drop_off = 0;
     LTRACE(0);
     pdl_enter();
     LTRACE(1);
+    if constexpr (DR) drop_off = dk.offset + (dk.dev_offset ? *dk.dev_offset : 0ull);
     extern __shared__ float sm[];
     float* xch = sm;                    // [2][G][16][2] per-warp row statistics, double buffered by row parity
     float* sacc = sm + 2 * 8 * 16 * 2;  // [G][3][N][GS] accumulators of the groups (end phase)
@@ -240,6 +246,15 @@ __global__ void __launch_bounds__(512, 1) ln_bwd_kernel(const T* __restrict__ dy
             Vec16<T> ov;
             ov.pack(o);
             ov.store(dx + base);
+            if constexpr (DR) {
+                uint32_t u[N];
+                dropout_uniforms<N>((unsigned long long)base, dk.key, drop_off, u);
+                ov.unpack(o);   // the stored (rounded) values, as a separate dropout pass would read them
+#pragma unroll
+                for (int j = 0; j < N; ++j) o[j] = (u[j] >= dk.thresh16) ? o[j] * dk.scale : 0.f;
+                ov.pack(o);
+                ov.store(dx_drop + base);
+            }
             if (CS) {
                 ov.unpack(o);  // sum what was stored (the rounded values the consumer GEMMs read)
 #pragma unroll
@@ -435,7 +450,7 @@ static int launch_ln_fwd(const void* x, const void* res, const float* w, const f
 template <typename T>
 static int launch_ln_bwd(const void* dy, const void* s, const float* w, const float* b, const float* mean,
                          const float* rstd, const void* dres, void* dx, float* partial, bool colsum, int rows, int cols,
-                         int act, cudaStream_t st) {
+                         int act, cudaStream_t st, void* dx_drop = nullptr, const DropKeys* drop = nullptr) {
     constexpr int N = Vec16<T>::N;
     const int GS = ceil_div(ceil_div(cols, N), 32) * 32;  // threads per row
     if (GS > 512) { set_error("layernorm_bwd: cols=%d too large", cols); return B200ASR_ERR_UNSUPPORTED; }
@@ -449,18 +464,27 @@ static int launch_ln_bwd(const void* dy, const void* s, const float* w, const fl
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(ln_bwd_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(ln_bwd_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(ln_bwd_kernel<T, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(ln_bwd_kernel<T, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
         if (e != cudaSuccess) {
             set_error("layernorm_bwd: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
             return B200ASR_ERR_CUDA;
         }
         attr_set = true;
     }
-    if (colsum)
+    if (drop && dx_drop) {
+        if (colsum)
+            launch_pdl(ln_bwd_kernel<T, true, true>, dim3(grid), dim3(G * GS), smem, st, (const T*)dy, (const T*)s, w, b, mean,
+                       rstd, (const T*)dres, (T*)dx, partial, rows, cols, act, GS, G, (T*)dx_drop, *drop);
+        else
+            launch_pdl(ln_bwd_kernel<T, false, true>, dim3(grid), dim3(G * GS), smem, st, (const T*)dy, (const T*)s, w, b, mean,
+                       rstd, (const T*)dres, (T*)dx, partial, rows, cols, act, GS, G, (T*)dx_drop, *drop);
+    } else if (colsum)
         launch_pdl(ln_bwd_kernel<T, true>, dim3(grid), dim3(G * GS), smem, st, (const T*)dy, (const T*)s, w, b, mean, rstd,
-                   (const T*)dres, (T*)dx, partial, rows, cols, act, GS, G);
+                   (const T*)dres, (T*)dx, partial, rows, cols, act, GS, G, (T*)nullptr, DropKeys{});
     else
         launch_pdl(ln_bwd_kernel<T, false>, dim3(grid), dim3(G * GS), smem, st, (const T*)dy, (const T*)s, w, b, mean, rstd,
-                   (const T*)dres, (T*)dx, partial, rows, cols, act, GS, G);
+                   (const T*)dres, (T*)dx, partial, rows, cols, act, GS, G, (T*)nullptr, DropKeys{});
     return check_launch("layernorm_bwd");
 }
 
@@ -504,10 +528,35 @@ int b200asr_layernorm_dropout_fwd(const void* x, const void* res, const float* w
 
 size_t b200asr_layernorm_bwd_workspace_bytes(int cols) { return (size_t)LN_BWD_BLOCKS * 3 * cols * sizeof(float); }
 
+static int layernorm_bwd_impl(const void* dy, const void* s, const float* w, const float* b, const float* mean,
+                              const float* rstd, const void* dres_add, void* dx, float* dw, float* db, float* dx_colsum,
+                              void* workspace, size_t workspace_bytes, int rows, int cols, int act, int dtype,
+                              void* stream, void* dx_drop, const DropKeys* drop);
+
 int b200asr_layernorm_bwd(const void* dy, const void* s, const float* w, const float* b, const float* mean,
                           const float* rstd, const void* dres_add, void* dx, float* dw, float* db, float* dx_colsum,
                           void* workspace, size_t workspace_bytes, int rows, int cols, int act, int dtype,
                           void* stream) {
+    return layernorm_bwd_impl(dy, s, w, b, mean, rstd, dres_add, dx, dw, db, dx_colsum, workspace, workspace_bytes, rows, cols,
+                              act, dtype, stream, nullptr, nullptr);
+}
+
+int b200asr_layernorm_bwd_dropout(const void* dy, const void* s, const float* w, const float* b, const float* mean,
+                                  const float* rstd, const void* dres_add, void* dx, void* dx_drop, float* dw, float* db,
+                                  float* dx_drop_colsum, void* workspace, size_t workspace_bytes, int rows, int cols, int act,
+                                  float p, unsigned long long seed, unsigned long long site, unsigned long long offset,
+                                  const unsigned long long* dev_offset, int dtype, void* stream) {
+    B200_REQUIRE(dx_drop, "layernorm_bwd_dropout: null dx_drop");
+    B200_REQUIRE(p >= 0.f && p < 1.f, "layernorm_bwd_dropout: p=%f must be in [0, 1)", (double)p);
+    const DropKeys k = make_drop_keys(p, seed, site, offset, dev_offset);
+    return layernorm_bwd_impl(dy, s, w, b, mean, rstd, dres_add, dx, dw, db, dx_drop_colsum, workspace, workspace_bytes, rows,
+                              cols, act, dtype, stream, dx_drop, &k);
+}
+
+static int layernorm_bwd_impl(const void* dy, const void* s, const float* w, const float* b, const float* mean,
+                              const float* rstd, const void* dres_add, void* dx, float* dw, float* db, float* dx_colsum,
+                              void* workspace, size_t workspace_bytes, int rows, int cols, int act, int dtype,
+                              void* stream, void* dx_drop, const DropKeys* drop) {
     if (rows <= 0) return B200ASR_OK;
     B200_REQUIRE(dy && s && mean && rstd && dx, "layernorm_bwd: null pointer");
     B200_REQUIRE(cols > 0 && cols % (dtype == B200ASR_BF16 ? 8 : 4) == 0, "layernorm_bwd: bad cols=%d", cols);
@@ -522,7 +571,7 @@ int b200asr_layernorm_bwd(const void* dy, const void* s, const float* w, const f
     int rc;
     B200_DISPATCH_DTYPE(dtype, {
         rc = launch_ln_bwd<T>(dy, s, w, b, mean, rstd, dres_add, dx, partial, dx_colsum != nullptr, rows, cols, act,
-                              as_stream(stream));
+                              as_stream(stream), dx_drop, drop);
     });
     if (rc != B200ASR_OK) return rc;
     if (partial) {

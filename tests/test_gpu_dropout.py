@@ -89,6 +89,34 @@ def test_fused_dropout_entry_points_equal_the_composition(rows, cols, dtype):
     assert float((cs.double() - ref64).abs().max()) <= 1e-3 * max(1.0, float(ref64.abs().max()))
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("rows,cols", [(3992, 1024), (37, 128), (8, 2048)])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_layernorm_bwd_dropout_equals_the_composition(rows, cols, dtype, with_res):
+    """b200asr_layernorm_bwd_dropout: dx, dw, db as b200asr_layernorm_bwd; dx_drop == b200asr_dropout(dx) bit for bit;
+    the column sums are those of dx_drop (the dropped Linear's bias gradient)."""
+    g = torch.Generator().manual_seed(rows * 3 + cols)
+    s_in = torch.randn(rows, cols, generator=g).to(DEV).to(dtype)
+    dy = torch.randn(rows, cols, generator=g).to(DEV).to(dtype)
+    res = torch.randn(rows, cols, generator=g).to(DEV).to(dtype) if with_res else None
+    w = (1 + 0.1 * torch.randn(cols, generator=g)).to(DEV)
+    b = (0.1 * torch.randn(cols, generator=g)).to(DEV)
+    _, _, mean, rstd = ops.layernorm_fwd(s_in, w, b, 1e-5)
+    for ctr in (7, torch.tensor([7], dtype=torch.int64, device=DEV)):
+        keys = (0.15, 1234, 18, ctr)
+        dx0, dw0, db0 = ops.layernorm_bwd(dy, s_in, w, b, mean, rstd, dres_add=res)
+        cs = torch.empty(cols, device=DEV)
+        dx, dw, db, dxd = ops.layernorm_bwd(dy, s_in, w, b, mean, rstd, dres_add=res, dxsum_out=cs, drop=keys)
+        assert torch.equal(dx, dx0) and torch.equal(dw, dw0) and torch.equal(db, db0)
+        want = ops.dropout(dx0, *keys)
+        assert torch.equal(dxd, want)
+        ref64 = want.double().sum(0)
+        assert float((cs.double() - ref64).abs().max()) <= 1e-3 * max(1.0, float(ref64.abs().max()))
+        # without the affine gradients / column sums (frozen parameters)
+        dx1, _, _, dxd1 = ops.layernorm_bwd(dy, s_in, w, b, mean, rstd, dres_add=res, want_wgrad=False, drop=keys)
+        assert torch.equal(dx1, dx0) and torch.equal(dxd1, want)
+
+
 def _masks_from_library(backbone, cfg, B, T, ps):
     """Read the masks of the last training forward back: dropout(ones) with that forward's keys."""
     seed, ctr = backbone.dropout_seed, backbone._drop_ctr

@@ -82,6 +82,26 @@ def ln_bwd(cols, rows, affine, cs, act=ACT_NONE):
     return mk
 
 
+def ln_bwd_drop(cols, rows):
+    """LayerNorm backward + the hidden dropout's backward + the dropped Linear's bias gradient in one pass."""
+    def mk():
+        x = rnd(rows, cols); dy = rnd(rows, cols)
+        w = torch.ones(cols, device=dev); b = torch.zeros(cols, device=dev)
+        mean = torch.zeros(rows, device=dev); rstd = torch.ones(rows, device=dev)
+        dw = torch.empty(cols, device=dev); db = torch.empty(cols, device=dev); dxs = torch.empty(cols, device=dev)
+        return lambda: ops.layernorm_bwd(dy, x, w, b, mean, rstd, dw_out=dw, db_out=db, dxsum_out=dxs, drop=(0.1, 1234, 16, 7))
+    return mk
+
+
+def w1_gemm(drop):
+    """The FFN's first GEMM [M, d] x [4d, d]^T with GELU + saved gelu' epilogue, without / with the activation dropout."""
+    def mk():
+        from b200asr._lib import ACT_GELU_SAVE_GRAD
+        x = rnd(M, D); w = rnd(F, D); b = torch.zeros(F, device=dev)
+        return lambda: ops.linear_fwd(x, w, b, act=ACT_GELU_SAVE_GRAD, drop=(0.1, 1234, 17, 7) if drop else None)
+    return mk
+
+
 def colsum(cols):
     def mk():
         x = rnd(M, cols); out = torch.empty(cols, device=dev)
@@ -213,7 +233,10 @@ tot += 24 * bench("colsum   [3992,4096]                 (x24)", colsum(F), nbyte
 tot += 24 * bench("colsum   [3992,3072]                 (x24)", colsum(3 * D), nbytes=M * 3 * D * e)
 bench("dropout [3992,1024] + residual (x96 when p > 0)", dropout(D, True), nbytes=3 * M * D * e)
 bench("dropout [3992,1024]            (x52 when p > 0)", dropout(D, False), nbytes=2 * M * D * e)
-bench("dropout [3992,4096] activation (x48 when p > 0)", dropout(F, False), nbytes=2 * M * F * e)
+bench("dropout [3992,4096] activation (fp32 mode only: fused below)", dropout(F, False), nbytes=2 * M * F * e)
+bench("ln_bwd   [3992,1024] + hidden dropout bwd + colsum (x48 when p > 0)", ln_bwd_drop(D, M), nbytes=4 * M * D * e)
+bench("gemm W1  [3992,1024]x[4096,1024] gelu + gelu'        (x24)", w1_gemm(False), flops=2.0 * M * D * F)
+bench("gemm W1  ... + activation dropout in the epilogue    (x24 when p > 0)", w1_gemm(True), flops=2.0 * M * D * F)
 tot += 24 * bench("mha_fwd  B8 T499 H16 dh64            (x24)", mha_f(), flops=4.0 * B * H * T * T * 64)
 tot += 24 * bench("mha_bwd  B8 T499 H16 dh64 (+dsum,dQ) (x24)", mha_b(), flops=10.0 * B * H * T * T * 64)
 bench("mha_bwd  ... dQ in-kernel, fp32 bulk reduce-add", mha_b_mode(1), flops=10.0 * B * H * T * T * 64)
