@@ -80,6 +80,17 @@ int b200asr_layernorm_bwd_dropout(const void* dy, const void* s, const float* w,
 size_t b200asr_colsum_workspace_bytes(int cols);
 int b200asr_colsum(const void* x, float* out, void* workspace, size_t workspace_bytes, int rows, int cols, int ld,
                    int dtype, void* stream);
+/* b200asr_colsum for callers that cannot provide a workspace and must not allocate (CUDA graph capture, serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The partial sums go to a device array built into the library (2 MiB per GPU that loads it, held until exit), so the
+ * call allocates nothing -- no cudaMalloc / cudaFree / allocating library routine.  Limit: cols <=
+ * B200ASR_COLSUM_STATIC_MAX_COLS (also returned by b200asr_colsum_static_max_cols()); larger -> B200ASR_ERR_BAD_ARG with
+ * a message.  Same result, bit for bit, as b200asr_colsum.  All calls on one GPU share the array (it keeps the last
+ * call's partial sums; nothing in it has to be cleared, every call overwrites what it reads): calls that may overlap on
+ * the GPU -- different streams without an ordering between them -- race; order them or use b200asr_colsum. */
+#define B200ASR_COLSUM_STATIC_MAX_COLS 8192
+int b200asr_colsum_static_max_cols(void);
+int b200asr_colsum_static(const void* x, float* out, int rows, int cols, int ld, int dtype, void* stream);
 
 /* Zero the frames t >= lengths[b] of x [B, T, cols] in place (HF:369-371 `hidden_states[~mask] = 0`). */
 int b200asr_mask_frames(void* x, const int* lengths, int B, int T, int cols, int dtype, void* stream);

@@ -47,6 +47,8 @@ SIGNATURES = {
                                             u64, vp, i32, vp]),
     "b200asr_colsum_workspace_bytes": (sz, [i32]),
     "b200asr_colsum": (i32, [vp, vp, vp, sz, i32, i32, i32, i32, vp]),
+    "b200asr_colsum_static_max_cols": (i32, []),
+    "b200asr_colsum_static": (i32, [vp, vp, i32, i32, i32, i32, vp]),
     "b200asr_mask_frames": (i32, [vp, vp, i32, i32, i32, i32, vp]),
     "b200asr_cast_f32": (i32, [vp, vp, i64, i32, vp]),
     "b200asr_cast_to_f32": (i32, [vp, vp, i64, i32, vp]),

@@ -1,5 +1,7 @@
 // LayerNorm (+residual, +GELU) forward/backward, column sums.  HBM-bound: one warp per row, 128-bit
 // loads, values held in registers between the statistics pass and the normalise pass (one read, one write).
+#include <mutex>
+
 #include "common.cuh"
 
 namespace b200asr {
@@ -619,6 +621,53 @@ int b200asr_colsum(const void* x, float* out, void* workspace, size_t workspace_
     launch_pdl(reduce_partials_kernel, dim3(ceil_div(cols, 32)), dim3(1024), 0, as_stream(stream), (const float*)workspace, out,
                (float*)nullptr, (float*)nullptr, nchunks, cols, cols, cols);
     return check_launch("colsum_reduce");
+}
+
+// ---- b200asr_colsum without a caller-provided workspace and without any allocation --------------------------------------
+// The partial sums live in a file-scope device array (COLSUM_CHUNKS x B200ASR_COLSUM_STATIC_MAX_COLS floats = 2 MiB, held
+// by every GPU that loads the library until the process exits).  In host code `g_colsum_static_scratch` is only the host
+// side's handle of the symbol, not a device address: the address is looked up once per device, with that device current,
+// by cudaGetSymbolAddress, and that pointer is what the kernels get.
+static __device__ __align__(256) float g_colsum_static_scratch[COLSUM_CHUNKS * B200ASR_COLSUM_STATIC_MAX_COLS];
+
+static int colsum_static_scratch(float** out_ptr) {
+    constexpr int MAX_DEV = 64;
+    static float* ptrs[MAX_DEV] = {};
+    static std::mutex mu;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= MAX_DEV) {
+        set_error("colsum_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+        return B200ASR_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        float* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_colsum_static_scratch);
+        if (e != cudaSuccess || !ptr) {
+            set_error("colsum_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return B200ASR_ERR_CUDA;
+        }
+        ptrs[dev] = ptr;
+    }
+    *out_ptr = ptrs[dev];
+    return B200ASR_OK;
+}
+
+int b200asr_colsum_static_max_cols(void) { return B200ASR_COLSUM_STATIC_MAX_COLS; }
+
+int b200asr_colsum_static(const void* x, float* out, int rows, int cols, int ld, int dtype, void* stream) {
+    B200_REQUIRE(x && out, "colsum_static: null pointer");
+    B200_REQUIRE(rows > 0 && cols > 0 && ld >= cols, "colsum_static: bad shape");
+    B200_REQUIRE(cols <= B200ASR_COLSUM_STATIC_MAX_COLS,
+                 "colsum_static: cols=%d exceeds the built-in scratch (max %d columns); use b200asr_colsum with a workspace",
+                 cols, B200ASR_COLSUM_STATIC_MAX_COLS);
+    float* scratch = nullptr;
+    const int rc = colsum_static_scratch(&scratch);
+    if (rc != B200ASR_OK) return rc;
+    // nothing has to start at zero: every partial the reduction reads is written by the partial kernel of this same call
+    return b200asr_colsum(x, out, scratch, sizeof(float) * COLSUM_CHUNKS * B200ASR_COLSUM_STATIC_MAX_COLS, rows, cols, ld, dtype,
+                          stream);
 }
 
 int b200asr_dropout_colsum(const void* x, void* y, float* out, void* workspace, size_t workspace_bytes, int rows, int cols,
