@@ -346,6 +346,11 @@ class GraphedInference:
         self.graph = torch.cuda.CUDAGraph()
         with torch.no_grad(), torch.cuda.graph(self.graph):
             self.logits, self.ids, self.collapsed, self.clen = self._body()
+        self._params = list(model.parameters())
+        self._params_version = sum(p._version for p in self._params)
+        self._caches = [m.cache for m in model.modules() if hasattr(getattr(m, "cache", None), "refresh_in_place")]
+        self._host = (torch.empty(self.collapsed.shape, dtype=self.collapsed.dtype, pin_memory=True),
+                      torch.empty(self.clen.shape, dtype=self.clen.dtype, pin_memory=True))
 
     def _body(self):
         out = self.model(self.x, self.am)
@@ -355,16 +360,20 @@ class GraphedInference:
             klen = conv_out_lengths(self.model.config, self.am.sum(-1)).to(torch.int32).contiguous()
         ids, col, clen = ops.greedy_decode(out.logits, klen, self.blank)
         ops.join_side_stream()
-        return out.logits, ids, col, clen
+        return out.logits, ids.long(), col, clen
 
     def __call__(self, input_values: torch.Tensor, attention_mask: Optional[torch.Tensor] = None):
         self.x.copy_(input_values, non_blocking=True)
         if self.am is not None:
             self.am.copy_(attention_mask, non_blocking=True)
-        for m in self.model.modules():
-            cache = getattr(m, "cache", None)
-            if cache is not None and hasattr(cache, "refresh_in_place"):
+        ver = sum(p._version for p in self._params)
+        if ver != self._params_version:   # weights replaced through torch since the last call: recompute the cached copies
+            for cache in self._caches:    # INTO the tensors the captured kernels read (one integer sum per call otherwise)
                 cache.refresh_in_place()
+            self._params_version = ver
         self.graph.replay()
-        col, clen = self.collapsed.cpu(), self.clen.cpu()
-        return self.logits, self.ids.long(), [col[b, : int(clen[b])].tolist() for b in range(col.shape[0])]
+        col, clen = self._host
+        col.copy_(self.collapsed, non_blocking=True)
+        clen.copy_(self.clen, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self.logits, self.ids, [col[b, : int(clen[b])].tolist() for b in range(col.shape[0])]
