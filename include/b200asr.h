@@ -214,6 +214,10 @@ int b200asr_mha_bwd(const void* qkv, const void* out, const void* dout, const fl
  * through HBM; the key blocks of a head add in arrival order: reproducible to fp32 rounding, not bit for bit.
  * 2: measurement hook (as 1 without the reduce-adds: dQ is wrong).  Returns the old setting. */
 int b200asr_mha_set_dq_fused(int on);
+/* tuning hook: share of the softmax exponentials the fused attention kernels compute with a degree-3 polynomial on the FMA
+ * pipe (relative error 1e-4, far below the bf16 rounding of the probabilities) instead of the MUFU: fwd / bwd in
+ * {0 = none, 4 = 25 %, 2 = 50 %}, negative = leave unchanged.  Returns the previous setting (fwd * 16 + bwd). */
+int b200asr_mha_set_exp2_poly(int fwd, int bwd);
 
 /* Attention-probability dropout: `nn.functional.dropout(attn_weights, p=config.attention_dropout)` between the softmax and
  * the P V product (HF:189-197; Data2VecAudioConfig.attention_dropout = 0.1 in every reference training run, also inside the

@@ -68,6 +68,7 @@ SIGNATURES = {
     "b200asr_mha_fwd": (i32, [vp, vp, vp, vp, vp, sz, i32, i32, i32, i32, f32, i32, vp]),
     "b200asr_mha_set_fused": (i32, [i32]),
     "b200asr_mha_set_dq_fused": (i32, [i32]),
+    "b200asr_mha_set_exp2_poly": (i32, [i32, i32]),
     "b200asr_attn_keep_words": (sz, [i32, i32, i32]),
     "b200asr_attn_dropout_mask": (i32, [vp, i32, i32, i32, i32, f32, u64, u64, u64, u64, vp, vp]),
     "b200asr_mha_fwd_dropout": (i32, [vp, vp, vp, vp, vp, f32, vp, sz, i32, i32, i32, i32, f32, i32, vp]),

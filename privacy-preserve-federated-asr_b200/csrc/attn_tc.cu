@@ -61,9 +61,14 @@ struct FwdParams {
     unsigned long long* trace;   // diagnostics (b200asr_attn_set_trace): 24 time stamps per CTA, null in normal use
 };
 static unsigned long long* g_attn_trace = nullptr;
+// share of the softmax exponentials computed by the FMA-pipe polynomial (exp2_poly2): 0 = none, 4 = every 4th pair (25 %),
+// 2 = every 2nd (50 %); forward / backward kernel (b200asr_mha_set_exp2_poly)
+static int g_exp2_poly_fwd = 0, g_exp2_poly_bwd = 0;
 #define ATRACE(slot) do { if (p.trace) p.trace[(long long)((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 24 + (slot)] = (unsigned long long)clock64(); } while (0)
 
-template <bool DROP>
+// PM: every PM-th pair of probabilities is computed by exp2_poly2 on the FMA pipe instead of two MUFU ex2 (0 = none): the
+// exp2 / sum / pack phase of a key block was bound by the MUFU's 16 results per clock shared by the 16 softmax warps of an SM
+template <bool DROP, int PM>
 __global__ void __launch_bounds__(F_THREADS, 2)
 mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                   const __grid_constant__ CUtensorMap map_v, const FwdParams p) {
@@ -247,8 +252,15 @@ mha_fwd_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
             uint32_t pk[HC / 2];
 #pragma unroll
             for (int c = 0; c < HC; c += 2) {
-                const float p0 = fast_exp2(fmaf(__uint_as_float(r[c]), c2, -m_new));
-                const float p1 = fast_exp2(fmaf(__uint_as_float(r[c + 1]), c2, -m_new));
+                float p0, p1;
+                if (PM > 0 && ((c >> 1) % (PM > 0 ? PM : 1)) == (PM > 0 ? PM : 1) - 1) {
+                    const float2 pq = exp2_poly2(make_float2(fmaf(__uint_as_float(r[c]), c2, -m_new),
+                                                             fmaf(__uint_as_float(r[c + 1]), c2, -m_new)));
+                    p0 = pq.x; p1 = pq.y;
+                } else {
+                    p0 = fast_exp2(fmaf(__uint_as_float(r[c]), c2, -m_new));
+                    p1 = fast_exp2(fmaf(__uint_as_float(r[c + 1]), c2, -m_new));
+                }
                 sum0 += p0;
                 sum1 += p1;
                 if constexpr (DROP) pk[c >> 1] = bf2_pack((kbits >> c) & 1u ? p0 : 0.f, (kbits >> (c + 1)) & 1u ? p1 : 0.f);
@@ -375,7 +387,7 @@ __device__ __forceinline__ void bulk_reduce_add_f32(float* gdst, uint32_t ssrc, 
                  ::"l"(gdst), "r"(ssrc), "r"(bytes) : "memory");
 }
 
-template <bool DROP, bool FDQ>
+template <bool DROP, bool FDQ, int PM = 0>   // PM: share of the exponentials on the FMA pipe, as in the forward kernel
 __global__ void __launch_bounds__(BwdCfg<FDQ>::THREADS, 1)
 mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
                   const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_do,
@@ -681,8 +693,15 @@ mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap map_k, const __grid_consta
                 const float4 l4 = l2v[c >> 2], d4 = dqv[c >> 2];
                 float p0 = fast_exp2(fmaf(__uint_as_float(s[c]), c2, -l4.x));
                 float p1 = fast_exp2(fmaf(__uint_as_float(s[c + 1]), c2, -l4.y));
-                float p2 = fast_exp2(fmaf(__uint_as_float(s[c + 2]), c2, -l4.z));
-                float p3 = fast_exp2(fmaf(__uint_as_float(s[c + 3]), c2, -l4.w));
+                float p2, p3;
+                if (PM == 2 || (PM == 4 && ((c >> 2) & 1))) {
+                    const float2 pq = exp2_poly2(make_float2(fmaf(__uint_as_float(s[c + 2]), c2, -l4.z),
+                                                             fmaf(__uint_as_float(s[c + 3]), c2, -l4.w)));
+                    p2 = pq.x; p3 = pq.y;
+                } else {
+                    p2 = fast_exp2(fmaf(__uint_as_float(s[c + 2]), c2, -l4.z));
+                    p3 = fast_exp2(fmaf(__uint_as_float(s[c + 3]), c2, -l4.w));
+                }
                 if (!key_valid) p0 = p1 = p2 = p3 = 0.f;
                 if constexpr (DROP) {
                     // P_drop = P o M / (1 - p) feeds dV (the 1 / (1 - p) is applied once, when dV leaves TMEM);
@@ -907,8 +926,12 @@ int mha_fwd_tc_launch(const void* qkv, void* out, float* lse, const int* klen, c
     if (rc) return rc;
     static bool attr_set = false;
     if (!attr_set) {
-        if ((rc = set_max_smem(mha_fwd_tc_kernel<false>, F_SMEM, "mha_fwd(tcgen05)"))) return rc;
-        if ((rc = set_max_smem(mha_fwd_tc_kernel<true>, F_SMEM, "mha_fwd(tcgen05)"))) return rc;
+        if ((rc = set_max_smem(mha_fwd_tc_kernel<false, 0>, F_SMEM, "mha_fwd(tcgen05)"))) return rc;
+        if ((rc = set_max_smem(mha_fwd_tc_kernel<true, 0>, F_SMEM, "mha_fwd(tcgen05)"))) return rc;
+        if ((rc = set_max_smem(mha_fwd_tc_kernel<false, 2>, F_SMEM, "mha_fwd(tcgen05)"))) return rc;
+        if ((rc = set_max_smem(mha_fwd_tc_kernel<true, 2>, F_SMEM, "mha_fwd(tcgen05)"))) return rc;
+        if ((rc = set_max_smem(mha_fwd_tc_kernel<false, 4>, F_SMEM, "mha_fwd(tcgen05)"))) return rc;
+        if ((rc = set_max_smem(mha_fwd_tc_kernel<true, 4>, F_SMEM, "mha_fwd(tcgen05)"))) return rc;
         attr_set = true;
     }
     FwdParams p;
@@ -917,8 +940,11 @@ int mha_fwd_tc_launch(const void* qkv, void* out, float* lse, const int* klen, c
     p.keep = keep; p.KW = attn_keep_kw(T); p.TQ = attn_keep_tq(T); p.inv_keep = 1.0f / (1.0f - p_drop);
     p.trace = g_attn_trace;
     dim3 grid(ceil_div(T, FQ), H, B);
-    if (keep) launch_pdl(mha_fwd_tc_kernel<true>, grid, dim3(F_THREADS), (size_t)F_SMEM, st, mq, mk, mv, p);
-    else launch_pdl(mha_fwd_tc_kernel<false>, grid, dim3(F_THREADS), (size_t)F_SMEM, st, mq, mk, mv, p);
+#define FWD_LAUNCH(DR, PMV) launch_pdl(mha_fwd_tc_kernel<DR, PMV>, grid, dim3(F_THREADS), (size_t)F_SMEM, st, mq, mk, mv, p)
+    const int pm = g_exp2_poly_fwd;
+    if (keep) { if (pm == 2) FWD_LAUNCH(true, 2); else if (pm == 4) FWD_LAUNCH(true, 4); else FWD_LAUNCH(true, 0); }
+    else { if (pm == 2) FWD_LAUNCH(false, 2); else if (pm == 4) FWD_LAUNCH(false, 4); else FWD_LAUNCH(false, 0); }
+#undef FWD_LAUNCH
     return check_launch("mha_fwd_tcgen05");
 }
 
@@ -929,16 +955,16 @@ size_t mha_bwd_tc_workspace_bytes(int B, int T, int H) {
     return (dst > acc ? dst : acc) + (((size_t)B * H * T * 4 + 255) & ~(size_t)255);
 }
 
-template <bool DROP, bool FDQ>
+template <bool DROP, bool FDQ, int PM = 0>
 static int launch_bwd_kernel(dim3 grid, size_t smem, cudaStream_t st, const CUtensorMap& mk, const CUtensorMap& mv,
                              const CUtensorMap& mq, const CUtensorMap& mdo, const CUtensorMap& mdst, const attn::BwdParams& p) {
     static bool attr_set = false;
     if (!attr_set) {
-        int rc = attn::set_max_smem(attn::mha_bwd_tc_kernel<DROP, FDQ>, 227 * 1024, "mha_bwd(tcgen05)");
+        int rc = attn::set_max_smem(attn::mha_bwd_tc_kernel<DROP, FDQ, PM>, 227 * 1024, "mha_bwd(tcgen05)");
         if (rc) return rc;
         attr_set = true;
     }
-    launch_pdl(attn::mha_bwd_tc_kernel<DROP, FDQ>, grid, dim3(attn::BwdCfg<FDQ>::THREADS), smem, st, mk, mv, mq, mdo, mdst, p);
+    launch_pdl(attn::mha_bwd_tc_kernel<DROP, FDQ, PM>, grid, dim3(attn::BwdCfg<FDQ>::THREADS), smem, st, mk, mv, mq, mdo, mdst, p);
     return check_launch("mha_bwd_tcgen05");
 }
 
@@ -1003,8 +1029,16 @@ int mha_bwd_tc_launch(const void* qkv, const void* out, const void* dout, const 
         launch_pdl(mha_bwd_dq_store_kernel, dim3((unsigned)g), dim3(256), 0, st, (const float*)dq_acc, (__nv_bfloat16*)dqkv, B, T, H);
         return check_launch("mha_bwd_dq_store");
     }
-    rc = keep ? launch_bwd_kernel<true, false>(grid, smem, st, mk, mv, mq, mdo, mdst, p)
-              : launch_bwd_kernel<false, false>(grid, smem, st, mk, mv, mq, mdo, mdst, p);
+    const int pm = g_exp2_poly_bwd;
+    if (pm == 2)
+        rc = keep ? launch_bwd_kernel<true, false, 2>(grid, smem, st, mk, mv, mq, mdo, mdst, p)
+                  : launch_bwd_kernel<false, false, 2>(grid, smem, st, mk, mv, mq, mdo, mdst, p);
+    else if (pm == 4)
+        rc = keep ? launch_bwd_kernel<true, false, 4>(grid, smem, st, mk, mv, mq, mdo, mdst, p)
+                  : launch_bwd_kernel<false, false, 4>(grid, smem, st, mk, mv, mq, mdo, mdst, p);
+    else
+        rc = keep ? launch_bwd_kernel<true, false>(grid, smem, st, mk, mv, mq, mdo, mdst, p)
+                  : launch_bwd_kernel<false, false>(grid, smem, st, mk, mv, mq, mdo, mdst, p);
     if (rc) return rc;
     // dQ[q, n] = sum_key dS^T[key, q] K[key, n]   (dS already carries the softmax scale)
     b200asr_gemm_args g = {};
@@ -1029,6 +1063,16 @@ extern "C" int b200asr_attn_set_trace(void* buf) {
 // 0 (default): the backward stores dS^T and a batched GEMM produces dQ (bit-reproducible; measured faster);
 // 1: dQ is accumulated inside the backward kernel (fp32 bulk reduce-add, reproducible to rounding); 2: measurement hook.
 // Returns the previous setting.
+// Share of the softmax exponentials of the fused attention kernels computed by a degree-3 polynomial on the FMA pipe
+// instead of the MUFU: fwd / bwd in {0, 4 (every 4th pair: 25 %), 2 (50 %)}; a negative value keeps the current
+// setting.  Returns the previous setting as fwd * 16 + bwd.
+extern "C" int b200asr_mha_set_exp2_poly(int fwd, int bwd) {
+    const int old = b200asr::attn::g_exp2_poly_fwd * 16 + b200asr::attn::g_exp2_poly_bwd;
+    if (fwd >= 0) b200asr::attn::g_exp2_poly_fwd = (fwd == 2 || fwd == 4) ? fwd : 0;
+    if (bwd >= 0) b200asr::attn::g_exp2_poly_bwd = (bwd == 2 || bwd == 4) ? bwd : 0;
+    return old;
+}
+
 extern "C" int b200asr_mha_set_dq_fused(int on) {
     const int old = b200asr::attn::g_dq_fused;
     b200asr::attn::g_dq_fused = (on < 0 || on > 2) ? 0 : on;

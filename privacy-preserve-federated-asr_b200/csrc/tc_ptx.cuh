@@ -170,6 +170,28 @@ __device__ __forceinline__ float fast_exp2(float x) {
     return y;
 }
 
+// 2^x for a pair on the FMA / ALU pipes instead of the MUFU (16 ex2 per clock and SM against 128 FMA lanes): round-to-
+// nearest split x = i + f by the 1.5 * 2^23 trick, degree-3 polynomial for 2^f on [-0.5, 0.5] (relative error 1.0e-4, a
+// fortieth of a bf16 ulp -- the probabilities it produces are rounded to bf16 for the MMA), exponent add by an integer
+// shift.  Three packed FFMA2 + three packed FADD2 + 2 x (SHL, IADD) per pair.  x is clamped to >= -126 (result 2^-126
+// instead of 0 for masked entries: callers that need an exact zero select it).
+__device__ __forceinline__ float2 exp2_poly2(float2 x) {
+    x.x = fmaxf(x.x, -126.f);
+    x.y = fmaxf(x.y, -126.f);
+    const float2 magic = make_float2(12582912.f, 12582912.f);
+    const float2 xi = __fadd2_rn(x, magic);                                   // low mantissa bits = round(x)
+    const float2 fi = __fadd2_rn(xi, make_float2(-12582912.f, -12582912.f));  // round(x) as a float
+    const float2 f = __ffma2_rn(fi, make_float2(-1.f, -1.f), x);              // x - round(x) in [-0.5, 0.5]
+    float2 q = __ffma2_rn(make_float2(0.05583828315138817f, 0.05583828315138817f), f,
+                          make_float2(0.2426394820213318f, 0.2426394820213318f));
+    q = __ffma2_rn(q, f, make_float2(0.6931367516517639f, 0.6931367516517639f));
+    q = __ffma2_rn(q, f, make_float2(0.9999245405197144f, 0.9999245405197144f));
+    float2 r;
+    r.x = __int_as_float(__float_as_int(q.x) + (__float_as_int(xi.x) << 23));
+    r.y = __int_as_float(__float_as_int(q.y) + (__float_as_int(xi.y) << 23));
+    return r;
+}
+
 // ---- CTA-pair (cta_group::2) variants: two CTAs of a cluster drive one 256-row UMMA, each holding half of B
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;

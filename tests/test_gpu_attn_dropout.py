@@ -150,6 +150,43 @@ def test_fused_dq_matches_the_gemm_path(B, T, H, klens):
     assert float((res[1][0][:, :, 0].float() - res[1][1][:, :, 0].float()).abs().max()) <= 2 ** -7 * float(res[0][0][:, :, 0].float().abs().max())
 
 
+@pytest.mark.parametrize("B,T,H,klens", [(2, 499, 4, None), (3, 200, 2, [200, 77, 1]), (1, 1499, 2, [1016])])
+@pytest.mark.parametrize("share", [4, 2])
+@pytest.mark.parametrize("p_drop", [0.0, 0.1])
+def test_polynomial_exp2_share_matches_the_mufu_kernels(B, T, H, klens, share, p_drop):
+    """b200asr_mha_set_exp2_poly: a quarter / half of the softmax exponentials on the FMA pipe (degree-3 polynomial, 1e-4
+    relative) -- forward output, log-sum-exp and all three gradients equal the all-MUFU kernels' to bf16 rounding, with and
+    without attention dropout, ragged key lengths included."""
+    g = torch.Generator().manual_seed(7 * T + B)
+    dh, D_ = 64, H * 64
+    qd = (torch.randn(B * T, 3 * D_, generator=g) * 1.5).to(torch.bfloat16).to(DEV)
+    dout = torch.randn(B * T, D_, generator=g).to(torch.bfloat16).to(DEV)
+    kl = torch.tensor(klens, dtype=torch.int32, device=DEV) if klens is not None else None
+    keep = ops.attn_dropout_mask(1, B, T, H, p_drop, 77, 19, 4, 3)[0] if p_drop > 0 else None
+    scale = dh ** -0.5
+    res = {}
+    old = lib.b200asr_mha_set_exp2_poly(0, 0)
+    try:
+        for mode in (0, share):
+            lib.b200asr_mha_set_exp2_poly(mode, mode)
+            out, lse = ops.mha_fwd(qd, kl, B, T, H, dh, scale, keep=keep, p_drop=p_drop)
+            dqkv = ops.mha_bwd(qd, out, dout, lse, kl, B, T, H, dh, scale, keep=keep, p_drop=p_drop)
+            res[mode] = (out.float().clone(), lse.clone(), dqkv.float().clone())
+        torch.cuda.synchronize()
+    finally:
+        lib.b200asr_mha_set_exp2_poly(old >> 4, old & 15)
+    (o0, l0, g0), (o1, l1, g1) = res[0], res[share]
+    assert torch.isfinite(o1).all() and torch.isfinite(g1).all() and torch.isfinite(l1).all()
+    assert rel(o1, o0) < 1.2e-2
+    assert float((l1 - l0).abs().max()) < 5e-4          # log-sum-exp: 1e-4 relative error of the row sum
+    g0, g1 = g0.view(B, T, 3, H, dh), g1.view(B, T, 3, H, dh)
+    for i in range(3):
+        assert rel(g1[:, :, i], g0[:, :, i]) < 1.5e-2, i
+    if kl is not None:   # keys beyond an utterance's length get no gradient in either mode
+        masked = torch.arange(T, device=DEV)[None] >= kl[:, None]
+        assert float(g1[:, :, 1:][masked].abs().max()) == 0.0
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("family", ["data2vec_postln", "hubert_stable"])
 def test_all_dropouts_training_step_vs_oracle_given_masks(family, dtype):

@@ -154,6 +154,25 @@ def mha_drop(kind, dq_fused=1):
     return mk
 
 
+def mha_poly(kind, share):
+    """fused attention with `share` (4 = 25 %, 2 = 50 %) of the exponentials on the FMA pipe (b200asr_mha_set_exp2_poly)."""
+    from b200asr._lib import lib
+
+    def mk():
+        qkv = rnd(M, 3 * D); do = rnd(M, D, scale=0.1)
+        out, lse = ops.mha_fwd(qkv, None, B, T, H, 64, 0.125)
+
+        def run():
+            old = lib.b200asr_mha_set_exp2_poly(share, share)
+            if kind == "fwd":
+                ops.mha_fwd(qkv, None, B, T, H, 64, 0.125)
+            else:
+                ops.mha_bwd(qkv, out, do, lse, None, B, T, H, 64, 0.125)
+            lib.b200asr_mha_set_exp2_poly(old >> 4, old & 15)
+        return run
+    return mk
+
+
 def mha_b_mode(dq_fused):
     from b200asr._lib import lib
 
@@ -239,6 +258,9 @@ bench("gemm W1  [3992,1024]x[4096,1024] gelu + gelu'        (x24)", w1_gemm(Fals
 bench("gemm W1  ... + activation dropout in the epilogue    (x24 when p > 0)", w1_gemm(True), flops=2.0 * M * D * F)
 tot += 24 * bench("mha_fwd  B8 T499 H16 dh64            (x24)", mha_f(), flops=4.0 * B * H * T * T * 64)
 tot += 24 * bench("mha_bwd  B8 T499 H16 dh64 (+dsum,dQ) (x24)", mha_b(), flops=10.0 * B * H * T * T * 64)
+for share, pct in ((0, 0), (4, 25), (2, 50)):
+    bench(f"mha_fwd  ... {pct:2d} % of the exp2 as FMA-pipe polynomial", mha_poly("fwd", share), flops=4.0 * B * H * T * T * 64)
+    bench(f"mha_bwd  ... {pct:2d} % of the exp2 as FMA-pipe polynomial", mha_poly("bwd", share), flops=10.0 * B * H * T * T * 64)
 bench("mha_bwd  ... dQ in-kernel, fp32 bulk reduce-add", mha_b_mode(1), flops=10.0 * B * H * T * T * 64)
 bench("mha_bwd  ... dQ in-kernel, reduce-adds skipped (hook)", mha_b_mode(2), flops=10.0 * B * H * T * T * 64)
 bench("mha_fwd  ... + attention dropout 0.1 keep bits", mha_drop("fwd"), flops=4.0 * B * H * T * T * 64)
