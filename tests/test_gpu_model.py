@@ -88,19 +88,34 @@ def test_dacs_vs_reference_golden(golden_dir, name, dtype):
     gl = (-torch.from_numpy(g["exp_lm"]).log()).to(DEV)
     ga = (-torch.from_numpy(g["exp_ad"]).log()).to(DEV)
     out = model(input_values=b["input_values"].to(DEV), attention_mask=b["attention_mask"].to(DEV),
-                labels=b["labels"].to(DEV), dementia_labels=b["dementia_labels"].to(DEV), gumbel_noise=(gl, ga))
+                labels=b["labels"].to(DEV), dementia_labels=b["dementia_labels"].to(DEV), gumbel_noise=(gl, ga),
+                return_masks=True)
     out.loss.backward()
     params = dict(model.named_parameters())
     have_grad = {n for n, p in params.items() if p.grad is not None}
     assert have_grad == {str(n) for n in g["gnorm_names"]}  # stage freezing: same trainable set as the reference
+    logits = out.logits["ASR logits"]
     if dtype == torch.float32:
         # a bf16 run flips a few near-tie hard masks, so logits are only comparable elementwise in fp32
-        assert relinf(out.logits, g["logits"]) < TOL[dtype]
+        assert relinf(logits, g["logits"]) < TOL[dtype]
         assert abs(float(out.loss) - float(g["loss"])) / abs(float(g["loss"])) < TOL[dtype]
         for n in g["grad_names"]:
             assert relinf(params[str(n)].grad, g["grad:" + str(n)]) < 3e-3, n
     else:
-        assert abs(float(out.loss) - float(g["loss"])) / abs(float(g["loss"])) < 5e-2
+        # bf16: the hard decisions sit behind a comparison, so the 1e-2 error of the hidden states flips the near-ties.  Stated:
+        # the flip rate against the oracle's decisions; asserted within the bf16 tolerance: loss and logits against the
+        # oracle evaluated with THIS run's decisions (the large-configuration test does the same, test_gpu_large.py)
+        my_lm = (out.logits["lm_mask"].float() > 0.5).cpu()
+        my_ad = (out.logits["dementia_mask"].float() > 0.5).cpu()
+        ref = D.dacs_forward(sd, cfg, args, b["input_values"], b["attention_mask"], b["labels"], b["dementia_labels"],
+                             gl.cpu(), ga.cpu())
+        flip = float(((my_lm != (ref["lm_mask"] > 0.5)).float().mean() + (my_ad != (ref["ad_mask"] > 0.5)).float().mean()) / 2)
+        print(f"[dacs bf16] {name}: hard-mask flip rate {flip:.2e}")
+        assert flip < 2e-2, flip
+        given = D.dacs_forward(sd, cfg, args, b["input_values"], b["attention_mask"], b["labels"], b["dementia_labels"],
+                               gl.cpu(), ga.cpu(), hard_lm=my_lm, hard_ad=my_ad)
+        assert abs(float(out.loss) - float(given["loss"])) / abs(float(given["loss"])) < TOL[dtype]
+        assert relinf(logits, given["logits"]) < TOL[dtype]
 
 
 def test_eval_twin_returns_masks_and_greedy_matches_oracle():
