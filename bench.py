@@ -706,7 +706,7 @@ def main():
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around the timed steps (ncu --profile-from-start off)")
     ap.add_argument("--no-chunked-adamw", action="store_true", help="layer-wise FedAvg: keep AdamW inside the last graph instead of chunk by chunk")
     ap.add_argument("--no-layerwise", action="store_true", help="N>1: aggregate the whole buffer at once instead of block by block")
-    ap.add_argument("--fedavg-blocks", type=int, default=128, help="grid cap of the exchange kernels in the layer-wise pipelined FedAvg")
+    ap.add_argument("--fedavg-blocks", type=int, default=32, help="grid cap of the exchange kernels in the layer-wise pipelined FedAvg")
     ap.add_argument("--fedavg-group", type=int, default=2, help="encoder blocks per exchange of the layer-wise pipelined FedAvg")
     ap.add_argument("--dropout", type=float, default=0.1,
                     help="hidden = activation = attention = final dropout P in the timed training step (0.1 = the "
