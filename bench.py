@@ -362,9 +362,9 @@ def run_b200(args):
     if not args.eager:
         from b200asr.graph import GraphedTrainStep
         # N > 1: the frozen conv stack is a graph of its own, so that the next round's begin() can run under the aggregation
-        layerwise = world > 1 and ld > 0 and not args.no_overlap and not args.no_layerwise
+        layerwise = world > 1 and not args.no_overlap and not args.no_layerwise
         graphed = GraphedTrainStep(model, opt, resident[0], max_label_len=120, split_conv=(world > 1 and not args.no_overlap),
-                                   defer_adamw=(layerwise and not args.no_chunked_adamw))
+                                   defer_adamw=(layerwise and not args.no_chunked_adamw), per_block_graphs=layerwise)
     skipped_blocks = [0]
     # N > 1 with per-block graphs: layer-wise FedAvg on a comm stream, each block's graph of the NEXT round waits only for
     # its own parameters (fedavg.PipelinedFedAvg) -- the aggregation hides behind the forward pass

@@ -87,7 +87,7 @@ class GraphedTrainStep:
     next call overwrites.  `last_skipped_layers` holds the blocks LayerDrop skipped in the latest call."""
 
     def __init__(self, model, opt, example_batch: Dict[str, torch.Tensor], max_label_len: Optional[int] = None,
-                 warmup: int = 3, split_conv: bool = False, defer_adamw: bool = False):
+                 warmup: int = 3, split_conv: bool = False, defer_adamw: bool = False, per_block_graphs: bool = False):
         """split_conv: capture the frozen conv feature extractor as a graph of its own, replayed by `begin(batch)`; the
         rest of the update is replayed by `finish()`.  The conv stack does not depend on the trainable weights, so a
         federated client can run `begin(next batch)` while the FedAvg of the previous round is still in flight."""
@@ -100,7 +100,9 @@ class GraphedTrainStep:
             model.validate_labels = False  # the reference's host-side range check would synchronise (models.py:483)
         self.backbone = getattr(model, "backbone", None)
         self.layerdrop = _layerdrop_p(model)
-        self.segmented = self.layerdrop > 0.0
+        # per_block_graphs: cut the update at the block boundaries even without LayerDrop (the layer-wise pipelined FedAvg
+        # makes every block's graph wait only for the average of its own parameters)
+        self.segmented = self.layerdrop > 0.0 or bool(per_block_graphs)
         self.split_conv = bool(split_conv)
         if (self.segmented or self.split_conv) and self.backbone is None:
             raise ValueError("GraphedTrainStep: LayerDrop needs a model with a `backbone` (Data2VecAudioModel)")
@@ -223,7 +225,7 @@ class GraphedTrainStep:
         parameter outside the encoder blocks (projection, positional conv, encoder LayerNorm, heads), chunk 1 + l = block l.
         Each chunk is a list of (group index, start, end) in elements."""
         if not self.segmented:
-            raise RuntimeError("fedavg_chunks: needs the per-block graphs (config.layerdrop > 0)")
+            raise RuntimeError("fedavg_chunks: needs the per-block graphs (config.layerdrop > 0 or per_block_graphs=True)")
         chunks = [[] for _ in range(self.L + 1)]
         for gi, g in enumerate(self.opt.groups):
             fp = g["fp"]

@@ -248,3 +248,28 @@ def test_graphed_inference_matches_eager(dtype, ragged):
     lg, ids, seqs = infer(b["input_values"], b["attention_mask"] if ragged else None)
     lg_e, ids_e, seqs_e = eager(b)
     assert torch.equal(lg, lg_e) and torch.equal(ids, ids_e) and seqs == seqs_e
+
+
+def test_per_block_graphs_without_layerdrop_match_eager():
+    """per_block_graphs=True cuts the captured update at the block boundaries although no block is ever dropped (the
+    layer-wise pipelined FedAvg wants one graph per block): same losses and parameters as the eager path."""
+    cfg = R.ArchConfig.tiny(num_hidden_layers=3)
+    sd = R.init_state_dict(cfg, seed=33, dacs=False)
+    batches = [R.synth_batch(cfg, 2, 6000, seed=190 + i, ragged=True, max_label=12) for i in range(4)]
+    m1, o1 = make(cfg, sd, torch.float32)
+    eager = []
+    for b in batches:
+        o1.zero_grad()
+        out = m1(**dev(b))
+        out.loss.backward()
+        o1.step()
+        eager.append(float(out.loss))
+    m2, o2 = make(cfg, sd, torch.float32)
+    step = GraphedTrainStep(m2, o2, dev(batches[0]), max_label_len=16, split_conv=True, defer_adamw=True, per_block_graphs=True)
+    assert step.segmented and len(step.graphs) == 2 * 3 + 3 and len(step.fedavg_chunks()) == 3 + 1
+    graphed = [float(step(dev(b))) for b in batches]
+    assert step.last_skipped_layers == ()
+    for a, b in zip(eager, graphed):
+        assert abs(a - b) <= 1e-4 * abs(a), (eager, graphed)
+    for (n, p1), (_, p2) in zip(m1.named_parameters(), m2.named_parameters()):
+        assert relinf(p2.detach(), p1.detach()) < 1e-4, n
