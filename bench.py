@@ -373,7 +373,7 @@ def run_b200(args):
         ch = graphed.fedavg_chunks()   # [non-block parameters, block 0, block 1, ...]; --fedavg-group blocks per exchange
         G = max(1, args.fedavg_group)
         grouped = [ch[0]] + [sum(ch[1 + i:1 + i + G], []) for i in range(0, len(ch) - 1, G)]
-        pipe = PipelinedFedAvg([g["fp"] for g in opt.groups], grouped, agg=peer_agg, max_blocks=args.fedavg_blocks)
+        pipe = PipelinedFedAvg([g["fp"] for g in opt.groups], grouped, agg=peer_agg, max_blocks=args.fedavg_blocks or 128)
         pipe_event_of_block = [0] + [1 + i // G for i in range(len(ch) - 1)]   # chunk index per graph chunk
         cp = graphed.fedavg_chunk_params()
         grouped_cp = [cp[0]] + [sum(cp[1 + i:1 + i + G], []) for i in range(0, len(cp) - 1, G)]
@@ -548,6 +548,13 @@ def run_b200(args):
                 if "nvls_kernel_ms" in agg_alone:
                     cand["nvls"] = agg_alone["nvls_kernel_ms"]
                 chosen["impl"] = min(cand, key=cand.get)
+    if pipe is not None:
+        # grid cap of the overlapped exchange kernels, measured per implementation (N = 2 / 4 / 8 sweeps in profiles/
+        # r02_scaling.txt): the in-switch reduction is link bound with 32 CTAs and every further CTA only takes SM time from
+        # the forward pass; the peer kernel needs 128 CTAs of P2P loads in flight
+        if args.fedavg_blocks <= 0:
+            args.fedavg_blocks = 32 if chosen["impl"] == "nvls" else 128
+        pipe.max_blocks = args.fedavg_blocks
     clocks = ClockSampler(local_rank) if rank == 0 else None
     n0 = _lib.launch_count()
     if args.profile_range:   # `ncu --profile-from-start off`: exactly the timed steps are captured
@@ -706,7 +713,8 @@ def main():
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around the timed steps (ncu --profile-from-start off)")
     ap.add_argument("--no-chunked-adamw", action="store_true", help="layer-wise FedAvg: keep AdamW inside the last graph instead of chunk by chunk")
     ap.add_argument("--no-layerwise", action="store_true", help="N>1: aggregate the whole buffer at once instead of block by block")
-    ap.add_argument("--fedavg-blocks", type=int, default=32, help="grid cap of the exchange kernels in the layer-wise pipelined FedAvg")
+    ap.add_argument("--fedavg-blocks", type=int, default=0,
+                    help="grid cap of the exchange kernels in the layer-wise pipelined FedAvg (0 = 32 for nvls, 128 for peer / nccl)")
     ap.add_argument("--fedavg-group", type=int, default=2, help="encoder blocks per exchange of the layer-wise pipelined FedAvg")
     ap.add_argument("--dropout", type=float, default=0.1,
                     help="hidden = activation = attention = final dropout P in the timed training step (0.1 = the "
