@@ -160,6 +160,17 @@ int b200asr_gemm(const b200asr_gemm_args* args, void* stream);
  * by b200asr_dropout); one batch, ldc = N, N % 8 == 0. */
 int b200asr_gemm_dropout(const b200asr_gemm_args* args, float p, unsigned long long seed, unsigned long long site,
                          unsigned long long offset, const unsigned long long* dev_offset, void* stream);
+/* Keep bits of `nsites` dropout sites (site0, site0 + site_stride, ...) over a row-major [rows, cols] tensor each, drawn
+ * ahead of their consumer: bit (n & 31) of word out[(site * (cols / 32) + n / 32) * mpad + m] = "element (m, n) is kept" --
+ * the decision b200asr_dropout takes for the same (p, seed, site, offset, dev_offset).  cols % 32 == 0, mpad >= rows;
+ * b200asr_dropout_keep_words(cols, mpad) words per site.  One launch per training step serves the activation dropout
+ * (HF:335-339) of every encoder block; b200asr_gemm_dropout_bits is b200asr_gemm_dropout reading these bits (mpad >= M
+ * rounded up to 512, N % 64 == 0). */
+size_t b200asr_dropout_keep_words(int cols, int mpad);
+int b200asr_dropout_keep_bits(unsigned* out, int nsites, unsigned long long site0, unsigned long long site_stride, int rows,
+                              int cols, int mpad, float p, unsigned long long seed, unsigned long long offset,
+                              const unsigned long long* dev_offset, void* stream);
+int b200asr_gemm_dropout_bits(const b200asr_gemm_args* args, const unsigned* keep_bits, int mpad, float p, void* stream);
 
 /* test / tuning hook: force the tcgen05 tile configuration: 0 = built-in cost model, else ncta * 1000 + bn
  * (1064, 1128, 1256 single CTA; 2128, 2256 CTA pair = cluster of 2 with cta_group::2 MMA).  Returns the old value. */

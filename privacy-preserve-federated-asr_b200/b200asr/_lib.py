@@ -57,6 +57,9 @@ SIGNATURES = {
     "b200asr_conv0_ln_gelu_fwd": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, vp]),
     "b200asr_gemm": (i32, [C.POINTER(GemmArgs), vp]),
     "b200asr_gemm_dropout": (i32, [C.POINTER(GemmArgs), f32, u64, u64, u64, vp, vp]),
+    "b200asr_gemm_dropout_bits": (i32, [C.POINTER(GemmArgs), vp, i32, f32, vp]),
+    "b200asr_dropout_keep_words": (sz, [i32, i32]),
+    "b200asr_dropout_keep_bits": (i32, [vp, i32, u64, u64, i32, i32, i32, f32, u64, u64, vp, vp]),
     "b200asr_gemm_force_config": (i32, [i32]),
     "b200asr_gemm_set_trace": (i32, [vp]),
     "b200asr_attn_set_trace": (i32, [vp]),

@@ -492,13 +492,13 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
     (seed, site, counter) in the backward pass, never stored.  Dropout on the attention probabilities
     (attention_dropout, HF:189-197) is applied inside the attention kernels from keep bits drawn ahead of time
     (site0 + 3, ops.attn_dropout_mask): `keep` int32 bits of this block or None, `p_attn` its probability.
-    drop = (p_hidden, p_act, seed, site0, counter, keep, p_attn): sites site0 .. site0+3."""
+    drop = (p_hidden, p_act, seed, site0, counter, keep, p_attn[, (act_keep_bits, mpad)]): sites site0 .. site0+3."""
 
     @staticmethod
     def forward(ctx, x, klen, meta, cache: ShadowCache, drop, *P):
         (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = P
         B, T, H, eps = meta
-        ph, pa, seed, site, ctr, keep, pt = drop
+        ph, pa, seed, site, ctr, keep, pt, akeep = (tuple(drop) + (None,))[:8]
         M, d = x.shape
         dh = d // H
         scale = dh ** -0.5
@@ -513,7 +513,9 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
         # activation dropout inside the W1 GEMM epilogue: g and the saved gelu' both carry mask_a / (1 - p_a), so the
         # backward pass needs no dropout pass either (fp32 parity mode: separate passes, same mask)
         fused_a = pa > 0.0 and ops.gemm_dropout_fusable(x1, w1s)
-        g, u = ops.linear_fwd(x1, w1s, b1, act=ACT_GELU_SAVE_GRAD, drop=(pa, seed, site + 1, ctr) if fused_a else None)
+        # (akeep: the decisions were drawn ahead of time for all blocks, modeling._draw_activation_keep; else Philox in the epilogue)
+        adrop = None if not fused_a else ((pa, akeep[0], akeep[1]) if akeep is not None else (pa, seed, site + 1, ctr))
+        g, u = ops.linear_fwd(x1, w1s, b1, act=ACT_GELU_SAVE_GRAD, drop=adrop)
         if not fused_a:
             g = ops.dropout(g, pa, seed, site + 1, ctr, out=g)
         ctx.fused_a = fused_a
@@ -531,7 +533,7 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
         (x, qkv, attn, lse, s1, m1, r1, x1, u, g, s2, m2, r2, wqkv, wo, w1s, w2s) = ctx.saved_tensors
         (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = ctx.params
         B, T, H, dh, scale = ctx.meta
-        ph, pa, seed, site, ctr, keep, pt = ctx.drop
+        ph, pa, seed, site, ctr, keep, pt = ctx.drop[:7]
         d = x.shape[1]
         wg = any(ctx.needs_input_grad[5:])  # parameter gradients wanted?
         # LN2 backward emits ds2 (residual path), do2 = hidden-dropout backward of it (gradient of W2 f + b2) and b2's gradient
@@ -719,7 +721,7 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
     def forward(ctx, x, klen, meta, cache: ShadowCache, drop, *P):
         (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = P
         B, T, H, eps = meta
-        ph, pa, seed, site, ctr, keep, pt = drop
+        ph, pa, seed, site, ctr, keep, pt, akeep = (tuple(drop) + (None,))[:8]
         M, d = x.shape
         dh = d // H
         scale = dh ** -0.5
@@ -735,7 +737,9 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
         # activation dropout inside the W1 GEMM epilogue: g and the saved gelu' both carry mask_a / (1 - p_a), so the
         # backward pass needs no dropout pass either (fp32 parity mode: separate passes, same mask)
         fused_a = pa > 0.0 and ops.gemm_dropout_fusable(n2, w1s)
-        g, u = ops.linear_fwd(n2, w1s, b1, act=ACT_GELU_SAVE_GRAD, drop=(pa, seed, site + 1, ctr) if fused_a else None)
+        # (akeep: the decisions were drawn ahead of time for all blocks, modeling._draw_activation_keep; else Philox in the epilogue)
+        adrop = None if not fused_a else ((pa, akeep[0], akeep[1]) if akeep is not None else (pa, seed, site + 1, ctr))
+        g, u = ops.linear_fwd(n2, w1s, b1, act=ACT_GELU_SAVE_GRAD, drop=adrop)
         if not fused_a:
             g = ops.dropout(g, pa, seed, site + 1, ctr, out=g)
         ctx.fused_a = fused_a
@@ -753,7 +757,7 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
         (x, m1, r1, n1, qkv, attn, lse, s1, m2, r2, n2, u, g, wqkv, wo, w1s, w2s) = ctx.saved_tensors
         (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = ctx.params
         B, T, H, dh, scale = ctx.meta
-        ph, pa, seed, site, ctr, keep, pt = ctx.drop
+        ph, pa, seed, site, ctr, keep, pt = ctx.drop[:7]
         d = x.shape[1]
         wg = any(ctx.needs_input_grad[5:])
         if not dy.is_contiguous():

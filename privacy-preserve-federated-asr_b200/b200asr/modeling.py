@@ -205,6 +205,7 @@ class Data2VecAudioModel(nn.Module):
         self.register_buffer("dropout_counter", torch.zeros(1, dtype=torch.int64), persistent=False)
         self._drop_ctr = None
         self._attn_keep = None            # keep bits of this forward's attention-probability dropout, one row per block
+        self._act_keep = None             # (keep bits of the activation dropout, row pitch), one row per block
         self._segment_recorder = None     # set by graph.GraphedTrainStep while it captures an update with LayerDrop
         self._force_no_layerdrop = False
 
@@ -261,6 +262,7 @@ class Data2VecAudioModel(nn.Module):
         forward before the backward (gradient accumulation) cannot shift the first one's masks."""
         self._drop_ctr = None
         self._attn_keep = None
+        self._act_keep = None
         if self.training and any(self._p_drop(n) > 0 for n in ("hidden_dropout", "activation_dropout", "attention_dropout",
                                                                "feat_proj_dropout", "final_dropout")):
             if self.dropout_seed is None:
@@ -282,6 +284,22 @@ class Data2VecAudioModel(nn.Module):
             ops.attn_dropout_mask(n, B, T, H, p, self.dropout_seed, 16 + 3, 4, self._drop_ctr, out=keep)
         self._attn_keep = keep
 
+    def _draw_activation_keep(self, rows):
+        """Keep bits of the activation dropout (HF:335-339) of every block, drawn by ONE launch on the side stream while the
+        conv stack runs; the W1 GEMM's epilogue reads them instead of running Philox itself (the epilogue bounds that GEMM).
+        Same decisions as ops.dropout at site 16 + 4 l + 1.  bf16 path with 64-aligned intermediate size only."""
+        self._act_keep = None
+        p = self._p_drop("activation_dropout")
+        inter = int(self.config.intermediate_size)
+        if p <= 0.0 or self._drop_ctr is None or self.cache.dtype != torch.bfloat16 or inter % 64 != 0:
+            return
+        n = len(self.encoder.layers)
+        mpad = ops.dropout_keep_mpad(rows)
+        keep = torch.empty(n, ops.dropout_keep_words(inter, mpad), dtype=torch.int32, device=self._drop_ctr.device)
+        with ops.on_side_stream(keep, self._drop_ctr, manual_join=True):
+            ops.dropout_keep_bits(n, 16 + 1, 4, rows, inter, p, self.dropout_seed, self._drop_ctr, out=keep)
+        self._act_keep = (keep, mpad)
+
     def apply_dropout(self, x, name, site):
         """nn.Dropout(config.<name>) at a stand-alone site (training mode only)."""
         p = self._p_drop(name)
@@ -298,6 +316,9 @@ class Data2VecAudioModel(nn.Module):
         if self._drop_ctr is not None and self._p_drop("attention_dropout") > 0:
             L_in = int(input_values.shape[-1])
             self._draw_attention_keep(int(input_values.shape[0]), int(conv_out_lengths(c, torch.tensor(L_in))))
+        if self._drop_ctr is not None and self._p_drop("activation_dropout") > 0:
+            L_in = int(input_values.shape[-1])
+            self._draw_activation_keep(int(input_values.shape[0]) * int(conv_out_lengths(c, torch.tensor(L_in))))
         fe = self.feature_extractor.conv_layers
         lns = [getattr(l, "layer_norm", None) for l in fe]
         feats = Fn.feature_extractor_fwd(
@@ -340,7 +361,7 @@ class Data2VecAudioModel(nn.Module):
         drop_block = None
         if self._drop_ctr is not None and (ph > 0 or pa > 0 or pt > 0):
             drop_block = Fn.EncoderLayerStableDropoutFn if stable else Fn.EncoderLayerDropoutFn
-        if self._attn_keep is not None:
+        if self._attn_keep is not None or self._act_keep is not None:
             ops.join_side_stream()   # the keep bits were drawn on the side stream while the conv stack ran
         skipped = self._layerdrop_coins(len(enc.layers))
         self.last_skipped_layers = skipped
@@ -353,7 +374,8 @@ class Data2VecAudioModel(nn.Module):
             elif drop_block is not None:
                 x = drop_block.apply(x, klen, meta, cache,
                                      (ph, pa, self.dropout_seed, 16 + 4 * li, self._drop_ctr,
-                                      None if self._attn_keep is None else self._attn_keep[li], pt),
+                                      None if self._attn_keep is None else self._attn_keep[li], pt,
+                                      None if self._act_keep is None else (self._act_keep[0][li], self._act_keep[1])),
                                      *layer.params())
             else:
                 x = block.apply(x, klen, meta, cache, *layer.params())

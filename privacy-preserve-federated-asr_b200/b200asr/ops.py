@@ -400,7 +400,11 @@ def gemm_raw(A, B, Cout, M, N, K, lda, ldb, ldc, a_kmajor=True, b_kmajor=True, b
     if bias is not None:
         assert bias.dtype == torch.float32
     e0 = _prof_begin()
-    if drop is not None:   # (p, seed, site, counter): element dropout on C and aux_out inside the GELU_SAVE_GRAD epilogue
+    if drop is not None and len(drop) == 3:   # (p, keep_bits, mpad): decisions drawn ahead of time (dropout_keep_bits)
+        pd, bits, mpad = drop
+        assert bits.dtype == torch.int32 and bits.is_contiguous() and bits.numel() >= dropout_keep_words(N, mpad)
+        check(lib.b200asr_gemm_dropout_bits(C.byref(g), _p(bits), int(mpad), float(pd), _st()), "gemm_dropout_bits")
+    elif drop is not None:   # (p, seed, site, counter): element dropout on C and aux_out inside the GELU_SAVE_GRAD epilogue
         pd, seed, site, counter = drop
         dev = counter if isinstance(counter, torch.Tensor) else None
         host = 0 if dev is not None or counter is None else int(counter)
@@ -412,6 +416,31 @@ def gemm_raw(A, B, Cout, M, N, K, lda, ldb, ldc, a_kmajor=True, b_kmajor=True, b
         check(lib.b200asr_gemm_backend(C.byref(g), backend, _st()), "gemm_backend")
     _prof_end("gemm", e0, 2.0 * M * N * K * batch0 * batch1)
     return Cout
+
+
+def dropout_keep_mpad(rows: int) -> int:
+    """Row pitch of the keep-bit words for a GEMM with `rows` output rows (covers the largest tile's row overhang)."""
+    return (int(rows) + 511) // 512 * 512
+
+
+def dropout_keep_words(cols: int, mpad: int) -> int:
+    return int(lib.b200asr_dropout_keep_words(int(cols), int(mpad)))
+
+
+def dropout_keep_bits(nsites: int, site0: int, site_stride: int, rows: int, cols: int, p: float, seed: int, counter=None,
+                      out: Optional[torch.Tensor] = None, device=None) -> torch.Tensor:
+    """Keep bits of `nsites` dropout sites over a [rows, cols] tensor each (b200asr_dropout_keep_bits): int32
+    [nsites, cols / 32 * mpad], the decisions of ops.dropout(p, seed, site0 + i * site_stride, counter)."""
+    mpad = dropout_keep_mpad(rows)
+    words = dropout_keep_words(cols, mpad)
+    dev = counter if isinstance(counter, torch.Tensor) else None
+    host = 0 if dev is not None or counter is None else int(counter)
+    if out is None:
+        out = torch.empty(nsites, words, dtype=torch.int32, device=device if device is not None else dev.device)
+    assert out.dtype == torch.int32 and out.is_contiguous() and out.numel() >= nsites * words
+    check(lib.b200asr_dropout_keep_bits(_p(out), int(nsites), int(site0), int(site_stride), int(rows), int(cols), mpad, float(p),
+                                        int(seed) & (2 ** 64 - 1), host, _p(dev), _st()), "dropout_keep_bits")
+    return out
 
 
 def gemm_dropout_fusable(x, w, out_dtype=None) -> bool:

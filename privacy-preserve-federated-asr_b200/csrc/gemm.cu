@@ -54,7 +54,32 @@ extern "C" int b200asr_gemm_dropout(const b200asr_gemm_args* args, float p, unsi
     }
     if (a.M == 0 || a.N == 0) return B200ASR_OK;
     const DropKeys k = make_drop_keys(p, seed, site, offset, dev_offset);
-    return gemm_tc_launch_dropout(a, k, as_stream(stream));
+    return gemm_tc_launch_dropout(a, k, nullptr, 0, as_stream(stream));
+}
+
+// The same with the keep decisions read from bits drawn ahead of time by b200asr_dropout_keep_bits (one launch per step for
+// every block, off the critical path) instead of four Philox calls per 32 columns inside the epilogue.
+extern "C" int b200asr_gemm_dropout_bits(const b200asr_gemm_args* args, const unsigned* keep_bits, int mpad, float p,
+                                         void* stream) {
+    B200_REQUIRE(args && keep_bits, "gemm_dropout_bits: null pointer");
+    const b200asr_gemm_args& a = *args;
+    B200_REQUIRE(a.A && a.B && a.C && a.aux_out, "gemm_dropout_bits: null operand (aux_out is required)");
+    B200_REQUIRE(a.act == B200ASR_ACT_GELU_SAVE_GRAD && !a.mul_gelu_grad && !a.residual,
+                 "gemm_dropout_bits: only the GELU_SAVE_GRAD epilogue carries the fused dropout");
+    B200_REQUIRE(p >= 0.f && p < 1.f, "gemm_dropout_bits: p=%f must be in [0, 1)", (double)p);
+    B200_REQUIRE(a.batch0 == 1 && a.batch1 == 1 && a.ldc == a.N && a.N % 64 == 0,
+                 "gemm_dropout_bits: C must be one contiguous [M, N] matrix with N %% 64 == 0");
+    B200_REQUIRE(a.M >= 0 && a.N >= 0 && a.K >= 1, "gemm_dropout_bits: bad shape M=%d N=%d K=%d", a.M, a.N, a.K);
+    B200_REQUIRE(mpad >= (a.M + 511) / 512 * 512, "gemm_dropout_bits: mpad=%d must cover M=%d rounded up to 512 (the largest tile)",
+                 mpad, a.M);
+    const char* why = nullptr;
+    if (a.c_dtype != B200ASR_BF16 || !gemm_tc_eligible(a, &why)) {
+        set_error("gemm_dropout_bits: needs the tcgen05 back end with bf16 output (%s)", why ? why : "c_dtype is not bf16");
+        return B200ASR_ERR_UNSUPPORTED;
+    }
+    if (a.M == 0 || a.N == 0) return B200ASR_OK;
+    const DropKeys k = make_drop_keys(p, 0, 0, 0, nullptr);
+    return gemm_tc_launch_dropout(a, k, keep_bits, mpad, as_stream(stream));
 }
 
 // test hook: force a back end (0 = simt, 1 = tcgen05) regardless of the dispatch rule

@@ -92,6 +92,10 @@ struct Params {
     uint2 drop_key;
     unsigned long long drop_offset;
     const unsigned long long* drop_dev_offset;
+    // ... or read from keep bits drawn ahead of the GEMM (b200asr_dropout_keep_bits: word [(n / 32) * drop_mpad + m], bit n & 31):
+    // the four Philox calls per 32 columns are 45 % on top of the epilogue's own work, and the epilogue bounds the K = 1024 GEMMs
+    const uint32_t* drop_bits;
+    int drop_mpad;
     unsigned long long* trace;  // diagnostics (b200asr_gemm_set_trace): 12 time stamps per CTA, null in normal use
 };
 
@@ -551,18 +555,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                                         if constexpr (XK == 6) {
                                             // this lane's 32 columns of row m0w + lane = 4 Philox blocks of 8 elements of the
                                             // row-major [M, N] result (ldc = N, N % 8 == 0: checked by the caller)
-                                            const unsigned long long e0 =
-                                                (unsigned long long)(m0w + lane) * (unsigned long long)p.ldc + (unsigned long long)(n + g * 32);
+                                            if (p.drop_bits) {
+                                                const uint32_t kb = __ldg(p.drop_bits + (long long)((n + g * 32) >> 5) * p.drop_mpad + (m0w + lane));
 #pragma unroll
-                                            for (int q = 0; q < 4; ++q) {
-                                                uint32_t u[8];
-                                                dropout_uniforms<8>(e0 + 8 * q, p.drop_key, drop_off, u);
+                                                for (int j = 0; j < 16; ++j) {
+                                                    const float2 mk = make_float2((kb >> (2 * j)) & 1u ? p.drop_scale : 0.f,
+                                                                                  (kb >> (2 * j + 1)) & 1u ? p.drop_scale : 0.f);
+                                                    v2[j] = __fmul2_rn(v2[j], mk);
+                                                    g2[j] = __fmul2_rn(g2[j], mk);
+                                                }
+                                            } else {
+                                                const unsigned long long e0 =
+                                                    (unsigned long long)(m0w + lane) * (unsigned long long)p.ldc + (unsigned long long)(n + g * 32);
 #pragma unroll
-                                                for (int e = 0; e < 8; e += 2) {
-                                                    const float2 mk = make_float2(u[e] >= p.drop_thresh16 ? p.drop_scale : 0.f,
-                                                                                  u[e + 1] >= p.drop_thresh16 ? p.drop_scale : 0.f);
-                                                    v2[4 * q + e / 2] = __fmul2_rn(v2[4 * q + e / 2], mk);
-                                                    g2[4 * q + e / 2] = __fmul2_rn(g2[4 * q + e / 2], mk);
+                                                for (int q = 0; q < 4; ++q) {
+                                                    uint32_t u[8];
+                                                    dropout_uniforms<8>(e0 + 8 * q, p.drop_key, drop_off, u);
+#pragma unroll
+                                                    for (int e = 0; e < 8; e += 2) {
+                                                        const float2 mk = make_float2(u[e] >= p.drop_thresh16 ? p.drop_scale : 0.f,
+                                                                                      u[e + 1] >= p.drop_thresh16 ? p.drop_scale : 0.f);
+                                                        v2[4 * q + e / 2] = __fmul2_rn(v2[4 * q + e / 2], mk);
+                                                        g2[4 * q + e / 2] = __fmul2_rn(g2[4 * q + e / 2], mk);
+                                                    }
                                                 }
                                             }
                                         }
@@ -685,7 +700,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                             }
                         }
                         float mk[32];   // fused element dropout (drop_on): keep / (1 - p) per column of this row chunk
-                        if (p.drop_on) {
+                        if (p.drop_on && p.drop_bits) {
+                            const uint32_t kb = __ldg(p.drop_bits + (long long)(n >> 5) * p.drop_mpad + m);
+    #pragma unroll
+                            for (int j = 0; j < 32; ++j) mk[j] = (kb >> j) & 1u ? p.drop_scale : 0.f;
+                        } else if (p.drop_on) {
                             const unsigned long long doff = p.drop_offset + (p.drop_dev_offset ? *p.drop_dev_offset : 0ull);
                             const unsigned long long e0 = (unsigned long long)m * (unsigned long long)p.ldc + (unsigned long long)n;
     #pragma unroll
@@ -928,7 +947,12 @@ static bool make_epilogue_map(CUtensorMap* map, const void* base, int M, int N, 
 
 // keys of the element dropout fused into the next launch's GELU_SAVE_GRAD epilogue (set by gemm_tc_launch_dropout around
 // its call; thread-local: the argument struct of the C ABI stays as it is)
-static thread_local const DropKeys* t_epi_drop = nullptr;
+struct EpiDrop {
+    DropKeys k;
+    const uint32_t* bits;   // keep bits drawn ahead (b200asr_dropout_keep_bits) or null: Philox in the epilogue
+    int mpad;
+};
+static thread_local const EpiDrop* t_epi_drop = nullptr;
 
 template <int BN, typename TC, int NCTA = 1>
 static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
@@ -956,10 +980,12 @@ static int launch(const b200asr_gemm_args& a, cudaStream_t st) {
     // staged epilogue when the kernel variant has the shared memory for it and at most ONE second tensor is involved
     p.epi_tma = 0; p.x_kind = 0; p.epi_mode = 0;
     p.drop_on = 0; p.drop_thresh16 = 0; p.drop_scale = 1.f; p.drop_key = make_uint2(0, 0); p.drop_offset = 0;
-    p.drop_dev_offset = nullptr;
+    p.drop_dev_offset = nullptr; p.drop_bits = nullptr; p.drop_mpad = 0;
     if (t_epi_drop) {
-        p.drop_on = 1; p.drop_thresh16 = t_epi_drop->thresh16; p.drop_scale = t_epi_drop->scale; p.drop_key = t_epi_drop->key;
-        p.drop_offset = t_epi_drop->offset; p.drop_dev_offset = t_epi_drop->dev_offset;
+        const DropKeys& k = t_epi_drop->k;
+        p.drop_on = 1; p.drop_thresh16 = k.thresh16; p.drop_scale = k.scale; p.drop_key = k.key;
+        p.drop_offset = k.offset; p.drop_dev_offset = k.dev_offset;
+        p.drop_bits = t_epi_drop->bits; p.drop_mpad = t_epi_drop->mpad;
     }
     if (Cfg<BN, NCTA>::EPI_TMA && !(dbg & 8)) {
         const void* xs[3] = {a.aux_out, a.residual, a.mul_gelu_grad ? a.aux_in : nullptr};
@@ -1110,8 +1136,9 @@ int gemm_tc_launch(const b200asr_gemm_args& a, cudaStream_t st) {
     }
 }
 
-int gemm_tc_launch_dropout(const b200asr_gemm_args& a, const DropKeys& k, cudaStream_t st) {
-    tc::t_epi_drop = &k;
+int gemm_tc_launch_dropout(const b200asr_gemm_args& a, const DropKeys& k, const unsigned* keep_bits, int mpad, cudaStream_t st) {
+    const tc::EpiDrop ed{k, keep_bits, mpad};
+    tc::t_epi_drop = &ed;
     const int rc = gemm_tc_launch(a, st);
     tc::t_epi_drop = nullptr;
     return rc;

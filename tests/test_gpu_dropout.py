@@ -229,6 +229,10 @@ def test_gemm_epilogue_dropout_equals_gemm_then_dropout(shape, cfg):
         assert ops.gemm_dropout_fusable(x, w)
         for counter in (3, torch.tensor([3], device="cuda", dtype=torch.int64)):
             y1, u1 = ops.linear_fwd(x, w, b, act=ACT_GELU_SAVE_GRAD, drop=(p, seed, site, counter))
+            # the same decisions read from bits drawn ahead of the GEMM: identical outputs
+            bits = ops.dropout_keep_bits(2, site - 4, 4, Mr, N, p, seed, counter, device="cuda")
+            y2, u2 = ops.linear_fwd(x, w, b, act=ACT_GELU_SAVE_GRAD, drop=(p, bits[1], ops.dropout_keep_mpad(Mr)))
+            assert torch.equal(y2, y1) and torch.equal(u2, u1)
             mask = ops.dropout(torch.ones(Mr, N, device="cuda", dtype=torch.bfloat16), p, seed, site, counter).float()
             assert 0.85 < float((mask > 0).float().mean()) < 0.95
             for got, plain in ((y1, y0), (u1, u0)):
@@ -247,3 +251,22 @@ def test_gemm_epilogue_dropout_rejects_what_it_cannot_fuse():
     assert not ops.gemm_dropout_fusable(x, w)
     with pytest.raises(RuntimeError, match="gemm_dropout"):
         ops.linear_fwd(x, w, None, act=ACT_GELU_SAVE_GRAD, drop=(0.1, 1, 2, 3))
+
+
+@pytest.mark.parametrize("rows,cols", [(300, 256), (3992, 4096), (17, 64)])
+def test_dropout_keep_bits_are_the_dropout_kernels_decisions(rows, cols):
+    """b200asr_dropout_keep_bits: bit (n & 31) of word [site][n / 32][m] is set exactly where b200asr_dropout keeps element
+    (m, n) for the same keys -- for every site of the launch, host and device step counters; pad rows hold zeros."""
+    p, seed, site0, stride = 0.25, 4321, 17, 4
+    mpad = ops.dropout_keep_mpad(rows)
+    for counter in (9, torch.tensor([9], device="cuda", dtype=torch.int64)):
+        bits = ops.dropout_keep_bits(3, site0, stride, rows, cols, p, seed, counter, device="cuda")
+        assert bits.shape == (3, cols // 32 * mpad)
+        w = bits.view(3, cols // 32, mpad).cpu().numpy().astype(np.uint32)
+        for i in range(3):
+            mask = ops.dropout(torch.ones(rows, cols, device="cuda"), p, seed, site0 + i * stride, counter).cpu().numpy() > 0
+            got = ((w[i][:, :rows, None] >> np.arange(32, dtype=np.uint32)[None, None, :]) & 1).astype(bool)   # [cg, m, bit]
+            got = got.transpose(1, 0, 2).reshape(rows, cols)
+            assert np.array_equal(got, mask)
+            assert not w[i][:, rows:].any()
+        assert 0.70 < float(mask.mean()) < 0.80

@@ -33,8 +33,11 @@ for stage in "$@"; do
                echo "ncu gemm rc=$?";;
     ncu_ops)   # full sets of the memory-bound / latency-bound kernels and of the attention kernels
                timeout 600 python tools/op_one.py > gpurun_out/${TAG}_ncu_plain3.log 2>&1 &&
-               timeout 1500 ncu --set full --clock-control none --import-source on -k "regex:conv0_ln_gelu|ln_fwd|ln_bwd|ctc_kernel|ctc_grad|dacs_mask|mha_fwd_tc|mha_bwd_tc|attn_keep|dropout_kernel|dsum" -c 60 -o gpurun_out/${TAG}_prof_ops python tools/op_one.py > gpurun_out/${TAG}_ncu3.log 2>&1
-               echo "ncu ops rc=$?";;
+               timeout 1500 ncu --set full --clock-control none -k "regex:conv0_ln_gelu|ln_fwd|ln_bwd|ctc_kernel|ctc_grad|dacs_mask|mha_fwd_tc|mha_bwd_tc|attn_keep|dropout_kernel|dropout_keep|dsum" -c 60 -o /tmp/${TAG}_prof_ops python tools/op_one.py > gpurun_out/${TAG}_ncu3.log 2>&1
+               echo "ncu ops rc=$?"
+               # the report itself is too large to travel back (64 MiB limit): export the raw metric page as CSV on the box
+               ncu -i /tmp/${TAG}_prof_ops.ncu-rep --page raw --csv > gpurun_out/${TAG}_prof_ops_raw.csv 2> gpurun_out/${TAG}_ncu3_export.log
+               echo "ncu export rc=$?";;
     *) echo "unknown stage $stage";;
   esac
 done

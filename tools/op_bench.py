@@ -94,11 +94,24 @@ def ln_bwd_drop(cols, rows):
 
 
 def w1_gemm(drop):
-    """The FFN's first GEMM [M, d] x [4d, d]^T with GELU + saved gelu' epilogue, without / with the activation dropout."""
+    """The FFN's first GEMM [M, d] x [4d, d]^T with GELU + saved gelu' epilogue, without / with the activation dropout
+    (drop = "philox": decisions computed in the epilogue, "bits": read from bits drawn ahead)."""
     def mk():
         from b200asr._lib import ACT_GELU_SAVE_GRAD
         x = rnd(M, D); w = rnd(F, D); b = torch.zeros(F, device=dev)
-        return lambda: ops.linear_fwd(x, w, b, act=ACT_GELU_SAVE_GRAD, drop=(0.1, 1234, 17, 7) if drop else None)
+        d = None
+        if drop == "bits":
+            d = (0.1, ops.dropout_keep_bits(1, 17, 4, M, F, 0.1, 1234, 7, device=dev)[0], ops.dropout_keep_mpad(M))
+        elif drop:
+            d = (0.1, 1234, 17, 7)
+        return lambda: ops.linear_fwd(x, w, b, act=ACT_GELU_SAVE_GRAD, drop=d)
+    return mk
+
+
+def keep_bits_all_blocks():
+    def mk():
+        out = ops.dropout_keep_bits(24, 17, 4, M, F, 0.1, 1234, 7, device=dev)
+        return lambda: ops.dropout_keep_bits(24, 17, 4, M, F, 0.1, 1234, 7, out=out)
     return mk
 
 
@@ -255,7 +268,9 @@ bench("dropout [3992,1024]            (x52 when p > 0)", dropout(D, False), nbyt
 bench("dropout [3992,4096] activation (fp32 mode only: fused below)", dropout(F, False), nbytes=2 * M * F * e)
 bench("ln_bwd   [3992,1024] + hidden dropout bwd + colsum (x48 when p > 0)", ln_bwd_drop(D, M), nbytes=4 * M * D * e)
 bench("gemm W1  [3992,1024]x[4096,1024] gelu + gelu'        (x24)", w1_gemm(False), flops=2.0 * M * D * F)
-bench("gemm W1  ... + activation dropout in the epilogue    (x24 when p > 0)", w1_gemm(True), flops=2.0 * M * D * F)
+bench("gemm W1  ... + activation dropout, Philox in the epilogue", w1_gemm("philox"), flops=2.0 * M * D * F)
+bench("gemm W1  ... + activation dropout from keep bits     (x24 when p > 0)", w1_gemm("bits"), flops=2.0 * M * D * F)
+bench("activation keep bits, 24 blocks in one launch (x1, side stream)", keep_bits_all_blocks(), nbytes=24 * M * F // 8)
 tot += 24 * bench("mha_fwd  B8 T499 H16 dh64            (x24)", mha_f(), flops=4.0 * B * H * T * T * 64)
 tot += 24 * bench("mha_bwd  B8 T499 H16 dh64 (+dsum,dQ) (x24)", mha_b(), flops=10.0 * B * H * T * T * 64)
 for share, pct in ((0, 0), (4, 25), (2, 50)):

@@ -40,6 +40,7 @@ for _ in range(3):
     ops.dacs_mask_bwd(x, dy, hid, sl, sa, ml, ma, 1.0, 0.0, want_dh=False)
     ops.dropout(x, 0.1, 1234, 16, 7, residual=dy)
     ops.attn_dropout_mask(24, B, T, H, 0.1, 1234, 19, 4, 5, out=keep24)
+    ops.dropout_keep_bits(24, 17, 4, M, 4 * D, 0.1, 1234, 5, device="cuda")
     out, lse = ops.mha_fwd(qkv, None, B, T, H, 64, 0.125, keep=keep24[0], p_drop=0.1)
     ops.mha_bwd(qkv, out, do, lse, None, B, T, H, 64, 0.125, keep=keep24[0], p_drop=0.1)
 torch.cuda.synchronize()
