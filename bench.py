@@ -587,9 +587,13 @@ def run_b200(args):
     # the eager path is host bound (Python enqueues a step more slowly than the GPU executes it), which would put the host's
     # time between "record start event" and "launch" into every bracket: park the GPU on a 60 ms spin first, so that the
     # whole step is queued before its first kernel runs and the brackets hold device time only
+    # ... and keep the weight-gradient GEMMs on the main stream for this one step: a bracket around a kernel that shares the
+    # SMs with a kernel of the other stream would count the shared time twice
+    side_was, ops.SIDE_STREAM_ENABLED = ops.SIDE_STREAM_ENABLED, False
     torch.cuda._sleep(int(0.060 * 1.9e9))
     eager_step(resident[0])
     torch.cuda.synchronize()
+    ops.SIDE_STREAM_ENABLED = side_was
     prof, ops.PROFILE = ops.PROFILE, None
     kinds = {}
     for kind, e0, e1, fl in prof:

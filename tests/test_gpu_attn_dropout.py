@@ -187,11 +187,14 @@ def test_polynomial_exp2_share_matches_the_mufu_kernels(B, T, H, klens, share, p
         assert float(g1[:, :, 1:][masked].abs().max()) == 0.0
 
 
-@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, "bf16+activation_keep_bits"])
 @pytest.mark.parametrize("family", ["data2vec_postln", "hubert_stable"])
 def test_all_dropouts_training_step_vs_oracle_given_masks(family, dtype):
     """hidden / activation / feat_proj / final AND attention dropout in one training step: every mask the library drew is
-    read back and replayed by the CPU oracle; loss, logits and all gradients are compared."""
+    read back and replayed by the CPU oracle; loss, logits and all gradients are compared.  (Third variant: the activation
+    dropout's decisions drawn ahead as keep bits, Data2VecAudioModel.activation_keep_bits -- same masks by construction.)"""
+    act_bits = dtype == "bf16+activation_keep_bits"
+    dtype = torch.bfloat16 if act_bits else dtype
     PS = dict(hidden_dropout=0.1, activation_dropout=0.15, feat_proj_dropout=0.05, final_dropout=0.2, attention_dropout=0.2)
     if family == "data2vec_postln":
         cfg, cls = R.ArchConfig.tiny(), M.Data2VecAudioForCTC
@@ -208,9 +211,11 @@ def test_all_dropouts_training_step_vs_oracle_given_masks(family, dtype):
     model.to(DEV).train()
     bb = model.backbone
     bb.dropout_seed = 777
+    bb.activation_keep_bits = act_bits
     b = R.synth_batch(cfg, 3, 8000, seed=177, ragged=True, max_label=12)
     out = model(input_values=b["input_values"].to(DEV), attention_mask=b["attention_mask"].to(DEV), labels=b["labels"].to(DEV))
     out.loss.backward()
+    assert (bb._act_keep is not None) == act_bits
     B, T = out.logits.shape[:2]
     H, d, inter = cfg.num_attention_heads, cfg.hidden_size, cfg.intermediate_size
     seed, ctr = bb.dropout_seed, bb._drop_ctr
