@@ -407,23 +407,35 @@ class PipelinedFedAvg:
             with torch.cuda.stream(comm_stream):
                 if impl != "nccl" and ready is None:
                     self.agg.barrier()   # every client's local update is complete and visible
-                for c, (ev, ranges) in enumerate(zip(self.events, self.chunks)):
+                def landed(c):   # chunk c's average is in place on every rank: refresh its bf16 shadow slice, signal it
+                    for gi, a, b in self.chunks[c]:
+                        fp = self.flats[gi]
+                        if fp.shadow is not None:
+                            ops.cast_from_f32(fp.flat[a:b], torch.bfloat16, out=fp.shadow[a:b])
+                    self.events[c].record(comm_stream)
+
+                merged = ready is not None and impl != "nccl"
+                for c, ranges in enumerate(self.chunks):
                     if ready is not None:
                         comm_stream.wait_event(ready[c])
                         if impl != "nccl":
-                            self.agg.barrier()   # every client has updated chunk c (and chunk c - 1 has landed everywhere)
+                            # ONE barrier between two exchanges: every client has updated chunk c AND every rank's slice of
+                            # chunk c - 1 has landed everywhere
+                            self.agg.barrier()
+                            if c > 0:
+                                landed(c - 1)
                     for gi, a, b in ranges:
                         if impl == "nccl":
                             fedavg_allreduce(self.flats[gi].flat[a:b])
                         else:
                             self.agg.reduce_range(gi, a, b, impl)
-                    if impl != "nccl":
-                        self.agg.barrier()   # every rank's slice of this chunk has landed everywhere
-                    for gi, a, b in ranges:
-                        fp = self.flats[gi]
-                        if fp.shadow is not None:
-                            ops.cast_from_f32(fp.flat[a:b], torch.bfloat16, out=fp.shadow[a:b])
-                    ev.record(comm_stream)
+                    if not merged:
+                        if impl != "nccl":
+                            self.agg.barrier()   # every rank's slice of this chunk has landed everywhere
+                        landed(c)
+                if merged:
+                    self.agg.barrier()
+                    landed(len(self.chunks) - 1)
         finally:
             lib.b200asr_fedavg_set_max_blocks(old)
         for fp in self.flats:
