@@ -152,14 +152,20 @@ def grad_sink(ps):
     return fp.grad[off:nxt], fresh
 
 
-def _wgrad(ps, need, dy, x):
-    """dW = dy^T x for one parameter or several adjacent ones stacked along the output dim."""
+def _wgrad(ps, need, dy, x, side=True):
+    """dW = dy^T x for one parameter or several adjacent ones stacked along the output dim.
+    side=False: on the current stream (the last weight gradient of a block's backward pass, see TAIL_WGRAD_ON_MAIN)."""
     if not need:
         return None
     ps = ps if isinstance(ps, tuple) else (ps,)
     sink, fresh = grad_sink(ps)
     if sink is None:
         return ops.linear_wgrad(dy, x)
+    if not side:
+        if not fresh:
+            ops.join_side_stream()   # the sink's first write may still be in flight on a side stream
+        ops.linear_wgrad(dy, x, out=sink.view(dy.shape[1], x.shape[1]), accumulate=not fresh)
+        return None
     with ops.on_side_stream(dy, x, ordered=not fresh):
         ops.linear_wgrad(dy, x, out=sink.view(dy.shape[1], x.shape[1]), accumulate=not fresh)
     return None
@@ -182,6 +188,11 @@ def _bgrad(ps, need, dy):
 
 
 import os as _os
+# The QKV weight gradient is the last GEMM of a post-LN block's backward pass.  On the side stream it is still running when
+# the block's segment graph ends (graph.GraphedTrainStep cuts there and has to join the side stream): it is therefore
+# issued on the main stream, before the data gradient, and only the bias column sums stay on the side stream.
+# A/B at 8 x 10 s with layerdrop 0.1 (two runs each): 14.204 / 14.209 ms per step against 14.334 / 14.340 ms.
+TAIL_WGRAD_ON_MAIN = _os.environ.get("B200ASR_TAIL_WGRAD_MAIN", "1") != "0"
 # A/B on one B200 (profiles/r01_dropout_bgrad_ab_v17.txt): the fused pass saves 48 launches per step but puts the column
 # sums on the main stream's critical path (14.86-14.90 ms vs 14.79-14.80 ms with the sums on the side stream) -> opt-in.
 FUSED_DROPOUT_BGRAD = _os.environ.get("B200ASR_FUSED_DROPOUT_BGRAD", "0") != "0"
@@ -437,11 +448,16 @@ class EncoderLayerFn(torch.autograd.Function):
         dwo = _wgrad(o_w, wg, ds1, attn)
         dattn = ops.linear_dgrad(ds1, wo)
         dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale)
-        dx = ops.linear_dgrad(dqkv, wqkv, residual=ds1) if ctx.needs_input_grad[0] else None
         dqw = dkw = dvw = dqb = dkb = dvb = None
-        if wg:
+        dbqkv = dwqkv = None
+        if wg and TAIL_WGRAD_ON_MAIN:
             dbqkv = _bgrad((q_b, k_b, v_b), True, dqkv)
-            dwqkv = _wgrad((q_w, k_w, v_w), True, dqkv, x)
+            dwqkv = _wgrad((q_w, k_w, v_w), True, dqkv, x, side=False)
+        dx = ops.linear_dgrad(dqkv, wqkv, residual=ds1) if ctx.needs_input_grad[0] else None
+        if wg:
+            if not TAIL_WGRAD_ON_MAIN:
+                dbqkv = _bgrad((q_b, k_b, v_b), True, dqkv)
+                dwqkv = _wgrad((q_w, k_w, v_w), True, dqkv, x)
             if dwqkv is not None:
                 dqw, dkw, dvw = dwqkv[:d], dwqkv[d:2 * d], dwqkv[2 * d:]
             if dbqkv is not None:
@@ -549,11 +565,16 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
         dwo = _wgrad(o_w, wg, do, attn)
         dattn = ops.linear_dgrad(do, wo)
         dqkv = ops.mha_bwd(qkv, attn, dattn, lse, ctx.klen, B, T, H, dh, scale, keep=keep, p_drop=pt)
-        dx = ops.linear_dgrad(dqkv, wqkv, residual=ds1) if ctx.needs_input_grad[0] else None
         dqw = dkw = dvw = dqb = dkb = dvb = None
-        if wg:
+        dbqkv = dwqkv = None
+        if wg and TAIL_WGRAD_ON_MAIN:
             dbqkv = _bgrad((q_b, k_b, v_b), True, dqkv)
-            dwqkv = _wgrad((q_w, k_w, v_w), True, dqkv, x)
+            dwqkv = _wgrad((q_w, k_w, v_w), True, dqkv, x, side=False)
+        dx = ops.linear_dgrad(dqkv, wqkv, residual=ds1) if ctx.needs_input_grad[0] else None
+        if wg:
+            if not TAIL_WGRAD_ON_MAIN:
+                dbqkv = _bgrad((q_b, k_b, v_b), True, dqkv)
+                dwqkv = _wgrad((q_w, k_w, v_w), True, dqkv, x)
             if dwqkv is not None:
                 dqw, dkw, dvw = dwqkv[:d], dwqkv[d:2 * d], dwqkv[2 * d:]
             if dbqkv is not None:
