@@ -514,14 +514,19 @@ class EncoderLayerDropoutFn(torch.autograd.Function):
     def forward(ctx, x, klen, meta, cache: ShadowCache, drop, *P):
         (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = P
         B, T, H, eps = meta
-        ph, pa, seed, site, ctr, keep, pt, akeep = (tuple(drop) + (None,))[:8]
+        ph, pa, seed, site, ctr, keep, pt, akeep, lazy_keep = (tuple(drop) + (None, None))[:9]
         M, d = x.shape
         dh = d // H
         scale = dh ** -0.5
         wqkv = cache.qkv(q_w, k_w, v_w)
         bqkv = cache.qkv_bias(q_b, k_b, v_b)
         wo, w1s, w2s = cache.weight(o_w), cache.weight(w1), cache.weight(w2)
+        if lazy_keep and keep is not None:   # this block's attention keep bits, drawn on the side stream under the QKV GEMM
+            with ops.on_side_stream(keep, ctr, manual_join=True):
+                ops.attn_dropout_mask(1, B, T, H, pt, seed, site + 3, 4, ctr, out=keep)
         qkv, _ = ops.linear_fwd(x, wqkv, bqkv)
+        if lazy_keep and keep is not None:
+            ops.join_side_stream()
         attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale, keep=keep, p_drop=pt)
         o, _ = ops.linear_fwd(attn, wo, o_b)
         # s1 = x + drop_h(o) and LN1 in one pass (b200asr_layernorm_dropout_fwd)
@@ -742,7 +747,7 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
     def forward(ctx, x, klen, meta, cache: ShadowCache, drop, *P):
         (q_w, q_b, k_w, k_b, v_w, v_b, o_w, o_b, ln1_w, ln1_b, w1, b1, w2, b2, ln2_w, ln2_b) = P
         B, T, H, eps = meta
-        ph, pa, seed, site, ctr, keep, pt, akeep = (tuple(drop) + (None,))[:8]
+        ph, pa, seed, site, ctr, keep, pt, akeep, lazy_keep = (tuple(drop) + (None, None))[:9]
         M, d = x.shape
         dh = d // H
         scale = dh ** -0.5
@@ -750,7 +755,12 @@ class EncoderLayerStableDropoutFn(torch.autograd.Function):
         bqkv = cache.qkv_bias(q_b, k_b, v_b)
         wo, w1s, w2s = cache.weight(o_w), cache.weight(w1), cache.weight(w2)
         n1, _, m1, r1 = ops.layernorm_fwd(x, ln1_w, ln1_b, eps)
+        if lazy_keep and keep is not None:
+            with ops.on_side_stream(keep, ctr, manual_join=True):
+                ops.attn_dropout_mask(1, B, T, H, pt, seed, site + 3, 4, ctr, out=keep)
         qkv, _ = ops.linear_fwd(n1, wqkv, bqkv)
+        if lazy_keep and keep is not None:
+            ops.join_side_stream()
         attn, lse = ops.mha_fwd(qkv, klen, B, T, H, dh, scale, keep=keep, p_drop=pt)
         o, _ = ops.linear_fwd(attn, wo, o_b)
         # s1 = x + drop_h(o) and LN2 in one pass (b200asr_layernorm_dropout_fwd)

@@ -15,6 +15,8 @@ import warnings
 from dataclasses import dataclass
 from typing import List, Optional, Tuple
 
+import os as _os
+
 import torch
 import torch.nn as nn
 
@@ -206,6 +208,9 @@ class Data2VecAudioModel(nn.Module):
         self._drop_ctr = None
         self._attn_keep = None            # keep bits of this forward's attention-probability dropout, one row per block
         self._act_keep = None             # (keep bits of the activation dropout, row pitch), one row per block
+        # opt-in: every block draws its own attention keep bits under its QKV GEMM instead of one launch for all blocks under
+        # the conv stack (A/B on one box, two runs each: 14.36 / 14.41 against 14.31 / 14.33 ms per step -- no gain)
+        self.attn_keep_per_block = _os.environ.get("B200ASR_ATTN_KEEP_PER_BLOCK", "0") != "0"
         self.activation_keep_bits = False  # draw the activation dropout's decisions ahead as bits (measured slower: see below)
         self._segment_recorder = None     # set by graph.GraphedTrainStep while it captures an update with LayerDrop
         self._force_no_layerdrop = False
@@ -281,8 +286,10 @@ class Data2VecAudioModel(nn.Module):
         n = len(self.encoder.layers)
         H = int(self.config.num_attention_heads)
         keep = torch.empty(n, ops.attn_keep_words(B, T, H), dtype=torch.int32, device=self._drop_ctr.device)
-        with ops.on_side_stream(keep, self._drop_ctr, manual_join=True):
-            ops.attn_dropout_mask(n, B, T, H, p, self.dropout_seed, 16 + 3, 4, self._drop_ctr, out=keep)
+        if not self.attn_keep_per_block:
+            with ops.on_side_stream(keep, self._drop_ctr, manual_join=True):
+                ops.attn_dropout_mask(n, B, T, H, p, self.dropout_seed, 16 + 3, 4, self._drop_ctr, out=keep)
+        # (attn_keep_per_block: every block draws its own row at its start, on the side stream under its QKV GEMM)
         self._attn_keep = keep
 
     def _draw_activation_keep(self, rows):
@@ -381,7 +388,8 @@ class Data2VecAudioModel(nn.Module):
                 x = drop_block.apply(x, klen, meta, cache,
                                      (ph, pa, self.dropout_seed, 16 + 4 * li, self._drop_ctr,
                                       None if self._attn_keep is None else self._attn_keep[li], pt,
-                                      None if self._act_keep is None else (self._act_keep[0][li], self._act_keep[1])),
+                                      None if self._act_keep is None else (self._act_keep[0][li], self._act_keep[1]),
+                                      self.attn_keep_per_block),
                                      *layer.params())
             else:
                 x = block.apply(x, klen, meta, cache, *layer.params())
