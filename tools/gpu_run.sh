@@ -38,6 +38,12 @@ for stage in "$@"; do
                # the report itself is too large to travel back (64 MiB limit): export the raw metric page as CSV on the box
                ncu -i /tmp/${TAG}_prof_ops.ncu-rep --page raw --csv > gpurun_out/${TAG}_prof_ops_raw.csv 2> gpurun_out/${TAG}_ncu3_export.log
                echo "ncu export rc=$?";;
+    ncu_gemm_full)  # --set full of the encoder's GEMM shapes, one launch each
+               timeout 300 python tools/gemm_shapes_ncu.py > gpurun_out/${TAG}_ncu_plain4.log 2>&1 &&
+               timeout 900 ncu --profile-from-start off --set full --clock-control none -k regex:gemm_tc_kernel -o /tmp/${TAG}_prof_gemm python tools/gemm_shapes_ncu.py > gpurun_out/${TAG}_ncu4.log 2>&1
+               echo "ncu gemm full rc=$?"
+               ncu -i /tmp/${TAG}_prof_gemm.ncu-rep --page raw --csv > gpurun_out/${TAG}_prof_gemm_raw.csv 2> gpurun_out/${TAG}_ncu4_export.log
+               echo "ncu export rc=$?";;
     *) echo "unknown stage $stage";;
   esac
 done
