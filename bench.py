@@ -365,8 +365,7 @@ def run_b200(args):
         layerwise = world > 1 and not args.no_overlap and not args.no_layerwise
         graphed = GraphedTrainStep(model, opt, resident[0], max_label_len=120, split_conv=(world > 1 and not args.no_overlap),
                                    defer_adamw=(layerwise and not args.no_chunked_adamw),
-                                   per_block_graphs=(layerwise or args.per_block_graphs),
-                                   overlap_norm=not args.no_overlap_norm)
+                                   per_block_graphs=(layerwise or args.per_block_graphs))
     skipped_blocks = [0]
     # N > 1 with per-block graphs: layer-wise FedAvg on a comm stream, each block's graph of the NEXT round waits only for
     # its own parameters (fedavg.PipelinedFedAvg) -- the aggregation hides behind the forward pass
@@ -720,8 +719,6 @@ def main():
     ap.add_argument("--no-symm", action="store_true", help="do not try torch symmetric memory for the flat buffers (CUDA IPC + peer kernel)")
     ap.add_argument("--no-overlap", action="store_true", help="N>1: do not overlap the aggregation with the next round's conv stack")
     ap.add_argument("--nvls-blocks", type=int, default=0, help="cap of the NVLS kernel's grid (0 = full grid)")
-    ap.add_argument("--no-overlap-norm", action="store_true",
-                    help="per-block graphs: take the whole gradient norm after the backward pass instead of block by block under it")
     ap.add_argument("--per-block-graphs", action="store_true",
                     help="cut the captured update at the block boundaries even with layerdrop 0 (measures what the cuts cost)")
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around the timed steps (ncu --profile-from-start off)")

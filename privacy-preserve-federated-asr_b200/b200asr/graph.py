@@ -87,8 +87,7 @@ class GraphedTrainStep:
     next call overwrites.  `last_skipped_layers` holds the blocks LayerDrop skipped in the latest call."""
 
     def __init__(self, model, opt, example_batch: Dict[str, torch.Tensor], max_label_len: Optional[int] = None,
-                 warmup: int = 3, split_conv: bool = False, defer_adamw: bool = False, per_block_graphs: bool = False,
-                 overlap_norm: bool = False):
+                 warmup: int = 3, split_conv: bool = False, defer_adamw: bool = False, per_block_graphs: bool = False):
         """split_conv: capture the frozen conv feature extractor as a graph of its own, replayed by `begin(batch)`; the
         rest of the update is replayed by `finish()`.  The conv stack does not depend on the trainable weights, so a
         federated client can run `begin(next batch)` while the FedAvg of the previous round is still in flight."""
@@ -107,11 +106,6 @@ class GraphedTrainStep:
         self.split_conv = bool(split_conv)
         if (self.segmented or self.split_conv) and self.backbone is None:
             raise ValueError("GraphedTrainStep: LayerDrop needs a model with a `backbone` (Data2VecAudioModel)")
-        # overlap_norm (per-block graphs only): the sum of squares of a block's gradients is taken on a side stream as soon as
-        # the block's backward graph is done, under the backward pass of the next block; the graph's own clip-norm pass then
-        # reads only the non-block gradients instead of all 1.24 GB
-        self.overlap_norm = bool(overlap_norm) and self.segmented and opt.max_grad_norm is not None
-        self._norm_stream = torch.cuda.Stream() if self.overlap_norm else None
         self.static = {k: self._fit(k, v).clone() for k, v in example_batch.items()}
         saved = [t.clone() for t in opt.state_tensors()]
         host = opt.host_state()
@@ -170,9 +164,6 @@ class GraphedTrainStep:
         bb._segment_recorder = rec      # modeling.forward places a SegmentMarkFn before every block and after the last
         bb._force_no_layerdrop = True   # the capture holds every block; the coins are drawn per replay
         try:
-            if self.overlap_norm:
-                self.opt.enable_partial_norm(L, self._block_ranges(L))
-                self.opt._partial_norm_active = True
             with torch.cuda.stream(stream):
                 rec.begin()
                 self.loss = self._body()
@@ -180,7 +171,6 @@ class GraphedTrainStep:
         finally:
             bb._segment_recorder = None
             bb._force_no_layerdrop = False
-            self.opt._partial_norm_active = False
         torch.cuda.current_stream().wait_stream(stream)
         c0 = 1 if self.split_conv else 0
         want = c0 + (2 * L + 3 if self.segmented else 1)
@@ -212,19 +202,6 @@ class GraphedTrainStep:
                     b = fp.offsets[ii[-1]] + (fp.params[ii[-1]].numel() + 3) // 4 * 4
                     slices.append(fp.grad[a:b])
             self.layer_grad_slices.append(slices)
-
-    def _block_ranges(self, L):
-        """Per group, the (start, end) element ranges of the flat buffers that the encoder blocks own."""
-        out = []
-        for g in self.opt.groups:
-            fp, rs = g["fp"], []
-            for l in range(L):
-                tag = f"encoder.layers.{l}."
-                ii = [i for i, n in enumerate(fp.names) if tag in n]
-                if ii:
-                    rs.append((fp.offsets[ii[0]], fp.offsets[ii[-1]] + (fp.params[ii[-1]].numel() + 3) // 4 * 4))
-            out.append(rs)
-        return out
 
     def fedavg_chunk_params(self):
         """fedavg_chunks() in parameter indices: per chunk a list of (group index, first parameter, end parameter)."""
@@ -303,16 +280,8 @@ class GraphedTrainStep:
                 self.bwd_g[l].copy_(self.bwd_g[l + 1])
                 for s in self.layer_grad_slices[l]:         # no gradient: zero for the global norm, idle in AdamW
                     s.zero_()
-                if self.overlap_norm:
-                    self.opt.norm_parts[l:l + 1].zero_()
             else:
                 g[2 + L + (L - 1 - l)].replay()
-                if self.overlap_norm:                       # this block's share of the gradient norm, under the next block's backward
-                    self._norm_stream.wait_stream(main)
-                    with torch.cuda.stream(self._norm_stream):
-                        self.opt.partial_norm(l, self.layer_grad_slices[l])
-        if self.overlap_norm:
-            main.wait_stream(self._norm_stream)
         g[2 + 2 * L].replay()                               # positional conv / projection backward, clip, AdamW
 
     def __call__(self, batch: Dict[str, torch.Tensor]) -> torch.Tensor:

@@ -52,7 +52,6 @@ class FusedAdamW:
         # caller-owned partials + arrival counter of the deterministic sum of squares: two optimizers (two clients on one
         # GPU, a side stream) never share reduction state
         self.sumsq_ws = torch.zeros(int(lib.b200asr_sumsq_workspace_bytes()), dtype=torch.uint8, device=dev)
-        self.norm_parts, self.norm_rest, self._partial_norm_active = None, None, False
 
     def current_lr(self) -> float:
         s = self.step_count
@@ -149,46 +148,10 @@ class FusedAdamW:
     def _clip_norm(self):
         if self.max_grad_norm is None:
             return None
-        if self._partial_norm_active:
-            # graph.GraphedTrainStep(overlap_norm=True): the sums of squares of the encoder blocks' gradient slices were taken
-            # block by block while the backward pass was still running (partial_norm); only the rest is read here
-            self.gnorm_sq.copy_(self.norm_parts.sum().reshape(1))
-            for g, rest in zip(self.groups, self.norm_rest):
-                for a, b in rest:
-                    ops.sumsq_(g["fp"].grad[a:b], self.gnorm_sq, self.sumsq_ws)
-            return self.gnorm_sq
         self.gnorm_sq.zero_()
         for g in self.groups:
             ops.sumsq_(g["fp"].grad, self.gnorm_sq, self.sumsq_ws)
         return self.gnorm_sq
-
-    def enable_partial_norm(self, n_slots: int, covered: Sequence[Sequence[tuple]]):
-        """The global gradient norm in pieces: `n_slots` partial sums of squares (filled by partial_norm, e.g. one per encoder
-        block as soon as its backward pass is done) + one pass over what they do not cover.  covered: per group, the
-        (start, end) element ranges of the flat gradient that the slots account for."""
-        dev = self.gnorm_sq.device
-        self.norm_parts = torch.zeros(int(n_slots), dtype=torch.float32, device=dev)
-        self.norm_ws_side = torch.zeros(int(lib.b200asr_sumsq_workspace_bytes()), dtype=torch.uint8, device=dev)
-        self.norm_rest = []
-        for g, cov in zip(self.groups, covered):
-            rest, pos = [], 0
-            for a, b in sorted(cov):
-                if a < pos:
-                    raise ValueError("enable_partial_norm: overlapping ranges")
-                if a > pos:
-                    rest.append((pos, a))
-                pos = b
-            if pos < g["fp"].numel:
-                rest.append((pos, g["fp"].numel))
-            self.norm_rest.append(rest)
-
-    def partial_norm(self, slot: int, slices: Sequence[torch.Tensor]):
-        """norm_parts[slot] = sum of squares of the given gradient slices, on the current stream (its own workspace: may run
-        next to the main stream's reductions)."""
-        out = self.norm_parts[slot:slot + 1]
-        out.zero_()
-        for sl in slices:
-            ops.sumsq_(sl, out, self.norm_ws_side)
 
     def step(self):
         ops.join_side_stream()
