@@ -497,6 +497,13 @@ int b200asr_sumsq(const float* x, long long n, float* out, void* stream);
 size_t b200asr_sumsq_workspace_bytes(void);
 int b200asr_sumsq_ws(const float* x, long long n, float* out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Frame lengths after the conv feature extractor, `_get_feat_extract_output_lengths` (HF:507-526, centralized/Models.py:249-271):
+ * out[i] = the chain floor((len - k_j) / s_j) + 1 over the n_conv (<= 16) layers applied to lengths[i] (int64, e.g.
+ * attention_mask.sum(-1)); floor division as torch.div(rounding_mode="floor").  conv_kernel / conv_stride are HOST arrays.
+ * One launch instead of three element-wise kernels per layer on the critical path of every training step. */
+int b200asr_conv_out_lengths(const long long* lengths, int* out, int n, const int* conv_kernel, const int* conv_stride,
+                             int n_conv, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

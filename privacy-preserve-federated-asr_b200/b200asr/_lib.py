@@ -115,6 +115,7 @@ SIGNATURES = {
     "b200asr_ipc_export": (i32, [vp, C.c_char_p]),
     "b200asr_ipc_open": (i32, [C.c_char_p, C.POINTER(vp)]),
     "b200asr_ipc_close": (i32, [vp]),
+    "b200asr_conv_out_lengths": (i32, [vp, vp, i32, vp, vp, i32, vp]),
     "b200asr_normalize_pad_workspace_bytes": (sz, [i32, i64]),
     "b200asr_normalize_pad": (i32, [vp, vp, vp, vp, vp, vp, sz, i32, i32, vp, vp, i32, vp]),
     "b200asr_words_from_ids": (i32, [vp, vp, i32, i32, i32, vp, vp, i32, vp]),

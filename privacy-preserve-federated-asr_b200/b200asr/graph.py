@@ -358,8 +358,8 @@ class GraphedInference:
         out = self.model(self.x, self.am)
         klen = None
         if self.am is not None:   # frames beyond an utterance's length are not decoded (HF pads the logits there)
-            from .modeling import conv_out_lengths
-            klen = conv_out_lengths(self.model.config, self.am.sum(-1)).to(torch.int32).contiguous()
+            from .modeling import device_conv_out_lengths
+            klen = device_conv_out_lengths(self.model.config, self.am)
         ids, col, clen = ops.greedy_decode(out.logits, klen, self.blank)
         ops.join_side_stream()
         return out.logits, ids.long(), col, clen

@@ -179,6 +179,15 @@ def conv_out_lengths(config, lengths: torch.Tensor) -> torch.Tensor:
     return lengths
 
 
+def device_conv_out_lengths(config, attention_mask: torch.Tensor) -> torch.Tensor:
+    """int32 frame lengths of a padded batch from its attention mask: conv_out_lengths(attention_mask.sum(-1)) with the
+    whole per-layer chain in one launch (CUDA tensors; anything else takes the torch formula)."""
+    n = attention_mask.sum(-1)
+    if n.is_cuda and len(config.conv_kernel) <= 16:
+        return ops.conv_out_lengths(n.to(torch.int64).contiguous(), list(config.conv_kernel), list(config.conv_stride))
+    return conv_out_lengths(config, n).to(torch.int32).contiguous()
+
+
 class Data2VecAudioModel(nn.Module):
     """`data2vec_audio` sub-module: feature extractor -> projection -> encoder (HF:744-800).  The wav2vec2 / hubert
     sub-classes below switch the positional conv (one weight-normed conv), the conv-stack norm ("group") and the
@@ -343,7 +352,7 @@ class Data2VecAudioModel(nn.Module):
             self._segment_recorder.conv_mark()   # graph capture: the frozen conv stack becomes a graph of its own
         klen = None
         if attention_mask is not None:
-            klen = conv_out_lengths(c, attention_mask.sum(-1)).to(torch.int32).contiguous()
+            klen = device_conv_out_lengths(c, attention_mask)
         fp = self.feature_projection
         eps = float(_cfg(c, "layer_norm_eps", 1e-5))
         fln = getattr(fp, "layer_norm", None)

@@ -241,6 +241,18 @@ def dropout_colsum(x: torch.Tensor, p: float, seed: int, site: int, counter=None
     return y, out
 
 
+def conv_out_lengths(lengths: torch.Tensor, kernels, strides) -> torch.Tensor:
+    """int32 frame lengths after the conv feature extractor for int64 sample counts `lengths` [n] on the device
+    (b200asr_conv_out_lengths: the whole floor((len - k) / s) + 1 chain in one launch)."""
+    assert lengths.is_cuda and lengths.dtype == torch.int64 and lengths.is_contiguous() and len(kernels) == len(strides)
+    out = torch.empty(lengths.numel(), dtype=torch.int32, device=lengths.device)
+    nl = len(kernels)
+    ks = (C.c_int * nl)(*[int(k) for k in kernels])
+    ss = (C.c_int * nl)(*[int(v) for v in strides])
+    check(lib.b200asr_conv_out_lengths(_p(lengths), _p(out), lengths.numel(), ks, ss, nl, _st()), "conv_out_lengths")
+    return out.view(lengths.shape)
+
+
 def mask_frames_(x: torch.Tensor, lengths: torch.Tensor) -> torch.Tensor:
     """x [B, T, C]: zero frames t >= lengths[b] in place."""
     B, T, Cc = x.shape

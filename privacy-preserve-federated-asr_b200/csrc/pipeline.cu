@@ -168,6 +168,24 @@ __global__ void __launch_bounds__(128) edit_distance_kernel(const unsigned long 
     if (lane == 0) dist[b] = d1[n];  // after the last rotation d1 holds diagonal n + m, whose cell i = n is D(n, m)
 }
 
+// floor((len - k) / s) + 1 per conv layer (HF _get_feat_extract_output_lengths with torch.div(rounding_mode="floor")), all
+// layers in one launch instead of three element-wise torch kernels per layer on the step's critical path
+struct ConvGeom {
+    int k[16], s[16], n;
+};
+__global__ void conv_out_lengths_kernel(const long long* __restrict__ in, int* __restrict__ out, int n, ConvGeom g) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    long long l = in[i];
+    for (int j = 0; j < g.n; ++j) {
+        const long long a = l - g.k[j], s = g.s[j];
+        long long q = a / s;
+        if ((a % s != 0) && ((a < 0) != (s < 0))) --q;   // floor, not truncation, for negative numerators
+        l = q + 1;
+    }
+    out[i] = (int)l;
+}
+
 }  // namespace b200asr
 
 using namespace b200asr;
@@ -217,6 +235,21 @@ int b200asr_edit_distance(const unsigned long long* hyp, const int* hyp_len, con
     if (smem > 48 * 1024) cudaFuncSetAttribute(edit_distance_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     edit_distance_kernel<<<ceil_div(B, 4), 128, smem, as_stream(stream)>>>(hyp, hyp_len, ref, ref_len, dist, B, ld_hyp, ld_ref);
     return check_launch("edit_distance");
+}
+
+int b200asr_conv_out_lengths(const long long* lengths, int* out, int n, const int* conv_kernel, const int* conv_stride,
+                             int n_conv, void* stream) {
+    B200_REQUIRE(lengths && out && conv_kernel && conv_stride, "conv_out_lengths: null pointer");
+    B200_REQUIRE(n >= 1 && n_conv >= 1 && n_conv <= 16, "conv_out_lengths: bad n=%d or n_conv=%d (1..16)", n, n_conv);
+    ConvGeom g;
+    g.n = n_conv;
+    for (int j = 0; j < n_conv; ++j) {
+        B200_REQUIRE(conv_stride[j] >= 1 && conv_kernel[j] >= 1, "conv_out_lengths: bad conv geometry at layer %d", j);
+        g.k[j] = conv_kernel[j];
+        g.s[j] = conv_stride[j];
+    }
+    conv_out_lengths_kernel<<<(n + 127) / 128, 128, 0, as_stream(stream)>>>(lengths, out, n, g);
+    return check_launch("conv_out_lengths");
 }
 
 }  // extern "C"

@@ -87,3 +87,19 @@ def test_greedy_decode_to_wer_end_to_end():
     bad[:, 0] = 11  # not a delimiter: the first word of every reference changes
     dist, cnt = data.error_rate(col, clen, bad.cuda(), 4, "word")
     assert (dist.cpu() >= 1).all()
+
+
+def test_conv_out_lengths_kernel_matches_the_torch_chain():
+    """b200asr_conv_out_lengths: the per-layer floor((len - k) / s) + 1 chain of _get_feat_extract_output_lengths in one
+    launch equals modeling.conv_out_lengths (torch.div(rounding_mode="floor")), too-short inputs (negative numerators)
+    included; wired into the model through modeling.device_conv_out_lengths."""
+    from b200asr import modeling as M2
+    from b200asr import ops as O2
+    from oracle import data2vec_ref as R
+    cfg = R.ArchConfig()
+    lens = torch.tensor([160000, 159999, 80000, 400, 399, 25, 10, 9, 1, 0, 480000, 123457], dtype=torch.int64, device="cuda")
+    want = M2.conv_out_lengths(cfg, lens).to(torch.int32)
+    got = O2.conv_out_lengths(lens, list(cfg.conv_kernel), list(cfg.conv_stride))
+    assert got.dtype == torch.int32 and torch.equal(got, want)
+    mask = (torch.arange(2000, device="cuda")[None] < torch.tensor([2000, 1234, 400, 7], device="cuda")[:, None]).long()
+    assert torch.equal(M2.device_conv_out_lengths(cfg, mask), M2.conv_out_lengths(cfg, mask.sum(-1)).to(torch.int32))
